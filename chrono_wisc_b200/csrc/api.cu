@@ -1,0 +1,675 @@
+// api.cu -- the C ABI declared in include/chrono_b200.h: handle management, uploads/downloads, step driver.
+#include "common.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits.h>
+
+namespace cb200 {
+
+thread_local std::string g_last_error;
+int set_error(int code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+
+int timer_start(System* S, const char* name) {
+    Timer& t = S->timers[name];
+    if (!t.a) {
+        CB_CUDA(cudaEventCreate(&t.a));
+        CB_CUDA(cudaEventCreate(&t.b));
+    }
+    CB_CUDA(cudaEventRecord(t.a, S->stream));
+    t.armed = true;
+    return CB200_OK;
+}
+
+int timer_stop(System* S, const char* name) {
+    Timer& t = S->timers[name];
+    if (!t.armed)
+        return CB200_OK;
+    CB_CUDA(cudaEventRecord(t.b, S->stream));
+    CB_CUDA(cudaEventSynchronize(t.b));
+    float ms = 0;
+    CB_CUDA(cudaEventElapsedTime(&ms, t.a, t.b));
+    t.total_ms += ms;
+    t.armed = false;
+    return CB200_OK;
+}
+
+int fetch_counters(System* S) {
+    CB_CUDA(cudaMemcpyAsync(S->h_cnt, S->d_cnt, sizeof(DevCounters), cudaMemcpyDeviceToHost, S->stream));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    return CB200_OK;
+}
+
+template <typename T>
+static int upload(System* S, DevBuf<T>& buf, size_t offset, const T* src, size_t n) {
+    CB_CUDA(cudaMemcpyAsync(buf.p + offset, src, n * sizeof(T), cudaMemcpyHostToDevice, S->stream));
+    return CB200_OK;
+}
+template <typename T>
+static int download(System* S, const T* dev, T* dst, size_t n) {
+    if (n == 0 || !dst)
+        return CB200_OK;
+    CB_CUDA(cudaMemcpyAsync(dst, dev, n * sizeof(T), cudaMemcpyDeviceToHost, S->stream));
+    return CB200_OK;
+}
+
+static int check_step_counters(System* S) {
+    CB_TRY(fetch_counters(S));
+    if (S->h_cnt->overflow)
+        return set_error(CB200_ERR_UNSUPPORTED, "internal capacity exceeded (too many large shapes or heavy bodies)");
+    if (S->h_cnt->unsupported)
+        return set_error(CB200_ERR_UNSUPPORTED,
+                         std::to_string(S->h_cnt->unsupported) +
+                             " candidate pairs have a shape combination this backend cannot test yet");
+    return CB200_OK;
+}
+
+}  // namespace cb200
+
+using namespace cb200;
+
+static System* SYS(cb200_system* s) { return reinterpret_cast<System*>(s); }
+
+extern "C" {
+
+const char* cb200_last_error(void) { return g_last_error.c_str(); }
+
+int cb200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess)
+        return 0;
+    return n;
+}
+
+void cb200_default_settings(cb200_settings* s) {
+    memset(s, 0, sizeof(*s));
+    s->collision_envelope = 0;
+    s->broadphase_grid = 0;
+    s->bins_per_axis[0] = s->bins_per_axis[1] = s->bins_per_axis[2] = 10;
+    s->bin_size[0] = s->bin_size[1] = s->bin_size[2] = 1;
+    s->grid_density = 5;
+    s->narrowphase_algorithm = 2;
+    s->system_type = 0;
+    s->step_size = 0.01;
+    s->contact_force_model = 1;
+    s->adhesion_force_model = 0;
+    s->tangential_displ_mode = 1;
+    s->use_material_properties = 1;
+    s->characteristic_vel = 1;
+    s->min_slip_vel = 1e-4;
+    s->min_roll_vel = 1e-4;
+    s->min_spin_vel = 1e-4;
+    s->solver_type = 0;
+    s->solver_mode = 1;
+    s->max_iteration_normal = 0;
+    s->max_iteration_sliding = 100;
+    s->max_iteration_spinning = 0;
+    s->cache_step_length = 0;
+    s->alpha = .2;
+    s->contact_recovery_speed = .6;
+    s->tolerance = 1e-4;
+    s->deterministic = 1;
+}
+
+int cb200_create(int device, cb200_system** out) {
+    if (!out)
+        return set_error(CB200_ERR_ARG, "null output handle");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return set_error(CB200_ERR_CUDA, std::string("no CUDA device available (this backend has no CPU fallback): ") +
+                                             cudaGetErrorString(e));
+    if (device < 0 || device >= n)
+        return set_error(CB200_ERR_ARG, "device index out of range");
+    CB_CUDA(cudaSetDevice(device));
+    System* S = new System();
+    S->device = device;
+    cb200_default_settings(&S->set);
+    CB_CUDA(cudaStreamCreateWithFlags(&S->stream, cudaStreamNonBlocking));
+    CB_CUDA(cudaMalloc(&S->d_cnt, sizeof(DevCounters)));
+    CB_CUDA(cudaMemset(S->d_cnt, 0, sizeof(DevCounters)));
+    CB_CUDA(cudaMallocHost(&S->h_cnt, sizeof(DevCounters)));
+    memset(S->h_cnt, 0, sizeof(DevCounters));
+    *out = reinterpret_cast<cb200_system*>(S);
+    return CB200_OK;
+}
+
+void cb200_destroy(cb200_system* sys) {
+    System* S = SYS(sys);
+    if (!S)
+        return;
+    cudaSetDevice(S->device);
+    cudaStreamSynchronize(S->stream);
+#define REL(x) S->x.release()
+    REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(bflags); REL(heavy);
+    REL(s_type); REL(s_body); REL(s_fam); REL(s_mat); REL(s_lpos); REL(s_lrot); REL(s_dims); REL(s_wpos); REL(s_wrot);
+    REL(s_bp); REL(mat_smc); REL(mat_nsc); REL(bin_intersections); REL(bin_count); REL(bin_cursor);
+    REL(bin_entries_tmp); REL(bin_entries); REL(large_list); REL(pair_count); REL(pairs); REL(pair_aux);
+    REL(slot_index); REL(pair_nc); REL(t_norm); REL(t_pta); REL(t_ptb); REL(t_depth); REL(t_erad);
+    REL(c_norm); REL(c_pta); REL(c_ptb); REL(c_depth); REL(c_erad); REL(c_bids); REL(c_shapes); REL(c_mats);
+    REL(ct_force); REL(ct_torque); REL(b_deg); REL(b_cursor); REL(b_inc); REL(b_force); REL(heavy_list);
+    REL(heavy_part); REL(n_frame); REL(gamma); REL(n_r); REL(n_E); REL(n_work); REL(n_bodyvec); REL(n_scal);
+    REL(scan_tmp);
+#undef REL
+    for (auto& kv : S->timers) {
+        if (kv.second.a)
+            cudaEventDestroy(kv.second.a);
+        if (kv.second.b)
+            cudaEventDestroy(kv.second.b);
+    }
+    cudaFree(S->d_cnt);
+    cudaFreeHost(S->h_cnt);
+    cudaStreamDestroy(S->stream);
+    delete S;
+}
+
+int cb200_set_settings(cb200_system* sys, const cb200_settings* s) {
+    System* S = SYS(sys);
+    if (!S || !s)
+        return set_error(CB200_ERR_ARG, "null argument");
+    if (!(s->step_size > 0))
+        return set_error(CB200_ERR_ARG, "step_size must be positive");
+    if (s->broadphase_grid < 0 || s->broadphase_grid > 2)
+        return set_error(CB200_ERR_ARG, "broadphase_grid must be 0, 1 or 2");
+    if (s->narrowphase_algorithm < 0 || s->narrowphase_algorithm > 2)
+        return set_error(CB200_ERR_ARG, "narrowphase_algorithm must be 0, 1 or 2");
+    S->set = *s;
+    // ChSystemMulticoreSMC forces a zero envelope every step (MC/physics/ChSystemMulticoreSMC.cpp:27,56-67)
+    if (S->set.system_type == 1)
+        S->set.collision_envelope = 0;
+    return CB200_OK;
+}
+
+int cb200_append_bodies(cb200_system* sys, int n, const double* mass, const double* inertia_xx,
+                        const double* inv_inertia_xx, const char* active, const char* collide, int* first) {
+    System* S = SYS(sys);
+    if (!S || n < 0 || !mass || !inertia_xx)
+        return set_error(CB200_ERR_ARG, "bad argument to cb200_append_bodies");
+    CB_CUDA(cudaSetDevice(S->device));
+    const size_t nb0 = S->nb, nb1 = nb0 + (size_t)n;
+    cudaStream_t st = S->stream;
+    CB_TRY(S->pos.reserve(3 * nb1, true, st));
+    CB_TRY(S->rot.reserve(4 * nb1, true, st));
+    CB_TRY(S->vel.reserve(6 * nb1, true, st));
+    CB_TRY(S->hf.reserve(6 * nb1, true, st));
+    CB_TRY(S->fapp.reserve(6 * nb1, true, st));
+    CB_TRY(S->mass.reserve(nb1, true, st));
+    CB_TRY(S->inertia.reserve(3 * nb1, true, st));
+    CB_TRY(S->inv_inertia.reserve(3 * nb1, true, st));
+    CB_TRY(S->bflags.reserve(nb1, true, st));
+    CB_TRY(S->heavy.reserve(nb1, true, st));
+    std::vector<double> inv(3 * (size_t)n), rot0(4 * (size_t)n, 0.0);
+    std::vector<uint8_t> fl(n);
+    for (int i = 0; i < n; i++) {
+        for (int k = 0; k < 3; k++)
+            inv[3 * i + k] = inv_inertia_xx ? inv_inertia_xx[3 * i + k] : 1.0 / inertia_xx[3 * i + k];
+        rot0[4 * i] = 1.0;
+        fl[i] = (uint8_t)(((!active || active[i]) ? 1 : 0) | ((!collide || collide[i]) ? 2 : 0));
+    }
+    CB_TRY(upload(S, S->mass, nb0, mass, (size_t)n));
+    CB_TRY(upload(S, S->inertia, 3 * nb0, inertia_xx, 3 * (size_t)n));
+    CB_TRY(upload(S, S->inv_inertia, 3 * nb0, inv.data(), 3 * (size_t)n));
+    CB_TRY(upload(S, S->rot, 4 * nb0, rot0.data(), 4 * (size_t)n));
+    CB_TRY(upload(S, S->bflags, nb0, fl.data(), (size_t)n));
+    CB_CUDA(cudaMemsetAsync(S->pos.p + 3 * nb0, 0, 3 * (size_t)n * 8, st));
+    CB_CUDA(cudaMemsetAsync(S->vel.p + 6 * nb0, 0, 6 * (size_t)n * 8, st));
+    CB_CUDA(cudaMemsetAsync(S->hf.p + 6 * nb0, 0, 6 * (size_t)n * 8, st));
+    CB_CUDA(cudaMemsetAsync(S->fapp.p + 6 * nb0, 0, 6 * (size_t)n * 8, st));
+    CB_CUDA(cudaMemsetAsync(S->heavy.p + nb0, 0, (size_t)n, st));
+    CB_CUDA(cudaStreamSynchronize(st));  // host staging buffers go out of scope
+    if (first)
+        *first = (int)nb0;
+    S->nb = (uint32_t)nb1;
+    return CB200_OK;
+}
+
+int cb200_append_shapes(cb200_system* sys, int n, const int32_t* type, const uint32_t* body_id, const int16_t* fam,
+                        const double* pos_local, const double* rot_local, const double* dims,
+                        const int32_t* material_id) {
+    System* S = SYS(sys);
+    if (!S || n < 0 || !type || !body_id || !fam || !pos_local || !rot_local || !dims)
+        return set_error(CB200_ERR_ARG, "bad argument to cb200_append_shapes");
+    CB_CUDA(cudaSetDevice(S->device));
+    for (int i = 0; i < n; i++) {
+        switch (type[i]) {
+            case CB200_SPHERE: case CB200_ELLIPSOID: case CB200_BOX: case CB200_CYLINDER: case CB200_CYLSHELL:
+            case CB200_CAPSULE: case CB200_CONE: case CB200_ROUNDEDBOX: case CB200_ROUNDEDCYL:
+                break;
+            default:
+                return set_error(CB200_ERR_UNSUPPORTED, "shape type " + std::to_string(type[i]) +
+                                                            " (convex hull / triangle mesh) is not supported yet");
+        }
+        if (body_id[i] != UINT_MAX && body_id[i] >= S->nb)
+            return set_error(CB200_ERR_ARG, "shape refers to a body that was not added");
+        if (material_id && (material_id[i] < 0 || material_id[i] > 0xffff))
+            return set_error(CB200_ERR_ARG, "material id out of range");
+    }
+    const size_t ns0 = S->ns, ns1 = ns0 + (size_t)n;
+    cudaStream_t st = S->stream;
+    CB_TRY(S->s_type.reserve(ns1, true, st));
+    CB_TRY(S->s_body.reserve(ns1, true, st));
+    CB_TRY(S->s_fam.reserve(ns1, true, st));
+    CB_TRY(S->s_mat.reserve(ns1, true, st));
+    CB_TRY(S->s_lpos.reserve(3 * ns1, true, st));
+    CB_TRY(S->s_lrot.reserve(4 * ns1, true, st));
+    CB_TRY(S->s_dims.reserve(4 * ns1, true, st));
+    CB_TRY(S->s_wpos.reserve(4 * ns1, true, st));
+    CB_TRY(S->s_wrot.reserve(4 * ns1, true, st));
+    CB_TRY(S->s_bp.reserve(ns1, true, st));
+    std::vector<uint32_t> f(n);
+    std::vector<int32_t> m(n, 0);
+    for (int i = 0; i < n; i++) {
+        f[i] = (uint32_t)(uint16_t)fam[2 * i] | ((uint32_t)(uint16_t)fam[2 * i + 1] << 16);
+        if (material_id)
+            m[i] = material_id[i];
+    }
+    CB_TRY(upload(S, S->s_type, ns0, type, (size_t)n));
+    CB_TRY(upload(S, S->s_body, ns0, body_id, (size_t)n));
+    CB_TRY(upload(S, S->s_fam, ns0, f.data(), (size_t)n));
+    CB_TRY(upload(S, S->s_mat, ns0, m.data(), (size_t)n));
+    CB_TRY(upload(S, S->s_lpos, 3 * ns0, pos_local, 3 * (size_t)n));
+    CB_TRY(upload(S, S->s_lrot, 4 * ns0, rot_local, 4 * (size_t)n));
+    CB_TRY(upload(S, S->s_dims, 4 * ns0, dims, 4 * (size_t)n));
+    CB_CUDA(cudaStreamSynchronize(st));
+    S->ns = (uint32_t)ns1;
+    return CB200_OK;
+}
+
+// Composite of two SMC materials in float, term for term as ChContactMaterialCompositeSMC's constructor
+// (src/chrono/physics/ChContactMaterialSMC.cpp:107-130) with the default composition strategy
+// (src/chrono/physics/ChContactMaterial.h:157-169).
+int cb200_set_materials_smc(cb200_system* sys, int n, const float* t) {
+    System* S = SYS(sys);
+    if (!S || n <= 0 || !t)
+        return set_error(CB200_ERR_ARG, "bad argument to cb200_set_materials_smc");
+    if (n > 1024)
+        return set_error(CB200_ERR_UNSUPPORTED, "more than 1024 distinct materials");
+    CB_CUDA(cudaSetDevice(S->device));
+    std::vector<double> tab((size_t)n * n * SMC_MAT_STRIDE);
+    for (int a = 0; a < n; a++)
+        for (int b = 0; b < n; b++) {
+            const float* m1 = t + 14 * a;
+            const float* m2 = t + 14 * b;
+            const float E1 = m1[0], nu1 = m1[1], E2 = m2[0], nu2 = m2[1];
+            float inv_E = (1 - nu1 * nu1) / E1 + (1 - nu2 * nu2) / E2;
+            float inv_G = 2 * (2 - nu1) * (1 + nu1) / E1 + 2 * (2 - nu2) * (1 + nu2) / E2;
+            float E_eff = 1 / inv_E;
+            float G_eff = 1 / inv_G;
+            double* o = tab.data() + ((size_t)a * n + b) * SMC_MAT_STRIDE;
+            o[0] = std::min<float>(m1[2], m2[2]);            // static friction
+            o[1] = std::min<float>(m1[4], m2[4]);            // rolling
+            o[2] = std::min<float>(m1[5], m2[5]);            // spinning
+            o[3] = E_eff;
+            o[4] = G_eff;
+            o[5] = std::min<float>(m1[7], m2[7]);            // constant adhesion
+            o[6] = std::min<float>(m1[8], m2[8]);            // DMT multiplier
+            o[7] = std::min<float>(m1[9], m2[9]);            // Perko multiplier
+            o[8] = std::min<float>(m1[6], m2[6]);            // restitution
+            o[9] = (float)((m1[10] + m2[10]) / 2);           // kn
+            o[10] = (float)((m1[11] + m2[11]) / 2);          // kt
+            o[11] = (float)((m1[12] + m2[12]) / 2);          // gn
+            o[12] = (float)((m1[13] + m2[13]) / 2);          // gt
+        }
+    CB_TRY(S->mat_smc.reserve(tab.size()));
+    CB_TRY(upload(S, S->mat_smc, 0, tab.data(), tab.size()));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    S->nm_smc = n;
+    return CB200_OK;
+}
+
+// NSC composite (src/chrono/physics/ChContactMaterialNSC.cpp composite ctor): friction/cohesion/restitution by
+// min, compliances by sum; 8 doubles: mu, mu_roll, mu_spin, cohesion, compliance, complianceT, cRoll, cSpin.
+int cb200_set_materials_nsc(cb200_system* sys, int n, const float* t) {
+    System* S = SYS(sys);
+    if (!S || n <= 0 || !t)
+        return set_error(CB200_ERR_ARG, "bad argument to cb200_set_materials_nsc");
+    if (n > 1024)
+        return set_error(CB200_ERR_UNSUPPORTED, "more than 1024 distinct materials");
+    CB_CUDA(cudaSetDevice(S->device));
+    std::vector<double> tab((size_t)n * n * NSC_MAT_STRIDE);
+    for (int a = 0; a < n; a++)
+        for (int b = 0; b < n; b++) {
+            const float* m1 = t + 11 * a;
+            const float* m2 = t + 11 * b;
+            double* o = tab.data() + ((size_t)a * n + b) * NSC_MAT_STRIDE;
+            o[0] = std::min<float>(m1[0], m2[0]);
+            o[1] = std::min<float>(m1[2], m2[2]);
+            o[2] = std::min<float>(m1[3], m2[3]);
+            o[3] = std::min<float>(m1[5], m2[5]);
+            o[4] = (float)(m1[7] + m2[7]);
+            o[5] = (float)(m1[8] + m2[8]);
+            o[6] = (float)(m1[9] + m2[9]);
+            o[7] = (float)(m1[10] + m2[10]);
+        }
+    CB_TRY(S->mat_nsc.reserve(tab.size()));
+    CB_TRY(upload(S, S->mat_nsc, 0, tab.data(), tab.size()));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    S->nm_nsc = n;
+    return CB200_OK;
+}
+
+int cb200_upload_state(cb200_system* sys, int first, int n, const double* pos, const double* rot, const double* vel) {
+    System* S = SYS(sys);
+    if (!S || first < 0 || n < 0 || (uint32_t)(first + n) > S->nb)
+        return set_error(CB200_ERR_ARG, "body range out of bounds");
+    CB_CUDA(cudaSetDevice(S->device));
+    if (pos)
+        CB_TRY(upload(S, S->pos, 3 * (size_t)first, pos, 3 * (size_t)n));
+    if (rot)
+        CB_TRY(upload(S, S->rot, 4 * (size_t)first, rot, 4 * (size_t)n));
+    if (vel)
+        CB_TRY(upload(S, S->vel, 6 * (size_t)first, vel, 6 * (size_t)n));
+    return CB200_OK;
+}
+
+int cb200_upload_applied_forces(cb200_system* sys, int first, int n, const double* ft) {
+    System* S = SYS(sys);
+    if (!S || first < 0 || n < 0 || (uint32_t)(first + n) > S->nb)
+        return set_error(CB200_ERR_ARG, "body range out of bounds");
+    CB_CUDA(cudaSetDevice(S->device));
+    if (!ft) {
+        CB_CUDA(cudaMemsetAsync(S->fapp.p + 6 * (size_t)first, 0, 6 * (size_t)n * 8, S->stream));
+        return CB200_OK;
+    }
+    S->has_fapp = true;
+    return upload(S, S->fapp, 6 * (size_t)first, ft, 6 * (size_t)n);
+}
+
+int cb200_set_body_flags(cb200_system* sys, int first, int n, const char* active, const char* collide) {
+    System* S = SYS(sys);
+    if (!S || first < 0 || n < 0 || (uint32_t)(first + n) > S->nb || !active || !collide)
+        return set_error(CB200_ERR_ARG, "bad argument to cb200_set_body_flags");
+    CB_CUDA(cudaSetDevice(S->device));
+    std::vector<uint8_t> fl(n);
+    for (int i = 0; i < n; i++)
+        fl[i] = (uint8_t)((active[i] ? 1 : 0) | (collide[i] ? 2 : 0));
+    CB_TRY(upload(S, S->bflags, (size_t)first, fl.data(), (size_t)n));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    return CB200_OK;
+}
+
+int cb200_update_forces(cb200_system* sys) {
+    System* S = SYS(sys);
+    CB_CUDA(cudaSetDevice(S->device));
+    return stage_update_forces(S);
+}
+
+int cb200_run_collision(cb200_system* sys, int stages) {
+    System* S = SYS(sys);
+    CB_CUDA(cudaSetDevice(S->device));
+    if (stages & 1)
+        CB_TRY(stage_aabb(S));
+    if (stages & 2)
+        CB_TRY(stage_broadphase(S));
+    if (stages & 4)
+        CB_TRY(stage_narrowphase(S));
+    return CB200_OK;
+}
+
+int cb200_run_solver_smc(cb200_system* sys) {
+    System* S = SYS(sys);
+    CB_CUDA(cudaSetDevice(S->device));
+    return stage_smc(S);
+}
+
+int cb200_run_solver_nsc(cb200_system* sys) {
+    System* S = SYS(sys);
+    CB_CUDA(cudaSetDevice(S->device));
+    return stage_nsc(S);
+}
+
+int cb200_integrate(cb200_system* sys) {
+    System* S = SYS(sys);
+    CB_CUDA(cudaSetDevice(S->device));
+    return stage_integrate(S);
+}
+
+int cb200_do_steps(cb200_system* sys, int nsteps) {
+    System* S = SYS(sys);
+    if (!S || nsteps < 0)
+        return set_error(CB200_ERR_ARG, "bad argument to cb200_do_steps");
+    CB_CUDA(cudaSetDevice(S->device));
+    for (auto& kv : S->timers)
+        kv.second.total_ms = 0;
+    S->timed_steps = nsteps;
+    for (int s = 0; s < nsteps; s++) {
+        CB_TRY(timer_start(S, "step"));
+        CB_TRY(timer_start(S, "update"));
+        CB_TRY(stage_update_forces(S));
+        CB_TRY(timer_stop(S, "update"));
+        CB_TRY(timer_start(S, "collision"));
+        CB_TRY(timer_start(S, "collision_broad"));
+        CB_TRY(stage_aabb(S));
+        CB_TRY(stage_broadphase(S));
+        CB_TRY(timer_stop(S, "collision_broad"));
+        CB_TRY(timer_start(S, "collision_narrow"));
+        CB_TRY(stage_narrowphase(S));
+        CB_TRY(timer_stop(S, "collision_narrow"));
+        CB_TRY(timer_stop(S, "collision"));
+        CB_TRY(timer_start(S, "advance"));
+        if (S->set.system_type == 1)
+            CB_TRY(stage_smc(S));
+        else
+            CB_TRY(stage_nsc(S));
+        CB_TRY(timer_stop(S, "advance"));
+        CB_TRY(timer_start(S, "integrate"));
+        CB_TRY(stage_integrate(S));
+        CB_TRY(timer_stop(S, "integrate"));
+        CB_TRY(timer_stop(S, "step"));
+        CB_TRY(check_step_counters(S));
+    }
+    return CB200_OK;
+}
+
+int cb200_synchronize(cb200_system* sys) {
+    System* S = SYS(sys);
+    CB_CUDA(cudaSetDevice(S->device));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    return CB200_OK;
+}
+
+int cb200_get_counts(cb200_system* sys, cb200_counts* out) {
+    System* S = SYS(sys);
+    if (!S || !out)
+        return set_error(CB200_ERR_ARG, "null argument");
+    CB_CUDA(cudaSetDevice(S->device));
+    CB_TRY(check_step_counters(S));
+    memset(out, 0, sizeof(*out));
+    out->num_bodies = S->nb;
+    out->num_shapes = S->ns;
+    for (int a = 0; a < 3; a++) {
+        out->bins_per_axis[a] = (uint32_t)S->bins[a];
+        out->min_bounding_point[a] = S->origin[a];
+        out->max_bounding_point[a] = S->maxpt[a];
+        out->bin_size[a] = S->bin_size[a];
+    }
+    out->num_bins = S->num_bins;
+    out->num_bin_aabb_intersections = S->n_intersections;
+    out->num_active_bins = S->n_active_bins;
+    out->num_possible_collisions = S->n_pairs;
+    out->num_potential_contacts = S->n_slots;
+    out->num_rigid_contacts = S->n_contacts;
+    out->ct_body_count = S->h_cnt->ct_body_count;
+    out->solver_iterations = S->nsc_iters;
+    out->solver_residual = S->nsc_residual;
+    out->solver_objective = S->nsc_objective;
+    return CB200_OK;
+}
+
+int cb200_download_state(cb200_system* sys, int first, int n, double* pos, double* rot, double* vel) {
+    System* S = SYS(sys);
+    if (!S || first < 0 || n < 0 || (uint32_t)(first + n) > S->nb)
+        return set_error(CB200_ERR_ARG, "body range out of bounds");
+    CB_CUDA(cudaSetDevice(S->device));
+    CB_TRY(download(S, S->pos.p + 3 * (size_t)first, pos, 3 * (size_t)n));
+    CB_TRY(download(S, S->rot.p + 4 * (size_t)first, rot, 4 * (size_t)n));
+    CB_TRY(download(S, S->vel.p + 6 * (size_t)first, vel, 6 * (size_t)n));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    return CB200_OK;
+}
+
+int cb200_download_aabb(cb200_system* sys, double* aabb_min, double* aabb_max) {
+    System* S = SYS(sys);
+    CB_CUDA(cudaSetDevice(S->device));
+    std::vector<ShapeBP> h(S->ns);
+    CB_TRY(download(S, S->s_bp.p, h.data(), (size_t)S->ns));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    for (uint32_t i = 0; i < S->ns; i++)
+        for (int a = 0; a < 3; a++) {
+            if (aabb_min)
+                aabb_min[3 * i + a] = h[i].mn[a];
+            if (aabb_max)
+                aabb_max[3 * i + a] = h[i].mx[a];
+        }
+    return CB200_OK;
+}
+
+int cb200_download_bins(cb200_system* sys, uint32_t* bin_number, uint32_t* bin_aabb_number, uint32_t* bin_active,
+                        uint32_t* bin_start_index) {
+    System* S = SYS(sys);
+    CB_CUDA(cudaSetDevice(S->device));
+    if (S->n_intersections == 0)
+        return CB200_OK;
+    std::vector<uint64_t> packed(S->num_bins + 1);
+    CB_TRY(download(S, S->bin_count.p, packed.data(), packed.size()));
+    CB_TRY(download(S, S->bin_entries.p, bin_aabb_number, (size_t)S->n_intersections));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    uint32_t a = 0;
+    for (uint32_t b = 0; b < S->num_bins; b++) {
+        const uint32_t s = (uint32_t)packed[b], e = (uint32_t)packed[b + 1];
+        if (e == s)
+            continue;
+        if (bin_active)
+            bin_active[a] = b;
+        if (bin_start_index)
+            bin_start_index[a] = s;
+        if (bin_number)
+            for (uint32_t k = s; k < e; k++)
+                bin_number[k] = b;
+        a++;
+    }
+    if (bin_start_index)
+        bin_start_index[a] = S->n_intersections;
+    return CB200_OK;
+}
+
+int cb200_download_pairs(cb200_system* sys, int64_t* pairs) {
+    System* S = SYS(sys);
+    CB_CUDA(cudaSetDevice(S->device));
+    CB_TRY(download(S, S->pairs.p, pairs, (size_t)S->n_pairs));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    return CB200_OK;
+}
+
+int cb200_download_contacts(cb200_system* sys, double* normal, double* pt_a, double* pt_b, double* depth,
+                            double* eff_radius, int32_t* body_ids, int64_t* shape_ids) {
+    System* S = SYS(sys);
+    CB_CUDA(cudaSetDevice(S->device));
+    const size_t nc = S->n_contacts;
+    CB_TRY(download(S, S->c_norm.p, normal, 3 * nc));
+    CB_TRY(download(S, S->c_pta.p, pt_a, 3 * nc));
+    CB_TRY(download(S, S->c_ptb.p, pt_b, 3 * nc));
+    CB_TRY(download(S, S->c_depth.p, depth, nc));
+    CB_TRY(download(S, S->c_erad.p, eff_radius, nc));
+    CB_TRY(download(S, S->c_bids.p, body_ids, 2 * nc));
+    CB_TRY(download(S, S->c_shapes.p, shape_ids, nc));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    return CB200_OK;
+}
+
+int cb200_download_contact_forces(cb200_system* sys, double* ct_force, double* ct_torque) {
+    System* S = SYS(sys);
+    CB_CUDA(cudaSetDevice(S->device));
+    const size_t nc = S->n_contacts;
+    if (nc == 0)
+        return CB200_OK;
+    std::vector<double> f(3 * nc), t(6 * nc);
+    CB_TRY(download(S, S->ct_force.p, f.data(), 3 * nc));
+    CB_TRY(download(S, S->ct_torque.p, t.data(), 6 * nc));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    for (size_t i = 0; i < nc; i++)
+        for (int a = 0; a < 3; a++) {
+            if (ct_force) {
+                ct_force[6 * i + a] = -f[3 * i + a];
+                ct_force[6 * i + 3 + a] = f[3 * i + a];
+            }
+            if (ct_torque) {
+                ct_torque[6 * i + a] = t[6 * i + a];
+                ct_torque[6 * i + 3 + a] = t[6 * i + 3 + a];
+            }
+        }
+    return CB200_OK;
+}
+
+int cb200_download_body_contact_forces(cb200_system* sys, double* force, double* torque) {
+    System* S = SYS(sys);
+    CB_CUDA(cudaSetDevice(S->device));
+    const size_t nb = S->nb;
+    if (nb == 0)
+        return CB200_OK;
+    if (S->b_force.cap < 6 * nb)
+        return set_error(CB200_ERR_STATE, "no SMC solve has run yet");
+    std::vector<double> h(6 * nb);
+    CB_TRY(download(S, S->b_force.p, h.data(), 6 * nb));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    for (size_t b = 0; b < nb; b++)
+        for (int a = 0; a < 3; a++) {
+            if (force)
+                force[3 * b + a] = h[6 * b + a];
+            if (torque)
+                torque[3 * b + a] = h[6 * b + 3 + a];
+        }
+    return CB200_OK;
+}
+
+int cb200_download_hf(cb200_system* sys, double* hf) {
+    System* S = SYS(sys);
+    CB_CUDA(cudaSetDevice(S->device));
+    CB_TRY(download(S, S->hf.p, hf, 6 * (size_t)S->nb));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    return CB200_OK;
+}
+
+int cb200_get_timer(cb200_system* sys, const char* name, double* seconds) {
+    System* S = SYS(sys);
+    if (!S || !name || !seconds)
+        return set_error(CB200_ERR_ARG, "null argument");
+    auto it = S->timers.find(name);
+    if (it == S->timers.end())
+        return set_error(CB200_ERR_ARG, std::string("unknown timer '") + name + "'");
+    *seconds = it->second.total_ms * 1e-3 / (S->timed_steps > 0 ? S->timed_steps : 1);
+    return CB200_OK;
+}
+
+int64_t cb200_kernel_launches(cb200_system* sys) { return SYS(sys)->launches; }
+
+int cb200_device_array(cb200_system* sys, const char* name, void** dev_ptr, int64_t* count) {
+    System* S = SYS(sys);
+    if (!S || !name || !dev_ptr || !count)
+        return set_error(CB200_ERR_ARG, "null argument");
+    const std::string n(name);
+    struct E { const char* k; void* p; int64_t c; };
+    const E tab[] = {
+        {"pos", S->pos.p, 3 * (int64_t)S->nb},           {"rot", S->rot.p, 4 * (int64_t)S->nb},
+        {"vel", S->vel.p, 6 * (int64_t)S->nb},           {"hf", S->hf.p, 6 * (int64_t)S->nb},
+        {"mass", S->mass.p, (int64_t)S->nb},             {"contact_normal", S->c_norm.p, 3 * (int64_t)S->n_contacts},
+        {"contact_pt_a", S->c_pta.p, 3 * (int64_t)S->n_contacts},
+        {"contact_pt_b", S->c_ptb.p, 3 * (int64_t)S->n_contacts},
+        {"contact_depth", S->c_depth.p, (int64_t)S->n_contacts},
+        {"contact_body_ids", S->c_bids.p, 2 * (int64_t)S->n_contacts},
+        {"pair_shape_ids", S->pairs.p, (int64_t)S->n_pairs},
+        {"gamma", S->gamma.p, 3 * (int64_t)S->n_contacts},
+    };
+    for (const E& e : tab)
+        if (n == e.k) {
+            *dev_ptr = e.p;
+            *count = e.c;
+            return CB200_OK;
+        }
+    return set_error(CB200_ERR_ARG, "unknown device array '" + n + "'");
+}
+
+}  // extern "C"

@@ -1,0 +1,111 @@
+// integrate.cu -- per-body force gathering and time integration on the device.
+//
+// Reference path replaced:
+//   ChSystemMulticore::UpdateRigidBodies   MC/physics/ChSystemMulticore.cpp:329-377 with ChBody::Update,
+//       UpdateForces, ComputeGyro, VariablesFbLoadForces (src/chrono/physics/ChBody.cpp:552-594,423-426,247-257)
+//                                                                      -> k_update_forces
+//   scatter + ChBody::VariablesQbIncrementPosition  MC/physics/ChSystemMulticore.cpp:134-153,
+//       src/chrono/physics/ChBody.cpp:288-310                           -> k_integrate
+//
+// The reference walks one heap object per body on the host every step; here the state never leaves the device
+// and both loops are streaming kernels (one thread per body).
+#include "common.cuh"
+#include <float.h>
+
+namespace cb200 {
+
+// hf = h * (m g + F_applied ,  T_applied - w x (J w))
+__global__ void __launch_bounds__(256) k_update_forces(uint32_t nb, double h, d3 g, const double* __restrict__ mass,
+                                                       const double* __restrict__ inertia,
+                                                       const double* __restrict__ vel,
+                                                       const double* __restrict__ fapp /* may be null */,
+                                                       double* __restrict__ hf) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nb)
+        return;
+    const double m = mass[b];
+    const double* v = vel + 6 * (size_t)b;
+    const d3 w = mk3(v[3], v[4], v[5]);
+    // ComputeGyro: gyro = w x (J w), J diagonal in the body frame
+    const d3 Jw = mk3(inertia[3 * b] * w.x, inertia[3 * b + 1] * w.y, inertia[3 * b + 2] * w.z);
+    const d3 gyro = cross3(w, Jw);
+    d3 F = g * m;   // UpdateForces: Xforce = G_acc * mass
+    d3 T = mk3(0);
+    if (fapp) {
+        const double* a = fapp + 6 * (size_t)b;
+        F += mk3(a[0], a[1], a[2]);
+        T += mk3(a[3], a[4], a[5]);
+    }
+    const d3 hF = h * F;
+    const d3 hT = h * (T - gyro);
+    double* o = hf + 6 * (size_t)b;
+    o[0] = hF.x, o[1] = hF.y, o[2] = hF.z, o[3] = hT.x, o[4] = hT.y, o[5] = hT.z;
+}
+
+// x += h v ;  q <- dq(h R w) * q   (ChBody::VariablesQbIncrementPosition), active bodies only
+__global__ void __launch_bounds__(256) k_integrate(uint32_t nb, double h, const uint8_t* __restrict__ bflags,
+                                                   const double* __restrict__ vel, double* __restrict__ pos,
+                                                   double* __restrict__ rot) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nb || !(bflags[b] & 1u))
+        return;
+    const double* v = vel + 6 * (size_t)b;
+    double* p = pos + 3 * (size_t)b;
+    p[0] = p[0] + v[0] * h;
+    p[1] = p[1] + v[1] * h;
+    p[2] = p[2] + v[2] * h;
+
+    const double4 qa = reinterpret_cast<const double4*>(rot)[b];
+    const double e0 = qa.x, e1 = qa.y, e2 = qa.z, e3 = qa.w;
+    // ChMatrix33::SetFromQuaternion (src/chrono/core/ChMatrix33.h:253-274) times the local angular velocity
+    const double e0e0 = e0 * e0, e1e1 = e1 * e1, e2e2 = e2 * e2, e3e3 = e3 * e3;
+    const double e0e1 = e0 * e1, e0e2 = e0 * e2, e0e3 = e0 * e3, e1e2 = e1 * e2, e1e3 = e1 * e3, e2e3 = e2 * e3;
+    const double wx = v[3], wy = v[4], wz = v[5];
+    double ax = ((e0e0 + e1e1) * 2 - 1) * wx + ((e1e2 - e0e3) * 2) * wy + ((e1e3 + e0e2) * 2) * wz;
+    double ay = ((e1e2 + e0e3) * 2) * wx + ((e0e0 + e2e2) * 2 - 1) * wy + ((e2e3 - e0e1) * 2) * wz;
+    double az = ((e1e3 - e0e2) * 2) * wx + ((e2e3 + e0e1) * 2) * wy + ((e0e0 + e3e3) * 2 - 1) * wz;
+    const double len = sqrt(ax * ax + ay * ay + az * az);
+    const double angle = len * h;
+    // ChVector3::Normalize (src/chrono/core/ChVector3.h:873-883)
+    if (len < DBL_MIN) {
+        ax = 1, ay = 0, az = 0;
+    } else {
+        const double s = 1 / len;
+        ax *= s, ay *= s, az *= s;
+    }
+    // SetFromAngleAxis (ChQuaternion.h:1052-1059)
+    const double half = angle / 2;
+    const double sh = sin(half);
+    const double d0 = cos(half), d1 = ax * sh, d2 = ay * sh, d3_ = az * sh;
+    // mdeltarot * moldrot, ChQuaternion::Cross (ChQuaternion.h:891-903)
+    double4 qn;
+    qn.x = d0 * e0 - d1 * e1 - d2 * e2 - d3_ * e3;
+    qn.y = d0 * e1 + d1 * e0 - d3_ * e2 + d2 * e3;
+    qn.z = d0 * e2 + d2 * e0 + d3_ * e1 - d1 * e3;
+    qn.w = d0 * e3 + d3_ * e0 - d2 * e1 + d1 * e2;
+    reinterpret_cast<double4*>(rot)[b] = qn;
+}
+
+int stage_update_forces(System* S) {
+    if (S->nb == 0)
+        return CB200_OK;
+    const d3 g = mk3(S->set.gravity[0], S->set.gravity[1], S->set.gravity[2]);
+    k_update_forces<<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(S->nb, S->set.step_size, g, S->mass.p, S->inertia.p,
+                                                                   S->vel.p, S->has_fapp ? S->fapp.p : nullptr,
+                                                                   S->hf.p);
+    S->launches++;
+    CB_CUDA(cudaGetLastError());
+    return CB200_OK;
+}
+
+int stage_integrate(System* S) {
+    if (S->nb == 0)
+        return CB200_OK;
+    k_integrate<<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(S->nb, S->set.step_size, S->bflags.p, S->vel.p, S->pos.p,
+                                                               S->rot.p);
+    S->launches++;
+    CB_CUDA(cudaGetLastError());
+    return CB200_OK;
+}
+
+}  // namespace cb200

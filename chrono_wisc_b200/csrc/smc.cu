@@ -1,0 +1,528 @@
+// smc.cu -- SMC penalty-contact forces, per-body accumulation and the velocity update.
+//
+// Reference path replaced (MC = src/chrono_multicore):
+//   composite materials      MC/collision/ChContactContainerMulticoreSMC.cpp:123-174 +
+//                            src/chrono/physics/ChContactMaterialSMC.cpp:107-130  -> host table (float math) + lookup
+//   function_CalcContactForces  MC/solver/ChIterativeSolverMulticoreSMC.cpp:56-552 -> k_smc_force
+//   ProcessContacts sort_by_key + reduce_by_key + host_AddContactForces  :653-738   -> body->contact incidence lists
+//                            (counting sort by body) + ordered per-body sums (k_body_reduce), masked block
+//                            reduction for bodies with very many contacts (container walls)
+//   ComputeInvMassMatrix / ComputeImpulses  MC/solver/ChIterativeSolverMulticore.cpp:61-147,
+//                            ...SMC.cpp:854-868                                      -> k_vel_update
+//
+// Summation order: each body adds its contacts in ascending contact index, which is the order the reference's
+// stable sort produces; no floating-point atomics anywhere, so results are run-to-run reproducible.
+#include "common.cuh"
+#include <float.h>
+
+namespace cb200 {
+
+#define CH_PI_D 3.141592653589793238462643383279
+#define CH_2_3_D (2.0 / 3.0)
+
+struct SmcParams {
+    int force_model, adhesion_model, displ_mode, use_mat_props;
+    double char_vel, min_slip_vel, min_roll_vel, min_spin_vel, dT;
+    int nm;
+};
+
+struct BodyView {
+    d3 pos, v, w;
+    q4 rot;
+    double mass;
+};
+
+__device__ __forceinline__ BodyView load_body(uint32_t b, const double* __restrict__ pos,
+                                              const double* __restrict__ rot, const double* __restrict__ vel,
+                                              const double* __restrict__ mass) {
+    BodyView B;
+    B.pos = mk3(pos[3 * b], pos[3 * b + 1], pos[3 * b + 2]);
+    const double4 q = reinterpret_cast<const double4*>(rot)[b];
+    B.rot = mkq(q.x, q.y, q.z, q.w);
+    const double2* v = reinterpret_cast<const double2*>(vel + 6 * (size_t)b);
+    const double2 v0 = v[0], v1 = v[1], v2 = v[2];
+    B.v = mk3(v0.x, v0.y, v1.x);
+    B.w = mk3(v1.y, v2.x, v2.y);
+    B.mass = mass[b];
+    return B;
+}
+
+__global__ void __launch_bounds__(256) k_smc_force(uint32_t nc, SmcParams P, const int32_t* __restrict__ bids,
+                                                   const uint32_t* __restrict__ c_mats,
+                                                   const double* __restrict__ c_norm, const double* __restrict__ c_pta,
+                                                   const double* __restrict__ c_ptb, const double* __restrict__ c_depth,
+                                                   const double* __restrict__ c_erad, const double* __restrict__ pos,
+                                                   const double* __restrict__ rot, const double* __restrict__ vel,
+                                                   const double* __restrict__ mass, const double* __restrict__ mat,
+                                                   double* __restrict__ ct_force, double* __restrict__ ct_torque) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nc)
+        return;
+    d3 force = mk3(0), tq1 = mk3(0), tq2 = mk3(0);
+    const double depth = c_depth[i];
+    if (depth < 0) {
+        const uint32_t b1 = (uint32_t)bids[2 * i], b2 = (uint32_t)bids[2 * i + 1];
+        const BodyView B1 = load_body(b1, pos, rot, vel, mass);
+        const BodyView B2 = load_body(b2, pos, rot, vel, mass);
+        const d3 n = mk3(c_norm[3 * i], c_norm[3 * i + 1], c_norm[3 * i + 2]);
+        const d3 pt1 = mk3(c_pta[3 * i], c_pta[3 * i + 1], c_pta[3 * i + 2]);
+        const d3 pt2 = mk3(c_ptb[3 * i], c_ptb[3 * i + 1], c_ptb[3 * i + 2]);
+        const double erad = c_erad[i];
+
+        // kinematics (:110-135)
+        const d3 pt1_loc = parent_to_local(B1.pos, B1.rot, pt1);
+        const d3 pt2_loc = parent_to_local(B2.pos, B2.rot, pt2);
+        const d3 vel1 = B1.v + rotate(cross3(B1.w, pt1_loc), B1.rot);
+        const d3 vel2 = B2.v + rotate(cross3(B2.w, pt2_loc), B2.rot);
+        const d3 relvel = vel2 - vel1;
+        const double relvel_n_mag = dot3(relvel, n);
+        const d3 relvel_n = relvel_n_mag * n;
+        const d3 relvel_t = relvel - relvel_n;
+        const double relvel_t_mag = length3(relvel_t);
+
+        // composite material (:140-160)
+        const double m_eff = B1.mass * B2.mass / (B1.mass + B2.mass);
+        const uint32_t mm = c_mats[i];
+        const double* M = mat + ((size_t)(mm & 0xffff) * P.nm + (mm >> 16)) * SMC_MAT_STRIDE;
+        const double mu_eff = M[0];
+        double muRoll_eff = M[1], muSpin_eff = M[2];
+        const double E_eff = M[3], G_eff = M[4];
+        const double adhesion_eff = M[5], adhesionMultDMT_eff = M[6], adhesionSPerko_eff = M[7];
+        double cr_eff = M[8];
+        const double user_kn = M[9], user_kt = M[10], user_gn = M[11], user_gt = M[12];
+
+        double kn = 0, kt = 0, gn = 0, gt = 0, kn_simple = 0, gn_simple = 0;
+        const double t_contact = 0;
+        const double delta_n = -depth;
+        d3 delta_t = mk3(0);
+        if (P.displ_mode == 1)
+            delta_t = relvel_t * P.dT;
+        double char_vel = P.char_vel;
+        const double eps = DBL_EPSILON;
+        bool done = false;
+
+        switch (P.force_model) {
+            case 0:  // Hooke (:259-281)
+                if (P.use_mat_props) {
+                    const double tmp_k = (16.0 / 15) * sqrt(erad) * E_eff;
+                    const double v2 = char_vel * char_vel;
+                    double loge = (cr_eff < eps) ? log(eps) : log(cr_eff);
+                    loge = (cr_eff > 1 - eps) ? log(1 - eps) : loge;
+                    const double pl = CH_PI_D / loge;
+                    const double tmp_g = 1 + pl * pl;
+                    kn = tmp_k * pow(m_eff * v2 / tmp_k, 0.2);
+                    kt = kn;
+                    gn = sqrt(4 * m_eff * kn / tmp_g);
+                    gt = gn;
+                } else {
+                    kn = user_kn;
+                    kt = user_kt;
+                    gn = m_eff * user_gn;
+                    gt = m_eff * user_gt;
+                }
+                kn_simple = kn;
+                gn_simple = gn;
+                break;
+            case 1:  // Hertz (:283-306)
+                if (P.use_mat_props) {
+                    const double sqrt_Rd = sqrt(erad * delta_n);
+                    const double Sn = 2 * E_eff * sqrt_Rd;
+                    const double St = 8 * G_eff * sqrt_Rd;
+                    const double loge = (cr_eff < eps) ? log(eps) : log(cr_eff);
+                    const double beta = loge / sqrt(loge * loge + CH_PI_D * CH_PI_D);
+                    kn = CH_2_3_D * Sn;
+                    kt = St;
+                    gn = -2 * sqrt(5.0 / 6) * beta * sqrt(Sn * m_eff);
+                    gt = -2 * sqrt(5.0 / 6) * beta * sqrt(St * m_eff);
+                } else {
+                    const double tmp = erad * sqrt(delta_n);
+                    kn = tmp * user_kn;
+                    kt = tmp * user_kt;
+                    gn = tmp * m_eff * user_gn;
+                    gt = tmp * m_eff * user_gt;
+                }
+                kn_simple = kn / sqrt(delta_n);
+                gn_simple = gn / pow(delta_n, 0.25);
+                break;
+            case 3:  // Flores (:308-334)
+                if (P.use_mat_props) {
+                    const double sqrt_Rd = sqrt(erad * delta_n);
+                    const double Sn = 2 * E_eff * sqrt_Rd;
+                    const double St = 8 * G_eff * sqrt_Rd;
+                    cr_eff = (cr_eff < 0.01) ? 0.01 : cr_eff;
+                    cr_eff = (cr_eff > 1.0 - eps) ? 1.0 - eps : cr_eff;
+                    const double loge = log(cr_eff);
+                    const double beta = loge / sqrt(loge * loge + CH_PI_D * CH_PI_D);
+                    kn = CH_2_3_D * Sn;
+                    kt = CH_2_3_D * St;
+                    gn = 8.0 * (1.0 - cr_eff) * kn * delta_n / (5.0 * cr_eff * char_vel);
+                    gt = -2 * sqrt(5.0 / 6) * beta * sqrt(St * m_eff);
+                } else {
+                    const double tmp = erad * sqrt(delta_n);
+                    kn = tmp * user_kn;
+                    kt = tmp * user_kt;
+                    gn = tmp * m_eff * user_gn * delta_n;
+                    gt = tmp * m_eff * user_gt;
+                }
+                kn_simple = kn / sqrt(delta_n);
+                gn_simple = gn / pow(delta_n, 1.5);
+                break;
+            default:  // PlainCoulomb (:336-438)
+                if (P.use_mat_props) {
+                    const double sqrt_Rd = sqrt(delta_n);
+                    const double Sn = 2 * E_eff * sqrt_Rd;
+                    const double loge = (cr_eff < eps) ? log(eps) : log(cr_eff);
+                    const double beta = loge / sqrt(loge * loge + CH_PI_D * CH_PI_D);
+                    kn = CH_2_3_D * Sn;
+                    gn = -2 * sqrt(5.0 / 6) * beta * sqrt(Sn * m_eff);
+                } else {
+                    const double tmp = sqrt(delta_n);
+                    kn = tmp * user_kn;
+                    gn = tmp * user_gn;
+                }
+                kn_simple = kn / sqrt(delta_n);
+                gn_simple = gn / pow(delta_n, 0.25);
+                kt = 0;
+                gt = 0;
+                {
+                    const double forceN_mag = kn * delta_n - gn * relvel_n_mag;
+                    const double forceT_mag = mu_eff * tanh(5.0 * relvel_t_mag) * forceN_mag;
+                    force = forceN_mag * n;
+                    if (relvel_t_mag >= P.min_slip_vel)
+                        force -= (forceT_mag / relvel_t_mag) * relvel_t;
+                }
+                done = true;
+                break;
+        }
+
+        double forceN_mag = kn * delta_n - gn * relvel_n_mag;
+        if (!done) {
+            // normal + tangential force with Coulomb clamp (:447-475)
+            const d3 forceT_stiff = kt * delta_t;
+            const d3 forceT_damp = gt * relvel_t;
+            d3 forceT = forceT_stiff + forceT_damp;
+            const double forceT_mag = length3(forceT);
+            const double delta_t_mag = length3(delta_t);
+            const double forceT_slide = mu_eff * fabs(forceN_mag);
+            if (forceT_mag > forceT_slide) {
+                if (delta_t_mag > eps) {
+                    const double ratio = forceT_slide / forceT_mag;
+                    forceT *= ratio;
+                } else {
+                    forceT = mk3(0);
+                }
+            }
+            force = forceN_mag * n - forceT;
+        }
+
+        // torques in the body frames (:482-483)
+        const d3 torque1_loc = cross3(pt1_loc, rotate_t(force, B1.rot));
+        const d3 torque2_loc = cross3(pt2_loc, rotate_t(force, B2.rot));
+
+        // rolling / spinning friction only for persistent contacts (:488-530)
+        const double d_coeff = gn_simple / (2.0 * m_eff * sqrt(kn_simple / m_eff));
+        if (d_coeff < 1.0) {
+            const double t_collision = CH_PI_D * sqrt(m_eff / (kn_simple * (1 - d_coeff * d_coeff)));
+            if (t_contact <= t_collision) {
+                muRoll_eff = 0.0;
+                muSpin_eff = 0.0;
+            }
+        }
+        d3 m_roll1 = mk3(0), m_roll2 = mk3(0), m_spin1 = mk3(0), m_spin2 = mk3(0);
+        if (muRoll_eff > eps || muSpin_eff > eps) {
+            const d3 v_rot = rotate(cross3(B2.w, pt2_loc), B2.rot) - rotate(cross3(B1.w, pt1_loc), B1.rot);
+            const d3 rel_o = rotate(B2.w, B2.rot) - rotate(B1.w, B1.rot);
+            if (length3(v_rot) > P.min_roll_vel && muRoll_eff > eps) {
+                m_roll1 = muRoll_eff * cross3(forceN_mag * pt1_loc, rotate_t(v_rot, B1.rot)) / length3(v_rot);
+                m_roll2 = muRoll_eff * cross3(forceN_mag * pt2_loc, rotate_t(v_rot, B2.rot)) / length3(v_rot);
+            }
+            if (length3(rel_o) > P.min_spin_vel && muSpin_eff > eps) {
+                const double r1 = length3(pt1_loc), r2 = length3(pt2_loc);
+                const double xc = (r1 * r1 - r2 * r2) / (2 * (r1 + r2 - delta_n)) + 0.5 * (r1 + r2 - delta_n);
+                double rc = r1 * r1 - xc * xc;
+                rc = (rc < eps) ? eps : sqrt(rc);
+                const d3 fn = forceN_mag * n;
+                m_spin1 = muSpin_eff * rc * rotate_t(dot3(rel_o, fn) * n, B1.rot) / length3(rel_o);
+                m_spin2 = muSpin_eff * rc * rotate_t(dot3(rel_o, fn) * n, B2.rot) / length3(rel_o);
+            }
+        }
+
+        // adhesion is applied after the torques were formed (:533-543)
+        if (P.adhesion_model == 0)
+            force -= adhesion_eff * n;
+        else if (P.adhesion_model == 1)
+            force -= adhesionMultDMT_eff * sqrt(erad) * n;
+        else
+            force -= adhesionSPerko_eff * erad * n;
+
+        tq1 = -torque1_loc + m_roll1 + m_spin1;
+        tq2 = torque2_loc - m_roll2 - m_spin2;
+    }
+    ct_force[3 * i] = force.x, ct_force[3 * i + 1] = force.y, ct_force[3 * i + 2] = force.z;
+    double* t = ct_torque + 6 * (size_t)i;
+    t[0] = tq1.x, t[1] = tq1.y, t[2] = tq1.z, t[3] = tq2.x, t[4] = tq2.y, t[5] = tq2.z;
+}
+
+// ---- body -> contact incidence lists (counting sort by body id) ------------------------------------------------
+__global__ void __launch_bounds__(256) k_inc_count(uint32_t nc, const int32_t* __restrict__ bids,
+                                                   const uint8_t* __restrict__ heavy, uint32_t* __restrict__ deg) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nc)
+        return;
+    const uint32_t b1 = (uint32_t)bids[2 * i], b2 = (uint32_t)bids[2 * i + 1];
+    if (!heavy[b1])
+        atomicAdd(&deg[b1], 1u);
+    if (!heavy[b2])
+        atomicAdd(&deg[b2], 1u);
+}
+
+__global__ void __launch_bounds__(256) k_inc_fill(uint32_t nc, const int32_t* __restrict__ bids,
+                                                  const uint8_t* __restrict__ heavy, const uint32_t* __restrict__ off,
+                                                  uint32_t* __restrict__ cursor, uint32_t* __restrict__ inc) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nc)
+        return;
+    const uint32_t b1 = (uint32_t)bids[2 * i], b2 = (uint32_t)bids[2 * i + 1];
+    if (!heavy[b1])
+        inc[off[b1] + atomicAdd(&cursor[b1], 1u)] = i << 1;
+    if (!heavy[b2])
+        inc[off[b2] + atomicAdd(&cursor[b2], 1u)] = (i << 1) | 1u;
+}
+
+// one thread per body: add the body's contacts in ascending contact index, then hf += h * (F, T)
+__global__ void __launch_bounds__(256) k_body_reduce(uint32_t nb, const uint8_t* __restrict__ heavy,
+                                                     const uint32_t* __restrict__ off, const uint32_t* __restrict__ inc,
+                                                     const double* __restrict__ ct_force,
+                                                     const double* __restrict__ ct_torque, double h,
+                                                     double* __restrict__ b_force, double* __restrict__ hf,
+                                                     DevCounters* __restrict__ cnt) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    bool touched = false;
+    if (b < nb && !heavy[b]) {
+        const uint32_t s = off[b], d = off[b + 1] - s;
+        d3 F = mk3(0), T = mk3(0);
+        // selection walk: next smallest code each round (d is ~6..12 for sphere beds; lists sit in L1)
+        uint32_t last = 0;
+        for (uint32_t r = 0; r < d; r++) {
+            uint32_t best = 0xffffffffu;
+            for (uint32_t k = 0; k < d; k++) {
+                const uint32_t c = inc[s + k];
+                if ((r == 0 || c > last) && c < best)
+                    best = c;
+            }
+            last = best;
+            const uint32_t ci = best >> 1, side = best & 1u;
+            const d3 f = mk3(ct_force[3 * ci], ct_force[3 * ci + 1], ct_force[3 * ci + 2]);
+            const double* t = ct_torque + 6 * (size_t)ci + 3 * side;
+            if (r == 0) {
+                F = side ? f : -f;
+                T = mk3(t[0], t[1], t[2]);
+            } else {
+                F = F + (side ? f : -f);
+                T = T + mk3(t[0], t[1], t[2]);
+            }
+        }
+        double* o = b_force + 6 * (size_t)b;
+        o[0] = F.x, o[1] = F.y, o[2] = F.z, o[3] = T.x, o[4] = T.y, o[5] = T.z;
+        if (d) {
+            touched = true;
+            const d3 hF = h * F, hT = h * T;
+            double* q = hf + 6 * (size_t)b;
+            q[0] += hF.x, q[1] += hF.y, q[2] += hF.z, q[3] += hT.x, q[4] += hT.y, q[5] += hT.z;
+        }
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, touched);
+    if (m && (threadIdx.x & 31) == 0)
+        atomicAdd(&cnt->ct_body_count, (uint32_t)__popc(m));
+}
+
+__global__ void __launch_bounds__(256) k_heavy_list(uint32_t nb, const uint8_t* __restrict__ heavy,
+                                                    uint32_t* __restrict__ list, DevCounters* __restrict__ cnt) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < nb && heavy[b]) {
+        const uint32_t k = atomicAdd(&cnt->n_heavy, 1u);
+        if (k < MAX_HEAVY)
+            list[k] = b;
+        else
+            cnt->overflow = 1;
+    }
+}
+
+// Bodies with very many contacts (a container touching 10^5 spheres): fixed-shape masked reduction over the whole
+// contact list.  Chunk -> CTA mapping and the in-CTA tree are fixed, hence deterministic.
+constexpr int HEAVY_CHUNK = 4096;
+__global__ void __launch_bounds__(256) k_heavy_partial(uint32_t nc, const int32_t* __restrict__ bids,
+                                                       const double* __restrict__ ct_force,
+                                                       const double* __restrict__ ct_torque,
+                                                       const uint32_t* __restrict__ list,
+                                                       const DevCounters* __restrict__ cnt, uint32_t nchunks,
+                                                       double* __restrict__ part) {
+    __shared__ double sm[8][7];
+    const uint32_t nh = min(cnt->n_heavy, (uint32_t)MAX_HEAVY);
+    for (uint32_t hI = blockIdx.y; hI < nh; hI += gridDim.y) {
+        const uint32_t body = list[hI];
+        double acc[7] = {0, 0, 0, 0, 0, 0, 0};
+        const uint32_t c0 = blockIdx.x * HEAVY_CHUNK;
+        for (int k = 0; k < HEAVY_CHUNK / 256; k++) {
+            const uint32_t c = c0 + k * 256 + threadIdx.x;
+            if (c < nc) {
+                const uint32_t b1 = (uint32_t)bids[2 * c], b2 = (uint32_t)bids[2 * c + 1];
+                if (b1 == body) {
+                    acc[0] -= ct_force[3 * c], acc[1] -= ct_force[3 * c + 1], acc[2] -= ct_force[3 * c + 2];
+                    const double* t = ct_torque + 6 * (size_t)c;
+                    acc[3] += t[0], acc[4] += t[1], acc[5] += t[2];
+                    acc[6] += 1;
+                }
+                if (b2 == body) {
+                    acc[0] += ct_force[3 * c], acc[1] += ct_force[3 * c + 1], acc[2] += ct_force[3 * c + 2];
+                    const double* t = ct_torque + 6 * (size_t)c + 3;
+                    acc[3] += t[0], acc[4] += t[1], acc[5] += t[2];
+                    acc[6] += 1;
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < 7; q++)
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1)
+                acc[q] += __shfl_down_sync(0xffffffffu, acc[q], d);
+        const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+        if (lane == 0)
+            for (int q = 0; q < 7; q++)
+                sm[wid][q] = acc[q];
+        __syncthreads();
+        if (threadIdx.x < 7) {
+            double s = sm[0][threadIdx.x];
+            for (int w = 1; w < 8; w++)
+                s += sm[w][threadIdx.x];
+            part[((size_t)hI * nchunks + blockIdx.x) * 7 + threadIdx.x] = s;
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256) k_heavy_final(const uint32_t* __restrict__ list,
+                                                     const DevCounters* __restrict__ cnt_in, uint32_t nchunks,
+                                                     const double* __restrict__ part, double h,
+                                                     double* __restrict__ b_force, double* __restrict__ hf,
+                                                     DevCounters* __restrict__ cnt) {
+    __shared__ double sm[8][7];
+    const uint32_t nh = min(cnt_in->n_heavy, (uint32_t)MAX_HEAVY);
+    const uint32_t hI = blockIdx.x;
+    if (hI >= nh)
+        return;
+    double acc[7] = {0, 0, 0, 0, 0, 0, 0};
+    for (uint32_t k = threadIdx.x; k < nchunks; k += 256)
+        for (int q = 0; q < 7; q++)
+            acc[q] += part[((size_t)hI * nchunks + k) * 7 + q];
+#pragma unroll
+    for (int q = 0; q < 7; q++)
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1)
+            acc[q] += __shfl_down_sync(0xffffffffu, acc[q], d);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0)
+        for (int q = 0; q < 7; q++)
+            sm[wid][q] = acc[q];
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s[7];
+        for (int q = 0; q < 7; q++) {
+            s[q] = sm[0][q];
+            for (int w = 1; w < 8; w++)
+                s[q] += sm[w][q];
+        }
+        const uint32_t body = list[hI];
+        double* o = b_force + 6 * (size_t)body;
+        double* f = hf + 6 * (size_t)body;
+        for (int q = 0; q < 6; q++) {
+            o[q] = s[q];
+            if (s[6] > 0)
+                f[q] += h * s[q];
+        }
+        if (s[6] > 0)
+            atomicAdd(&cnt->ct_body_count, 1u);
+    }
+}
+
+// M_invk = v + M_inv * hf for active bodies (rows of inactive bodies do not exist)
+__global__ void __launch_bounds__(256) k_vel_update(uint32_t nb, const uint8_t* __restrict__ bflags,
+                                                    const double* __restrict__ mass,
+                                                    const double* __restrict__ inv_inertia,
+                                                    const double* __restrict__ hf, double* __restrict__ vel) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nb || !(bflags[b] & 1u))
+        return;
+    const double inv_mass = 1.0 / mass[b];
+    const double* f = hf + 6 * (size_t)b;
+    double* v = vel + 6 * (size_t)b;
+    v[0] = v[0] + inv_mass * f[0];
+    v[1] = v[1] + inv_mass * f[1];
+    v[2] = v[2] + inv_mass * f[2];
+    v[3] = v[3] + inv_inertia[3 * b] * f[3];
+    v[4] = v[4] + inv_inertia[3 * b + 1] * f[4];
+    v[5] = v[5] + inv_inertia[3 * b + 2] * f[5];
+}
+
+int stage_smc(System* S) {
+    if (S->nb == 0)
+        return CB200_OK;
+    const uint32_t nc = S->n_contacts, nb = S->nb;
+    const cb200_settings& st = S->set;
+    if (st.tangential_displ_mode == 2)
+        return set_error(CB200_ERR_UNSUPPORTED, "MultiStep tangential displacement history is not implemented");
+    CB_TRY(S->b_force.reserve(6 * (size_t)nb));
+    if (nc > 0) {
+        if (S->nm_smc == 0)
+            return set_error(CB200_ERR_STATE, "cb200_set_materials_smc was not called");
+        SmcParams P;
+        P.force_model = st.contact_force_model;
+        P.adhesion_model = st.adhesion_force_model;
+        P.displ_mode = st.tangential_displ_mode;
+        P.use_mat_props = st.use_material_properties;
+        P.char_vel = st.characteristic_vel;
+        P.min_slip_vel = st.min_slip_vel;
+        P.min_roll_vel = st.min_roll_vel;
+        P.min_spin_vel = st.min_spin_vel;
+        P.dT = st.step_size;
+        P.nm = S->nm_smc;
+        CB_TRY(S->ct_force.reserve(3 * (size_t)nc));
+        CB_TRY(S->ct_torque.reserve(6 * (size_t)nc));
+        CB_TRY(S->b_deg.reserve(nb + 1));
+        CB_TRY(S->b_cursor.reserve(nb));
+        CB_TRY(S->b_inc.reserve(2 * (size_t)nc));
+        CB_TRY(S->heavy_list.reserve(MAX_HEAVY));
+        const uint32_t nchunks = (nc + HEAVY_CHUNK - 1) / HEAVY_CHUNK;
+        CB_TRY(S->heavy_part.reserve((size_t)MAX_HEAVY * nchunks * 7));
+
+        k_smc_force<<<blocks_for(nc, 256), 256, 0, S->stream>>>(nc, P, S->c_bids.p, S->c_mats.p, S->c_norm.p,
+                                                                S->c_pta.p, S->c_ptb.p, S->c_depth.p, S->c_erad.p,
+                                                                S->pos.p, S->rot.p, S->vel.p, S->mass.p, S->mat_smc.p,
+                                                                S->ct_force.p, S->ct_torque.p);
+        CB_CUDA(cudaMemsetAsync(S->b_deg.p, 0, (size_t)(nb + 1) * 4, S->stream));
+        CB_CUDA(cudaMemsetAsync(S->b_cursor.p, 0, (size_t)nb * 4, S->stream));
+        k_inc_count<<<blocks_for(nc, 256), 256, 0, S->stream>>>(nc, S->c_bids.p, S->heavy.p, S->b_deg.p);
+        S->launches += 2;
+        CB_TRY(scan_u32(S, S->b_deg.p, S->b_deg.p, nb));
+        k_inc_fill<<<blocks_for(nc, 256), 256, 0, S->stream>>>(nc, S->c_bids.p, S->heavy.p, S->b_deg.p, S->b_cursor.p,
+                                                               S->b_inc.p);
+        k_heavy_list<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->heavy.p, S->heavy_list.p, S->d_cnt);
+        k_body_reduce<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->heavy.p, S->b_deg.p, S->b_inc.p,
+                                                                  S->ct_force.p, S->ct_torque.p, st.step_size,
+                                                                  S->b_force.p, S->hf.p, S->d_cnt);
+        k_heavy_partial<<<dim3(nchunks, 4), 256, 0, S->stream>>>(nc, S->c_bids.p, S->ct_force.p, S->ct_torque.p,
+                                                                 S->heavy_list.p, S->d_cnt, nchunks, S->heavy_part.p);
+        k_heavy_final<<<MAX_HEAVY, 256, 0, S->stream>>>(S->heavy_list.p, S->d_cnt, nchunks, S->heavy_part.p,
+                                                        st.step_size, S->b_force.p, S->hf.p, S->d_cnt);
+        S->launches += 5;
+    } else {
+        CB_CUDA(cudaMemsetAsync(S->b_force.p, 0, 6 * (size_t)nb * 8, S->stream));
+    }
+    k_vel_update<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->bflags.p, S->mass.p, S->inv_inertia.p, S->hf.p,
+                                                             S->vel.p);
+    S->launches++;
+    CB_CUDA(cudaGetLastError());
+    return CB200_OK;
+}
+
+}  // namespace cb200

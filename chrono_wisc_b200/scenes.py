@@ -1,0 +1,207 @@
+"""Synthetic scenes for the configurations named in BASELINE.json, as plain numpy arrays.
+
+A scene is a dict with body arrays (``mass, inertia, pos, rot, vel, active, collide``), shape arrays in the
+reference's ``shape_container`` layout (``shape_type, shape_body, shape_dims, shape_pos, shape_rot, shape_fam,
+shape_mat``), a material table and a ``settings`` dict whose keys are ``cb200_settings`` fields.  The same dict
+feeds the CUDA backend (``system.load_scene``), the CPU oracle and the reference build, so all three start from
+identical bits.
+"""
+import numpy as np
+
+from .system import (BOX, CAPSULE, SPHERE, FIXED_DENSITY, FIXED_RESOLUTION, HERTZ, HYBRID, MODE_SLIDING,
+                     SOLVER_APGD)
+
+SMC_MAT_FIELDS = ("young_modulus", "poisson_ratio", "static_friction", "sliding_friction", "rolling_friction",
+                  "spinning_friction", "restitution", "constant_adhesion", "adhesionMultDMT", "adhesionSPerko",
+                  "kn", "kt", "gn", "gt")
+NSC_MAT_FIELDS = ("static_friction", "sliding_friction", "rolling_friction", "spinning_friction", "restitution",
+                  "cohesion", "dampingf", "compliance", "complianceT", "complianceRoll", "complianceSpin")
+
+
+def smc_material(young=2e5, poisson=0.3, friction=0.6, restitution=0.4, adhesion=0.0, rolling=0.0, spinning=0.0,
+                 kn=2e5, kt=2e5, gn=40.0, gt=20.0, dmt=0.0, perko=0.0):
+    """One row of the SMC material table; defaults of ChContactMaterialSMC
+    (src/chrono/physics/ChContactMaterialSMC.cpp:27-37, ChContactMaterial.cpp:32)."""
+    return np.array([young, poisson, friction, friction, rolling, spinning, restitution, adhesion, dmt, perko, kn, kt,
+                     gn, gt], dtype=np.float32)
+
+
+def nsc_material(friction=0.6, restitution=0.4, cohesion=0.0, rolling=0.0, spinning=0.0, dampingf=0.0,
+                 compliance=0.0, complianceT=0.0, complianceRoll=0.0, complianceSpin=0.0):
+    return np.array([friction, friction, rolling, spinning, restitution, cohesion, dampingf, compliance, complianceT,
+                     complianceRoll, complianceSpin], dtype=np.float32)
+
+
+class SceneBuilder:
+    def __init__(self):
+        self.mass, self.inertia, self.pos, self.rot, self.vel, self.active, self.collide = [], [], [], [], [], [], []
+        self.s_type, self.s_body, self.s_dims, self.s_pos, self.s_rot, self.s_fam, self.s_mat = [], [], [], [], [], [], []
+        self.nb = 0
+
+    def add_bodies(self, mass, inertia, pos, rot=None, vel=None, active=1, collide=1):
+        pos = np.atleast_2d(np.asarray(pos, dtype=np.float64))
+        n = pos.shape[0]
+        mass = np.broadcast_to(np.asarray(mass, dtype=np.float64), (n,))
+        inertia = np.broadcast_to(np.asarray(inertia, dtype=np.float64), (n, 3))
+        if rot is None:
+            rot = np.tile([1.0, 0, 0, 0], (n, 1))
+        if vel is None:
+            vel = np.zeros((n, 6))
+        first = self.nb
+        self.mass.append(mass), self.inertia.append(inertia), self.pos.append(pos)
+        self.rot.append(np.asarray(rot, dtype=np.float64).reshape(n, 4))
+        self.vel.append(np.asarray(vel, dtype=np.float64).reshape(n, 6))
+        self.active.append(np.full(n, active, dtype=np.int8)), self.collide.append(np.full(n, collide, dtype=np.int8))
+        self.nb += n
+        return first
+
+    def add_shapes(self, type, body, dims, pos=None, rot=None, fam=(1, 0x7FFF), mat=0):
+        body = np.atleast_1d(np.asarray(body, dtype=np.uint32))
+        n = body.size
+        d = np.zeros((n, 4))
+        dims = np.atleast_2d(np.asarray(dims, dtype=np.float64))
+        dims = np.broadcast_to(dims, (n, dims.shape[1]))
+        d[:, :dims.shape[1]] = dims
+        self.s_type.append(np.broadcast_to(np.asarray(type, dtype=np.int32), (n,)))
+        self.s_body.append(body), self.s_dims.append(d)
+        self.s_pos.append(np.zeros((n, 3)) if pos is None else np.asarray(pos, dtype=np.float64).reshape(n, 3))
+        self.s_rot.append(np.tile([1.0, 0, 0, 0], (n, 1)) if rot is None else np.asarray(rot, dtype=np.float64).reshape(n, 4))
+        self.s_fam.append(np.broadcast_to(np.asarray(fam, dtype=np.int16), (n, 2)))
+        self.s_mat.append(np.broadcast_to(np.asarray(mat, dtype=np.int32), (n,)))
+
+    def add_box_container(self, body, center, size, thickness, faces=(2, 2, -1), mat=0):
+        """utils::AddBoxContainer (src/chrono/utils/ChUtilsCreators.cpp:559-615): walls are boxes attached to `body`;
+        order Z-, Z+, X-, X+, Y-, Y+ as in the reference."""
+        sx, sy, sz = size
+        hx, hy, hz, ht = sx / 2, sy / 2, sz / 2, thickness / 2
+        c = np.asarray(center, dtype=np.float64)
+        walls = []
+        if faces[2] in (-1, 2):
+            walls.append(((0, 0, -hz - ht), (sx / 2, sy / 2, ht)))
+        if faces[2] in (1, 2):
+            walls.append(((0, 0, hz + ht), (sx / 2, sy / 2, ht)))
+        if faces[0] in (-1, 2):
+            walls.append(((-hx - ht, 0, 0), (ht, sy / 2, sz / 2)))
+        if faces[0] in (1, 2):
+            walls.append(((hx + ht, 0, 0), (ht, sy / 2, sz / 2)))
+        if faces[1] in (-1, 2):
+            walls.append(((0, -hy - ht, 0), (sx / 2, ht, sz / 2)))
+        if faces[1] in (1, 2):
+            walls.append(((0, hy + ht, 0), (sx / 2, ht, sz / 2)))
+        for p, h in walls:
+            self.add_shapes(BOX, [body], np.array([h]), pos=[c + np.asarray(p)], mat=mat)
+
+    def finish(self, materials, settings):
+        cat = np.concatenate
+        return dict(
+            mass=cat(self.mass), inertia=cat(self.inertia), pos=cat(self.pos), rot=cat(self.rot), vel=cat(self.vel),
+            active=cat(self.active), collide=cat(self.collide), shape_type=cat(self.s_type).astype(np.int32),
+            shape_body=cat(self.s_body).astype(np.uint32), shape_dims=cat(self.s_dims), shape_pos=cat(self.s_pos),
+            shape_rot=cat(self.s_rot), shape_fam=cat(self.s_fam).astype(np.int16),
+            shape_mat=cat(self.s_mat).astype(np.int32), materials=np.atleast_2d(np.asarray(materials, np.float32)),
+            settings=dict(settings))
+
+
+def lattice_positions(nx, ny, nz, spacing, jitter, z0, seed):
+    """nx*ny*nz sphere centres on a jittered lattice centred on the z axis; x fastest, then y, then z."""
+    rng = np.random.Generator(np.random.MT19937(seed))
+    ix, iy, iz = np.meshgrid(np.arange(nx), np.arange(ny), np.arange(nz), indexing="ij")
+    p = np.stack([ix.transpose(2, 1, 0).ravel(), iy.transpose(2, 1, 0).ravel(), iz.transpose(2, 1, 0).ravel()], 1)
+    p = p.astype(np.float64)
+    p[:, 0] = (p[:, 0] - (nx - 1) / 2) * spacing
+    p[:, 1] = (p[:, 1] - (ny - 1) / 2) * spacing
+    p[:, 2] = z0 + p[:, 2] * spacing
+    p += rng.uniform(-jitter, jitter, size=p.shape)
+    return p
+
+
+def settling_smc(nx=32, ny=32, nz=8, radius=0.02, seed=12345, grid="density", bins=(10, 10, 1), step=1e-3,
+                 young=2e6, mu=0.4, cr=0.4, rho=2000.0, spacing_factor=2.02, jitter_factor=0.005, wall_thickness=0.2):
+    """SMC Hertz settling of monodisperse spheres in an open box (configs A/B/C of BASELINE.json; scene after
+    src/tests/benchmark_tests/multicore/btest_MCORE_settling.cpp:59-131 with a jittered lattice instead of the
+    Poisson-disk sampler).  1M spheres = settling_smc(250, 250, 16)."""
+    b = SceneBuilder()
+    spacing = spacing_factor * radius
+    sx = nx * spacing + 2 * radius * 0.5
+    sy = ny * spacing + 2 * radius * 0.5
+    sz = max(1.0, (nz + 2) * spacing)
+    bin_body = b.add_bodies(1.0, (1.0, 1.0, 1.0), [[0.0, 0.0, 0.0]], active=0, collide=1)
+    b.add_box_container(bin_body, (0, 0, sz / 2), (sx, sy, sz), wall_thickness, faces=(2, 2, -1))
+    m = rho * 4.0 / 3.0 * np.pi * radius ** 3
+    inertia = 0.4 * m * radius * radius
+    pos = lattice_positions(nx, ny, nz, spacing, jitter_factor * radius, 1.01 * radius, seed)
+    first = b.add_bodies(m, (inertia, inertia, inertia), pos)
+    n = pos.shape[0]
+    b.add_shapes(SPHERE, np.arange(first, first + n), np.full((n, 1), radius))
+    settings = dict(system_type=1, step_size=step, gravity=(0.0, 0.0, -9.81), contact_force_model=HERTZ,
+                    adhesion_force_model=0, tangential_displ_mode=1, use_material_properties=1,
+                    narrowphase_algorithm=HYBRID, collision_envelope=0.0)
+    if grid == "density":
+        settings.update(broadphase_grid=FIXED_DENSITY, grid_density=5.0)
+    else:
+        settings.update(broadphase_grid=FIXED_RESOLUTION, bins_per_axis=tuple(bins))
+    return b.finish([smc_material(young=young, friction=mu, restitution=cr)], settings)
+
+
+def mixed_smc(n_side=6, seed=7, radius=0.1, step=1e-3, shapes=("sphere", "box", "capsule")):
+    """Small mixed-shape SMC scene (config E flavour, after src/demos/multicore/demo_MCORE_mixerSMC.cpp:51-169):
+    a lattice cycling through the requested shape kinds inside an open box."""
+    b = SceneBuilder()
+    spacing = 2.4 * radius
+    sx = sy = n_side * spacing + radius
+    sz = (n_side + 2) * spacing
+    bin_body = b.add_bodies(1.0, (1.0, 1.0, 1.0), [[0.0, 0.0, 0.0]], active=0, collide=1)
+    b.add_box_container(bin_body, (0, 0, sz / 2), (sx, sy, sz), 0.2, faces=(2, 2, -1))
+    pos = lattice_positions(n_side, n_side, n_side, spacing, 0.02 * radius, 1.2 * radius, seed)
+    rng = np.random.Generator(np.random.MT19937(seed + 1))
+    n = pos.shape[0]
+    q = rng.normal(size=(n, 4))
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    kinds = [shapes[i % len(shapes)] for i in range(n)]
+    rho = 1000.0
+    for i, k in enumerate(kinds):
+        if k == "sphere":
+            m = rho * 4 / 3 * np.pi * radius ** 3
+            I = (0.4 * m * radius ** 2,) * 3
+            bid = b.add_bodies(m, I, [pos[i]], rot=[q[i]])
+            b.add_shapes(SPHERE, [bid], [[radius]])
+        elif k == "box":
+            h = np.array([radius, 0.8 * radius, 0.6 * radius])
+            m = rho * 8 * h.prod()
+            I = m / 3 * np.array([h[1] ** 2 + h[2] ** 2, h[0] ** 2 + h[2] ** 2, h[0] ** 2 + h[1] ** 2])
+            bid = b.add_bodies(m, I, [pos[i]], rot=[q[i]])
+            b.add_shapes(BOX, [bid], [h])
+        else:
+            r, hl = 0.6 * radius, 0.6 * radius  # stored (radius, radius): SURVEY Appendix A.1
+            m = rho * (np.pi * r * r * 2 * hl + 4 / 3 * np.pi * r ** 3)
+            I = (0.5 * m * r * r,) * 3
+            bid = b.add_bodies(m, I, [pos[i]], rot=[q[i]])
+            b.add_shapes(CAPSULE, [bid], [[r, hl]])
+    settings = dict(system_type=1, step_size=step, gravity=(0.0, 0.0, -9.81), contact_force_model=HERTZ,
+                    narrowphase_algorithm=HYBRID, broadphase_grid=FIXED_DENSITY, grid_density=5.0)
+    return b.finish([smc_material(young=2e5, friction=0.4, restitution=0.1)], settings)
+
+
+def balls_nsc(nx=16, ny=16, nz=4, radius=0.15, seed=3, step=1e-2, envelope=0.01, iterations=100, mu=0.4):
+    """NSC ball bed (config D, after src/demos/multicore/demo_MCORE_ballsNSC.cpp:121-149): unit-mass spheres with
+    I = 0.4 m r^2, friction 0.4, SLIDING mode, alpha = 0, recovery speed 1e4, APGD with a fixed iteration count.
+    262,144 spheres = balls_nsc(128, 128, 16)."""
+    b = SceneBuilder()
+    spacing = 2.05 * radius
+    sx = nx * spacing + radius
+    sy = ny * spacing + radius
+    sz = (nz + 4) * spacing
+    bin_body = b.add_bodies(1.0, (1.0, 1.0, 1.0), [[0.0, 0.0, 0.0]], active=0, collide=1)
+    b.add_box_container(bin_body, (0, 0, sz / 2), (sx, sy, sz), 0.2, faces=(2, 2, -1))
+    m = 1.0
+    inertia = 0.4 * m * radius * radius
+    pos = lattice_positions(nx, ny, nz, spacing, 0.01 * radius, 1.05 * radius, seed)
+    first = b.add_bodies(m, (inertia,) * 3, pos)
+    n = pos.shape[0]
+    b.add_shapes(SPHERE, np.arange(first, first + n), np.full((n, 1), radius))
+    settings = dict(system_type=0, step_size=step, gravity=(0.0, 0.0, -9.81), collision_envelope=envelope,
+                    narrowphase_algorithm=HYBRID, broadphase_grid=FIXED_DENSITY, grid_density=5.0,
+                    solver_type=SOLVER_APGD, solver_mode=MODE_SLIDING, max_iteration_normal=0,
+                    max_iteration_sliding=iterations, max_iteration_spinning=0, alpha=0.0,
+                    contact_recovery_speed=1e4, tolerance=0.0)
+    return b.finish([nsc_material(friction=mu)], settings)

@@ -1,0 +1,310 @@
+"""Host-side mirror of the reference's system interface for the granular-contact hot path.
+
+``ChSystemMulticoreSMC`` / ``ChSystemMulticoreNSC`` keep the names and meaning of the reference classes
+(src/chrono_multicore/physics/ChSystemMulticore.h:52-267): ``GetSettings()``, ``SetGravitationalAcceleration``,
+``DoStepDynamics``, ``GetNumContacts``, ``GetBodyContactForce``, ``GetTimerCollisionBroad`` ... but bodies and
+shapes are added in bulk as arrays (the C++ shim in INTEGRATION.md does the per-``ChBody`` gather).  All state
+lives on the B200; every method is a thin call into the C ABI (include/chrono_b200.h).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import cb200_counts, cb200_settings, check
+
+# ChCollisionShape::Type values (src/chrono/collision/ChCollisionShape.h:31-53)
+SPHERE, ELLIPSOID, BOX, CYLINDER, CYLSHELL, CONVEXHULL = 0, 1, 2, 3, 4, 5
+TRIANGLE, CAPSULE, CONE, ROUNDEDBOX, ROUNDEDCYL = 10, 12, 13, 14, 15
+
+# ChBroadphase::GridType, ChNarrowphase::Algorithm
+FIXED_RESOLUTION, FIXED_BIN_SIZE, FIXED_DENSITY = 0, 1, 2
+MPR, PRIMS, HYBRID = 0, 1, 2
+# ChSystemSMC enums
+HOOKE, HERTZ, PLAIN_COULOMB, FLORES = 0, 1, 2, 3
+ADHESION_CONSTANT, ADHESION_DMT, ADHESION_PERKO = 0, 1, 2
+DISPL_NONE, DISPL_ONE_STEP, DISPL_MULTI_STEP = 0, 1, 2
+# SolverMode / SolverType
+MODE_NORMAL, MODE_SLIDING, MODE_SPINNING = 0, 1, 2
+SOLVER_APGD, SOLVER_APGDREF = 0, 1
+
+
+def _f64(a, shape=None):
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    if shape is not None:
+        a = a.reshape(shape)
+    return a
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class ChSystemMulticore:
+    """Common part (reference: ChSystemMulticore, src/chrono_multicore/physics/ChSystemMulticore.{h,cpp})."""
+
+    system_type = 0
+
+    def __init__(self, device=0):
+        self._lib = _lib.load()
+        self._h = C.c_void_p()
+        check(self._lib.cb200_create(int(device), C.byref(self._h)))
+        self.device = int(device)
+        self.settings = cb200_settings()
+        self._lib.cb200_default_settings(C.byref(self.settings))
+        self.settings.system_type = self.system_type
+        self.num_bodies = 0
+        self.num_shapes = 0
+        self.ch_time = 0.0
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None) and self._h.value:
+                self._lib.cb200_destroy(self._h)
+                self._h = C.c_void_p()
+        except Exception:
+            pass
+
+    # ---- configuration -------------------------------------------------------------------------------------
+    def GetSettings(self):
+        """``sys.GetSettings()`` (ChSystemMulticore.cpp:684-686); pushed to the device at every step."""
+        return self.settings
+
+    def SetGravitationalAcceleration(self, g):
+        self.settings.gravity[:] = [float(g[0]), float(g[1]), float(g[2])]
+
+    def SetStep(self, h):
+        self.settings.step_size = float(h)
+
+    def _push_settings(self):
+        check(self._lib.cb200_set_settings(self._h, C.byref(self.settings)))
+
+    # ---- model building ------------------------------------------------------------------------------------
+    def AddBodies(self, mass, inertia_xx, pos, rot=None, vel=None, active=None, collide=None, inv_inertia_xx=None):
+        """Bulk ``AddBody`` (ChSystemMulticore.cpp:205-226). Returns the index of the first new body."""
+        mass = _f64(mass).ravel()
+        n = mass.size
+        inertia_xx = _f64(inertia_xx, (n, 3))
+        inv = None if inv_inertia_xx is None else _f64(inv_inertia_xx, (n, 3))
+        act = None if active is None else np.ascontiguousarray(active, dtype=np.int8)
+        col = None if collide is None else np.ascontiguousarray(collide, dtype=np.int8)
+        first = C.c_int(0)
+        check(self._lib.cb200_append_bodies(self._h, n, _ptr(mass), _ptr(inertia_xx), _ptr(inv), _ptr(act), _ptr(col),
+                                            C.byref(first)))
+        self.num_bodies += n
+        self.SetBodyState(first.value, pos, rot, vel, n)
+        return first.value
+
+    def SetBodyState(self, first, pos=None, rot=None, vel=None, n=None):
+        """Gather of UpdateRigidBodies (ChSystemMulticore.cpp:329-377): host pose/velocity -> device."""
+        arrs = [None if a is None else _f64(a) for a in (pos, rot, vel)]
+        if n is None:
+            n = next(a.size // k for a, k in zip(arrs, (3, 4, 6)) if a is not None)
+        check(self._lib.cb200_upload_state(self._h, int(first), int(n), _ptr(arrs[0]), _ptr(arrs[1]), _ptr(arrs[2])))
+
+    def SetAppliedForces(self, first, force_torque):
+        ft = None if force_torque is None else _f64(force_torque)
+        n = self.num_bodies - first if ft is None else ft.size // 6
+        check(self._lib.cb200_upload_applied_forces(self._h, int(first), int(n), _ptr(ft)))
+
+    def AddShapes(self, type, body_id, dims, pos_local=None, rot_local=None, family=None, material_id=None):
+        """Bulk ``ChCollisionSystemMulticore::Add`` (ChCollisionSystemMulticore.cpp:86-187)."""
+        type = np.ascontiguousarray(type, dtype=np.int32).ravel()
+        n = type.size
+        body_id = np.ascontiguousarray(body_id, dtype=np.uint32).ravel()
+        dims = _f64(dims, (n, 4))
+        pl = np.zeros((n, 3)) if pos_local is None else _f64(pos_local, (n, 3))
+        if rot_local is None:
+            rl = np.zeros((n, 4))
+            rl[:, 0] = 1
+        else:
+            rl = _f64(rot_local, (n, 4))
+        if family is None:
+            fam = np.empty((n, 2), dtype=np.int16)
+            fam[:, 0] = 1  # family group bit 0, mask all (ChCollisionModel defaults)
+            fam[:, 1] = 0x7FFF
+        else:
+            fam = np.ascontiguousarray(family, dtype=np.int16).reshape(n, 2)
+        mat = np.zeros(n, dtype=np.int32) if material_id is None else np.ascontiguousarray(material_id, dtype=np.int32)
+        check(self._lib.cb200_append_shapes(self._h, n, _ptr(type), _ptr(body_id), _ptr(fam), _ptr(pl), _ptr(rl),
+                                            _ptr(dims), _ptr(mat)))
+        self.num_shapes += n
+
+    def SetMaterials(self, table):
+        table = np.ascontiguousarray(table, dtype=np.float32)
+        if self.system_type == 1:
+            table = table.reshape(-1, 14)
+            check(self._lib.cb200_set_materials_smc(self._h, table.shape[0], _ptr(table)))
+        else:
+            table = table.reshape(-1, 11)
+            check(self._lib.cb200_set_materials_nsc(self._h, table.shape[0], _ptr(table)))
+
+    # ---- stepping ------------------------------------------------------------------------------------------
+    def DoStepDynamics(self, step=None):
+        """``ChSystem::DoStepDynamics`` -> AdvanceDynamics (ChSystemMulticore.cpp:73-200)."""
+        if step is not None:
+            self.settings.step_size = float(step)
+        self.DoSteps(1)
+
+    def DoSteps(self, n):
+        self._push_settings()
+        check(self._lib.cb200_do_steps(self._h, int(n)))
+        self.ch_time += n * self.settings.step_size
+
+    # the reference's own seams, for stage-level parity tests
+    def Update(self):
+        self._push_settings()
+        check(self._lib.cb200_update_forces(self._h))
+
+    def RunCollision(self, stages=7):
+        self._push_settings()
+        check(self._lib.cb200_run_collision(self._h, int(stages)))
+
+    def RunSolver(self):
+        self._push_settings()
+        if self.system_type == 1:
+            check(self._lib.cb200_run_solver_smc(self._h))
+        else:
+            check(self._lib.cb200_run_solver_nsc(self._h))
+
+    def Integrate(self):
+        self._push_settings()
+        check(self._lib.cb200_integrate(self._h))
+
+    def Synchronize(self):
+        check(self._lib.cb200_synchronize(self._h))
+
+    # ---- read-backs ----------------------------------------------------------------------------------------
+    def GetCounts(self):
+        c = cb200_counts()
+        check(self._lib.cb200_get_counts(self._h, C.byref(c)))
+        return c
+
+    def GetNumContacts(self):
+        return int(self.GetCounts().num_rigid_contacts)
+
+    def GetBodyState(self, first=0, n=None):
+        n = self.num_bodies - first if n is None else n
+        pos, rot, vel = np.empty((n, 3)), np.empty((n, 4)), np.empty((n, 6))
+        check(self._lib.cb200_download_state(self._h, int(first), int(n), _ptr(pos), _ptr(rot), _ptr(vel)))
+        return pos, rot, vel
+
+    def GetAABB(self):
+        mn, mx = np.empty((self.num_shapes, 3)), np.empty((self.num_shapes, 3))
+        check(self._lib.cb200_download_aabb(self._h, _ptr(mn), _ptr(mx)))
+        return mn, mx
+
+    def GetBins(self):
+        c = self.GetCounts()
+        ni, na = c.num_bin_aabb_intersections, c.num_active_bins
+        bn, ba = np.empty(ni, np.uint32), np.empty(ni, np.uint32)
+        act, st = np.empty(na, np.uint32), np.empty(na + 1, np.uint32)
+        check(self._lib.cb200_download_bins(self._h, _ptr(bn), _ptr(ba), _ptr(act), _ptr(st)))
+        return bn, ba, act, st
+
+    def GetPairs(self):
+        n = self.GetCounts().num_possible_collisions
+        p = np.empty(n, np.int64)
+        check(self._lib.cb200_download_pairs(self._h, _ptr(p)))
+        return p
+
+    def GetContacts(self):
+        n = self.GetCounts().num_rigid_contacts
+        out = dict(normal=np.empty((n, 3)), pt_a=np.empty((n, 3)), pt_b=np.empty((n, 3)), depth=np.empty(n),
+                   eff_radius=np.empty(n), body_ids=np.empty((n, 2), np.int32), shape_ids=np.empty(n, np.int64))
+        check(self._lib.cb200_download_contacts(self._h, _ptr(out["normal"]), _ptr(out["pt_a"]), _ptr(out["pt_b"]),
+                                                _ptr(out["depth"]), _ptr(out["eff_radius"]), _ptr(out["body_ids"]),
+                                                _ptr(out["shape_ids"])))
+        return out
+
+    def GetContactForces(self):
+        """host_data.ct_force / ct_torque, two rows per contact (body 1, body 2)."""
+        n = self.GetCounts().num_rigid_contacts
+        f, t = np.empty((2 * n, 3)), np.empty((2 * n, 3))
+        check(self._lib.cb200_download_contact_forces(self._h, _ptr(f), _ptr(t)))
+        return f, t
+
+    def GetBodyContactForces(self):
+        f, t = np.empty((self.num_bodies, 3)), np.empty((self.num_bodies, 3))
+        check(self._lib.cb200_download_body_contact_forces(self._h, _ptr(f), _ptr(t)))
+        return f, t
+
+    def GetBodyContactForce(self, body):
+        """``ChSystemMulticoreSMC::GetBodyContactForce`` (ChSystemMulticoreSMC.cpp:74-81)."""
+        return self.GetBodyContactForces()[0][body]
+
+    def GetBodyContactTorque(self, body):
+        return self.GetBodyContactForces()[1][body]
+
+    def GetHf(self):
+        hf = np.empty((self.num_bodies, 6))
+        check(self._lib.cb200_download_hf(self._h, _ptr(hf)))
+        return hf
+
+    def GetGamma(self):
+        n = 3 * self.GetCounts().num_rigid_contacts
+        g = np.empty(n)
+        check(self._lib.cb200_download_gamma(self._h, _ptr(g), int(n)))
+        return g
+
+    def GetTimer(self, name):
+        s = C.c_double(0)
+        check(self._lib.cb200_get_timer(self._h, name.encode(), C.byref(s)))
+        return s.value
+
+    # reference timer accessors (ChSystemMulticore.cpp:656-682)
+    def GetTimerStep(self):
+        return self.GetTimer("step")
+
+    def GetTimerAdvance(self):
+        return self.GetTimer("advance")
+
+    def GetTimerUpdate(self):
+        return self.GetTimer("update")
+
+    def GetTimerCollision(self):
+        return self.GetTimer("collision")
+
+    def GetTimerCollisionBroad(self):
+        return self.GetTimer("collision_broad")
+
+    def GetTimerCollisionNarrow(self):
+        return self.GetTimer("collision_narrow")
+
+    def KernelLaunches(self):
+        return int(self._lib.cb200_kernel_launches(self._h))
+
+    def DeviceArray(self, name):
+        """(device pointer, element count) of a resident array, for zero-copy tooling."""
+        p, n = C.c_void_p(), C.c_int64()
+        check(self._lib.cb200_device_array(self._h, name.encode(), C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+
+class ChSystemMulticoreSMC(ChSystemMulticore):
+    """Penalty (SMC) system, reference: src/chrono_multicore/physics/ChSystemMulticoreSMC.cpp."""
+
+    system_type = 1
+
+
+class ChSystemMulticoreNSC(ChSystemMulticore):
+    """Complementarity (NSC / DVI) system, reference: src/chrono_multicore/physics/ChSystemMulticoreNSC.cpp."""
+
+    system_type = 0
+
+
+def load_scene(sys_, scene):
+    """Push a scene dict produced by ``chrono_wisc_b200.scenes`` into a system."""
+    st = sys_.GetSettings()
+    for k, v in scene["settings"].items():
+        cur = getattr(st, k)
+        if hasattr(cur, "__len__"):
+            cur[:] = list(v)
+        else:
+            setattr(st, k, v)
+    sys_.AddBodies(scene["mass"], scene["inertia"], scene["pos"], scene["rot"], scene["vel"], scene["active"],
+                   scene["collide"])
+    sys_.AddShapes(scene["shape_type"], scene["shape_body"], scene["shape_dims"], scene["shape_pos"],
+                   scene["shape_rot"], scene["shape_fam"], scene["shape_mat"])
+    sys_.SetMaterials(scene["materials"])
+    return sys_

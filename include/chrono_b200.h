@@ -1,0 +1,211 @@
+/* chrono_b200.h -- C ABI of libchrono_b200: the B200 (sm_100a) backend for the Chrono::Multicore granular-contact
+ * hot path (collision pipeline, SMC force accumulation, NSC APGD solve, body integration).
+ *
+ * The reference has no C ABI for this path; its seam is C++ virtual dispatch over two plain data structs
+ * (SURVEY.md 8b).  Every entry point below names the reference interface it replaces (paths relative to the
+ * reference root, MC = src/chrono_multicore, CMC = src/chrono/collision/multicore).  INTEGRATION.md shows the
+ * C++ shim a Chrono maintainer adds on top (ChCollisionSystemB200 / ChIterativeSolverB200).
+ *
+ * Conventions
+ *   - plain pointers and sizes, no C++ or torch types; all arrays are HOST pointers unless a name ends in _dev
+ *   - 3-vectors are packed (x,y,z) doubles (the reference pads real3 to 4 doubles, MM/real3.h:85-90; the shim
+ *     strips the pad), quaternions are (w,x,y,z), velocities 6 per body (vx,vy,vz, wx,wy,wz) with w in the body
+ *     frame, as in host_data.v (MC/physics/ChSystemMulticore.cpp:350-362)
+ *   - every function returns CB200_OK or a negative status; cb200_last_error() gives the message
+ *     (the reference throws std::runtime_error / asserts; the shim rethrows)
+ *   - one caller thread per system (same rule as the reference, SURVEY.md 8b "Threading")
+ *   - there is no CPU fallback: cb200_create fails if no CUDA device is usable.
+ */
+#ifndef CHRONO_B200_H
+#define CHRONO_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct cb200_system cb200_system; /* opaque handle: owns one CUDA stream and all device SoA state */
+
+enum {
+    CB200_OK = 0,
+    CB200_ERR_CUDA = -1,      /* a CUDA runtime call failed */
+    CB200_ERR_ARG = -2,       /* bad argument */
+    CB200_ERR_UNSUPPORTED = -3, /* feature of the reference not covered by this backend */
+    CB200_ERR_STATE = -4      /* call sequence error (e.g. step before bodies were added) */
+};
+
+/* Shape types: values of chrono::ChCollisionShape::Type (src/chrono/collision/ChCollisionShape.h:31-53). */
+enum {
+    CB200_SPHERE = 0, CB200_ELLIPSOID = 1, CB200_BOX = 2, CB200_CYLINDER = 3, CB200_CYLSHELL = 4,
+    CB200_CONVEXHULL = 5, CB200_TRIANGLE = 10, CB200_CAPSULE = 12, CB200_CONE = 13, CB200_ROUNDEDBOX = 14,
+    CB200_ROUNDEDCYL = 15
+};
+
+/* Mirror of collision_settings + solver_settings + step/gravity (MC/ChSettings.h:39-246).  Re-read every step,
+ * like ChCollisionSystemChronoMulticore::PreProcess does (MC/collision/ChCollisionSystemChronoMulticore.cpp:67-77). */
+typedef struct cb200_settings {
+    /* --- collision_settings (MC/ChSettings.h:39-89) */
+    double collision_envelope;
+    int32_t broadphase_grid;       /* ChBroadphase::GridType: 0 FIXED_RESOLUTION, 1 FIXED_BIN_SIZE, 2 FIXED_DENSITY */
+    int32_t bins_per_axis[3];
+    double bin_size[3];
+    double grid_density;
+    int32_t narrowphase_algorithm; /* ChNarrowphase::Algorithm: 0 MPR, 1 PRIMS, 2 HYBRID */
+    /* --- system */
+    int32_t system_type;           /* 0 = NSC (ChSystemMulticoreNSC), 1 = SMC (ChSystemMulticoreSMC) */
+    double step_size;
+    double gravity[3];
+    /* --- solver_settings, SMC part (MC/ChSettings.h:93-218) */
+    int32_t contact_force_model;   /* ChSystemSMC::ContactForceModel: 0 Hooke, 1 Hertz, 2 PlainCoulomb, 3 Flores */
+    int32_t adhesion_force_model;  /* 0 Constant, 1 DMT, 2 Perko */
+    int32_t tangential_displ_mode; /* 0 None, 1 OneStep, 2 MultiStep */
+    int32_t use_material_properties;
+    double characteristic_vel;
+    double min_slip_vel;
+    double min_roll_vel;
+    double min_spin_vel;
+    /* --- solver_settings, NSC part */
+    int32_t solver_type;           /* SolverType: 0 APGD, 1 APGDREF (subset of MC/ChMulticoreDefines.h) */
+    int32_t solver_mode;           /* SolverMode: 0 NORMAL, 1 SLIDING, 2 SPINNING */
+    int32_t max_iteration_normal;
+    int32_t max_iteration_sliding;
+    int32_t max_iteration_spinning;
+    int32_t cache_step_length;
+    double alpha;
+    double contact_recovery_speed;
+    double tolerance;
+    /* --- backend-only knobs (no reference counterpart) */
+    int32_t deterministic;         /* 1: fixed summation order everywhere (default); 0: allow FP64 atomics */
+    int32_t reserved[7];
+} cb200_settings;
+
+/* Counters of the last step: measures_container (MC/ChMeasures.h:34-120) + cd_data counters
+ * (CMC/ChCollisionData.h:185-221). */
+typedef struct cb200_counts {
+    uint32_t num_bodies;
+    uint32_t num_shapes;
+    uint32_t bins_per_axis[3];
+    uint32_t num_bins;
+    uint32_t num_bin_aabb_intersections; /* N_i */
+    uint32_t num_active_bins;            /* N_a */
+    uint32_t num_possible_collisions;    /* N_p */
+    uint32_t num_potential_contacts;     /* pre-compaction slots, CMC/ChNarrowphase.cpp:136 */
+    uint32_t num_rigid_contacts;         /* N_c */
+    uint32_t ct_body_count;              /* bodies with >= 1 contact, MC/solver/ChIterativeSolverMulticoreSMC.cpp:726 */
+    uint32_t solver_iterations;          /* NSC: iterations of the last Solve */
+    uint32_t reserved[3];
+    double min_bounding_point[3];        /* global_origin */
+    double max_bounding_point[3];
+    double bin_size[3];
+    double solver_residual;
+    double solver_objective;
+} cb200_counts;
+
+const char* cb200_last_error(void);
+int cb200_device_count(void);
+
+/* ChSystemMulticore ctor/dtor (MC/physics/ChSystemMulticore.cpp:36-71): creates the data manager equivalent on
+ * CUDA device `device`. */
+int cb200_create(int device, cb200_system** out);
+void cb200_destroy(cb200_system* sys);
+
+/* sys.GetSettings() write-back (MC/physics/ChSystemMulticore.cpp:684-686). */
+void cb200_default_settings(cb200_settings* s); /* defaults of MC/ChSettings.h:41-48,96-131 */
+int cb200_set_settings(cb200_system* sys, const cb200_settings* s);
+
+/* ChSystemMulticore::AddBody (MC/physics/ChSystemMulticore.cpp:205-226) for n bodies at once: mass, body-frame
+ * inertia diagonal (ChBody::GetInertiaXX), the diagonal of ChBody::GetInvInertia() as Chrono computed it (NULL:
+ * 1/inertia_xx is used) and flags.  Bodies with off-diagonal inertia are not supported yet.
+ * Returns the index of the first new body in *first. */
+int cb200_append_bodies(cb200_system* sys, int n, const double* mass, const double* inertia_xx,
+                        const double* inv_inertia_xx, const char* active, const char* collide, int* first);
+
+/* ChCollisionSystemMulticore::Add (CMC/ChCollisionSystemMulticore.cpp:86-187): append n shapes as shape_container
+ * slices.  dims is 4 doubles per shape: sphere (r,-,-,-); ellipsoid/box/cylinder/cylshell/cone (B.x,B.y,B.z,-);
+ * capsule (radius, hlen-as-stored,-,-) [sic, SURVEY Appendix A.1]; rounded box/cyl (x,y,z,sweep radius).
+ * fam is (group, mask) int16 pairs.  material_id indexes the table given to cb200_set_materials_*. */
+int cb200_append_shapes(cb200_system* sys, int n, const int32_t* type, const uint32_t* body_id, const int16_t* fam,
+                        const double* pos_local, const double* rot_local, const double* dims,
+                        const int32_t* material_id);
+
+/* Per-shape contact materials replacing the per-contact pointer chase of
+ * ChContactContainerMulticoreSMC::AddContact (MC/collision/ChContactContainerMulticoreSMC.cpp:123-174).
+ * 14 floats per material in ChContactMaterialSMC member order: young_modulus, poisson_ratio, static_friction,
+ * sliding_friction, rolling_friction, spinning_friction, restitution, constant_adhesion, adhesionMultDMT,
+ * adhesionSPerko, kn, kt, gn, gt. Composition is done on device in float, as the reference does
+ * (src/chrono/physics/ChContactMaterialSMC.cpp:107-130). */
+int cb200_set_materials_smc(cb200_system* sys, int n, const float* table);
+/* NSC (MC/collision/ChContactContainerMulticoreNSC.cpp:130-180): 11 floats per material: static_friction,
+ * sliding_friction, rolling_friction, spinning_friction, restitution, cohesion, dampingf, compliance, complianceT,
+ * complianceRoll, complianceSpin. */
+int cb200_set_materials_nsc(cb200_system* sys, int n, const float* table);
+
+/* ChSystemMulticore::UpdateRigidBodies gather (MC/physics/ChSystemMulticore.cpp:329-377): upload pose and velocity of
+ * bodies [first, first+n).  Any of pos/rot/vel may be NULL to leave it unchanged. */
+int cb200_upload_state(cb200_system* sys, int first, int n, const double* pos, const double* rot, const double* vel);
+/* Per-body applied force/torque other than gravity (accumulators / force list of ChBody::UpdateForces,
+ * src/chrono/physics/ChBody.cpp:552-574): 6 doubles per body (F global, T local).  NULL clears. */
+int cb200_upload_applied_forces(cb200_system* sys, int first, int n, const double* force_torque);
+int cb200_set_body_flags(cb200_system* sys, int first, int n, const char* active, const char* collide);
+
+/* --- the step, split at the reference's own seams ------------------------------------------------------------ */
+/* ChSystemMulticore::Update -> UpdateRigidBodies force part (ChBody::Update/VariablesFbLoadForces): hf = h*(F,T-gyro). */
+int cb200_update_forces(cb200_system* sys);
+/* ChCollisionSystem::Run (CMC/ChCollisionSystemMulticore.cpp:286-322): GenerateAABB + ChBroadphase::Process +
+ * ChNarrowphase::Process.  stages: bit0 AABB, bit1 broadphase, bit2 narrowphase (7 = all). */
+int cb200_run_collision(cb200_system* sys, int stages);
+/* ChIterativeSolverMulticoreSMC::RunTimeStep (MC/solver/ChIterativeSolverMulticoreSMC.cpp:792-852). */
+int cb200_run_solver_smc(cb200_system* sys);
+/* ChIterativeSolverMulticoreNSC::RunTimeStep (MC/solver/ChIterativeSolverMulticoreNSC.cpp:22-139). */
+int cb200_run_solver_nsc(cb200_system* sys);
+/* Scatter + integrate (MC/physics/ChSystemMulticore.cpp:134-153, ChBody::VariablesQbIncrementPosition). */
+int cb200_integrate(cb200_system* sys);
+/* ChSystem::DoStepDynamics x nsteps = the five calls above in sequence, state resident on device throughout. */
+int cb200_do_steps(cb200_system* sys, int nsteps);
+/* Block until all queued work of this system is done. */
+int cb200_synchronize(cb200_system* sys);
+
+/* --- read-backs (lazy downloads; each synchronizes) ---------------------------------------------------------- */
+int cb200_get_counts(cb200_system* sys, cb200_counts* out);
+int cb200_download_state(cb200_system* sys, int first, int n, double* pos, double* rot, double* vel);
+/* cd_data->aabb_min/max after OffsetAABB (relative to global_origin, CMC/ChBroadphase.cpp:168-176) */
+int cb200_download_aabb(cb200_system* sys, double* aabb_min, double* aabb_max);
+/* bin_number/bin_aabb_number [N_i] sorted by (bin, shape); bin_active [N_a]; bin_start_index [N_a+1] */
+int cb200_download_bins(cb200_system* sys, uint32_t* bin_number, uint32_t* bin_aabb_number, uint32_t* bin_active,
+                        uint32_t* bin_start_index);
+/* cd_data->pair_shapeIDs [N_p] */
+int cb200_download_pairs(cb200_system* sys, int64_t* pair_shape_ids);
+/* cd_data->{norm,cpta,cptb,dpth,erad,bids}_rigid_rigid and contact_shapeIDs, [N_c] */
+int cb200_download_contacts(cb200_system* sys, double* normal, double* pt_a, double* pt_b, double* depth,
+                            double* eff_radius, int32_t* body_ids, int64_t* shape_ids);
+/* host_data.ct_force / ct_torque [2*N_c*3] in the reference's duplicated layout
+ * (MC/solver/ChIterativeSolverMulticoreSMC.cpp:680-685) */
+int cb200_download_contact_forces(cb200_system* sys, double* ct_force, double* ct_torque);
+/* ChSystemMulticoreSMC::GetBodyContactForce/Torque for all bodies (MC/physics/ChSystemMulticoreSMC.cpp:74-90):
+ * 3 doubles per body each, zero for bodies without contacts. */
+int cb200_download_body_contact_forces(cb200_system* sys, double* force, double* torque);
+/* host_data.hf (h * generalized force, 6 per body) as consumed by ComputeInvMassMatrix */
+int cb200_download_hf(cb200_system* sys, double* hf);
+/* NSC multipliers host_data.gamma in the reference layout [n | u v | ...] (MC/ChDataManager.h:307-317) */
+int cb200_download_gamma(cb200_system* sys, double* gamma, int capacity);
+
+/* Timers with the reference's names (MC/ChTimerMulticore.h): seconds of GPU time measured with CUDA
+ * events over the last cb200_do_steps call, averaged per step.  Unknown name -> CB200_ERR_ARG. */
+int cb200_get_timer(cb200_system* sys, const char* name, double* seconds);
+/* Number of kernels this library launched since creation (for bench.py's gpu_launches). */
+int64_t cb200_kernel_launches(cb200_system* sys);
+
+/* --- device-pointer access for zero-copy tooling and multi-GPU halo exchange ---------------------- */
+/* names: "pos","rot","vel","hf","aabb_min","aabb_max","contact_normal",... ; returns device pointer + element count */
+int cb200_device_array(cb200_system* sys, const char* name, void** dev_ptr, int64_t* count);
+/* Slab decomposition: pack bodies whose centre lies in [lo,hi) along axis into a caller-provided DEVICE buffer
+ * (13 doubles + id per body) and report how many were packed; unpack overwrites the state of the listed bodies. */
+int cb200_pack_slab_dev(cb200_system* sys, int axis, double lo, double hi, void* buffer_dev, int64_t capacity,
+                        int64_t* count);
+int cb200_unpack_slab_dev(cb200_system* sys, const void* buffer_dev, int64_t count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CHRONO_B200_H */
