@@ -8,7 +8,7 @@ identical bits.
 """
 import numpy as np
 
-from .system import (BOX, CAPSULE, SPHERE, FIXED_DENSITY, FIXED_RESOLUTION, HERTZ, HYBRID, MODE_SLIDING,
+from .system import (BOX, CAPSULE, SPHERE, FIXED_BIN_SIZE, FIXED_DENSITY, FIXED_RESOLUTION, HERTZ, HYBRID, MODE_SLIDING,
                      SOLVER_APGD)
 
 SMC_MAT_FIELDS = ("young_modulus", "poisson_ratio", "static_friction", "sliding_friction", "rolling_friction",
@@ -115,7 +115,7 @@ def lattice_positions(nx, ny, nz, spacing, jitter, z0, seed):
     return p
 
 
-def settling_smc(nx=32, ny=32, nz=8, radius=0.02, seed=12345, grid="density", bins=(10, 10, 1), step=1e-3,
+def settling_smc(nx=32, ny=32, nz=8, radius=0.02, seed=12345, grid="density", bins=(10, 10, 1), bin_edge=2.0, step=1e-3,
                  young=2e6, mu=0.4, cr=0.4, rho=2000.0, spacing_factor=2.02, jitter_factor=0.005, wall_thickness=0.2):
     """SMC Hertz settling of monodisperse spheres in an open box (configs A/B/C of BASELINE.json; scene after
     src/tests/benchmark_tests/multicore/btest_MCORE_settling.cpp:59-131 with a jittered lattice instead of the
@@ -138,6 +138,9 @@ def settling_smc(nx=32, ny=32, nz=8, radius=0.02, seed=12345, grid="density", bi
                     narrowphase_algorithm=HYBRID, collision_envelope=0.0)
     if grid == "density":
         settings.update(broadphase_grid=FIXED_DENSITY, grid_density=5.0)
+    elif grid == "bin_size":
+        # FIXED_BIN_SIZE with a cubic bin of `bin_edge` sphere diameters ("or bin edge 2.5 diameters")
+        settings.update(broadphase_grid=FIXED_BIN_SIZE, bin_size=(bin_edge * 2 * radius,) * 3)
     else:
         settings.update(broadphase_grid=FIXED_RESOLUTION, bins_per_axis=tuple(bins))
     return b.finish([smc_material(young=young, friction=mu, restitution=cr)], settings)

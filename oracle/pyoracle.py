@@ -210,6 +210,134 @@ class Ref:
         return r, (a.value, b.value, c.value)
 
 
+class Oracle:
+    """The CPU restatement (oracle/oracle.cpp) of the whole SMC hot path."""
+
+    def __init__(self, scene=None, threads=None):
+        if not os.path.exists(ORACLE_LIB):
+            build()
+        L = C.CDLL(ORACLE_LIB)
+        L.orc_create.restype = P
+        L.orc_max_threads.restype = C.c_int
+        for name in ("orc_destroy", "orc_set_threads", "orc_set_settings", "orc_set_bodies", "orc_set_shapes",
+                     "orc_set_materials_smc", "orc_set_state", "orc_get_state", "orc_collide", "orc_smc_step",
+                     "orc_get_counts", "orc_get_grid", "orc_get_aabb", "orc_get_pairs", "orc_get_contacts",
+                     "orc_get_contact_forces", "orc_get_body_forces", "orc_get_hf", "orc_get_timers"):
+            getattr(L, name).restype = None
+        self.L = L
+        self.h = P(L.orc_create())
+        self.nb = self.ns = 0
+        if threads is not None:
+            self.set_threads(threads)
+        if scene is not None:
+            self.set_scene(scene)
+
+    def __del__(self):
+        try:
+            self.L.orc_destroy(self.h)
+        except Exception:
+            pass
+
+    def set_threads(self, n):
+        self.L.orc_set_threads(C.c_int(int(n)))
+
+    def max_threads(self):
+        return int(self.L.orc_max_threads())
+
+    def set_scene(self, scene):
+        from chrono_wisc_b200._lib import cb200_settings, load  # struct layout + defaults of the boundary only
+
+        st = cb200_settings()
+        load().cb200_default_settings(C.byref(st))
+        for k, v in scene["settings"].items():
+            cur = getattr(st, k)
+            if hasattr(cur, "__len__"):
+                cur[:] = list(v)
+            else:
+                setattr(st, k, v)
+        self.settings = st
+        self.L.orc_set_settings(self.h, C.byref(st))
+        self.nb, self.ns = scene["mass"].size, scene["shape_type"].size
+        act = np.ascontiguousarray(scene["active"], dtype=np.int8)
+        col = np.ascontiguousarray(scene["collide"], dtype=np.int8)
+        self.L.orc_set_bodies(self.h, C.c_int(self.nb), _p(_f64(scene["mass"])), _p(_f64(scene["inertia"])), _p(act),
+                              _p(col))
+        self.L.orc_set_shapes(self.h, C.c_int(self.ns), _p(np.ascontiguousarray(scene["shape_type"], np.int32)),
+                              _p(np.ascontiguousarray(scene["shape_body"], np.uint32)),
+                              _p(np.ascontiguousarray(scene["shape_fam"], np.int16)), _p(_f64(scene["shape_pos"])),
+                              _p(_f64(scene["shape_rot"])), _p(_f64(scene["shape_dims"])),
+                              _p(np.ascontiguousarray(scene["shape_mat"], np.int32)))
+        m = np.ascontiguousarray(scene["materials"], dtype=np.float32)
+        if m.shape[-1] == 14:
+            self.L.orc_set_materials_smc(self.h, C.c_int(m.shape[0]), _p(m))
+        self.set_state(scene["pos"], scene["rot"], scene["vel"])
+
+    def set_state(self, pos, rot, vel):
+        self.L.orc_set_state(self.h, _p(_f64(pos)), _p(_f64(rot)), _p(_f64(vel)))
+
+    def state(self):
+        pos, rot, vel = np.empty((self.nb, 3)), np.empty((self.nb, 4)), np.empty((self.nb, 6))
+        self.L.orc_get_state(self.h, _p(pos), _p(rot), _p(vel))
+        return pos, rot, vel
+
+    def collide(self):
+        self.L.orc_collide(self.h)
+
+    def step(self, n=1):
+        self.L.orc_smc_step(self.h, C.c_int(int(n)))
+
+    def counts(self):
+        c = np.zeros(8, dtype=np.uint32)
+        self.L.orc_get_counts(self.h, _p(c))
+        return dict(N_i=int(c[0]), N_a=int(c[1]), N_p=int(c[2]), N_c=int(c[3]), bins=tuple(int(x) for x in c[4:7]),
+                    num_bins=int(c[7]))
+
+    def grid(self):
+        g = np.zeros(12)
+        self.L.orc_get_grid(self.h, _p(g))
+        g = g.reshape(4, 3)
+        return dict(min_bounding_point=g[0], max_bounding_point=g[1], bin_size=g[2], inv_bin_size=g[3])
+
+    def aabb(self):
+        mn, mx = np.empty((self.ns, 3)), np.empty((self.ns, 3))
+        self.L.orc_get_aabb(self.h, _p(mn), _p(mx))
+        return mn, mx
+
+    def pairs(self):
+        p = np.empty(self.counts()["N_p"], np.int64)
+        self.L.orc_get_pairs(self.h, _p(p))
+        return p
+
+    def contacts(self):
+        n = self.counts()["N_c"]
+        out = dict(normal=np.empty((n, 3)), pt_a=np.empty((n, 3)), pt_b=np.empty((n, 3)), depth=np.empty(n),
+                   eff_radius=np.empty(n), body_ids=np.empty((n, 2), np.int32), shape_ids=np.empty(n, np.int64))
+        self.L.orc_get_contacts(self.h, _p(out["normal"]), _p(out["pt_a"]), _p(out["pt_b"]), _p(out["depth"]),
+                                _p(out["eff_radius"]), _p(out["body_ids"]), _p(out["shape_ids"]))
+        return out
+
+    def contact_forces(self):
+        n = self.counts()["N_c"]
+        f, t = np.zeros((2 * n, 3)), np.zeros((2 * n, 3))
+        self.L.orc_get_contact_forces(self.h, _p(f), _p(t))
+        return f, t
+
+    def body_forces(self):
+        f, t = np.zeros((self.nb, 3)), np.zeros((self.nb, 3))
+        self.L.orc_get_body_forces(self.h, _p(f), _p(t))
+        return f, t
+
+    def hf(self):
+        hf = np.empty((self.nb, 6))
+        self.L.orc_get_hf(self.h, _p(hf))
+        return hf
+
+    def timers(self):
+        t = np.zeros(6)
+        self.L.orc_get_timers(self.h, _p(t))
+        return dict(zip(("update", "collision_broad", "collision_narrow", "forces", "accumulate", "integrate"), t))
+
+
 def canonical_pairs(p):
     """Canonical order for pair lists: ascending packed key."""
     return np.sort(np.asarray(p, dtype=np.int64))
