@@ -77,6 +77,8 @@ _SIGNATURES = {
     "cb200_last_error": (C.c_char_p, []),
     "cb200_device_count": (C.c_int, []),
     "cb200_create": (C.c_int, [C.c_int, C.POINTER(_P)]),
+    "cb200_host_alloc": (C.c_int, [C.c_uint64, C.POINTER(_P)]),
+    "cb200_host_free": (C.c_int, [_P]),
     "cb200_destroy": (None, [_P]),
     "cb200_default_settings": (None, [C.POINTER(cb200_settings)]),
     "cb200_set_settings": (C.c_int, [_P, C.POINTER(cb200_settings)]),

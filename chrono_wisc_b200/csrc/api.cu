@@ -13,13 +13,17 @@ int set_error(int code, const std::string& msg) {
     return code;
 }
 
+// Timers never block the stream: every start/stop records into a pool of event pairs, and the pairs are
+// resolved in one go (flush_timers) at the end of cb200_do_steps or when the pool holds 64 intervals.
 int timer_start(System* S, const char* name) {
     Timer& t = S->timers[name];
-    if (!t.a) {
-        CB_CUDA(cudaEventCreate(&t.a));
-        CB_CUDA(cudaEventCreate(&t.b));
+    if (t.used == t.pool.size()) {
+        cudaEvent_t a, b;
+        CB_CUDA(cudaEventCreate(&a));
+        CB_CUDA(cudaEventCreate(&b));
+        t.pool.emplace_back(a, b);
     }
-    CB_CUDA(cudaEventRecord(t.a, S->stream));
+    CB_CUDA(cudaEventRecord(t.pool[t.used].first, S->stream));
     t.armed = true;
     return CB200_OK;
 }
@@ -28,12 +32,23 @@ int timer_stop(System* S, const char* name) {
     Timer& t = S->timers[name];
     if (!t.armed)
         return CB200_OK;
-    CB_CUDA(cudaEventRecord(t.b, S->stream));
-    CB_CUDA(cudaEventSynchronize(t.b));
-    float ms = 0;
-    CB_CUDA(cudaEventElapsedTime(&ms, t.a, t.b));
-    t.total_ms += ms;
+    CB_CUDA(cudaEventRecord(t.pool[t.used].second, S->stream));
+    t.used++;
     t.armed = false;
+    return CB200_OK;
+}
+
+int flush_timers(System* S) {
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    for (auto& kv : S->timers) {
+        Timer& t = kv.second;
+        for (size_t i = 0; i < t.used; i++) {
+            float ms = 0;
+            CB_CUDA(cudaEventElapsedTime(&ms, t.pool[i].first, t.pool[i].second));
+            t.total_ms += ms;
+        }
+        t.used = 0;
+    }
     return CB200_OK;
 }
 
@@ -56,15 +71,99 @@ static int download(System* S, const T* dev, T* dst, size_t n) {
     return CB200_OK;
 }
 
-static int check_step_counters(System* S) {
-    CB_TRY(fetch_counters(S));
-    if (S->h_cnt->overflow)
-        return set_error(CB200_ERR_UNSUPPORTED, "internal capacity exceeded (too many large shapes or heavy bodies)");
-    if (S->h_cnt->unsupported)
-        return set_error(CB200_ERR_UNSUPPORTED,
-                         std::to_string(S->h_cnt->unsupported) +
-                             " candidate pairs have a shape combination this backend cannot test yet");
+// ---- capacities -------------------------------------------------------------------------------------------
+static int alloc_bins(System* S, uint32_t n) {
+    CB_TRY(S->bin_start.reserve((size_t)n + 2));
+    CB_TRY(S->bin_cursor.reserve((size_t)n + 1));
+    S->cap_bins = (uint32_t)std::min<size_t>(S->bin_cursor.cap - 1, S->bin_start.cap - 2);
     return CB200_OK;
+}
+static int alloc_entries(System* S, uint32_t n) {
+    CB_TRY(S->ent_tmp.reserve(n));
+    CB_TRY(S->ent_bin.reserve(n));
+    CB_TRY(S->ent_shape.reserve(n));
+    CB_TRY(S->ent_count.reserve(n));
+    S->cap_entries = (uint32_t)S->ent_tmp.cap;
+    CB_TRY(S->tile_count.reserve((size_t)S->cap_entries / PAIR_TILE + 4));
+    return CB200_OK;
+}
+static int alloc_contacts(System* S, uint32_t n) {
+    CB_TRY(S->c_depth.reserve(n));
+    const size_t c = S->c_depth.cap;
+    CB_TRY(S->c_norm.reserve(3 * c));
+    CB_TRY(S->c_pta.reserve(3 * c));
+    CB_TRY(S->c_ptb.reserve(3 * c));
+    CB_TRY(S->c_erad.reserve(c));
+    CB_TRY(S->c_bids.reserve(2 * c));
+    CB_TRY(S->c_shapes.reserve(c));
+    CB_TRY(S->c_mats.reserve(c));
+    CB_TRY(S->ct_force.reserve(3 * c));
+    CB_TRY(S->ct_torque.reserve(6 * c));
+    CB_TRY(S->b_inc.reserve(2 * c));
+    CB_TRY(S->heavy_part.reserve((size_t)MAX_HEAVY * (c / 4096 + 2) * 7));
+    S->cap_contacts = (uint32_t)c;
+    return CB200_OK;
+}
+static int alloc_pairs(System* S, uint32_t n) {
+    CB_TRY(S->pairs.reserve(n));
+    S->cap_pairs = (uint32_t)S->pairs.cap;
+    return CB200_OK;
+}
+
+// First-use allocation of everything a step touches.  Sizes are guesses; a guess that turns out too small costs one
+// re-run of the step that found out (grow_after_overflow).
+int ensure_capacity(System* S) {
+    const size_t nb = S->nb, ns = S->ns;
+    CB_TRY(S->b_deg.reserve(nb + 2));
+    CB_TRY(S->b_cursor.reserve(nb + 1));
+    CB_TRY(S->b_force.reserve(6 * nb + 6));
+    CB_TRY(S->heavy_list.reserve(MAX_HEAVY));
+    CB_TRY(S->large_list.reserve(MAX_LARGE));
+    CB_TRY(S->bin_intersections.reserve(ns + 1));
+    if (S->cap_bins == 0)
+        CB_TRY(alloc_bins(S, (uint32_t)std::max<size_t>(4 * ns, 1 << 14)));
+    if (S->cap_entries < 4 * ns + 1024)
+        CB_TRY(alloc_entries(S, (uint32_t)(8 * ns + 4096)));
+    if (S->cap_contacts < 2 * ns + 1024)
+        CB_TRY(alloc_contacts(S, (uint32_t)(6 * ns + 4096)));
+    return CB200_OK;
+}
+
+// Called after fetch_counters() found the overflow mask set: grow what was too small and clear the mask.
+int grow_after_overflow(System* S) {
+    const DevCounters& c = *S->h_cnt;
+    if (c.overflow & OVF_LARGE)
+        return set_error(CB200_ERR_UNSUPPORTED, "more than 4096 shapes span more than 48 bins each");
+    if (c.overflow & OVF_HEAVY)
+        return set_error(CB200_ERR_UNSUPPORTED, "more than 64 bodies own a shape spanning more than 48 bins");
+    if (c.overflow & OVF_BINS) {
+        if (c.need_bins > (1u << 28))
+            return set_error(CB200_ERR_UNSUPPORTED, "broadphase grid has more than 2^28 bins");
+        CB_TRY(alloc_bins(S, c.need_bins + c.need_bins / 8));
+    }
+    if (c.overflow & OVF_ENTRIES)
+        CB_TRY(alloc_entries(S, c.need_entries + c.need_entries / 4));
+    if (c.overflow & OVF_CONTACTS)
+        CB_TRY(alloc_contacts(S, c.need_contacts + c.need_contacts / 4));
+    if (c.overflow & OVF_PAIRS)
+        CB_TRY(alloc_pairs(S, c.need_pairs + c.need_pairs / 8));
+    CB_CUDA(cudaMemsetAsync(&S->d_cnt->overflow, 0, 4, S->stream));
+    S->h_cnt->overflow = 0;
+    return CB200_OK;
+}
+
+// Enqueue `what`, wait, and repeat while a capacity was exceeded (stage-level calls; one sync per call).
+template <typename F>
+static int run_stage(System* S, F what) {
+    CB_TRY(ensure_capacity(S));
+    for (int attempt = 0; attempt < 8; attempt++) {
+        CB_TRY(what());
+        CB_TRY(fetch_counters(S));
+        if (!S->h_cnt->overflow)
+            return CB200_OK;
+        CB_TRY(grow_after_overflow(S));
+    }
+    return set_error(CB200_ERR_STATE, "capacity growth did not converge");
 }
 
 }  // namespace cb200
@@ -82,6 +181,19 @@ int cb200_device_count(void) {
     if (cudaGetDeviceCount(&n) != cudaSuccess)
         return 0;
     return n;
+}
+
+int cb200_host_alloc(uint64_t bytes, void** out) {
+    if (!out)
+        return set_error(CB200_ERR_ARG, "null output pointer");
+    CB_CUDA(cudaMallocHost(out, bytes ? bytes : 1));
+    return CB200_OK;
+}
+
+int cb200_host_free(void* p) {
+    if (p)
+        CB_CUDA(cudaFreeHost(p));
+    return CB200_OK;
 }
 
 void cb200_default_settings(cb200_settings* s) {
@@ -127,6 +239,7 @@ int cb200_create(int device, cb200_system** out) {
     CB_CUDA(cudaSetDevice(device));
     System* S = new System();
     S->device = device;
+    CB_CUDA(cudaDeviceGetAttribute(&S->num_sms, cudaDevAttrMultiProcessorCount, device));
     cb200_default_settings(&S->set);
     CB_CUDA(cudaStreamCreateWithFlags(&S->stream, cudaStreamNonBlocking));
     CB_CUDA(cudaMalloc(&S->d_cnt, sizeof(DevCounters)));
@@ -146,20 +259,18 @@ void cb200_destroy(cb200_system* sys) {
 #define REL(x) S->x.release()
     REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(bflags); REL(heavy);
     REL(s_type); REL(s_body); REL(s_fam); REL(s_mat); REL(s_lpos); REL(s_lrot); REL(s_dims); REL(s_wpos); REL(s_wrot);
-    REL(s_bp); REL(mat_smc); REL(mat_nsc); REL(bin_intersections); REL(bin_count); REL(bin_cursor);
-    REL(bin_entries_tmp); REL(bin_entries); REL(large_list); REL(pair_count); REL(pairs); REL(pair_aux);
-    REL(slot_index); REL(pair_nc); REL(t_norm); REL(t_pta); REL(t_ptb); REL(t_depth); REL(t_erad);
+    REL(s_box); REL(s_meta); REL(mat_smc); REL(mat_nsc); REL(bin_intersections); REL(bin_start); REL(bin_cursor);
+    REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_count); REL(tile_count); REL(large_list); REL(pairs);
     REL(c_norm); REL(c_pta); REL(c_ptb); REL(c_depth); REL(c_erad); REL(c_bids); REL(c_shapes); REL(c_mats);
     REL(ct_force); REL(ct_torque); REL(b_deg); REL(b_cursor); REL(b_inc); REL(b_force); REL(heavy_list);
     REL(heavy_part); REL(n_frame); REL(gamma); REL(n_r); REL(n_E); REL(n_work); REL(n_bodyvec); REL(n_scal);
     REL(scan_tmp);
 #undef REL
-    for (auto& kv : S->timers) {
-        if (kv.second.a)
-            cudaEventDestroy(kv.second.a);
-        if (kv.second.b)
-            cudaEventDestroy(kv.second.b);
-    }
+    for (auto& kv : S->timers)
+        for (auto& ev : kv.second.pool) {
+            cudaEventDestroy(ev.first);
+            cudaEventDestroy(ev.second);
+        }
     cudaFree(S->d_cnt);
     cudaFreeHost(S->h_cnt);
     cudaStreamDestroy(S->stream);
@@ -258,7 +369,8 @@ int cb200_append_shapes(cb200_system* sys, int n, const int32_t* type, const uin
     CB_TRY(S->s_dims.reserve(4 * ns1, true, st));
     CB_TRY(S->s_wpos.reserve(4 * ns1, true, st));
     CB_TRY(S->s_wrot.reserve(4 * ns1, true, st));
-    CB_TRY(S->s_bp.reserve(ns1, true, st));
+    CB_TRY(S->s_box.reserve(ns1, true, st));
+    CB_TRY(S->s_meta.reserve(ns1, true, st));
     std::vector<uint32_t> f(n);
     std::vector<int32_t> m(n, 0);
     for (int i = 0; i < n; i++) {
@@ -275,6 +387,9 @@ int cb200_append_shapes(cb200_system* sys, int n, const int32_t* type, const uin
     CB_TRY(upload(S, S->s_dims, 4 * ns0, dims, 4 * (size_t)n));
     CB_CUDA(cudaStreamSynchronize(st));
     S->ns = (uint32_t)ns1;
+    S->meta_dirty = true;
+    for (int i = 0; i < n; i++)
+        S->n_nonsphere += type[i] != CB200_SPHERE;
     return CB200_OK;
 }
 
@@ -388,78 +503,116 @@ int cb200_set_body_flags(cb200_system* sys, int first, int n, const char* active
         fl[i] = (uint8_t)((active[i] ? 1 : 0) | (collide[i] ? 2 : 0));
     CB_TRY(upload(S, S->bflags, (size_t)first, fl.data(), (size_t)n));
     CB_CUDA(cudaStreamSynchronize(S->stream));
+    S->meta_dirty = true;
     return CB200_OK;
 }
 
 int cb200_update_forces(cb200_system* sys) {
     System* S = SYS(sys);
     CB_CUDA(cudaSetDevice(S->device));
-    return stage_update_forces(S);
+    return run_stage(S, [&] { return enqueue_update_forces(S); });
 }
 
 int cb200_run_collision(cb200_system* sys, int stages) {
     System* S = SYS(sys);
     CB_CUDA(cudaSetDevice(S->device));
-    if (stages & 1)
-        CB_TRY(stage_aabb(S));
-    if (stages & 2)
-        CB_TRY(stage_broadphase(S));
-    if (stages & 4)
-        CB_TRY(stage_narrowphase(S));
-    return CB200_OK;
+    return run_stage(S, [&]() -> int {
+        // a retry after a capacity overflow restarts from the AABBs (OffsetAABB rewrites the boxes in place)
+        if ((stages & 1) || ((stages & 2) && S->box_relative))
+            CB_TRY(enqueue_aabb(S));
+        if (stages & 2) {
+            if (!S->pairs.p)
+                CB_TRY(alloc_pairs(S, 8 * S->ns + 1024));
+            CB_TRY(enqueue_broadphase(S, true, (stages & 4) != 0));
+        } else if (stages & 4) {
+            CB_TRY(enqueue_pairs_only(S, false, true));
+        }
+        return CB200_OK;
+    });
 }
 
 int cb200_run_solver_smc(cb200_system* sys) {
     System* S = SYS(sys);
     CB_CUDA(cudaSetDevice(S->device));
-    return stage_smc(S);
+    return run_stage(S, [&] { return enqueue_smc(S); });
 }
 
 int cb200_run_solver_nsc(cb200_system* sys) {
     System* S = SYS(sys);
     CB_CUDA(cudaSetDevice(S->device));
-    return stage_nsc(S);
+    return run_stage(S, [&] { return enqueue_nsc(S); });
 }
 
 int cb200_integrate(cb200_system* sys) {
     System* S = SYS(sys);
     CB_CUDA(cudaSetDevice(S->device));
-    return stage_integrate(S);
+    return run_stage(S, [&] { return enqueue_integrate(S); });
 }
 
+static int enqueue_one_step(System* S) {
+    CB_TRY(timer_start(S, "step"));
+    CB_TRY(timer_start(S, "update"));
+    CB_TRY(enqueue_update_forces(S));
+    CB_TRY(timer_stop(S, "update"));
+    CB_TRY(timer_start(S, "collision"));
+    CB_TRY(timer_start(S, "collision_broad"));
+    CB_TRY(enqueue_aabb(S));
+    CB_TRY(enqueue_bins(S));
+    CB_TRY(timer_stop(S, "collision_broad"));
+    CB_TRY(timer_start(S, "collision_narrow"));  // in-bin pair tests fused with the single-contact narrowphase
+    CB_TRY(enqueue_pairs_only(S, false, true));
+    CB_TRY(timer_stop(S, "collision_narrow"));
+    CB_TRY(timer_stop(S, "collision"));
+    CB_TRY(timer_start(S, "advance"));
+    if (S->set.system_type == 1)
+        CB_TRY(enqueue_smc(S));
+    else
+        CB_TRY(enqueue_nsc(S));
+    CB_TRY(timer_stop(S, "advance"));
+    CB_TRY(timer_start(S, "integrate"));
+    CB_TRY(enqueue_integrate(S));
+    CB_TRY(timer_stop(S, "integrate"));
+    CB_TRY(timer_stop(S, "step"));
+    return CB200_OK;
+}
+
+// ChSystem::DoStepDynamics x nsteps.  Steps are enqueued back to back with no host synchronisation in between
+// (all extents live on the device); the host syncs once per chunk of 64 steps to resolve timers and to find out
+// whether a capacity was exceeded, in which case the steps that did not run (the device counts them) are redone.
 int cb200_do_steps(cb200_system* sys, int nsteps) {
     System* S = SYS(sys);
     if (!S || nsteps < 0)
         return set_error(CB200_ERR_ARG, "bad argument to cb200_do_steps");
     CB_CUDA(cudaSetDevice(S->device));
+    if (S->nb == 0)
+        return CB200_OK;
     for (auto& kv : S->timers)
         kv.second.total_ms = 0;
     S->timed_steps = nsteps;
-    for (int s = 0; s < nsteps; s++) {
-        CB_TRY(timer_start(S, "step"));
-        CB_TRY(timer_start(S, "update"));
-        CB_TRY(stage_update_forces(S));
-        CB_TRY(timer_stop(S, "update"));
-        CB_TRY(timer_start(S, "collision"));
-        CB_TRY(timer_start(S, "collision_broad"));
-        CB_TRY(stage_aabb(S));
-        CB_TRY(stage_broadphase(S));
-        CB_TRY(timer_stop(S, "collision_broad"));
-        CB_TRY(timer_start(S, "collision_narrow"));
-        CB_TRY(stage_narrowphase(S));
-        CB_TRY(timer_stop(S, "collision_narrow"));
-        CB_TRY(timer_stop(S, "collision"));
-        CB_TRY(timer_start(S, "advance"));
-        if (S->set.system_type == 1)
-            CB_TRY(stage_smc(S));
-        else
-            CB_TRY(stage_nsc(S));
-        CB_TRY(timer_stop(S, "advance"));
-        CB_TRY(timer_start(S, "integrate"));
-        CB_TRY(stage_integrate(S));
-        CB_TRY(timer_stop(S, "integrate"));
-        CB_TRY(timer_stop(S, "step"));
-        CB_TRY(check_step_counters(S));
+    CB_TRY(ensure_capacity(S));
+    int remaining = nsteps, stalls = 0;
+    while (remaining > 0) {
+        const int chunk = remaining < 64 ? remaining : 64;
+        CB_TRY(timer_start(S, "do_steps"));
+        CB_CUDA(cudaMemsetAsync(&S->d_cnt->steps_done, 0, 4, S->stream));
+        for (int s = 0; s < chunk; s++)
+            CB_TRY(enqueue_one_step(S));
+        CB_TRY(timer_stop(S, "do_steps"));
+        CB_TRY(flush_timers(S));
+        CB_TRY(fetch_counters(S));
+        const int done = (int)S->h_cnt->steps_done;
+        remaining -= done;
+        if (S->h_cnt->overflow) {
+            CB_TRY(grow_after_overflow(S));
+            if (++stalls > 16 && done == 0)
+                return set_error(CB200_ERR_STATE, "capacity growth did not converge");
+        } else if (done != chunk) {
+            return set_error(CB200_ERR_STATE, "step accounting mismatch");
+        }
+        if (S->h_cnt->unsupported)
+            return set_error(CB200_ERR_UNSUPPORTED,
+                             std::to_string(S->h_cnt->unsupported) +
+                                 " candidate pairs have a shape combination this backend cannot test yet");
     }
     return CB200_OK;
 }
@@ -476,26 +629,31 @@ int cb200_get_counts(cb200_system* sys, cb200_counts* out) {
     if (!S || !out)
         return set_error(CB200_ERR_ARG, "null argument");
     CB_CUDA(cudaSetDevice(S->device));
-    CB_TRY(check_step_counters(S));
+    CB_TRY(fetch_counters(S));
+    const DevCounters& c = *S->h_cnt;
+    if (c.unsupported)
+        return set_error(CB200_ERR_UNSUPPORTED,
+                         std::to_string(c.unsupported) +
+                             " candidate pairs have a shape combination this backend cannot test yet");
     memset(out, 0, sizeof(*out));
     out->num_bodies = S->nb;
     out->num_shapes = S->ns;
     for (int a = 0; a < 3; a++) {
-        out->bins_per_axis[a] = (uint32_t)S->bins[a];
-        out->min_bounding_point[a] = S->origin[a];
-        out->max_bounding_point[a] = S->maxpt[a];
-        out->bin_size[a] = S->bin_size[a];
+        out->bins_per_axis[a] = (uint32_t)c.bins[a];
+        out->min_bounding_point[a] = c.origin[a];
+        out->max_bounding_point[a] = c.maxpt[a];
+        out->bin_size[a] = c.bin_size[a];
     }
-    out->num_bins = S->num_bins;
-    out->num_bin_aabb_intersections = S->n_intersections;
-    out->num_active_bins = S->n_active_bins;
-    out->num_possible_collisions = S->n_pairs;
-    out->num_potential_contacts = S->n_slots;
-    out->num_rigid_contacts = S->n_contacts;
-    out->ct_body_count = S->h_cnt->ct_body_count;
-    out->solver_iterations = S->nsc_iters;
-    out->solver_residual = S->nsc_residual;
-    out->solver_objective = S->nsc_objective;
+    out->num_bins = c.num_bins;
+    out->num_bin_aabb_intersections = c.n_intersections;
+    out->num_active_bins = c.n_active_bins;
+    out->num_possible_collisions = c.n_pairs;
+    out->num_potential_contacts = c.n_pairs;
+    out->num_rigid_contacts = c.n_contacts;
+    out->ct_body_count = c.ct_body_count;
+    out->solver_iterations = c.nsc_iters;
+    out->solver_residual = c.nsc_residual;
+    out->solver_objective = c.nsc_objective;
     return CB200_OK;
 }
 
@@ -514,16 +672,42 @@ int cb200_download_state(cb200_system* sys, int first, int n, double* pos, doubl
 int cb200_download_aabb(cb200_system* sys, double* aabb_min, double* aabb_max) {
     System* S = SYS(sys);
     CB_CUDA(cudaSetDevice(S->device));
-    std::vector<ShapeBP> h(S->ns);
-    CB_TRY(download(S, S->s_bp.p, h.data(), (size_t)S->ns));
-    CB_CUDA(cudaStreamSynchronize(S->stream));
-    for (uint32_t i = 0; i < S->ns; i++)
+    const size_t ns = S->ns;
+    if (ns == 0)
+        return CB200_OK;
+    std::vector<ShapeBox> box(ns);
+    std::vector<double> wpos(4 * ns);
+    std::vector<int32_t> type(ns);
+    CB_TRY(download(S, S->s_box.p, box.data(), ns));
+    CB_TRY(download(S, S->s_wpos.p, wpos.data(), 4 * ns));
+    CB_TRY(download(S, S->s_type.p, type.data(), ns));
+    CB_TRY(fetch_counters(S));
+    const double env = S->set.collision_envelope;
+    const double* org = S->h_cnt->origin;
+    for (size_t i = 0; i < ns; i++) {
+        double mn[3], mx[3];
+        if (type[i] == CB200_SPHERE) {
+            // spheres keep no box record on the device; same operations as k_aabb + OffsetAABB
+            const double r = wpos[4 * i + 3] + env;
+            for (int a = 0; a < 3; a++) {
+                mn[a] = wpos[4 * i + a] - r;
+                mx[a] = wpos[4 * i + a] + r;
+                if (S->box_relative) {
+                    mn[a] = mn[a] - org[a];
+                    mx[a] = mx[a] - org[a];
+                }
+            }
+        } else {
+            for (int a = 0; a < 3; a++)
+                mn[a] = box[i].mn[a], mx[a] = box[i].mx[a];
+        }
         for (int a = 0; a < 3; a++) {
             if (aabb_min)
-                aabb_min[3 * i + a] = h[i].mn[a];
+                aabb_min[3 * i + a] = mn[a];
             if (aabb_max)
-                aabb_max[3 * i + a] = h[i].mx[a];
+                aabb_max[3 * i + a] = mx[a];
         }
+    }
     return CB200_OK;
 }
 
@@ -531,14 +715,16 @@ int cb200_download_bins(cb200_system* sys, uint32_t* bin_number, uint32_t* bin_a
                         uint32_t* bin_start_index) {
     System* S = SYS(sys);
     CB_CUDA(cudaSetDevice(S->device));
-    if (S->n_intersections == 0)
+    CB_TRY(fetch_counters(S));
+    const uint32_t ni = S->h_cnt->n_intersections, nbins = S->h_cnt->num_bins;
+    if (ni == 0)
         return CB200_OK;
-    std::vector<uint64_t> packed(S->num_bins + 1);
-    CB_TRY(download(S, S->bin_count.p, packed.data(), packed.size()));
-    CB_TRY(download(S, S->bin_entries.p, bin_aabb_number, (size_t)S->n_intersections));
+    std::vector<uint64_t> packed((size_t)nbins + 1);
+    CB_TRY(download(S, S->bin_start.p, packed.data(), packed.size()));
+    CB_TRY(download(S, S->ent_shape.p, bin_aabb_number, (size_t)ni));
     CB_CUDA(cudaStreamSynchronize(S->stream));
     uint32_t a = 0;
-    for (uint32_t b = 0; b < S->num_bins; b++) {
+    for (uint32_t b = 0; b < nbins; b++) {
         const uint32_t s = (uint32_t)packed[b], e = (uint32_t)packed[b + 1];
         if (e == s)
             continue;
@@ -552,14 +738,25 @@ int cb200_download_bins(cb200_system* sys, uint32_t* bin_number, uint32_t* bin_a
         a++;
     }
     if (bin_start_index)
-        bin_start_index[a] = S->n_intersections;
+        bin_start_index[a] = ni;
     return CB200_OK;
 }
 
+// The candidate pair list is not part of the step (pairs are resolved into contacts on the fly); it is
+// materialised here, from the bins of the last collision stage, when somebody asks for it.
 int cb200_download_pairs(cb200_system* sys, int64_t* pairs) {
     System* S = SYS(sys);
     CB_CUDA(cudaSetDevice(S->device));
-    CB_TRY(download(S, S->pairs.p, pairs, (size_t)S->n_pairs));
+    if (S->ns == 0)
+        return CB200_OK;
+    if (!S->pairs_valid) {
+        if (!S->pairs.p)
+            CB_TRY(alloc_pairs(S, 8 * S->ns + 1024));
+        CB_TRY(run_stage(S, [&] { return enqueue_pairs_only(S, true, false); }));
+    } else {
+        CB_TRY(fetch_counters(S));
+    }
+    CB_TRY(download(S, S->pairs.p, pairs, (size_t)S->h_cnt->n_pairs));
     CB_CUDA(cudaStreamSynchronize(S->stream));
     return CB200_OK;
 }
@@ -568,7 +765,8 @@ int cb200_download_contacts(cb200_system* sys, double* normal, double* pt_a, dou
                             double* eff_radius, int32_t* body_ids, int64_t* shape_ids) {
     System* S = SYS(sys);
     CB_CUDA(cudaSetDevice(S->device));
-    const size_t nc = S->n_contacts;
+    CB_TRY(fetch_counters(S));
+    const size_t nc = S->h_cnt->n_contacts;
     CB_TRY(download(S, S->c_norm.p, normal, 3 * nc));
     CB_TRY(download(S, S->c_pta.p, pt_a, 3 * nc));
     CB_TRY(download(S, S->c_ptb.p, pt_b, 3 * nc));
@@ -583,7 +781,8 @@ int cb200_download_contacts(cb200_system* sys, double* normal, double* pt_a, dou
 int cb200_download_contact_forces(cb200_system* sys, double* ct_force, double* ct_torque) {
     System* S = SYS(sys);
     CB_CUDA(cudaSetDevice(S->device));
-    const size_t nc = S->n_contacts;
+    CB_TRY(fetch_counters(S));
+    const size_t nc = S->h_cnt->n_contacts;
     if (nc == 0)
         return CB200_OK;
     std::vector<double> f(3 * nc), t(6 * nc);
@@ -655,13 +854,13 @@ int cb200_device_array(cb200_system* sys, const char* name, void** dev_ptr, int6
     const E tab[] = {
         {"pos", S->pos.p, 3 * (int64_t)S->nb},           {"rot", S->rot.p, 4 * (int64_t)S->nb},
         {"vel", S->vel.p, 6 * (int64_t)S->nb},           {"hf", S->hf.p, 6 * (int64_t)S->nb},
-        {"mass", S->mass.p, (int64_t)S->nb},             {"contact_normal", S->c_norm.p, 3 * (int64_t)S->n_contacts},
-        {"contact_pt_a", S->c_pta.p, 3 * (int64_t)S->n_contacts},
-        {"contact_pt_b", S->c_ptb.p, 3 * (int64_t)S->n_contacts},
-        {"contact_depth", S->c_depth.p, (int64_t)S->n_contacts},
-        {"contact_body_ids", S->c_bids.p, 2 * (int64_t)S->n_contacts},
-        {"pair_shape_ids", S->pairs.p, (int64_t)S->n_pairs},
-        {"gamma", S->gamma.p, 3 * (int64_t)S->n_contacts},
+        {"mass", S->mass.p, (int64_t)S->nb},             {"contact_normal", S->c_norm.p, 3 * (int64_t)S->h_cnt->n_contacts},
+        {"contact_pt_a", S->c_pta.p, 3 * (int64_t)S->h_cnt->n_contacts},
+        {"contact_pt_b", S->c_ptb.p, 3 * (int64_t)S->h_cnt->n_contacts},
+        {"contact_depth", S->c_depth.p, (int64_t)S->h_cnt->n_contacts},
+        {"contact_body_ids", S->c_bids.p, 2 * (int64_t)S->h_cnt->n_contacts},
+        {"pair_shape_ids", S->pairs.p, (int64_t)S->h_cnt->n_pairs},
+        {"gamma", S->gamma.p, 3 * (int64_t)S->h_cnt->n_contacts},
     };
     for (const E& e : tab)
         if (n == e.k) {

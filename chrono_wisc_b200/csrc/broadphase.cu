@@ -1,94 +1,173 @@
-// broadphase.cu -- AABB generation and uniform-grid broadphase on the device.
+// broadphase.cu -- AABB generation, uniform-grid broadphase and the fused single-contact narrowphase on the device.
 //
 // Reference path replaced (CMC = src/chrono/collision/multicore):
-//   GenerateAABB                      CMC/ChCollisionSystemMulticore.cpp:458-545   -> k_aabb (+ fused bbox reduce, C1+C2,
+//   GenerateAABB                      CMC/ChCollisionSystemMulticore.cpp:458-545   -> k_aabb (+ fused bbox reduce C1+C2,
 //                                                                                   + PreprocessLocalToParent C14)
-//   ChBroadphase::DetermineBoundingBox/ComputeTopLevelResolution  CMC/ChBroadphase.cpp:142-208 -> host_grid()
+//   ChBroadphase::DetermineBoundingBox/ComputeTopLevelResolution  CMC/ChBroadphase.cpp:142-208 -> compute_grid()
+//                                       (on the device, so the step needs no host round trip)
 //   OffsetAABB + f_Count_AABB_BIN     CMC/ChBroadphase.cpp:168-176,261-268         -> k_bin_count
 //   exclusive_scan / sort_by_key / RLE CMC/ChBroadphase.cpp:271-301                -> counting sort: histogram with
-//                                       warp-aggregated atomics, packed u64 scan, scatter, per-bin rank sort
-//   f_Count/Store_AABB_AABB_Intersection  CMC/ChCollisionUtilsBroadphase.cpp:86-217 -> k_bin_pairs<false/true>
+//                                       warp-aggregated atomics, packed u64 scan, scatter, in-bin rank sort
+//   f_Count/Store_AABB_AABB_Intersection  CMC/ChCollisionUtilsBroadphase.cpp:86-217
+//   + PreprocessCount / DispatchPRIMS / remove_if  CMC/ChNarrowphase.cpp:94-155,264-320,366-385
+//                                                                                  -> k_pairs<COUNT>, k_pairs<STORE>
 //
-// Design notes: instead of sorting N_i (bin, shape) keys we histogram into a dense bin array (atomics resolve in
-// L2), scan it once (entry offsets in the low word, active-bin index in the high word), scatter, and let the warp
-// that owns a bin order its few entries by shape id.  That reproduces exactly the (bin, shape) order of the
-// reference's sort_by_key, so pair emission order -- and with it the contact order -- equals the reference's.
+// Design notes
+//  * Instead of sorting N_i (bin, shape) keys we histogram into a dense bin array (atomics resolve in L2), scan it
+//    once (entry offsets in the low word, active-bin index in the high word), scatter, and rank-sort the few entries
+//    of each bin by shape id.  That reproduces exactly the (bin, shape) order of the reference's sort_by_key, so
+//    pair emission order -- and with it the contact order -- equals the reference's.
+//  * The pair kernels give one thread to every (bin, shape) entry; a CTA stages the records of its 256-entry tile
+//    plus a forward halo in shared memory (the "neighbour-cell tile"), so the O(k^2) in-bin tests never touch
+//    global memory.  A pair that passes the broadphase filter and has a single-contact analytic test (anything
+//    against a sphere) is resolved on the spot: the candidate pair list is not written unless somebody asks for
+//    it, and contacts come out already compacted, in the reference's order (stable: bin, shape A, shape B).
+//  * Spheres carry no AABB record: (centre, radius) is 32 B and the box is recomputed with the reference's own
+//    operations, (c - (r + envelope)) - global_origin, bit for bit.
 #include "common.cuh"
+#include "prims.cuh"
 #include <float.h>
 #include <limits.h>
 #include <math.h>
 
 namespace cb200 {
 
+struct GridSettings {
+    int type;  // 0 FIXED_RESOLUTION, 1 FIXED_BIN_SIZE, 2 FIXED_DENSITY
+    int bins[3];
+    double bin_size[3];
+    double density;
+    uint32_t ns;
+    uint32_t cap_bins;
+};
+
+struct GridParams {
+    double origin[3];
+    double inv[3];
+    int bins[3];
+    uint32_t num_bins;
+};
+
+__device__ __forceinline__ GridParams load_grid(const DevCounters* __restrict__ cnt) {
+    GridParams g;
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        g.origin[a] = cnt->origin[a];
+        g.inv[a] = cnt->inv_bin_size[a];
+        g.bins[a] = cnt->bins[a];
+    }
+    g.num_bins = cnt->num_bins;
+    return g;
+}
+
 // --------------------------------------------------------------------------------------------------------------
-// k_aabb: one thread per shape.
+// per-shape integer record; rebuilt only when shapes or body flags change
 // --------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_aabb(uint32_t ns, const int32_t* __restrict__ s_type,
-                                              const uint32_t* __restrict__ s_body, const uint32_t* __restrict__ s_fam,
-                                              const int32_t* __restrict__ s_mat, const double* __restrict__ s_lpos,
-                                              const double* __restrict__ s_lrot, const double* __restrict__ s_dims,
-                                              const double* __restrict__ pos, const double* __restrict__ rot,
-                                              const uint8_t* __restrict__ bflags, double envelope,
+__global__ void __launch_bounds__(256) k_build_meta(uint32_t ns, const int32_t* __restrict__ s_type,
+                                                    const uint32_t* __restrict__ s_body,
+                                                    const uint32_t* __restrict__ s_fam,
+                                                    const int32_t* __restrict__ s_mat,
+                                                    const double* __restrict__ s_lpos,
+                                                    const uint8_t* __restrict__ bflags, ShapeMeta* __restrict__ meta) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ns; i += gridDim.x * blockDim.x) {
+        ShapeMeta m;
+        m.body = s_body[i];
+        m.fam = s_fam[i];
+        m.pad = 0;
+        const uint32_t type = (uint32_t)s_type[i] & 0xff;
+        m.info = type << 8 | ((uint32_t)s_mat[i] & 0xffff) << 16;
+        if (m.body != UINT_MAX)
+            m.info |= bflags[m.body] & 3u;
+        // bit 2: sphere centred on its body (ObA == 0): world centre == body position, no rotation needed
+        if (type == CB200_SPHERE && s_lpos[3 * i] == 0 && s_lpos[3 * i + 1] == 0 && s_lpos[3 * i + 2] == 0)
+            m.info |= 4u;
+        meta[i] = m;
+    }
+}
+
+__global__ void k_reset_counters(DevCounters* cnt, uint32_t nb, uint32_t ns) {
+    if (threadIdx.x == 0) {
+        cnt->n_bodies = nb;
+        cnt->n_shapes = ns;
+        cnt->bbox[0] = cnt->bbox[1] = cnt->bbox[2] = ~0ull;
+        cnt->bbox[3] = cnt->bbox[4] = cnt->bbox[5] = 0ull;
+        cnt->n_large = 0;
+        cnt->n_heavy = 0;
+        cnt->ct_body_count = 0;
+        cnt->unsupported = 0;
+    }
+}
+
+// --------------------------------------------------------------------------------------------------------------
+// k_aabb: one thread per shape (grid-stride).
+// --------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_aabb(uint32_t ns, const ShapeMeta* __restrict__ meta,
+                                              const double* __restrict__ s_lpos, const double* __restrict__ s_lrot,
+                                              const double* __restrict__ s_dims, const double* __restrict__ pos,
+                                              const double* __restrict__ rot, double envelope,
                                               double* __restrict__ s_wpos, double* __restrict__ s_wrot,
-                                              ShapeBP* __restrict__ s_bp, DevCounters* __restrict__ cnt) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+                                              ShapeBox* __restrict__ s_box, DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
     d3 mn = mk3(DBL_MAX), mx = mk3(-DBL_MAX);
     bool counted = false;
-    if (i < ns) {
-        const uint32_t body = s_body[i];
-        ShapeBP bp;
-        bp.body = body;
-        bp.fam = s_fam[i];
-        bp.pad = 0;
-        const int type = s_type[i];
-        bp.info = ((uint32_t)type & 0xff) << 8 | ((uint32_t)s_mat[i] & 0xffff) << 16;
-        d3 amin = mk3(0), amax = mk3(0);
-        if (body != UINT_MAX) {
-            const uint8_t bf = bflags[body];
-            bp.info |= bf & 3u;
-            const d3 p = mk3(pos[3 * body], pos[3 * body + 1], pos[3 * body + 2]);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ns; i += gridDim.x * blockDim.x) {
+        const ShapeMeta m = meta[i];
+        if (m.body == UINT_MAX)
+            continue;
+        const int type = (m.info >> 8) & 0xff;
+        const uint32_t body = m.body;
+        const d3 p = mk3(pos[3 * body], pos[3 * body + 1], pos[3 * body + 2]);
+        const double4 dm = reinterpret_cast<const double4*>(s_dims)[i];
+        d3 amin, amax;
+        bool ok = true;
+        if (m.info & 4u) {
+            // centred sphere: Rotate(0, q) + p == p
+            reinterpret_cast<double4*>(s_wpos)[i] = make_double4(p.x, p.y, p.z, dm.x);
+            const double r = dm.x + envelope;
+            amin = p - r;
+            amax = p + r;
+        } else {
             const double4 qa = reinterpret_cast<const double4*>(rot)[body];
             const q4 q = mkq(qa.x, qa.y, qa.z, qa.w);
             const d3 lp = mk3(s_lpos[3 * i], s_lpos[3 * i + 1], s_lpos[3 * i + 2]);
             const double4 la = reinterpret_cast<const double4*>(s_lrot)[i];
             const q4 lq = mkq(la.x, la.y, la.z, la.w);
-            const double4 dm = reinterpret_cast<const double4*>(s_dims)[i];
-
             const d3 wp = rotate(lp, q) + p;  // == TransformLocalToParent(p, q, lp): IEEE addition commutes
             const q4 wq = qmul(q, lq);
             reinterpret_cast<double4*>(s_wpos)[i] = make_double4(wp.x, wp.y, wp.z, dm.x);
             reinterpret_cast<double4*>(s_wrot)[i] = make_double4(wq.w, wq.x, wq.y, wq.z);
-
-            bool ok = true;
             if (type == CB200_SPHERE) {
                 const double r = dm.x + envelope;
                 amin = wp - r;
                 amax = wp + r;
-            } else if (type == CB200_ELLIPSOID || type == CB200_BOX || type == CB200_CYLINDER ||
-                       type == CB200_CYLSHELL || type == CB200_CONE) {
-                const d3 t = abs_rotate(wq, mk3(dm.x, dm.y, dm.z) + envelope);
-                amin = wp - t;
-                amax = wp + t;
-            } else if (type == CB200_ROUNDEDBOX || type == CB200_ROUNDEDCYL) {
-                const d3 t = abs_rotate(wq, mk3(dm.x, dm.y, dm.z) + dm.w + envelope);
-                amin = wp - t;
-                amax = wp + t;
-            } else if (type == CB200_CAPSULE) {
-                const d3 t = abs_rotate(wq, mk3(dm.x, dm.x + dm.y, dm.x) + envelope);
-                amin = wp - t;
-                amax = wp + t;
             } else {
-                ok = false;  // type without an AABB rule: the reference `continue`s and keeps stale values
-            }
-            if (ok && (bf & 2u)) {
-                mn = amin;
-                mx = amax;
-                counted = true;
+                d3 t = mk3(0);
+                if (type == CB200_ELLIPSOID || type == CB200_BOX || type == CB200_CYLINDER ||
+                    type == CB200_CYLSHELL || type == CB200_CONE) {
+                    t = abs_rotate(wq, mk3(dm.x, dm.y, dm.z) + envelope);
+                } else if (type == CB200_ROUNDEDBOX || type == CB200_ROUNDEDCYL) {
+                    t = abs_rotate(wq, mk3(dm.x, dm.y, dm.z) + dm.w + envelope);
+                } else if (type == CB200_CAPSULE) {
+                    t = abs_rotate(wq, mk3(dm.x, dm.x + dm.y, dm.x) + envelope);
+                } else {
+                    ok = false;  // type without an AABB rule: the reference `continue`s and keeps stale values
+                }
+                amin = wp - t;
+                amax = wp + t;
+                if (!ok)
+                    amin = amax = mk3(0);
+                ShapeBox b;
+                b.mn[0] = amin.x, b.mn[1] = amin.y, b.mn[2] = amin.z;
+                b.mx[0] = amax.x, b.mx[1] = amax.y, b.mx[2] = amax.z;
+                s_box[i] = b;
             }
         }
-        bp.mn[0] = amin.x, bp.mn[1] = amin.y, bp.mn[2] = amin.z;
-        bp.mx[0] = amax.x, bp.mx[1] = amax.y, bp.mx[2] = amax.z;
-        s_bp[i] = bp;
+        if (ok && (m.info & 2u)) {
+            mn = min3(mn, amin);
+            mx = max3(mx, amax);
+            counted = true;
+        }
     }
     // union of the AABBs of colliding shapes (BoxInvert/BoxReduce, CMC/ChBroadphase.cpp:38-100): min/max are exact
     // and order-free, so warp shuffles + ordered-integer atomics give the reference's result bit for bit.
@@ -114,117 +193,211 @@ __global__ void __launch_bounds__(256) k_aabb(uint32_t ns, const int32_t* __rest
     }
 }
 
-__global__ void k_reset_counters(DevCounters* cnt) {
-    if (threadIdx.x == 0) {
-        cnt->bbox[0] = cnt->bbox[1] = cnt->bbox[2] = ~0ull;
-        cnt->bbox[3] = cnt->bbox[4] = cnt->bbox[5] = 0ull;
-        cnt->n_large = 0;
-        cnt->n_intersections = cnt->n_active_bins = cnt->n_pairs = cnt->n_slots = cnt->n_contacts = 0;
-        cnt->multi_slot = 0;
-        cnt->n_heavy = 0;
-        cnt->ct_body_count = 0;
-        cnt->overflow = 0;
-        cnt->unsupported = 0;
+// DetermineBoundingBox + ComputeTopLevelResolution (CMC/ChBroadphase.cpp:142-208) and Compute_Grid_Resolution
+// (CMC/ChCollisionUtilsBroadphase.cpp:36-46).  Evaluated by one thread per CTA; all CTAs get the same bits.
+// (FIXED_DENSITY uses pow(): CUDA's differs from glibc's by at most 2 ulp, which can change the truncated bin count
+// only if diag * cbrt(k N / V) lies within ~1e-15 of an integer.)
+struct GridFull {
+    GridParams g;
+    double maxpt[3], bin_size[3];
+};
+__device__ GridFull compute_grid(const DevCounters* __restrict__ cnt, const GridSettings& st) {
+    GridFull G;
+    double mn[3], mx[3], diag[3];
+    const bool none = cnt->bbox[0] == ~0ull;  // no colliding shape at all
+    for (int a = 0; a < 3; a++) {
+        mn[a] = none ? 0.0 : dec_ordered(cnt->bbox[a]);
+        mx[a] = none ? 0.0 : dec_ordered(cnt->bbox[3 + a]);
+    }
+    const double fraction = 1e-3;
+    for (int a = 0; a < 3; a++) {
+        const double size = mx[a] - mn[a];
+        const double minp = mn[a] - fraction * size;
+        const double maxp = mx[a] + fraction * size;
+        G.g.origin[a] = minp;
+        G.maxpt[a] = maxp;
+        diag[a] = fabs(maxp - minp);
+    }
+    if (st.type == 0) {
+        for (int a = 0; a < 3; a++)
+            G.g.bins[a] = st.bins[a];
+    } else if (st.type == 1) {
+        for (int a = 0; a < 3; a++)
+            G.g.bins[a] = (int)ceil(diag[a] / st.bin_size[a]);
+    } else {
+        const double V = diag[0] * diag[1] * diag[2];
+        const double scale = pow(st.density * st.ns / V, 1.0 / 3.0);
+        for (int a = 0; a < 3; a++) {
+            const int v = (int)(diag[a] * scale);
+            G.g.bins[a] = v > 1 ? v : 1;
+        }
+    }
+    unsigned long long nb = 1;
+    for (int a = 0; a < 3; a++) {
+        if (G.g.bins[a] < 1)
+            G.g.bins[a] = 1;
+        G.bin_size[a] = diag[a] / (double)G.g.bins[a];
+        G.g.inv[a] = 1.0 / G.bin_size[a];
+        nb *= (unsigned long long)G.g.bins[a];
+    }
+    G.g.num_bins = nb > 0xfffffff0ull ? 0xfffffff0u : (uint32_t)nb;
+    return G;
+}
+
+// origin-relative AABB of any shape: spheres from (centre, radius), others from their box record
+__device__ __forceinline__ void shape_box_rel(uint32_t i, uint32_t info, const double* __restrict__ s_wpos,
+                                              const ShapeBox* __restrict__ s_box, const double* origin,
+                                              double envelope, double* mn, double* mx) {
+    if (((info >> 8) & 0xff) == CB200_SPHERE) {
+        const double4 w = reinterpret_cast<const double4*>(s_wpos)[i];
+        const double r = w.w + envelope;
+        mn[0] = (w.x - r) - origin[0], mn[1] = (w.y - r) - origin[1], mn[2] = (w.z - r) - origin[2];
+        mx[0] = (w.x + r) - origin[0], mx[1] = (w.y + r) - origin[1], mx[2] = (w.z + r) - origin[2];
+    } else {
+        const double2* p = reinterpret_cast<const double2*>(s_box + i);
+        const double2 a = p[0], b = p[1], c = p[2];
+        mn[0] = a.x, mn[1] = a.y, mn[2] = b.x;
+        mx[0] = b.y, mx[1] = c.x, mx[2] = c.y;
     }
 }
 
-struct GridParams {
-    double origin[3];
-    double inv[3];
-    int bins[3];
-    uint32_t num_bins;
-};
-
-__device__ __forceinline__ bool bin_range(const ShapeBP& bp, const GridParams& g, int* lo, int* hi) {
+__device__ __forceinline__ bool bin_range(const double* mn, const double* mx, const GridParams& g, int* lo, int* hi) {
     // HashMin / HashMax, CMC/ChCollisionUtils.h:44-60
-    lo[0] = (int)floor(bp.mn[0] * g.inv[0]);
-    lo[1] = (int)floor(bp.mn[1] * g.inv[1]);
-    lo[2] = (int)floor(bp.mn[2] * g.inv[2]);
-    hi[0] = (int)ceil(bp.mx[0] * g.inv[0]) - 1;
-    hi[1] = (int)ceil(bp.mx[1] * g.inv[1]) - 1;
-    hi[2] = (int)ceil(bp.mx[2] * g.inv[2]) - 1;
+    lo[0] = (int)floor(mn[0] * g.inv[0]);
+    lo[1] = (int)floor(mn[1] * g.inv[1]);
+    lo[2] = (int)floor(mn[2] * g.inv[2]);
+    hi[0] = (int)ceil(mx[0] * g.inv[0]) - 1;
+    hi[1] = (int)ceil(mx[1] * g.inv[1]) - 1;
+    hi[2] = (int)ceil(mx[2] * g.inv[2]) - 1;
     // A shape outside the grid (only possible for shapes of non-colliding bodies, which are excluded from the
     // global box) would index outside the dense histogram; it can never form a pair, so it is not binned.
     return lo[0] >= 0 && lo[1] >= 0 && lo[2] >= 0 && hi[0] < g.bins[0] && hi[1] < g.bins[1] && hi[2] < g.bins[2] &&
            hi[0] >= lo[0] && hi[1] >= lo[1] && hi[2] >= lo[2];
 }
 
-// Warp-aggregated increment: lanes that target the same counter elect a leader that adds the group size once;
-// every lane gets its own slot.  All 32 lanes must call (valid=false lanes pass through).
-__device__ __forceinline__ uint32_t warp_agg_inc(uint32_t* counters, uint32_t key, bool valid) {
+// Warp-aggregated counter update: lanes that target the same counter elect a leader that applies the group size
+// once; every lane gets its own slot.  All 32 lanes must call (valid=false lanes pass through).
+// DIR = +1: counter counts up from 0 (histogram);  DIR = -1: counts down from the histogram value (scatter).
+template <int DIR>
+__device__ __forceinline__ uint32_t warp_agg(uint32_t* counters, uint32_t key, bool valid) {
     const unsigned lane = threadIdx.x & 31;
     const unsigned grp = __match_any_sync(0xffffffffu, valid ? key : 0xffffffffu);
     const int leader = __ffs(grp) - 1;
     const unsigned rank = __popc(grp & ((1u << lane) - 1));
     uint32_t base = 0;
-    if (valid && (int)lane == leader)
-        base = atomicAdd(&counters[key], (uint32_t)__popc(grp));
+    if (valid && (int)lane == leader) {
+        const uint32_t n = (uint32_t)__popc(grp);
+        base = DIR > 0 ? atomicAdd(&counters[key], n) : atomicSub(&counters[key], n) - n;
+    }
     base = __shfl_sync(0xffffffffu, base, leader);
     return base + rank;
 }
 
 // --------------------------------------------------------------------------------------------------------------
-// k_bin_count: OffsetAABB (in place) + bins touched per shape + dense histogram.
+// k_bin_count: grid of this step + OffsetAABB (in place, non-spheres) + bins touched per shape + dense histogram.
 // --------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_bin_count(uint32_t ns, GridParams g, ShapeBP* __restrict__ s_bp,
+__global__ void __launch_bounds__(256) k_bin_count(GridSettings st, double envelope,
+                                                   const ShapeMeta* __restrict__ meta,
+                                                   const double* __restrict__ s_wpos, ShapeBox* __restrict__ s_box,
                                                    uint32_t* __restrict__ bin_intersections,
-                                                   uint32_t* __restrict__ bin_count, uint32_t* __restrict__ large_list,
+                                                   uint32_t* __restrict__ hist, uint32_t* __restrict__ large_list,
                                                    uint8_t* __restrict__ heavy, DevCounters* __restrict__ cnt) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    int lo[3] = {0, 0, 0}, hi[3] = {-1, -1, -1};
-    uint32_t n = 0;
-    if (i < ns) {
-        ShapeBP bp = s_bp[i];
-        if (bp.body != UINT_MAX) {
-            bp.mn[0] -= g.origin[0], bp.mn[1] -= g.origin[1], bp.mn[2] -= g.origin[2];
-            bp.mx[0] -= g.origin[0], bp.mx[1] -= g.origin[1], bp.mx[2] -= g.origin[2];
-            s_bp[i] = bp;
-            if (bin_range(bp, g, lo, hi))
-                n = (uint32_t)(hi[0] - lo[0] + 1) * (uint32_t)(hi[1] - lo[1] + 1) * (uint32_t)(hi[2] - lo[2] + 1);
+    __shared__ GridFull sG;
+    if (cnt->overflow)
+        return;
+    if (threadIdx.x == 0)
+        sG = compute_grid(cnt, st);
+    __syncthreads();
+    const GridParams g = sG.g;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        for (int a = 0; a < 3; a++) {
+            cnt->origin[a] = g.origin[a];
+            cnt->maxpt[a] = sG.maxpt[a];
+            cnt->bin_size[a] = sG.bin_size[a];
+            cnt->inv_bin_size[a] = g.inv[a];
+            cnt->bins[a] = g.bins[a];
         }
-        bin_intersections[i] = n;
-        if (n > LARGE_BINS) {
-            const uint32_t k = atomicAdd(&cnt->n_large, 1u);
-            if (k < MAX_LARGE)
-                large_list[k] = i;
-            else
-                cnt->overflow = 1;
-            heavy[bp.body] = 1;
+        cnt->num_bins = g.num_bins;
+        if (g.num_bins > st.cap_bins) {
+            cnt->need_bins = g.num_bins;
+            atomicOr(&cnt->overflow, (uint32_t)OVF_BINS);
         }
     }
-    const uint32_t mine = (n <= LARGE_BINS) ? n : 0;
-    uint32_t wmax = mine;
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1)
-        wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, d));
-    const int ny = hi[1] - lo[1] + 1, nz = hi[2] - lo[2] + 1;
-    for (uint32_t it = 0; it < wmax; it++) {
-        const bool valid = it < mine;
-        uint32_t b = 0;
-        if (valid) {
-            const int ix = lo[0] + (int)(it / (uint32_t)(ny * nz));
-            const int rem = (int)(it % (uint32_t)(ny * nz));
-            const int iy = lo[1] + rem / nz, iz = lo[2] + rem % nz;
-            b = (uint32_t)((iz * g.bins[1]) * g.bins[0] + iy * g.bins[0] + ix);  // Hash_Index
+    if (g.num_bins > st.cap_bins)
+        return;
+    const uint32_t ns = st.ns;
+    const uint32_t nround = (ns + 31u) & ~31u;  // whole warps stay together for the aggregated atomics
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nround; i += gridDim.x * blockDim.x) {
+        int lo[3] = {0, 0, 0}, hi[3] = {-1, -1, -1};
+        uint32_t n = 0;
+        if (i < ns) {
+            const ShapeMeta m = meta[i];
+            if (m.body != UINT_MAX) {
+                double mn[3], mx[3];
+                if (((m.info >> 8) & 0xff) == CB200_SPHERE) {
+                    shape_box_rel(i, m.info, s_wpos, s_box, g.origin, envelope, mn, mx);
+                } else {
+                    ShapeBox b = s_box[i];
+                    for (int a = 0; a < 3; a++) {
+                        mn[a] = b.mn[a] = b.mn[a] - g.origin[a];
+                        mx[a] = b.mx[a] = b.mx[a] - g.origin[a];
+                    }
+                    s_box[i] = b;
+                }
+                if (bin_range(mn, mx, g, lo, hi))
+                    n = (uint32_t)(hi[0] - lo[0] + 1) * (uint32_t)(hi[1] - lo[1] + 1) * (uint32_t)(hi[2] - lo[2] + 1);
+                if (n > LARGE_BINS) {
+                    const uint32_t k = atomicAdd(&cnt->n_large, 1u);
+                    if (k < MAX_LARGE)
+                        large_list[k] = i;
+                    else
+                        atomicOr(&cnt->overflow, (uint32_t)OVF_LARGE);
+                    heavy[m.body] = 1;
+                }
+            }
+            bin_intersections[i] = n;
         }
-        warp_agg_inc(bin_count, b, valid);
+        const uint32_t mine = (n <= LARGE_BINS) ? n : 0;
+        uint32_t wmax = mine;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1)
+            wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, d));
+        const int ny = hi[1] - lo[1] + 1, nz = hi[2] - lo[2] + 1;
+        for (uint32_t it = 0; it < wmax; it++) {
+            const bool valid = it < mine;
+            uint32_t b = 0;
+            if (valid) {
+                const int ix = lo[0] + (int)(it / (uint32_t)(ny * nz));
+                const int rem = (int)(it % (uint32_t)(ny * nz));
+                const int iy = lo[1] + rem / nz, iz = lo[2] + rem % nz;
+                b = (uint32_t)((iz * g.bins[1]) * g.bins[0] + iy * g.bins[0] + ix);  // Hash_Index
+            }
+            warp_agg<1>(hist, b, valid);
+        }
     }
 }
 
 // Shapes spanning many bins (container walls): one CTA per shape, threads stride over its bins.
 template <bool FILL>
-__global__ void __launch_bounds__(256) k_bin_large(GridParams g, const ShapeBP* __restrict__ s_bp,
+__global__ void __launch_bounds__(256) k_bin_large(const ShapeMeta* __restrict__ meta,
+                                                   const double* __restrict__ s_wpos,
+                                                   const ShapeBox* __restrict__ s_box, double envelope,
                                                    const uint32_t* __restrict__ large_list,
-                                                   const DevCounters* __restrict__ cnt,
-                                                   uint32_t* __restrict__ bin_count /* or cursor */,
-                                                   const uint64_t* __restrict__ bin_start,
-                                                   uint32_t* __restrict__ entries) {
+                                                   const DevCounters* __restrict__ cnt, uint32_t cap_entries,
+                                                   uint32_t* __restrict__ cursor, const uint64_t* __restrict__ bin_start,
+                                                   uint32_t* __restrict__ ent_tmp, uint32_t* __restrict__ ent_bin) {
+    if (cnt->overflow)
+        return;
+    const GridParams g = load_grid(cnt);
+    if (FILL && (uint32_t)bin_start[g.num_bins] > cap_entries)
+        return;
     const uint32_t nl = min(cnt->n_large, (uint32_t)MAX_LARGE);
     for (uint32_t s = blockIdx.x; s < nl; s += gridDim.x) {
         const uint32_t shape = large_list[s];
-        const ShapeBP bp = s_bp[shape];
+        double mn[3], mx[3];
+        shape_box_rel(shape, meta[shape].info, s_wpos, s_box, g.origin, envelope, mn, mx);
         int lo[3], hi[3];
-        if (!bin_range(bp, g, lo, hi))
+        if (!bin_range(mn, mx, g, lo, hi))
             continue;
         const int ny = hi[1] - lo[1] + 1, nz = hi[2] - lo[2] + 1;
         const uint32_t n = (uint32_t)(hi[0] - lo[0] + 1) * ny * nz;
@@ -233,89 +406,129 @@ __global__ void __launch_bounds__(256) k_bin_large(GridParams g, const ShapeBP* 
             const int rem = (int)(it % (uint32_t)(ny * nz));
             const int iy = lo[1] + rem / nz, iz = lo[2] + rem % nz;
             const uint32_t b = (uint32_t)((iz * g.bins[1]) * g.bins[0] + iy * g.bins[0] + ix);
-            const uint32_t slot = atomicAdd(&bin_count[b], 1u);
-            if (FILL)
-                entries[(uint32_t)bin_start[b] + slot] = shape;
+            if (FILL) {
+                const uint32_t slot = atomicSub(&cursor[b], 1u) - 1u;
+                const uint32_t e = (uint32_t)bin_start[b] + slot;
+                ent_tmp[e] = shape;
+                ent_bin[e] = b;
+            } else {
+                atomicAdd(&cursor[b], 1u);
+            }
         }
     }
 }
 
-__global__ void __launch_bounds__(256) k_bin_pack(uint32_t num_bins, const uint32_t* __restrict__ c,
-                                                  uint64_t* __restrict__ packed) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < num_bins) {
-        const uint32_t v = c[i];
-        packed[i] = (uint64_t)v | ((uint64_t)(v != 0) << 32);
-    }
-}
-
-__global__ void __launch_bounds__(256) k_bin_fill(uint32_t ns, GridParams g, const ShapeBP* __restrict__ s_bp,
+// scatter: the histogram doubles as a countdown cursor, so no second clear is needed
+__global__ void __launch_bounds__(256) k_bin_fill(uint32_t ns, double envelope, const ShapeMeta* __restrict__ meta,
+                                                  const double* __restrict__ s_wpos,
+                                                  const ShapeBox* __restrict__ s_box,
                                                   const uint32_t* __restrict__ bin_intersections,
-                                                  const uint64_t* __restrict__ bin_start,
-                                                  uint32_t* __restrict__ cursor, uint32_t* __restrict__ entries) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    int lo[3] = {0, 0, 0}, hi[3] = {-1, -1, -1};
-    uint32_t mine = 0;
-    if (i < ns) {
-        const uint32_t n = bin_intersections[i];
-        if (n != 0 && n <= LARGE_BINS) {
-            const ShapeBP bp = s_bp[i];
-            bin_range(bp, g, lo, hi);
-            mine = n;
+                                                  const uint64_t* __restrict__ bin_start, uint32_t cap_entries,
+                                                  uint32_t* __restrict__ cursor, uint32_t* __restrict__ ent_tmp,
+                                                  uint32_t* __restrict__ ent_bin, DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    const GridParams g = load_grid(cnt);
+    const uint64_t tot = bin_start[g.num_bins];
+    const uint32_t ni = (uint32_t)tot;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        cnt->n_intersections = ni;
+        cnt->n_active_bins = (uint32_t)(tot >> 32);
+        cnt->n_tiles = (ni + PAIR_TILE - 1) / PAIR_TILE;
+        if (ni > cap_entries) {
+            cnt->need_entries = ni;
+            atomicOr(&cnt->overflow, (uint32_t)OVF_ENTRIES);
         }
     }
-    uint32_t wmax = mine;
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1)
-        wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, d));
-    const int ny = hi[1] - lo[1] + 1, nz = hi[2] - lo[2] + 1;
-    for (uint32_t it = 0; it < wmax; it++) {
-        const bool valid = it < mine;
-        uint32_t b = 0;
-        if (valid) {
-            const int ix = lo[0] + (int)(it / (uint32_t)(ny * nz));
-            const int rem = (int)(it % (uint32_t)(ny * nz));
-            const int iy = lo[1] + rem / nz, iz = lo[2] + rem % nz;
-            b = (uint32_t)((iz * g.bins[1]) * g.bins[0] + iy * g.bins[0] + ix);
+    if (ni > cap_entries)
+        return;
+    const uint32_t nround = (ns + 31u) & ~31u;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nround; i += gridDim.x * blockDim.x) {
+        int lo[3] = {0, 0, 0}, hi[3] = {-1, -1, -1};
+        uint32_t mine = 0;
+        if (i < ns) {
+            const uint32_t n = bin_intersections[i];
+            if (n != 0 && n <= LARGE_BINS) {
+                double mn[3], mx[3];
+                shape_box_rel(i, meta[i].info, s_wpos, s_box, g.origin, envelope, mn, mx);
+                bin_range(mn, mx, g, lo, hi);
+                mine = n;
+            }
         }
-        const uint32_t slot = warp_agg_inc(cursor, b, valid);
-        if (valid)
-            entries[(uint32_t)bin_start[b] + slot] = i;
+        uint32_t wmax = mine;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1)
+            wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, d));
+        const int ny = hi[1] - lo[1] + 1, nz = hi[2] - lo[2] + 1;
+        for (uint32_t it = 0; it < wmax; it++) {
+            const bool valid = it < mine;
+            uint32_t b = 0;
+            if (valid) {
+                const int ix = lo[0] + (int)(it / (uint32_t)(ny * nz));
+                const int rem = (int)(it % (uint32_t)(ny * nz));
+                const int iy = lo[1] + rem / nz, iz = lo[2] + rem % nz;
+                b = (uint32_t)((iz * g.bins[1]) * g.bins[0] + iy * g.bins[0] + ix);
+            }
+            const uint32_t slot = warp_agg<-1>(cursor, b, valid);
+            if (valid) {
+                const uint32_t e = (uint32_t)bin_start[b] + slot;
+                ent_tmp[e] = i;
+                ent_bin[e] = b;
+            }
+        }
+    }
+}
+
+// rank sort of every bin's entries by shape id (ids are unique inside a bin): what the reference gets from its
+// stable sort_by_key on the bin number
+__global__ void __launch_bounds__(256) k_bin_sort(const uint32_t* __restrict__ ent_tmp,
+                                                  const uint32_t* __restrict__ ent_bin,
+                                                  const uint64_t* __restrict__ bin_start,
+                                                  uint32_t* __restrict__ ent_shape, const DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    const uint32_t ni = cnt->n_intersections;
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < ni; e += gridDim.x * blockDim.x) {
+        const uint32_t b = ent_bin[e];
+        const uint32_t s = (uint32_t)bin_start[b], t = (uint32_t)bin_start[b + 1];
+        const uint32_t id = ent_tmp[e];
+        uint32_t rank = 0;
+        for (uint32_t j = s; j < t; j++)
+            rank += ent_tmp[j] < id;
+        ent_shape[s + rank] = id;
     }
 }
 
 // --------------------------------------------------------------------------------------------------------------
-// k_bin_pairs: one warp per bin.  COUNT pass also orders the bin's entries by shape id (what the reference gets
-// from its stable sort_by_key) so both passes walk pairs in the reference's (i, k>i) order.
+// k_pairs: one thread per (bin, shape) entry, shared-memory staged tile + forward halo.
 // --------------------------------------------------------------------------------------------------------------
-struct BPRec {
-    double mn[3], mx[3];
-    uint32_t body, fam, info;
+struct __align__(16) Rec {
+    double mn[3], mx[3];  // origin-relative AABB
+    double cx, cy, cz, r; // world position + dims[0]
+    uint32_t body, fam, info, id;
 };
 
-__device__ __forceinline__ BPRec load_bp(const ShapeBP* __restrict__ s_bp, uint32_t shape) {
-    const double2* p = reinterpret_cast<const double2*>(s_bp + shape);
-    const double2 a = p[0], b = p[1], c = p[2];
-    const uint4 u = reinterpret_cast<const uint4*>(s_bp + shape)[3];
-    BPRec r;
-    r.mn[0] = a.x, r.mn[1] = a.y, r.mn[2] = b.x;
-    r.mx[0] = b.y, r.mx[1] = c.x, r.mx[2] = c.y;
-    r.body = u.x, r.fam = u.y, r.info = u.z;
-    return r;
+__device__ __forceinline__ void load_rec(Rec& R, uint32_t id, const ShapeMeta* __restrict__ meta,
+                                         const double* __restrict__ s_wpos, const ShapeBox* __restrict__ s_box,
+                                         const double* origin, double envelope) {
+    const ShapeMeta m = meta[id];
+    const double4 w = reinterpret_cast<const double4*>(s_wpos)[id];
+    R.cx = w.x, R.cy = w.y, R.cz = w.z, R.r = w.w;
+    R.body = m.body, R.fam = m.fam, R.info = m.info, R.id = id;
+    if (((m.info >> 8) & 0xff) == CB200_SPHERE) {
+        const double r = w.w + envelope;
+        R.mn[0] = (w.x - r) - origin[0], R.mn[1] = (w.y - r) - origin[1], R.mn[2] = (w.z - r) - origin[2];
+        R.mx[0] = (w.x + r) - origin[0], R.mx[1] = (w.y + r) - origin[1], R.mx[2] = (w.z + r) - origin[2];
+    } else {
+        const double2* p = reinterpret_cast<const double2*>(s_box + id);
+        const double2 a = p[0], b = p[1], c = p[2];
+        R.mn[0] = a.x, R.mn[1] = a.y, R.mn[2] = b.x;
+        R.mx[0] = b.y, R.mx[1] = c.x, R.mx[2] = c.y;
+    }
 }
 
-__device__ __forceinline__ bool pair_passes(const BPRec& A, uint32_t sA, const BPRec& B, uint32_t sB,
-                                            const GridParams& g, uint32_t bin) {
-    // filter order of CMC/ChCollisionUtilsBroadphase.cpp:114-140
-    if (B.body == UINT_MAX || sA == sB || A.body == B.body)
-        return false;
-    if (!(B.info & 2u))
-        return false;
-    if (!(A.info & 1u) && !(B.info & 1u))
-        return false;
-    const uint32_t gA = A.fam & 0xffffu, mA = A.fam >> 16, gB = B.fam & 0xffffu, mB = B.fam >> 16;
-    if (!((mA & gB) && (mB & gA)))
-        return false;
+// CMC/ChCollisionUtilsBroadphase.cpp:114-140 (a pure conjunction, so the evaluation order is free)
+__device__ __forceinline__ bool pair_passes(const Rec& A, const Rec& B, const GridParams& g, uint32_t bin) {
     if (!((A.mn[0] <= B.mx[0] && B.mn[0] <= A.mx[0]) && (A.mn[1] <= B.mx[1] && B.mn[1] <= A.mx[1]) &&
           (A.mn[2] <= B.mx[2] && B.mn[2] <= A.mx[2])))
         return false;
@@ -323,258 +536,367 @@ __device__ __forceinline__ bool pair_passes(const BPRec& A, uint32_t sA, const B
     const int cx = (int)floor(fmax(A.mn[0], B.mn[0]) * g.inv[0]);
     const int cy = (int)floor(fmax(A.mn[1], B.mn[1]) * g.inv[1]);
     const int cz = (int)floor(fmax(A.mn[2], B.mn[2]) * g.inv[2]);
-    return (uint32_t)((cz * g.bins[1]) * g.bins[0] + cy * g.bins[0] + cx) == bin;
+    if ((uint32_t)((cz * g.bins[1]) * g.bins[0] + cy * g.bins[0] + cx) != bin)
+        return false;
+    if (B.body == UINT_MAX || A.body == B.body)
+        return false;
+    if (!(B.info & 2u))
+        return false;
+    if (!(A.info & 1u) && !(B.info & 1u))
+        return false;
+    const uint32_t gA = A.fam & 0xffffu, mA = A.fam >> 16, gB = B.fam & 0xffffu, mB = B.fam >> 16;
+    return (mA & gB) && (mB & gA);
 }
+
+struct ShapeView {
+    int type;
+    d3 pos;
+    q4 rot;
+    double d0, d1, d2, d3_;
+};
+
+__device__ __forceinline__ ShapeView view_of(const Rec& R, const double* __restrict__ s_wrot,
+                                             const double* __restrict__ s_dims) {
+    ShapeView v;
+    v.type = (R.info >> 8) & 0xff;
+    v.pos = mk3(R.cx, R.cy, R.cz);
+    v.d0 = R.r;
+    v.d1 = v.d2 = v.d3_ = 0;
+    v.rot = mkq(1, 0, 0, 0);
+    if (v.type != CB200_SPHERE) {
+        const double4 r = reinterpret_cast<const double4*>(s_wrot)[R.id];
+        v.rot = mkq(r.x, r.y, r.z, r.w);
+        const double4 d = reinterpret_cast<const double4*>(s_dims)[R.id];
+        v.d1 = d.y, v.d2 = d.z, v.d3_ = d.w;
+    }
+    return v;
+}
+
+// Analytic dispatcher for pairs with at most one contact (everything that involves a sphere),
+// PRIMSCollision, CMC/ChNarrowphasePRIMS.cpp:1406-1607.
+// Returns 1/0 contacts, or -1 when the combination is not of that kind (multi-contact analytic pair or MPR).
+__device__ __forceinline__ int prims_single(const ShapeView& A, const ShapeView& B, double sep, Contact& c) {
+    bool hit;
+    if (A.type == CB200_SPHERE && B.type == CB200_SPHERE)
+        return sphere_sphere(A.pos, A.d0, B.pos, B.d0, sep, c) ? 1 : 0;
+    if (B.type == CB200_SPHERE) {
+        switch (A.type) {
+            case CB200_CAPSULE:
+                return capsule_sphere(A.pos, A.rot, A.d0, A.d1, B.pos, B.d0, sep, c) ? 1 : 0;
+            case CB200_CYLINDER:
+                return cylinder_sphere(A.pos, A.rot, A.d0, A.d1, B.pos, B.d0, sep, c) ? 1 : 0;
+            case CB200_ROUNDEDCYL:
+                return roundedcyl_sphere(A.pos, A.rot, A.d0, A.d1, A.d3_, B.pos, B.d0, sep, c) ? 1 : 0;
+            case CB200_BOX:
+                return box_sphere(A.pos, A.rot, mk3(A.d0, A.d1, A.d2), B.pos, B.d0, sep, c) ? 1 : 0;
+            case CB200_ROUNDEDBOX:
+                return roundedbox_sphere(A.pos, A.rot, mk3(A.d0, A.d1, A.d2), A.d3_, B.pos, B.d0, sep, c) ? 1 : 0;
+            default:
+                return -1;
+        }
+    }
+    if (A.type == CB200_SPHERE) {
+        // swapped call: the shape function sees (B, A); points are exchanged and the normal negated
+        // (ChNarrowphasePRIMS.cpp:1435-1443 and siblings)
+        switch (B.type) {
+            case CB200_CAPSULE:
+                hit = capsule_sphere(B.pos, B.rot, B.d0, B.d1, A.pos, A.d0, sep, c);
+                break;
+            case CB200_CYLINDER:
+                hit = cylinder_sphere(B.pos, B.rot, B.d0, B.d1, A.pos, A.d0, sep, c);
+                break;
+            case CB200_ROUNDEDCYL:
+                hit = roundedcyl_sphere(B.pos, B.rot, B.d0, B.d1, B.d3_, A.pos, A.d0, sep, c);
+                break;
+            case CB200_BOX:
+                hit = box_sphere(B.pos, B.rot, mk3(B.d0, B.d1, B.d2), A.pos, A.d0, sep, c);
+                break;
+            case CB200_ROUNDEDBOX:
+                hit = roundedbox_sphere(B.pos, B.rot, mk3(B.d0, B.d1, B.d2), B.d3_, A.pos, A.d0, sep, c);
+                break;
+            default:
+                return -1;
+        }
+        if (hit) {
+            const d3 t = c.p1;
+            c.p1 = c.p2;
+            c.p2 = t;
+            c.n = -c.n;
+            return 1;
+        }
+        return 0;
+    }
+    return -1;
+}
+
+template <typename T>
+__device__ __forceinline__ T warp_incl_scan_bp(T v, int lane) {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        T o = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d)
+            v += o;
+    }
+    return v;
+}
+
+struct PairOut {
+    int64_t* pairs;  // null: candidate pair list not materialised
+    double *c_norm, *c_pta, *c_ptb, *c_depth, *c_erad;  // c_norm null: contacts not materialised
+    int32_t* c_bids;
+    int64_t* c_shapes;
+    uint32_t* c_mats;
+    uint32_t cap_pairs, cap_contacts;
+};
 
 template <bool STORE>
-__global__ void __launch_bounds__(256) k_bin_pairs(GridParams g, const ShapeBP* __restrict__ s_bp,
-                                                   const uint64_t* __restrict__ bin_start,
-                                                   const uint32_t* __restrict__ entries_tmp,
-                                                   uint32_t* __restrict__ entries, uint32_t* __restrict__ pair_count,
-                                                   int64_t* __restrict__ pairs, PairAux* __restrict__ aux,
-                                                   DevCounters* __restrict__ cnt) {
-    const uint32_t bin = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const unsigned lane = threadIdx.x & 31;
-    if (bin >= g.num_bins)
+__global__ void __launch_bounds__(PAIR_TILE) k_pairs(const ShapeMeta* __restrict__ meta,
+                                                     const double* __restrict__ s_wpos,
+                                                     const ShapeBox* __restrict__ s_box,
+                                                     const double* __restrict__ s_wrot,
+                                                     const double* __restrict__ s_dims,
+                                                     const uint32_t* __restrict__ ent_shape,
+                                                     const uint32_t* __restrict__ ent_bin,
+                                                     const uint64_t* __restrict__ bin_start, double envelope,
+                                                     int algorithm, uint64_t* __restrict__ ent_count,
+                                                     uint64_t* __restrict__ tile_count, PairOut out,
+                                                     DevCounters* __restrict__ cnt) {
+    __shared__ Rec win[PAIR_TILE + PAIR_HALO];
+    __shared__ uint64_t wsum[PAIR_TILE / 32 + 1];
+    if (cnt->overflow)
         return;
-    const uint32_t start = (uint32_t)bin_start[bin];
-    const uint32_t k = (uint32_t)bin_start[bin + 1] - start;
-    if (k == 0) {
-        if (!STORE && lane == 0)
-            pair_count[bin] = 0;
-        return;
-    }
-    if (!STORE) {
-        // rank sort by shape id (ids are unique inside a bin)
-        for (uint32_t e = lane; e < k; e += 32) {
-            const uint32_t id = entries_tmp[start + e];
-            uint32_t rank = 0;
-            for (uint32_t j = 0; j < k; j++)
-                rank += entries_tmp[start + j] < id;
-            entries[start + rank] = id;
+    const GridParams g = load_grid(cnt);
+    const uint32_t ni = cnt->n_intersections;
+    const uint32_t ntiles = cnt->n_tiles;
+    const double sep = 2 * envelope;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+
+    if (STORE) {
+        const uint64_t tot = tile_count[ntiles];
+        const uint32_t np = (uint32_t)tot, nc = (uint32_t)(tot >> 32);
+        bool bad = false;
+        if (out.c_norm && nc > out.cap_contacts)
+            bad = true;
+        if (out.pairs && np > out.cap_pairs)
+            bad = true;
+        if (blockIdx.x == 0 && threadIdx.x == 0) {
+            cnt->n_pairs = np;
+            cnt->n_contacts = nc;
+            if (out.c_norm && nc > out.cap_contacts) {
+                cnt->need_contacts = nc;
+                atomicOr(&cnt->overflow, (uint32_t)OVF_CONTACTS);
+            }
+            if (out.pairs && np > out.cap_pairs) {
+                cnt->need_pairs = np;
+                atomicOr(&cnt->overflow, (uint32_t)OVF_PAIRS);
+            }
         }
-        __syncwarp();
-        if (k == 1) {
-            if (lane == 0)
-                pair_count[bin] = 0;
+        if (bad)
             return;
-        }
-    } else if (k == 1) {
-        return;
     }
 
-    uint32_t out = STORE ? pair_count[bin] : 0;  // exclusive offset in STORE, running count otherwise
-    const unsigned lt = (1u << lane) - 1;
-    bool multi = false;
+    for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const uint32_t e0 = tile * PAIR_TILE;
+        const uint32_t wend = min(ni, e0 + PAIR_TILE + PAIR_HALO);
+        __syncthreads();  // previous tile's readers are done with the window
+        for (uint32_t k = threadIdx.x; e0 + k < wend; k += PAIR_TILE)
+            load_rec(win[k], ent_shape[e0 + k], meta, s_wpos, s_box, g.origin, envelope);
+        __syncthreads();
 
-    if (k <= 32) {
-        // fast path: lane j keeps entry j in registers, entry i arrives by a uniform (broadcast) load
-        uint32_t sB = 0;
-        BPRec B;
-        if (lane < k) {
-            sB = entries[start + lane];
-            B = load_bp(s_bp, sB);
+        const uint32_t e = e0 + threadIdx.x;
+        uint32_t np = 0, nc = 0, ncx = 0;
+        uint32_t bin = 0, bend = 0;
+        uint32_t o_pair = 0, o_con = 0;
+        if (e < ni) {
+            bin = ent_bin[e];
+            bend = (uint32_t)bin_start[bin + 1];
         }
-        for (uint32_t i = 0; i + 1 < k; i++) {
-            const uint32_t sA = entries[start + i];
-            const BPRec A = load_bp(s_bp, sA);
-            if (A.body == UINT_MAX || !(A.info & 2u))
-                continue;
-            const bool hit = (lane > i && lane < k) && pair_passes(A, sA, B, sB, g, bin);
-            const unsigned bal = __ballot_sync(0xffffffffu, hit);
-            if (STORE && hit) {
-                const uint32_t o = out + __popc(bal & lt);
-                pairs[o] = ((int64_t)sA << 32) | (int64_t)sB;
-                PairAux a;
-                a.bodyA = A.body, a.bodyB = B.body;
-                const uint32_t tA = (A.info >> 8) & 0xff, tB = (B.info >> 8) & 0xff;
-                a.types = tA | tB << 8;
-                a.mats = (A.info >> 16) | (B.info >> 16) << 16;
-                aux[o] = a;
-                multi |= (tA != CB200_SPHERE && tB != CB200_SPHERE);
+        if (STORE) {
+            // exclusive offsets of this thread's outputs: tile offset + in-tile scan of the counts of pass 1
+            const uint64_t mine = (e < ni) ? ent_count[e] : 0ull;
+            uint64_t incl = warp_incl_scan_bp(mine, lane);
+            if (lane == 31)
+                wsum[wid] = incl;
+            __syncthreads();
+            if (wid == 0) {
+                uint64_t w = (lane < PAIR_TILE / 32) ? wsum[lane] : 0ull;
+                uint64_t wi = warp_incl_scan_bp(w, lane);
+                if (lane < PAIR_TILE / 32)
+                    wsum[lane] = wi - w;
             }
-            out += __popc(bal);
+            __syncthreads();
+            const uint64_t off = tile_count[tile] + wsum[wid] + incl - mine;
+            o_pair = (uint32_t)off;
+            o_con = (uint32_t)(off >> 32);
         }
-    } else {
-        for (uint32_t i = 0; i + 1 < k; i++) {
-            const uint32_t sA = entries[start + i];
-            const BPRec A = load_bp(s_bp, sA);
-            if (A.body == UINT_MAX || !(A.info & 2u))
-                continue;
-            for (uint32_t j0 = i + 1; j0 < k; j0 += 32) {
-                const uint32_t j = j0 + lane;
-                bool hit = false;
-                uint32_t sB = 0;
-                BPRec B;
-                if (j < k) {
-                    sB = entries[start + j];
-                    B = load_bp(s_bp, sB);
-                    hit = pair_passes(A, sA, B, sB, g, bin);
+        if (e < ni) {
+            const Rec& A = win[threadIdx.x];
+            const bool a_ok = A.body != UINT_MAX && (A.info & 2u);
+            if (a_ok) {
+                for (uint32_t j = e + 1; j < bend; j++) {
+                    Rec Bg;
+                    const Rec* Bp;
+                    if (j < wend) {
+                        Bp = &win[j - e0];
+                    } else {  // bin longer than the halo (coarse grids): fall back to global memory
+                        load_rec(Bg, ent_shape[j], meta, s_wpos, s_box, g.origin, envelope);
+                        Bp = &Bg;
+                    }
+                    const Rec& B = *Bp;
+                    if (!pair_passes(A, B, g, bin))
+                        continue;
+                    if (STORE && out.pairs)
+                        out.pairs[o_pair + np] = ((int64_t)A.id << 32) | (int64_t)B.id;
+                    np++;
+                    // fused narrowphase (single-contact analytic pairs), CMC/ChNarrowphase.cpp:264-320
+                    const int tA = (A.info >> 8) & 0xff, tB = (B.info >> 8) & 0xff;
+                    Contact c;
+                    int n = -1;
+                    if (algorithm != 0) {
+                        if (tA == CB200_SPHERE && tB == CB200_SPHERE)
+                            n = sphere_sphere(mk3(A.cx, A.cy, A.cz), A.r, mk3(B.cx, B.cy, B.cz), B.r, sep, c) ? 1 : 0;
+                        else
+                            n = prims_single(view_of(A, s_wrot, s_dims), view_of(B, s_wrot, s_dims), sep, c);
+                    }
+                    if (n < 0) {
+                        ncx++;
+                    } else if (n == 1) {
+                        if (STORE && out.c_norm) {
+                            const uint32_t o = o_con + nc;
+                            out.c_norm[3 * o] = c.n.x, out.c_norm[3 * o + 1] = c.n.y, out.c_norm[3 * o + 2] = c.n.z;
+                            out.c_pta[3 * o] = c.p1.x, out.c_pta[3 * o + 1] = c.p1.y, out.c_pta[3 * o + 2] = c.p1.z;
+                            out.c_ptb[3 * o] = c.p2.x, out.c_ptb[3 * o + 1] = c.p2.y, out.c_ptb[3 * o + 2] = c.p2.z;
+                            out.c_depth[o] = c.depth;
+                            out.c_erad[o] = c.erad;
+                            out.c_bids[2 * o] = (int32_t)A.body;
+                            out.c_bids[2 * o + 1] = (int32_t)B.body;
+                            out.c_shapes[o] = ((int64_t)A.id << 32) | (int64_t)B.id;
+                            out.c_mats[o] = (A.info >> 16) | (B.info >> 16) << 16;
+                        }
+                        nc++;
+                    }
                 }
-                const unsigned bal = __ballot_sync(0xffffffffu, hit);
-                if (STORE && hit) {
-                    const uint32_t o = out + __popc(bal & lt);
-                    pairs[o] = ((int64_t)sA << 32) | (int64_t)sB;
-                    PairAux a;
-                    a.bodyA = A.body, a.bodyB = B.body;
-                    const uint32_t tA = (A.info >> 8) & 0xff, tB = (B.info >> 8) & 0xff;
-                    a.types = tA | tB << 8;
-                    a.mats = (A.info >> 16) | (B.info >> 16) << 16;
-                    aux[o] = a;
-                    multi |= (tA != CB200_SPHERE && tB != CB200_SPHERE);
-                }
-                out += __popc(bal);
             }
         }
-    }
-    if (!STORE) {
-        if (lane == 0)
-            pair_count[bin] = out;
-    } else if (__any_sync(0xffffffffu, multi) && lane == 0) {
-        cnt->multi_slot = 1;
+        if (!STORE) {
+            const uint64_t mine = (uint64_t)np | ((uint64_t)nc << 32);
+            if (e < ni)
+                ent_count[e] = mine;
+            uint64_t s = mine;
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1)
+                s += __shfl_xor_sync(0xffffffffu, s, d);
+            if (lane == 0)
+                wsum[wid] = s;
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                uint64_t t = 0;
+                for (int w = 0; w < PAIR_TILE / 32; w++)
+                    t += wsum[w];
+                tile_count[tile] = t;
+            }
+            if (ncx)
+                atomicAdd(&cnt->unsupported, ncx);
+        }
     }
 }
 
 // --------------------------------------------------------------------------------------------------------------
-// host side
+// host side: enqueue only, no synchronisation
 // --------------------------------------------------------------------------------------------------------------
-
-// DetermineBoundingBox + ComputeTopLevelResolution (CMC/ChBroadphase.cpp:142-208) and Compute_Grid_Resolution
-// (CMC/ChCollisionUtilsBroadphase.cpp:36-46), evaluated on the host with the same libm the reference uses.
-static void host_grid(System* S, const double* mn, const double* mx) {
-    const double fraction = 1e-3;
-    double minp[3], maxp[3], diag[3];
-    for (int a = 0; a < 3; a++) {
-        const double size = mx[a] - mn[a];
-        minp[a] = mn[a] - fraction * size;
-        maxp[a] = mx[a] + fraction * size;
-        S->origin[a] = minp[a];
-        S->maxpt[a] = maxp[a];
-        diag[a] = fabs(maxp[a] - minp[a]);
-    }
-    const cb200_settings& st = S->set;
-    if (st.broadphase_grid == 0) {
-        for (int a = 0; a < 3; a++)
-            S->bins[a] = st.bins_per_axis[a];
-    } else if (st.broadphase_grid == 1) {
-        for (int a = 0; a < 3; a++)
-            S->bins[a] = (int)std::ceil(diag[a] / st.bin_size[a]);
-    } else {
-        const double V = diag[0] * diag[1] * diag[2];
-        const double k = st.grid_density;
-        const unsigned num_aabb = S->ns;
-        for (int a = 0; a < 3; a++) {
-            int v = int(diag[a] * std::pow(k * num_aabb / V, 1.0 / 3.0));
-            S->bins[a] = v > 1 ? v : 1;
-        }
-    }
-    for (int a = 0; a < 3; a++) {
-        if (S->bins[a] < 1)
-            S->bins[a] = 1;
-        S->bin_size[a] = diag[a] / (double)S->bins[a];
-        S->inv_bin_size[a] = 1.0 / S->bin_size[a];
-    }
-}
-
-static GridParams grid_params(const System* S) {
-    GridParams g;
-    for (int a = 0; a < 3; a++) {
-        g.origin[a] = S->origin[a];
-        g.inv[a] = S->inv_bin_size[a];
-        g.bins[a] = S->bins[a];
-    }
-    g.num_bins = S->num_bins;
-    return g;
-}
-
-int stage_aabb(System* S) {
+int enqueue_aabb(System* S) {
     if (S->ns == 0)
         return CB200_OK;
-    k_reset_counters<<<1, 32, 0, S->stream>>>(S->d_cnt);
+    if (S->meta_dirty) {
+        k_build_meta<<<grid_for(S, S->ns, 256), 256, 0, S->stream>>>(S->ns, S->s_type.p, S->s_body.p, S->s_fam.p,
+                                                                     S->s_mat.p, S->s_lpos.p, S->bflags.p,
+                                                                     S->s_meta.p);
+        S->meta_dirty = false;
+        S->launches++;
+    }
+    k_reset_counters<<<1, 32, 0, S->stream>>>(S->d_cnt, S->nb, S->ns);
     CB_CUDA(cudaMemsetAsync(S->heavy.p, 0, S->nb, S->stream));
-    k_aabb<<<blocks_for(S->ns, 256), 256, 0, S->stream>>>(S->ns, S->s_type.p, S->s_body.p, S->s_fam.p, S->s_mat.p,
-                                                          S->s_lpos.p, S->s_lrot.p, S->s_dims.p, S->pos.p, S->rot.p,
-                                                          S->bflags.p, S->set.collision_envelope, S->s_wpos.p,
-                                                          S->s_wrot.p, S->s_bp.p, S->d_cnt);
+    k_aabb<<<grid_for(S, S->ns, 256), 256, 0, S->stream>>>(S->ns, S->s_meta.p, S->s_lpos.p, S->s_lrot.p, S->s_dims.p,
+                                                           S->pos.p, S->rot.p, S->set.collision_envelope, S->s_wpos.p,
+                                                           S->s_wrot.p, S->s_box.p, S->d_cnt);
     S->launches += 2;
+    S->pairs_valid = false;
+    S->box_relative = false;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;
 }
 
-int stage_broadphase(System* S) {
-    S->n_pairs = S->n_intersections = S->n_active_bins = 0;
+int enqueue_pairs_only(System* S, bool want_pairs, bool want_contacts) {
     if (S->ns == 0)
         return CB200_OK;
-    // sync point 1: global bounding box -> grid (host libm pow for FIXED_DENSITY)
-    CB_TRY(fetch_counters(S));
-    double mn[3], mx[3];
-    for (int a = 0; a < 3; a++) {
-        mn[a] = dec_ordered(S->h_cnt->bbox[a]);
-        mx[a] = dec_ordered(S->h_cnt->bbox[3 + a]);
+    const double env = S->set.collision_envelope;
+    const int algorithm = S->set.narrowphase_algorithm;
+    PairOut out;
+    memset(&out, 0, sizeof(out));
+    out.cap_pairs = S->cap_pairs;
+    out.cap_contacts = S->cap_contacts;
+    const int grid = grid_for(S, S->cap_entries, PAIR_TILE, 6);
+    k_pairs<false><<<grid, PAIR_TILE, 0, S->stream>>>(S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p,
+                                                      S->ent_shape.p, S->ent_bin.p, S->bin_start.p, env, algorithm,
+                                                      S->ent_count.p, S->tile_count.p, out, S->d_cnt);
+    S->launches++;
+    CB_TRY(scan_u64(S, S->tile_count.p, S->tile_count.p, &S->d_cnt->n_tiles, S->cap_entries / PAIR_TILE + 1));
+    if (want_pairs)
+        out.pairs = S->pairs.p;
+    if (want_contacts) {
+        out.c_norm = S->c_norm.p, out.c_pta = S->c_pta.p, out.c_ptb = S->c_ptb.p, out.c_depth = S->c_depth.p;
+        out.c_erad = S->c_erad.p, out.c_bids = S->c_bids.p, out.c_shapes = S->c_shapes.p, out.c_mats = S->c_mats.p;
     }
-    if (S->h_cnt->bbox[0] == ~0ull) {  // no colliding shape at all
-        for (int a = 0; a < 3; a++)
-            mn[a] = mx[a] = 0;
-    }
-    host_grid(S, mn, mx);
-    const uint64_t nbins64 = (uint64_t)S->bins[0] * S->bins[1] * S->bins[2];
-    if (nbins64 > (1ull << 27))
-        return set_error(CB200_ERR_UNSUPPORTED, "broadphase grid has more than 2^27 bins");
-    S->num_bins = (uint32_t)nbins64;
-    const GridParams g = grid_params(S);
-
-    CB_TRY(S->bin_intersections.reserve(S->ns + 1));
-    CB_TRY(S->bin_count.reserve(S->num_bins + 1));
-    CB_TRY(S->bin_cursor.reserve(S->num_bins + 1));
-    CB_TRY(S->pair_count.reserve(S->num_bins + 1));
-    CB_TRY(S->large_list.reserve(MAX_LARGE));
-
-    // histogram (bin_cursor doubles as the 32-bit histogram, then as the scatter cursor)
-    CB_CUDA(cudaMemsetAsync(S->bin_cursor.p, 0, (size_t)S->num_bins * 4, S->stream));
-    k_bin_count<<<blocks_for(S->ns, 256), 256, 0, S->stream>>>(S->ns, g, S->s_bp.p, S->bin_intersections.p,
-                                                               S->bin_cursor.p, S->large_list.p, S->heavy.p, S->d_cnt);
-    k_bin_large<false><<<64, 256, 0, S->stream>>>(g, S->s_bp.p, S->large_list.p, S->d_cnt, S->bin_cursor.p, nullptr,
-                                                  nullptr);
-    k_bin_pack<<<blocks_for(S->num_bins, 256), 256, 0, S->stream>>>(S->num_bins, S->bin_cursor.p, S->bin_count.p);
-    S->launches += 3;
-    CB_TRY(scan_u64(S, S->bin_count.p, S->bin_count.p, S->num_bins));
-    // sync point 2: N_i / N_a size the entry arrays
-    uint64_t tot = 0;
-    CB_CUDA(cudaMemcpyAsync(&tot, S->bin_count.p + S->num_bins, 8, cudaMemcpyDeviceToHost, S->stream));
-    CB_CUDA(cudaStreamSynchronize(S->stream));
-    S->n_intersections = (uint32_t)tot;
-    S->n_active_bins = (uint32_t)(tot >> 32);
-    if (S->n_intersections == 0)
-        return CB200_OK;
-    CB_TRY(S->bin_entries_tmp.reserve(S->n_intersections));
-    CB_TRY(S->bin_entries.reserve(S->n_intersections));
-
-    CB_CUDA(cudaMemsetAsync(S->bin_cursor.p, 0, (size_t)S->num_bins * 4, S->stream));
-    k_bin_fill<<<blocks_for(S->ns, 256), 256, 0, S->stream>>>(S->ns, g, S->s_bp.p, S->bin_intersections.p,
-                                                              S->bin_count.p, S->bin_cursor.p, S->bin_entries_tmp.p);
-    k_bin_large<true><<<64, 256, 0, S->stream>>>(g, S->s_bp.p, S->large_list.p, S->d_cnt, S->bin_cursor.p,
-                                                 S->bin_count.p, S->bin_entries_tmp.p);
-    const int pair_blocks = blocks_for((size_t)S->num_bins * 32, 256);
-    k_bin_pairs<false><<<pair_blocks, 256, 0, S->stream>>>(g, S->s_bp.p, S->bin_count.p, S->bin_entries_tmp.p,
-                                                           S->bin_entries.p, S->pair_count.p, nullptr, nullptr,
-                                                           S->d_cnt);
-    S->launches += 3;
-    CB_TRY(scan_u32(S, S->pair_count.p, S->pair_count.p, S->num_bins));
-    // sync point 3: N_p sizes the pair list
-    uint32_t np = 0;
-    CB_CUDA(cudaMemcpyAsync(&np, S->pair_count.p + S->num_bins, 4, cudaMemcpyDeviceToHost, S->stream));
-    CB_CUDA(cudaStreamSynchronize(S->stream));
-    S->n_pairs = np;
-    if (np == 0)
-        return CB200_OK;
-    CB_TRY(S->pairs.reserve(np));
-    CB_TRY(S->pair_aux.reserve(np));
-    k_bin_pairs<true><<<pair_blocks, 256, 0, S->stream>>>(g, S->s_bp.p, S->bin_count.p, S->bin_entries_tmp.p,
-                                                          S->bin_entries.p, S->pair_count.p, S->pairs.p,
-                                                          S->pair_aux.p, S->d_cnt);
-    S->launches += 1;
+    k_pairs<true><<<grid, PAIR_TILE, 0, S->stream>>>(S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p,
+                                                     S->ent_shape.p, S->ent_bin.p, S->bin_start.p, env, algorithm,
+                                                     S->ent_count.p, S->tile_count.p, out, S->d_cnt);
+    S->launches++;
+    if (want_pairs)
+        S->pairs_valid = true;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;
+}
+
+int enqueue_bins(System* S) {
+    if (S->ns == 0)
+        return CB200_OK;
+    const cb200_settings& st = S->set;
+    GridSettings gs;
+    gs.type = st.broadphase_grid;
+    for (int a = 0; a < 3; a++) {
+        gs.bins[a] = st.bins_per_axis[a];
+        gs.bin_size[a] = st.bin_size[a];
+    }
+    gs.density = st.grid_density;
+    gs.ns = S->ns;
+    gs.cap_bins = S->cap_bins;
+    const double env = st.collision_envelope;
+    const int sgrid = grid_for(S, S->ns, 256);
+    S->box_relative = true;
+
+    CB_CUDA(cudaMemsetAsync(S->bin_cursor.p, 0, (size_t)S->cap_bins * 4, S->stream));
+    k_bin_count<<<sgrid, 256, 0, S->stream>>>(gs, env, S->s_meta.p, S->s_wpos.p, S->s_box.p, S->bin_intersections.p,
+                                              S->bin_cursor.p, S->large_list.p, S->heavy.p, S->d_cnt);
+    k_bin_large<false><<<64, 256, 0, S->stream>>>(S->s_meta.p, S->s_wpos.p, S->s_box.p, env, S->large_list.p, S->d_cnt,
+                                                  S->cap_entries, S->bin_cursor.p, nullptr, nullptr, nullptr);
+    S->launches += 2;
+    CB_TRY(scan_bins(S, S->bin_cursor.p, S->bin_start.p, &S->d_cnt->num_bins, S->cap_bins));
+    k_bin_fill<<<sgrid, 256, 0, S->stream>>>(S->ns, env, S->s_meta.p, S->s_wpos.p, S->s_box.p, S->bin_intersections.p,
+                                             S->bin_start.p, S->cap_entries, S->bin_cursor.p, S->ent_tmp.p,
+                                             S->ent_bin.p, S->d_cnt);
+    k_bin_large<true><<<64, 256, 0, S->stream>>>(S->s_meta.p, S->s_wpos.p, S->s_box.p, env, S->large_list.p, S->d_cnt,
+                                                 S->cap_entries, S->bin_cursor.p, S->bin_start.p, S->ent_tmp.p,
+                                                 S->ent_bin.p);
+    k_bin_sort<<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(S->ent_tmp.p, S->ent_bin.p, S->bin_start.p,
+                                                                        S->ent_shape.p, S->d_cnt);
+    S->launches += 3;
+    CB_CUDA(cudaGetLastError());
+    return CB200_OK;
+}
+
+int enqueue_broadphase(System* S, bool want_pairs, bool want_contacts) {
+    CB_TRY(enqueue_bins(S));
+    return enqueue_pairs_only(S, want_pairs, want_contacts);
 }
 
 }  // namespace cb200

@@ -1,13 +1,21 @@
 // common.cuh -- device buffers, error plumbing and the device-resident system state.
 //
 // Replaces the reference's struct-of-std::vector data contract (host_container, MC/ChDataManager.h:204-324, and
-// ChCollisionData, CMC/ChCollisionData.h:89-222) with persistent device SoA arrays sized by high-water marks.
+// ChCollisionData, CMC/ChCollisionData.h:89-222) with persistent device SoA arrays.
+//
+// Execution model ("device-driven step"): every count the reference keeps on the host (N_i, N_a, N_p, N_c, the grid)
+// lives in one DevCounters block in device memory.  Kernels read their extents from it and run grid-stride, so a whole
+// DoStepDynamics is enqueued without a single host synchronisation.  Output arrays have capacities; a kernel that
+// would exceed one raises the sticky `overflow` mask and records the size it needed, every later kernel of the
+// stream then returns immediately (state is never advanced with incomplete lists), and the host -- at its one sync
+// at the end of cb200_do_steps or of a stage call -- grows the arrays and re-enqueues the steps that did not run.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <string>
 #include <vector>
 #include <map>
+#include <utility>
 
 #include "../../include/chrono_b200.h"
 #include "vmath.cuh"
@@ -61,53 +69,64 @@ struct DevBuf {
     }
 };
 
-// Per-shape broadphase record (64 B, two sectors): AABB (relative to global_origin once OffsetAABB has run,
-// CMC/ChBroadphase.cpp:168-176) + everything the per-bin pair filter needs
-// (CMC/ChCollisionUtilsBroadphase.cpp:86-146), so a pair test costs one gather per shape.
-struct __align__(16) ShapeBP {
+// Per-shape AABB record (48 B): absolute after the AABB stage, relative to global_origin once the binning has run
+// (OffsetAABB, CMC/ChBroadphase.cpp:168-176).
+struct __align__(16) ShapeBox {
     double mn[3];
     double mx[3];
+};
+
+// Per-shape integer record (16 B) holding everything the per-bin pair filter needs
+// (CMC/ChCollisionUtilsBroadphase.cpp:86-146), so a pair test costs one gather per shape.
+struct __align__(16) ShapeMeta {
     uint32_t body;   // id_rigid (UINT_MAX = removed)
     uint32_t fam;    // group | mask << 16
     uint32_t info;   // bit0 body active, bit1 body collide, bits 8..15 shape type, bits 16..31 material id
     uint32_t pad;
 };
-static_assert(sizeof(ShapeBP) == 64, "ShapeBP must be 64 bytes");
 
-// Per-pair side data written with the pair list so that the narrowphase never gathers per-shape integers.
-struct __align__(16) PairAux {
-    uint32_t bodyA, bodyB;
-    uint32_t types;  // typeA | typeB << 8
-    uint32_t mats;   // matA | matB << 16
-};
+// overflow mask bits
+enum { OVF_BINS = 1, OVF_ENTRIES = 2, OVF_CONTACTS = 4, OVF_PAIRS = 8, OVF_LARGE = 16, OVF_HEAVY = 32, OVF_COMPLEX = 64 };
 
-// Device-side counters (one pinned-host mirror, read back at the few sync points of a step).
+// Device-side counters and the broadphase grid (one pinned-host mirror, read back at the single sync of a call).
 struct DevCounters {
-    unsigned long long bbox[6];  // order-preserving encodings of min xyz / max xyz
+    unsigned long long bbox[6];  // order-preserving encodings of min xyz / max xyz of the colliding shapes' AABBs
+    // grid of this step, ChBroadphase::DetermineBoundingBox/ComputeTopLevelResolution (CMC/ChBroadphase.cpp:142-208)
+    double origin[3], maxpt[3], bin_size[3], inv_bin_size[3];
+    int32_t bins[3];
+    uint32_t num_bins;
     uint32_t n_large;            // shapes touching more than LARGE_BINS bins
     uint32_t n_intersections;    // N_i
     uint32_t n_active_bins;      // N_a
+    uint32_t n_tiles;            // ceil(N_i / PAIR_TILE)
     uint32_t n_pairs;            // N_p
-    uint32_t n_slots;            // pre-compaction contact slots
     uint32_t n_contacts;         // N_c
-    uint32_t multi_slot;         // !=0 if some pair can yield more than one contact
+    uint32_t n_complex;          // candidate pairs that need the multi-contact / MPR path
     uint32_t n_heavy;            // bodies reduced by the masked path
     uint32_t ct_body_count;
-    uint32_t overflow;           // a capacity was exceeded
     uint32_t unsupported;        // pairs whose shape combination this backend cannot test yet
+    uint32_t overflow;           // sticky OVF_* mask; while set every kernel is a no-op
+    uint32_t need_bins, need_entries, need_contacts, need_pairs, need_complex;
+    uint32_t steps_done;         // steps fully applied since the host last reset it
+    uint32_t nsc_iters;
+    uint32_t n_bodies, n_shapes; // extents of body / shape arrays (for device-count scans)
     uint32_t pad;
+    double nsc_residual, nsc_objective;
 };
 
 struct Timer {
-    cudaEvent_t a = nullptr, b = nullptr;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pool;  // event pairs, resolved lazily by flush_timers
+    size_t used = 0;
     double total_ms = 0;
     bool armed = false;
 };
 
-enum { LARGE_BINS = 48, MAX_LARGE = 4096, MAX_HEAVY = 64, SMC_MAT_STRIDE = 13, NSC_MAT_STRIDE = 8 };
+enum { LARGE_BINS = 48, MAX_LARGE = 4096, MAX_HEAVY = 64, SMC_MAT_STRIDE = 13, NSC_MAT_STRIDE = 8, PAIR_TILE = 256,
+       PAIR_HALO = 96 };
 
 struct System {
     int device = 0;
+    int num_sms = 148;
     cudaStream_t stream = nullptr;
     cb200_settings set;
     int64_t launches = 0;
@@ -137,37 +156,36 @@ struct System {
     DevBuf<double> s_dims;   // 4 ns
     DevBuf<double> s_wpos;   // 4 ns  world position + dims[0]  (obj_data_A_global)
     DevBuf<double> s_wrot;   // 4 ns  world rotation            (obj_data_R_global)
-    DevBuf<ShapeBP> s_bp;    // ns
-    bool all_spheres_unit = false;
+    DevBuf<ShapeBox> s_box;  // ns    AABB
+    DevBuf<ShapeMeta> s_meta;  // ns
+    bool meta_dirty = true;    // body flags / shapes changed: rebuild s_meta
+    uint32_t n_nonsphere = 0;  // shapes that are not spheres (host count; >= 2 => multi-contact / MPR pairs possible)
 
     // ---- materials: nm x nm composite table computed on the host in float (same arithmetic as the reference) ----
     int nm_smc = 0, nm_nsc = 0;
     DevBuf<double> mat_smc;  // nm*nm*SMC_MAT_STRIDE
     DevBuf<double> mat_nsc;
 
-    // ---- broadphase (CMC/ChCollisionData.h:199-221) ----
-    double origin[3], maxpt[3], bin_size[3], inv_bin_size[3];
-    int bins[3] = {1, 1, 1};
-    uint32_t num_bins = 0;
-    DevBuf<uint32_t> bin_intersections;  // ns+1
-    DevBuf<uint64_t> bin_count;          // num_bins+1: low 32 = entries in bin, high 32 = 1 if active (packed scan)
-    DevBuf<uint32_t> bin_cursor;         // num_bins
-    DevBuf<uint32_t> bin_entries_tmp;    // N_i  (unsorted inside a bin)
-    DevBuf<uint32_t> bin_entries;        // N_i  (sorted by shape inside a bin) == bin_aabb_number
+    // ---- broadphase (CMC/ChCollisionData.h:199-221); capacities cap_* are what the kernels check against ----
+    uint32_t cap_bins = 0, cap_entries = 0, cap_contacts = 0, cap_pairs = 0;
+    DevBuf<uint32_t> bin_intersections;  // ns
+    DevBuf<uint64_t> bin_start;          // cap_bins+1: low 32 = first entry of bin, high 32 = index among active bins
+    DevBuf<uint32_t> bin_cursor;         // cap_bins (histogram, then countdown cursor of the scatter)
+    DevBuf<uint32_t> ent_tmp;            // cap_entries  shape ids, unsorted inside a bin
+    DevBuf<uint32_t> ent_bin;            // cap_entries  bin of every entry
+    DevBuf<uint32_t> ent_shape;          // cap_entries  shape ids sorted inside a bin == bin_aabb_number
+    DevBuf<uint64_t> ent_count;          // cap_entries  pairs | contacts << 32 found by each entry
+    DevBuf<uint64_t> tile_count;         // cap_entries / PAIR_TILE + 2
     DevBuf<uint32_t> large_list;         // MAX_LARGE
-    DevBuf<uint32_t> pair_count;         // num_bins+1
-    DevBuf<int64_t> pairs;               // N_p
-    DevBuf<PairAux> pair_aux;            // N_p
+    DevBuf<int64_t> pairs;               // cap_pairs (materialised on demand only)
+    bool pairs_valid = false;
+    bool box_relative = false;  // s_box holds origin-relative boxes (the binning ran since the last AABB stage)
 
-    // ---- narrowphase ----
-    DevBuf<uint32_t> slot_index;  // N_p+1 (contact_index)
-    DevBuf<uint32_t> pair_nc;     // N_p+1 contacts found per pair -> exclusive scan
-    DevBuf<double> t_norm, t_pta, t_ptb, t_depth, t_erad;  // pre-compaction slot arrays
-    DevBuf<double> c_norm, c_pta, c_ptb, c_depth, c_erad;  // N_c
-    DevBuf<int32_t> c_bids;      // 2 N_c
-    DevBuf<int64_t> c_shapes;    // N_c
-    DevBuf<uint32_t> c_mats;     // N_c
-    uint32_t n_pairs = 0, n_slots = 0, n_contacts = 0, n_intersections = 0, n_active_bins = 0;
+    // ---- narrowphase output: the contact list (CMC/ChCollisionData.h:159-183) ----
+    DevBuf<double> c_norm, c_pta, c_ptb, c_depth, c_erad;  // cap_contacts
+    DevBuf<int32_t> c_bids;      // 2 per contact
+    DevBuf<int64_t> c_shapes;    // 1 per contact
+    DevBuf<uint32_t> c_mats;     // 1 per contact
 
     // ---- SMC (MC/solver/ChIterativeSolverMulticoreSMC.cpp) ----
     DevBuf<double> ct_force;    // 3 N_c  force on body 2 (body 1 gets the negative)
@@ -184,8 +202,6 @@ struct System {
     DevBuf<double> gamma, n_r, n_E, n_work;  // 3 N_c each (work: several vectors)
     DevBuf<double> n_bodyvec;  // 6 nb scratch
     DevBuf<double> n_scal;     // small scalar block
-    uint32_t nsc_iters = 0;
-    double nsc_residual = 0, nsc_objective = 0;
 
     // ---- scan scratch / counters ----
     DevBuf<uint64_t> scan_tmp;
@@ -199,22 +215,37 @@ struct System {
 // ---- shared host helpers (defined in api.cu) ----
 int timer_start(System* S, const char* name);
 int timer_stop(System* S, const char* name);
-int fetch_counters(System* S);  // D2H of DevCounters + stream sync
+int flush_timers(System* S);
+int fetch_counters(System* S);       // D2H of DevCounters + stream sync
+int ensure_capacity(System* S);      // first-use allocation of every capacity-bound array
+int grow_after_overflow(System* S);  // reads h_cnt->need_*, grows, clears the device overflow mask
 
-// ---- stage entry points ----
-int stage_update_forces(System* S);   // integrate.cu
-int stage_integrate(System* S);       // integrate.cu
-int stage_aabb(System* S);            // broadphase.cu
-int stage_broadphase(System* S);      // broadphase.cu
-int stage_narrowphase(System* S);     // narrowphase.cu
-int stage_smc(System* S);             // smc.cu
-int stage_nsc(System* S);             // nsc.cu
+// ---- stage enqueue functions: no host synchronisation inside ----
+int enqueue_update_forces(System* S);                                    // integrate.cu
+int enqueue_integrate(System* S);                                        // integrate.cu (also counts the step as done)
+int enqueue_aabb(System* S);                                             // broadphase.cu
+int enqueue_bins(System* S);                                             // broadphase.cu: grid + counting sort
+int enqueue_broadphase(System* S, bool want_pairs, bool want_contacts);  // broadphase.cu
+int enqueue_pairs_only(System* S, bool want_pairs, bool want_contacts);  // broadphase.cu: pair kernels on existing bins
+int enqueue_smc(System* S);                                              // smc.cu
+int enqueue_nsc(System* S);                                              // nsc.cu
 
-// exclusive scans (scan.cu). n+1 outputs: out[n] = total. In-place allowed.
-int scan_u32(System* S, const uint32_t* in, uint32_t* out, size_t n);
-int scan_u64(System* S, const uint64_t* in, uint64_t* out, size_t n);
+// exclusive scans (scan.cu) over a device-side element count (*n_dev <= n_cap). n+1 outputs: out[n] = total.
+// In-place allowed.
+int scan_u32(System* S, const uint32_t* in, uint32_t* out, const uint32_t* n_dev, size_t n_cap);
+int scan_u64(System* S, const uint64_t* in, uint64_t* out, const uint32_t* n_dev, size_t n_cap);
+// bin histogram (u32) -> packed u64 (first entry | index among active bins << 32), CMC/ChBroadphase.cpp:290-301
+int scan_bins(System* S, const uint32_t* hist, uint64_t* out, const uint32_t* n_dev, size_t n_cap);
 
 inline int blocks_for(size_t n, int threads) { return (int)((n + threads - 1) / threads); }
+// grid for a grid-stride kernel over at most n_cap items: enough CTAs to fill the machine, never more than needed
+inline int grid_for(const System* S, size_t n_cap, int threads, int per_sm = 8) {
+    size_t need = (n_cap + threads - 1) / threads;
+    size_t full = (size_t)S->num_sms * per_sm;
+    if (need < 1)
+        need = 1;
+    return (int)(need < full ? need : full);
+}
 
 // Order-preserving map double <-> uint64 so that min/max reductions can use integer atomics (exact, order-free).
 HD unsigned long long enc_ordered(double d) {

@@ -19,7 +19,9 @@ __global__ void __launch_bounds__(256) k_update_forces(uint32_t nb, double h, d3
                                                        const double* __restrict__ inertia,
                                                        const double* __restrict__ vel,
                                                        const double* __restrict__ fapp /* may be null */,
-                                                       double* __restrict__ hf) {
+                                                       double* __restrict__ hf, const DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= nb)
         return;
@@ -45,8 +47,12 @@ __global__ void __launch_bounds__(256) k_update_forces(uint32_t nb, double h, d3
 // x += h v ;  q <- dq(h R w) * q   (ChBody::VariablesQbIncrementPosition), active bodies only
 __global__ void __launch_bounds__(256) k_integrate(uint32_t nb, double h, const uint8_t* __restrict__ bflags,
                                                    const double* __restrict__ vel, double* __restrict__ pos,
-                                                   double* __restrict__ rot) {
+                                                   double* __restrict__ rot, DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b == 0)
+        cnt->steps_done++;  // this step was applied in full (nothing upstream overflowed)
     if (b >= nb || !(bflags[b] & 1u))
         return;
     const double* v = vel + 6 * (size_t)b;
@@ -86,23 +92,23 @@ __global__ void __launch_bounds__(256) k_integrate(uint32_t nb, double h, const 
     reinterpret_cast<double4*>(rot)[b] = qn;
 }
 
-int stage_update_forces(System* S) {
+int enqueue_update_forces(System* S) {
     if (S->nb == 0)
         return CB200_OK;
     const d3 g = mk3(S->set.gravity[0], S->set.gravity[1], S->set.gravity[2]);
     k_update_forces<<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(S->nb, S->set.step_size, g, S->mass.p, S->inertia.p,
                                                                    S->vel.p, S->has_fapp ? S->fapp.p : nullptr,
-                                                                   S->hf.p);
+                                                                   S->hf.p, S->d_cnt);
     S->launches++;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;
 }
 
-int stage_integrate(System* S) {
+int enqueue_integrate(System* S) {
     if (S->nb == 0)
         return CB200_OK;
     k_integrate<<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(S->nb, S->set.step_size, S->bflags.p, S->vel.p, S->pos.p,
-                                                               S->rot.p);
+                                                               S->rot.p, S->d_cnt);
     S->launches++;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;

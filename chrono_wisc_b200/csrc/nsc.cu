@@ -1,7 +1,7 @@
 // nsc.cu -- NSC DVI solve (APGD + matrix-free Schur product). Placeholder until the SMC path is measured.
 #include "common.cuh"
 namespace cb200 {
-int stage_nsc(System* S) {
+int enqueue_nsc(System* S) {
     (void)S;
     return set_error(CB200_ERR_UNSUPPORTED, "NSC solver not built yet");
 }

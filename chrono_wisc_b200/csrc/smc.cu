@@ -47,21 +47,30 @@ __device__ __forceinline__ BodyView load_body(uint32_t b, const double* __restri
     return B;
 }
 
-__global__ void __launch_bounds__(256) k_smc_force(uint32_t nc, SmcParams P, const int32_t* __restrict__ bids,
+__global__ void __launch_bounds__(256) k_smc_force(SmcParams P, const int32_t* __restrict__ bids,
                                                    const uint32_t* __restrict__ c_mats,
                                                    const double* __restrict__ c_norm, const double* __restrict__ c_pta,
                                                    const double* __restrict__ c_ptb, const double* __restrict__ c_depth,
                                                    const double* __restrict__ c_erad, const double* __restrict__ pos,
                                                    const double* __restrict__ rot, const double* __restrict__ vel,
                                                    const double* __restrict__ mass, const double* __restrict__ mat,
-                                                   double* __restrict__ ct_force, double* __restrict__ ct_torque) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nc)
+                                                   const uint8_t* __restrict__ heavy, uint32_t* __restrict__ deg,
+                                                   double* __restrict__ ct_force, double* __restrict__ ct_torque,
+                                                   const DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
         return;
+    const uint32_t nc = cnt->n_contacts;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nc; i += gridDim.x * blockDim.x) {
     d3 force = mk3(0), tq1 = mk3(0), tq2 = mk3(0);
     const double depth = c_depth[i];
+    const uint32_t b1 = (uint32_t)bids[2 * i], b2 = (uint32_t)bids[2 * i + 1];
+    // body -> contact incidence counts (first half of the counting sort by body that replaces the reference's
+    // sort_by_key, ...SMC.cpp:702-703)
+    if (!heavy[b1])
+        atomicAdd(&deg[b1], 1u);
+    if (!heavy[b2])
+        atomicAdd(&deg[b2], 1u);
     if (depth < 0) {
-        const uint32_t b1 = (uint32_t)bids[2 * i], b2 = (uint32_t)bids[2 * i + 1];
         const BodyView B1 = load_body(b1, pos, rot, vel, mass);
         const BodyView B2 = load_body(b2, pos, rot, vel, mass);
         const d3 n = mk3(c_norm[3 * i], c_norm[3 * i + 1], c_norm[3 * i + 2]);
@@ -261,32 +270,24 @@ __global__ void __launch_bounds__(256) k_smc_force(uint32_t nc, SmcParams P, con
     ct_force[3 * i] = force.x, ct_force[3 * i + 1] = force.y, ct_force[3 * i + 2] = force.z;
     double* t = ct_torque + 6 * (size_t)i;
     t[0] = tq1.x, t[1] = tq1.y, t[2] = tq1.z, t[3] = tq2.x, t[4] = tq2.y, t[5] = tq2.z;
+    }
 }
 
 // ---- body -> contact incidence lists (counting sort by body id) ------------------------------------------------
-__global__ void __launch_bounds__(256) k_inc_count(uint32_t nc, const int32_t* __restrict__ bids,
-                                                   const uint8_t* __restrict__ heavy, uint32_t* __restrict__ deg) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nc)
-        return;
-    const uint32_t b1 = (uint32_t)bids[2 * i], b2 = (uint32_t)bids[2 * i + 1];
-    if (!heavy[b1])
-        atomicAdd(&deg[b1], 1u);
-    if (!heavy[b2])
-        atomicAdd(&deg[b2], 1u);
-}
-
-__global__ void __launch_bounds__(256) k_inc_fill(uint32_t nc, const int32_t* __restrict__ bids,
+__global__ void __launch_bounds__(256) k_inc_fill(const int32_t* __restrict__ bids,
                                                   const uint8_t* __restrict__ heavy, const uint32_t* __restrict__ off,
-                                                  uint32_t* __restrict__ cursor, uint32_t* __restrict__ inc) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nc)
+                                                  uint32_t* __restrict__ cursor, uint32_t* __restrict__ inc,
+                                                  const DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
         return;
-    const uint32_t b1 = (uint32_t)bids[2 * i], b2 = (uint32_t)bids[2 * i + 1];
-    if (!heavy[b1])
-        inc[off[b1] + atomicAdd(&cursor[b1], 1u)] = i << 1;
-    if (!heavy[b2])
-        inc[off[b2] + atomicAdd(&cursor[b2], 1u)] = (i << 1) | 1u;
+    const uint32_t nc = cnt->n_contacts;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nc; i += gridDim.x * blockDim.x) {
+        const uint32_t b1 = (uint32_t)bids[2 * i], b2 = (uint32_t)bids[2 * i + 1];
+        if (!heavy[b1])
+            inc[off[b1] + atomicAdd(&cursor[b1], 1u)] = i << 1;
+        if (!heavy[b2])
+            inc[off[b2] + atomicAdd(&cursor[b2], 1u)] = (i << 1) | 1u;
+    }
 }
 
 // one thread per body: add the body's contacts in ascending contact index, then hf += h * (F, T)
@@ -296,6 +297,8 @@ __global__ void __launch_bounds__(256) k_body_reduce(uint32_t nb, const uint8_t*
                                                      const double* __restrict__ ct_torque, double h,
                                                      double* __restrict__ b_force, double* __restrict__ hf,
                                                      DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     bool touched = false;
     if (b < nb && !heavy[b]) {
@@ -338,31 +341,38 @@ __global__ void __launch_bounds__(256) k_body_reduce(uint32_t nb, const uint8_t*
 
 __global__ void __launch_bounds__(256) k_heavy_list(uint32_t nb, const uint8_t* __restrict__ heavy,
                                                     uint32_t* __restrict__ list, DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b < nb && heavy[b]) {
         const uint32_t k = atomicAdd(&cnt->n_heavy, 1u);
         if (k < MAX_HEAVY)
             list[k] = b;
         else
-            cnt->overflow = 1;
+            atomicOr(&cnt->overflow, (uint32_t)OVF_HEAVY);
     }
 }
 
 // Bodies with very many contacts (a container touching 10^5 spheres): fixed-shape masked reduction over the whole
 // contact list.  Chunk -> CTA mapping and the in-CTA tree are fixed, hence deterministic.
 constexpr int HEAVY_CHUNK = 4096;
-__global__ void __launch_bounds__(256) k_heavy_partial(uint32_t nc, const int32_t* __restrict__ bids,
+__global__ void __launch_bounds__(256) k_heavy_partial(const int32_t* __restrict__ bids,
                                                        const double* __restrict__ ct_force,
                                                        const double* __restrict__ ct_torque,
                                                        const uint32_t* __restrict__ list,
-                                                       const DevCounters* __restrict__ cnt, uint32_t nchunks,
+                                                       const DevCounters* __restrict__ cnt, uint32_t chunk_cap,
                                                        double* __restrict__ part) {
     __shared__ double sm[8][7];
+    if (cnt->overflow)
+        return;
+    const uint32_t nc = cnt->n_contacts;
+    const uint32_t nchunks = (nc + HEAVY_CHUNK - 1) / HEAVY_CHUNK;
     const uint32_t nh = min(cnt->n_heavy, (uint32_t)MAX_HEAVY);
-    for (uint32_t hI = blockIdx.y; hI < nh; hI += gridDim.y) {
+    for (uint32_t hI = blockIdx.y; hI < nh; hI += gridDim.y)
+    for (uint32_t chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x) {
         const uint32_t body = list[hI];
         double acc[7] = {0, 0, 0, 0, 0, 0, 0};
-        const uint32_t c0 = blockIdx.x * HEAVY_CHUNK;
+        const uint32_t c0 = chunk * HEAVY_CHUNK;
         for (int k = 0; k < HEAVY_CHUNK / 256; k++) {
             const uint32_t c = c0 + k * 256 + threadIdx.x;
             if (c < nc) {
@@ -395,18 +405,21 @@ __global__ void __launch_bounds__(256) k_heavy_partial(uint32_t nc, const int32_
             double s = sm[0][threadIdx.x];
             for (int w = 1; w < 8; w++)
                 s += sm[w][threadIdx.x];
-            part[((size_t)hI * nchunks + blockIdx.x) * 7 + threadIdx.x] = s;
+            part[((size_t)hI * chunk_cap + chunk) * 7 + threadIdx.x] = s;
         }
         __syncthreads();
     }
 }
 
 __global__ void __launch_bounds__(256) k_heavy_final(const uint32_t* __restrict__ list,
-                                                     const DevCounters* __restrict__ cnt_in, uint32_t nchunks,
+                                                     const DevCounters* __restrict__ cnt_in, uint32_t chunk_cap,
                                                      const double* __restrict__ part, double h,
                                                      double* __restrict__ b_force, double* __restrict__ hf,
                                                      DevCounters* __restrict__ cnt) {
     __shared__ double sm[8][7];
+    if (cnt_in->overflow)
+        return;
+    const uint32_t nchunks = (cnt_in->n_contacts + HEAVY_CHUNK - 1) / HEAVY_CHUNK;
     const uint32_t nh = min(cnt_in->n_heavy, (uint32_t)MAX_HEAVY);
     const uint32_t hI = blockIdx.x;
     if (hI >= nh)
@@ -414,7 +427,7 @@ __global__ void __launch_bounds__(256) k_heavy_final(const uint32_t* __restrict_
     double acc[7] = {0, 0, 0, 0, 0, 0, 0};
     for (uint32_t k = threadIdx.x; k < nchunks; k += 256)
         for (int q = 0; q < 7; q++)
-            acc[q] += part[((size_t)hI * nchunks + k) * 7 + q];
+            acc[q] += part[((size_t)hI * chunk_cap + k) * 7 + q];
 #pragma unroll
     for (int q = 0; q < 7; q++)
 #pragma unroll
@@ -449,7 +462,10 @@ __global__ void __launch_bounds__(256) k_heavy_final(const uint32_t* __restrict_
 __global__ void __launch_bounds__(256) k_vel_update(uint32_t nb, const uint8_t* __restrict__ bflags,
                                                     const double* __restrict__ mass,
                                                     const double* __restrict__ inv_inertia,
-                                                    const double* __restrict__ hf, double* __restrict__ vel) {
+                                                    const double* __restrict__ hf, double* __restrict__ vel,
+                                                    const DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= nb || !(bflags[b] & 1u))
         return;
@@ -464,63 +480,48 @@ __global__ void __launch_bounds__(256) k_vel_update(uint32_t nb, const uint8_t* 
     v[5] = v[5] + inv_inertia[3 * b + 2] * f[5];
 }
 
-int stage_smc(System* S) {
+int enqueue_smc(System* S) {
     if (S->nb == 0)
         return CB200_OK;
-    const uint32_t nc = S->n_contacts, nb = S->nb;
+    const uint32_t nb = S->nb;
     const cb200_settings& st = S->set;
     if (st.tangential_displ_mode == 2)
         return set_error(CB200_ERR_UNSUPPORTED, "MultiStep tangential displacement history is not implemented");
-    CB_TRY(S->b_force.reserve(6 * (size_t)nb));
-    if (nc > 0) {
-        if (S->nm_smc == 0)
-            return set_error(CB200_ERR_STATE, "cb200_set_materials_smc was not called");
-        SmcParams P;
-        P.force_model = st.contact_force_model;
-        P.adhesion_model = st.adhesion_force_model;
-        P.displ_mode = st.tangential_displ_mode;
-        P.use_mat_props = st.use_material_properties;
-        P.char_vel = st.characteristic_vel;
-        P.min_slip_vel = st.min_slip_vel;
-        P.min_roll_vel = st.min_roll_vel;
-        P.min_spin_vel = st.min_spin_vel;
-        P.dT = st.step_size;
-        P.nm = S->nm_smc;
-        CB_TRY(S->ct_force.reserve(3 * (size_t)nc));
-        CB_TRY(S->ct_torque.reserve(6 * (size_t)nc));
-        CB_TRY(S->b_deg.reserve(nb + 1));
-        CB_TRY(S->b_cursor.reserve(nb));
-        CB_TRY(S->b_inc.reserve(2 * (size_t)nc));
-        CB_TRY(S->heavy_list.reserve(MAX_HEAVY));
-        const uint32_t nchunks = (nc + HEAVY_CHUNK - 1) / HEAVY_CHUNK;
-        CB_TRY(S->heavy_part.reserve((size_t)MAX_HEAVY * nchunks * 7));
-
-        k_smc_force<<<blocks_for(nc, 256), 256, 0, S->stream>>>(nc, P, S->c_bids.p, S->c_mats.p, S->c_norm.p,
-                                                                S->c_pta.p, S->c_ptb.p, S->c_depth.p, S->c_erad.p,
-                                                                S->pos.p, S->rot.p, S->vel.p, S->mass.p, S->mat_smc.p,
-                                                                S->ct_force.p, S->ct_torque.p);
-        CB_CUDA(cudaMemsetAsync(S->b_deg.p, 0, (size_t)(nb + 1) * 4, S->stream));
-        CB_CUDA(cudaMemsetAsync(S->b_cursor.p, 0, (size_t)nb * 4, S->stream));
-        k_inc_count<<<blocks_for(nc, 256), 256, 0, S->stream>>>(nc, S->c_bids.p, S->heavy.p, S->b_deg.p);
-        S->launches += 2;
-        CB_TRY(scan_u32(S, S->b_deg.p, S->b_deg.p, nb));
-        k_inc_fill<<<blocks_for(nc, 256), 256, 0, S->stream>>>(nc, S->c_bids.p, S->heavy.p, S->b_deg.p, S->b_cursor.p,
-                                                               S->b_inc.p);
-        k_heavy_list<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->heavy.p, S->heavy_list.p, S->d_cnt);
-        k_body_reduce<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->heavy.p, S->b_deg.p, S->b_inc.p,
-                                                                  S->ct_force.p, S->ct_torque.p, st.step_size,
-                                                                  S->b_force.p, S->hf.p, S->d_cnt);
-        k_heavy_partial<<<dim3(nchunks, 4), 256, 0, S->stream>>>(nc, S->c_bids.p, S->ct_force.p, S->ct_torque.p,
-                                                                 S->heavy_list.p, S->d_cnt, nchunks, S->heavy_part.p);
-        k_heavy_final<<<MAX_HEAVY, 256, 0, S->stream>>>(S->heavy_list.p, S->d_cnt, nchunks, S->heavy_part.p,
-                                                        st.step_size, S->b_force.p, S->hf.p, S->d_cnt);
-        S->launches += 5;
-    } else {
-        CB_CUDA(cudaMemsetAsync(S->b_force.p, 0, 6 * (size_t)nb * 8, S->stream));
-    }
-    k_vel_update<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->bflags.p, S->mass.p, S->inv_inertia.p, S->hf.p,
-                                                             S->vel.p);
+    if (S->ns > 0 && S->nm_smc == 0)
+        return set_error(CB200_ERR_STATE, "cb200_set_materials_smc was not called");
+    SmcParams P;
+    P.force_model = st.contact_force_model;
+    P.adhesion_model = st.adhesion_force_model;
+    P.displ_mode = st.tangential_displ_mode;
+    P.use_mat_props = st.use_material_properties;
+    P.char_vel = st.characteristic_vel;
+    P.min_slip_vel = st.min_slip_vel;
+    P.min_roll_vel = st.min_roll_vel;
+    P.min_spin_vel = st.min_spin_vel;
+    P.dT = st.step_size;
+    P.nm = S->nm_smc;
+    const uint32_t chunk_cap = S->cap_contacts / HEAVY_CHUNK + 1;
+    const int cgrid = grid_for(S, S->cap_contacts, 256);
+    CB_CUDA(cudaMemsetAsync(S->b_deg.p, 0, (size_t)(nb + 1) * 4, S->stream));
+    CB_CUDA(cudaMemsetAsync(S->b_cursor.p, 0, (size_t)nb * 4, S->stream));
+    k_smc_force<<<cgrid, 256, 0, S->stream>>>(P, S->c_bids.p, S->c_mats.p, S->c_norm.p, S->c_pta.p, S->c_ptb.p,
+                                              S->c_depth.p, S->c_erad.p, S->pos.p, S->rot.p, S->vel.p, S->mass.p,
+                                              S->mat_smc.p, S->heavy.p, S->b_deg.p, S->ct_force.p, S->ct_torque.p,
+                                              S->d_cnt);
     S->launches++;
+    CB_TRY(scan_u32(S, S->b_deg.p, S->b_deg.p, &S->d_cnt->n_bodies, nb));
+    k_inc_fill<<<cgrid, 256, 0, S->stream>>>(S->c_bids.p, S->heavy.p, S->b_deg.p, S->b_cursor.p, S->b_inc.p, S->d_cnt);
+    k_heavy_list<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->heavy.p, S->heavy_list.p, S->d_cnt);
+    k_body_reduce<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->heavy.p, S->b_deg.p, S->b_inc.p, S->ct_force.p,
+                                                              S->ct_torque.p, st.step_size, S->b_force.p, S->hf.p,
+                                                              S->d_cnt);
+    k_heavy_partial<<<dim3(grid_for(S, chunk_cap, 1, 4), 4), 256, 0, S->stream>>>(
+        S->c_bids.p, S->ct_force.p, S->ct_torque.p, S->heavy_list.p, S->d_cnt, chunk_cap, S->heavy_part.p);
+    k_heavy_final<<<MAX_HEAVY, 256, 0, S->stream>>>(S->heavy_list.p, S->d_cnt, chunk_cap, S->heavy_part.p,
+                                                    st.step_size, S->b_force.p, S->hf.p, S->d_cnt);
+    k_vel_update<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->bflags.p, S->mass.p, S->inv_inertia.p, S->hf.p,
+                                                             S->vel.p, S->d_cnt);
+    S->launches += 6;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;
 }

@@ -110,6 +110,12 @@ int cb200_device_count(void);
 int cb200_create(int device, cb200_system** out);
 void cb200_destroy(cb200_system* sys);
 
+/* Page-locked host buffers for the upload/download calls below (the reference's host_data vectors are plain
+ * std::vector, MC/ChDataManager.h:204-324; pinning them lets the copies run at PCIe speed).  Optional: every
+ * entry point also accepts pageable memory. */
+int cb200_host_alloc(uint64_t bytes, void** out);
+int cb200_host_free(void* p);
+
 /* sys.GetSettings() write-back (MC/physics/ChSystemMulticore.cpp:684-686). */
 void cb200_default_settings(cb200_settings* s); /* defaults of MC/ChSettings.h:41-48,96-131 */
 int cb200_set_settings(cb200_system* sys, const cb200_settings* s);
