@@ -4,6 +4,7 @@
 #include <cmath>
 #include <cstring>
 #include <limits.h>
+#include <limits>
 
 namespace cb200 {
 
@@ -82,9 +83,11 @@ static int alloc_entries(System* S, uint32_t n) {
     CB_TRY(S->ent_tmp.reserve(n));
     CB_TRY(S->ent_bin.reserve(n));
     CB_TRY(S->ent_shape.reserve(n));
-    CB_TRY(S->ent_count.reserve(n));
+    CB_TRY(S->ent_mask.reserve(n));
+    CB_TRY(S->ent_c.reserve(4 * (size_t)S->ent_tmp.cap));
+    CB_TRY(S->ent_m.reserve(S->ent_tmp.cap));
     S->cap_entries = (uint32_t)S->ent_tmp.cap;
-    CB_TRY(S->tile_count.reserve((size_t)S->cap_entries / PAIR_TILE + 4));
+    CB_TRY(S->ent_off.reserve((size_t)S->cap_entries + 4));
     return CB200_OK;
 }
 static int alloc_contacts(System* S, uint32_t n) {
@@ -260,7 +263,7 @@ void cb200_destroy(cb200_system* sys) {
     REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(bflags); REL(heavy);
     REL(s_type); REL(s_body); REL(s_fam); REL(s_mat); REL(s_lpos); REL(s_lrot); REL(s_dims); REL(s_wpos); REL(s_wrot);
     REL(s_box); REL(s_meta); REL(mat_smc); REL(mat_nsc); REL(bin_intersections); REL(bin_start); REL(bin_cursor);
-    REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_count); REL(tile_count); REL(large_list); REL(pairs);
+    REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_mask); REL(ent_c); REL(ent_m); REL(ent_off); REL(large_list); REL(pairs);
     REL(c_norm); REL(c_pta); REL(c_ptb); REL(c_depth); REL(c_erad); REL(c_bids); REL(c_shapes); REL(c_mats);
     REL(ct_force); REL(ct_torque); REL(b_deg); REL(b_cursor); REL(b_inc); REL(b_force); REL(heavy_list);
     REL(heavy_part); REL(n_frame); REL(gamma); REL(n_r); REL(n_E); REL(n_work); REL(n_bodyvec); REL(n_scal);
@@ -427,6 +430,12 @@ int cb200_set_materials_smc(cb200_system* sys, int n, const float* t) {
             o[10] = (float)((m1[11] + m2[11]) / 2);          // kt
             o[11] = (float)((m1[12] + m2[12]) / 2);          // gn
             o[12] = (float)((m1[13] + m2[13]) / 2);          // gt
+            // Hertz damping ratio beta (MC/solver/ChIterativeSolverMulticoreSMC.cpp:289-290), constant per pair
+            {
+                const double cr = o[8], eps = std::numeric_limits<double>::epsilon();
+                const double loge = (cr < eps) ? std::log(eps) : std::log(cr);
+                o[13] = loge / std::sqrt(loge * loge + M_PI * M_PI);
+            }
         }
     CB_TRY(S->mat_smc.reserve(tab.size()));
     CB_TRY(upload(S, S->mat_smc, 0, tab.data(), tab.size()));

@@ -25,7 +25,7 @@
 //  * Spheres carry no AABB record: (centre, radius) is 32 B and the box is recomputed with the reference's own
 //    operations, (c - (r + envelope)) - global_origin, bit for bit.
 #include "common.cuh"
-#include "prims.cuh"
+#include "grid.cuh"
 #include <float.h>
 #include <limits.h>
 #include <math.h>
@@ -40,25 +40,6 @@ struct GridSettings {
     uint32_t ns;
     uint32_t cap_bins;
 };
-
-struct GridParams {
-    double origin[3];
-    double inv[3];
-    int bins[3];
-    uint32_t num_bins;
-};
-
-__device__ __forceinline__ GridParams load_grid(const DevCounters* __restrict__ cnt) {
-    GridParams g;
-#pragma unroll
-    for (int a = 0; a < 3; a++) {
-        g.origin[a] = cnt->origin[a];
-        g.inv[a] = cnt->inv_bin_size[a];
-        g.bins[a] = cnt->bins[a];
-    }
-    g.num_bins = cnt->num_bins;
-    return g;
-}
 
 // --------------------------------------------------------------------------------------------------------------
 // per-shape integer record; rebuilt only when shapes or body flags change
@@ -244,23 +225,6 @@ __device__ GridFull compute_grid(const DevCounters* __restrict__ cnt, const Grid
     return G;
 }
 
-// origin-relative AABB of any shape: spheres from (centre, radius), others from their box record
-__device__ __forceinline__ void shape_box_rel(uint32_t i, uint32_t info, const double* __restrict__ s_wpos,
-                                              const ShapeBox* __restrict__ s_box, const double* origin,
-                                              double envelope, double* mn, double* mx) {
-    if (((info >> 8) & 0xff) == CB200_SPHERE) {
-        const double4 w = reinterpret_cast<const double4*>(s_wpos)[i];
-        const double r = w.w + envelope;
-        mn[0] = (w.x - r) - origin[0], mn[1] = (w.y - r) - origin[1], mn[2] = (w.z - r) - origin[2];
-        mx[0] = (w.x + r) - origin[0], mx[1] = (w.y + r) - origin[1], mx[2] = (w.z + r) - origin[2];
-    } else {
-        const double2* p = reinterpret_cast<const double2*>(s_box + i);
-        const double2 a = p[0], b = p[1], c = p[2];
-        mn[0] = a.x, mn[1] = a.y, mn[2] = b.x;
-        mx[0] = b.y, mx[1] = c.x, mx[2] = c.y;
-    }
-}
-
 __device__ __forceinline__ bool bin_range(const double* mn, const double* mx, const GridParams& g, int* lo, int* hi) {
     // HashMin / HashMax, CMC/ChCollisionUtils.h:44-60
     lo[0] = (int)floor(mn[0] * g.inv[0]);
@@ -392,8 +356,13 @@ __global__ void __launch_bounds__(256) k_bin_large(const ShapeMeta* __restrict__
     if (FILL && (uint32_t)bin_start[g.num_bins] > cap_entries)
         return;
     const uint32_t nl = min(cnt->n_large, (uint32_t)MAX_LARGE);
-    for (uint32_t s = blockIdx.x; s < nl; s += gridDim.x) {
-        const uint32_t shape = large_list[s];
+    if (nl == 0)
+        return;
+    // several CTAs share one large shape: work item w = (shape w % nl, part w / nl)
+    const uint32_t nparts = max(1u, gridDim.x / nl);
+    for (uint32_t w = blockIdx.x; w < nl * nparts; w += gridDim.x) {
+        const uint32_t shape = large_list[w % nl];
+        const uint32_t part = w / nl;
         double mn[3], mx[3];
         shape_box_rel(shape, meta[shape].info, s_wpos, s_box, g.origin, envelope, mn, mx);
         int lo[3], hi[3];
@@ -401,7 +370,7 @@ __global__ void __launch_bounds__(256) k_bin_large(const ShapeMeta* __restrict__
             continue;
         const int ny = hi[1] - lo[1] + 1, nz = hi[2] - lo[2] + 1;
         const uint32_t n = (uint32_t)(hi[0] - lo[0] + 1) * ny * nz;
-        for (uint32_t it = threadIdx.x; it < n; it += blockDim.x) {
+        for (uint32_t it = part * blockDim.x + threadIdx.x; it < n; it += nparts * blockDim.x) {
             const int ix = lo[0] + (int)(it / (uint32_t)(ny * nz));
             const int rem = (int)(it % (uint32_t)(ny * nz));
             const int iy = lo[1] + rem / nz, iz = lo[2] + rem % nz;
@@ -484,7 +453,10 @@ __global__ void __launch_bounds__(256) k_bin_fill(uint32_t ns, double envelope, 
 __global__ void __launch_bounds__(256) k_bin_sort(const uint32_t* __restrict__ ent_tmp,
                                                   const uint32_t* __restrict__ ent_bin,
                                                   const uint64_t* __restrict__ bin_start,
-                                                  uint32_t* __restrict__ ent_shape, const DevCounters* __restrict__ cnt) {
+                                                  const ShapeMeta* __restrict__ meta,
+                                                  const double* __restrict__ s_wpos,
+                                                  uint32_t* __restrict__ ent_shape, double* __restrict__ ent_c,
+                                                  ShapeMeta* __restrict__ ent_m, const DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
     const uint32_t ni = cnt->n_intersections;
@@ -492,312 +464,18 @@ __global__ void __launch_bounds__(256) k_bin_sort(const uint32_t* __restrict__ e
         const uint32_t b = ent_bin[e];
         const uint32_t s = (uint32_t)bin_start[b], t = (uint32_t)bin_start[b + 1];
         const uint32_t id = ent_tmp[e];
+        // the gathers of the per-shape records happen here, in a cheap, latency-tolerant kernel; the pair kernel
+        // then streams the bin-sorted copies
+        ShapeMeta m = meta[id];
+        const double4 w = reinterpret_cast<const double4*>(s_wpos)[id];
         uint32_t rank = 0;
         for (uint32_t j = s; j < t; j++)
             rank += ent_tmp[j] < id;
-        ent_shape[s + rank] = id;
-    }
-}
-
-// --------------------------------------------------------------------------------------------------------------
-// k_pairs: one thread per (bin, shape) entry, shared-memory staged tile + forward halo.
-// --------------------------------------------------------------------------------------------------------------
-struct __align__(16) Rec {
-    double mn[3], mx[3];  // origin-relative AABB
-    double cx, cy, cz, r; // world position + dims[0]
-    uint32_t body, fam, info, id;
-};
-
-__device__ __forceinline__ void load_rec(Rec& R, uint32_t id, const ShapeMeta* __restrict__ meta,
-                                         const double* __restrict__ s_wpos, const ShapeBox* __restrict__ s_box,
-                                         const double* origin, double envelope) {
-    const ShapeMeta m = meta[id];
-    const double4 w = reinterpret_cast<const double4*>(s_wpos)[id];
-    R.cx = w.x, R.cy = w.y, R.cz = w.z, R.r = w.w;
-    R.body = m.body, R.fam = m.fam, R.info = m.info, R.id = id;
-    if (((m.info >> 8) & 0xff) == CB200_SPHERE) {
-        const double r = w.w + envelope;
-        R.mn[0] = (w.x - r) - origin[0], R.mn[1] = (w.y - r) - origin[1], R.mn[2] = (w.z - r) - origin[2];
-        R.mx[0] = (w.x + r) - origin[0], R.mx[1] = (w.y + r) - origin[1], R.mx[2] = (w.z + r) - origin[2];
-    } else {
-        const double2* p = reinterpret_cast<const double2*>(s_box + id);
-        const double2 a = p[0], b = p[1], c = p[2];
-        R.mn[0] = a.x, R.mn[1] = a.y, R.mn[2] = b.x;
-        R.mx[0] = b.y, R.mx[1] = c.x, R.mx[2] = c.y;
-    }
-}
-
-// CMC/ChCollisionUtilsBroadphase.cpp:114-140 (a pure conjunction, so the evaluation order is free)
-__device__ __forceinline__ bool pair_passes(const Rec& A, const Rec& B, const GridParams& g, uint32_t bin) {
-    if (!((A.mn[0] <= B.mx[0] && B.mn[0] <= A.mx[0]) && (A.mn[1] <= B.mx[1] && B.mn[1] <= A.mx[1]) &&
-          (A.mn[2] <= B.mx[2] && B.mn[2] <= A.mx[2])))
-        return false;
-    // current_bin (CMC/ChCollisionUtils.h:97-110): the pair belongs to the bin holding max(Amin, Bmin)
-    const int cx = (int)floor(fmax(A.mn[0], B.mn[0]) * g.inv[0]);
-    const int cy = (int)floor(fmax(A.mn[1], B.mn[1]) * g.inv[1]);
-    const int cz = (int)floor(fmax(A.mn[2], B.mn[2]) * g.inv[2]);
-    if ((uint32_t)((cz * g.bins[1]) * g.bins[0] + cy * g.bins[0] + cx) != bin)
-        return false;
-    if (B.body == UINT_MAX || A.body == B.body)
-        return false;
-    if (!(B.info & 2u))
-        return false;
-    if (!(A.info & 1u) && !(B.info & 1u))
-        return false;
-    const uint32_t gA = A.fam & 0xffffu, mA = A.fam >> 16, gB = B.fam & 0xffffu, mB = B.fam >> 16;
-    return (mA & gB) && (mB & gA);
-}
-
-struct ShapeView {
-    int type;
-    d3 pos;
-    q4 rot;
-    double d0, d1, d2, d3_;
-};
-
-__device__ __forceinline__ ShapeView view_of(const Rec& R, const double* __restrict__ s_wrot,
-                                             const double* __restrict__ s_dims) {
-    ShapeView v;
-    v.type = (R.info >> 8) & 0xff;
-    v.pos = mk3(R.cx, R.cy, R.cz);
-    v.d0 = R.r;
-    v.d1 = v.d2 = v.d3_ = 0;
-    v.rot = mkq(1, 0, 0, 0);
-    if (v.type != CB200_SPHERE) {
-        const double4 r = reinterpret_cast<const double4*>(s_wrot)[R.id];
-        v.rot = mkq(r.x, r.y, r.z, r.w);
-        const double4 d = reinterpret_cast<const double4*>(s_dims)[R.id];
-        v.d1 = d.y, v.d2 = d.z, v.d3_ = d.w;
-    }
-    return v;
-}
-
-// Analytic dispatcher for pairs with at most one contact (everything that involves a sphere),
-// PRIMSCollision, CMC/ChNarrowphasePRIMS.cpp:1406-1607.
-// Returns 1/0 contacts, or -1 when the combination is not of that kind (multi-contact analytic pair or MPR).
-__device__ __forceinline__ int prims_single(const ShapeView& A, const ShapeView& B, double sep, Contact& c) {
-    bool hit;
-    if (A.type == CB200_SPHERE && B.type == CB200_SPHERE)
-        return sphere_sphere(A.pos, A.d0, B.pos, B.d0, sep, c) ? 1 : 0;
-    if (B.type == CB200_SPHERE) {
-        switch (A.type) {
-            case CB200_CAPSULE:
-                return capsule_sphere(A.pos, A.rot, A.d0, A.d1, B.pos, B.d0, sep, c) ? 1 : 0;
-            case CB200_CYLINDER:
-                return cylinder_sphere(A.pos, A.rot, A.d0, A.d1, B.pos, B.d0, sep, c) ? 1 : 0;
-            case CB200_ROUNDEDCYL:
-                return roundedcyl_sphere(A.pos, A.rot, A.d0, A.d1, A.d3_, B.pos, B.d0, sep, c) ? 1 : 0;
-            case CB200_BOX:
-                return box_sphere(A.pos, A.rot, mk3(A.d0, A.d1, A.d2), B.pos, B.d0, sep, c) ? 1 : 0;
-            case CB200_ROUNDEDBOX:
-                return roundedbox_sphere(A.pos, A.rot, mk3(A.d0, A.d1, A.d2), A.d3_, B.pos, B.d0, sep, c) ? 1 : 0;
-            default:
-                return -1;
-        }
-    }
-    if (A.type == CB200_SPHERE) {
-        // swapped call: the shape function sees (B, A); points are exchanged and the normal negated
-        // (ChNarrowphasePRIMS.cpp:1435-1443 and siblings)
-        switch (B.type) {
-            case CB200_CAPSULE:
-                hit = capsule_sphere(B.pos, B.rot, B.d0, B.d1, A.pos, A.d0, sep, c);
-                break;
-            case CB200_CYLINDER:
-                hit = cylinder_sphere(B.pos, B.rot, B.d0, B.d1, A.pos, A.d0, sep, c);
-                break;
-            case CB200_ROUNDEDCYL:
-                hit = roundedcyl_sphere(B.pos, B.rot, B.d0, B.d1, B.d3_, A.pos, A.d0, sep, c);
-                break;
-            case CB200_BOX:
-                hit = box_sphere(B.pos, B.rot, mk3(B.d0, B.d1, B.d2), A.pos, A.d0, sep, c);
-                break;
-            case CB200_ROUNDEDBOX:
-                hit = roundedbox_sphere(B.pos, B.rot, mk3(B.d0, B.d1, B.d2), B.d3_, A.pos, A.d0, sep, c);
-                break;
-            default:
-                return -1;
-        }
-        if (hit) {
-            const d3 t = c.p1;
-            c.p1 = c.p2;
-            c.p2 = t;
-            c.n = -c.n;
-            return 1;
-        }
-        return 0;
-    }
-    return -1;
-}
-
-template <typename T>
-__device__ __forceinline__ T warp_incl_scan_bp(T v, int lane) {
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        T o = __shfl_up_sync(0xffffffffu, v, d);
-        if (lane >= d)
-            v += o;
-    }
-    return v;
-}
-
-struct PairOut {
-    int64_t* pairs;  // null: candidate pair list not materialised
-    double *c_norm, *c_pta, *c_ptb, *c_depth, *c_erad;  // c_norm null: contacts not materialised
-    int32_t* c_bids;
-    int64_t* c_shapes;
-    uint32_t* c_mats;
-    uint32_t cap_pairs, cap_contacts;
-};
-
-template <bool STORE>
-__global__ void __launch_bounds__(PAIR_TILE) k_pairs(const ShapeMeta* __restrict__ meta,
-                                                     const double* __restrict__ s_wpos,
-                                                     const ShapeBox* __restrict__ s_box,
-                                                     const double* __restrict__ s_wrot,
-                                                     const double* __restrict__ s_dims,
-                                                     const uint32_t* __restrict__ ent_shape,
-                                                     const uint32_t* __restrict__ ent_bin,
-                                                     const uint64_t* __restrict__ bin_start, double envelope,
-                                                     int algorithm, uint64_t* __restrict__ ent_count,
-                                                     uint64_t* __restrict__ tile_count, PairOut out,
-                                                     DevCounters* __restrict__ cnt) {
-    __shared__ Rec win[PAIR_TILE + PAIR_HALO];
-    __shared__ uint64_t wsum[PAIR_TILE / 32 + 1];
-    if (cnt->overflow)
-        return;
-    const GridParams g = load_grid(cnt);
-    const uint32_t ni = cnt->n_intersections;
-    const uint32_t ntiles = cnt->n_tiles;
-    const double sep = 2 * envelope;
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-
-    if (STORE) {
-        const uint64_t tot = tile_count[ntiles];
-        const uint32_t np = (uint32_t)tot, nc = (uint32_t)(tot >> 32);
-        bool bad = false;
-        if (out.c_norm && nc > out.cap_contacts)
-            bad = true;
-        if (out.pairs && np > out.cap_pairs)
-            bad = true;
-        if (blockIdx.x == 0 && threadIdx.x == 0) {
-            cnt->n_pairs = np;
-            cnt->n_contacts = nc;
-            if (out.c_norm && nc > out.cap_contacts) {
-                cnt->need_contacts = nc;
-                atomicOr(&cnt->overflow, (uint32_t)OVF_CONTACTS);
-            }
-            if (out.pairs && np > out.cap_pairs) {
-                cnt->need_pairs = np;
-                atomicOr(&cnt->overflow, (uint32_t)OVF_PAIRS);
-            }
-        }
-        if (bad)
-            return;
-    }
-
-    for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const uint32_t e0 = tile * PAIR_TILE;
-        const uint32_t wend = min(ni, e0 + PAIR_TILE + PAIR_HALO);
-        __syncthreads();  // previous tile's readers are done with the window
-        for (uint32_t k = threadIdx.x; e0 + k < wend; k += PAIR_TILE)
-            load_rec(win[k], ent_shape[e0 + k], meta, s_wpos, s_box, g.origin, envelope);
-        __syncthreads();
-
-        const uint32_t e = e0 + threadIdx.x;
-        uint32_t np = 0, nc = 0, ncx = 0;
-        uint32_t bin = 0, bend = 0;
-        uint32_t o_pair = 0, o_con = 0;
-        if (e < ni) {
-            bin = ent_bin[e];
-            bend = (uint32_t)bin_start[bin + 1];
-        }
-        if (STORE) {
-            // exclusive offsets of this thread's outputs: tile offset + in-tile scan of the counts of pass 1
-            const uint64_t mine = (e < ni) ? ent_count[e] : 0ull;
-            uint64_t incl = warp_incl_scan_bp(mine, lane);
-            if (lane == 31)
-                wsum[wid] = incl;
-            __syncthreads();
-            if (wid == 0) {
-                uint64_t w = (lane < PAIR_TILE / 32) ? wsum[lane] : 0ull;
-                uint64_t wi = warp_incl_scan_bp(w, lane);
-                if (lane < PAIR_TILE / 32)
-                    wsum[lane] = wi - w;
-            }
-            __syncthreads();
-            const uint64_t off = tile_count[tile] + wsum[wid] + incl - mine;
-            o_pair = (uint32_t)off;
-            o_con = (uint32_t)(off >> 32);
-        }
-        if (e < ni) {
-            const Rec& A = win[threadIdx.x];
-            const bool a_ok = A.body != UINT_MAX && (A.info & 2u);
-            if (a_ok) {
-                for (uint32_t j = e + 1; j < bend; j++) {
-                    Rec Bg;
-                    const Rec* Bp;
-                    if (j < wend) {
-                        Bp = &win[j - e0];
-                    } else {  // bin longer than the halo (coarse grids): fall back to global memory
-                        load_rec(Bg, ent_shape[j], meta, s_wpos, s_box, g.origin, envelope);
-                        Bp = &Bg;
-                    }
-                    const Rec& B = *Bp;
-                    if (!pair_passes(A, B, g, bin))
-                        continue;
-                    if (STORE && out.pairs)
-                        out.pairs[o_pair + np] = ((int64_t)A.id << 32) | (int64_t)B.id;
-                    np++;
-                    // fused narrowphase (single-contact analytic pairs), CMC/ChNarrowphase.cpp:264-320
-                    const int tA = (A.info >> 8) & 0xff, tB = (B.info >> 8) & 0xff;
-                    Contact c;
-                    int n = -1;
-                    if (algorithm != 0) {
-                        if (tA == CB200_SPHERE && tB == CB200_SPHERE)
-                            n = sphere_sphere(mk3(A.cx, A.cy, A.cz), A.r, mk3(B.cx, B.cy, B.cz), B.r, sep, c) ? 1 : 0;
-                        else
-                            n = prims_single(view_of(A, s_wrot, s_dims), view_of(B, s_wrot, s_dims), sep, c);
-                    }
-                    if (n < 0) {
-                        ncx++;
-                    } else if (n == 1) {
-                        if (STORE && out.c_norm) {
-                            const uint32_t o = o_con + nc;
-                            out.c_norm[3 * o] = c.n.x, out.c_norm[3 * o + 1] = c.n.y, out.c_norm[3 * o + 2] = c.n.z;
-                            out.c_pta[3 * o] = c.p1.x, out.c_pta[3 * o + 1] = c.p1.y, out.c_pta[3 * o + 2] = c.p1.z;
-                            out.c_ptb[3 * o] = c.p2.x, out.c_ptb[3 * o + 1] = c.p2.y, out.c_ptb[3 * o + 2] = c.p2.z;
-                            out.c_depth[o] = c.depth;
-                            out.c_erad[o] = c.erad;
-                            out.c_bids[2 * o] = (int32_t)A.body;
-                            out.c_bids[2 * o + 1] = (int32_t)B.body;
-                            out.c_shapes[o] = ((int64_t)A.id << 32) | (int64_t)B.id;
-                            out.c_mats[o] = (A.info >> 16) | (B.info >> 16) << 16;
-                        }
-                        nc++;
-                    }
-                }
-            }
-        }
-        if (!STORE) {
-            const uint64_t mine = (uint64_t)np | ((uint64_t)nc << 32);
-            if (e < ni)
-                ent_count[e] = mine;
-            uint64_t s = mine;
-#pragma unroll
-            for (int d = 16; d > 0; d >>= 1)
-                s += __shfl_xor_sync(0xffffffffu, s, d);
-            if (lane == 0)
-                wsum[wid] = s;
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                uint64_t t = 0;
-                for (int w = 0; w < PAIR_TILE / 32; w++)
-                    t += wsum[w];
-                tile_count[tile] = t;
-            }
-            if (ncx)
-                atomicAdd(&cnt->unsupported, ncx);
-        }
+        const uint32_t o = s + rank;
+        ent_shape[o] = id;
+        m.pad = id;
+        ent_m[o] = m;
+        reinterpret_cast<double4*>(ent_c)[o] = w;
     }
 }
 
@@ -826,37 +504,6 @@ int enqueue_aabb(System* S) {
     return CB200_OK;
 }
 
-int enqueue_pairs_only(System* S, bool want_pairs, bool want_contacts) {
-    if (S->ns == 0)
-        return CB200_OK;
-    const double env = S->set.collision_envelope;
-    const int algorithm = S->set.narrowphase_algorithm;
-    PairOut out;
-    memset(&out, 0, sizeof(out));
-    out.cap_pairs = S->cap_pairs;
-    out.cap_contacts = S->cap_contacts;
-    const int grid = grid_for(S, S->cap_entries, PAIR_TILE, 6);
-    k_pairs<false><<<grid, PAIR_TILE, 0, S->stream>>>(S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p,
-                                                      S->ent_shape.p, S->ent_bin.p, S->bin_start.p, env, algorithm,
-                                                      S->ent_count.p, S->tile_count.p, out, S->d_cnt);
-    S->launches++;
-    CB_TRY(scan_u64(S, S->tile_count.p, S->tile_count.p, &S->d_cnt->n_tiles, S->cap_entries / PAIR_TILE + 1));
-    if (want_pairs)
-        out.pairs = S->pairs.p;
-    if (want_contacts) {
-        out.c_norm = S->c_norm.p, out.c_pta = S->c_pta.p, out.c_ptb = S->c_ptb.p, out.c_depth = S->c_depth.p;
-        out.c_erad = S->c_erad.p, out.c_bids = S->c_bids.p, out.c_shapes = S->c_shapes.p, out.c_mats = S->c_mats.p;
-    }
-    k_pairs<true><<<grid, PAIR_TILE, 0, S->stream>>>(S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p,
-                                                     S->ent_shape.p, S->ent_bin.p, S->bin_start.p, env, algorithm,
-                                                     S->ent_count.p, S->tile_count.p, out, S->d_cnt);
-    S->launches++;
-    if (want_pairs)
-        S->pairs_valid = true;
-    CB_CUDA(cudaGetLastError());
-    return CB200_OK;
-}
-
 int enqueue_bins(System* S) {
     if (S->ns == 0)
         return CB200_OK;
@@ -877,18 +524,19 @@ int enqueue_bins(System* S) {
     CB_CUDA(cudaMemsetAsync(S->bin_cursor.p, 0, (size_t)S->cap_bins * 4, S->stream));
     k_bin_count<<<sgrid, 256, 0, S->stream>>>(gs, env, S->s_meta.p, S->s_wpos.p, S->s_box.p, S->bin_intersections.p,
                                               S->bin_cursor.p, S->large_list.p, S->heavy.p, S->d_cnt);
-    k_bin_large<false><<<64, 256, 0, S->stream>>>(S->s_meta.p, S->s_wpos.p, S->s_box.p, env, S->large_list.p, S->d_cnt,
+    k_bin_large<false><<<S->num_sms * 4, 256, 0, S->stream>>>(S->s_meta.p, S->s_wpos.p, S->s_box.p, env, S->large_list.p, S->d_cnt,
                                                   S->cap_entries, S->bin_cursor.p, nullptr, nullptr, nullptr);
     S->launches += 2;
     CB_TRY(scan_bins(S, S->bin_cursor.p, S->bin_start.p, &S->d_cnt->num_bins, S->cap_bins));
     k_bin_fill<<<sgrid, 256, 0, S->stream>>>(S->ns, env, S->s_meta.p, S->s_wpos.p, S->s_box.p, S->bin_intersections.p,
                                              S->bin_start.p, S->cap_entries, S->bin_cursor.p, S->ent_tmp.p,
                                              S->ent_bin.p, S->d_cnt);
-    k_bin_large<true><<<64, 256, 0, S->stream>>>(S->s_meta.p, S->s_wpos.p, S->s_box.p, env, S->large_list.p, S->d_cnt,
+    k_bin_large<true><<<S->num_sms * 4, 256, 0, S->stream>>>(S->s_meta.p, S->s_wpos.p, S->s_box.p, env, S->large_list.p, S->d_cnt,
                                                  S->cap_entries, S->bin_cursor.p, S->bin_start.p, S->ent_tmp.p,
                                                  S->ent_bin.p);
     k_bin_sort<<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(S->ent_tmp.p, S->ent_bin.p, S->bin_start.p,
-                                                                        S->ent_shape.p, S->d_cnt);
+                                                                        S->s_meta.p, S->s_wpos.p, S->ent_shape.p,
+                                                                        S->ent_c.p, S->ent_m.p, S->d_cnt);
     S->launches += 3;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;

@@ -121,7 +121,7 @@ struct Timer {
     bool armed = false;
 };
 
-enum { LARGE_BINS = 48, MAX_LARGE = 4096, MAX_HEAVY = 64, SMC_MAT_STRIDE = 13, NSC_MAT_STRIDE = 8, PAIR_TILE = 256,
+enum { LARGE_BINS = 48, MAX_LARGE = 4096, MAX_HEAVY = 64, SMC_MAT_STRIDE = 14, NSC_MAT_STRIDE = 8, PAIR_TILE = 256,
        PAIR_HALO = 96 };
 
 struct System {
@@ -174,8 +174,10 @@ struct System {
     DevBuf<uint32_t> ent_tmp;            // cap_entries  shape ids, unsorted inside a bin
     DevBuf<uint32_t> ent_bin;            // cap_entries  bin of every entry
     DevBuf<uint32_t> ent_shape;          // cap_entries  shape ids sorted inside a bin == bin_aabb_number
-    DevBuf<uint64_t> ent_count;          // cap_entries  pairs | contacts << 32 found by each entry
-    DevBuf<uint64_t> tile_count;         // cap_entries / PAIR_TILE + 2
+    DevBuf<double> ent_c;                // 4 per entry: world position + dims[0] of the entry's shape, bin-sorted
+    DevBuf<ShapeMeta> ent_m;             // per entry: integer record of the shape (pad = shape id), bin-sorted
+    DevBuf<uint64_t> ent_mask;           // cap_entries  bit j set: the entry pairs with the j-th entry of its bin
+    DevBuf<uint32_t> ent_off;            // cap_entries+2 outputs per entry -> exclusive offsets
     DevBuf<uint32_t> large_list;         // MAX_LARGE
     DevBuf<int64_t> pairs;               // cap_pairs (materialised on demand only)
     bool pairs_valid = false;

@@ -1,0 +1,546 @@
+// pairs.cu -- in-bin pair tests fused with the narrowphase decision, and contact generation.
+//
+// Reference path replaced (CMC = src/chrono/collision/multicore):
+//   f_Count/Store_AABB_AABB_Intersection  CMC/ChCollisionUtilsBroadphase.cpp:86-217  (per-bin O(k^2) filter)
+//   PreprocessCount + Thrust_Expand       CMC/ChNarrowphase.cpp:94-155               (slot allocation)
+//   DispatchPRIMS / DispatchHybridMPR     CMC/ChNarrowphase.cpp:264-320 + PRIMSCollision (ChNarrowphasePRIMS.cpp:1406-1607)
+//   count + remove_if                     CMC/ChNarrowphase.cpp:366-385              (stable compaction)
+//
+// Kernels (instead of the reference's two bin passes + five-pass expand + dispatch + seven-array remove_if):
+//   k_pair_masks   a CTA stages the records of its 256-entry tile plus a forward halo in shared memory as
+//                  struct-of-arrays (conflict-free); every warp spreads the pairs of the bins it owns evenly over its
+//                  lanes, applies the broadphase filter and -- for pairs with a single-contact analytic test (anything
+//                  against a sphere) -- the cheap part of that test (no sqrt, no division) that decides whether a
+//                  contact exists; the result is one 64-bit mask per (bin, shape) entry.
+//   (scan of the per-entry counts)
+//   k_pair_store   masks -> 64-bit shape-pair keys at their final, compacted slots (contacts; or the candidate pair
+//                  list, which is materialised only when somebody asks for it).
+//   k_contact_gen  one thread per contact, fully convergent: evaluates the analytic contact (normal, points,
+//                  depth, effective radius) and writes the contact SoA.
+// Order of the contact list = (bin, shape A, shape B) = the order the reference's stable compaction leaves.
+#include "grid.cuh"
+#include "prims.cuh"
+#include <limits.h>
+
+namespace cb200 {
+
+constexpr int WIN = PAIR_TILE + PAIR_HALO;
+
+// Shared-memory window, struct-of-arrays: lane-consecutive entries are word-consecutive in every array.
+struct Window {
+    double mn[3][WIN], mx[3][WIN];  // origin-relative AABB
+    double c[4][WIN];               // world position + dims[0] (sphere: centre, radius)
+    uint32_t body[WIN], fam[WIN], info[WIN], id[WIN];
+};
+
+struct Rec {
+    double mn[3], mx[3];
+    double cx, cy, cz, r;
+    uint32_t body, fam, info, id;
+};
+
+__device__ __forceinline__ void load_rec(Rec& R, uint32_t id, const ShapeMeta* __restrict__ meta,
+                                         const double* __restrict__ s_wpos, const ShapeBox* __restrict__ s_box,
+                                         const double* origin, double envelope) {
+    const ShapeMeta m = meta[id];
+    const double4 w = reinterpret_cast<const double4*>(s_wpos)[id];
+    R.cx = w.x, R.cy = w.y, R.cz = w.z, R.r = w.w;
+    R.body = m.body, R.fam = m.fam, R.info = m.info, R.id = id;
+    shape_box_rel(id, m.info, s_wpos, s_box, origin, envelope, R.mn, R.mx);
+}
+
+// record of entry e from the bin-sorted copies (coalesced); boxes of non-spheres are gathered
+__device__ __forceinline__ void load_rec_sorted(Rec& R, uint32_t e, const ShapeMeta* __restrict__ ent_m,
+                                                const double* __restrict__ ent_c, const double* __restrict__ s_wpos,
+                                                const ShapeBox* __restrict__ s_box, const double* origin,
+                                                double envelope) {
+    const ShapeMeta m = ent_m[e];
+    const double4 w = reinterpret_cast<const double4*>(ent_c)[e];
+    R.cx = w.x, R.cy = w.y, R.cz = w.z, R.r = w.w;
+    R.body = m.body, R.fam = m.fam, R.info = m.info, R.id = m.pad;
+    if (((m.info >> 8) & 0xff) == CB200_SPHERE) {
+        const double r = w.w + envelope;
+        R.mn[0] = (w.x - r) - origin[0], R.mn[1] = (w.y - r) - origin[1], R.mn[2] = (w.z - r) - origin[2];
+        R.mx[0] = (w.x + r) - origin[0], R.mx[1] = (w.y + r) - origin[1], R.mx[2] = (w.z + r) - origin[2];
+    } else {
+        shape_box_rel(m.pad, m.info, s_wpos, s_box, origin, envelope, R.mn, R.mx);
+    }
+}
+
+__device__ __forceinline__ void win_put(Window& W, int k, const Rec& R) {
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        W.mn[a][k] = R.mn[a];
+        W.mx[a][k] = R.mx[a];
+    }
+    W.c[0][k] = R.cx, W.c[1][k] = R.cy, W.c[2][k] = R.cz, W.c[3][k] = R.r;
+    W.body[k] = R.body, W.fam[k] = R.fam, W.info[k] = R.info, W.id[k] = R.id;
+}
+
+__device__ __forceinline__ void win_get(const Window& W, int k, Rec& R) {
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        R.mn[a] = W.mn[a][k];
+        R.mx[a] = W.mx[a][k];
+    }
+    R.cx = W.c[0][k], R.cy = W.c[1][k], R.cz = W.c[2][k], R.r = W.c[3][k];
+    R.body = W.body[k], R.fam = W.fam[k], R.info = W.info[k], R.id = W.id[k];
+}
+
+// CMC/ChCollisionUtilsBroadphase.cpp:114-140 (a pure conjunction, so the evaluation order is free)
+__device__ __forceinline__ bool pair_passes(const Rec& A, const Rec& B, const GridParams& g, uint32_t bin) {
+    if (!((A.mn[0] <= B.mx[0] && B.mn[0] <= A.mx[0]) && (A.mn[1] <= B.mx[1] && B.mn[1] <= A.mx[1]) &&
+          (A.mn[2] <= B.mx[2] && B.mn[2] <= A.mx[2])))
+        return false;
+    // current_bin (CMC/ChCollisionUtils.h:97-110): the pair belongs to the bin holding max(Amin, Bmin)
+    const int cx = (int)floor(fmax(A.mn[0], B.mn[0]) * g.inv[0]);
+    const int cy = (int)floor(fmax(A.mn[1], B.mn[1]) * g.inv[1]);
+    const int cz = (int)floor(fmax(A.mn[2], B.mn[2]) * g.inv[2]);
+    if ((uint32_t)((cz * g.bins[1]) * g.bins[0] + cy * g.bins[0] + cx) != bin)
+        return false;
+    if (B.body == UINT_MAX || A.body == B.body)
+        return false;
+    if (!(B.info & 2u))
+        return false;
+    if (!(A.info & 1u) && !(B.info & 1u))
+        return false;
+    const uint32_t gA = A.fam & 0xffffu, mA = A.fam >> 16, gB = B.fam & 0xffffu, mB = B.fam >> 16;
+    return (mA & gB) && (mB & gA);
+}
+
+struct ShapeView {
+    int type;
+    d3 pos;
+    q4 rot;
+    double d0, d1, d2, d3_;
+};
+
+__device__ __forceinline__ ShapeView make_view(uint32_t id, int type, const double4& w,
+                                               const double* __restrict__ s_wrot, const double* __restrict__ s_dims) {
+    ShapeView v;
+    v.type = type;
+    v.pos = mk3(w.x, w.y, w.z);
+    v.d0 = w.w;
+    v.d1 = v.d2 = v.d3_ = 0;
+    v.rot = mkq(1, 0, 0, 0);
+    if (type != CB200_SPHERE) {
+        const double4 r = reinterpret_cast<const double4*>(s_wrot)[id];
+        v.rot = mkq(r.x, r.y, r.z, r.w);
+        const double4 d = reinterpret_cast<const double4*>(s_dims)[id];
+        v.d1 = d.y, v.d2 = d.z, v.d3_ = d.w;
+    }
+    return v;
+}
+
+// Analytic dispatcher for pairs with at most one contact (everything that involves a sphere),
+// PRIMSCollision, CMC/ChNarrowphasePRIMS.cpp:1406-1607.
+// Returns 1/0 contacts, or -1 when the combination is not of that kind (multi-contact analytic pair or MPR).
+// Callers that only use the return value get the decision alone: the compiler drops the sqrt/divisions that
+// feed nothing but the unused Contact.
+__device__ __forceinline__ int prims_single(const ShapeView& A, const ShapeView& B, double sep, Contact& c) {
+    bool hit;
+    if (A.type == CB200_SPHERE && B.type == CB200_SPHERE)
+        return sphere_sphere(A.pos, A.d0, B.pos, B.d0, sep, c) ? 1 : 0;
+    if (B.type == CB200_SPHERE) {
+        switch (A.type) {
+            case CB200_CAPSULE:
+                return capsule_sphere(A.pos, A.rot, A.d0, A.d1, B.pos, B.d0, sep, c) ? 1 : 0;
+            case CB200_CYLINDER:
+                return cylinder_sphere(A.pos, A.rot, A.d0, A.d1, B.pos, B.d0, sep, c) ? 1 : 0;
+            case CB200_ROUNDEDCYL:
+                return roundedcyl_sphere(A.pos, A.rot, A.d0, A.d1, A.d3_, B.pos, B.d0, sep, c) ? 1 : 0;
+            case CB200_BOX:
+                return box_sphere(A.pos, A.rot, mk3(A.d0, A.d1, A.d2), B.pos, B.d0, sep, c) ? 1 : 0;
+            case CB200_ROUNDEDBOX:
+                return roundedbox_sphere(A.pos, A.rot, mk3(A.d0, A.d1, A.d2), A.d3_, B.pos, B.d0, sep, c) ? 1 : 0;
+            default:
+                return -1;
+        }
+    }
+    if (A.type == CB200_SPHERE) {
+        // swapped call: the shape function sees (B, A); points are exchanged and the normal negated
+        // (ChNarrowphasePRIMS.cpp:1435-1443 and siblings)
+        switch (B.type) {
+            case CB200_CAPSULE:
+                hit = capsule_sphere(B.pos, B.rot, B.d0, B.d1, A.pos, A.d0, sep, c);
+                break;
+            case CB200_CYLINDER:
+                hit = cylinder_sphere(B.pos, B.rot, B.d0, B.d1, A.pos, A.d0, sep, c);
+                break;
+            case CB200_ROUNDEDCYL:
+                hit = roundedcyl_sphere(B.pos, B.rot, B.d0, B.d1, B.d3_, A.pos, A.d0, sep, c);
+                break;
+            case CB200_BOX:
+                hit = box_sphere(B.pos, B.rot, mk3(B.d0, B.d1, B.d2), A.pos, A.d0, sep, c);
+                break;
+            case CB200_ROUNDEDBOX:
+                hit = roundedbox_sphere(B.pos, B.rot, mk3(B.d0, B.d1, B.d2), B.d3_, A.pos, A.d0, sep, c);
+                break;
+            default:
+                return -1;
+        }
+        if (hit) {
+            const d3 t = c.p1;
+            c.p1 = c.p2;
+            c.p2 = t;
+            c.n = -c.n;
+            return 1;
+        }
+        return 0;
+    }
+    return -1;
+}
+
+// cold path of pair_hit (a non-sphere is involved): kept out of line so that the sphere-sphere loop stays lean
+__device__ __noinline__ int pair_hit_general(uint32_t idA, int tA, double4 wA, uint32_t idB, int tB, double4 wB,
+                                             double sep, const double* __restrict__ s_wrot,
+                                             const double* __restrict__ s_dims) {
+    Contact c;
+    return prims_single(make_view(idA, tA, wA, s_wrot, s_dims), make_view(idB, tB, wB, s_wrot, s_dims), sep, c);
+}
+
+// decision only: does the pair (A, B) produce a contact?  1 / 0 / -1 (not a single-contact analytic pair)
+__device__ __forceinline__ int pair_hit(const Rec& A, const Rec& B, double sep, int algorithm,
+                                        const double* __restrict__ s_wrot, const double* __restrict__ s_dims) {
+    if (algorithm == 0)
+        return -1;  // MPR for everything
+    const int tA = (A.info >> 8) & 0xff, tB = (B.info >> 8) & 0xff;
+    if (tA == CB200_SPHERE && tB == CB200_SPHERE) {
+        // the deciding lines of sphere_sphere, ChNarrowphasePRIMS.cpp:52-60
+        const d3 delta = mk3(B.cx, B.cy, B.cz) - mk3(A.cx, A.cy, A.cz);
+        const double dist2 = dot3(delta, delta);
+        const double radSum_s = (A.r + B.r) + sep;
+        return !(dist2 >= radSum_s * radSum_s || dist2 < 1e-12);
+    }
+    return pair_hit_general(A.id, tA, make_double4(A.cx, A.cy, A.cz, A.r), B.id, tB,
+                            make_double4(B.cx, B.cy, B.cz, B.r), sep, s_wrot, s_dims);
+}
+
+template <typename T>
+__device__ __forceinline__ T warp_incl_scan_bp(T v, int lane) {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        T o = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d)
+            v += o;
+    }
+    return v;
+}
+
+
+// --------------------------------------------------------------------------------------------------------------
+// k_pair_masks: all unordered pairs of a bin, spread evenly over the lanes of the warp that owns the bin.
+//
+// A warp owns the bins whose first entry lies in its 32-entry chunk.  For a bin of k <= 64 entries it walks the
+// k(k-1)/2 pairs in the cyclic order (i, i+d mod k), d = 1..(k-1)/2 (+ half a diagonal when k is even): every
+// lane always has a pair, whatever its position in the bin.  A pair that passes (the broadphase filter alone in
+// PAIRS mode, filter + contact decision in CONTACTS mode) sets bit max(i,j) in the 64-bit mask of entry min(i,j).
+// The masks are all the store pass needs: its output slot for (i, j) is offset[i] + popc(mask[i] below bit j),
+// i.e. the reference's emission order (bin, shape A, shape B), without re-running a single test.
+// Bins with more than 64 entries (coarse grids) are walked row by row by the owning warp and only counted; the
+// store pass re-tests those rows.
+// --------------------------------------------------------------------------------------------------------------
+enum { MODE_PAIRS = 0, MODE_CONTACTS = 1 };
+
+__device__ __forceinline__ bool pair_decide(const Rec& A, const Rec& B, const GridParams& g, uint32_t bin, int mode,
+                                            double sep, int algorithm, const double* __restrict__ s_wrot,
+                                            const double* __restrict__ s_dims, uint32_t& np, uint32_t& ncx) {
+    if (A.body == UINT_MAX || !(A.info & 2u))
+        return false;
+    if (!pair_passes(A, B, g, bin))
+        return false;
+    np++;
+    if (mode == MODE_PAIRS)
+        return true;
+    const int n = pair_hit(A, B, sep, algorithm, s_wrot, s_dims);
+    if (n < 0)
+        ncx++;
+    return n == 1;
+}
+
+__global__ void __launch_bounds__(PAIR_TILE, 3) k_pair_masks(const ShapeMeta* __restrict__ meta,
+                                                          const ShapeMeta* __restrict__ ent_m,
+                                                          const double* __restrict__ ent_c,
+                                                          const double* __restrict__ s_wpos,
+                                                          const ShapeBox* __restrict__ s_box,
+                                                          const double* __restrict__ s_wrot,
+                                                          const double* __restrict__ s_dims,
+                                                          const uint32_t* __restrict__ ent_shape,
+                                                          const uint32_t* __restrict__ ent_bin,
+                                                          const uint64_t* __restrict__ bin_start, double envelope,
+                                                          int algorithm, int mode, uint64_t* __restrict__ ent_mask,
+                                                          uint32_t* __restrict__ ent_cnt,
+                                                          DevCounters* __restrict__ cnt) {
+    __shared__ Window W;
+    __shared__ unsigned long long smask[WIN];
+    if (cnt->overflow)
+        return;
+    const GridParams g = load_grid(cnt);
+    const uint32_t ni = cnt->n_intersections;
+    const uint32_t ntiles = cnt->n_tiles;
+    const double sep = 2 * envelope;
+    const int lane = threadIdx.x & 31;
+    uint32_t np = 0, ncx = 0;
+
+    for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const uint32_t e0 = tile * PAIR_TILE;
+        const uint32_t wend = min(ni, e0 + WIN);
+        __syncthreads();  // previous tile's readers are done with the window
+        for (uint32_t k = threadIdx.x; e0 + k < wend; k += PAIR_TILE) {
+            Rec R;
+            load_rec_sorted(R, e0 + k, ent_m, ent_c, s_wpos, s_box, g.origin, envelope);
+            win_put(W, k, R);
+            smask[k] = 0ull;
+        }
+        __syncthreads();
+
+        // bins that start in this warp's chunk
+        const uint32_t e = e0 + threadIdx.x;
+        uint32_t bin = 0, bs = 0, bk = 0;
+        bool starts = false;
+        if (e < ni) {
+            bin = ent_bin[e];
+            const uint32_t s = (uint32_t)bin_start[bin];
+            starts = (s == e);
+            if (starts) {
+                bs = s;
+                bk = (uint32_t)bin_start[bin + 1] - s;
+            }
+        }
+        unsigned todo = __ballot_sync(0xffffffffu, starts);
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const uint32_t b = __shfl_sync(0xffffffffu, bin, src);
+            const uint32_t s = __shfl_sync(0xffffffffu, bs, src);
+            const uint32_t k = __shfl_sync(0xffffffffu, bk, src);
+            if (k < 2) {
+                if (lane == 0) {
+                    ent_mask[s] = 0ull;
+                    ent_cnt[s] = 0;
+                }
+                continue;
+            }
+            const uint32_t w0 = s - e0;  // window index of the bin's first entry
+            if (k <= 64) {
+                const uint32_t h = (k - 1) >> 1;
+                const uint32_t full = k * h;
+                const uint32_t total = full + ((k & 1u) ? 0u : (k >> 1));
+                const uint32_t M = ((1u << 20) + k - 1) / k;  // p / k == (p * M) >> 20 for p < 2048, k <= 64
+                for (uint32_t p0 = 0; p0 < total; p0 += 32) {
+                    const uint32_t p = p0 + lane;
+                    if (p < total) {
+                        uint32_t i, j;
+                        if (p < full) {
+                            const uint32_t d = (p * M) >> 20;
+                            i = p - d * k;
+                            j = i + d + 1;
+                            if (j >= k)
+                                j -= k;
+                        } else {
+                            i = p - full;
+                            j = i + (k >> 1);
+                        }
+                        const uint32_t a = min(i, j), c = max(i, j);
+                        Rec A, B;
+                        win_get(W, (int)(w0 + a), A);
+                        win_get(W, (int)(w0 + c), B);
+                        if (pair_decide(A, B, g, b, mode, sep, algorithm, s_wrot, s_dims, np, ncx))
+                            atomicOr(&smask[w0 + a], 1ull << c);
+                    }
+                }
+                __syncwarp();
+                for (uint32_t t = lane; t < k; t += 32) {
+                    const unsigned long long m = smask[w0 + t];
+                    ent_mask[s + t] = m;
+                    ent_cnt[s + t] = (uint32_t)__popcll(m);
+                }
+            } else {
+                // long bin: rows one after the other, lanes across the row; count only
+                for (uint32_t i = 0; i + 1 < k; i++) {
+                    Rec A;
+                    if (s + i < wend)
+                        win_get(W, (int)(w0 + i), A);
+                    else
+                        load_rec(A, ent_shape[s + i], meta, s_wpos, s_box, g.origin, envelope);
+                    uint32_t hits = 0;
+                    for (uint32_t j = i + 1 + lane; j < k; j += 32) {
+                        Rec B;
+                        if (s + j < wend)
+                            win_get(W, (int)(w0 + j), B);
+                        else
+                            load_rec(B, ent_shape[s + j], meta, s_wpos, s_box, g.origin, envelope);
+                        hits += pair_decide(A, B, g, b, mode, sep, algorithm, s_wrot, s_dims, np, ncx) ? 1u : 0u;
+                    }
+#pragma unroll
+                    for (int d = 16; d > 0; d >>= 1)
+                        hits += __shfl_xor_sync(0xffffffffu, hits, d);
+                    if (lane == 0) {
+                        ent_mask[s + i] = 0ull;
+                        ent_cnt[s + i] = hits;
+                    }
+                }
+                if (lane == 0) {
+                    ent_mask[s + k - 1] = 0ull;
+                    ent_cnt[s + k - 1] = 0;
+                }
+            }
+        }
+    }
+    // totals that are not tied to an entry: N_p (contacts mode) and the pairs this backend cannot test
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        np += __shfl_xor_sync(0xffffffffu, np, d);
+        ncx += __shfl_xor_sync(0xffffffffu, ncx, d);
+    }
+    if (lane == 0) {
+        if (mode == MODE_CONTACTS && np)
+            atomicAdd(&cnt->n_pairs, np);
+        if (ncx)
+            atomicAdd(&cnt->unsupported, ncx);
+    }
+}
+
+// k_pair_store: one thread per entry; turns masks (or, for long bins, a re-walk of the row) into 64-bit shape-pair
+// keys at their final, compacted positions.
+__global__ void __launch_bounds__(256) k_pair_store(const ShapeMeta* __restrict__ meta,
+                                                    const double* __restrict__ s_wpos,
+                                                    const ShapeBox* __restrict__ s_box,
+                                                    const double* __restrict__ s_wrot,
+                                                    const double* __restrict__ s_dims,
+                                                    const uint32_t* __restrict__ ent_shape,
+                                                    const uint32_t* __restrict__ ent_bin,
+                                                    const uint64_t* __restrict__ bin_start, double envelope,
+                                                    int algorithm, int mode, const uint64_t* __restrict__ ent_mask,
+                                                    const uint32_t* __restrict__ ent_off, int64_t* __restrict__ out,
+                                                    uint32_t cap, DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    const uint32_t ni = cnt->n_intersections;
+    const uint32_t total = ent_off[ni];
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        if (mode == MODE_CONTACTS) {
+            cnt->n_contacts = total;
+            if (total > cap) {
+                cnt->need_contacts = total;
+                atomicOr(&cnt->overflow, (uint32_t)OVF_CONTACTS);
+            }
+        } else {
+            cnt->n_pairs = total;
+            if (total > cap) {
+                cnt->need_pairs = total;
+                atomicOr(&cnt->overflow, (uint32_t)OVF_PAIRS);
+            }
+        }
+    }
+    if (total > cap)
+        return;
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < ni; e += gridDim.x * blockDim.x) {
+        uint32_t o = ent_off[e];
+        if (ent_off[e + 1] == o)
+            continue;
+        const uint32_t bin = ent_bin[e];
+        const uint32_t s = (uint32_t)bin_start[bin], k = (uint32_t)bin_start[bin + 1] - s;
+        const int64_t hiA = (int64_t)ent_shape[e] << 32;
+        if (k <= 64) {
+            unsigned long long m = ent_mask[e];
+            while (m) {
+                const int j = __ffsll((long long)m) - 1;
+                m &= m - 1;
+                out[o++] = hiA | (int64_t)ent_shape[s + j];
+            }
+        } else {
+            const GridParams g = load_grid(cnt);
+            Rec A;
+            load_rec(A, ent_shape[e], meta, s_wpos, s_box, g.origin, envelope);
+            uint32_t np = 0, ncx = 0;
+            for (uint32_t j = e + 1; j < s + k; j++) {
+                Rec B;
+                load_rec(B, ent_shape[j], meta, s_wpos, s_box, g.origin, envelope);
+                if (pair_decide(A, B, g, bin, mode, 2 * envelope, algorithm, s_wrot, s_dims, np, ncx))
+                    out[o++] = hiA | (int64_t)B.id;
+            }
+        }
+    }
+}
+// --------------------------------------------------------------------------------------------------------------
+// k_contact_gen: one thread per contact key -> the contact record (DispatchPRIMS on the compacted list).
+// --------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_contact_gen(const ShapeMeta* __restrict__ meta,
+                                                     const double* __restrict__ s_wpos,
+                                                     const double* __restrict__ s_wrot,
+                                                     const double* __restrict__ s_dims,
+                                                     const int64_t* __restrict__ c_shapes, double envelope,
+                                                     double* __restrict__ c_norm, double* __restrict__ c_pta,
+                                                     double* __restrict__ c_ptb, double* __restrict__ c_depth,
+                                                     double* __restrict__ c_erad, int32_t* __restrict__ c_bids,
+                                                     uint32_t* __restrict__ c_mats,
+                                                     const DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    const uint32_t nc = cnt->n_contacts;
+    const double sep = 2 * envelope;
+    for (uint32_t o = blockIdx.x * blockDim.x + threadIdx.x; o < nc; o += gridDim.x * blockDim.x) {
+        const int64_t key = c_shapes[o];
+        const uint32_t sA = (uint32_t)(key >> 32), sB = (uint32_t)(key & 0xffffffff);
+        const ShapeMeta mA = meta[sA], mB = meta[sB];
+        const double4 wA = reinterpret_cast<const double4*>(s_wpos)[sA];
+        const double4 wB = reinterpret_cast<const double4*>(s_wpos)[sB];
+        const int tA = (mA.info >> 8) & 0xff, tB = (mB.info >> 8) & 0xff;
+        Contact c;
+        if (tA == CB200_SPHERE && tB == CB200_SPHERE)
+            sphere_sphere(mk3(wA.x, wA.y, wA.z), wA.w, mk3(wB.x, wB.y, wB.z), wB.w, sep, c);
+        else
+            prims_single(make_view(sA, tA, wA, s_wrot, s_dims), make_view(sB, tB, wB, s_wrot, s_dims), sep, c);
+        c_norm[3 * o] = c.n.x, c_norm[3 * o + 1] = c.n.y, c_norm[3 * o + 2] = c.n.z;
+        c_pta[3 * o] = c.p1.x, c_pta[3 * o + 1] = c.p1.y, c_pta[3 * o + 2] = c.p1.z;
+        c_ptb[3 * o] = c.p2.x, c_ptb[3 * o + 1] = c.p2.y, c_ptb[3 * o + 2] = c.p2.z;
+        c_depth[o] = c.depth;
+        c_erad[o] = c.erad;
+        reinterpret_cast<int2*>(c_bids)[o] = make_int2((int)mA.body, (int)mB.body);
+        c_mats[o] = (mA.info >> 16) | (mB.info >> 16) << 16;
+    }
+}
+
+// --------------------------------------------------------------------------------------------------------------
+
+// --------------------------------------------------------------------------------------------------------------
+// host side: enqueue only, no synchronisation
+// --------------------------------------------------------------------------------------------------------------
+static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
+    const double env = S->set.collision_envelope;
+    const int algorithm = S->set.narrowphase_algorithm;
+    if (mode == MODE_CONTACTS)
+        CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_pairs, 0, 4, S->stream));
+    k_pair_masks<<<grid_for(S, S->cap_entries, PAIR_TILE, 6), PAIR_TILE, 0, S->stream>>>(
+        S->s_meta.p, S->ent_m.p, S->ent_c.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
+        env, algorithm, mode, S->ent_mask.p, S->ent_off.p, S->d_cnt);
+    S->launches++;
+    CB_TRY(scan_u32(S, S->ent_off.p, S->ent_off.p, &S->d_cnt->n_intersections, S->cap_entries));
+    k_pair_store<<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
+        S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
+        env, algorithm, mode, S->ent_mask.p, S->ent_off.p, out, cap, S->d_cnt);
+    S->launches++;
+    CB_CUDA(cudaGetLastError());
+    return CB200_OK;
+}
+
+int enqueue_pairs_only(System* S, bool want_pairs, bool want_contacts) {
+    if (S->ns == 0)
+        return CB200_OK;
+    if (want_pairs) {
+        CB_TRY(enqueue_pair_pass(S, MODE_PAIRS, S->pairs.p, S->cap_pairs));
+        S->pairs_valid = true;
+    }
+    if (want_contacts) {
+        CB_TRY(enqueue_pair_pass(S, MODE_CONTACTS, S->c_shapes.p, S->cap_contacts));
+        k_contact_gen<<<grid_for(S, S->cap_contacts, 256), 256, 0, S->stream>>>(
+            S->s_meta.p, S->s_wpos.p, S->s_wrot.p, S->s_dims.p, S->c_shapes.p, S->set.collision_envelope, S->c_norm.p,
+            S->c_pta.p, S->c_ptb.p, S->c_depth.p, S->c_erad.p, S->c_bids.p, S->c_mats.p, S->d_cnt);
+        S->launches++;
+        CB_CUDA(cudaGetLastError());
+    }
+    return CB200_OK;
+}
+
+}  // namespace cb200

@@ -109,6 +109,9 @@ __global__ void __launch_bounds__(256) k_smc_force(SmcParams P, const int32_t* _
         double char_vel = P.char_vel;
         const double eps = DBL_EPSILON;
         bool done = false;
+        // kn_simple / gn_simple only decide whether rolling / spinning friction is switched off (:485-495);
+        // without such friction in the material pair they are never looked at
+        const bool need_simple = muRoll_eff > eps || muSpin_eff > eps;
 
         switch (P.force_model) {
             case 0:  // Hooke (:259-281)
@@ -137,8 +140,9 @@ __global__ void __launch_bounds__(256) k_smc_force(SmcParams P, const int32_t* _
                     const double sqrt_Rd = sqrt(erad * delta_n);
                     const double Sn = 2 * E_eff * sqrt_Rd;
                     const double St = 8 * G_eff * sqrt_Rd;
-                    const double loge = (cr_eff < eps) ? log(eps) : log(cr_eff);
-                    const double beta = loge / sqrt(loge * loge + CH_PI_D * CH_PI_D);
+                    // beta = loge / sqrt(loge^2 + pi^2), loge = log(max(cr, eps)): a per-material-pair constant,
+                    // tabulated on the host (M[13]) instead of one log + sqrt + division per contact
+                    const double beta = M[13];
                     kn = CH_2_3_D * Sn;
                     kt = St;
                     gn = -2 * sqrt(5.0 / 6) * beta * sqrt(Sn * m_eff);
@@ -150,8 +154,10 @@ __global__ void __launch_bounds__(256) k_smc_force(SmcParams P, const int32_t* _
                     gn = tmp * m_eff * user_gn;
                     gt = tmp * m_eff * user_gt;
                 }
-                kn_simple = kn / sqrt(delta_n);
-                gn_simple = gn / pow(delta_n, 0.25);
+                if (need_simple) {
+                    kn_simple = kn / sqrt(delta_n);
+                    gn_simple = gn / sqrt(sqrt(delta_n));  // delta_n^0.25
+                }
                 break;
             case 3:  // Flores (:308-334)
                 if (P.use_mat_props) {
@@ -229,12 +235,14 @@ __global__ void __launch_bounds__(256) k_smc_force(SmcParams P, const int32_t* _
         const d3 torque2_loc = cross3(pt2_loc, rotate_t(force, B2.rot));
 
         // rolling / spinning friction only for persistent contacts (:488-530)
-        const double d_coeff = gn_simple / (2.0 * m_eff * sqrt(kn_simple / m_eff));
-        if (d_coeff < 1.0) {
-            const double t_collision = CH_PI_D * sqrt(m_eff / (kn_simple * (1 - d_coeff * d_coeff)));
-            if (t_contact <= t_collision) {
-                muRoll_eff = 0.0;
-                muSpin_eff = 0.0;
+        if (need_simple) {
+            const double d_coeff = gn_simple / (2.0 * m_eff * sqrt(kn_simple / m_eff));
+            if (d_coeff < 1.0) {
+                const double t_collision = CH_PI_D * sqrt(m_eff / (kn_simple * (1 - d_coeff * d_coeff)));
+                if (t_contact <= t_collision) {
+                    muRoll_eff = 0.0;
+                    muSpin_eff = 0.0;
+                }
             }
         }
         d3 m_roll1 = mk3(0), m_roll2 = mk3(0), m_spin1 = mk3(0), m_spin2 = mk3(0);
