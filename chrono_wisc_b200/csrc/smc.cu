@@ -47,7 +47,8 @@ __device__ __forceinline__ BodyView load_body(uint32_t b, const double* __restri
     return B;
 }
 
-__global__ void __launch_bounds__(256) k_smc_force(SmcParams P, const int32_t* __restrict__ bids,
+template <int FORCE_MODEL, bool USE_MAT>
+__global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, const int32_t* __restrict__ bids,
                                                    const uint32_t* __restrict__ c_mats,
                                                    const double* __restrict__ c_norm, const double* __restrict__ c_pta,
                                                    const double* __restrict__ c_ptb, const double* __restrict__ c_depth,
@@ -113,9 +114,9 @@ __global__ void __launch_bounds__(256) k_smc_force(SmcParams P, const int32_t* _
         // without such friction in the material pair they are never looked at
         const bool need_simple = muRoll_eff > eps || muSpin_eff > eps;
 
-        switch (P.force_model) {
+        switch (FORCE_MODEL) {
             case 0:  // Hooke (:259-281)
-                if (P.use_mat_props) {
+                if (USE_MAT) {
                     const double tmp_k = (16.0 / 15) * sqrt(erad) * E_eff;
                     const double v2 = char_vel * char_vel;
                     double loge = (cr_eff < eps) ? log(eps) : log(cr_eff);
@@ -136,7 +137,7 @@ __global__ void __launch_bounds__(256) k_smc_force(SmcParams P, const int32_t* _
                 gn_simple = gn;
                 break;
             case 1:  // Hertz (:283-306)
-                if (P.use_mat_props) {
+                if (USE_MAT) {
                     const double sqrt_Rd = sqrt(erad * delta_n);
                     const double Sn = 2 * E_eff * sqrt_Rd;
                     const double St = 8 * G_eff * sqrt_Rd;
@@ -160,7 +161,7 @@ __global__ void __launch_bounds__(256) k_smc_force(SmcParams P, const int32_t* _
                 }
                 break;
             case 3:  // Flores (:308-334)
-                if (P.use_mat_props) {
+                if (USE_MAT) {
                     const double sqrt_Rd = sqrt(erad * delta_n);
                     const double Sn = 2 * E_eff * sqrt_Rd;
                     const double St = 8 * G_eff * sqrt_Rd;
@@ -183,7 +184,7 @@ __global__ void __launch_bounds__(256) k_smc_force(SmcParams P, const int32_t* _
                 gn_simple = gn / pow(delta_n, 1.5);
                 break;
             default:  // PlainCoulomb (:336-438)
-                if (P.use_mat_props) {
+                if (USE_MAT) {
                     const double sqrt_Rd = sqrt(delta_n);
                     const double Sn = 2 * E_eff * sqrt_Rd;
                     const double loge = (cr_eff < eps) ? log(eps) : log(cr_eff);
@@ -512,10 +513,21 @@ int enqueue_smc(System* S) {
     const int cgrid = grid_for(S, S->cap_contacts, 256);
     CB_CUDA(cudaMemsetAsync(S->b_deg.p, 0, (size_t)(nb + 1) * 4, S->stream));
     CB_CUDA(cudaMemsetAsync(S->b_cursor.p, 0, (size_t)nb * 4, S->stream));
-    k_smc_force<<<cgrid, 256, 0, S->stream>>>(P, S->c_bids.p, S->c_mats.p, S->c_norm.p, S->c_pta.p, S->c_ptb.p,
-                                              S->c_depth.p, S->c_erad.p, S->pos.p, S->rot.p, S->vel.p, S->mass.p,
-                                              S->mat_smc.p, S->heavy.p, S->b_deg.p, S->ct_force.p, S->ct_torque.p,
-                                              S->d_cnt);
+    const int fgrid = grid_for(S, S->cap_contacts, 128, 16);
+#define SMC_LAUNCH(FM, UM)                                                                                        \
+    k_smc_force<FM, UM><<<fgrid, 128, 0, S->stream>>>(P, S->c_bids.p, S->c_mats.p, S->c_norm.p, S->c_pta.p,        \
+                                                      S->c_ptb.p, S->c_depth.p, S->c_erad.p, S->pos.p, S->rot.p,   \
+                                                      S->vel.p, S->mass.p, S->mat_smc.p, S->heavy.p, S->b_deg.p,   \
+                                                      S->ct_force.p, S->ct_torque.p, S->d_cnt)
+    // one instantiation per force model: the runtime switch of the reference (...SMC.cpp:258-440) costs registers
+    const bool um = P.use_mat_props != 0;
+    switch (P.force_model) {
+        case 0: if (um) SMC_LAUNCH(0, true); else SMC_LAUNCH(0, false); break;
+        case 1: if (um) SMC_LAUNCH(1, true); else SMC_LAUNCH(1, false); break;
+        case 3: if (um) SMC_LAUNCH(3, true); else SMC_LAUNCH(3, false); break;
+        default: if (um) SMC_LAUNCH(2, true); else SMC_LAUNCH(2, false); break;
+    }
+#undef SMC_LAUNCH
     S->launches++;
     CB_TRY(scan_u32(S, S->b_deg.p, S->b_deg.p, &S->d_cnt->n_bodies, nb));
     k_inc_fill<<<cgrid, 256, 0, S->stream>>>(S->c_bids.p, S->heavy.p, S->b_deg.p, S->b_cursor.p, S->b_inc.p, S->d_cnt);
