@@ -62,6 +62,34 @@ class ClockSampler(threading.Thread):
         self.stop_flag = threading.Event()
 
     def run(self):
+        # NVML in-process (no nvidia-smi fork per sample: a fork every 200 ms perturbs the launch thread)
+        try:
+            import pynvml as nv
+
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            bits = {"hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown if hasattr(nv, "nvmlClocksEventReasonHwSlowdown")
+                    else nv.nvmlClocksThrottleReasonHwSlowdown,
+                    "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown",
+                                                   getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0)),
+                    "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown",
+                                                   getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0)),
+                    "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap",
+                                            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0))}
+            while not self.stop_flag.is_set():
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for n, b in bits.items():
+                    if b and (r & b):
+                        self.reasons.add(n)
+                self.stop_flag.wait(0.05)
+            return
+        except Exception:
+            pass
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
@@ -279,7 +307,7 @@ def main():
     ap.add_argument("--ny", type=int, default=250)
     ap.add_argument("--nz", type=int, default=16)
     ap.add_argument("--spacing", type=float, default=2.0, help="lattice spacing in sphere radii")
-    ap.add_argument("--bin-edge", type=float, default=0.0,
+    ap.add_argument("--bin-edge", type=float, default=2.5,
                     help="0: FIXED_DENSITY 5 shapes/bin; >0: FIXED_BIN_SIZE with this edge in sphere diameters")
     ap.add_argument("--settle", type=int, default=300, help="untimed steps before warm-up (bed forms its contacts)")
     ap.add_argument("--e2e-steps", type=int, default=20)
