@@ -106,6 +106,11 @@ _SIGNATURES = {
     "cb200_download_body_contact_forces": (C.c_int, [_P, _P, _P]),
     "cb200_download_hf": (C.c_int, [_P, _P]),
     "cb200_download_gamma": (C.c_int, [_P, _P, C.c_int]),
+    "cb200_download_nsc_rhs": (C.c_int, [_P, _P]),
+    "cb200_download_nsc_history": (C.c_int, [_P, _P, _P, C.c_int, C.POINTER(C.c_int)]),
+    "cb200_download_nsc_jacobian": (C.c_int, [_P, _P, _P]),
+    "cb200_nsc_schur_product": (C.c_int, [_P, C.c_int, _P, _P]),
+    "cb200_nsc_project": (C.c_int, [_P, C.c_int, _P]),
     "cb200_get_timer": (C.c_int, [_P, C.c_char_p, C.POINTER(C.c_double)]),
     "cb200_kernel_launches": (C.c_int64, [_P]),
     "cb200_device_array": (C.c_int, [_P, C.c_char_p, C.POINTER(_P), C.POINTER(C.c_int64)]),

@@ -150,6 +150,8 @@ int grow_after_overflow(System* S) {
         CB_TRY(alloc_contacts(S, c.need_contacts + c.need_contacts / 4));
     if (c.overflow & OVF_PAIRS)
         CB_TRY(alloc_pairs(S, c.need_pairs + c.need_pairs / 8));
+    if (c.overflow & OVF_NSC)
+        S->nsc_extra_slots = 2 * S->nsc_extra_slots + 32 + (int)c.need_nsc_slots / 4;
     CB_CUDA(cudaMemsetAsync(&S->d_cnt->overflow, 0, 4, S->stream));
     S->h_cnt->overflow = 0;
     return CB200_OK;
@@ -266,7 +268,10 @@ void cb200_destroy(cb200_system* sys) {
     REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_mask); REL(ent_c); REL(ent_m); REL(ent_off); REL(large_list); REL(pairs);
     REL(c_norm); REL(c_pta); REL(c_ptb); REL(c_depth); REL(c_erad); REL(c_bids); REL(c_shapes); REL(c_mats);
     REL(ct_force); REL(ct_torque); REL(b_deg); REL(b_cursor); REL(b_inc); REL(b_force); REL(heavy_list);
-    REL(heavy_part); REL(n_frame); REL(gamma); REL(n_r); REL(n_E); REL(n_work); REL(n_bodyvec); REL(n_scal);
+    REL(heavy_part); REL(n_frame); REL(n_aux); REL(gamma); REL(n_gamma_hat); REL(n_y); REL(n_gn); REL(n_g); REL(n_rfull);
+    REL(n_w); REL(n_w0); REL(n_mk); REL(n_part); REL(n_hist); REL(n_rows);
+    if (S->n_ctl)
+        cudaFree(S->n_ctl);
     REL(scan_tmp);
 #undef REL
     for (auto& kv : S->timers)
@@ -454,12 +459,13 @@ int cb200_set_materials_nsc(cb200_system* sys, int n, const float* t) {
         return set_error(CB200_ERR_UNSUPPORTED, "more than 1024 distinct materials");
     CB_CUDA(cudaSetDevice(S->device));
     std::vector<double> tab((size_t)n * n * NSC_MAT_STRIDE);
+    bool has_aux = false;
     for (int a = 0; a < n; a++)
         for (int b = 0; b < n; b++) {
             const float* m1 = t + 11 * a;
             const float* m2 = t + 11 * b;
             double* o = tab.data() + ((size_t)a * n + b) * NSC_MAT_STRIDE;
-            o[0] = std::min<float>(m1[0], m2[0]);
+            o[0] = std::min<float>(m1[1], m2[1]);  // sliding friction is the mu of the cone (…NSC.cpp:174)
             o[1] = std::min<float>(m1[2], m2[2]);
             o[2] = std::min<float>(m1[3], m2[3]);
             o[3] = std::min<float>(m1[5], m2[5]);
@@ -467,7 +473,10 @@ int cb200_set_materials_nsc(cb200_system* sys, int n, const float* t) {
             o[5] = (float)(m1[8] + m2[8]);
             o[6] = (float)(m1[9] + m2[9]);
             o[7] = (float)(m1[10] + m2[10]);
+            for (int k = 1; k < 8; k++)
+                has_aux |= o[k] != 0;
         }
+    S->nsc_has_aux = has_aux ? 1 : 0;
     CB_TRY(S->mat_nsc.reserve(tab.size()));
     CB_TRY(upload(S, S->mat_nsc, 0, tab.data(), tab.size()));
     CB_CUDA(cudaStreamSynchronize(S->stream));

@@ -86,7 +86,8 @@ struct __align__(16) ShapeMeta {
 };
 
 // overflow mask bits
-enum { OVF_BINS = 1, OVF_ENTRIES = 2, OVF_CONTACTS = 4, OVF_PAIRS = 8, OVF_LARGE = 16, OVF_HEAVY = 32, OVF_COMPLEX = 64 };
+enum { OVF_BINS = 1, OVF_ENTRIES = 2, OVF_CONTACTS = 4, OVF_PAIRS = 8, OVF_LARGE = 16, OVF_HEAVY = 32, OVF_COMPLEX = 64,
+       OVF_NSC = 128 };
 
 // Device-side counters and the broadphase grid (one pinned-host mirror, read back at the single sync of a call).
 struct DevCounters {
@@ -110,7 +111,7 @@ struct DevCounters {
     uint32_t steps_done;         // steps fully applied since the host last reset it
     uint32_t nsc_iters;
     uint32_t n_bodies, n_shapes; // extents of body / shape arrays (for device-count scans)
-    uint32_t pad;
+    uint32_t need_nsc_slots;     // APGD slot budget that would have sufficed (OVF_NSC)
     double nsc_residual, nsc_objective;
 };
 
@@ -199,11 +200,19 @@ struct System {
     DevBuf<uint32_t> heavy_list;
     DevBuf<double> heavy_part;
 
-    // ---- NSC ----
-    DevBuf<double> n_frame;   // per contact: U,V,W (9) + sbar_a (3) + sbar_b (3)
-    DevBuf<double> gamma, n_r, n_E, n_work;  // 3 N_c each (work: several vectors)
-    DevBuf<double> n_bodyvec;  // 6 nb scratch
-    DevBuf<double> n_scal;     // small scalar block
+    // ---- NSC (nsc.cu) ----
+    DevBuf<double> n_frame;   // 10 per contact: U (3), world arms s_A, s_B (3 + 3), friction
+    DevBuf<double> n_aux;     // 8 per contact: cohesion, E_n, E_t, mu_roll, mu_spin, E_spin, E_roll (only if nsc_has_aux)
+    DevBuf<double> gamma, n_gamma_hat, n_y, n_gn, n_g, n_rfull;  // rows per contact each, interleaved (n,u,v[,tn,tu,tv])
+    DevBuf<double> n_w, n_w0, n_mk;  // 6 nb: M^-1 D x (world angular part), M_invk world / body frame
+    DevBuf<double> n_part;    // per-CTA partial sums of the fixed-shape reductions
+    DevBuf<double> n_hist;    // (residual, objective) per APGD iteration of the last solve
+    DevBuf<double> n_rows;    // D_T rows on request (parity path)
+    void* n_ctl = nullptr;    // NscCtl
+    int nsc_rows_alloc = 0;   // rows per contact the vectors are sized for
+    int nsc_has_aux = 0;      // some material pair has cohesion / compliance / rolling / spinning friction
+    int nsc_extra_slots = 0;  // APGD slot budget beyond max_iter * 1.5 + 16 (grown on OVF_NSC)
+    int nsc_hist_cap = 0;
 
     // ---- scan scratch / counters ----
     DevBuf<uint64_t> scan_tmp;

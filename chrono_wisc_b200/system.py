@@ -241,10 +241,48 @@ class ChSystemMulticore:
         check(self._lib.cb200_download_hf(self._h, _ptr(hf)))
         return hf
 
+    # ---- NSC read-backs (host_data.gamma / R_full / D_T, measures.solver) ------------------------------------
+    def _nsc_rows(self):
+        return {MODE_NORMAL: 1, MODE_SLIDING: 3, MODE_SPINNING: 6}[int(self.settings.solver_mode)]
+
     def GetGamma(self):
-        n = 3 * self.GetCounts().num_rigid_contacts
-        g = np.empty(n)
+        n = self._nsc_rows() * self.GetCounts().num_rigid_contacts
+        g = np.zeros(n)
         check(self._lib.cb200_download_gamma(self._h, _ptr(g), int(n)))
+        return g
+
+    def GetRhs(self):
+        g = np.zeros(self._nsc_rows() * self.GetCounts().num_rigid_contacts)
+        check(self._lib.cb200_download_nsc_rhs(self._h, _ptr(g)))
+        return g
+
+    def GetJacobianRows(self):
+        n = self._nsc_rows() * self.GetCounts().num_rigid_contacts
+        rows, bids = np.zeros((n, 12)), np.zeros((n, 2), np.int32)
+        check(self._lib.cb200_download_nsc_jacobian(self._h, _ptr(rows), _ptr(bids)))
+        return rows, bids
+
+    def GetSolverHistory(self):
+        """(residual, objective) per APGD iteration of the last solve (measures.solver.maxd_hist)."""
+        n = C.c_int(0)
+        check(self._lib.cb200_download_nsc_history(self._h, None, None, 0, C.byref(n)))
+        r, o = np.zeros(n.value), np.zeros(n.value)
+        check(self._lib.cb200_download_nsc_history(self._h, _ptr(r), _ptr(o), n.value, C.byref(n)))
+        return r, o
+
+    def SchurProduct(self, x, local_mode=None):
+        """``ChSchurProduct::operator()`` on the system of the last NSC solve."""
+        x = _f64(x)
+        out = np.zeros_like(x)
+        lm = int(self.settings.solver_mode) if local_mode is None else int(local_mode)
+        check(self._lib.cb200_nsc_schur_product(self._h, lm, _ptr(x), _ptr(out)))
+        return out
+
+    def Project(self, gamma, local_mode=None):
+        """``ChProjectConstraints::operator()``."""
+        g = _f64(gamma).copy()
+        lm = int(self.settings.solver_mode) if local_mode is None else int(local_mode)
+        check(self._lib.cb200_nsc_project(self._h, lm, _ptr(g)))
         return g
 
     def GetTimer(self, name):

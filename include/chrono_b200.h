@@ -193,8 +193,29 @@ int cb200_download_contact_forces(cb200_system* sys, double* ct_force, double* c
 int cb200_download_body_contact_forces(cb200_system* sys, double* force, double* torque);
 /* host_data.hf (h * generalized force, 6 per body) as consumed by ComputeInvMassMatrix */
 int cb200_download_hf(cb200_system* sys, double* hf);
-/* NSC multipliers host_data.gamma in the reference layout [n | u v | ...] (MC/ChDataManager.h:307-317) */
+/* NSC multipliers host_data.gamma in the reference layout [n | u v | tn tu tv] (MC/ChDataManager.h:307-317);
+ * rows per contact = 1 / 3 / 6 for solver_mode NORMAL / SLIDING / SPINNING */
 int cb200_download_gamma(cb200_system* sys, double* gamma, int capacity);
+/* host_data.R_full = -b - D_T (v + M_inv hf) of the last NSC solve (MC/solver/ChIterativeSolverMulticoreNSC.cpp:80-82),
+ * reference layout */
+int cb200_download_nsc_rhs(cb200_system* sys, double* r_full);
+/* measures.solver.maxd_hist / objective per APGD iteration of the last solve (AtIterationEnd,
+ * MC/solver/ChSolverMulticoreAPGD.cpp:182); *count = iterations recorded */
+int cb200_download_nsc_history(cb200_system* sys, double* residual, double* objective, int capacity, int* count);
+/* Rows of host_data.D_T for the rigid contacts (ChConstraintRigidRigid::Build_D,
+ * MC/constraints/ChConstraintRigidRigid.cpp:377-452), reference row order: 12 values per row = the 6 entries at the
+ * columns of body A (bids.x) then the 6 of body B; body_ids (may be NULL) gets the two body ids per row.  The solver
+ * itself is matrix-free; this is the read-back the reference's Jacobian unit test (utest_MCORE_jacobians.cpp) needs. */
+int cb200_download_nsc_jacobian(cb200_system* sys, double* rows12, int32_t* body_ids);
+
+/* --- functor seams of the inner NSC solver (ChSolverMulticore::Solve arguments, MC/solver/ChSolverMulticore.h:107-113)
+ * on the system assembled by the last NSC solve; host vectors in the reference layout.  local_mode = the reference's
+ * settings.solver.local_solver_mode (0 NORMAL, 1 SLIDING, 2 SPINNING), not above solver_mode. */
+/* ChSchurProduct::operator()(x, out): out = D_T M_inv D x + E x (MC/solver/ChSchurProduct.cpp:58-173) */
+int cb200_nsc_schur_product(cb200_system* sys, int local_mode, const double* x, double* out);
+/* ChProjectConstraints::operator()(gamma) (MC/solver/ChSolverMulticore.cpp:25-30 ->
+ * ChConstraintRigidRigid::Project), in place */
+int cb200_nsc_project(cb200_system* sys, int local_mode, double* gamma);
 
 /* Timers with the reference's names (MC/ChTimerMulticore.h): seconds of GPU time measured with CUDA
  * events over the last cb200_do_steps call, averaged per step.  Unknown name -> CB200_ERR_ARG. */

@@ -80,8 +80,10 @@ double now() {
 
 }  // namespace
 
+struct orc_nsc;
 struct orc_system {
     cb200_settings st;
+    orc_nsc* nsc = nullptr;  // NSC solver state (oracle_nsc.inc)
     int nb = 0, ns = 0, nm = 0;
     std::vector<double> mass, inertia;
     std::vector<char> active, collide;
@@ -707,6 +709,8 @@ void advance(orc_system& S) {
 
 }  // namespace
 
+#include "oracle_nsc.inc"
+
 extern "C" {
 
 orc_system* orc_create(void) {
@@ -714,7 +718,10 @@ orc_system* orc_create(void) {
     memset(&S->st, 0, sizeof(S->st));
     return S;
 }
-void orc_destroy(orc_system* S) { delete S; }
+void orc_destroy(orc_system* S) {
+    delete S->nsc;
+    delete S;
+}
 void orc_set_threads(int n) { omp_set_num_threads(n > 0 ? n : 1); }
 int orc_max_threads(void) { return omp_get_max_threads(); }
 void orc_set_settings(orc_system* S, const cb200_settings* s) { S->st = *s; }

@@ -222,8 +222,11 @@ class Oracle:
         for name in ("orc_destroy", "orc_set_threads", "orc_set_settings", "orc_set_bodies", "orc_set_shapes",
                      "orc_set_materials_smc", "orc_set_state", "orc_get_state", "orc_collide", "orc_smc_step",
                      "orc_get_counts", "orc_get_grid", "orc_get_aabb", "orc_get_pairs", "orc_get_contacts",
-                     "orc_get_contact_forces", "orc_get_body_forces", "orc_get_hf", "orc_get_timers"):
+                     "orc_get_contact_forces", "orc_get_body_forces", "orc_get_hf", "orc_get_timers",
+                     "orc_set_materials_nsc", "orc_nsc_solve", "orc_nsc_step", "orc_nsc_info", "orc_nsc_get_vectors",
+                     "orc_nsc_get_rows", "orc_nsc_schur", "orc_nsc_project"):
             getattr(L, name).restype = None
+        L.orc_nsc_hist.restype = C.c_int
         self.L = L
         self.h = P(L.orc_create())
         self.nb = self.ns = 0
@@ -270,6 +273,8 @@ class Oracle:
         m = np.ascontiguousarray(scene["materials"], dtype=np.float32)
         if m.shape[-1] == 14:
             self.L.orc_set_materials_smc(self.h, C.c_int(m.shape[0]), _p(m))
+        else:
+            self.L.orc_set_materials_nsc(self.h, C.c_int(m.shape[0]), _p(m))
         self.set_state(scene["pos"], scene["rot"], scene["vel"])
 
     def set_state(self, pos, rot, vel):
@@ -284,7 +289,55 @@ class Oracle:
         self.L.orc_collide(self.h)
 
     def step(self, n=1):
-        self.L.orc_smc_step(self.h, C.c_int(int(n)))
+        if self.settings.system_type == 1:
+            self.L.orc_smc_step(self.h, C.c_int(int(n)))
+        else:
+            self.L.orc_nsc_step(self.h, C.c_int(int(n)))
+
+    # ---- NSC (oracle_nsc.inc) ----
+    def nsc_rows(self):
+        return {0: 1, 1: 3, 2: 6}[int(self.settings.solver_mode)]
+
+    def nsc_solve(self):
+        """Forces + NSC solve on the current contact list (call collide() first); updates the velocities."""
+        self.L.orc_nsc_solve(self.h)
+
+    def nsc_info(self):
+        i = np.zeros(4)
+        self.L.orc_nsc_info(self.h, _p(i))
+        return dict(iterations=int(i[0]), residual=i[1], objective=i[2], L=i[3])
+
+    def nsc_hist(self):
+        n = self.L.orc_nsc_hist(self.h, None, None, C.c_int(0))
+        r, o = np.zeros(n), np.zeros(n)
+        self.L.orc_nsc_hist(self.h, _p(r), _p(o), C.c_int(n))
+        return r, o
+
+    def nsc_vectors(self):
+        n = self.nsc_rows() * self.counts()["N_c"]
+        out = dict(gamma=np.zeros(n), R=np.zeros(n), b=np.zeros(n), E=np.zeros(n))
+        self.L.orc_nsc_get_vectors(self.h, _p(out["gamma"]), _p(out["R"]), _p(out["b"]), _p(out["E"]))
+        return out
+
+    def nsc_jacobian_rows(self):
+        """D_T rows in the reference's row order: 12 values (block of the lower body id first) + the two body ids."""
+        n = self.nsc_rows() * self.counts()["N_c"]
+        v, b = np.zeros((n, 12)), np.zeros((n, 2), np.int32)
+        self.L.orc_nsc_get_rows(self.h, _p(v), _p(b))
+        return v, b
+
+    def nsc_schur(self, x, local_mode=None):
+        x = _f64(x)
+        out = np.zeros_like(x)
+        lm = int(self.settings.solver_mode) if local_mode is None else int(local_mode)
+        self.L.orc_nsc_schur(self.h, C.c_int(lm), _p(x), _p(out))
+        return out
+
+    def nsc_project(self, gamma, local_mode=None):
+        g = _f64(gamma).copy()
+        lm = int(self.settings.solver_mode) if local_mode is None else int(local_mode)
+        self.L.orc_nsc_project(self.h, C.c_int(lm), _p(g))
+        return g
 
     def counts(self):
         c = np.zeros(8, dtype=np.uint32)
