@@ -828,7 +828,9 @@ int cb200_download_body_contact_forces(cb200_system* sys, double* force, double*
     if (nb == 0)
         return CB200_OK;
     if (S->b_force.cap < 6 * nb)
-        return set_error(CB200_ERR_STATE, "no SMC solve has run yet");
+        return set_error(CB200_ERR_STATE, "no solve has run yet");
+    if (S->set.system_type == 0)
+        CB_TRY(nsc_contact_forces_inactive(S));
     std::vector<double> h(6 * nb);
     CB_TRY(download(S, S->b_force.p, h.data(), 6 * nb));
     CB_CUDA(cudaStreamSynchronize(S->stream));

@@ -113,6 +113,8 @@ struct DevCounters {
     uint32_t n_bodies, n_shapes; // extents of body / shape arrays (for device-count scans)
     uint32_t need_nsc_slots;     // APGD slot budget that would have sufficed (OVF_NSC)
     double nsc_residual, nsc_objective;
+    uint32_t nsc_hist_count;     // iterations recorded in the residual history (includes the one that broke out)
+    uint32_t pad2;
 };
 
 struct Timer {
@@ -213,6 +215,7 @@ struct System {
     int nsc_has_aux = 0;      // some material pair has cohesion / compliance / rolling / spinning friction
     int nsc_extra_slots = 0;  // APGD slot budget beyond max_iter * 1.5 + 16 (grown on OVF_NSC)
     int nsc_hist_cap = 0;
+    bool nsc_fc_current = false;  // b_force also holds the contact forces on inactive bodies (Fc_current)
 
     // ---- scan scratch / counters ----
     DevBuf<uint64_t> scan_tmp;
@@ -240,6 +243,7 @@ int enqueue_broadphase(System* S, bool want_pairs, bool want_contacts);  // broa
 int enqueue_pairs_only(System* S, bool want_pairs, bool want_contacts);  // broadphase.cu: pair kernels on existing bins
 int enqueue_smc(System* S);                                              // smc.cu
 int enqueue_nsc(System* S);                                              // nsc.cu
+int nsc_contact_forces_inactive(System* S);                              // nsc.cu: on-demand part of CalculateContactForces
 
 // exclusive scans (scan.cu) over a device-side element count (*n_dev <= n_cap). n+1 outputs: out[n] = total.
 // In-place allowed.

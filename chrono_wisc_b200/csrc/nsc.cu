@@ -39,6 +39,7 @@ enum { NSC_FRAME = 10, NSC_PART = 8, NSC_THREADS = 256 };
 struct NscCtl {
     double L, t, theta, theta_new, beta, obj2, residual, objective, g_diff, tol_speed, norm_temp, dot_g_temp;
     int32_t iter, max_iter, act, done, redo, accepted, improved, restart, ref_variant, slots, total_iter, hist_cap;
+    int32_t ret_iter, pad;  // sum of the values Solve() returned over the phases (measures.solver.total_iteration)
 };
 
 struct NscFrame {
@@ -594,6 +595,7 @@ __global__ void k_nsc_phase_begin(NscCtl* __restrict__ ctl, int act, int max_ite
     ctl->hist_cap = hist_cap;
     if (first_phase) {
         ctl->total_iter = 0;
+        ctl->ret_iter = 0;
         ctl->slots = 0;
     }
 }
@@ -806,6 +808,7 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_scalar(NscCtl* __restrict__
     if (ctl->residual < ctl->tol_speed) {
         ctl->done = 1;  // break: the iteration counter is not advanced (:189-191)
         ctl->restart = 0;
+        ctl->ret_iter += ctl->iter;
         return;
     }
     ctl->restart = se[4] > 0 ? 1 : 0;
@@ -817,8 +820,10 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_scalar(NscCtl* __restrict__
     ctl->theta = theta_new;
     ctl->theta_new = theta_new;
     ctl->iter++;
-    if (ctl->iter >= ctl->max_iter)
+    if (ctl->iter >= ctl->max_iter) {
         ctl->done = 1;
+        ctl->ret_iter += ctl->iter;
+    }
 }
 
 // slot kernel F: commit an accepted iteration: gamma_hat (:175), y (:159,195), gamma (:203)
@@ -869,7 +874,8 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_phase_end(const NscCtl* __r
         return;
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
-        cnt->nsc_iters = (uint32_t)ctl->total_iter;
+        cnt->nsc_iters = (uint32_t)ctl->ret_iter;
+        cnt->nsc_hist_count = (uint32_t)ctl->total_iter;
         cnt->nsc_residual = ctl->residual;
         cnt->nsc_objective = ctl->objective;
     }
@@ -938,6 +944,61 @@ __global__ void k_nsc_set_act(NscCtl* ctl, int act) {
     ctl->act = act;
     ctl->done = 0;
     ctl->redo = 0;
+}
+
+// CalculateContactForces for bodies without rows in M_inv (inactive: container walls): their share of D gamma / h is
+// not needed by the solve, so it is accumulated only when somebody asks (the reference's Fc_current protocol,
+// MC/physics/ChSystemMulticoreNSC.cpp:92-109).  FP64 atomics: reporting path only.
+template <int ROWS>
+__global__ void __launch_bounds__(256) k_nsc_fc_inactive(const int32_t* __restrict__ bids,
+                                                         const uint8_t* __restrict__ bflags,
+                                                         const double* __restrict__ frame,
+                                                         const double* __restrict__ gamma, double* __restrict__ acc,
+                                                         const DevCounters* __restrict__ cnt) {
+    const uint32_t nc = cnt->n_contacts;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nc; i += gridDim.x * blockDim.x) {
+        const uint32_t bA = (uint32_t)bids[2 * i], bB = (uint32_t)bids[2 * i + 1];
+        const bool inA = !(bflags[bA] & 1u), inB = !(bflags[bB] & 1u);
+        if (!inA && !inB)
+            continue;
+        const NscFrame F = load_frame(frame, i);
+        double g[ROWS];
+        load_vec<ROWS>(gamma, i, g);
+        d3 f = F.U * g[0], tau = mk3(0);
+        if (ROWS >= 3) {
+            d3 V, W;
+            orthogonalize(F.U, V, W);
+            f = f + V * g[1] + W * g[2];
+            if (ROWS == 6)
+                tau = F.U * g[3] + V * g[4] + W * g[5];
+        }
+        if (inA) {
+            const d3 t = cross3(f, F.sA) - tau;
+            double* o = acc + 6 * (size_t)bA;
+            atomicAdd(o, -f.x), atomicAdd(o + 1, -f.y), atomicAdd(o + 2, -f.z);
+            atomicAdd(o + 3, t.x), atomicAdd(o + 4, t.y), atomicAdd(o + 5, t.z);
+        }
+        if (inB) {
+            const d3 t = tau - cross3(f, F.sB);
+            double* o = acc + 6 * (size_t)bB;
+            atomicAdd(o, f.x), atomicAdd(o + 1, f.y), atomicAdd(o + 2, f.z);
+            atomicAdd(o + 3, t.x), atomicAdd(o + 4, t.y), atomicAdd(o + 5, t.z);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) k_nsc_fc_finish(uint32_t nb, const uint8_t* __restrict__ bflags,
+                                                       const double* __restrict__ rot, const double* __restrict__ acc,
+                                                       double inv_h, double* __restrict__ b_force) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nb || (bflags[b] & 1u))
+        return;
+    const double* a = acc + 6 * (size_t)b;
+    const double4 qq = reinterpret_cast<const double4*>(rot)[b];
+    const d3 tl = rotate_t(mk3(a[3], a[4], a[5]), mkq(qq.x, qq.y, qq.z, qq.w));
+    double* o = b_force + 6 * (size_t)b;
+    o[0] = a[0] * inv_h, o[1] = a[1] * inv_h, o[2] = a[2] * inv_h;
+    o[3] = tl.x * inv_h, o[4] = tl.y * inv_h, o[5] = tl.z * inv_h;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -1072,15 +1133,37 @@ static int nsc_run(System* S) {
         CB_TRY((nsc_phase<ROWS>(S, acts[ph], iters[ph], first)));
         first = false;
     }
-    if (first)  // no phase ran: counters of an empty solve
+    if (first) {  // no phase ran: counters of an empty solve
         k_nsc_phase_begin<<<1, 1, 0, S->stream>>>((NscCtl*)S->n_ctl, ROWS, 0, ROWS, 0, 0.0, 1, S->nsc_hist_cap,
                                                   S->d_cnt);
+        k_nsc_phase_end<ROWS><<<1, NSC_THREADS, 0, S->stream>>>((NscCtl*)S->n_ctl, S->n_gamma_hat.p, S->gamma.p, 0,
+                                                                S->d_cnt);
+        S->launches += 2;
+    }
     // ComputeImpulses + CalculateContactForces
     k_nsc_scatter<ROWS, 1><<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(
         S->nb, (NscCtl*)S->n_ctl, 0, S->bflags.p, S->mass.p, S->inv_inertia.p, S->rot.p, S->b_deg.p, S->b_inc.p,
         S->n_frame.p, S->gamma.p, nullptr, S->n_mk.p, S->vel.p, S->b_force.p, 1 / st.step_size, S->d_cnt);
     S->launches++;
     CB_CUDA(cudaGetLastError());
+    return CB200_OK;
+}
+
+int nsc_contact_forces_inactive(System* S) {
+    if (S->nsc_fc_current || S->nb == 0 || !S->n_ctl)
+        return CB200_OK;
+    CB_CUDA(cudaMemsetAsync(S->n_w.p, 0, 6 * (size_t)S->nb * 8, S->stream));
+    const int G = nsc_grid(S);
+    switch (S->nsc_rows_alloc) {
+        case 1: k_nsc_fc_inactive<1><<<G, 256, 0, S->stream>>>(S->c_bids.p, S->bflags.p, S->n_frame.p, S->gamma.p, S->n_w.p, S->d_cnt); break;
+        case 3: k_nsc_fc_inactive<3><<<G, 256, 0, S->stream>>>(S->c_bids.p, S->bflags.p, S->n_frame.p, S->gamma.p, S->n_w.p, S->d_cnt); break;
+        default: k_nsc_fc_inactive<6><<<G, 256, 0, S->stream>>>(S->c_bids.p, S->bflags.p, S->n_frame.p, S->gamma.p, S->n_w.p, S->d_cnt); break;
+    }
+    k_nsc_fc_finish<<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(S->nb, S->bflags.p, S->rot.p, S->n_w.p,
+                                                                  1 / S->set.step_size, S->b_force.p);
+    S->launches += 2;
+    CB_CUDA(cudaGetLastError());
+    S->nsc_fc_current = true;
     return CB200_OK;
 }
 
@@ -1095,6 +1178,7 @@ int enqueue_nsc(System* S) {
     if (st.solver_mode < 0 || st.solver_mode > 2)
         return set_error(CB200_ERR_ARG, "solver_mode must be NORMAL, SLIDING or SPINNING");
     CB_TRY(nsc_reserve(S));
+    S->nsc_fc_current = false;
     switch (nsc_rows_of(S)) {
         case 1: return nsc_run<1>(S);
         case 3: return nsc_run<3>(S);
@@ -1177,7 +1261,7 @@ extern "C" int cb200_download_nsc_history(cb200_system* sys, double* residual, d
         return set_error(CB200_ERR_ARG, "null argument");
     CB_CUDA(cudaSetDevice(S->device));
     CB_TRY(fetch_counters(S));
-    const int n = std::min<int>((int)S->h_cnt->nsc_iters, S->nsc_hist_cap);
+    const int n = std::min<int>((int)S->h_cnt->nsc_hist_count, S->nsc_hist_cap);
     *count = n;
     if (n == 0 || capacity <= 0)
         return CB200_OK;
