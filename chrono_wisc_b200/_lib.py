@@ -114,8 +114,17 @@ _SIGNATURES = {
     "cb200_get_timer": (C.c_int, [_P, C.c_char_p, C.POINTER(C.c_double)]),
     "cb200_kernel_launches": (C.c_int64, [_P]),
     "cb200_device_array": (C.c_int, [_P, C.c_char_p, C.POINTER(_P), C.POINTER(C.c_int64)]),
-    "cb200_pack_slab_dev": (C.c_int, [_P, C.c_int, C.c_double, C.c_double, _P, C.c_int64, C.POINTER(C.c_int64)]),
-    "cb200_unpack_slab_dev": (C.c_int, [_P, _P, C.c_int64]),
+    "cb200_set_stream": (C.c_int, [_P, _P, C.c_int]),
+    "cb200_enqueue_steps": (C.c_int, [_P, C.c_int]),
+    "cb200_check": (C.c_int, [_P]),
+    "cb200_reset_timers": (C.c_int, [_P]),
+    "cb200_upload_body_ids": (C.c_int, [_P, C.c_int, C.c_int, _P]),
+    "cb200_download_body_ids": (C.c_int, [_P, C.c_int, C.c_int, _P, _P]),
+    "cb200_slab_configure": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int,
+                                       C.c_int, C.c_int, C.c_int]),
+    "cb200_slab_buffer_doubles": (C.c_int64, [_P]),
+    "cb200_slab_pack_dev": (C.c_int, [_P, _P, _P]),
+    "cb200_slab_unpack_dev": (C.c_int, [_P, _P, _P]),
 }
 
 _lib = None

@@ -247,6 +247,7 @@ int cb200_create(int device, cb200_system** out) {
     CB_CUDA(cudaDeviceGetAttribute(&S->num_sms, cudaDevAttrMultiProcessorCount, device));
     cb200_default_settings(&S->set);
     CB_CUDA(cudaStreamCreateWithFlags(&S->stream, cudaStreamNonBlocking));
+    S->own_stream = S->stream;
     CB_CUDA(cudaMalloc(&S->d_cnt, sizeof(DevCounters)));
     CB_CUDA(cudaMemset(S->d_cnt, 0, sizeof(DevCounters)));
     CB_CUDA(cudaMallocHost(&S->h_cnt, sizeof(DevCounters)));
@@ -281,7 +282,10 @@ void cb200_destroy(cb200_system* sys) {
         }
     cudaFree(S->d_cnt);
     cudaFreeHost(S->h_cnt);
-    cudaStreamDestroy(S->stream);
+    S->b_gid.release(); S->slab_flags.release(); S->slab_vacant.release();
+    if (S->slab_cnt)
+        cudaFree(S->slab_cnt);
+    cudaStreamDestroy(S->own_stream);
     delete S;
 }
 
@@ -632,6 +636,59 @@ int cb200_do_steps(cb200_system* sys, int nsteps) {
                              std::to_string(S->h_cnt->unsupported) +
                                  " candidate pairs have a shape combination this backend cannot test yet");
     }
+    return CB200_OK;
+}
+
+// Asynchronous stepping for callers that interleave their own work on the stream (slab exchange): no host
+// synchronisation and no capacity recovery here; cb200_check() reports a capacity overflow as an error.
+int cb200_enqueue_steps(cb200_system* sys, int nsteps) {
+    System* S = SYS(sys);
+    if (!S || nsteps < 0)
+        return set_error(CB200_ERR_ARG, "bad argument to cb200_enqueue_steps");
+    CB_CUDA(cudaSetDevice(S->device));
+    if (S->nb == 0)
+        return CB200_OK;
+    CB_TRY(ensure_capacity(S));
+    S->timed_steps += nsteps;
+    for (int s = 0; s < nsteps; s++)
+        CB_TRY(enqueue_one_step(S));
+    return CB200_OK;
+}
+
+int cb200_check(cb200_system* sys) {
+    System* S = SYS(sys);
+    if (!S)
+        return set_error(CB200_ERR_ARG, "null system");
+    CB_CUDA(cudaSetDevice(S->device));
+    CB_TRY(flush_timers(S));
+    CB_TRY(fetch_counters(S));
+    if (S->h_cnt->overflow)
+        return set_error(CB200_ERR_STATE, "a device capacity was exceeded during asynchronous stepping (overflow mask " +
+                                              std::to_string(S->h_cnt->overflow) + "); steps after it did not run");
+    if (S->h_cnt->unsupported)
+        return set_error(CB200_ERR_UNSUPPORTED, std::to_string(S->h_cnt->unsupported) +
+                                                    " candidate pairs have a shape combination this backend cannot test yet");
+    return CB200_OK;
+}
+
+int cb200_reset_timers(cb200_system* sys) {
+    System* S = SYS(sys);
+    if (!S)
+        return set_error(CB200_ERR_ARG, "null system");
+    CB_TRY(flush_timers(S));
+    for (auto& kv : S->timers)
+        kv.second.total_ms = 0;
+    S->timed_steps = 0;
+    return CB200_OK;
+}
+
+int cb200_set_stream(cb200_system* sys, void* cuda_stream, int use_own) {
+    System* S = SYS(sys);
+    if (!S)
+        return set_error(CB200_ERR_ARG, "null system");
+    CB_CUDA(cudaSetDevice(S->device));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    S->stream = use_own ? S->own_stream : (cudaStream_t)cuda_stream;  // 0 is a valid handle: the legacy default stream
     return CB200_OK;
 }
 

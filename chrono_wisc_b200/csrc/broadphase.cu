@@ -57,8 +57,12 @@ __global__ void __launch_bounds__(256) k_build_meta(uint32_t ns, const int32_t* 
         m.pad = 0;
         const uint32_t type = (uint32_t)s_type[i] & 0xff;
         m.info = type << 8 | ((uint32_t)s_mat[i] & 0xffff) << 16;
-        if (m.body != UINT_MAX)
-            m.info |= bflags[m.body] & 3u;
+        if (m.body != UINT_MAX) {
+            const uint32_t fl = bflags[m.body];
+            m.info |= fl & 3u;
+            if (fl & 4u)
+                m.body = UINT_MAX;  // vacant slot of a slab system: treated like a removed shape
+        }
         // bit 2: sphere centred on its body (ObA == 0): world centre == body position, no rotation needed
         if (type == CB200_SPHERE && s_lpos[3 * i] == 0 && s_lpos[3 * i + 1] == 0 && s_lpos[3 * i + 2] == 0)
             m.info |= 4u;

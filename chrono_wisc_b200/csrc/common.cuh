@@ -87,7 +87,7 @@ struct __align__(16) ShapeMeta {
 
 // overflow mask bits
 enum { OVF_BINS = 1, OVF_ENTRIES = 2, OVF_CONTACTS = 4, OVF_PAIRS = 8, OVF_LARGE = 16, OVF_HEAVY = 32, OVF_COMPLEX = 64,
-       OVF_NSC = 128 };
+       OVF_NSC = 128, OVF_SLAB = 256 };
 
 // Device-side counters and the broadphase grid (one pinned-host mirror, read back at the single sync of a call).
 struct DevCounters {
@@ -145,7 +145,7 @@ struct System {
     DevBuf<double> mass;     // nb
     DevBuf<double> inertia;  // 3 nb (body-frame diagonal)
     DevBuf<double> inv_inertia;  // 3 nb
-    DevBuf<uint8_t> bflags;  // bit0 active, bit1 collide
+    DevBuf<uint8_t> bflags;  // bit0 active, bit1 collide, bit2 vacant slot (slab decomposition: no body lives here)
     DevBuf<uint8_t> heavy;   // body owns a large shape this step
 
     // ---- shapes (shape_container, CMC/ChCollisionData.h:35-59) ----
@@ -216,6 +216,17 @@ struct System {
     int nsc_extra_slots = 0;  // APGD slot budget beyond max_iter * 1.5 + 16 (grown on OVF_NSC)
     int nsc_hist_cap = 0;
     bool nsc_fc_current = false;  // b_force also holds the contact forces on inactive bodies (Fc_current)
+
+    // ---- slab decomposition (slab.cu) ----
+    bool slab_on = false;
+    int slab_axis = 0, slab_has_left = 0, slab_has_right = 0;
+    double slab_lo = 0, slab_hi = 0, slab_w = 0;
+    uint32_t slab_nb_static = 0, slab_ns_static = 0, slab_owned_cap = 0, slab_ghost_cap = 0;
+    DevBuf<int64_t> b_gid;          // global body id per slot
+    DevBuf<uint64_t> slab_flags;    // owned_cap + 2: packed (to-left | to-right << 21 | vacant << 42), then offsets
+    DevBuf<uint32_t> slab_vacant;   // vacant owned slots in slot order
+    uint32_t* slab_cnt = nullptr;   // device: [0] owned_cap (scan extent) [1] n_vacant [2] arrivals of last unpack
+    cudaStream_t own_stream = nullptr;  // the stream cb200_create made (stream may be the caller's, cb200_set_stream)
 
     // ---- scan scratch / counters ----
     DevBuf<uint64_t> scan_tmp;

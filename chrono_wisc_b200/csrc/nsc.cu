@@ -1371,10 +1371,3 @@ extern "C" int cb200_nsc_project(cb200_system* sys, int local_mode, double* gamm
     CB_CUDA(cudaGetLastError());
     return download_rows_vector(S, S->n_gn.p, gamma, -1);
 }
-
-extern "C" int cb200_pack_slab_dev(cb200_system*, int, double, double, void*, int64_t, int64_t*) {
-    return cb200::set_error(CB200_ERR_UNSUPPORTED, "slab exchange not built yet");
-}
-extern "C" int cb200_unpack_slab_dev(cb200_system*, const void*, int64_t) {
-    return cb200::set_error(CB200_ERR_UNSUPPORTED, "slab exchange not built yet");
-}

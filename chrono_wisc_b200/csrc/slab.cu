@@ -1,0 +1,387 @@
+// slab.cu -- spatial slab decomposition of one system across GPUs: device-side pack / unpack of ghost-layer bodies.
+//
+// The reference is single-node OpenMP; BASELINE.json's north_star asks for 1-D slabs with a ghost-layer exchange
+// each step.  One process per GPU owns the bodies whose centre lies in [lo, hi) along `axis`.
+//
+// Slot model (no array ever changes size, so a step stays free of host synchronisation):
+//   bodies [0, nb_static)                       static geometry replicated on every rank (container walls)
+//   bodies [nb_static, +owned_cap)              owned region: bodies this rank integrates; vacant slots in between
+//   then ghost_cap slots for the left neighbour's ghost layer, ghost_cap for the right neighbour's
+// Every dynamic slot b owns exactly one shape, ns_static + (b - nb_static).  A vacant slot has bflags bit 2 set and
+// is invisible to collision (k_build_meta turns its shape into a removed one).  Ghost bodies are inactive
+// (not integrated, M_inv = 0) but collide: a contact between an owned body and a ghost is evaluated on both ranks
+// from the same state and applied to the owned body only, so no force is exchanged.
+//
+// Per step, after integration:
+//   pack    one pass over the owned region + one packed 64-bit scan: bodies within `width` of a cut plane (or past
+//           it) are written, in slot order, to that neighbour's send buffer; bodies past the plane are handed over
+//           (the neighbour adopts them; here the slot lingers one step as a ghost, then becomes vacant); the list
+//           of vacant owned slots is rebuilt in slot order.
+//   (the caller moves the two buffers: NCCL send/recv between neighbours, chrono_wisc_b200/slab.py)
+//   unpack  the ghost regions are rebuilt from scratch from the received records; a record whose centre lies in
+//           [lo, hi) is an arrival and takes the next vacant owned slot (in record order: deterministic).
+// Record = 33 doubles: gid, pos 3, rot 4, vel 6, mass, inertia 3, inv_inertia 3, shape dims 4, shape local pos 3,
+// local rot 4, packed (type | material << 8 | family << 32).  Buffer = [count, 0, records...].
+#include "common.cuh"
+#include <float.h>
+#include <limits.h>
+#include <vector>
+
+namespace cb200 {
+
+enum { SLAB_REC = 33, SLAB_HDR = 2 };
+
+struct SlabArrays {
+    double *pos, *rot, *vel, *mass, *inertia, *inv_inertia;
+    int64_t* gid;
+    uint8_t* bflags;
+    double *s_dims, *s_lpos, *s_lrot;
+    int32_t *s_type, *s_mat;
+    uint32_t* s_fam;
+    uint32_t nb_static, ns_static;
+};
+
+__device__ __forceinline__ void slab_write_record(const SlabArrays& A, uint32_t b, double* __restrict__ r) {
+    const uint32_t s = A.ns_static + (b - A.nb_static);
+    r[0] = (double)A.gid[b];
+    for (int k = 0; k < 3; k++)
+        r[1 + k] = A.pos[3 * (size_t)b + k];
+    for (int k = 0; k < 4; k++)
+        r[4 + k] = A.rot[4 * (size_t)b + k];
+    for (int k = 0; k < 6; k++)
+        r[8 + k] = A.vel[6 * (size_t)b + k];
+    r[14] = A.mass[b];
+    for (int k = 0; k < 3; k++) {
+        r[15 + k] = A.inertia[3 * (size_t)b + k];
+        r[18 + k] = A.inv_inertia[3 * (size_t)b + k];
+        r[25 + k] = A.s_lpos[3 * (size_t)s + k];
+    }
+    for (int k = 0; k < 4; k++) {
+        r[21 + k] = A.s_dims[4 * (size_t)s + k];
+        r[28 + k] = A.s_lrot[4 * (size_t)s + k];
+    }
+    const unsigned long long bits = ((unsigned long long)A.s_type[s] & 0xffull) |
+                                    (((unsigned long long)A.s_mat[s] & 0xffffull) << 8) |
+                                    ((unsigned long long)A.s_fam[s] << 32);
+    r[32] = __longlong_as_double((long long)bits);
+}
+
+__device__ __forceinline__ void slab_read_record(const SlabArrays& A, uint32_t b, const double* __restrict__ r,
+                                                 uint8_t flags) {
+    const uint32_t s = A.ns_static + (b - A.nb_static);
+    A.gid[b] = (int64_t)r[0];
+    for (int k = 0; k < 3; k++)
+        A.pos[3 * (size_t)b + k] = r[1 + k];
+    for (int k = 0; k < 4; k++)
+        A.rot[4 * (size_t)b + k] = r[4 + k];
+    for (int k = 0; k < 6; k++)
+        A.vel[6 * (size_t)b + k] = r[8 + k];
+    A.mass[b] = r[14];
+    for (int k = 0; k < 3; k++) {
+        A.inertia[3 * (size_t)b + k] = r[15 + k];
+        A.inv_inertia[3 * (size_t)b + k] = r[18 + k];
+        A.s_lpos[3 * (size_t)s + k] = r[25 + k];
+    }
+    for (int k = 0; k < 4; k++) {
+        A.s_dims[4 * (size_t)s + k] = r[21 + k];
+        A.s_lrot[4 * (size_t)s + k] = r[28 + k];
+    }
+    const unsigned long long bits = (unsigned long long)__double_as_longlong(r[32]);
+    A.s_type[s] = (int32_t)(bits & 0xff);
+    A.s_mat[s] = (int32_t)((bits >> 8) & 0xffff);
+    A.s_fam[s] = (uint32_t)(bits >> 32);
+    A.bflags[b] = flags;
+}
+
+struct SlabGeom {
+    int axis, has_left, has_right;
+    double lo, hi, w;
+    uint32_t owned_cap, ghost_cap;
+};
+
+// flags of one owned slot: bit 0 send left, bit 21 send right, bit 42 vacant after this step's departures
+__global__ void __launch_bounds__(256) k_slab_flags(SlabGeom G, SlabArrays A, uint64_t* __restrict__ flags,
+                                                    const DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < G.owned_cap; s += gridDim.x * blockDim.x) {
+        const uint32_t b = A.nb_static + s;
+        uint64_t f = 0;
+        if (A.bflags[b] & (4u | 8u)) {
+            f = 1ull << 42;  // vacant, or left during the previous exchange (kept one step as a ghost, see k_slab_pack)
+        } else {
+            const double p = A.pos[3 * (size_t)b + G.axis];
+            if (G.has_left && p < G.lo + G.w)
+                f |= 1ull;
+            if (G.has_right && p >= G.hi - G.w)
+                f |= 1ull << 21;
+        }
+        flags[s] = f;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_slab_pack(SlabGeom G, SlabArrays A, const uint64_t* __restrict__ offs,
+                                                   double* __restrict__ send_left, double* __restrict__ send_right,
+                                                   uint32_t* __restrict__ vacant, uint32_t* __restrict__ scnt,
+                                                   DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    const uint64_t tot = offs[G.owned_cap];
+    const uint32_t nL = (uint32_t)(tot & 0x1fffff), nR = (uint32_t)((tot >> 21) & 0x1fffff), nV = (uint32_t)(tot >> 42);
+    if (nL > G.ghost_cap || nR > G.ghost_cap) {
+        if (blockIdx.x == 0 && threadIdx.x == 0)
+            atomicOr(&cnt->overflow, (uint32_t)OVF_SLAB);
+        return;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        if (send_left)
+            send_left[0] = (double)nL, send_left[1] = 0;
+        if (send_right)
+            send_right[0] = (double)nR, send_right[1] = 0;
+        scnt[1] = nV;
+    }
+    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < G.owned_cap; s += gridDim.x * blockDim.x) {
+        const uint32_t b = A.nb_static + s;
+        const uint64_t o = offs[s], f = offs[s + 1] - o;  // exclusive scan: the slot's own flags are the difference
+        if (f & 1ull)
+            slab_write_record(A, b, send_left + SLAB_HDR + (size_t)SLAB_REC * (uint32_t)(o & 0x1fffff));
+        if (f & (1ull << 21))
+            slab_write_record(A, b, send_right + SLAB_HDR + (size_t)SLAB_REC * (uint32_t)((o >> 21) & 0x1fffff));
+        if (f & (1ull << 42)) {
+            A.bflags[b] = 4;
+            vacant[(uint32_t)(o >> 42)] = b;
+        } else {
+            // A body past the plane now belongs to the neighbour (it is in the buffer just written).  Its slot stays
+            // one more step as a ghost -- the neighbour's own ghost layer will only list it from the next exchange
+            // on -- and is released by the next pack (bit 3).
+            const double p = A.pos[3 * (size_t)b + G.axis];
+            if ((G.has_left && p < G.lo) || (G.has_right && p >= G.hi))
+                A.bflags[b] = 2 | 8;
+        }
+    }
+}
+
+// One CTA: rebuild one ghost region from a received buffer; arrivals take vacant owned slots in record order.
+__global__ void __launch_bounds__(1024) k_slab_unpack(SlabGeom G, SlabArrays A, const double* __restrict__ recv,
+                                                      uint32_t ghost_base, const uint32_t* __restrict__ vacant,
+                                                      uint32_t* __restrict__ scnt, int first_side,
+                                                      DevCounters* __restrict__ cnt) {
+    __shared__ uint32_t warp_tot[32];
+    __shared__ uint32_t base;
+    if (cnt->overflow)
+        return;
+    const uint32_t n = recv ? (uint32_t)recv[0] : 0u;
+    const uint32_t n_vac = scnt[1];
+    if (threadIdx.x == 0)
+        base = first_side ? 0u : scnt[2];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (uint32_t j0 = 0; j0 < G.ghost_cap; j0 += blockDim.x) {
+        const uint32_t j = j0 + threadIdx.x;
+        bool arrival = false;
+        const double* r = nullptr;
+        if (j < n) {
+            r = recv + SLAB_HDR + (size_t)SLAB_REC * j;
+            const double p = r[1 + G.axis];
+            arrival = (!G.has_left || p >= G.lo) && (!G.has_right || p < G.hi);
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, arrival);
+        if (lane == 0)
+            warp_tot[wid] = (uint32_t)__popc(m);
+        __syncthreads();
+        uint32_t before = base;
+        for (int w = 0; w < wid; w++)
+            before += warp_tot[w];
+        const uint32_t rank = before + (uint32_t)__popc(m & ((1u << lane) - 1));
+        uint32_t chunk_total = 0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); w++)
+            chunk_total += warp_tot[w];
+        if (j < G.ghost_cap) {
+            const uint32_t gslot = ghost_base + j;
+            if (j < n && !arrival) {
+                slab_read_record(A, gslot, r, 2);  // ghost: collides, not integrated
+            } else {
+                A.bflags[gslot] = 4;
+                if (arrival) {
+                    if (rank < n_vac)
+                        slab_read_record(A, vacant[rank], r, 3);
+                    else
+                        atomicOr(&cnt->overflow, (uint32_t)OVF_SLAB);
+                }
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0)
+            base += chunk_total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0)
+        scnt[2] = base;
+}
+
+static SlabArrays slab_arrays(System* S) {
+    SlabArrays A;
+    A.pos = S->pos.p, A.rot = S->rot.p, A.vel = S->vel.p, A.mass = S->mass.p, A.inertia = S->inertia.p;
+    A.inv_inertia = S->inv_inertia.p, A.gid = S->b_gid.p, A.bflags = S->bflags.p;
+    A.s_dims = S->s_dims.p, A.s_lpos = S->s_lpos.p, A.s_lrot = S->s_lrot.p;
+    A.s_type = S->s_type.p, A.s_mat = S->s_mat.p, A.s_fam = S->s_fam.p;
+    A.nb_static = S->slab_nb_static, A.ns_static = S->slab_ns_static;
+    return A;
+}
+static SlabGeom slab_geom(const System* S) {
+    SlabGeom G;
+    G.axis = S->slab_axis, G.has_left = S->slab_has_left, G.has_right = S->slab_has_right;
+    G.lo = S->slab_lo, G.hi = S->slab_hi, G.w = S->slab_w;
+    G.owned_cap = S->slab_owned_cap, G.ghost_cap = S->slab_ghost_cap;
+    return G;
+}
+
+}  // namespace cb200
+
+using namespace cb200;
+static System* SYSL(cb200_system* s) { return reinterpret_cast<System*>(s); }
+
+extern "C" {
+
+// Global ids of bodies [first, first+n) (what ChBody::GetIdentifier / the body's index in the undecomposed system is).
+int cb200_upload_body_ids(cb200_system* sys, int first, int n, const int64_t* ids) {
+    System* S = SYSL(sys);
+    if (!S || first < 0 || n < 0 || (uint32_t)(first + n) > S->nb || !ids)
+        return set_error(CB200_ERR_ARG, "bad argument to cb200_upload_body_ids");
+    CB_CUDA(cudaSetDevice(S->device));
+    CB_TRY(S->b_gid.reserve(S->pos.cap / 3 + 1, true, S->stream));
+    CB_CUDA(cudaMemcpyAsync(S->b_gid.p + first, ids, (size_t)n * 8, cudaMemcpyHostToDevice, S->stream));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    return CB200_OK;
+}
+
+// ids (global id, -1 for bodies that never got one) and flags (bit0 active = owned, bit1 collide, bit2 vacant)
+int cb200_download_body_ids(cb200_system* sys, int first, int n, int64_t* ids, uint8_t* flags) {
+    System* S = SYSL(sys);
+    if (!S || first < 0 || n < 0 || (uint32_t)(first + n) > S->nb)
+        return set_error(CB200_ERR_ARG, "bad argument to cb200_download_body_ids");
+    CB_CUDA(cudaSetDevice(S->device));
+    if (ids) {
+        if (S->b_gid.cap < S->nb)
+            return set_error(CB200_ERR_STATE, "no body ids were uploaded");
+        CB_CUDA(cudaMemcpyAsync(ids, S->b_gid.p + first, (size_t)n * 8, cudaMemcpyDeviceToHost, S->stream));
+    }
+    if (flags)
+        CB_CUDA(cudaMemcpyAsync(flags, S->bflags.p + first, (size_t)n, cudaMemcpyDeviceToHost, S->stream));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    return CB200_OK;
+}
+
+// Turn the system into one slab of a decomposed system.  Bodies [nb_static, nb) added so far are this rank's
+// owned bodies, each with exactly one shape, in order (shape ns_static + k belongs to body nb_static + k).  The call
+// appends vacant slots up to owned_cap and the two ghost regions.  lo/hi: this rank's interval along axis (ignored
+// on a side without neighbour); width: ghost-layer width, >= 2 r_max + 2 envelope.
+int cb200_slab_configure(cb200_system* sys, int nb_static, int ns_static, int axis, double lo, double hi,
+                         double width, int has_left, int has_right, int owned_cap, int ghost_cap) {
+    System* S = SYSL(sys);
+    if (!S || nb_static < 0 || (uint32_t)nb_static > S->nb || axis < 0 || axis > 2 || !(width > 0) || ghost_cap <= 0)
+        return set_error(CB200_ERR_ARG, "bad argument to cb200_slab_configure");
+    if (S->slab_on)
+        return set_error(CB200_ERR_STATE, "the system is already configured as a slab");
+    if (ghost_cap >= (1 << 21) || owned_cap >= (1 << 22))
+        return set_error(CB200_ERR_UNSUPPORTED, "slab capacities above 2^21 ghost / 2^22 owned slots");
+    CB_CUDA(cudaSetDevice(S->device));
+    const uint32_t n_dyn = S->nb - (uint32_t)nb_static;
+    if ((uint32_t)owned_cap < n_dyn)
+        return set_error(CB200_ERR_ARG, "owned_cap is smaller than the number of dynamic bodies already added");
+    if (S->ns - (uint32_t)ns_static != n_dyn)
+        return set_error(CB200_ERR_ARG, "slab mode needs exactly one shape per dynamic body");
+    {
+        std::vector<uint32_t> sb(n_dyn);
+        CB_CUDA(cudaMemcpy(sb.data(), S->s_body.p + ns_static, (size_t)n_dyn * 4, cudaMemcpyDeviceToHost));
+        for (uint32_t k = 0; k < n_dyn; k++)
+            if (sb[k] != (uint32_t)nb_static + k)
+                return set_error(CB200_ERR_ARG, "slab mode needs shape ns_static + k to belong to body nb_static + k");
+    }
+    const int extra = owned_cap - (int)n_dyn + 2 * ghost_cap;
+    {
+        std::vector<double> mass(extra, 1.0), inr(3 * (size_t)extra, 1.0), lp(3 * (size_t)extra, 0.0),
+            lr(4 * (size_t)extra, 0.0), dims(4 * (size_t)extra, 0.0);
+        std::vector<char> zero(extra, 0);
+        std::vector<int32_t> type(extra, CB200_SPHERE), mat(extra, 0);
+        std::vector<uint32_t> body(extra);
+        std::vector<int16_t> fam(2 * (size_t)extra);
+        int first = 0;
+        CB_TRY(cb200_append_bodies(sys, extra, mass.data(), inr.data(), nullptr, zero.data(), zero.data(), &first));
+        for (int k = 0; k < extra; k++) {
+            body[k] = (uint32_t)(first + k);
+            lr[4 * (size_t)k] = 1.0;
+            fam[2 * k] = 1, fam[2 * k + 1] = 0x7fff;
+        }
+        CB_TRY(cb200_append_shapes(sys, extra, type.data(), body.data(), fam.data(), lp.data(), lr.data(), dims.data(),
+                                   mat.data()));
+        std::vector<uint8_t> vac(extra, 4);
+        CB_CUDA(cudaMemcpy(S->bflags.p + first, vac.data(), (size_t)extra, cudaMemcpyHostToDevice));
+    }
+    if (S->b_gid.cap < S->nb) {
+        const size_t old = S->b_gid.cap;
+        CB_TRY(S->b_gid.reserve(S->nb, true, S->stream));
+        if (old == 0)
+            CB_CUDA(cudaMemset(S->b_gid.p, 0xff, (size_t)S->nb * 8));
+    }
+    CB_TRY(S->slab_flags.reserve((size_t)owned_cap + 4));
+    CB_TRY(S->slab_vacant.reserve((size_t)owned_cap + 1));
+    CB_CUDA(cudaMalloc(&S->slab_cnt, 16));
+    const uint32_t init[4] = {(uint32_t)owned_cap, 0, 0, 0};
+    CB_CUDA(cudaMemcpy(S->slab_cnt, init, 16, cudaMemcpyHostToDevice));
+    S->slab_on = true;
+    S->slab_axis = axis, S->slab_lo = lo, S->slab_hi = hi, S->slab_w = width;
+    S->slab_has_left = has_left ? 1 : 0, S->slab_has_right = has_right ? 1 : 0;
+    S->slab_nb_static = (uint32_t)nb_static, S->slab_ns_static = (uint32_t)ns_static;
+    S->slab_owned_cap = (uint32_t)owned_cap, S->slab_ghost_cap = (uint32_t)ghost_cap;
+    S->meta_dirty = true;
+    return CB200_OK;
+}
+
+// doubles a send / receive buffer must hold
+int64_t cb200_slab_buffer_doubles(cb200_system* sys) {
+    System* S = SYSL(sys);
+    return S && S->slab_on ? (int64_t)SLAB_HDR + (int64_t)SLAB_REC * S->slab_ghost_cap : 0;
+}
+
+// Enqueue the pack pass on the system's stream.  Buffers are DEVICE pointers (NULL on a side without neighbour).
+int cb200_slab_pack_dev(cb200_system* sys, void* send_left_dev, void* send_right_dev) {
+    System* S = SYSL(sys);
+    if (!S || !S->slab_on)
+        return set_error(CB200_ERR_STATE, "cb200_slab_configure was not called");
+    if ((S->slab_has_left && !send_left_dev) || (S->slab_has_right && !send_right_dev))
+        return set_error(CB200_ERR_ARG, "missing send buffer for a side that has a neighbour");
+    CB_CUDA(cudaSetDevice(S->device));
+    const SlabGeom G = slab_geom(S);
+    const SlabArrays A = slab_arrays(S);
+    const int grid = grid_for(S, G.owned_cap, 256);
+    k_slab_flags<<<grid, 256, 0, S->stream>>>(G, A, S->slab_flags.p, S->d_cnt);
+    S->launches++;
+    CB_TRY(scan_u64(S, S->slab_flags.p, S->slab_flags.p, S->slab_cnt, G.owned_cap));
+    k_slab_pack<<<grid, 256, 0, S->stream>>>(G, A, S->slab_flags.p, (double*)send_left_dev, (double*)send_right_dev,
+                                             S->slab_vacant.p, S->slab_cnt, S->d_cnt);
+    S->launches++;
+    CB_CUDA(cudaGetLastError());
+    return CB200_OK;
+}
+
+// Enqueue the unpack pass: ghost regions rebuilt from the two received DEVICE buffers, arrivals adopted.
+int cb200_slab_unpack_dev(cb200_system* sys, const void* recv_left_dev, const void* recv_right_dev) {
+    System* S = SYSL(sys);
+    if (!S || !S->slab_on)
+        return set_error(CB200_ERR_STATE, "cb200_slab_configure was not called");
+    CB_CUDA(cudaSetDevice(S->device));
+    const SlabGeom G = slab_geom(S);
+    const SlabArrays A = slab_arrays(S);
+    const uint32_t gl = S->slab_nb_static + G.owned_cap, gr = gl + G.ghost_cap;
+    k_slab_unpack<<<1, 1024, 0, S->stream>>>(G, A, S->slab_has_left ? (const double*)recv_left_dev : nullptr, gl,
+                                             S->slab_vacant.p, S->slab_cnt, 1, S->d_cnt);
+    k_slab_unpack<<<1, 1024, 0, S->stream>>>(G, A, S->slab_has_right ? (const double*)recv_right_dev : nullptr, gr,
+                                             S->slab_vacant.p, S->slab_cnt, 0, S->d_cnt);
+    S->launches += 2;
+    CB_CUDA(cudaGetLastError());
+    S->meta_dirty = true;
+    return CB200_OK;
+}
+
+}  // extern "C"

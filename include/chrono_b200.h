@@ -226,11 +226,34 @@ int64_t cb200_kernel_launches(cb200_system* sys);
 /* --- device-pointer access for zero-copy tooling and multi-GPU halo exchange ---------------------- */
 /* names: "pos","rot","vel","hf","aabb_min","aabb_max","contact_normal",... ; returns device pointer + element count */
 int cb200_device_array(cb200_system* sys, const char* name, void** dev_ptr, int64_t* count);
-/* Slab decomposition: pack bodies whose centre lies in [lo,hi) along axis into a caller-provided DEVICE buffer
- * (13 doubles + id per body) and report how many were packed; unpack overwrites the state of the listed bodies. */
-int cb200_pack_slab_dev(cb200_system* sys, int axis, double lo, double hi, void* buffer_dev, int64_t capacity,
-                        int64_t* count);
-int cb200_unpack_slab_dev(cb200_system* sys, const void* buffer_dev, int64_t count);
+/* --- asynchronous stepping (callers that interleave their own work on the stream, e.g. the slab exchange) ----- */
+/* Use the caller's CUDA stream (a cudaStream_t, e.g. torch.cuda.current_stream().cuda_stream; 0 = the legacy default
+ * stream) for everything the library enqueues; use_own != 0 returns to the stream cb200_create made. */
+int cb200_set_stream(cb200_system* sys, void* cuda_stream, int use_own);
+/* cb200_do_steps without the final synchronisation and without capacity recovery. */
+int cb200_enqueue_steps(cb200_system* sys, int nsteps);
+/* Synchronise, resolve timers, and fail if a capacity overflowed since the last check (the steps after an overflow
+ * did not run). */
+int cb200_check(cb200_system* sys);
+int cb200_reset_timers(cb200_system* sys);
+
+/* --- slab decomposition across GPUs (no reference counterpart: Chrono::Multicore is single-node) ---- */
+/* Global body ids (index in the undecomposed system) of bodies [first, first+n). */
+int cb200_upload_body_ids(cb200_system* sys, int first, int n, const int64_t* ids);
+/* ids and flags (bit0 owned/active, bit1 collide, bit2 vacant slot) of bodies [first, first+n); either may be NULL */
+int cb200_download_body_ids(cb200_system* sys, int first, int n, int64_t* ids, uint8_t* flags);
+/* Make this system one slab: bodies [nb_static, nb) are its owned bodies (one shape each, in order); appends vacant
+ * owned slots up to owned_cap and two ghost regions of ghost_cap slots.  [lo, hi) is the owned interval along axis,
+ * width the ghost-layer width (>= 2 r_max + 2 envelope). */
+int cb200_slab_configure(cb200_system* sys, int nb_static, int ns_static, int axis, double lo, double hi, double width,
+                         int has_left, int has_right, int owned_cap, int ghost_cap);
+/* doubles in one exchange buffer: 2 (count, reserved) + 33 per record * ghost_cap */
+int64_t cb200_slab_buffer_doubles(cb200_system* sys);
+/* After a step: write the bodies within `width` of (or past) each cut plane into the neighbour's DEVICE send buffer
+ * and release the slots of bodies that left [lo, hi).  Asynchronous on the system's stream. */
+int cb200_slab_pack_dev(cb200_system* sys, void* send_left_dev, void* send_right_dev);
+/* Rebuild the ghost regions from the two received DEVICE buffers; records inside [lo, hi) are adopted as owned. */
+int cb200_slab_unpack_dev(cb200_system* sys, const void* recv_left_dev, const void* recv_right_dev);
 
 #ifdef __cplusplus
 }
