@@ -213,6 +213,8 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     lib = _lib.load()
+    if world > 1:
+        return run_b200_slabs(args, rank, world, local, barrier)
     scene = make_scene(args, rank, world)
     nb = scene["mass"].size
     sys_ = cw.load_scene(cw.ChSystemMulticoreSMC(local), scene)
@@ -295,6 +297,118 @@ def run_b200(args):
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_b200_slabs(args, rank, world, local, barrier):
+    """N > 1: BASELINE.json configs[2] -- one bed of world * nx x ny x nz spheres cut into slabs along x, one slab per
+    GPU, ghost layers exchanged with NCCL send/recv after every step (weak scaling: 1M spheres per GPU)."""
+    import torch
+    import torch.distributed as dist
+
+    from chrono_wisc_b200 import _lib, scenes, slab
+
+    lib = _lib.load()
+    scene, gids, cuts, width = scenes.settling_smc_slab(rank, world, args.nx, args.ny, args.nz, seed=12345,
+                                                        bin_edge=args.bin_edge if args.bin_edge > 0 else 2.5,
+                                                        spacing_factor=args.spacing, jitter_factor=0.005)
+    spacing = args.spacing * 0.02
+    ghost_cap = int(2.5 * args.ny * args.nz * (width / spacing + 1)) + 1024
+    layout = slab.SlabLayout(world, rank, cuts, axis=0, width=width)
+    n_owned0 = gids.size
+    sys_ = slab.SlabSystemSMC(layout, device=local, exchange=slab.DistExchange(layout), ghost_cap=ghost_cap,
+                              owned_cap=int(n_owned0 * 1.1) + 4096)
+    nb_static = 1
+    ns_static = int((scene["shape_body"] < nb_static).sum())
+    sys_.LoadPart(scene, gids, nb_static, ns_static)
+    nb_total = world * n_owned0 + 1
+    sys_.ExchangeGhosts()  # initial ghost layers
+    sys_.DoSteps(args.settle)
+    sys_.DoSteps(args.warmup)
+    sys_.Check()
+    sys_.ResetTimers()
+
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = sys_.KernelLaunches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t0 = time.perf_counter()
+    e0.record()
+    sys_.DoSteps(args.steps)
+    e1.record()
+    torch.cuda.synchronize()
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.result()
+    sys_.Check()
+    launches = sys_.KernelLaunches() - l0
+    dev_ms = e0.elapsed_time(e1) / args.steps  # step + pack + NCCL exchange + unpack, on the one stream they share
+    counts = sys_.GetCounts()
+    stage_ms = {n: sys_.GetTimer(n) * 1e3 for n in ("update", "collision_broad", "collision_narrow", "advance",
+                                                   "integrate")}
+    t = torch.tensor([dev_ms, wall], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, wall = float(t[0].item()), float(t[1].item())
+    value = (nb_total - 1) * args.steps / (dev_ms * 1e-3 * args.steps)
+    owned = torch.tensor([sys_.GetOwned()[0].size, sys_.GetGhostIds().size], dtype=torch.float64, device="cuda")
+    tot = owned.clone()
+    dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    assert int(tot[0].item()) == nb_total - 1, "slabs lost or duplicated bodies"
+
+    # e2e: host pose + velocity of every slot in, one step with exchange, host state out (pinned buffers)
+    nbs = sys_.num_bodies
+    n_e2e = max(1, min(args.steps, args.e2e_steps))
+    pin = []
+
+    def pinned(shape):
+        n = int(np.prod(shape)) * 8
+        p = C.c_void_p()
+        _lib.check(lib.cb200_host_alloc(n, C.byref(p)))
+        pin.append(p)
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_double)), shape=(int(np.prod(shape)),)).reshape(shape)
+
+    hp, hq, hv = pinned((nbs, 3)), pinned((nbs, 4)), pinned((nbs, 6))
+    p0, q0, v0 = sys_.GetBodyState()
+    hp[:], hq[:], hv[:] = p0, q0, v0
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(n_e2e):
+        sys_.SetBodyState(0, hp, hq, hv, nbs)
+        sys_.DoSteps(1)
+        _lib.check(lib.cb200_download_state(sys_._h, 0, nbs, hp.ctypes.data_as(C.c_void_p),
+                                            hq.ctypes.data_as(C.c_void_p), hv.ctypes.data_as(C.c_void_p)))
+    barrier()
+    e2e_wall = time.perf_counter() - t0
+    t = torch.tensor([e2e_wall], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = (nb_total - 1) * n_e2e / float(t.item())
+    for p in pin:
+        lib.cb200_host_free(p)
+
+    if rank == 0:
+        peak, peak_kind = measured_peak_gbs()
+        bytes_step = algorithmic_bytes(n_owned0 + int(owned[1].item()), counts)
+        achieved = bytes_step / (dev_ms * 1e-3) / 1e9
+        cfg = workload_config(args, counts, n_owned0)
+        cfg["workload"] = (f"{world * args.nx}x{args.ny}x{args.nz} = {world * n_owned0} monodisperse spheres r=0.02, Hertz SMC "
+                           f"settling in a 5-wall box, FP64, h=1e-3, FIXED_BIN_SIZE {args.bin_edge} diameters, {world} slabs "
+                           "along x with NCCL ghost-layer exchange every step (BASELINE.json configs[2] at 1M spheres/GPU)")
+        cfg.update({"parallelism": f"slab{world}", "ghost_width": width, "ghost_bodies_rank0": int(owned[1].item()),
+                    "exchange_bytes_per_step_per_neighbour": int(8 * (2 + 33 * ghost_cap))})
+        line = {
+            "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dev_ms, "wall_ms_per_step": wall / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": cfg, "stage_ms": stage_ms, "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": nbs * 13 * 8 * world,
+                    "d2h_bytes_per_step": nbs * 13 * 8 * world, "steps": n_e2e},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_kind": peak_kind, "kernel": "whole step of rank 0 (all kernels + exchange)",
+                         "algorithmic_bytes_per_step": bytes_step},
+        }
+        print(json.dumps(line))
+    dist.destroy_process_group()
 
 
 def main():

@@ -208,3 +208,55 @@ def balls_nsc(nx=16, ny=16, nz=4, radius=0.15, seed=3, step=1e-2, envelope=0.01,
                     max_iteration_sliding=iterations, max_iteration_spinning=0, alpha=0.0,
                     contact_recovery_speed=1e4, tolerance=0.0)
     return b.finish([nsc_material(friction=mu)], settings)
+
+
+def settling_smc_slab(rank, world, nx=250, ny=250, nz=16, radius=0.02, seed=12345, bin_edge=2.5, step=1e-3,
+                      young=2e6, mu=0.4, cr=0.4, rho=2000.0, spacing_factor=2.0, jitter_factor=0.005,
+                      wall_thickness=0.2, ghost_width=None):
+    """Rank ``rank``'s share of the (world * nx) x ny x nz settling bed of BASELINE.json configs[2] (8M spheres =
+    8 ranks of 250 x 250 x 16), generated locally: slabs are cut along x between lattice planes; the container is one
+    static body whose floor and y walls are boxes covering this rank's interval plus a margin, the x walls exist on
+    the first and last rank only.  Returns (scene, gids, cuts, ghost_width); gids follow the global lattice order
+    (x fastest, then y, then z; body 0 is the container)."""
+    b = SceneBuilder()
+    spacing = spacing_factor * radius
+    gnx = world * nx
+    sx = gnx * spacing + 2 * radius * 0.5
+    sy = ny * spacing + 2 * radius * 0.5
+    sz = max(1.0, (nz + 2) * spacing)
+    if ghost_width is None:
+        ghost_width = 2 * radius * 1.25  # >= 2 r_max + 2 envelope (SMC: envelope 0), with room for one step of motion
+    x_of = lambda i: (i - (gnx - 1) / 2) * spacing
+    cuts = [x_of(g * nx) - spacing / 2 for g in range(world + 1)]
+    cuts[0], cuts[-1] = -sx, sx
+    lo = -sx / 2 if rank == 0 else cuts[rank] - 4 * ghost_width
+    hi = sx / 2 if rank == world - 1 else cuts[rank + 1] + 4 * ghost_width
+    cx, lx = (lo + hi) / 2, hi - lo
+    ht = wall_thickness / 2
+    bin_body = b.add_bodies(1.0, (1.0, 1.0, 1.0), [[0.0, 0.0, 0.0]], active=0, collide=1)
+    walls = [((cx, 0, -ht), (lx / 2, sy / 2, ht)),
+             ((cx, -sy / 2 - ht, sz / 2), (lx / 2, ht, sz / 2)), ((cx, sy / 2 + ht, sz / 2), (lx / 2, ht, sz / 2))]
+    if rank == 0:
+        walls.append(((-sx / 2 - ht, 0, sz / 2), (ht, sy / 2, sz / 2)))
+    if rank == world - 1:
+        walls.append(((sx / 2 + ht, 0, sz / 2), (ht, sy / 2, sz / 2)))
+    for p, h in walls:
+        b.add_shapes(BOX, [bin_body], np.array([h]), pos=[np.asarray(p, dtype=np.float64)])
+    m = rho * 4.0 / 3.0 * np.pi * radius ** 3
+    inertia = 0.4 * m * radius * radius
+    rng = np.random.Generator(np.random.MT19937(seed + rank))
+    ix, iy, iz = np.meshgrid(np.arange(nx), np.arange(ny), np.arange(nz), indexing="ij")
+    ix, iy, iz = (a.transpose(2, 1, 0).ravel() for a in (ix, iy, iz))
+    gi = ix + rank * nx
+    pos = np.stack([x_of(gi), (iy - (ny - 1) / 2) * spacing, 1.01 * radius + iz * spacing], 1).astype(np.float64)
+    pos += rng.uniform(-jitter_factor * radius, jitter_factor * radius, size=pos.shape)
+    first = b.add_bodies(m, (inertia, inertia, inertia), pos)
+    n = pos.shape[0]
+    b.add_shapes(SPHERE, np.arange(first, first + n), np.full((n, 1), radius))
+    gids = (iz.astype(np.int64) * ny + iy) * gnx + gi + 1
+    settings = dict(system_type=1, step_size=step, gravity=(0.0, 0.0, -9.81), contact_force_model=HERTZ,
+                    adhesion_force_model=0, tangential_displ_mode=1, use_material_properties=1,
+                    narrowphase_algorithm=HYBRID, collision_envelope=0.0, broadphase_grid=FIXED_BIN_SIZE,
+                    bin_size=(bin_edge * 2 * radius,) * 3)
+    scene = b.finish([smc_material(young=young, friction=mu, restitution=cr)], settings)
+    return scene, gids, cuts, ghost_width

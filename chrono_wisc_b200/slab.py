@@ -139,16 +139,29 @@ class _SlabMixin:
         import torch
 
         L = self.layout
-        part, my_gids, self.nb_static, self.ns_static = split_scene(global_scene, L, gids)
-        load_scene(self, part)
-        n_dyn = my_gids.size
-        owned_cap = self._owned_cap or int(n_dyn * 1.25) + 1024
+        part, my_gids, nb_static, ns_static = split_scene(global_scene, L, gids)
         if self._ghost_cap is None:
             # must be the same on every rank (it sizes the exchange buffers): four times the mean population of a
             # band of the ghost width in the global scene, plus head room
-            x = global_scene["pos"][self.nb_static:, L.axis]
+            x = global_scene["pos"][nb_static:, L.axis]
             span = max(float(x.max() - x.min()), 2 * L.width)
             self._ghost_cap = int(4 * x.size * L.width / span) + 4096
+        return self.LoadPart(part, my_gids, nb_static, ns_static)
+
+    def LoadPart(self, part, my_gids, nb_static, ns_static):
+        """Load a scene that already holds only this rank's share: ``nb_static`` static bodies (``ns_static`` shapes)
+        followed by the owned bodies, one shape each; ``my_gids`` are their global ids.  ``ghost_cap`` must have been
+        given to the constructor (the same value on every rank)."""
+        import torch
+
+        L = self.layout
+        if self._ghost_cap is None:
+            raise ValueError("ghost_cap must be set (identical on all ranks) when loading a per-rank scene")
+        self.nb_static, self.ns_static = int(nb_static), int(ns_static)
+        load_scene(self, part)
+        my_gids = np.ascontiguousarray(my_gids, dtype=np.int64)
+        n_dyn = my_gids.size
+        owned_cap = self._owned_cap or int(n_dyn * 1.25) + 1024
         ids = np.full(self.num_bodies, -1, np.int64)
         ids[self.nb_static:] = my_gids
         check(self._lib.cb200_upload_body_ids(self._h, 0, self.num_bodies, ids.ctypes.data_as(C.c_void_p)))
