@@ -88,6 +88,10 @@ static int alloc_entries(System* S, uint32_t n) {
     CB_TRY(S->ent_m.reserve(S->ent_tmp.cap));
     S->cap_entries = (uint32_t)S->ent_tmp.cap;
     CB_TRY(S->ent_off.reserve((size_t)S->cap_entries + 4));
+    if (use_complex(S)) {
+        CB_TRY(S->ent_cmask.reserve(S->cap_entries));
+        CB_TRY(S->ent_cbase.reserve(S->cap_entries));
+    }
     return CB200_OK;
 }
 static int alloc_contacts(System* S, uint32_t n) {
@@ -105,6 +109,18 @@ static int alloc_contacts(System* S, uint32_t n) {
     CB_TRY(S->b_inc.reserve(2 * c));
     CB_TRY(S->heavy_part.reserve((size_t)MAX_HEAVY * (c / 4096 + 2) * 7));
     S->cap_contacts = (uint32_t)c;
+    if (use_complex(S))
+        CB_TRY(S->c_src.reserve(c));
+    return CB200_OK;
+}
+static int alloc_complex(System* S, uint32_t nrec, uint32_t nslots) {
+    if (nslots < 2 * nrec)
+        nslots = 2 * nrec;
+    CB_TRY(S->cplx_rec.reserve(4 * (size_t)nrec));
+    S->cap_complex = (uint32_t)(S->cplx_rec.cap / 4);
+    CB_TRY(S->cplx_n.reserve(S->cap_complex));
+    CB_TRY(S->cplx_out.reserve(11 * (size_t)nslots));
+    S->cap_cslots = (uint32_t)(S->cplx_out.cap / 11);
     return CB200_OK;
 }
 static int alloc_pairs(System* S, uint32_t n) {
@@ -129,6 +145,13 @@ int ensure_capacity(System* S) {
         CB_TRY(alloc_entries(S, (uint32_t)(8 * ns + 4096)));
     if (S->cap_contacts < 2 * ns + 1024)
         CB_TRY(alloc_contacts(S, (uint32_t)(6 * ns + 4096)));
+    if (use_complex(S)) {
+        CB_TRY(S->ent_cmask.reserve(S->cap_entries));
+        CB_TRY(S->ent_cbase.reserve(S->cap_entries));
+        CB_TRY(S->c_src.reserve(S->cap_contacts));
+        if (S->cap_complex == 0)
+            CB_TRY(alloc_complex(S, (uint32_t)(4 * (size_t)S->n_nonsphere + 4096), 0));
+    }
     return CB200_OK;
 }
 
@@ -150,6 +173,8 @@ int grow_after_overflow(System* S) {
         CB_TRY(alloc_contacts(S, c.need_contacts + c.need_contacts / 4));
     if (c.overflow & OVF_PAIRS)
         CB_TRY(alloc_pairs(S, c.need_pairs + c.need_pairs / 8));
+    if (c.overflow & OVF_COMPLEX)
+        CB_TRY(alloc_complex(S, c.need_complex + c.need_complex / 4, c.need_cslots + c.need_cslots / 4));
     if (c.overflow & OVF_NSC)
         S->nsc_extra_slots = 2 * S->nsc_extra_slots + 32 + (int)c.need_nsc_slots / 4;
     CB_CUDA(cudaMemsetAsync(&S->d_cnt->overflow, 0, 4, S->stream));
@@ -268,6 +293,7 @@ void cb200_destroy(cb200_system* sys) {
     REL(s_box); REL(s_meta); REL(mat_smc); REL(mat_nsc); REL(bin_intersections); REL(bin_start); REL(bin_cursor);
     REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_mask); REL(ent_c); REL(ent_m); REL(ent_off); REL(large_list); REL(pairs);
     REL(c_norm); REL(c_pta); REL(c_ptb); REL(c_depth); REL(c_erad); REL(c_bids); REL(c_shapes); REL(c_mats);
+    REL(ent_cmask); REL(ent_cbase); REL(cplx_rec); REL(cplx_n); REL(cplx_out); REL(c_src);
     REL(ct_force); REL(ct_torque); REL(b_deg); REL(b_cursor); REL(b_inc); REL(b_force); REL(heavy_list);
     REL(heavy_part); REL(n_frame); REL(n_aux); REL(gamma); REL(n_gamma_hat); REL(n_y); REL(n_gn); REL(n_g); REL(n_rfull);
     REL(n_w); REL(n_w0); REL(n_mk); REL(n_part); REL(n_hist); REL(n_rows);

@@ -114,7 +114,8 @@ struct DevCounters {
     uint32_t need_nsc_slots;     // APGD slot budget that would have sufficed (OVF_NSC)
     double nsc_residual, nsc_objective;
     uint32_t nsc_hist_count;     // iterations recorded in the residual history (includes the one that broke out)
-    uint32_t pad2;
+    uint32_t n_cslots;           // contact slots reserved for the complex pairs (PreprocessCount's rule per pair)
+    uint32_t need_cslots, pad2;
 };
 
 struct Timer {
@@ -192,6 +193,15 @@ struct System {
     DevBuf<int64_t> c_shapes;    // 1 per contact
     DevBuf<uint32_t> c_mats;     // 1 per contact
 
+    // ---- multi-contact / MPR pairs ("complex" pairs: no sphere involved, or algorithm == MPR) ----
+    uint32_t cap_complex = 0, cap_cslots = 0;
+    DevBuf<uint64_t> ent_cmask;  // cap_entries  bit j set: the pair (entry, j-th entry of its bin) needs the complex path
+    DevBuf<uint32_t> ent_cbase;  // cap_entries  first complex record of the entry
+    DevBuf<uint32_t> cplx_rec;   // 4 per record: entry, shape A, shape B, first slot
+    DevBuf<uint32_t> cplx_n;     // contacts found per record
+    DevBuf<double> cplx_out;     // 11 per slot: normal, point A, point B, depth, effective radius
+    DevBuf<uint32_t> c_src;      // cap_contacts  slot + 1 of a contact computed by the complex path, 0 otherwise
+
     // ---- SMC (MC/solver/ChIterativeSolverMulticoreSMC.cpp) ----
     DevBuf<double> ct_force;    // 3 N_c  force on body 2 (body 1 gets the negative)
     DevBuf<double> ct_torque;   // 6 N_c  torque on body 1, torque on body 2 (body frames)
@@ -236,6 +246,9 @@ struct System {
     std::map<std::string, Timer> timers;
     int timed_steps = 0;
 };
+
+// multi-contact / MPR pairs can occur: two or more non-sphere shapes, or MPR requested for everything
+inline bool use_complex(const System* S) { return S->n_nonsphere >= 2 || S->set.narrowphase_algorithm == 0; }
 
 // ---- shared host helpers (defined in api.cu) ----
 int timer_start(System* S, const char* name);

@@ -20,6 +20,8 @@
 // Order of the contact list = (bin, shape A, shape B) = the order the reference's stable compaction leaves.
 #include "grid.cuh"
 #include "prims.cuh"
+#include "mpr.cuh"
+#include "prims_multi.cuh"
 #include <limits.h>
 
 namespace cb200 {
@@ -108,13 +110,6 @@ __device__ __forceinline__ bool pair_passes(const Rec& A, const Rec& B, const Gr
     return (mA & gB) && (mB & gA);
 }
 
-struct ShapeView {
-    int type;
-    d3 pos;
-    q4 rot;
-    double d0, d1, d2, d3_;
-};
-
 __device__ __forceinline__ ShapeView make_view(uint32_t id, int type, const double4& w,
                                                const double* __restrict__ s_wrot, const double* __restrict__ s_dims) {
     ShapeView v;
@@ -191,6 +186,89 @@ __device__ __forceinline__ int prims_single(const ShapeView& A, const ShapeView&
     return -1;
 }
 
+// Full shape view for the complex path: spheres carry their true world rotation too (MPR rotates the search
+// direction into the shape frame, ChCollisionUtilsMPR.cpp:71-74); a body-centred sphere has no s_wrot entry.
+__device__ __forceinline__ ShapeView make_view_full(uint32_t id, const ShapeMeta& m, const double* __restrict__ s_wpos,
+                                                    const double* __restrict__ s_wrot,
+                                                    const double* __restrict__ s_dims,
+                                                    const double* __restrict__ s_lrot,
+                                                    const double* __restrict__ rot) {
+    ShapeView v;
+    v.type = (m.info >> 8) & 0xff;
+    const double4 w = reinterpret_cast<const double4*>(s_wpos)[id];
+    v.pos = mk3(w.x, w.y, w.z);
+    const double4 d = reinterpret_cast<const double4*>(s_dims)[id];
+    v.d0 = d.x, v.d1 = d.y, v.d2 = d.z, v.d3_ = d.w;
+    if (m.info & 4u) {
+        const double4 qa = reinterpret_cast<const double4*>(rot)[m.body];
+        const double4 la = reinterpret_cast<const double4*>(s_lrot)[id];
+        v.rot = qmul(mkq(qa.x, qa.y, qa.z, qa.w), mkq(la.x, la.y, la.z, la.w));
+    } else {
+        const double4 r = reinterpret_cast<const double4*>(s_wrot)[id];
+        v.rot = mkq(r.x, r.y, r.z, r.w);
+    }
+    return v;
+}
+
+// slots the reference reserves for a pair (PreprocessCount, CMC/ChNarrowphase.cpp:94-137)
+__device__ __forceinline__ uint32_t pair_slots(int tA, int tB, int algorithm) {
+    if (algorithm == 0)
+        return 1;
+    if (tA == CB200_SPHERE || tB == CB200_SPHERE)
+        return 1;
+    if (tA == CB200_CAPSULE || tB == CB200_CAPSULE)
+        return 2;
+    if (tA == CB200_CYLSHELL || tB == CB200_CYLSHELL)
+        return 8;
+    if (tA == CB200_BOX && tB == CB200_BOX)
+        return 8;
+    return 1;
+}
+
+__device__ __forceinline__ void flip_contacts(Contact* out, int n) {
+    for (int i = 0; i < n && i < MAX_PAIR_CONTACTS; i++) {
+        const d3 t = out[i].p1;
+        out[i].p1 = out[i].p2;
+        out[i].p2 = t;
+        out[i].n = -out[i].n;
+    }
+}
+
+// Narrowphase of one complex pair: DispatchMPR / DispatchPRIMS / DispatchHybridMPR (CMC/ChNarrowphase.cpp:232-320)
+// over PRIMSCollision (ChNarrowphasePRIMS.cpp:1406-1607) and MPRCollision (ChNarrowphaseMPR.cpp:627-645).
+// Returns the number of contacts written to out[0..], or -1 for a combination this backend does not cover
+// (box - cylindrical shell, whose analytic test is not implemented here).
+__device__ __noinline__ int narrow_complex(const ShapeView& A, const ShapeView& B, int algorithm, double envelope,
+                                           Contact* out) {
+    const double sep = 2 * envelope;
+    if (algorithm != 0) {
+        int n = prims_single(A, B, sep, out[0]);
+        if (n >= 0)
+            return n;
+        const int tA = A.type, tB = B.type;
+        if (tA == CB200_CAPSULE && tB == CB200_CAPSULE)
+            return capsule_capsule(A.pos, A.rot, A.d0, A.d1, B.pos, B.rot, B.d0, B.d1, sep, out);
+        if (tA == CB200_BOX && tB == CB200_CAPSULE)
+            return box_capsule(A.pos, A.rot, mk3(A.d0, A.d1, A.d2), B.pos, B.rot, B.d0, B.d1, sep, out);
+        if (tA == CB200_CAPSULE && tB == CB200_BOX) {
+            n = box_capsule(B.pos, B.rot, mk3(B.d0, B.d1, B.d2), A.pos, A.rot, A.d0, A.d1, sep, out);
+            flip_contacts(out, n);
+            return n;
+        }
+        if (tA == CB200_BOX && tB == CB200_BOX)
+            return box_box(A.pos, A.rot, mk3(A.d0, A.d1, A.d2), B.pos, B.rot, mk3(B.d0, B.d1, B.d2), sep, out);
+        if ((tA == CB200_BOX && tB == CB200_CYLSHELL) || (tA == CB200_CYLSHELL && tB == CB200_BOX))
+            return -1;
+        if (algorithm == 1)
+            return 0;  // PRIMS only: no analytic test, no contact
+    }
+    if (mpr_collision(A, B, envelope, out[0].n, out[0].p1, out[0].p2, out[0].depth)) {
+        out[0].erad = DEFAULT_EFF_RADIUS;
+        return 1;
+    }
+    return 0;
+}
+
 // cold path of pair_hit (a non-sphere is involved): kept out of line so that the sphere-sphere loop stays lean
 __device__ __noinline__ int pair_hit_general(uint32_t idA, int tA, double4 wA, uint32_t idB, int tB, double4 wB,
                                              double sep, const double* __restrict__ s_wrot,
@@ -242,22 +320,23 @@ __device__ __forceinline__ T warp_incl_scan_bp(T v, int lane) {
 // --------------------------------------------------------------------------------------------------------------
 enum { MODE_PAIRS = 0, MODE_CONTACTS = 1 };
 
-__device__ __forceinline__ bool pair_decide(const Rec& A, const Rec& B, const GridParams& g, uint32_t bin, int mode,
-                                            double sep, int algorithm, const double* __restrict__ s_wrot,
-                                            const double* __restrict__ s_dims, uint32_t& np, uint32_t& ncx) {
+// 0: no output, 1: the pair yields one contact (or, in PAIRS mode, passes the broadphase filter),
+// 2: the pair needs the complex path (multi-contact analytic test or MPR)
+__device__ __forceinline__ int pair_decide(const Rec& A, const Rec& B, const GridParams& g, uint32_t bin, int mode,
+                                           double sep, int algorithm, const double* __restrict__ s_wrot,
+                                           const double* __restrict__ s_dims, uint32_t& np) {
     if (A.body == UINT_MAX || !(A.info & 2u))
-        return false;
+        return 0;
     if (!pair_passes(A, B, g, bin))
-        return false;
+        return 0;
     np++;
     if (mode == MODE_PAIRS)
-        return true;
+        return 1;
     const int n = pair_hit(A, B, sep, algorithm, s_wrot, s_dims);
-    if (n < 0)
-        ncx++;
-    return n == 1;
+    return n < 0 ? 2 : n;
 }
 
+template <bool CPLX>
 __global__ void __launch_bounds__(PAIR_TILE, 3) k_pair_masks(const ShapeMeta* __restrict__ meta,
                                                           const ShapeMeta* __restrict__ ent_m,
                                                           const double* __restrict__ ent_c,
@@ -269,10 +348,12 @@ __global__ void __launch_bounds__(PAIR_TILE, 3) k_pair_masks(const ShapeMeta* __
                                                           const uint32_t* __restrict__ ent_bin,
                                                           const uint64_t* __restrict__ bin_start, double envelope,
                                                           int algorithm, int mode, uint64_t* __restrict__ ent_mask,
+                                                          uint64_t* __restrict__ ent_cmask,
                                                           uint32_t* __restrict__ ent_cnt,
                                                           DevCounters* __restrict__ cnt) {
     __shared__ Window W;
     __shared__ unsigned long long smask[WIN];
+    __shared__ unsigned long long scmask[CPLX ? WIN : 1];
     if (cnt->overflow)
         return;
     const GridParams g = load_grid(cnt);
@@ -291,6 +372,8 @@ __global__ void __launch_bounds__(PAIR_TILE, 3) k_pair_masks(const ShapeMeta* __
             load_rec_sorted(R, e0 + k, ent_m, ent_c, s_wpos, s_box, g.origin, envelope);
             win_put(W, k, R);
             smask[k] = 0ull;
+            if (CPLX)
+                scmask[k] = 0ull;
         }
         __syncthreads();
 
@@ -318,6 +401,8 @@ __global__ void __launch_bounds__(PAIR_TILE, 3) k_pair_masks(const ShapeMeta* __
                 if (lane == 0) {
                     ent_mask[s] = 0ull;
                     ent_cnt[s] = 0;
+                    if (CPLX)
+                        ent_cmask[s] = 0ull;
                 }
                 continue;
             }
@@ -345,8 +430,15 @@ __global__ void __launch_bounds__(PAIR_TILE, 3) k_pair_masks(const ShapeMeta* __
                         Rec A, B;
                         win_get(W, (int)(w0 + a), A);
                         win_get(W, (int)(w0 + c), B);
-                        if (pair_decide(A, B, g, b, mode, sep, algorithm, s_wrot, s_dims, np, ncx))
+                        const int dec = pair_decide(A, B, g, b, mode, sep, algorithm, s_wrot, s_dims, np);
+                        if (dec == 1)
                             atomicOr(&smask[w0 + a], 1ull << c);
+                        else if (dec == 2) {
+                            if (CPLX)
+                                atomicOr(&scmask[w0 + a], 1ull << c);
+                            else
+                                ncx++;
+                        }
                     }
                 }
                 __syncwarp();
@@ -354,6 +446,8 @@ __global__ void __launch_bounds__(PAIR_TILE, 3) k_pair_masks(const ShapeMeta* __
                     const unsigned long long m = smask[w0 + t];
                     ent_mask[s + t] = m;
                     ent_cnt[s + t] = (uint32_t)__popcll(m);
+                    if (CPLX)
+                        ent_cmask[s + t] = scmask[w0 + t];
                 }
             } else {
                 // long bin: rows one after the other, lanes across the row; count only
@@ -370,7 +464,9 @@ __global__ void __launch_bounds__(PAIR_TILE, 3) k_pair_masks(const ShapeMeta* __
                             win_get(W, (int)(w0 + j), B);
                         else
                             load_rec(B, ent_shape[s + j], meta, s_wpos, s_box, g.origin, envelope);
-                        hits += pair_decide(A, B, g, b, mode, sep, algorithm, s_wrot, s_dims, np, ncx) ? 1u : 0u;
+                        const int dec = pair_decide(A, B, g, b, mode, sep, algorithm, s_wrot, s_dims, np);
+                        hits += dec == 1 ? 1u : 0u;
+                        ncx += dec == 2 ? 1u : 0u;  // long bins have no complex path
                     }
 #pragma unroll
                     for (int d = 16; d > 0; d >>= 1)
@@ -378,11 +474,15 @@ __global__ void __launch_bounds__(PAIR_TILE, 3) k_pair_masks(const ShapeMeta* __
                     if (lane == 0) {
                         ent_mask[s + i] = 0ull;
                         ent_cnt[s + i] = hits;
+                        if (CPLX)
+                            ent_cmask[s + i] = 0ull;
                     }
                 }
                 if (lane == 0) {
                     ent_mask[s + k - 1] = 0ull;
                     ent_cnt[s + k - 1] = 0;
+                    if (CPLX)
+                        ent_cmask[s + k - 1] = 0ull;
                 }
             }
         }
@@ -401,8 +501,104 @@ __global__ void __launch_bounds__(PAIR_TILE, 3) k_pair_masks(const ShapeMeta* __
     }
 }
 
+// --------------------------------------------------------------------------------------------------------------
+// Complex pairs (multi-contact analytic tests and MPR).
+//   k_cplx_collect  one thread per entry: reserves records and contact slots for the entry's complex candidates
+//                   (atomic cursors; the order of the records is irrelevant, the final position of a contact is
+//                   derived from the entry offsets, so the result is deterministic)
+//   k_cplx_narrow   one thread per record: narrow_complex -> up to 8 contacts into the record's slots; adds the
+//                   number found to the entry's output count
+// --------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_cplx_collect(const ShapeMeta* __restrict__ meta,
+                                                      const uint32_t* __restrict__ ent_shape,
+                                                      const uint32_t* __restrict__ ent_bin,
+                                                      const uint64_t* __restrict__ bin_start,
+                                                      const uint64_t* __restrict__ ent_cmask, int algorithm,
+                                                      uint32_t* __restrict__ ent_cbase, uint32_t* __restrict__ rec,
+                                                      uint32_t cap_rec, DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    const uint32_t ni = cnt->n_intersections;
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < ni; e += gridDim.x * blockDim.x) {
+        unsigned long long m = ent_cmask[e];
+        if (!m)
+            continue;
+        const uint32_t count = (uint32_t)__popcll(m);
+        uint32_t base = atomicAdd(&cnt->n_complex, count);
+        ent_cbase[e] = base;
+        const uint32_t s = (uint32_t)bin_start[ent_bin[e]];
+        const uint32_t sA = ent_shape[e];
+        const int tA = (meta[sA].info >> 8) & 0xff;
+        while (m) {
+            const int j = __ffsll((long long)m) - 1;
+            m &= m - 1;
+            const uint32_t sB = ent_shape[s + j];
+            const int tB = (meta[sB].info >> 8) & 0xff;
+            const uint32_t slot = atomicAdd(&cnt->n_cslots, pair_slots(tA, tB, algorithm));
+            if (base < cap_rec)
+                reinterpret_cast<uint4*>(rec)[base] = make_uint4(e, sA, sB, slot);
+            base++;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(128) k_cplx_narrow(const ShapeMeta* __restrict__ meta,
+                                                     const double* __restrict__ s_wpos,
+                                                     const double* __restrict__ s_wrot,
+                                                     const double* __restrict__ s_dims,
+                                                     const double* __restrict__ s_lrot,
+                                                     const double* __restrict__ rot, double envelope, int algorithm,
+                                                     const uint32_t* __restrict__ rec, uint32_t cap_rec,
+                                                     uint32_t cap_slots, uint32_t* __restrict__ cplx_n,
+                                                     double* __restrict__ cplx_out, uint32_t* __restrict__ ent_cnt,
+                                                     DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    const uint32_t nrec = cnt->n_complex, nslots = cnt->n_cslots;
+    if (nrec > cap_rec || nslots > cap_slots) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) {
+            cnt->need_complex = nrec;
+            cnt->need_cslots = nslots;
+        }
+        // every CTA sees the same counters, so all of them leave; the flag is raised by the last line of the grid
+        if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0)
+            atomicOr(&cnt->overflow, (uint32_t)OVF_COMPLEX);
+        return;
+    }
+    uint32_t bad = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nrec; i += gridDim.x * blockDim.x) {
+        const uint4 r = reinterpret_cast<const uint4*>(rec)[i];
+        const ShapeMeta mA = meta[r.y], mB = meta[r.z];
+        const ShapeView A = make_view_full(r.y, mA, s_wpos, s_wrot, s_dims, s_lrot, rot);
+        const ShapeView B = make_view_full(r.z, mB, s_wpos, s_wrot, s_dims, s_lrot, rot);
+        Contact out[MAX_PAIR_CONTACTS];
+        int n = narrow_complex(A, B, algorithm, envelope, out);
+        if (n < 0) {
+            bad++;
+            n = 0;
+        }
+        const uint32_t slots = pair_slots(A.type, B.type, algorithm);
+        if ((uint32_t)n > slots)
+            n = (int)slots;
+        cplx_n[i] = (uint32_t)n;
+        for (int t = 0; t < n; t++) {
+            double* o = cplx_out + 11 * (size_t)(r.w + t);
+            o[0] = out[t].n.x, o[1] = out[t].n.y, o[2] = out[t].n.z;
+            o[3] = out[t].p1.x, o[4] = out[t].p1.y, o[5] = out[t].p1.z;
+            o[6] = out[t].p2.x, o[7] = out[t].p2.y, o[8] = out[t].p2.z;
+            o[9] = out[t].depth, o[10] = out[t].erad;
+        }
+        if (n)
+            atomicAdd(&ent_cnt[r.x], (uint32_t)n);
+    }
+    if (bad)
+        atomicAdd(&cnt->unsupported, bad);
+}
+
 // k_pair_store: one thread per entry; turns masks (or, for long bins, a re-walk of the row) into 64-bit shape-pair
-// keys at their final, compacted positions.
+// keys at their final, compacted positions.  With CPLX the contacts of complex pairs are interleaved in (j, contact)
+// order -- the order the reference's slot layout + stable compaction leaves -- and c_src points at their records.
+template <bool CPLX>
 __global__ void __launch_bounds__(256) k_pair_store(const ShapeMeta* __restrict__ meta,
                                                     const double* __restrict__ s_wpos,
                                                     const ShapeBox* __restrict__ s_box,
@@ -413,7 +609,11 @@ __global__ void __launch_bounds__(256) k_pair_store(const ShapeMeta* __restrict_
                                                     const uint64_t* __restrict__ bin_start, double envelope,
                                                     int algorithm, int mode, const uint64_t* __restrict__ ent_mask,
                                                     const uint32_t* __restrict__ ent_off, int64_t* __restrict__ out,
-                                                    uint32_t cap, DevCounters* __restrict__ cnt) {
+                                                    uint32_t cap, const uint64_t* __restrict__ ent_cmask,
+                                                    const uint32_t* __restrict__ ent_cbase,
+                                                    const uint32_t* __restrict__ rec,
+                                                    const uint32_t* __restrict__ cplx_n, uint32_t* __restrict__ c_src,
+                                                    DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
     const uint32_t ni = cnt->n_intersections;
@@ -444,21 +644,47 @@ __global__ void __launch_bounds__(256) k_pair_store(const ShapeMeta* __restrict_
         const int64_t hiA = (int64_t)ent_shape[e] << 32;
         if (k <= 64) {
             unsigned long long m = ent_mask[e];
-            while (m) {
-                const int j = __ffsll((long long)m) - 1;
-                m &= m - 1;
-                out[o++] = hiA | (int64_t)ent_shape[s + j];
+            if (CPLX && mode == MODE_CONTACTS) {
+                const unsigned long long cm = ent_cmask[e];
+                unsigned long long u = m | cm;
+                uint32_t ci = cm ? ent_cbase[e] : 0;
+                while (u) {
+                    const int j = __ffsll((long long)u) - 1;
+                    u &= u - 1;
+                    const int64_t key = hiA | (int64_t)ent_shape[s + j];
+                    if ((cm >> j) & 1ull) {
+                        const uint32_t n = cplx_n[ci];
+                        const uint32_t slot = rec[4 * (size_t)ci + 3];
+                        for (uint32_t t = 0; t < n; t++) {
+                            out[o] = key;
+                            c_src[o++] = slot + t + 1;
+                        }
+                        ci++;
+                    } else {
+                        out[o] = key;
+                        c_src[o++] = 0;
+                    }
+                }
+            } else {
+                while (m) {
+                    const int j = __ffsll((long long)m) - 1;
+                    m &= m - 1;
+                    out[o++] = hiA | (int64_t)ent_shape[s + j];
+                }
             }
         } else {
             const GridParams g = load_grid(cnt);
             Rec A;
             load_rec(A, ent_shape[e], meta, s_wpos, s_box, g.origin, envelope);
-            uint32_t np = 0, ncx = 0;
+            uint32_t np = 0;
             for (uint32_t j = e + 1; j < s + k; j++) {
                 Rec B;
                 load_rec(B, ent_shape[j], meta, s_wpos, s_box, g.origin, envelope);
-                if (pair_decide(A, B, g, bin, mode, 2 * envelope, algorithm, s_wrot, s_dims, np, ncx))
+                if (pair_decide(A, B, g, bin, mode, 2 * envelope, algorithm, s_wrot, s_dims, np) == 1) {
+                    if (CPLX && mode == MODE_CONTACTS)
+                        c_src[o] = 0;
                     out[o++] = hiA | (int64_t)B.id;
+                }
             }
         }
     }
@@ -475,6 +701,8 @@ __global__ void __launch_bounds__(256) k_contact_gen(const ShapeMeta* __restrict
                                                      double* __restrict__ c_ptb, double* __restrict__ c_depth,
                                                      double* __restrict__ c_erad, int32_t* __restrict__ c_bids,
                                                      uint32_t* __restrict__ c_mats,
+                                                     const uint32_t* __restrict__ c_src,
+                                                     const double* __restrict__ cplx_out,
                                                      const DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
@@ -488,7 +716,12 @@ __global__ void __launch_bounds__(256) k_contact_gen(const ShapeMeta* __restrict
         const double4 wB = reinterpret_cast<const double4*>(s_wpos)[sB];
         const int tA = (mA.info >> 8) & 0xff, tB = (mB.info >> 8) & 0xff;
         Contact c;
-        if (tA == CB200_SPHERE && tB == CB200_SPHERE)
+        const uint32_t src = c_src ? c_src[o] : 0u;
+        if (src) {
+            const double* q = cplx_out + 11 * (size_t)(src - 1);
+            c.n = mk3(q[0], q[1], q[2]), c.p1 = mk3(q[3], q[4], q[5]), c.p2 = mk3(q[6], q[7], q[8]);
+            c.depth = q[9], c.erad = q[10];
+        } else if (tA == CB200_SPHERE && tB == CB200_SPHERE)
             sphere_sphere(mk3(wA.x, wA.y, wA.z), wA.w, mk3(wB.x, wB.y, wB.z), wB.w, sep, c);
         else
             prims_single(make_view(sA, tA, wA, s_wrot, s_dims), make_view(sB, tB, wB, s_wrot, s_dims), sep, c);
@@ -510,16 +743,40 @@ __global__ void __launch_bounds__(256) k_contact_gen(const ShapeMeta* __restrict
 static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
     const double env = S->set.collision_envelope;
     const int algorithm = S->set.narrowphase_algorithm;
+    const bool cplx = mode == MODE_CONTACTS && use_complex(S);
     if (mode == MODE_CONTACTS)
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_pairs, 0, 4, S->stream));
-    k_pair_masks<<<grid_for(S, S->cap_entries, PAIR_TILE, 6), PAIR_TILE, 0, S->stream>>>(
-        S->s_meta.p, S->ent_m.p, S->ent_c.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
-        env, algorithm, mode, S->ent_mask.p, S->ent_off.p, S->d_cnt);
-    S->launches++;
+    const int gm = grid_for(S, S->cap_entries, PAIR_TILE, 6);
+    if (cplx) {
+        CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_complex, 0, 4, S->stream));
+        CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_cslots, 0, 4, S->stream));
+        k_pair_masks<true><<<gm, PAIR_TILE, 0, S->stream>>>(
+            S->s_meta.p, S->ent_m.p, S->ent_c.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p,
+            S->ent_bin.p, S->bin_start.p, env, algorithm, mode, S->ent_mask.p, S->ent_cmask.p, S->ent_off.p, S->d_cnt);
+        k_cplx_collect<<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
+            S->s_meta.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p, S->ent_cmask.p, algorithm, S->ent_cbase.p,
+            S->cplx_rec.p, S->cap_complex, S->d_cnt);
+        k_cplx_narrow<<<grid_for(S, S->cap_complex, 128), 128, 0, S->stream>>>(
+            S->s_meta.p, S->s_wpos.p, S->s_wrot.p, S->s_dims.p, S->s_lrot.p, S->rot.p, env, algorithm, S->cplx_rec.p,
+            S->cap_complex, S->cap_cslots, S->cplx_n.p, S->cplx_out.p, S->ent_off.p, S->d_cnt);
+        S->launches += 3;
+    } else {
+        k_pair_masks<false><<<gm, PAIR_TILE, 0, S->stream>>>(
+            S->s_meta.p, S->ent_m.p, S->ent_c.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p,
+            S->ent_bin.p, S->bin_start.p, env, algorithm, mode, S->ent_mask.p, nullptr, S->ent_off.p, S->d_cnt);
+        S->launches++;
+    }
     CB_TRY(scan_u32(S, S->ent_off.p, S->ent_off.p, &S->d_cnt->n_intersections, S->cap_entries));
-    k_pair_store<<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
-        S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
-        env, algorithm, mode, S->ent_mask.p, S->ent_off.p, out, cap, S->d_cnt);
+    if (cplx)
+        k_pair_store<true><<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
+            S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p,
+            S->bin_start.p, env, algorithm, mode, S->ent_mask.p, S->ent_off.p, out, cap, S->ent_cmask.p,
+            S->ent_cbase.p, S->cplx_rec.p, S->cplx_n.p, S->c_src.p, S->d_cnt);
+    else
+        k_pair_store<false><<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
+            S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p,
+            S->bin_start.p, env, algorithm, mode, S->ent_mask.p, S->ent_off.p, out, cap, nullptr, nullptr, nullptr,
+            nullptr, nullptr, S->d_cnt);
     S->launches++;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;
@@ -536,7 +793,8 @@ int enqueue_pairs_only(System* S, bool want_pairs, bool want_contacts) {
         CB_TRY(enqueue_pair_pass(S, MODE_CONTACTS, S->c_shapes.p, S->cap_contacts));
         k_contact_gen<<<grid_for(S, S->cap_contacts, 256), 256, 0, S->stream>>>(
             S->s_meta.p, S->s_wpos.p, S->s_wrot.p, S->s_dims.p, S->c_shapes.p, S->set.collision_envelope, S->c_norm.p,
-            S->c_pta.p, S->c_ptb.p, S->c_depth.p, S->c_erad.p, S->c_bids.p, S->c_mats.p, S->d_cnt);
+            S->c_pta.p, S->c_ptb.p, S->c_depth.p, S->c_erad.p, S->c_bids.p, S->c_mats.p,
+            use_complex(S) ? S->c_src.p : nullptr, S->cplx_out.p, S->d_cnt);
         S->launches++;
         CB_CUDA(cudaGetLastError());
     }
