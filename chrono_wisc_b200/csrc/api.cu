@@ -426,8 +426,21 @@ int cb200_append_shapes(cb200_system* sys, int n, const int32_t* type, const uin
     CB_CUDA(cudaStreamSynchronize(st));
     S->ns = (uint32_t)ns1;
     S->meta_dirty = true;
-    for (int i = 0; i < n; i++)
-        S->n_nonsphere += type[i] != CB200_SPHERE;
+    for (int i = 0; i < n; i++) {
+        if (type[i] == CB200_SPHERE)
+            continue;
+        S->n_nonsphere++;
+        // non-sphere shapes on two different bodies: pairs without a sphere can occur (shapes of one body never pair)
+        if (S->nonsphere_bodies == 0) {
+            S->nonsphere_bodies = 1;
+            S->nonsphere_body0 = body_id[i];
+        } else if (body_id[i] != S->nonsphere_body0) {
+            S->nonsphere_bodies = 2;
+        }
+        // no analytic test against a sphere either: such pairs go to MPR, i.e. the complex path
+        if (type[i] == CB200_ELLIPSOID || type[i] == CB200_CONE || type[i] == CB200_CYLSHELL)
+            S->nonsphere_bodies = 2;
+    }
     return CB200_OK;
 }
 

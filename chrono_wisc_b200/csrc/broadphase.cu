@@ -459,11 +459,13 @@ __global__ void __launch_bounds__(256) k_bin_sort(const uint32_t* __restrict__ e
                                                   const uint64_t* __restrict__ bin_start,
                                                   const ShapeMeta* __restrict__ meta,
                                                   const double* __restrict__ s_wpos,
+                                                  const ShapeBox* __restrict__ s_box, double envelope,
                                                   uint32_t* __restrict__ ent_shape, double* __restrict__ ent_c,
                                                   ShapeMeta* __restrict__ ent_m, const DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
     const uint32_t ni = cnt->n_intersections;
+    const GridParams g = load_grid(cnt);
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < ni; e += gridDim.x * blockDim.x) {
         const uint32_t b = ent_bin[e];
         const uint32_t s = (uint32_t)bin_start[b], t = (uint32_t)bin_start[b + 1];
@@ -478,6 +480,19 @@ __global__ void __launch_bounds__(256) k_bin_sort(const uint32_t* __restrict__ e
         const uint32_t o = s + rank;
         ent_shape[o] = id;
         m.pad = id;
+        // info bits 3..5: the shape's lower corner hashes to this bin's x / y / z coordinate.  HashMin is monotone, so
+        // current_bin(A, B) (CMC/ChCollisionUtils.h:97-110), i.e. Hash(max(Amin, Bmin)) == bin, holds iff on every
+        // axis at least one of the two entries carries the flag (both lower corners hash to <= the bin coordinate).
+        {
+            double mn[3], mx[3];
+            shape_box_rel(id, m.info, s_wpos, s_box, g.origin, envelope, mn, mx);
+            const int bx = (int)(b % (uint32_t)g.bins[0]), by = (int)((b / (uint32_t)g.bins[0]) % (uint32_t)g.bins[1]),
+                      bz = (int)(b / ((uint32_t)g.bins[0] * (uint32_t)g.bins[1]));
+            const uint32_t f = ((int)floor(mn[0] * g.inv[0]) == bx ? 8u : 0u) |
+                               ((int)floor(mn[1] * g.inv[1]) == by ? 16u : 0u) |
+                               ((int)floor(mn[2] * g.inv[2]) == bz ? 32u : 0u);
+            m.info = (m.info & ~56u) | f;
+        }
         ent_m[o] = m;
         reinterpret_cast<double4*>(ent_c)[o] = w;
     }
@@ -539,8 +554,8 @@ int enqueue_bins(System* S) {
                                                  S->cap_entries, S->bin_cursor.p, S->bin_start.p, S->ent_tmp.p,
                                                  S->ent_bin.p);
     k_bin_sort<<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(S->ent_tmp.p, S->ent_bin.p, S->bin_start.p,
-                                                                        S->s_meta.p, S->s_wpos.p, S->ent_shape.p,
-                                                                        S->ent_c.p, S->ent_m.p, S->d_cnt);
+                                                                        S->s_meta.p, S->s_wpos.p, S->s_box.p, env,
+                                                                        S->ent_shape.p, S->ent_c.p, S->ent_m.p, S->d_cnt);
     S->launches += 3;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;

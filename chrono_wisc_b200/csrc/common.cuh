@@ -163,7 +163,8 @@ struct System {
     DevBuf<ShapeBox> s_box;  // ns    AABB
     DevBuf<ShapeMeta> s_meta;  // ns
     bool meta_dirty = true;    // body flags / shapes changed: rebuild s_meta
-    uint32_t n_nonsphere = 0;  // shapes that are not spheres (host count; >= 2 => multi-contact / MPR pairs possible)
+    uint32_t n_nonsphere = 0;  // shapes that are not spheres (host count)
+    uint32_t nonsphere_bodies = 0, nonsphere_body0 = 0;  // 0 / 1 / 2 (= two or more) bodies own non-sphere shapes
 
     // ---- materials: nm x nm composite table computed on the host in float (same arithmetic as the reference) ----
     int nm_smc = 0, nm_nsc = 0;
@@ -248,7 +249,7 @@ struct System {
 };
 
 // multi-contact / MPR pairs can occur: two or more non-sphere shapes, or MPR requested for everything
-inline bool use_complex(const System* S) { return S->n_nonsphere >= 2 || S->set.narrowphase_algorithm == 0; }
+inline bool use_complex(const System* S) { return S->nonsphere_bodies >= 2 || S->set.narrowphase_algorithm == 0; }
 
 // ---- shared host helpers (defined in api.cu) ----
 int timer_start(System* S, const char* name);

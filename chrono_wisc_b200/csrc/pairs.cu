@@ -23,6 +23,8 @@
 #include "mpr.cuh"
 #include "prims_multi.cuh"
 #include <limits.h>
+#include <stdio.h>
+#include <stdlib.h>
 
 namespace cb200 {
 
@@ -90,16 +92,24 @@ __device__ __forceinline__ void win_get(const Window& W, int k, Rec& R) {
 }
 
 // CMC/ChCollisionUtilsBroadphase.cpp:114-140 (a pure conjunction, so the evaluation order is free)
+// FLAGS: both records come from the bin-sorted copies, whose info bits 3..5 say "lower corner hashes to this bin's
+// x / y / z" (k_bin_sort): current_bin then is a bit test instead of three floor(max * inv).
+template <bool FLAGS>
 __device__ __forceinline__ bool pair_passes(const Rec& A, const Rec& B, const GridParams& g, uint32_t bin) {
     if (!((A.mn[0] <= B.mx[0] && B.mn[0] <= A.mx[0]) && (A.mn[1] <= B.mx[1] && B.mn[1] <= A.mx[1]) &&
           (A.mn[2] <= B.mx[2] && B.mn[2] <= A.mx[2])))
         return false;
     // current_bin (CMC/ChCollisionUtils.h:97-110): the pair belongs to the bin holding max(Amin, Bmin)
-    const int cx = (int)floor(fmax(A.mn[0], B.mn[0]) * g.inv[0]);
-    const int cy = (int)floor(fmax(A.mn[1], B.mn[1]) * g.inv[1]);
-    const int cz = (int)floor(fmax(A.mn[2], B.mn[2]) * g.inv[2]);
-    if ((uint32_t)((cz * g.bins[1]) * g.bins[0] + cy * g.bins[0] + cx) != bin)
-        return false;
+    if (FLAGS) {
+        if (((A.info | B.info) & 56u) != 56u)
+            return false;
+    } else {
+        const int cx = (int)floor(fmax(A.mn[0], B.mn[0]) * g.inv[0]);
+        const int cy = (int)floor(fmax(A.mn[1], B.mn[1]) * g.inv[1]);
+        const int cz = (int)floor(fmax(A.mn[2], B.mn[2]) * g.inv[2]);
+        if ((uint32_t)((cz * g.bins[1]) * g.bins[0] + cy * g.bins[0] + cx) != bin)
+            return false;
+    }
     if (B.body == UINT_MAX || A.body == B.body)
         return false;
     if (!(B.info & 2u))
@@ -322,12 +332,13 @@ enum { MODE_PAIRS = 0, MODE_CONTACTS = 1 };
 
 // 0: no output, 1: the pair yields one contact (or, in PAIRS mode, passes the broadphase filter),
 // 2: the pair needs the complex path (multi-contact analytic test or MPR)
+template <bool FLAGS>
 __device__ __forceinline__ int pair_decide(const Rec& A, const Rec& B, const GridParams& g, uint32_t bin, int mode,
                                            double sep, int algorithm, const double* __restrict__ s_wrot,
                                            const double* __restrict__ s_dims, uint32_t& np) {
     if (A.body == UINT_MAX || !(A.info & 2u))
         return 0;
-    if (!pair_passes(A, B, g, bin))
+    if (!pair_passes<FLAGS>(A, B, g, bin))
         return 0;
     np++;
     if (mode == MODE_PAIRS)
@@ -350,7 +361,7 @@ __global__ void __launch_bounds__(PAIR_TILE, 3) k_pair_masks(const ShapeMeta* __
                                                           int algorithm, int mode, uint64_t* __restrict__ ent_mask,
                                                           uint64_t* __restrict__ ent_cmask,
                                                           uint32_t* __restrict__ ent_cnt,
-                                                          DevCounters* __restrict__ cnt) {
+                                                          DevCounters* __restrict__ cnt, int dbg) {
     __shared__ Window W;
     __shared__ unsigned long long smask[WIN];
     __shared__ unsigned long long scmask[CPLX ? WIN : 1];
@@ -408,38 +419,117 @@ __global__ void __launch_bounds__(PAIR_TILE, 3) k_pair_masks(const ShapeMeta* __
             }
             const uint32_t w0 = s - e0;  // window index of the bin's first entry
             if (k <= 64) {
+                // rows in registers: lane l owns entry i = rb + l and meets its partners j = i + d (mod k),
+                // d = 1..(k-1)/2 (+ half a diagonal when k is even) -- every unordered pair exactly once, the
+                // partner read is one conflict-free shared-memory access per lane.  In a bin of spheres only
+                // (the bulk of a granular bed) the partner's AABB is recomputed from (centre, radius) -- the very
+                // operations that produced the stored one -- instead of being loaded: FP64 adds are cheaper than
+                // 64-bit shared loads here.
+                bool nonsphere = false;
+                for (uint32_t t = lane; t < k; t += 32)
+                    nonsphere |= ((W.info[w0 + t] >> 8) & 0xff) != CB200_SPHERE;
+                const bool fast = !__any_sync(0xffffffffu, nonsphere) && algorithm != 0;
                 const uint32_t h = (k - 1) >> 1;
-                const uint32_t full = k * h;
-                const uint32_t total = full + ((k & 1u) ? 0u : (k >> 1));
-                const uint32_t M = ((1u << 20) + k - 1) / k;  // p / k == (p * M) >> 20 for p < 2048, k <= 64
-                for (uint32_t p0 = 0; p0 < total; p0 += 32) {
-                    const uint32_t p = p0 + lane;
-                    if (p < total) {
-                        uint32_t i, j;
-                        if (p < full) {
-                            const uint32_t d = (p * M) >> 20;
-                            i = p - d * k;
-                            j = i + d + 1;
-                            if (j >= k)
-                                j -= k;
-                        } else {
-                            i = p - full;
-                            j = i + (k >> 1);
-                        }
-                        const uint32_t a = min(i, j), c = max(i, j);
-                        Rec A, B;
-                        win_get(W, (int)(w0 + a), A);
-                        win_get(W, (int)(w0 + c), B);
-                        const int dec = pair_decide(A, B, g, b, mode, sep, algorithm, s_wrot, s_dims, np);
-                        if (dec == 1)
-                            atomicOr(&smask[w0 + a], 1ull << c);
-                        else if (dec == 2) {
-                            if (CPLX)
-                                atomicOr(&scmask[w0 + a], 1ull << c);
-                            else
-                                ncx++;
+                const uint32_t nd = h + ((k & 1u) ? 0u : 1u);
+                if (!fast) {
+                    // a bin with a non-sphere in it (walls, mixed beds): pairs spread evenly over the lanes,
+                    // both records from the window, ordered (lower entry, higher entry) for the shape functions
+                    const uint32_t full = k * h;
+                    const uint32_t total = full + ((k & 1u) ? 0u : (k >> 1));
+                    const uint32_t M = ((1u << 20) + k - 1) / k;  // p / k == (p * M) >> 20 for p < 2048, k <= 64
+                    for (uint32_t p0 = 0; p0 < total; p0 += 32) {
+                        const uint32_t p = p0 + lane;
+                        if (p < total) {
+                            uint32_t i, j;
+                            if (p < full) {
+                                const uint32_t d = (p * M) >> 20;
+                                i = p - d * k;
+                                j = i + d + 1;
+                                if (j >= k)
+                                    j -= k;
+                            } else {
+                                i = p - full;
+                                j = i + (k >> 1);
+                            }
+                            const uint32_t a = min(i, j), c = max(i, j);
+                            Rec A, B;
+                            win_get(W, (int)(w0 + a), A);
+                            win_get(W, (int)(w0 + c), B);
+                            const int dec = pair_decide<true>(A, B, g, b, mode, sep, algorithm, s_wrot, s_dims, np);
+                            if (dec == 1)
+                                atomicOr(&smask[w0 + a], 1ull << c);
+                            else if (dec == 2) {
+                                if (CPLX)
+                                    atomicOr(&scmask[w0 + a], 1ull << c);
+                                else
+                                    ncx++;
+                            }
                         }
                     }
+                } else
+                for (uint32_t rb = 0; rb < k; rb += 32) {
+                    const uint32_t i = rb + lane;
+                    const bool vi = i < k;
+                    Rec A;
+                    if (vi)
+                        win_get(W, (int)(w0 + i), A);
+                    const bool a_ok = vi && A.body != UINT_MAX && (A.info & 2u);
+                    unsigned long long mym = 0ull, mycm = 0ull;
+                    for (uint32_t d = 1; d <= nd; d++) {
+                        uint32_t j = i + d;
+                        if (d > h) {  // the half diagonal of an even k
+                            if (i >= (k >> 1))
+                                continue;
+                        } else if (j >= k) {
+                            j -= k;
+                        }
+                        if (!a_ok)
+                            continue;
+                        const int wj = (int)(w0 + j);
+                        int dec;
+                        {
+                            Rec B;
+                            B.cx = W.c[0][wj], B.cy = W.c[1][wj], B.cz = W.c[2][wj], B.r = W.c[3][wj];
+                            B.body = W.body[wj], B.fam = W.fam[wj], B.info = W.info[wj];
+                            const double rr = B.r + envelope;
+                            B.mn[0] = (B.cx - rr) - g.origin[0], B.mn[1] = (B.cy - rr) - g.origin[1];
+                            B.mn[2] = (B.cz - rr) - g.origin[2];
+                            B.mx[0] = (B.cx + rr) - g.origin[0], B.mx[1] = (B.cy + rr) - g.origin[1];
+                            B.mx[2] = (B.cz + rr) - g.origin[2];
+                            dec = 0;
+                            if (pair_passes<true>(A, B, g, b)) {
+                                np++;
+                                dec = 1;
+                                if (mode == MODE_CONTACTS) {
+                                    // the deciding lines of sphere_sphere, ChNarrowphasePRIMS.cpp:52-60
+                                    // (symmetric in the two shapes bit for bit)
+                                    const d3 delta = mk3(B.cx, B.cy, B.cz) - mk3(A.cx, A.cy, A.cz);
+                                    const double dist2 = dot3(delta, delta);
+                                    const double radSum_s = (A.r + B.r) + sep;
+                                    dec = !(dist2 >= radSum_s * radSum_s || dist2 < 1e-12);
+                                }
+                            }
+                        }
+                        if (dec == 1) {
+                            if (j > i)
+                                mym |= 1ull << j;
+                            else
+                                atomicOr(&smask[wj], 1ull << i);
+                        } else if (dec == 2) {
+                            if (CPLX) {
+                                if (j > i)
+                                    mycm |= 1ull << j;
+                                else
+                                    atomicOr(&scmask[wj], 1ull << i);
+                            } else {
+                                ncx++;
+                            }
+                        }
+                    }
+                    if (mym)
+                        atomicOr(&smask[w0 + i], mym);
+                    if (CPLX && mycm)
+                        atomicOr(&scmask[w0 + i], mycm);
                 }
                 __syncwarp();
                 for (uint32_t t = lane; t < k; t += 32) {
@@ -464,7 +554,7 @@ __global__ void __launch_bounds__(PAIR_TILE, 3) k_pair_masks(const ShapeMeta* __
                             win_get(W, (int)(w0 + j), B);
                         else
                             load_rec(B, ent_shape[s + j], meta, s_wpos, s_box, g.origin, envelope);
-                        const int dec = pair_decide(A, B, g, b, mode, sep, algorithm, s_wrot, s_dims, np);
+                        const int dec = pair_decide<false>(A, B, g, b, mode, sep, algorithm, s_wrot, s_dims, np);
                         hits += dec == 1 ? 1u : 0u;
                         ncx += dec == 2 ? 1u : 0u;  // long bins have no complex path
                     }
@@ -680,7 +770,7 @@ __global__ void __launch_bounds__(256) k_pair_store(const ShapeMeta* __restrict_
             for (uint32_t j = e + 1; j < s + k; j++) {
                 Rec B;
                 load_rec(B, ent_shape[j], meta, s_wpos, s_box, g.origin, envelope);
-                if (pair_decide(A, B, g, bin, mode, 2 * envelope, algorithm, s_wrot, s_dims, np) == 1) {
+                if (pair_decide<false>(A, B, g, bin, mode, 2 * envelope, algorithm, s_wrot, s_dims, np) == 1) {
                     if (CPLX && mode == MODE_CONTACTS)
                         c_src[o] = 0;
                     out[o++] = hiA | (int64_t)B.id;
