@@ -361,7 +361,7 @@ __global__ void __launch_bounds__(PAIR_TILE, 3) k_pair_masks(const ShapeMeta* __
                                                           int algorithm, int mode, uint64_t* __restrict__ ent_mask,
                                                           uint64_t* __restrict__ ent_cmask,
                                                           uint32_t* __restrict__ ent_cnt,
-                                                          DevCounters* __restrict__ cnt, int dbg) {
+                                                          DevCounters* __restrict__ cnt) {
     __shared__ Window W;
     __shared__ unsigned long long smask[WIN];
     __shared__ unsigned long long scmask[CPLX ? WIN : 1];
