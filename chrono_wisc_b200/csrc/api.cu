@@ -17,6 +17,8 @@ int set_error(int code, const std::string& msg) {
 // Timers never block the stream: every start/stop records into a pool of event pairs, and the pairs are
 // resolved in one go (flush_timers) at the end of cb200_do_steps or when the pool holds 64 intervals.
 int timer_start(System* S, const char* name) {
+    if (S->capturing)
+        return CB200_OK;
     Timer& t = S->timers[name];
     if (t.used == t.pool.size()) {
         cudaEvent_t a, b;
@@ -29,12 +31,15 @@ int timer_start(System* S, const char* name) {
     return CB200_OK;
 }
 
-int timer_stop(System* S, const char* name) {
+int timer_stop(System* S, const char* name, int steps) {
+    if (S->capturing)
+        return CB200_OK;
     Timer& t = S->timers[name];
     if (!t.armed)
         return CB200_OK;
     CB_CUDA(cudaEventRecord(t.pool[t.used].second, S->stream));
     t.used++;
+    t.steps += steps;
     t.armed = false;
     return CB200_OK;
 }
@@ -297,6 +302,8 @@ void cb200_destroy(cb200_system* sys) {
     REL(ct_force); REL(ct_torque); REL(b_deg); REL(b_cursor); REL(b_inc); REL(b_force); REL(heavy_list);
     REL(heavy_part); REL(n_frame); REL(n_aux); REL(gamma); REL(n_gamma_hat); REL(n_y); REL(n_gn); REL(n_g); REL(n_rfull);
     REL(n_w); REL(n_w0); REL(n_mk); REL(n_part); REL(n_hist); REL(n_rows);
+    if (S->step_graph)
+        cudaGraphExecDestroy(S->step_graph);
     if (S->n_ctl)
         cudaFree(S->n_ctl);
     REL(scan_tmp);
@@ -637,6 +644,34 @@ static int enqueue_one_step(System* S) {
     return CB200_OK;
 }
 
+// One step captured into an executable graph (stage timers are skipped while capturing; every allocation a step can
+// need was made by the directly enqueued step before it).
+static int capture_step_graph(System* S) {
+    cudaGraph_t g = nullptr;
+    const int64_t l0 = S->launches;
+    CB_CUDA(cudaStreamBeginCapture(S->stream, cudaStreamCaptureModeThreadLocal));
+    S->capturing = true;
+    const int rc = enqueue_one_step(S);
+    S->capturing = false;
+    const cudaError_t e = cudaStreamEndCapture(S->stream, &g);
+    S->step_graph_launches = (int)(S->launches - l0);
+    S->launches = l0;
+    if (rc != CB200_OK) {
+        if (g)
+            cudaGraphDestroy(g);
+        return rc;
+    }
+    if (e != cudaSuccess)
+        return set_error(CB200_ERR_CUDA, std::string("cudaStreamEndCapture: ") + cudaGetErrorString(e));
+    const cudaError_t e2 = cudaGraphInstantiate(&S->step_graph, g, 0);
+    cudaGraphDestroy(g);
+    if (e2 != cudaSuccess) {
+        S->step_graph = nullptr;
+        return set_error(CB200_ERR_CUDA, std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e2));
+    }
+    return CB200_OK;
+}
+
 // ChSystem::DoStepDynamics x nsteps.  Steps are enqueued back to back with no host synchronisation in between
 // (all extents live on the device); the host syncs once per chunk of 64 steps to resolve timers and to find out
 // whether a capacity was exceeded, in which case the steps that did not run (the device counts them) are redone.
@@ -647,22 +682,46 @@ int cb200_do_steps(cb200_system* sys, int nsteps) {
     CB_CUDA(cudaSetDevice(S->device));
     if (S->nb == 0)
         return CB200_OK;
-    for (auto& kv : S->timers)
+    for (auto& kv : S->timers) {
         kv.second.total_ms = 0;
+        kv.second.steps = 0;
+    }
     S->timed_steps = nsteps;
     CB_TRY(ensure_capacity(S));
     int remaining = nsteps, stalls = 0;
+    // Launch-bound inner loop: with every extent on the device a step is the same launch sequence each time, so
+    // after one directly enqueued step (which also samples the stage timers) the rest of a chunk replays a CUDA
+    // graph of that step.  The graph is rebuilt per call and after every capacity growth (pointers change).
+    const bool use_graph = S->set.system_type == 1 && nsteps >= 8 && !S->slab_on && !getenv("CB200_NO_GRAPH");
+    if (S->step_graph) {
+        cudaGraphExecDestroy(S->step_graph);
+        S->step_graph = nullptr;
+    }
     while (remaining > 0) {
         const int chunk = remaining < 64 ? remaining : 64;
         CB_TRY(timer_start(S, "do_steps"));
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->steps_done, 0, 4, S->stream));
-        for (int s = 0; s < chunk; s++)
-            CB_TRY(enqueue_one_step(S));
-        CB_TRY(timer_stop(S, "do_steps"));
+        CB_TRY(enqueue_one_step(S));
+        if (use_graph && chunk > 1 && !S->step_graph)
+            CB_TRY(capture_step_graph(S));
+        for (int s = 1; s < chunk; s++) {
+            if (S->step_graph) {
+                CB_CUDA(cudaGraphLaunch(S->step_graph, S->stream));
+                S->launches += S->step_graph_launches;
+            } else {
+                CB_TRY(enqueue_one_step(S));
+            }
+        }
+        CB_TRY(timer_stop(S, "do_steps", 0));
         CB_TRY(flush_timers(S));
         CB_TRY(fetch_counters(S));
         const int done = (int)S->h_cnt->steps_done;
+        S->timers["do_steps"].steps += done;
         remaining -= done;
+        if (S->h_cnt->overflow && S->step_graph) {
+            cudaGraphExecDestroy(S->step_graph);
+            S->step_graph = nullptr;
+        }
         if (S->h_cnt->overflow) {
             CB_TRY(grow_after_overflow(S));
             if (++stalls > 16 && done == 0)
@@ -716,7 +775,7 @@ int cb200_reset_timers(cb200_system* sys) {
         return set_error(CB200_ERR_ARG, "null system");
     CB_TRY(flush_timers(S));
     for (auto& kv : S->timers)
-        kv.second.total_ms = 0;
+        kv.second.total_ms = 0, kv.second.steps = 0;
     S->timed_steps = 0;
     return CB200_OK;
 }
@@ -955,7 +1014,7 @@ int cb200_get_timer(cb200_system* sys, const char* name, double* seconds) {
     auto it = S->timers.find(name);
     if (it == S->timers.end())
         return set_error(CB200_ERR_ARG, std::string("unknown timer '") + name + "'");
-    *seconds = it->second.total_ms * 1e-3 / (S->timed_steps > 0 ? S->timed_steps : 1);
+    *seconds = it->second.total_ms * 1e-3 / (it->second.steps > 0 ? it->second.steps : 1);
     return CB200_OK;
 }
 

@@ -122,6 +122,7 @@ struct Timer {
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pool;  // event pairs, resolved lazily by flush_timers
     size_t used = 0;
     double total_ms = 0;
+    long steps = 0;  // simulation steps the accumulated intervals cover
     bool armed = false;
 };
 
@@ -246,6 +247,9 @@ struct System {
 
     std::map<std::string, Timer> timers;
     int timed_steps = 0;
+    bool capturing = false;          // a step is being captured into a CUDA graph: timers are skipped
+    cudaGraphExec_t step_graph = nullptr;
+    int step_graph_launches = 0;     // kernel / memset nodes of one captured step
 };
 
 // multi-contact / MPR pairs can occur: two or more non-sphere shapes, or MPR requested for everything
@@ -253,7 +257,7 @@ inline bool use_complex(const System* S) { return S->nonsphere_bodies >= 2 || S-
 
 // ---- shared host helpers (defined in api.cu) ----
 int timer_start(System* S, const char* name);
-int timer_stop(System* S, const char* name);
+int timer_stop(System* S, const char* name, int steps = 1);
 int flush_timers(System* S);
 int fetch_counters(System* S);       // D2H of DevCounters + stream sync
 int ensure_capacity(System* S);      // first-use allocation of every capacity-bound array
