@@ -121,6 +121,42 @@ def algorithmic_bytes(nb, c):
             c.num_rigid_contacts * 192 + nb * 96)
 
 
+KERNEL_TIMERS = ("k_pair_masks", "k_smc_force", "k_body_reduce", "k_contact_gen", "k_pair_store", "k_bin_sort")
+
+
+def kernel_rooflines(sys_, nb, c, peak):
+    """Per-kernel roofline entries for the heaviest kernels: live CUDA-event durations (events around the launch, on
+    the library stream, in the directly enqueued steps of the timed region) against each kernel's own share of the
+    SURVEY.md 8(d) algorithmic bytes.  `traffic` = DRAM bytes per launch from the committed
+    ncu --set full capture (profiles/r1_traffic.json), when the capture holds that kernel."""
+    ni, np_, nc = c.num_bin_aabb_intersections, c.num_possible_collisions, c.num_rigid_contacts
+    alg = {
+        "k_pair_masks": ni * 16 + np_ * 16,          # entries read; the pair list it decides but never materialises
+        "k_smc_force": nc * (96 + 2 * 112 + 72),     # contact record + two body states in, force/torques out
+        "k_body_reduce": nb * 96 + nc * 2 * 56,      # per-body accumulators + (index, force, torque) per incidence
+        "k_contact_gen": nc * (8 + 96),              # key in, contact record out
+        "k_pair_store": ni * 16 + nc * 8,            # masks + offsets in, keys out
+        "k_bin_sort": ni * 16,                       # (bin, shape) key/value moved once
+    }
+    traffic = {}
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")) as f:
+            traffic = json.load(f).get("dram_bytes_per_launch", {})
+    except Exception:
+        pass
+    out = {}
+    for k in KERNEL_TIMERS:
+        try:
+            ms = sys_.GetTimer(k) * 1e3
+        except Exception:
+            continue
+        if ms <= 0:
+            continue
+        a = alg[k] / (ms * 1e-3) / 1e9
+        out[k] = {"ms": ms, "algorithmic_bytes": alg[k], "achieved": a, "frac": a / peak, "traffic": traffic.get(k)}
+    return out
+
+
 def cpu_baseline_sample(scene, seconds_budget=20.0):
     """Oracle ("port": oracle/liboracle.so, OpenMP over the host cores) on a bounded sample: the same bed state,
     as many whole steps as fit the budget (at least 1)."""
@@ -288,10 +324,20 @@ def run_b200(args):
             "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": nb * 13 * 8,
                     "d2h_bytes_per_step": nb * 13 * 8, "steps": n_e2e},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_kind": peak_kind, "kernel": "whole step (all kernels)",
-                         "algorithmic_bytes_per_step": bytes_step},
+            "roofline_step": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                              "frac": achieved / peak, "peak_kind": peak_kind, "kernel": "whole step (all kernels)",
+                              "algorithmic_bytes_per_step": bytes_step},
         }
+        kr = kernel_rooflines(sys_, nb, counts, peak)
+        line["kernels"] = kr
+        if kr:
+            dom = max(kr, key=lambda k: kr[k]["ms"])
+            line["roofline"] = {"bound": "hbm", "achieved": kr[dom]["achieved"], "peak": peak, "unit": "GB/s",
+                                "frac": kr[dom]["frac"], "traffic": kr[dom]["traffic"], "peak_kind": peak_kind,
+                                "kernel": dom, "ms_per_launch": kr[dom]["ms"],
+                                "algorithmic_bytes_per_launch": kr[dom]["algorithmic_bytes"]}
+        else:
+            line["roofline"] = dict(line["roofline_step"], traffic=None)
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline_sample(dict(scene, pos=p0, rot=q0, vel=v0), args.cpu_seconds)
         print(json.dumps(line))
@@ -316,6 +362,7 @@ def run_b200_slabs(args, rank, world, local, barrier):
     layout = slab.SlabLayout(world, rank, cuts, axis=0, width=width)
     n_owned0 = gids.size
     sys_ = slab.SlabSystemSMC(layout, device=local, exchange=slab.DistExchange(layout), ghost_cap=ghost_cap,
+                              own_stream=True,
                               owned_cap=int(n_owned0 * 1.1) + 4096)
     nb_static = 1
     ns_static = int((scene["shape_body"] < nb_static).sum())
@@ -333,9 +380,9 @@ def run_b200_slabs(args, rank, world, local, barrier):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     t0 = time.perf_counter()
-    e0.record()
+    e0.record(sys_.stream)
     sys_.DoSteps(args.steps)
-    e1.record()
+    e1.record(sys_.stream)
     torch.cuda.synchronize()
     barrier()
     wall = time.perf_counter() - t0

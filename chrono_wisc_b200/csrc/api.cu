@@ -58,6 +58,14 @@ int flush_timers(System* S) {
     return CB200_OK;
 }
 
+void invalidate_step_graph(System* S) {
+    if (S->step_graph) {
+        cudaGraphExecDestroy(S->step_graph);
+        S->step_graph = nullptr;
+    }
+    S->direct_steps = 0;
+}
+
 int fetch_counters(System* S) {
     CB_CUDA(cudaMemcpyAsync(S->h_cnt, S->d_cnt, sizeof(DevCounters), cudaMemcpyDeviceToHost, S->stream));
     CB_CUDA(cudaStreamSynchronize(S->stream));
@@ -79,12 +87,14 @@ static int download(System* S, const T* dev, T* dst, size_t n) {
 
 // ---- capacities -------------------------------------------------------------------------------------------
 static int alloc_bins(System* S, uint32_t n) {
+    invalidate_step_graph(S);
     CB_TRY(S->bin_start.reserve((size_t)n + 2));
     CB_TRY(S->bin_cursor.reserve((size_t)n + 1));
     S->cap_bins = (uint32_t)std::min<size_t>(S->bin_cursor.cap - 1, S->bin_start.cap - 2);
     return CB200_OK;
 }
 static int alloc_entries(System* S, uint32_t n) {
+    invalidate_step_graph(S);
     CB_TRY(S->ent_tmp.reserve(n));
     CB_TRY(S->ent_bin.reserve(n));
     CB_TRY(S->ent_shape.reserve(n));
@@ -100,6 +110,7 @@ static int alloc_entries(System* S, uint32_t n) {
     return CB200_OK;
 }
 static int alloc_contacts(System* S, uint32_t n) {
+    invalidate_step_graph(S);
     CB_TRY(S->c_depth.reserve(n));
     const size_t c = S->c_depth.cap;
     CB_TRY(S->c_norm.reserve(3 * c));
@@ -119,6 +130,7 @@ static int alloc_contacts(System* S, uint32_t n) {
     return CB200_OK;
 }
 static int alloc_complex(System* S, uint32_t nrec, uint32_t nslots) {
+    invalidate_step_graph(S);
     if (nslots < 2 * nrec)
         nslots = 2 * nrec;
     CB_TRY(S->cplx_rec.reserve(4 * (size_t)nrec));
@@ -129,6 +141,7 @@ static int alloc_complex(System* S, uint32_t nrec, uint32_t nslots) {
     return CB200_OK;
 }
 static int alloc_pairs(System* S, uint32_t n) {
+    invalidate_step_graph(S);
     CB_TRY(S->pairs.reserve(n));
     S->cap_pairs = (uint32_t)S->pairs.cap;
     return CB200_OK;
@@ -326,6 +339,13 @@ int cb200_set_settings(cb200_system* sys, const cb200_settings* s) {
     System* S = SYS(sys);
     if (!S || !s)
         return set_error(CB200_ERR_ARG, "null argument");
+    {
+        cb200_settings eff = *s;
+        if (eff.system_type == 1)
+            eff.collision_envelope = 0;
+        if (memcmp(&eff, &S->set, sizeof(eff)) != 0)
+            invalidate_step_graph(S);  // captured launches carry the settings by value
+    }
     if (!(s->step_size > 0))
         return set_error(CB200_ERR_ARG, "step_size must be positive");
     if (s->broadphase_grid < 0 || s->broadphase_grid > 2)
@@ -342,6 +362,8 @@ int cb200_set_settings(cb200_system* sys, const cb200_settings* s) {
 int cb200_append_bodies(cb200_system* sys, int n, const double* mass, const double* inertia_xx,
                         const double* inv_inertia_xx, const char* active, const char* collide, int* first) {
     System* S = SYS(sys);
+    if (S)
+        invalidate_step_graph(S);
     if (!S || n < 0 || !mass || !inertia_xx)
         return set_error(CB200_ERR_ARG, "bad argument to cb200_append_bodies");
     CB_CUDA(cudaSetDevice(S->device));
@@ -386,6 +408,8 @@ int cb200_append_shapes(cb200_system* sys, int n, const int32_t* type, const uin
                         const double* pos_local, const double* rot_local, const double* dims,
                         const int32_t* material_id) {
     System* S = SYS(sys);
+    if (S)
+        invalidate_step_graph(S);
     if (!S || n < 0 || !type || !body_id || !fam || !pos_local || !rot_local || !dims)
         return set_error(CB200_ERR_ARG, "bad argument to cb200_append_shapes");
     CB_CUDA(cudaSetDevice(S->device));
@@ -456,6 +480,8 @@ int cb200_append_shapes(cb200_system* sys, int n, const int32_t* type, const uin
 // (src/chrono/physics/ChContactMaterial.h:157-169).
 int cb200_set_materials_smc(cb200_system* sys, int n, const float* t) {
     System* S = SYS(sys);
+    if (S)
+        invalidate_step_graph(S);
     if (!S || n <= 0 || !t)
         return set_error(CB200_ERR_ARG, "bad argument to cb200_set_materials_smc");
     if (n > 1024)
@@ -503,6 +529,8 @@ int cb200_set_materials_smc(cb200_system* sys, int n, const float* t) {
 // min, compliances by sum; 8 doubles: mu, mu_roll, mu_spin, cohesion, compliance, complianceT, cRoll, cSpin.
 int cb200_set_materials_nsc(cb200_system* sys, int n, const float* t) {
     System* S = SYS(sys);
+    if (S)
+        invalidate_step_graph(S);
     if (!S || n <= 0 || !t)
         return set_error(CB200_ERR_ARG, "bad argument to cb200_set_materials_nsc");
     if (n > 1024)
@@ -550,6 +578,8 @@ int cb200_upload_state(cb200_system* sys, int first, int n, const double* pos, c
 
 int cb200_upload_applied_forces(cb200_system* sys, int first, int n, const double* ft) {
     System* S = SYS(sys);
+    if (S)
+        invalidate_step_graph(S);
     if (!S || first < 0 || n < 0 || (uint32_t)(first + n) > S->nb)
         return set_error(CB200_ERR_ARG, "body range out of bounds");
     CB_CUDA(cudaSetDevice(S->device));
@@ -563,6 +593,8 @@ int cb200_upload_applied_forces(cb200_system* sys, int first, int n, const doubl
 
 int cb200_set_body_flags(cb200_system* sys, int first, int n, const char* active, const char* collide) {
     System* S = SYS(sys);
+    if (S)
+        invalidate_step_graph(S);
     if (!S || first < 0 || n < 0 || (uint32_t)(first + n) > S->nb || !active || !collide)
         return set_error(CB200_ERR_ARG, "bad argument to cb200_set_body_flags");
     CB_CUDA(cudaSetDevice(S->device));
@@ -649,6 +681,8 @@ static int enqueue_one_step(System* S) {
 static int capture_step_graph(System* S) {
     cudaGraph_t g = nullptr;
     const int64_t l0 = S->launches;
+    invalidate_step_graph(S);
+    S->step_graph_meta = S->meta_dirty;
     CB_CUDA(cudaStreamBeginCapture(S->stream, cudaStreamCaptureModeThreadLocal));
     S->capturing = true;
     const int rc = enqueue_one_step(S);
@@ -672,6 +706,29 @@ static int capture_step_graph(System* S) {
     return CB200_OK;
 }
 
+// the legacy / per-thread default streams cannot be captured
+static bool graph_capable(const System* S) {
+    return S->stream != nullptr && S->stream != cudaStreamLegacy && S->stream != cudaStreamPerThread &&
+           !getenv("CB200_NO_GRAPH");
+}
+
+// A step through the cached graph (captured once a directly enqueued step has made every lazy allocation).
+static int replay_or_enqueue_step(System* S) {
+    if (S->direct_steps < 1) {
+        S->direct_steps++;
+        return enqueue_one_step(S);
+    }
+    if (!S->step_graph || (S->meta_dirty && !S->step_graph_meta))
+        CB_TRY(capture_step_graph(S));
+    CB_CUDA(cudaGraphLaunch(S->step_graph, S->stream));
+    S->launches += S->step_graph_launches;
+    if (S->step_graph_meta)
+        S->meta_dirty = false;
+    S->pairs_valid = false;
+    S->box_relative = true;
+    return CB200_OK;
+}
+
 // ChSystem::DoStepDynamics x nsteps.  Steps are enqueued back to back with no host synchronisation in between
 // (all extents live on the device); the host syncs once per chunk of 64 steps to resolve timers and to find out
 // whether a capacity was exceeded, in which case the steps that did not run (the device counts them) are redone.
@@ -692,36 +749,23 @@ int cb200_do_steps(cb200_system* sys, int nsteps) {
     // Launch-bound inner loop: with every extent on the device a step is the same launch sequence each time, so
     // after one directly enqueued step (which also samples the stage timers) the rest of a chunk replays a CUDA
     // graph of that step.  The graph is rebuilt per call and after every capacity growth (pointers change).
-    const bool use_graph = S->set.system_type == 1 && nsteps >= 8 && !S->slab_on && !getenv("CB200_NO_GRAPH");
-    if (S->step_graph) {
-        cudaGraphExecDestroy(S->step_graph);
-        S->step_graph = nullptr;
-    }
+    const bool use_graph = S->set.system_type == 1 && nsteps >= 8 && graph_capable(S);
     while (remaining > 0) {
         const int chunk = remaining < 64 ? remaining : 64;
         CB_TRY(timer_start(S, "do_steps"));
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->steps_done, 0, 4, S->stream));
         CB_TRY(enqueue_one_step(S));
-        if (use_graph && chunk > 1 && !S->step_graph)
-            CB_TRY(capture_step_graph(S));
-        for (int s = 1; s < chunk; s++) {
-            if (S->step_graph) {
-                CB_CUDA(cudaGraphLaunch(S->step_graph, S->stream));
-                S->launches += S->step_graph_launches;
-            } else {
-                CB_TRY(enqueue_one_step(S));
-            }
-        }
+        S->direct_steps++;
+        for (int s = 1; s < chunk; s++)
+            CB_TRY(use_graph ? replay_or_enqueue_step(S) : enqueue_one_step(S));
         CB_TRY(timer_stop(S, "do_steps", 0));
         CB_TRY(flush_timers(S));
         CB_TRY(fetch_counters(S));
         const int done = (int)S->h_cnt->steps_done;
         S->timers["do_steps"].steps += done;
         remaining -= done;
-        if (S->h_cnt->overflow && S->step_graph) {
-            cudaGraphExecDestroy(S->step_graph);
-            S->step_graph = nullptr;
-        }
+        if (S->h_cnt->overflow)
+            invalidate_step_graph(S);
         if (S->h_cnt->overflow) {
             CB_TRY(grow_after_overflow(S));
             if (++stalls > 16 && done == 0)
@@ -748,8 +792,17 @@ int cb200_enqueue_steps(cb200_system* sys, int nsteps) {
         return CB200_OK;
     CB_TRY(ensure_capacity(S));
     S->timed_steps += nsteps;
-    for (int s = 0; s < nsteps; s++)
-        CB_TRY(enqueue_one_step(S));
+    // the first step of a call is enqueued directly (it samples the stage timers), the others replay the graph;
+    // single-step callers (slab stepping) sample one step in 16
+    const bool use_graph = S->set.system_type == 1 && graph_capable(S);
+    for (int s = 0; s < nsteps; s++) {
+        if (use_graph && (s > 0 || (S->async_calls++ & 15)))
+            CB_TRY(replay_or_enqueue_step(S));
+        else {
+            CB_TRY(enqueue_one_step(S));
+            S->direct_steps++;
+        }
+    }
     return CB200_OK;
 }
 
@@ -782,6 +835,8 @@ int cb200_reset_timers(cb200_system* sys) {
 
 int cb200_set_stream(cb200_system* sys, void* cuda_stream, int use_own) {
     System* S = SYS(sys);
+    if (S)
+        invalidate_step_graph(S);
     if (!S)
         return set_error(CB200_ERR_ARG, "null system");
     CB_CUDA(cudaSetDevice(S->device));

@@ -553,9 +553,11 @@ int enqueue_bins(System* S) {
     k_bin_large<true><<<S->num_sms * 4, 256, 0, S->stream>>>(S->s_meta.p, S->s_wpos.p, S->s_box.p, env, S->large_list.p, S->d_cnt,
                                                  S->cap_entries, S->bin_cursor.p, S->bin_start.p, S->ent_tmp.p,
                                                  S->ent_bin.p);
+    CB_TRY(timer_start(S, "k_bin_sort"));
     k_bin_sort<<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(S->ent_tmp.p, S->ent_bin.p, S->bin_start.p,
                                                                         S->s_meta.p, S->s_wpos.p, S->s_box.p, env,
                                                                         S->ent_shape.p, S->ent_c.p, S->ent_m.p, S->d_cnt);
+    CB_TRY(timer_stop(S, "k_bin_sort"));
     S->launches += 3;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;

@@ -250,6 +250,9 @@ struct System {
     bool capturing = false;          // a step is being captured into a CUDA graph: timers are skipped
     cudaGraphExec_t step_graph = nullptr;
     int step_graph_launches = 0;     // kernel / memset nodes of one captured step
+    bool step_graph_meta = false;    // the captured step rebuilds the per-shape records (meta_dirty at capture)
+    int direct_steps = 0;            // steps enqueued directly since the graph was last invalidated
+    unsigned async_calls = 0;
 };
 
 // multi-contact / MPR pairs can occur: two or more non-sphere shapes, or MPR requested for everything
@@ -259,6 +262,7 @@ inline bool use_complex(const System* S) { return S->nonsphere_bodies >= 2 || S-
 int timer_start(System* S, const char* name);
 int timer_stop(System* S, const char* name, int steps = 1);
 int flush_timers(System* S);
+void invalidate_step_graph(System* S);  // any change to what a step's launches capture (pointers, sizes, settings)
 int fetch_counters(System* S);       // D2H of DevCounters + stream sync
 int ensure_capacity(System* S);      // first-use allocation of every capacity-bound array
 int grow_after_overflow(System* S);  // reads h_cnt->need_*, grows, clears the device overflow mask

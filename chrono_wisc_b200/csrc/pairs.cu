@@ -837,12 +837,14 @@ static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
     if (mode == MODE_CONTACTS)
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_pairs, 0, 4, S->stream));
     const int gm = grid_for(S, S->cap_entries, PAIR_TILE, 6);
+    CB_TRY(timer_start(S, "k_pair_masks"));
     if (cplx) {
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_complex, 0, 4, S->stream));
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_cslots, 0, 4, S->stream));
         k_pair_masks<true><<<gm, PAIR_TILE, 0, S->stream>>>(
             S->s_meta.p, S->ent_m.p, S->ent_c.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p,
             S->ent_bin.p, S->bin_start.p, env, algorithm, mode, S->ent_mask.p, S->ent_cmask.p, S->ent_off.p, S->d_cnt);
+        CB_TRY(timer_stop(S, "k_pair_masks"));
         k_cplx_collect<<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
             S->s_meta.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p, S->ent_cmask.p, algorithm, S->ent_cbase.p,
             S->cplx_rec.p, S->cap_complex, S->d_cnt);
@@ -854,9 +856,11 @@ static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
         k_pair_masks<false><<<gm, PAIR_TILE, 0, S->stream>>>(
             S->s_meta.p, S->ent_m.p, S->ent_c.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p,
             S->ent_bin.p, S->bin_start.p, env, algorithm, mode, S->ent_mask.p, nullptr, S->ent_off.p, S->d_cnt);
+        CB_TRY(timer_stop(S, "k_pair_masks"));
         S->launches++;
     }
     CB_TRY(scan_u32(S, S->ent_off.p, S->ent_off.p, &S->d_cnt->n_intersections, S->cap_entries));
+    CB_TRY(timer_start(S, "k_pair_store"));
     if (cplx)
         k_pair_store<true><<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
             S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p,
@@ -867,6 +871,7 @@ static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
             S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p,
             S->bin_start.p, env, algorithm, mode, S->ent_mask.p, S->ent_off.p, out, cap, nullptr, nullptr, nullptr,
             nullptr, nullptr, S->d_cnt);
+    CB_TRY(timer_stop(S, "k_pair_store"));
     S->launches++;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;
@@ -881,10 +886,12 @@ int enqueue_pairs_only(System* S, bool want_pairs, bool want_contacts) {
     }
     if (want_contacts) {
         CB_TRY(enqueue_pair_pass(S, MODE_CONTACTS, S->c_shapes.p, S->cap_contacts));
+        CB_TRY(timer_start(S, "k_contact_gen"));
         k_contact_gen<<<grid_for(S, S->cap_contacts, 256), 256, 0, S->stream>>>(
             S->s_meta.p, S->s_wpos.p, S->s_wrot.p, S->s_dims.p, S->c_shapes.p, S->set.collision_envelope, S->c_norm.p,
             S->c_pta.p, S->c_ptb.p, S->c_depth.p, S->c_erad.p, S->c_bids.p, S->c_mats.p,
             use_complex(S) ? S->c_src.p : nullptr, S->cplx_out.p, S->d_cnt);
+        CB_TRY(timer_stop(S, "k_contact_gen"));
         S->launches++;
         CB_CUDA(cudaGetLastError());
     }

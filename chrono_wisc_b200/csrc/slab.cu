@@ -279,6 +279,8 @@ int cb200_download_body_ids(cb200_system* sys, int first, int n, int64_t* ids, u
 int cb200_slab_configure(cb200_system* sys, int nb_static, int ns_static, int axis, double lo, double hi,
                          double width, int has_left, int has_right, int owned_cap, int ghost_cap) {
     System* S = SYSL(sys);
+    if (S)
+        invalidate_step_graph(S);
     if (!S || nb_static < 0 || (uint32_t)nb_static > S->nb || axis < 0 || axis > 2 || !(width > 0) || ghost_cap <= 0)
         return set_error(CB200_ERR_ARG, "bad argument to cb200_slab_configure");
     if (S->slab_on)

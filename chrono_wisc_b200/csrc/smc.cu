@@ -521,6 +521,7 @@ int enqueue_smc(System* S) {
                                                       S->ct_force.p, S->ct_torque.p, S->d_cnt)
     // one instantiation per force model: the runtime switch of the reference (...SMC.cpp:258-440) costs registers
     const bool um = P.use_mat_props != 0;
+    CB_TRY(timer_start(S, "k_smc_force"));
     switch (P.force_model) {
         case 0: if (um) SMC_LAUNCH(0, true); else SMC_LAUNCH(0, false); break;
         case 1: if (um) SMC_LAUNCH(1, true); else SMC_LAUNCH(1, false); break;
@@ -528,13 +529,16 @@ int enqueue_smc(System* S) {
         default: if (um) SMC_LAUNCH(2, true); else SMC_LAUNCH(2, false); break;
     }
 #undef SMC_LAUNCH
+    CB_TRY(timer_stop(S, "k_smc_force"));
     S->launches++;
     CB_TRY(scan_u32(S, S->b_deg.p, S->b_deg.p, &S->d_cnt->n_bodies, nb));
     k_inc_fill<<<cgrid, 256, 0, S->stream>>>(S->c_bids.p, S->heavy.p, S->b_deg.p, S->b_cursor.p, S->b_inc.p, S->d_cnt);
     k_heavy_list<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->heavy.p, S->heavy_list.p, S->d_cnt);
+    CB_TRY(timer_start(S, "k_body_reduce"));
     k_body_reduce<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->heavy.p, S->b_deg.p, S->b_inc.p, S->ct_force.p,
                                                               S->ct_torque.p, st.step_size, S->b_force.p, S->hf.p,
                                                               S->d_cnt);
+    CB_TRY(timer_stop(S, "k_body_reduce"));
     k_heavy_partial<<<dim3(grid_for(S, chunk_cap, 1, 4), 4), 256, 0, S->stream>>>(
         S->c_bids.p, S->ct_force.p, S->ct_torque.p, S->heavy_list.p, S->d_cnt, chunk_cap, S->heavy_part.p);
     k_heavy_final<<<MAX_HEAVY, 256, 0, S->stream>>>(S->heavy_list.p, S->d_cnt, chunk_cap, S->heavy_part.p,

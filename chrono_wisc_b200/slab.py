@@ -127,8 +127,11 @@ class LocalExchange:
 class _SlabMixin:
     """Stepping with ghost exchange on top of a ChSystemMulticore{SMC,NSC}."""
 
-    def _slab_init(self, layout, exchange=None, owned_cap=None, ghost_cap=None):
+    def _slab_init(self, layout, exchange=None, owned_cap=None, ghost_cap=None, own_stream=False):
         self.layout = layout
+        # own_stream: step, pack/unpack and the NCCL transfers run on a dedicated (capturable) CUDA stream, which lets
+        # the library replay its step as a CUDA graph; otherwise everything is ordered on torch's current stream
+        self._own_stream, self.stream = bool(own_stream), None
         self.exchange = exchange
         self._owned_cap, self._ghost_cap = owned_cap, ghost_cap
         self.nb_static = self.ns_static = 0
@@ -177,9 +180,19 @@ class _SlabMixin:
         with torch.cuda.device(dev):
             self.send_left, self.send_right, self.recv_left, self.recv_right = (
                 torch.zeros(n, dtype=torch.float64, device=dev) for _ in range(4))
-            # everything the library enqueues goes on torch's current stream: ordered with the NCCL transfers
-            check(self._lib.cb200_set_stream(self._h, C.c_void_p(torch.cuda.current_stream(dev).cuda_stream), 0))
+            # everything the library enqueues goes on one torch stream: ordered with the NCCL transfers
+            self.stream = torch.cuda.Stream(dev) if self._own_stream else torch.cuda.current_stream(dev)
+            if self._own_stream:
+                self.stream.wait_stream(torch.cuda.current_stream(dev))
+            check(self._lib.cb200_set_stream(self._h, C.c_void_p(self.stream.cuda_stream), 0))
         return self
+
+    def _on_stream(self):
+        import contextlib
+
+        import torch
+
+        return torch.cuda.stream(self.stream) if self._own_stream else contextlib.nullcontext()
 
     def _ptr(self, t, side):
         return C.c_void_p(t.data_ptr()) if side is not None else None
@@ -193,17 +206,19 @@ class _SlabMixin:
         check(self._lib.cb200_slab_unpack_dev(self._h, self._ptr(self.recv_left, L.left), self._ptr(self.recv_right, L.right)))
 
     def ExchangeGhosts(self):
-        self.Pack()
-        if self.exchange is not None:
-            self.exchange(self.send_left, self.send_right, self.recv_left, self.recv_right)
-        self.Unpack()
+        with self._on_stream():
+            self.Pack()
+            if self.exchange is not None:
+                self.exchange(self.send_left, self.send_right, self.recv_left, self.recv_right)
+            self.Unpack()
 
     def DoSteps(self, n):
         """n steps, each followed by the ghost exchange; asynchronous (call Check() or Synchronize())."""
         self._push_settings()
-        for _ in range(int(n)):
-            check(self._lib.cb200_enqueue_steps(self._h, 1))
-            self.ExchangeGhosts()
+        with self._on_stream():
+            for _ in range(int(n)):
+                check(self._lib.cb200_enqueue_steps(self._h, 1))
+                self.ExchangeGhosts()
         self.ch_time += n * self.settings.step_size
 
     def StepOnly(self):
@@ -239,6 +254,6 @@ class _SlabMixin:
 
 
 class SlabSystemSMC(_SlabMixin, ChSystemMulticoreSMC):
-    def __init__(self, layout, device=0, exchange=None, owned_cap=None, ghost_cap=None):
+    def __init__(self, layout, device=0, exchange=None, owned_cap=None, ghost_cap=None, own_stream=False):
         ChSystemMulticoreSMC.__init__(self, device)
-        self._slab_init(layout, exchange, owned_cap, ghost_cap)
+        self._slab_init(layout, exchange, owned_cap, ghost_cap, own_stream)
