@@ -103,6 +103,7 @@ static int alloc_entries(System* S, uint32_t n) {
     CB_TRY(S->ent_m.reserve(S->ent_tmp.cap));
     S->cap_entries = (uint32_t)S->ent_tmp.cap;
     CB_TRY(S->ent_off.reserve((size_t)S->cap_entries + 4));
+    CB_TRY(S->slow_bins.reserve((size_t)S->cap_entries + 4));
     if (use_complex(S)) {
         CB_TRY(S->ent_cmask.reserve(S->cap_entries));
         CB_TRY(S->ent_cbase.reserve(S->cap_entries));
@@ -309,7 +310,7 @@ void cb200_destroy(cb200_system* sys) {
     REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(bflags); REL(heavy);
     REL(s_type); REL(s_body); REL(s_fam); REL(s_mat); REL(s_lpos); REL(s_lrot); REL(s_dims); REL(s_wpos); REL(s_wrot);
     REL(s_box); REL(s_meta); REL(mat_smc); REL(mat_nsc); REL(bin_intersections); REL(bin_start); REL(bin_cursor);
-    REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_mask); REL(ent_c); REL(ent_m); REL(ent_off); REL(large_list); REL(pairs);
+    REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_mask); REL(ent_c); REL(ent_m); REL(ent_off); REL(slow_bins); REL(large_list); REL(pairs);
     REL(c_norm); REL(c_pta); REL(c_ptb); REL(c_depth); REL(c_erad); REL(c_bids); REL(c_shapes); REL(c_mats);
     REL(ent_cmask); REL(ent_cbase); REL(cplx_rec); REL(cplx_n); REL(cplx_out); REL(c_src);
     REL(ct_force); REL(ct_torque); REL(b_deg); REL(b_cursor); REL(b_inc); REL(b_force); REL(heavy_list);

@@ -115,7 +115,8 @@ struct DevCounters {
     double nsc_residual, nsc_objective;
     uint32_t nsc_hist_count;     // iterations recorded in the residual history (includes the one that broke out)
     uint32_t n_cslots;           // contact slots reserved for the complex pairs (PreprocessCount's rule per pair)
-    uint32_t need_cslots, pad2;
+    uint32_t need_cslots;
+    uint32_t n_slow;             // bins queued for k_pair_masks_slow
 };
 
 struct Timer {
@@ -127,7 +128,7 @@ struct Timer {
 };
 
 enum { LARGE_BINS = 48, MAX_LARGE = 4096, MAX_HEAVY = 64, SMC_MAT_STRIDE = 14, NSC_MAT_STRIDE = 8, PAIR_TILE = 256,
-       PAIR_HALO = 96 };
+       PAIR_HALO = 64 };
 
 struct System {
     int device = 0;
@@ -184,6 +185,7 @@ struct System {
     DevBuf<ShapeMeta> ent_m;             // per entry: integer record of the shape (pad = shape id), bin-sorted
     DevBuf<uint64_t> ent_mask;           // cap_entries  bit j set: the entry pairs with the j-th entry of its bin
     DevBuf<uint32_t> ent_off;            // cap_entries+2 outputs per entry -> exclusive offsets
+    DevBuf<uint32_t> slow_bins;          // cap_entries  first entries of the bins the warp-per-bin pair kernel takes
     DevBuf<uint32_t> large_list;         // MAX_LARGE
     DevBuf<int64_t> pairs;               // cap_pairs (materialised on demand only)
     bool pairs_valid = false;

@@ -29,13 +29,16 @@
 namespace cb200 {
 
 constexpr int WIN = PAIR_TILE + PAIR_HALO;
+constexpr int PAIR_THREADS = WIN;  // one thread per window entry
 
 // Shared-memory window, struct-of-arrays: lane-consecutive entries are word-consecutive in every array.
-struct Window {
-    double mn[3][WIN], mx[3][WIN];  // origin-relative AABB
-    double c[4][WIN];               // world position + dims[0] (sphere: centre, radius)
-    uint32_t body[WIN], fam[WIN], info[WIN], id[WIN];
+template <int N>
+struct WindowT {
+    double mn[3][N], mx[3][N];  // origin-relative AABB
+    double c[4][N];             // world position + dims[0] (sphere: centre, radius)
+    uint32_t body[N], fam[N], info[N], id[N];
 };
+using Window = WindowT<WIN>;
 
 struct Rec {
     double mn[3], mx[3];
@@ -71,7 +74,8 @@ __device__ __forceinline__ void load_rec_sorted(Rec& R, uint32_t e, const ShapeM
     }
 }
 
-__device__ __forceinline__ void win_put(Window& W, int k, const Rec& R) {
+template <int N>
+__device__ __forceinline__ void win_put(WindowT<N>& W, int k, const Rec& R) {
 #pragma unroll
     for (int a = 0; a < 3; a++) {
         W.mn[a][k] = R.mn[a];
@@ -81,7 +85,8 @@ __device__ __forceinline__ void win_put(Window& W, int k, const Rec& R) {
     W.body[k] = R.body, W.fam[k] = R.fam, W.info[k] = R.info, W.id[k] = R.id;
 }
 
-__device__ __forceinline__ void win_get(const Window& W, int k, Rec& R) {
+template <int N>
+__device__ __forceinline__ void win_get(const WindowT<N>& W, int k, Rec& R) {
 #pragma unroll
     for (int a = 0; a < 3; a++) {
         R.mn[a] = W.mn[a][k];
@@ -348,23 +353,25 @@ __device__ __forceinline__ int pair_decide(const Rec& A, const Rec& B, const Gri
 }
 
 template <bool CPLX>
-__global__ void __launch_bounds__(PAIR_TILE, 3) k_pair_masks(const ShapeMeta* __restrict__ meta,
-                                                          const ShapeMeta* __restrict__ ent_m,
-                                                          const double* __restrict__ ent_c,
-                                                          const double* __restrict__ s_wpos,
-                                                          const ShapeBox* __restrict__ s_box,
-                                                          const double* __restrict__ s_wrot,
-                                                          const double* __restrict__ s_dims,
-                                                          const uint32_t* __restrict__ ent_shape,
-                                                          const uint32_t* __restrict__ ent_bin,
-                                                          const uint64_t* __restrict__ bin_start, double envelope,
-                                                          int algorithm, int mode, uint64_t* __restrict__ ent_mask,
-                                                          uint64_t* __restrict__ ent_cmask,
-                                                          uint32_t* __restrict__ ent_cnt,
-                                                          DevCounters* __restrict__ cnt) {
+__global__ void __launch_bounds__(PAIR_THREADS, 2) k_pair_masks(const ShapeMeta* __restrict__ meta,
+                                                             const ShapeMeta* __restrict__ ent_m,
+                                                             const double* __restrict__ ent_c,
+                                                             const double* __restrict__ s_wpos,
+                                                             const ShapeBox* __restrict__ s_box,
+                                                             const double* __restrict__ s_wrot,
+                                                             const double* __restrict__ s_dims,
+                                                             const uint32_t* __restrict__ ent_shape,
+                                                             const uint32_t* __restrict__ ent_bin,
+                                                             const uint64_t* __restrict__ bin_start, double envelope,
+                                                             int algorithm, int mode, uint64_t* __restrict__ ent_mask,
+                                                             uint64_t* __restrict__ ent_cmask,
+                                                             uint32_t* __restrict__ ent_cnt,
+                                                             uint32_t* __restrict__ slow_bins,
+                                                             DevCounters* __restrict__ cnt) {
     __shared__ Window W;
     __shared__ unsigned long long smask[WIN];
     __shared__ unsigned long long scmask[CPLX ? WIN : 1];
+    __shared__ uint8_t mixed[WIN];  // the row's bin holds a non-sphere
     if (cnt->overflow)
         return;
     const GridParams g = load_grid(cnt);
@@ -372,189 +379,212 @@ __global__ void __launch_bounds__(PAIR_TILE, 3) k_pair_masks(const ShapeMeta* __
     const uint32_t ntiles = cnt->n_tiles;
     const double sep = 2 * envelope;
     const int lane = threadIdx.x & 31;
+    const uint32_t t = threadIdx.x;  // window index == row of this thread (WIN == blockDim.x)
     uint32_t np = 0, ncx = 0;
 
     for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const uint32_t e0 = tile * PAIR_TILE;
         const uint32_t wend = min(ni, e0 + WIN);
+        const uint32_t e = e0 + t;
         __syncthreads();  // previous tile's readers are done with the window
-        for (uint32_t k = threadIdx.x; e0 + k < wend; k += PAIR_TILE) {
-            Rec R;
-            load_rec_sorted(R, e0 + k, ent_m, ent_c, s_wpos, s_box, g.origin, envelope);
-            win_put(W, k, R);
-            smask[k] = 0ull;
-            if (CPLX)
-                scmask[k] = 0ull;
+        smask[t] = 0ull;
+        if (CPLX)
+            scmask[t] = 0ull;
+        mixed[t] = 0;
+        __syncthreads();
+        // every thread stages one entry and learns its bin (first entry s, length k)
+        Rec A;
+        uint32_t bin = 0, s = 0, k = 0;
+        if (e < wend) {
+            load_rec_sorted(A, e, ent_m, ent_c, s_wpos, s_box, g.origin, envelope);
+            win_put(W, (int)t, A);
+            bin = ent_bin[e];
+            s = (uint32_t)bin_start[bin];
+            k = (uint32_t)bin_start[bin + 1] - s;
+            if (((A.info >> 8) & 0xff) != CB200_SPHERE) {
+                const uint32_t lo = max(s, e0), hi = min(s + k, wend);
+                for (uint32_t x = lo; x < hi; x++)
+                    mixed[x - e0] = 1;
+            }
         }
         __syncthreads();
+        // the tile owns the bins that start in its first PAIR_TILE entries, including their rows in the halo
+        const bool own = e < wend && s >= e0 && s < e0 + PAIR_TILE;
+        const bool fast = !mixed[t] && algorithm != 0;
 
-        // bins that start in this warp's chunk
-        const uint32_t e = e0 + threadIdx.x;
-        uint32_t bin = 0, bs = 0, bk = 0;
-        bool starts = false;
-        if (e < ni) {
-            bin = ent_bin[e];
-            const uint32_t s = (uint32_t)bin_start[bin];
-            starts = (s == e);
-            if (starts) {
-                bs = s;
-                bk = (uint32_t)bin_start[bin + 1] - s;
+        // ---- phase A: one thread per row of a sphere-only bin of 2..64 entries.  Row i meets its partners
+        // j = i + d (mod k), d = 1..(k-1)/2 (+ half a diagonal when k is even): every unordered pair exactly once,
+        // the same amount of work for every row of a bin, no idle lanes whatever k is.  The partner's AABB is
+        // recomputed from (centre, radius) -- the very operations that produced the stored one -- because FP64
+        // adds are cheaper here than 64-bit shared-memory loads.
+        if (own && fast && k >= 2 && k <= 64 && A.body != UINT_MAX && (A.info & 2u)) {
+            const uint32_t i = e - s;
+            const int w0 = (int)(s - e0);
+            const uint32_t h = (k - 1) >> 1;
+            const uint32_t nd = h + (((k & 1u) || i >= (k >> 1)) ? 0u : 1u);
+            unsigned long long mym = 0ull;
+            const uint32_t gA = A.fam & 0xffffu, mA = A.fam >> 16;
+            // Straight-line body: with ~1 pair in 8 passing, a warp never skips a section as a whole, so early
+            // exits only add branches; all loads are issued up front and two partners are in flight per trip.
+#pragma unroll 2
+            for (uint32_t d = 1; d <= nd; d++) {
+                uint32_t j = i + d;
+                if (j >= k)
+                    j -= k;
+                const int wj = w0 + (int)j;
+                const double bx = W.c[0][wj], by = W.c[1][wj], bz = W.c[2][wj], br = W.c[3][wj];
+                const uint32_t bbody = W.body[wj], bfam = W.fam[wj], binfo = W.info[wj];
+                const double rr = br + envelope;
+                const double n0 = (bx - rr) - g.origin[0], n1 = (by - rr) - g.origin[1], n2 = (bz - rr) - g.origin[2];
+                const double x0 = (bx + rr) - g.origin[0], x1 = (by + rr) - g.origin[1], x2 = (bz + rr) - g.origin[2];
+                // f_Count_AABB_AABB_Intersection's conjunction, CMC/ChCollisionUtilsBroadphase.cpp:114-140
+                const bool ov = (A.mn[0] <= x0) & (n0 <= A.mx[0]) & (A.mn[1] <= x1) & (n1 <= A.mx[1]) &
+                                (A.mn[2] <= x2) & (n2 <= A.mx[2]);
+                const uint32_t both = A.info | binfo;
+                const bool ok = ((both & 56u) == 56u) & (bbody != UINT_MAX) & (bbody != A.body) &
+                                ((binfo & 2u) != 0) & ((both & 1u) != 0) & ((mA & (bfam & 0xffffu)) != 0) &
+                                (((bfam >> 16) & gA) != 0);
+                bool hit = ov & ok;
+                np += hit ? 1u : 0u;
+                if (mode == MODE_CONTACTS) {
+                    // the deciding lines of sphere_sphere, ChNarrowphasePRIMS.cpp:52-60 (symmetric in the two
+                    // shapes bit for bit)
+                    const d3 delta = mk3(bx, by, bz) - mk3(A.cx, A.cy, A.cz);
+                    const double dist2 = dot3(delta, delta);
+                    const double radSum_s = (A.r + br) + sep;
+                    hit = hit & !((dist2 >= radSum_s * radSum_s) | (dist2 < 1e-12));
+                }
+                if (hit) {
+                    if (j > i)
+                        mym |= 1ull << j;
+                    else
+                        atomicOr(&smask[wj], 1ull << i);
+                }
             }
+            if (mym)
+                atomicOr(&smask[t], mym);
         }
-        unsigned todo = __ballot_sync(0xffffffffu, starts);
-        while (todo) {
-            const int src = __ffs(todo) - 1;
-            todo &= todo - 1;
-            const uint32_t b = __shfl_sync(0xffffffffu, bin, src);
-            const uint32_t s = __shfl_sync(0xffffffffu, bs, src);
-            const uint32_t k = __shfl_sync(0xffffffffu, bk, src);
-            if (k < 2) {
-                if (lane == 0) {
-                    ent_mask[s] = 0ull;
-                    ent_cnt[s] = 0;
-                    if (CPLX)
-                        ent_cmask[s] = 0ull;
-                }
-                continue;
-            }
-            const uint32_t w0 = s - e0;  // window index of the bin's first entry
-            if (k <= 64) {
-                // rows in registers: lane l owns entry i = rb + l and meets its partners j = i + d (mod k),
-                // d = 1..(k-1)/2 (+ half a diagonal when k is even) -- every unordered pair exactly once, the
-                // partner read is one conflict-free shared-memory access per lane.  In a bin of spheres only
-                // (the bulk of a granular bed) the partner's AABB is recomputed from (centre, radius) -- the very
-                // operations that produced the stored one -- instead of being loaded: FP64 adds are cheaper than
-                // 64-bit shared loads here.
-                bool nonsphere = false;
-                for (uint32_t t = lane; t < k; t += 32)
-                    nonsphere |= ((W.info[w0 + t] >> 8) & 0xff) != CB200_SPHERE;
-                const bool fast = !__any_sync(0xffffffffu, nonsphere) && algorithm != 0;
-                const uint32_t h = (k - 1) >> 1;
-                const uint32_t nd = h + ((k & 1u) ? 0u : 1u);
-                if (!fast) {
-                    // a bin with a non-sphere in it (walls, mixed beds): pairs spread evenly over the lanes,
-                    // both records from the window, ordered (lower entry, higher entry) for the shape functions
-                    const uint32_t full = k * h;
-                    const uint32_t total = full + ((k & 1u) ? 0u : (k >> 1));
-                    const uint32_t M = ((1u << 20) + k - 1) / k;  // p / k == (p * M) >> 20 for p < 2048, k <= 64
-                    for (uint32_t p0 = 0; p0 < total; p0 += 32) {
-                        const uint32_t p = p0 + lane;
-                        if (p < total) {
-                            uint32_t i, j;
-                            if (p < full) {
-                                const uint32_t d = (p * M) >> 20;
-                                i = p - d * k;
-                                j = i + d + 1;
-                                if (j >= k)
-                                    j -= k;
-                            } else {
-                                i = p - full;
-                                j = i + (k >> 1);
-                            }
-                            const uint32_t a = min(i, j), c = max(i, j);
-                            Rec A, B;
-                            win_get(W, (int)(w0 + a), A);
-                            win_get(W, (int)(w0 + c), B);
-                            const int dec = pair_decide<true>(A, B, g, b, mode, sep, algorithm, s_wrot, s_dims, np);
-                            if (dec == 1)
-                                atomicOr(&smask[w0 + a], 1ull << c);
-                            else if (dec == 2) {
-                                if (CPLX)
-                                    atomicOr(&scmask[w0 + a], 1ull << c);
-                                else
-                                    ncx++;
-                            }
+
+        // ---- the rest (a non-sphere in the bin, MPR for everything, or more than 64 entries) is queued for
+        // k_pair_masks_slow, a warp per bin: kept out of this kernel so that a tile along a wall does not hold
+        // its CTA at the barrier below while the other warps idle
+        if (own && s == e && (k > 64 || (k >= 2 && !fast)))
+            slow_bins[atomicAdd(&cnt->n_slow, 1u)] = s;
+        __syncthreads();
+        // masks of the rows this tile owns and has decided
+        if (own && (k < 2 || (k <= 64 && fast))) {
+            const unsigned long long m = smask[t];
+            ent_mask[e] = m;
+            ent_cnt[e] = (uint32_t)__popcll(m);
+            if (CPLX)
+                ent_cmask[e] = scmask[t];
+        }
+    }
+    // totals that are not tied to an entry: N_p (contacts mode) and the pairs this backend cannot test
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        np += __shfl_xor_sync(0xffffffffu, np, d);
+        ncx += __shfl_xor_sync(0xffffffffu, ncx, d);
+    }
+    if (lane == 0) {
+        if (mode == MODE_CONTACTS && np)
+            atomicAdd(&cnt->n_pairs, np);
+        if (ncx)
+            atomicAdd(&cnt->unsupported, ncx);
+    }
+}
+
+// --------------------------------------------------------------------------------------------------------------
+// k_pair_masks_slow: a warp per queued bin (non-sphere in the bin, MPR for everything, or more than 64 entries);
+// the warp stages up to 64 of the bin's entries in its own shared-memory window.
+// --------------------------------------------------------------------------------------------------------------
+constexpr int SLOW_WIN = 64, SLOW_WARPS = 4;
+
+template <bool CPLX>
+__global__ void __launch_bounds__(32 * SLOW_WARPS) k_pair_masks_slow(
+    const ShapeMeta* __restrict__ meta, const ShapeMeta* __restrict__ ent_m, const double* __restrict__ ent_c,
+    const double* __restrict__ s_wpos, const ShapeBox* __restrict__ s_box, const double* __restrict__ s_wrot,
+    const double* __restrict__ s_dims, const uint32_t* __restrict__ ent_shape, const uint32_t* __restrict__ ent_bin,
+    const uint64_t* __restrict__ bin_start, double envelope, int algorithm, int mode,
+    uint64_t* __restrict__ ent_mask, uint64_t* __restrict__ ent_cmask, uint32_t* __restrict__ ent_cnt,
+    const uint32_t* __restrict__ slow_bins, DevCounters* __restrict__ cnt) {
+    __shared__ WindowT<SLOW_WIN> W[SLOW_WARPS];
+    __shared__ unsigned long long smask[SLOW_WARPS][SLOW_WIN];
+    __shared__ unsigned long long scmask[CPLX ? SLOW_WARPS : 1][SLOW_WIN];
+    if (cnt->overflow)
+        return;
+    const GridParams g = load_grid(cnt);
+    const uint32_t nslow = cnt->n_slow;
+    const double sep = 2 * envelope;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const uint32_t w0 = 0;
+    uint32_t np = 0, ncx = 0;
+    for (uint32_t q = blockIdx.x * SLOW_WARPS + wid; q < nslow; q += gridDim.x * SLOW_WARPS) {
+        const uint32_t bs = slow_bins[q];
+        const uint32_t b = ent_bin[bs];
+        const uint32_t bk = (uint32_t)bin_start[b + 1] - bs;
+        __syncwarp();
+        for (uint32_t x = lane; x < min(bk, (uint32_t)SLOW_WIN); x += 32) {
+            Rec R;
+            load_rec_sorted(R, bs + x, ent_m, ent_c, s_wpos, s_box, g.origin, envelope);
+            win_put(W[wid], (int)x, R);
+            smask[wid][x] = 0ull;
+            if (CPLX)
+                scmask[wid][x] = 0ull;
+        }
+        __syncwarp();
+            if (bk <= 64) {
+                // pairs spread evenly over the lanes in the cyclic order (i, i+d mod k); both records from the
+                // window, ordered (lower entry, higher entry) for the shape functions
+                const uint32_t h = (bk - 1) >> 1;
+                const uint32_t full = bk * h;
+                const uint32_t total = full + ((bk & 1u) ? 0u : (bk >> 1));
+                const uint32_t M = ((1u << 20) + bk - 1) / bk;  // p / k == (p * M) >> 20 for p < 2048, k <= 64
+                for (uint32_t p0 = 0; p0 < total; p0 += 32) {
+                    const uint32_t p = p0 + lane;
+                    if (p < total) {
+                        uint32_t i, j;
+                        if (p < full) {
+                            const uint32_t d = (p * M) >> 20;
+                            i = p - d * bk;
+                            j = i + d + 1;
+                            if (j >= bk)
+                                j -= bk;
+                        } else {
+                            i = p - full;
+                            j = i + (bk >> 1);
                         }
-                    }
-                } else
-                for (uint32_t rb = 0; rb < k; rb += 32) {
-                    const uint32_t i = rb + lane;
-                    const bool vi = i < k;
-                    Rec A;
-                    if (vi)
-                        win_get(W, (int)(w0 + i), A);
-                    const bool a_ok = vi && A.body != UINT_MAX && (A.info & 2u);
-                    unsigned long long mym = 0ull, mycm = 0ull;
-                    for (uint32_t d = 1; d <= nd; d++) {
-                        uint32_t j = i + d;
-                        if (d > h) {  // the half diagonal of an even k
-                            if (i >= (k >> 1))
-                                continue;
-                        } else if (j >= k) {
-                            j -= k;
-                        }
-                        if (!a_ok)
-                            continue;
-                        const int wj = (int)(w0 + j);
-                        int dec;
-                        {
-                            Rec B;
-                            B.cx = W.c[0][wj], B.cy = W.c[1][wj], B.cz = W.c[2][wj], B.r = W.c[3][wj];
-                            B.body = W.body[wj], B.fam = W.fam[wj], B.info = W.info[wj];
-                            const double rr = B.r + envelope;
-                            B.mn[0] = (B.cx - rr) - g.origin[0], B.mn[1] = (B.cy - rr) - g.origin[1];
-                            B.mn[2] = (B.cz - rr) - g.origin[2];
-                            B.mx[0] = (B.cx + rr) - g.origin[0], B.mx[1] = (B.cy + rr) - g.origin[1];
-                            B.mx[2] = (B.cz + rr) - g.origin[2];
-                            dec = 0;
-                            if (pair_passes<true>(A, B, g, b)) {
-                                np++;
-                                dec = 1;
-                                if (mode == MODE_CONTACTS) {
-                                    // the deciding lines of sphere_sphere, ChNarrowphasePRIMS.cpp:52-60
-                                    // (symmetric in the two shapes bit for bit)
-                                    const d3 delta = mk3(B.cx, B.cy, B.cz) - mk3(A.cx, A.cy, A.cz);
-                                    const double dist2 = dot3(delta, delta);
-                                    const double radSum_s = (A.r + B.r) + sep;
-                                    dec = !(dist2 >= radSum_s * radSum_s || dist2 < 1e-12);
-                                }
-                            }
-                        }
-                        if (dec == 1) {
-                            if (j > i)
-                                mym |= 1ull << j;
+                        const uint32_t a = min(i, j), c = max(i, j);
+                        Rec RA, RB;
+                        win_get(W[wid], (int)(w0 + a), RA);
+                        win_get(W[wid], (int)(w0 + c), RB);
+                        const int dec = pair_decide<true>(RA, RB, g, b, mode, sep, algorithm, s_wrot, s_dims, np);
+                        if (dec == 1)
+                            atomicOr(&smask[wid][w0 + a], 1ull << c);
+                        else if (dec == 2) {
+                            if (CPLX)
+                                atomicOr(&scmask[CPLX ? wid : 0][w0 + a], 1ull << c);
                             else
-                                atomicOr(&smask[wj], 1ull << i);
-                        } else if (dec == 2) {
-                            if (CPLX) {
-                                if (j > i)
-                                    mycm |= 1ull << j;
-                                else
-                                    atomicOr(&scmask[wj], 1ull << i);
-                            } else {
                                 ncx++;
-                            }
                         }
                     }
-                    if (mym)
-                        atomicOr(&smask[w0 + i], mym);
-                    if (CPLX && mycm)
-                        atomicOr(&scmask[w0 + i], mycm);
-                }
-                __syncwarp();
-                for (uint32_t t = lane; t < k; t += 32) {
-                    const unsigned long long m = smask[w0 + t];
-                    ent_mask[s + t] = m;
-                    ent_cnt[s + t] = (uint32_t)__popcll(m);
-                    if (CPLX)
-                        ent_cmask[s + t] = scmask[w0 + t];
                 }
             } else {
-                // long bin: rows one after the other, lanes across the row; count only
-                for (uint32_t i = 0; i + 1 < k; i++) {
-                    Rec A;
-                    if (s + i < wend)
-                        win_get(W, (int)(w0 + i), A);
+                // long bin: rows one after the other, lanes across the row; count only (the store pass re-tests)
+                for (uint32_t i = 0; i + 1 < bk; i++) {
+                    Rec RA;
+                    if (i < SLOW_WIN)
+                        win_get(W[wid], (int)(w0 + i), RA);
                     else
-                        load_rec(A, ent_shape[s + i], meta, s_wpos, s_box, g.origin, envelope);
+                        load_rec(RA, ent_shape[bs + i], meta, s_wpos, s_box, g.origin, envelope);
                     uint32_t hits = 0;
-                    for (uint32_t j = i + 1 + lane; j < k; j += 32) {
-                        Rec B;
-                        if (s + j < wend)
-                            win_get(W, (int)(w0 + j), B);
+                    for (uint32_t j = i + 1 + lane; j < bk; j += 32) {
+                        Rec RB;
+                        if (j < SLOW_WIN)
+                            win_get(W[wid], (int)(w0 + j), RB);
                         else
-                            load_rec(B, ent_shape[s + j], meta, s_wpos, s_box, g.origin, envelope);
-                        const int dec = pair_decide<false>(A, B, g, b, mode, sep, algorithm, s_wrot, s_dims, np);
+                            load_rec(RB, ent_shape[bs + j], meta, s_wpos, s_box, g.origin, envelope);
+                        const int dec = pair_decide<false>(RA, RB, g, b, mode, sep, algorithm, s_wrot, s_dims, np);
                         hits += dec == 1 ? 1u : 0u;
                         ncx += dec == 2 ? 1u : 0u;  // long bins have no complex path
                     }
@@ -562,22 +592,30 @@ __global__ void __launch_bounds__(PAIR_TILE, 3) k_pair_masks(const ShapeMeta* __
                     for (int d = 16; d > 0; d >>= 1)
                         hits += __shfl_xor_sync(0xffffffffu, hits, d);
                     if (lane == 0) {
-                        ent_mask[s + i] = 0ull;
-                        ent_cnt[s + i] = hits;
+                        ent_mask[bs + i] = 0ull;
+                        ent_cnt[bs + i] = hits;
                         if (CPLX)
-                            ent_cmask[s + i] = 0ull;
+                            ent_cmask[bs + i] = 0ull;
                     }
                 }
                 if (lane == 0) {
-                    ent_mask[s + k - 1] = 0ull;
-                    ent_cnt[s + k - 1] = 0;
+                    ent_mask[bs + bk - 1] = 0ull;
+                    ent_cnt[bs + bk - 1] = 0;
                     if (CPLX)
-                        ent_cmask[s + k - 1] = 0ull;
+                        ent_cmask[bs + bk - 1] = 0ull;
                 }
+            }
+        if (bk <= 64) {
+            __syncwarp();
+            for (uint32_t x = lane; x < bk; x += 32) {
+                const unsigned long long m = smask[wid][x];
+                ent_mask[bs + x] = m;
+                ent_cnt[bs + x] = (uint32_t)__popcll(m);
+                if (CPLX)
+                    ent_cmask[bs + x] = scmask[CPLX ? wid : 0][x];
             }
         }
     }
-    // totals that are not tied to an entry: N_p (contacts mode) and the pairs this backend cannot test
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
         np += __shfl_xor_sync(0xffffffffu, np, d);
@@ -836,14 +874,22 @@ static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
     const bool cplx = mode == MODE_CONTACTS && use_complex(S);
     if (mode == MODE_CONTACTS)
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_pairs, 0, 4, S->stream));
-    const int gm = grid_for(S, S->cap_entries, PAIR_TILE, 6);
+    const int gm = grid_for(S, S->cap_entries, PAIR_TILE, 4);
+    CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_slow, 0, 4, S->stream));
+    const int gs = S->num_sms * 8;
     CB_TRY(timer_start(S, "k_pair_masks"));
     if (cplx) {
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_complex, 0, 4, S->stream));
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_cslots, 0, 4, S->stream));
-        k_pair_masks<true><<<gm, PAIR_TILE, 0, S->stream>>>(
+        k_pair_masks<true><<<gm, PAIR_THREADS, 0, S->stream>>>(
             S->s_meta.p, S->ent_m.p, S->ent_c.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p,
-            S->ent_bin.p, S->bin_start.p, env, algorithm, mode, S->ent_mask.p, S->ent_cmask.p, S->ent_off.p, S->d_cnt);
+            S->ent_bin.p, S->bin_start.p, env, algorithm, mode, S->ent_mask.p, S->ent_cmask.p, S->ent_off.p,
+            S->slow_bins.p, S->d_cnt);
+        k_pair_masks_slow<true><<<gs, 32 * SLOW_WARPS, 0, S->stream>>>(
+            S->s_meta.p, S->ent_m.p, S->ent_c.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p,
+            S->ent_bin.p, S->bin_start.p, env, algorithm, mode, S->ent_mask.p, S->ent_cmask.p, S->ent_off.p,
+            S->slow_bins.p, S->d_cnt);
+        S->launches++;
         CB_TRY(timer_stop(S, "k_pair_masks"));
         k_cplx_collect<<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
             S->s_meta.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p, S->ent_cmask.p, algorithm, S->ent_cbase.p,
@@ -853,9 +899,15 @@ static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
             S->cap_complex, S->cap_cslots, S->cplx_n.p, S->cplx_out.p, S->ent_off.p, S->d_cnt);
         S->launches += 3;
     } else {
-        k_pair_masks<false><<<gm, PAIR_TILE, 0, S->stream>>>(
+        k_pair_masks<false><<<gm, PAIR_THREADS, 0, S->stream>>>(
             S->s_meta.p, S->ent_m.p, S->ent_c.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p,
-            S->ent_bin.p, S->bin_start.p, env, algorithm, mode, S->ent_mask.p, nullptr, S->ent_off.p, S->d_cnt);
+            S->ent_bin.p, S->bin_start.p, env, algorithm, mode, S->ent_mask.p, nullptr, S->ent_off.p,
+            S->slow_bins.p, S->d_cnt);
+        k_pair_masks_slow<false><<<gs, 32 * SLOW_WARPS, 0, S->stream>>>(
+            S->s_meta.p, S->ent_m.p, S->ent_c.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p,
+            S->ent_bin.p, S->bin_start.p, env, algorithm, mode, S->ent_mask.p, nullptr, S->ent_off.p,
+            S->slow_bins.p, S->d_cnt);
+        S->launches++;
         CB_TRY(timer_stop(S, "k_pair_masks"));
         S->launches++;
     }
