@@ -251,8 +251,7 @@ __device__ __forceinline__ void flip_contacts(Contact* out, int n) {
 
 // Narrowphase of one complex pair: DispatchMPR / DispatchPRIMS / DispatchHybridMPR (CMC/ChNarrowphase.cpp:232-320)
 // over PRIMSCollision (ChNarrowphasePRIMS.cpp:1406-1607) and MPRCollision (ChNarrowphaseMPR.cpp:627-645).
-// Returns the number of contacts written to out[0..], or -1 for a combination this backend does not cover
-// (box - cylindrical shell, whose analytic test is not implemented here).
+// Returns the number of contacts written to out[0..].
 __device__ __noinline__ int narrow_complex(const ShapeView& A, const ShapeView& B, int algorithm, double envelope,
                                            Contact* out) {
     const double sep = 2 * envelope;
@@ -272,8 +271,18 @@ __device__ __noinline__ int narrow_complex(const ShapeView& A, const ShapeView& 
         }
         if (tA == CB200_BOX && tB == CB200_BOX)
             return box_box(A.pos, A.rot, mk3(A.d0, A.d1, A.d2), B.pos, B.rot, mk3(B.d0, B.d1, B.d2), sep, out);
-        if ((tA == CB200_BOX && tB == CB200_CYLSHELL) || (tA == CB200_CYLSHELL && tB == CB200_BOX))
-            return -1;
+        if (tA == CB200_BOX && tB == CB200_CYLSHELL) {
+            n = box_cylshell(A.pos, A.rot, mk3(A.d0, A.d1, A.d2), B.pos, B.rot, B.d0, B.d1, sep, out);
+            if (n >= 0)
+                return n;  // -1: not an axis-aligned configuration, PRIMSCollision returns false -> MPR in HYBRID
+        }
+        if (tA == CB200_CYLSHELL && tB == CB200_BOX) {
+            n = box_cylshell(B.pos, B.rot, mk3(B.d0, B.d1, B.d2), A.pos, A.rot, A.d0, A.d1, sep, out);
+            if (n >= 0) {
+                flip_contacts(out, n);
+                return n;
+            }
+        }
         if (algorithm == 1)
             return 0;  // PRIMS only: no analytic test, no contact
     }

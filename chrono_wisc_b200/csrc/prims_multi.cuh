@@ -1,9 +1,10 @@
 // prims_multi.cuh -- analytic pair tests that can return more than one contact (capsule-capsule, box-capsule,
-// box-box), for the device narrowphase of non-sphere pairs.
+// box-cylshell, box-box), for the device narrowphase of non-sphere pairs.
 //
 // Arithmetic follows the reference operation for operation (bit-exact under -fmad=false):
 //   capsule_capsule   src/chrono/collision/multicore/ChNarrowphasePRIMS.cpp:446-564
 //   box_capsule       ChNarrowphasePRIMS.cpp:575-707
+//   box_cylshell      ChNarrowphasePRIMS.cpp:719-915
 //   box_box           ChNarrowphasePRIMS.cpp:924-1224
 //   helpers           ChCollisionUtils.h:567-730 (snap_to_box_face/edge, get_*_corners, box_farthest_corner,
 //                     box_closest_feature), ChCollisionUtilsPRIMS.cpp:142-330 (point_vs_face, segment_vs_edge,
@@ -555,6 +556,129 @@ __device__ inline int box_box(const d3& posT, const q4& rotT, const d3& hdimsT, 
         return j < MAX_PAIR_CONTACTS ? j : MAX_PAIR_CONTACTS;
     }
     return 0;
+}
+
+// ChNarrowphasePRIMS.cpp:719-915.  Only axis-parallel / axis-perpendicular configurations are analytic; -1 asks for the
+// MPR fall-back.  (The reference clamps the circle/edge intersections with c[i2] in the i2-edge cases and with c[i3] in
+// the i3-edge cases; kept as is.)
+__device__ inline int box_cylshell(const d3& pos1, const q4& rot1, const d3& hdims_, const d3& pos2, const q4& rot2,
+                                   double radius, double hlen, double separation, Contact* out) {
+    const v3 c = tov(rotate_t(pos2 - pos1, rot1));
+    const q4 rot = qmul(qinv(rot1), rot2);
+    const v3 a = tov(amat_w(rot));
+    const v3 hdims = tov(hdims_);
+    v3 c_abs, a_abs;
+#pragma unroll
+    for (int x = 0; x < 3; x++)
+        c_abs[x] = fabs(c[x]), a_abs[x] = fabs(a[x]);
+    const double threshold_par = 1e-4, threshold_perp = 1e-4;
+#pragma unroll
+    for (int i1 = 0; i1 < 3; i1++) {
+        const int i2 = (i1 + 1) % 3, i3 = (i1 + 2) % 3;
+        // (1) cylinder axis parallel to the i1 box face
+        if (a_abs[i1] < threshold_par) {
+            if (c_abs[i1] > hdims[i1] + radius + separation)
+                return 0;
+            if (c_abs[i1] < hdims[i1])
+                continue;
+            double tMin = -DBL_MAX, tMax = DBL_MAX;
+            if (a_abs[i2] > threshold_par) {
+                const double t1 = (-hdims[i2] - c[i2]) / a[i2];
+                const double t2 = (+hdims[i2] - c[i2]) / a[i2];
+                tMin = smax(tMin, smin(t1, t2));
+                tMax = smin(tMax, smax(t1, t2));
+                if (tMin > tMax)
+                    return 0;
+            }
+            if (a_abs[i3] > threshold_par) {
+                const double t1 = (-hdims[i3] - c[i3]) / a[i3];
+                const double t2 = (+hdims[i3] - c[i3]) / a[i3];
+                tMin = smax(tMin, smin(t1, t2));
+                tMax = smin(tMax, smax(t1, t2));
+                if (tMin > tMax)
+                    return 0;
+            }
+            clamp_value(tMin, -hlen, +hlen);
+            clamp_value(tMax, -hlen, +hlen);
+            const d3 cd = tod(c), ad = tod(a);
+            const d3 locs[2] = {cd + tMin * ad, cd + tMax * ad};
+            int j = 0;
+            for (int i = 0; i < 2; i++) {
+                d3 boxPoint = locs[i];
+                snap_to_box(hdims_, boxPoint);
+                d3 u = locs[i] - boxPoint;
+                const double u_nrm = sqrt(dot3(u, u));
+                u = u / u_nrm;
+                const d3 cylPoint = locs[i] - radius * u;
+                push_contact(out, j, rotate(u, rot1), local_to_parent(pos1, rot1, boxPoint),
+                             local_to_parent(pos1, rot1, cylPoint), u_nrm - radius, radius);
+            }
+            return 2;
+        }
+        // (2) cylinder axis perpendicular to the i1 box face
+        if (a_abs[i1] > 1 - threshold_perp) {
+            if (c_abs[i1] > hdims[i1] + hlen + separation)
+                return 0;
+            if (c_abs[i1] < hdims[i1])
+                continue;
+            if (c_abs[i2] > hdims[i2] || c_abs[i3] > hdims[i3])
+                continue;
+            const int sign = (c[i1] > 0) ? +1 : -1;
+            v3 u;
+            u[0] = u[1] = u[2] = 0;
+            u[i1] = sign;
+            v3 locs[8];
+            int nc = 0;
+            double discr;
+            // negative i2 edge
+            discr = radius * radius - (c[i2] + hdims[i2]) * (c[i2] + hdims[i2]);
+            if (discr > 0) {
+                const double sq = sqrt(discr);
+                locs[nc][i2] = -hdims[i2], locs[nc][i3] = clampd(c[i2] + sq, -hdims[i3], +hdims[i3]), nc++;
+                locs[nc][i2] = -hdims[i2], locs[nc][i3] = clampd(c[i2] - sq, -hdims[i3], +hdims[i3]), nc++;
+            } else {
+                locs[nc][i2] = c[i2] - radius, locs[nc][i3] = c[i3], nc++;
+            }
+            // positive i2 edge
+            discr = radius * radius - (c[i2] - hdims[i2]) * (c[i2] - hdims[i2]);
+            if (discr > 0) {
+                const double sq = sqrt(discr);
+                locs[nc][i2] = +hdims[i2], locs[nc][i3] = clampd(c[i2] + sq, -hdims[i3], +hdims[i3]), nc++;
+                locs[nc][i2] = +hdims[i2], locs[nc][i3] = clampd(c[i2] - sq, -hdims[i3], +hdims[i3]), nc++;
+            } else {
+                locs[nc][i2] = c[i2] + radius, locs[nc][i3] = c[i3], nc++;
+            }
+            // negative i3 edge
+            discr = radius * radius - (c[i3] + hdims[i3]) * (c[i3] + hdims[i3]);
+            if (discr > 0) {
+                const double sq = sqrt(discr);
+                locs[nc][i3] = -hdims[i3], locs[nc][i2] = clampd(c[i3] + sq, -hdims[i2], +hdims[i2]), nc++;
+                locs[nc][i3] = -hdims[i3], locs[nc][i2] = clampd(c[i3] - sq, -hdims[i2], +hdims[i2]), nc++;
+            } else {
+                locs[nc][i3] = c[i3] - radius, locs[nc][i2] = c[i2], nc++;
+            }
+            // positive i3 edge
+            discr = radius * radius - (c[i3] - hdims[i3]) * (c[i3] - hdims[i3]);
+            if (discr > 0) {
+                const double sq = sqrt(discr);
+                locs[nc][i3] = +hdims[i3], locs[nc][i2] = clampd(c[i3] + sq, -hdims[i2], +hdims[i2]), nc++;
+                locs[nc][i3] = +hdims[i3], locs[nc][i2] = clampd(c[i3] - sq, -hdims[i2], +hdims[i2]), nc++;
+            } else {
+                locs[nc][i3] = c[i3] + radius, locs[nc][i2] = c[i2], nc++;
+            }
+            int j = 0;
+            const d3 nrm = rotate(tod(u), rot1);
+            for (int i = 0; i < nc; i++) {
+                locs[i][i1] = sign * hdims[i1];
+                const d3 p1 = local_to_parent(pos1, rot1, tod(locs[i]));
+                locs[i][i1] = c[i1] - sign * hlen;
+                const d3 p2 = local_to_parent(pos1, rot1, tod(locs[i]));
+                push_contact(out, j, nrm, p1, p2, c[i1] - sign * hlen - sign * hdims[i1], radius);
+            }
+            return nc;
+        }
+    }
+    return -1;
 }
 
 }  // namespace cb200

@@ -10,7 +10,8 @@ import pytest
 
 import chrono_wisc_b200 as cw
 from chrono_wisc_b200 import scenes
-from chrono_wisc_b200.system import (BOX, CAPSULE, CONE, CYLINDER, ELLIPSOID, ROUNDEDBOX, ROUNDEDCYL, SPHERE)
+from chrono_wisc_b200.system import (BOX, CAPSULE, CONE, CYLINDER, CYLSHELL, ELLIPSOID, ROUNDEDBOX, ROUNDEDCYL,
+                                     SPHERE)
 
 pytestmark = pytest.mark.gpu
 
@@ -26,6 +27,7 @@ DIMS = {
     ELLIPSOID: [0.1, 0.07, 0.05, 0],
     ROUNDEDBOX: [0.08, 0.07, 0.05, 0.02],
     ROUNDEDCYL: [0.06, 0.06, 0.08, 0.02],
+    CYLSHELL: [0.06, 0.08, 0.08, 0],  # PRIMS reads (radius, hlen) = (x, y), MPR (radius, hheight) = (x, z)
 }
 
 
@@ -41,7 +43,10 @@ def cluttered(kinds, n_side, spacing, seed, algorithm, envelope, aligned=False, 
         for iy in range(n_side):
             for iz in range(n_side):
                 p = np.array([ix, iy, iz]) * spacing + rng.uniform(-0.15, 0.15, 3) * spacing
-                if aligned:
+                if aligned == 2:  # identity, quarter turn about z, quarter turn about x (axis along -y)
+                    q = [np.array([1.0, 0, 0, 0]), np.array([np.sqrt(0.5), 0, 0, np.sqrt(0.5)]),
+                         np.array([np.sqrt(0.5), np.sqrt(0.5), 0, 0])][(i // 2) % 3]
+                elif aligned:
                     q = np.array([1.0, 0, 0, 0]) if (i % 3) else np.array([np.sqrt(0.5), 0, 0, np.sqrt(0.5)])
                 else:
                     q = rng.normal(size=4)
@@ -103,6 +108,20 @@ def test_face_face_boxes_many_contacts(ref):
     scene, rk = compare(scene, ref, 300)
     _, counts = np.unique(rk["shape_ids"], return_counts=True)
     assert counts.max() >= 4, counts.max()
+
+
+@pytest.mark.parametrize("algorithm", [PRIMS, HYBRID])
+@pytest.mark.parametrize("aligned", [2, False])
+def test_box_cylshell(ref, algorithm, aligned):
+    """box_cylshell (ChNarrowphasePRIMS.cpp:719-915): analytic only when the shell's axis is parallel or perpendicular
+    to a box face (up to 8 contacts); any other configuration makes PRIMSCollision return false, i.e. MPR in HYBRID
+    mode and no contact in PRIMS mode."""
+    scene = cluttered([BOX, CYLSHELL], 6, 0.13, 11, algorithm, 0.01, aligned=aligned)
+    scene, rk = compare(scene, ref, 50 if (aligned or algorithm == HYBRID) else 0)
+    if aligned:
+        types = scene["shape_type"]
+        seen = set(zip(types[rk["shape_ids"] >> 32], types[rk["shape_ids"] & 0xFFFFFFFF]))
+        assert (BOX, CYLSHELL) in seen or (CYLSHELL, BOX) in seen, seen
 
 
 def test_spheres_only_under_mpr(ref):
