@@ -298,10 +298,7 @@ def run_b200(args):
     barrier()
     t0 = time.perf_counter()
     for _ in range(n_e2e):
-        sys_.SetBodyState(0, hp, hq, hv, nb)
-        sys_.DoSteps(1)
-        _lib.check(lib.cb200_download_state(sys_._h, 0, nb, hp.ctypes.data_as(C.c_void_p),
-                                            hq.ctypes.data_as(C.c_void_p), hv.ctypes.data_as(C.c_void_p)))
+        sys_.StepHost(hp, hq, hv)  # cb200_step_host: H2D pose + velocity, one step, D2H pose + velocity
     barrier()
     e2e_wall = time.perf_counter() - t0
     t = torch.tensor([e2e_wall], dtype=torch.float64, device="cuda")

@@ -98,6 +98,7 @@ _SIGNATURES = {
     "cb200_synchronize": (C.c_int, [_P]),
     "cb200_get_counts": (C.c_int, [_P, C.POINTER(cb200_counts)]),
     "cb200_download_state": (C.c_int, [_P, C.c_int, C.c_int, _P, _P, _P]),
+    "cb200_step_host": (C.c_int, [_P, _P, _P, _P]),
     "cb200_download_aabb": (C.c_int, [_P, _P, _P]),
     "cb200_download_bins": (C.c_int, [_P, _P, _P, _P, _P]),
     "cb200_download_pairs": (C.c_int, [_P, _P]),

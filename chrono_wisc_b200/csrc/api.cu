@@ -318,6 +318,11 @@ void cb200_destroy(cb200_system* sys) {
     REL(n_w); REL(n_w0); REL(n_mk); REL(n_part); REL(n_hist); REL(n_rows);
     if (S->step_graph)
         cudaGraphExecDestroy(S->step_graph);
+    if (S->copy_stream) {
+        cudaStreamDestroy(S->copy_stream);
+        cudaEventDestroy(S->ev_copy);
+        cudaEventDestroy(S->ev_main);
+    }
     if (S->n_ctl)
         cudaFree(S->n_ctl);
     REL(scan_tmp);
@@ -780,6 +785,63 @@ int cb200_do_steps(cb200_system* sys, int nsteps) {
                                  " candidate pairs have a shape combination this backend cannot test yet");
     }
     return CB200_OK;
+}
+
+// DoStepDynamics for a caller whose state lives in HOST buffers (the reference's per-step gather from / scatter to the
+// ChBody objects, MC/physics/ChSystemMulticore.cpp:329-377 and :134-153): pose up, step, pose and velocity down, as one
+// pipelined call.  The collision stages need positions and rotations only, so the velocity upload (48 of the 104
+// bytes per body) travels on a second stream while the main stream already runs AABBs, binning and the pair kernels;
+// the force stage waits for it.  pos/rot/vel are in-out and should be pinned (cb200_host_alloc).
+int cb200_step_host(cb200_system* sys, double* pos, double* rot, double* vel) {
+    System* S = SYS(sys);
+    if (!S || !pos || !rot || !vel)
+        return set_error(CB200_ERR_ARG, "null argument to cb200_step_host");
+    CB_CUDA(cudaSetDevice(S->device));
+    if (S->nb == 0)
+        return CB200_OK;
+    if (S->slab_on)
+        return set_error(CB200_ERR_STATE, "cb200_step_host is not available on a slab system");
+    if (!S->copy_stream) {
+        CB_CUDA(cudaStreamCreateWithFlags(&S->copy_stream, cudaStreamNonBlocking));
+        CB_CUDA(cudaEventCreateWithFlags(&S->ev_copy, cudaEventDisableTiming));
+        CB_CUDA(cudaEventCreateWithFlags(&S->ev_main, cudaEventDisableTiming));
+    }
+    CB_TRY(ensure_capacity(S));
+    const size_t nb = S->nb;
+    for (int attempt = 0; attempt < 8; attempt++) {
+        CB_CUDA(cudaMemsetAsync(&S->d_cnt->steps_done, 0, 4, S->stream));
+        CB_CUDA(cudaMemcpyAsync(S->pos.p, pos, 3 * nb * sizeof(double), cudaMemcpyHostToDevice, S->stream));
+        CB_CUDA(cudaMemcpyAsync(S->rot.p, rot, 4 * nb * sizeof(double), cudaMemcpyHostToDevice, S->stream));
+        // the velocities follow the pose over the link (not beside it: both would share the bandwidth and the
+        // collision stages would start later), on the second stream, while the main stream computes
+        CB_CUDA(cudaEventRecord(S->ev_main, S->stream));
+        CB_CUDA(cudaStreamWaitEvent(S->copy_stream, S->ev_main, 0));
+        CB_CUDA(cudaMemcpyAsync(S->vel.p, vel, 6 * nb * sizeof(double), cudaMemcpyHostToDevice, S->copy_stream));
+        CB_CUDA(cudaEventRecord(S->ev_copy, S->copy_stream));
+        CB_TRY(enqueue_aabb(S));
+        CB_TRY(enqueue_bins(S));
+        CB_TRY(enqueue_pairs_only(S, false, true));
+        CB_CUDA(cudaStreamWaitEvent(S->stream, S->ev_copy, 0));
+        CB_TRY(enqueue_update_forces(S));
+        if (S->set.system_type == 1)
+            CB_TRY(enqueue_smc(S));
+        else
+            CB_TRY(enqueue_nsc(S));
+        CB_TRY(enqueue_integrate(S));
+        CB_CUDA(cudaMemcpyAsync(pos, S->pos.p, 3 * nb * sizeof(double), cudaMemcpyDeviceToHost, S->stream));
+        CB_CUDA(cudaMemcpyAsync(rot, S->rot.p, 4 * nb * sizeof(double), cudaMemcpyDeviceToHost, S->stream));
+        CB_CUDA(cudaMemcpyAsync(vel, S->vel.p, 6 * nb * sizeof(double), cudaMemcpyDeviceToHost, S->stream));
+        S->direct_steps++;
+        CB_TRY(fetch_counters(S));
+        if (S->h_cnt->unsupported)
+            return set_error(CB200_ERR_UNSUPPORTED, std::to_string(S->h_cnt->unsupported) +
+                                                        " candidate pairs have a shape combination this backend cannot test yet");
+        if (!S->h_cnt->overflow)
+            return S->h_cnt->steps_done == 1 ? CB200_OK : set_error(CB200_ERR_STATE, "step accounting mismatch");
+        // a capacity was exceeded: every kernel after it was a no-op, the host buffers got the uploaded state back
+        CB_TRY(grow_after_overflow(S));
+    }
+    return set_error(CB200_ERR_STATE, "capacity growth did not converge");
 }
 
 // Asynchronous stepping for callers that interleave their own work on the stream (slab exchange): no host

@@ -255,6 +255,8 @@ struct System {
     bool step_graph_meta = false;    // the captured step rebuilds the per-shape records (meta_dirty at capture)
     int direct_steps = 0;            // steps enqueued directly since the graph was last invalidated
     unsigned async_calls = 0;
+    cudaStream_t copy_stream = nullptr;  // second copy engine queue of cb200_step_host
+    cudaEvent_t ev_copy = nullptr, ev_main = nullptr;
 };
 
 // multi-contact / MPR pairs can occur: two or more non-sphere shapes, or MPR requested for everything

@@ -146,6 +146,17 @@ class ChSystemMulticore:
             self.settings.step_size = float(step)
         self.DoSteps(1)
 
+    def StepHost(self, pos, rot, vel):
+        """One DoStepDynamics on host-resident state (in place): the per-step gather / scatter of the reference
+        (ChSystemMulticore.cpp:329-377, :134-153) as one pipelined call.  Arrays must be C-contiguous float64,
+        ideally pinned (``_lib.load().cb200_host_alloc``)."""
+        for a, w in ((pos, 3), (rot, 4), (vel, 6)):
+            if a.dtype != np.float64 or not a.flags.c_contiguous or a.size != w * self.num_bodies:
+                raise ValueError("StepHost needs C-contiguous float64 arrays of nb x (3, 4, 6)")
+        self._push_settings()
+        check(self._lib.cb200_step_host(self._h, _ptr(pos), _ptr(rot), _ptr(vel)))
+        self.ch_time += self.settings.step_size
+
     def DoSteps(self, n):
         self._push_settings()
         check(self._lib.cb200_do_steps(self._h, int(n)))

@@ -155,6 +155,12 @@ int cb200_upload_state(cb200_system* sys, int first, int n, const double* pos, c
 int cb200_upload_applied_forces(cb200_system* sys, int first, int n, const double* force_torque);
 int cb200_set_body_flags(cb200_system* sys, int first, int n, const char* active, const char* collide);
 
+/* ChSystem::DoStepDynamics for a caller that keeps the body state in host memory (what the reference does: gather from
+ * the ChBody objects before, scatter to them after every step, MC/physics/ChSystemMulticore.cpp:329-377, :134-153):
+ * uploads pos[3nb], rot[4nb], vel[6nb], runs one step, downloads the three arrays into the same buffers.  The
+ * velocity upload overlaps the collision stages.  Buffers should come from cb200_host_alloc (pinned). */
+int cb200_step_host(cb200_system* sys, double* pos, double* rot, double* vel);
+
 /* --- the step, split at the reference's own seams ------------------------------------------------------------ */
 /* ChSystemMulticore::Update -> UpdateRigidBodies force part (ChBody::Update/VariablesFbLoadForces): hf = h*(F,T-gyro). */
 int cb200_update_forces(cb200_system* sys);

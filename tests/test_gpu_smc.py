@@ -173,3 +173,20 @@ def test_determinism():
         outs.append(sys.GetBodyState())
     for a, b in zip(*outs):
         assert np.array_equal(a, b)
+
+
+def test_step_host_equals_upload_step_download():
+    """cb200_step_host (host state in, one step, host state out, velocity upload overlapped with the collision stages)
+    returns exactly what upload_state -> do_steps(1) -> download_state returns."""
+    scene = scenes.settling_smc(24, 24, 6, spacing_factor=1.98, jitter_factor=0.03)
+    a = cw.load_scene(cw.ChSystemMulticoreSMC(), scene)
+    b = cw.load_scene(cw.ChSystemMulticoreSMC(), scene)
+    a.DoSteps(5)
+    b.DoSteps(5)
+    p, q, v = (np.ascontiguousarray(x) for x in a.GetBodyState())
+    for _ in range(3):
+        a.StepHost(p, q, v)
+        b.DoSteps(1)
+    pb, qb, vb = b.GetBodyState()
+    assert np.array_equal(p, pb) and np.array_equal(q, qb) and np.array_equal(v, vb)
+    assert a.GetNumContacts() == b.GetNumContacts() > 0
