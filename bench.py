@@ -132,7 +132,9 @@ def kernel_rooflines(sys_, nb, c, peak):
     ni, np_, nc = c.num_bin_aabb_intersections, c.num_possible_collisions, c.num_rigid_contacts
     alg = {
         "k_pair_masks": ni * 16 + np_ * 16,          # entries read; the pair list it decides but never materialises
-        "k_smc_force": nc * (96 + 2 * 112 + 72),     # contact record + two body states in, force/torques out
+        # pair key + two shape poses (centre, radius) + two body states in; body/material ids, force, torques out
+        # (the contact geometry is evaluated in the kernel, no contact record is read in the step)
+        "k_smc_force": nc * (8 + 2 * 32 + 2 * 112 + 16 + 72),
         "k_body_reduce": nb * 96 + nc * 2 * 56,      # per-body accumulators + (index, force, torque) per incidence
         "k_contact_gen": nc * (8 + 96),              # key in, contact record out
         "k_pair_store": ni * 16 + nc * 8,            # masks + offsets in, keys out

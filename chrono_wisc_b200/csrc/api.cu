@@ -666,7 +666,7 @@ static int enqueue_one_step(System* S) {
     CB_TRY(enqueue_bins(S));
     CB_TRY(timer_stop(S, "collision_broad"));
     CB_TRY(timer_start(S, "collision_narrow"));  // in-bin pair tests fused with the single-contact narrowphase
-    CB_TRY(enqueue_pairs_only(S, false, true));
+    CB_TRY(enqueue_pairs_only(S, false, true, /*defer_geometry=*/S->set.system_type == 1));
     CB_TRY(timer_stop(S, "collision_narrow"));
     CB_TRY(timer_stop(S, "collision"));
     CB_TRY(timer_start(S, "advance"));
@@ -820,7 +820,7 @@ int cb200_step_host(cb200_system* sys, double* pos, double* rot, double* vel) {
         CB_CUDA(cudaEventRecord(S->ev_copy, S->copy_stream));
         CB_TRY(enqueue_aabb(S));
         CB_TRY(enqueue_bins(S));
-        CB_TRY(enqueue_pairs_only(S, false, true));
+        CB_TRY(enqueue_pairs_only(S, false, true, /*defer_geometry=*/S->set.system_type == 1));
         CB_CUDA(cudaStreamWaitEvent(S->stream, S->ev_copy, 0));
         CB_TRY(enqueue_update_forces(S));
         if (S->set.system_type == 1)
@@ -833,6 +833,7 @@ int cb200_step_host(cb200_system* sys, double* pos, double* rot, double* vel) {
         CB_CUDA(cudaMemcpyAsync(vel, S->vel.p, 6 * nb * sizeof(double), cudaMemcpyDeviceToHost, S->stream));
         S->direct_steps++;
         CB_TRY(fetch_counters(S));
+        CB_TRY(flush_timers(S));
         if (S->h_cnt->unsupported)
             return set_error(CB200_ERR_UNSUPPORTED, std::to_string(S->h_cnt->unsupported) +
                                                         " candidate pairs have a shape combination this backend cannot test yet");
@@ -1056,6 +1057,7 @@ int cb200_download_contacts(cb200_system* sys, double* normal, double* pt_a, dou
                             double* eff_radius, int32_t* body_ids, int64_t* shape_ids) {
     System* S = SYS(sys);
     CB_CUDA(cudaSetDevice(S->device));
+    CB_TRY(ensure_contact_geometry(S));  // an SMC step leaves the records unwritten until somebody reads them
     CB_TRY(fetch_counters(S));
     const size_t nc = S->h_cnt->n_contacts;
     CB_TRY(download(S, S->c_norm.p, normal, 3 * nc));
@@ -1129,6 +1131,7 @@ int cb200_get_timer(cb200_system* sys, const char* name, double* seconds) {
     System* S = SYS(sys);
     if (!S || !name || !seconds)
         return set_error(CB200_ERR_ARG, "null argument");
+    CB_TRY(flush_timers(S));  // resolve intervals recorded since the last synchronising call
     auto it = S->timers.find(name);
     if (it == S->timers.end())
         return set_error(CB200_ERR_ARG, std::string("unknown timer '") + name + "'");
@@ -1143,6 +1146,8 @@ int cb200_device_array(cb200_system* sys, const char* name, void** dev_ptr, int6
     if (!S || !name || !dev_ptr || !count)
         return set_error(CB200_ERR_ARG, "null argument");
     const std::string n(name);
+    if (n.rfind("contact_", 0) == 0)
+        CB_TRY(ensure_contact_geometry(S));
     struct E { const char* k; void* p; int64_t c; };
     const E tab[] = {
         {"pos", S->pos.p, 3 * (int64_t)S->nb},           {"rot", S->rot.p, 4 * (int64_t)S->nb},

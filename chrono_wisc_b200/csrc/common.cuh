@@ -189,6 +189,7 @@ struct System {
     DevBuf<uint32_t> large_list;         // MAX_LARGE
     DevBuf<int64_t> pairs;               // cap_pairs (materialised on demand only)
     bool pairs_valid = false;
+    bool contacts_geom_valid = false;  // c_norm/c_pta/c_ptb/c_depth/c_erad hold the records of the current key list
     bool box_relative = false;  // s_box holds origin-relative boxes (the binning ran since the last AABB stage)
 
     // ---- narrowphase output: the contact list (CMC/ChCollisionData.h:159-183) ----
@@ -277,7 +278,8 @@ int enqueue_integrate(System* S);                                        // inte
 int enqueue_aabb(System* S);                                             // broadphase.cu
 int enqueue_bins(System* S);                                             // broadphase.cu: grid + counting sort
 int enqueue_broadphase(System* S, bool want_pairs, bool want_contacts);  // broadphase.cu
-int enqueue_pairs_only(System* S, bool want_pairs, bool want_contacts);  // broadphase.cu: pair kernels on existing bins
+int enqueue_pairs_only(System* S, bool want_pairs, bool want_contacts, bool defer_geometry = false);  // pairs.cu
+int ensure_contact_geometry(System* S);  // pairs.cu: contact records on demand
 int enqueue_smc(System* S);                                              // smc.cu
 int enqueue_nsc(System* S);                                              // nsc.cu
 int nsc_contact_forces_inactive(System* S);                              // nsc.cu: on-demand part of CalculateContactForces

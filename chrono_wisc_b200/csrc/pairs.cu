@@ -21,6 +21,7 @@
 #include "grid.cuh"
 #include "prims.cuh"
 #include "mpr.cuh"
+#include "narrow_single.cuh"
 #include "prims_multi.cuh"
 #include <limits.h>
 #include <stdio.h>
@@ -123,82 +124,6 @@ __device__ __forceinline__ bool pair_passes(const Rec& A, const Rec& B, const Gr
         return false;
     const uint32_t gA = A.fam & 0xffffu, mA = A.fam >> 16, gB = B.fam & 0xffffu, mB = B.fam >> 16;
     return (mA & gB) && (mB & gA);
-}
-
-__device__ __forceinline__ ShapeView make_view(uint32_t id, int type, const double4& w,
-                                               const double* __restrict__ s_wrot, const double* __restrict__ s_dims) {
-    ShapeView v;
-    v.type = type;
-    v.pos = mk3(w.x, w.y, w.z);
-    v.d0 = w.w;
-    v.d1 = v.d2 = v.d3_ = 0;
-    v.rot = mkq(1, 0, 0, 0);
-    if (type != CB200_SPHERE) {
-        const double4 r = reinterpret_cast<const double4*>(s_wrot)[id];
-        v.rot = mkq(r.x, r.y, r.z, r.w);
-        const double4 d = reinterpret_cast<const double4*>(s_dims)[id];
-        v.d1 = d.y, v.d2 = d.z, v.d3_ = d.w;
-    }
-    return v;
-}
-
-// Analytic dispatcher for pairs with at most one contact (everything that involves a sphere),
-// PRIMSCollision, CMC/ChNarrowphasePRIMS.cpp:1406-1607.
-// Returns 1/0 contacts, or -1 when the combination is not of that kind (multi-contact analytic pair or MPR).
-// Callers that only use the return value get the decision alone: the compiler drops the sqrt/divisions that
-// feed nothing but the unused Contact.
-__device__ __forceinline__ int prims_single(const ShapeView& A, const ShapeView& B, double sep, Contact& c) {
-    bool hit;
-    if (A.type == CB200_SPHERE && B.type == CB200_SPHERE)
-        return sphere_sphere(A.pos, A.d0, B.pos, B.d0, sep, c) ? 1 : 0;
-    if (B.type == CB200_SPHERE) {
-        switch (A.type) {
-            case CB200_CAPSULE:
-                return capsule_sphere(A.pos, A.rot, A.d0, A.d1, B.pos, B.d0, sep, c) ? 1 : 0;
-            case CB200_CYLINDER:
-                return cylinder_sphere(A.pos, A.rot, A.d0, A.d1, B.pos, B.d0, sep, c) ? 1 : 0;
-            case CB200_ROUNDEDCYL:
-                return roundedcyl_sphere(A.pos, A.rot, A.d0, A.d1, A.d3_, B.pos, B.d0, sep, c) ? 1 : 0;
-            case CB200_BOX:
-                return box_sphere(A.pos, A.rot, mk3(A.d0, A.d1, A.d2), B.pos, B.d0, sep, c) ? 1 : 0;
-            case CB200_ROUNDEDBOX:
-                return roundedbox_sphere(A.pos, A.rot, mk3(A.d0, A.d1, A.d2), A.d3_, B.pos, B.d0, sep, c) ? 1 : 0;
-            default:
-                return -1;
-        }
-    }
-    if (A.type == CB200_SPHERE) {
-        // swapped call: the shape function sees (B, A); points are exchanged and the normal negated
-        // (ChNarrowphasePRIMS.cpp:1435-1443 and siblings)
-        switch (B.type) {
-            case CB200_CAPSULE:
-                hit = capsule_sphere(B.pos, B.rot, B.d0, B.d1, A.pos, A.d0, sep, c);
-                break;
-            case CB200_CYLINDER:
-                hit = cylinder_sphere(B.pos, B.rot, B.d0, B.d1, A.pos, A.d0, sep, c);
-                break;
-            case CB200_ROUNDEDCYL:
-                hit = roundedcyl_sphere(B.pos, B.rot, B.d0, B.d1, B.d3_, A.pos, A.d0, sep, c);
-                break;
-            case CB200_BOX:
-                hit = box_sphere(B.pos, B.rot, mk3(B.d0, B.d1, B.d2), A.pos, A.d0, sep, c);
-                break;
-            case CB200_ROUNDEDBOX:
-                hit = roundedbox_sphere(B.pos, B.rot, mk3(B.d0, B.d1, B.d2), B.d3_, A.pos, A.d0, sep, c);
-                break;
-            default:
-                return -1;
-        }
-        if (hit) {
-            const d3 t = c.p1;
-            c.p1 = c.p2;
-            c.p2 = t;
-            c.n = -c.n;
-            return 1;
-        }
-        return 0;
-    }
-    return -1;
 }
 
 // Full shape view for the complex path: spheres carry their true world rotation too (MPR rotates the search
@@ -938,7 +863,30 @@ static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
     return CB200_OK;
 }
 
-int enqueue_pairs_only(System* S, bool want_pairs, bool want_contacts) {
+// k_contact_gen over the current key list: the contact records (CMC/ChCollisionData.h:159-183).  The shape frames
+// it reads (s_wpos, s_wrot) are those of the collision stage that made the keys and stay untouched until the next one.
+int enqueue_contact_gen(System* S) {
+    CB_TRY(timer_start(S, "k_contact_gen"));
+    k_contact_gen<<<grid_for(S, S->cap_contacts, 256), 256, 0, S->stream>>>(
+        S->s_meta.p, S->s_wpos.p, S->s_wrot.p, S->s_dims.p, S->c_shapes.p, S->set.collision_envelope, S->c_norm.p,
+        S->c_pta.p, S->c_ptb.p, S->c_depth.p, S->c_erad.p, S->c_bids.p, S->c_mats.p,
+        use_complex(S) ? S->c_src.p : nullptr, S->cplx_out.p, S->d_cnt);
+    CB_TRY(timer_stop(S, "k_contact_gen"));
+    S->launches++;
+    S->contacts_geom_valid = true;
+    CB_CUDA(cudaGetLastError());
+    return CB200_OK;
+}
+
+// Readers of the contact records call this first: a step of the SMC system leaves them unwritten (the force kernel
+// evaluates the geometry in place) until somebody asks.
+int ensure_contact_geometry(System* S) {
+    if (S->contacts_geom_valid || S->ns == 0)
+        return CB200_OK;
+    return enqueue_contact_gen(S);
+}
+
+int enqueue_pairs_only(System* S, bool want_pairs, bool want_contacts, bool defer_geometry) {
     if (S->ns == 0)
         return CB200_OK;
     if (want_pairs) {
@@ -947,14 +895,9 @@ int enqueue_pairs_only(System* S, bool want_pairs, bool want_contacts) {
     }
     if (want_contacts) {
         CB_TRY(enqueue_pair_pass(S, MODE_CONTACTS, S->c_shapes.p, S->cap_contacts));
-        CB_TRY(timer_start(S, "k_contact_gen"));
-        k_contact_gen<<<grid_for(S, S->cap_contacts, 256), 256, 0, S->stream>>>(
-            S->s_meta.p, S->s_wpos.p, S->s_wrot.p, S->s_dims.p, S->c_shapes.p, S->set.collision_envelope, S->c_norm.p,
-            S->c_pta.p, S->c_ptb.p, S->c_depth.p, S->c_erad.p, S->c_bids.p, S->c_mats.p,
-            use_complex(S) ? S->c_src.p : nullptr, S->cplx_out.p, S->d_cnt);
-        CB_TRY(timer_stop(S, "k_contact_gen"));
-        S->launches++;
-        CB_CUDA(cudaGetLastError());
+        S->contacts_geom_valid = false;
+        if (!defer_geometry)
+            CB_TRY(enqueue_contact_gen(S));
     }
     return CB200_OK;
 }

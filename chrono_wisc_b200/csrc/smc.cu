@@ -13,6 +13,7 @@
 // Summation order: each body adds its contacts in ascending contact index, which is the order the reference's
 // stable sort produces; no floating-point atomics anywhere, so results are run-to-run reproducible.
 #include "common.cuh"
+#include "narrow_single.cuh"
 #include <float.h>
 
 namespace cb200 {
@@ -47,8 +48,29 @@ __device__ __forceinline__ BodyView load_body(uint32_t b, const double* __restri
     return B;
 }
 
-template <int FORCE_MODEL, bool USE_MAT>
-__global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, const int32_t* __restrict__ bids,
+// Contact geometry evaluated inside the force kernel (GEN): in a step nobody reads the contact records, so writing
+// them in k_contact_gen and reading them back here would be 200 bytes of traffic per contact for nothing.  The
+// records are produced on demand instead (ensure_contact_geometry, pairs.cu).
+struct GenArgs {
+    const int64_t* c_shapes;
+    const ShapeMeta* meta;
+    const double *s_wpos, *s_wrot, *s_dims;
+    const uint32_t* c_src;
+    const double* cplx_out;
+    double sep;
+    int32_t* bids_out;
+    uint32_t* mats_out;
+};
+
+// cold path: a contact that involves a non-sphere
+__device__ __noinline__ void contact_general(uint32_t sA, int tA, double4 wA, uint32_t sB, int tB, double4 wB,
+                                             double sep, const double* __restrict__ s_wrot,
+                                             const double* __restrict__ s_dims, Contact& c) {
+    prims_single(make_view(sA, tA, wA, s_wrot, s_dims), make_view(sB, tB, wB, s_wrot, s_dims), sep, c);
+}
+
+template <int FORCE_MODEL, bool USE_MAT, bool GEN>
+__global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, GenArgs G, const int32_t* __restrict__ bids,
                                                    const uint32_t* __restrict__ c_mats,
                                                    const double* __restrict__ c_norm, const double* __restrict__ c_pta,
                                                    const double* __restrict__ c_ptb, const double* __restrict__ c_depth,
@@ -63,8 +85,38 @@ __global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, const int32_t
     const uint32_t nc = cnt->n_contacts;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nc; i += gridDim.x * blockDim.x) {
     d3 force = mk3(0), tq1 = mk3(0), tq2 = mk3(0);
-    const double depth = c_depth[i];
-    const uint32_t b1 = (uint32_t)bids[2 * i], b2 = (uint32_t)bids[2 * i + 1];
+    Contact C;
+    uint32_t b1, b2, mm;
+    if (GEN) {
+        // DispatchPRIMS on the compacted key list, as k_contact_gen does it
+        const int64_t key = G.c_shapes[i];
+        const uint32_t sA = (uint32_t)(key >> 32), sB = (uint32_t)(key & 0xffffffff);
+        const ShapeMeta mA = G.meta[sA], mB = G.meta[sB];
+        const double4 wA = reinterpret_cast<const double4*>(G.s_wpos)[sA];
+        const double4 wB = reinterpret_cast<const double4*>(G.s_wpos)[sB];
+        const int tA = (mA.info >> 8) & 0xff, tB = (mB.info >> 8) & 0xff;
+        const uint32_t src = G.c_src ? G.c_src[i] : 0u;
+        if (src) {
+            const double* q = G.cplx_out + 11 * (size_t)(src - 1);
+            C.n = mk3(q[0], q[1], q[2]), C.p1 = mk3(q[3], q[4], q[5]), C.p2 = mk3(q[6], q[7], q[8]);
+            C.depth = q[9], C.erad = q[10];
+        } else if (tA == CB200_SPHERE && tB == CB200_SPHERE) {
+            sphere_sphere(mk3(wA.x, wA.y, wA.z), wA.w, mk3(wB.x, wB.y, wB.z), wB.w, G.sep, C);
+        } else {
+            Contact cg;  // only this one has its address taken: the hot path stays in registers
+            contact_general(sA, tA, wA, sB, tB, wB, G.sep, G.s_wrot, G.s_dims, cg);
+            C.n = cg.n, C.p1 = cg.p1, C.p2 = cg.p2, C.depth = cg.depth, C.erad = cg.erad;
+        }
+        b1 = mA.body, b2 = mB.body;
+        mm = (mA.info >> 16) | (mB.info >> 16) << 16;
+        reinterpret_cast<int2*>(G.bids_out)[i] = make_int2((int)b1, (int)b2);
+        G.mats_out[i] = mm;
+    } else {
+        C.depth = c_depth[i];
+        b1 = (uint32_t)bids[2 * i], b2 = (uint32_t)bids[2 * i + 1];
+        mm = c_mats[i];
+    }
+    const double depth = C.depth;
     // body -> contact incidence counts (first half of the counting sort by body that replaces the reference's
     // sort_by_key, ...SMC.cpp:702-703)
     if (!heavy[b1])
@@ -74,10 +126,14 @@ __global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, const int32_t
     if (depth < 0) {
         const BodyView B1 = load_body(b1, pos, rot, vel, mass);
         const BodyView B2 = load_body(b2, pos, rot, vel, mass);
-        const d3 n = mk3(c_norm[3 * i], c_norm[3 * i + 1], c_norm[3 * i + 2]);
-        const d3 pt1 = mk3(c_pta[3 * i], c_pta[3 * i + 1], c_pta[3 * i + 2]);
-        const d3 pt2 = mk3(c_ptb[3 * i], c_ptb[3 * i + 1], c_ptb[3 * i + 2]);
-        const double erad = c_erad[i];
+        if (!GEN) {
+            C.n = mk3(c_norm[3 * i], c_norm[3 * i + 1], c_norm[3 * i + 2]);
+            C.p1 = mk3(c_pta[3 * i], c_pta[3 * i + 1], c_pta[3 * i + 2]);
+            C.p2 = mk3(c_ptb[3 * i], c_ptb[3 * i + 1], c_ptb[3 * i + 2]);
+            C.erad = c_erad[i];
+        }
+        const d3 n = C.n, pt1 = C.p1, pt2 = C.p2;
+        const double erad = C.erad;
 
         // kinematics (:110-135)
         const d3 pt1_loc = parent_to_local(B1.pos, B1.rot, pt1);
@@ -92,7 +148,6 @@ __global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, const int32_t
 
         // composite material (:140-160)
         const double m_eff = B1.mass * B2.mass / (B1.mass + B2.mass);
-        const uint32_t mm = c_mats[i];
         const double* M = mat + ((size_t)(mm & 0xffff) * P.nm + (mm >> 16)) * SMC_MAT_STRIDE;
         const double mu_eff = M[0];
         double muRoll_eff = M[1], muSpin_eff = M[2];
@@ -514,11 +569,24 @@ int enqueue_smc(System* S) {
     CB_CUDA(cudaMemsetAsync(S->b_deg.p, 0, (size_t)(nb + 1) * 4, S->stream));
     CB_CUDA(cudaMemsetAsync(S->b_cursor.p, 0, (size_t)nb * 4, S->stream));
     const int fgrid = grid_for(S, S->cap_contacts, 128, 16);
-#define SMC_LAUNCH(FM, UM)                                                                                        \
-    k_smc_force<FM, UM><<<fgrid, 128, 0, S->stream>>>(P, S->c_bids.p, S->c_mats.p, S->c_norm.p, S->c_pta.p,        \
-                                                      S->c_ptb.p, S->c_depth.p, S->c_erad.p, S->pos.p, S->rot.p,   \
-                                                      S->vel.p, S->mass.p, S->mat_smc.p, S->heavy.p, S->b_deg.p,   \
-                                                      S->ct_force.p, S->ct_torque.p, S->d_cnt)
+    GenArgs G;
+    G.c_shapes = S->c_shapes.p, G.meta = S->s_meta.p, G.s_wpos = S->s_wpos.p, G.s_wrot = S->s_wrot.p;
+    G.s_dims = S->s_dims.p, G.c_src = use_complex(S) ? S->c_src.p : nullptr, G.cplx_out = S->cplx_out.p;
+    G.sep = 2 * S->set.collision_envelope, G.bids_out = S->c_bids.p, G.mats_out = S->c_mats.p;
+    const bool gen = !S->contacts_geom_valid;  // the step skipped k_contact_gen: evaluate the geometry here
+#define SMC_LAUNCH2(FM, UM, GN)                                                                                     \
+    k_smc_force<FM, UM, GN><<<fgrid, 128, 0, S->stream>>>(P, G, S->c_bids.p, S->c_mats.p, S->c_norm.p, S->c_pta.p, \
+                                                          S->c_ptb.p, S->c_depth.p, S->c_erad.p, S->pos.p,         \
+                                                          S->rot.p, S->vel.p, S->mass.p, S->mat_smc.p,             \
+                                                          S->heavy.p, S->b_deg.p, S->ct_force.p, S->ct_torque.p,   \
+                                                          S->d_cnt)
+#define SMC_LAUNCH(FM, UM)         \
+    do {                           \
+        if (gen)                   \
+            SMC_LAUNCH2(FM, UM, true);  \
+        else                       \
+            SMC_LAUNCH2(FM, UM, false); \
+    } while (0)
     // one instantiation per force model: the runtime switch of the reference (...SMC.cpp:258-440) costs registers
     const bool um = P.use_mat_props != 0;
     CB_TRY(timer_start(S, "k_smc_force"));
@@ -529,6 +597,7 @@ int enqueue_smc(System* S) {
         default: if (um) SMC_LAUNCH(2, true); else SMC_LAUNCH(2, false); break;
     }
 #undef SMC_LAUNCH
+#undef SMC_LAUNCH2
     CB_TRY(timer_stop(S, "k_smc_force"));
     S->launches++;
     CB_TRY(scan_u32(S, S->b_deg.p, S->b_deg.p, &S->d_cnt->n_bodies, nb));
