@@ -308,7 +308,7 @@ void cb200_destroy(cb200_system* sys) {
     cudaStreamSynchronize(S->stream);
 #define REL(x) S->x.release()
     REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(bflags); REL(heavy);
-    REL(s_type); REL(s_body); REL(s_fam); REL(s_mat); REL(s_lpos); REL(s_lrot); REL(s_dims); REL(s_wpos); REL(s_wrot);
+    REL(s_type); REL(s_body); REL(s_fam); REL(s_mat); REL(s_lpos); REL(s_lrot); REL(s_dims); REL(s_verts); REL(s_wpos); REL(s_wrot);
     REL(s_box); REL(s_meta); REL(mat_smc); REL(mat_nsc); REL(bin_intersections); REL(bin_start); REL(bin_cursor);
     REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_mask); REL(ent_c); REL(ent_m); REL(ent_off); REL(slow_bins); REL(large_list); REL(pairs);
     REL(c_norm); REL(c_pta); REL(c_ptb); REL(c_depth); REL(c_erad); REL(c_bids); REL(c_shapes); REL(c_mats);
@@ -424,9 +424,15 @@ int cb200_append_shapes(cb200_system* sys, int n, const int32_t* type, const uin
             case CB200_SPHERE: case CB200_ELLIPSOID: case CB200_BOX: case CB200_CYLINDER: case CB200_CYLSHELL:
             case CB200_CAPSULE: case CB200_CONE: case CB200_ROUNDEDBOX: case CB200_ROUNDEDCYL:
                 break;
+            case CB200_TRIANGLE: case CB200_CONVEXHULL: {
+                const double first = dims[4 * i], count = type[i] == CB200_TRIANGLE ? 3.0 : dims[4 * i + 1];
+                if (!(first >= 0) || !(count >= 1) || first + count > (double)S->n_verts)
+                    return set_error(CB200_ERR_ARG, "triangle / convex hull refers to vertices that were not added "
+                                                    "(cb200_append_shape_vertices)");
+                break;
+            }
             default:
-                return set_error(CB200_ERR_UNSUPPORTED, "shape type " + std::to_string(type[i]) +
-                                                            " (convex hull / triangle mesh) is not supported yet");
+                return set_error(CB200_ERR_UNSUPPORTED, "shape type " + std::to_string(type[i]) + " is not supported");
         }
         if (body_id[i] != UINT_MAX && body_id[i] >= S->nb)
             return set_error(CB200_ERR_ARG, "shape refers to a body that was not added");
@@ -475,9 +481,27 @@ int cb200_append_shapes(cb200_system* sys, int n, const int32_t* type, const uin
             S->nonsphere_bodies = 2;
         }
         // no analytic test against a sphere either: such pairs go to MPR, i.e. the complex path
-        if (type[i] == CB200_ELLIPSOID || type[i] == CB200_CONE || type[i] == CB200_CYLSHELL)
+        if (type[i] == CB200_ELLIPSOID || type[i] == CB200_CONE || type[i] == CB200_CYLSHELL ||
+            type[i] == CB200_CONVEXHULL)
             S->nonsphere_bodies = 2;
     }
+    return CB200_OK;
+}
+
+int cb200_append_shape_vertices(cb200_system* sys, int n, const double* xyz, int* first) {
+    System* S = SYS(sys);
+    if (S)
+        invalidate_step_graph(S);
+    if (!S || n < 0 || (n > 0 && !xyz))
+        return set_error(CB200_ERR_ARG, "bad argument to cb200_append_shape_vertices");
+    CB_CUDA(cudaSetDevice(S->device));
+    const size_t n0 = S->n_verts, n1 = n0 + (size_t)n;
+    CB_TRY(S->s_verts.reserve(3 * n1, true, S->stream));
+    CB_TRY(upload(S, S->s_verts, 3 * n0, xyz, 3 * (size_t)n));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    S->n_verts = (uint32_t)n1;
+    if (first)
+        *first = (int)n0;
     return CB200_OK;
 }
 

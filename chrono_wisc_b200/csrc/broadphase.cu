@@ -88,7 +88,8 @@ __global__ void k_reset_counters(DevCounters* cnt, uint32_t nb, uint32_t ns) {
 // --------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_aabb(uint32_t ns, const ShapeMeta* __restrict__ meta,
                                               const double* __restrict__ s_lpos, const double* __restrict__ s_lrot,
-                                              const double* __restrict__ s_dims, const double* __restrict__ pos,
+                                              double* s_dims, const double* __restrict__ s_verts,
+                                              const double* __restrict__ pos,
                                               const double* __restrict__ rot, double envelope,
                                               double* __restrict__ s_wpos, double* __restrict__ s_wrot,
                                               ShapeBox* __restrict__ s_box, DevCounters* __restrict__ cnt) {
@@ -120,6 +121,30 @@ __global__ void __launch_bounds__(256) k_aabb(uint32_t ns, const ShapeMeta* __re
             const q4 lq = mkq(la.x, la.y, la.z, la.w);
             const d3 wp = rotate(lp, q) + p;  // == TransformLocalToParent(p, q, lp): IEEE addition commutes
             const q4 wq = qmul(q, lq);
+            if (type == CB200_TRIANGLE) {
+                // GenerateAABB :524-535 and PreprocessLocalToParent (CMC/ChNarrowphase.cpp:186-194): the vertices are
+                // given in the BODY frame; no envelope on a triangle's box.  The world vertices (triangle_global) take
+                // the shape's wpos / wrot / dims.yzw slots, which a triangle has no other use for (mpr.cuh ShapeView).
+                const double* t = s_verts + 3 * (size_t)dm.x;
+                const d3 A = rotate(mk3(t[0], t[1], t[2]), q) + p;
+                const d3 B = rotate(mk3(t[3], t[4], t[5]), q) + p;
+                const d3 C = rotate(mk3(t[6], t[7], t[8]), q) + p;
+                reinterpret_cast<double4*>(s_wpos)[i] = make_double4(A.x, A.y, A.z, dm.x);
+                reinterpret_cast<double4*>(s_wrot)[i] = make_double4(B.x, B.y, B.z, 0.0);
+                s_dims[4 * i + 1] = C.x, s_dims[4 * i + 2] = C.y, s_dims[4 * i + 3] = C.z;
+                amin = min3(A, min3(B, C));
+                amax = max3(A, max3(B, C));
+                ShapeBox b;
+                b.mn[0] = amin.x, b.mn[1] = amin.y, b.mn[2] = amin.z;
+                b.mx[0] = amax.x, b.mx[1] = amax.y, b.mx[2] = amax.z;
+                s_box[i] = b;
+                if (m.info & 2u) {
+                    mn = min3(mn, amin);
+                    mx = max3(mx, amax);
+                    counted = true;
+                }
+                continue;
+            }
             reinterpret_cast<double4*>(s_wpos)[i] = make_double4(wp.x, wp.y, wp.z, dm.x);
             reinterpret_cast<double4*>(s_wrot)[i] = make_double4(wq.w, wq.x, wq.y, wq.z);
             if (type == CB200_SPHERE) {
@@ -135,6 +160,28 @@ __global__ void __launch_bounds__(256) k_aabb(uint32_t ns, const ShapeMeta* __re
                     t = abs_rotate(wq, mk3(dm.x, dm.y, dm.z) + dm.w + envelope);
                 } else if (type == CB200_CAPSULE) {
                     t = abs_rotate(wq, mk3(dm.x, dm.x + dm.y, dm.x) + envelope);
+                } else if (type == CB200_CONVEXHULL) {
+                    // ComputeAABBConvex, CMC/ChCollisionSystemMulticore.cpp:424-456: Rotate(point + lpos, body*local)
+                    const double* h = s_verts + 3 * (size_t)dm.x;
+                    const int nv = (int)dm.y;
+                    d3 lo = rotate(mk3(h[0], h[1], h[2]) + lp, wq) + p, hi = lo;
+                    for (int k = 0; k < nv; k++) {
+                        const d3 c = rotate(mk3(h[3 * k], h[3 * k + 1], h[3 * k + 2]) + lp, wq) + p;
+                        lo = min3(lo, c);
+                        hi = max3(hi, c);
+                    }
+                    amin = lo - envelope;
+                    amax = hi + envelope;
+                    ShapeBox b;
+                    b.mn[0] = amin.x, b.mn[1] = amin.y, b.mn[2] = amin.z;
+                    b.mx[0] = amax.x, b.mx[1] = amax.y, b.mx[2] = amax.z;
+                    s_box[i] = b;
+                    if (m.info & 2u) {
+                        mn = min3(mn, amin);
+                        mx = max3(mx, amax);
+                        counted = true;
+                    }
+                    continue;
                 } else {
                     ok = false;  // type without an AABB rule: the reference `continue`s and keeps stale values
                 }
@@ -513,7 +560,7 @@ int enqueue_aabb(System* S) {
     }
     k_reset_counters<<<1, 32, 0, S->stream>>>(S->d_cnt, S->nb, S->ns);
     CB_CUDA(cudaMemsetAsync(S->heavy.p, 0, S->nb, S->stream));
-    k_aabb<<<grid_for(S, S->ns, 256), 256, 0, S->stream>>>(S->ns, S->s_meta.p, S->s_lpos.p, S->s_lrot.p, S->s_dims.p,
+    k_aabb<<<grid_for(S, S->ns, 256), 256, 0, S->stream>>>(S->ns, S->s_meta.p, S->s_lpos.p, S->s_lrot.p, S->s_dims.p, S->s_verts.p,
                                                            S->pos.p, S->rot.p, S->set.collision_envelope, S->s_wpos.p,
                                                            S->s_wrot.p, S->s_box.p, S->d_cnt);
     S->launches += 2;

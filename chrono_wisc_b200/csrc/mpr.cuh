@@ -25,7 +25,16 @@ struct ShapeView {
     d3 pos;
     q4 rot;
     double d0, d1, d2, d3_;
+    // CONVEXHULL: the hull's points in the shape frame (nv of them, 3 doubles each); unused by every other type.
+    // TRIANGLE: the three WORLD vertices (shape_container::triangle_global) ride in pos, (rot.w, rot.x, rot.y) and
+    // (d1, d2, d3_) -- a triangle has no frame or dimensions of its own (k_aabb packs them, tri_vertex reads them).
+    const double* hull;
+    int nv;
 };
+
+HD d3 tri_vertex(const ShapeView& S, int i) {
+    return i == 0 ? S.pos : (i == 1 ? mk3(S.rot.w, S.rot.x, S.rot.y) : mk3(S.d1, S.d2, S.d3_));
+}
 
 // MM/real.h:59-68
 HD double sign1(double x) { return x < 0 ? -1.0 : (x > 0 ? 1.0 : 0.0); }
@@ -94,6 +103,19 @@ HD d3 support_local(const ShapeView& S, const d3& nv, double envelope) {
         case CB200_ROUNDEDCYL:
             p = support_cylinder(S.d0, S.d2, n) + S.d3_ * n;
             break;
+        case CB200_CONVEXHULL: {  // GetSupportPoint_Convex, ChCollisionUtils.h:358-370
+            double best = -DBL_MAX;
+            p = mk3(S.hull[0], S.hull[1], S.hull[2]);
+            for (int i = 0; i < S.nv; i++) {
+                const d3 q = mk3(S.hull[3 * i], S.hull[3 * i + 1], S.hull[3 * i + 2]);
+                const double dp = dot3(q, n);
+                if (dp > best) {
+                    best = dp;
+                    p = q;
+                }
+            }
+            break;
+        }
         default:
             break;
     }
@@ -103,6 +125,19 @@ HD d3 support_local(const ShapeView& S, const d3& nv, double envelope) {
 
 // TransformSupportVert, ChCollisionUtilsMPR.cpp:76-97
 HD d3 support_world(const ShapeView& S, const d3& n, double envelope) {
+    if (S.type == CB200_TRIANGLE) {
+        // world vertices, direction used as given (not normalised); GetSupportPoint_Triangle, ChCollisionUtils.h:227-243
+        const d3 t0 = tri_vertex(S, 0), t1 = tri_vertex(S, 1), t2 = tri_vertex(S, 2);
+        double dist = dot3(t0, n);
+        d3 point = t0;
+        if (dot3(t1, n) > dist) {
+            dist = dot3(t1, n);
+            point = t1;
+        }
+        if (dot3(t2, n) > dist)
+            point = t2;
+        return point + envelope * n;
+    }
     return local_to_parent(S.pos, S.rot, support_local(S, rotate_t(n, S.rot), envelope));
 }
 
@@ -171,11 +206,25 @@ HD bool portal_reach_tolerance(const MprPortal& P, const d3& n) {
     return is_equal(m12, MPR_TOL) || m13 < MPR_TOL;
 }
 
-// DiscoverPortal, ChNarrowphaseMPR.cpp:487-555.  Shape centres: all supported types are locally centred (:48-51).
+// GetCenter, ChNarrowphaseMPR.cpp:40-55: a triangle's centroid; a hull's mean point as stored (shape frame, NOT
+// rotated) plus the shape's world position [sic]; every other type is centred on its frame.
+HD d3 shape_center(const ShapeView& S) {
+    if (S.type == CB200_TRIANGLE)
+        return (tri_vertex(S, 0) + tri_vertex(S, 1) + tri_vertex(S, 2)) * (1.0 / 3.0);
+    if (S.type == CB200_CONVEXHULL) {
+        d3 point = mk3(0);
+        for (int i = 0; i < S.nv; i++)
+            point += mk3(S.hull[3 * i], S.hull[3 * i + 1], S.hull[3 * i + 2]);
+        return point / (double)S.nv + S.pos;
+    }
+    return S.pos;
+}
+
+// DiscoverPortal, ChNarrowphaseMPR.cpp:487-555.
 __device__ inline int discover_portal(const ShapeView& A, const ShapeView& B, double envelope, MprPortal& P) {
     d3 n;
-    P.s0.v1 = A.pos;
-    P.s0.v2 = B.pos;
+    P.s0.v1 = shape_center(A);
+    P.s0.v2 = shape_center(B);
     P.s0.v = P.s0.v2 - P.s0.v1;
     if (is_zero3(P.s0.v))
         P.s0.v = mk3(1, 0, 0);

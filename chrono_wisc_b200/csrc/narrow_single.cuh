@@ -15,6 +15,7 @@ __device__ __forceinline__ ShapeView make_view(uint32_t id, int type, const doub
     v.pos = mk3(w.x, w.y, w.z);
     v.d0 = w.w;
     v.d1 = v.d2 = v.d3_ = 0;
+    v.hull = nullptr, v.nv = 0;  // a hull never has a single-contact analytic test: it is seen by the complex path only
     v.rot = mkq(1, 0, 0, 0);
     if (type != CB200_SPHERE) {
         const double4 r = reinterpret_cast<const double4*>(s_wrot)[id];
@@ -46,6 +47,8 @@ __device__ __forceinline__ int prims_single(const ShapeView& A, const ShapeView&
                 return box_sphere(A.pos, A.rot, mk3(A.d0, A.d1, A.d2), B.pos, B.d0, sep, c) ? 1 : 0;
             case CB200_ROUNDEDBOX:
                 return roundedbox_sphere(A.pos, A.rot, mk3(A.d0, A.d1, A.d2), A.d3_, B.pos, B.d0, sep, c) ? 1 : 0;
+            case CB200_TRIANGLE:
+                return triangle_sphere(tri_vertex(A, 0), tri_vertex(A, 1), tri_vertex(A, 2), B.pos, B.d0, sep, c) ? 1 : 0;
             default:
                 return -1;
         }
@@ -68,6 +71,9 @@ __device__ __forceinline__ int prims_single(const ShapeView& A, const ShapeView&
                 break;
             case CB200_ROUNDEDBOX:
                 hit = roundedbox_sphere(B.pos, B.rot, mk3(B.d0, B.d1, B.d2), B.d3_, A.pos, A.d0, sep, c);
+                break;
+            case CB200_TRIANGLE:
+                hit = triangle_sphere(tri_vertex(B, 0), tri_vertex(B, 1), tri_vertex(B, 2), A.pos, A.d0, sep, c);
                 break;
             default:
                 return -1;

@@ -132,13 +132,19 @@ __device__ __forceinline__ ShapeView make_view_full(uint32_t id, const ShapeMeta
                                                     const double* __restrict__ s_wrot,
                                                     const double* __restrict__ s_dims,
                                                     const double* __restrict__ s_lrot,
-                                                    const double* __restrict__ rot) {
+                                                    const double* __restrict__ rot,
+                                                    const double* __restrict__ s_verts) {
     ShapeView v;
     v.type = (m.info >> 8) & 0xff;
+    v.hull = nullptr, v.nv = 0;
     const double4 w = reinterpret_cast<const double4*>(s_wpos)[id];
     v.pos = mk3(w.x, w.y, w.z);
     const double4 d = reinterpret_cast<const double4*>(s_dims)[id];
     v.d0 = d.x, v.d1 = d.y, v.d2 = d.z, v.d3_ = d.w;
+    if (v.type == CB200_CONVEXHULL) {  // dims = (first vertex, count) into the vertex pool
+        v.hull = s_verts + 3 * (size_t)d.x;
+        v.nv = (int)d.y;
+    }
     if (m.info & 4u) {
         const double4 qa = reinterpret_cast<const double4*>(rot)[m.body];
         const double4 la = reinterpret_cast<const double4*>(s_lrot)[id];
@@ -162,6 +168,8 @@ __device__ __forceinline__ uint32_t pair_slots(int tA, int tB, int algorithm) {
         return 8;
     if (tA == CB200_BOX && tB == CB200_BOX)
         return 8;
+    if ((tA == CB200_BOX && tB == CB200_TRIANGLE) || (tA == CB200_TRIANGLE && tB == CB200_BOX))
+        return 6;  // slots only: PRIMSCollision reports triangle_box as unsupported (:1590-1603), MPR decides in HYBRID
     return 1;
 }
 
@@ -609,7 +617,8 @@ __global__ void __launch_bounds__(128) k_cplx_narrow(const ShapeMeta* __restrict
                                                      const double* __restrict__ s_wrot,
                                                      const double* __restrict__ s_dims,
                                                      const double* __restrict__ s_lrot,
-                                                     const double* __restrict__ rot, double envelope, int algorithm,
+                                                     const double* __restrict__ rot,
+                                                     const double* __restrict__ s_verts, double envelope, int algorithm,
                                                      const uint32_t* __restrict__ rec, uint32_t cap_rec,
                                                      uint32_t cap_slots, uint32_t* __restrict__ cplx_n,
                                                      double* __restrict__ cplx_out, uint32_t* __restrict__ ent_cnt,
@@ -631,8 +640,8 @@ __global__ void __launch_bounds__(128) k_cplx_narrow(const ShapeMeta* __restrict
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nrec; i += gridDim.x * blockDim.x) {
         const uint4 r = reinterpret_cast<const uint4*>(rec)[i];
         const ShapeMeta mA = meta[r.y], mB = meta[r.z];
-        const ShapeView A = make_view_full(r.y, mA, s_wpos, s_wrot, s_dims, s_lrot, rot);
-        const ShapeView B = make_view_full(r.z, mB, s_wpos, s_wrot, s_dims, s_lrot, rot);
+        const ShapeView A = make_view_full(r.y, mA, s_wpos, s_wrot, s_dims, s_lrot, rot, s_verts);
+        const ShapeView B = make_view_full(r.z, mB, s_wpos, s_wrot, s_dims, s_lrot, rot, s_verts);
         Contact out[MAX_PAIR_CONTACTS];
         int n = narrow_complex(A, B, algorithm, envelope, out);
         if (n < 0) {
@@ -829,7 +838,8 @@ static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
             S->s_meta.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p, S->ent_cmask.p, algorithm, S->ent_cbase.p,
             S->cplx_rec.p, S->cap_complex, S->d_cnt);
         k_cplx_narrow<<<grid_for(S, S->cap_complex, 128), 128, 0, S->stream>>>(
-            S->s_meta.p, S->s_wpos.p, S->s_wrot.p, S->s_dims.p, S->s_lrot.p, S->rot.p, env, algorithm, S->cplx_rec.p,
+            S->s_meta.p, S->s_wpos.p, S->s_wrot.p, S->s_dims.p, S->s_lrot.p, S->rot.p, S->s_verts.p, env, algorithm,
+            S->cplx_rec.p,
             S->cap_complex, S->cap_cslots, S->cplx_n.p, S->cplx_out.p, S->ent_off.p, S->d_cnt);
         S->launches += 3;
     } else {

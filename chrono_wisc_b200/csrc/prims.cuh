@@ -197,4 +197,83 @@ HD bool roundedbox_sphere(const d3& pos1, const q4& rot1, const d3& hdims1, doub
     return true;
 }
 
+// ChCollisionUtils.h:467-474
+HD d3 triangle_normal(const d3& A, const d3& B, const d3& C) {
+    const d3 n = cross3(B - A, C - A);
+    return n / length3(n);
+}
+
+// ChCollisionUtilsPRIMS.cpp:41-106 (Ericson's closest point on a triangle): true when `res` lies on the boundary
+HD bool snap_to_triangle(const d3& A, const d3& B, const d3& C, const d3& P, d3& res) {
+    const d3 AB = B - A, AC = C - A, AP = P - A;
+    const double d1 = dot3(AB, AP), d2 = dot3(AC, AP);
+    if (d1 <= 0 && d2 <= 0) {
+        res = A;
+        return true;
+    }
+    const d3 BP = P - B;
+    const double d3_ = dot3(AB, BP), d4 = dot3(AC, BP);
+    if (d3_ >= 0 && d4 <= d3_) {
+        res = B;
+        return true;
+    }
+    const double vc = d1 * d4 - d3_ * d2;
+    if (vc <= 0 && d1 >= 0 && d3_ <= 0) {
+        const double v = d1 / (d1 - d3_);
+        res = A + v * AB;
+        return true;
+    }
+    const d3 CP = P - C;
+    const double d5 = dot3(AB, CP), d6 = dot3(AC, CP);
+    if (d6 >= 0 && d5 <= d6) {
+        res = C;
+        return true;
+    }
+    const double vb = d5 * d2 - d1 * d6;
+    if (vb <= 0 && d2 >= 0 && d6 <= 0) {
+        const double w = d2 / (d2 - d6);
+        res = A + w * AC;
+        return true;
+    }
+    const double va = d3_ * d6 - d5 * d4;
+    if (va <= 0 && (d4 - d3_) >= 0 && (d5 - d6) >= 0) {
+        const double w = (d4 - d3_) / ((d4 - d3_) + (d5 - d6));
+        res = B + w * (C - B);
+        return true;
+    }
+    const double denom = 1 / (va + vb + vc);
+    const double v = vb * denom;
+    const double w = vc * denom;
+    res = A + v * AB + w * AC;
+    return false;
+}
+
+// ChNarrowphasePRIMS.cpp:379-434: one-sided (a sphere centre below the face plane gives no contact)
+HD bool triangle_sphere(const d3& A1, const d3& B1, const d3& C1, const d3& pos2, double r2, double separation,
+                        Contact& c) {
+    const double r2_s = r2 + separation;
+    const d3 nrm1 = triangle_normal(A1, B1, C1);
+    const double h = dot3(pos2 - A1, nrm1);
+    if (h >= r2_s || h <= 0)
+        return false;
+    d3 faceLoc;
+    if (snap_to_triangle(A1, B1, C1, pos2, faceLoc)) {
+        const d3 delta = pos2 - faceLoc;
+        const double dist2 = dot3(delta, delta);
+        if (dist2 >= r2_s * r2_s || dist2 <= TINY_F)
+            return false;
+        const double dist = sqrt(dist2);
+        c.n = delta / dist;
+        c.depth = dist - r2;
+        c.erad = r2 * EDGE_RADIUS / (r2 + EDGE_RADIUS);
+    } else {
+        c.n = nrm1;
+        c.depth = h - r2;
+        c.erad = r2;
+    }
+    c.p1 = faceLoc;
+    c.p2 = pos2 - c.n * r2;
+    return true;
+}
+
 }  // namespace cb200

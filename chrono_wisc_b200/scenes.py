@@ -8,7 +8,7 @@ identical bits.
 """
 import numpy as np
 
-from .system import (BOX, CAPSULE, SPHERE, FIXED_BIN_SIZE, FIXED_DENSITY, FIXED_RESOLUTION, HERTZ, HYBRID, MODE_SLIDING,
+from .system import (BOX, CAPSULE, CONVEXHULL, SPHERE, TRIANGLE, FIXED_BIN_SIZE, FIXED_DENSITY, FIXED_RESOLUTION, HERTZ, HYBRID, MODE_SLIDING,
                      SOLVER_APGD)
 
 SMC_MAT_FIELDS = ("young_modulus", "poisson_ratio", "static_friction", "sliding_friction", "rolling_friction",
@@ -37,6 +37,25 @@ class SceneBuilder:
         self.mass, self.inertia, self.pos, self.rot, self.vel, self.active, self.collide = [], [], [], [], [], [], []
         self.s_type, self.s_body, self.s_dims, self.s_pos, self.s_rot, self.s_fam, self.s_mat = [], [], [], [], [], [], []
         self.nb = 0
+        self.verts = []  # vertex pool of triangles (body frame) and convex hulls (shape frame)
+        self.nv = 0
+
+    def add_vertices(self, xyz):
+        """Append points to the vertex pool; returns the index of the first."""
+        xyz = np.asarray(xyz, dtype=np.float64).reshape(-1, 3)
+        first = self.nv
+        self.verts.append(xyz)
+        self.nv += xyz.shape[0]
+        return first
+
+    def add_triangle(self, body, v0, v1, v2, **kw):
+        """ChCollisionShapeTriangle on `body`: vertices in the body frame (triangle_rigid)."""
+        self.add_shapes(TRIANGLE, [body], [[self.add_vertices([v0, v1, v2]), 3, 0, 0]], **kw)
+
+    def add_convex_hull(self, body, points, **kw):
+        """ChCollisionShapeConvexHull on `body`: points in the shape frame (convex_rigid)."""
+        points = np.asarray(points, dtype=np.float64).reshape(-1, 3)
+        self.add_shapes(CONVEXHULL, [body], [[self.add_vertices(points), points.shape[0], 0, 0]], **kw)
 
     def add_bodies(self, mass, inertia, pos, rot=None, vel=None, active=1, collide=1):
         pos = np.atleast_2d(np.asarray(pos, dtype=np.float64))
@@ -99,7 +118,7 @@ class SceneBuilder:
             shape_body=cat(self.s_body).astype(np.uint32), shape_dims=cat(self.s_dims), shape_pos=cat(self.s_pos),
             shape_rot=cat(self.s_rot), shape_fam=cat(self.s_fam).astype(np.int16),
             shape_mat=cat(self.s_mat).astype(np.int32), materials=np.atleast_2d(np.asarray(materials, np.float32)),
-            settings=dict(settings))
+            shape_verts=cat(self.verts) if self.verts else np.zeros((0, 3)), settings=dict(settings))
 
 
 def lattice_positions(nx, ny, nz, spacing, jitter, z0, seed):

@@ -130,6 +130,14 @@ class ChSystemMulticore:
                                             _ptr(dims), _ptr(mat)))
         self.num_shapes += n
 
+    def AddShapeVertices(self, xyz):
+        """Append points to the vertex pool of triangles (body frame) and convex hulls (shape frame) --
+        shape_container::triangle_rigid / convex_rigid (CMC/ChCollisionData.h:35-59).  Returns the first index."""
+        xyz = _f64(xyz, (-1, 3))
+        first = C.c_int(0)
+        check(self._lib.cb200_append_shape_vertices(self._h, xyz.shape[0], _ptr(xyz), C.byref(first)))
+        return first.value
+
     def SetMaterials(self, table):
         table = np.ascontiguousarray(table, dtype=np.float32)
         if self.system_type == 1:
@@ -353,6 +361,8 @@ def load_scene(sys_, scene):
             setattr(st, k, v)
     sys_.AddBodies(scene["mass"], scene["inertia"], scene["pos"], scene["rot"], scene["vel"], scene["active"],
                    scene["collide"])
+    if scene.get("shape_verts") is not None and len(scene["shape_verts"]):
+        assert sys_.AddShapeVertices(scene["shape_verts"]) == 0
     sys_.AddShapes(scene["shape_type"], scene["shape_body"], scene["shape_dims"], scene["shape_pos"],
                    scene["shape_rot"], scene["shape_fam"], scene["shape_mat"])
     sys_.SetMaterials(scene["materials"])

@@ -130,10 +130,17 @@ int cb200_append_bodies(cb200_system* sys, int n, const double* mass, const doub
 /* ChCollisionSystemMulticore::Add (CMC/ChCollisionSystemMulticore.cpp:86-187): append n shapes as shape_container
  * slices.  dims is 4 doubles per shape: sphere (r,-,-,-); ellipsoid/box/cylinder/cylshell/cone (B.x,B.y,B.z,-);
  * capsule (radius, hlen-as-stored,-,-) [sic, SURVEY Appendix A.1]; rounded box/cyl (x,y,z,sweep radius).
+ * triangle / convex hull (first vertex, vertex count, -, -) into the pool of cb200_append_shape_vertices.
  * fam is (group, mask) int16 pairs.  material_id indexes the table given to cb200_set_materials_*. */
 int cb200_append_shapes(cb200_system* sys, int n, const int32_t* type, const uint32_t* body_id, const int16_t* fam,
                         const double* pos_local, const double* rot_local, const double* dims,
                         const int32_t* material_id);
+
+/* shape_container::triangle_rigid and ::convex_rigid (CMC/ChCollisionData.h:35-59) as one vertex pool: append n
+ * points (3 doubles each) and get the index of the first in *first.  A triangle's three vertices are in the BODY
+ * frame (GenerateAABB, CMC/ChCollisionSystemMulticore.cpp:524-535), a hull's points in the SHAPE frame (:424-456).
+ * Add the vertices before the shapes that refer to them. */
+int cb200_append_shape_vertices(cb200_system* sys, int n, const double* xyz, int* first);
 
 /* Per-shape contact materials replacing the per-contact pointer chase of
  * ChContactContainerMulticoreSMC::AddContact (MC/collision/ChContactContainerMulticoreSMC.cpp:123-174).

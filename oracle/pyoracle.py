@@ -93,8 +93,24 @@ class Ref:
         fam = np.ascontiguousarray(scene["shape_fam"], dtype=np.int16)
         oba, obr, dims = _f64(scene["shape_pos"]), _f64(scene["shape_rot"]), _f64(scene["shape_dims"])
         self.ns = typ.size
+        # vertex pool (scene["shape_verts"], dims = (first vertex, count)) -> the driver's conventions: triangles
+        # index a list of 9-double triangles, hulls give (count, offset) into convex_rigid (the whole pool)
+        verts = _f64(scene["shape_verts"]) if scene.get("shape_verts") is not None else np.zeros((0, 3))
+        tri = np.zeros((0, 9))
+        if verts.size:
+            dims = dims.reshape(-1, 4).copy()
+            tsel = np.flatnonzero(typ == 10)
+            tri = np.ascontiguousarray(
+                np.stack([verts.reshape(-1, 3)[int(dims[i, 0]):int(dims[i, 0]) + 3].ravel() for i in tsel])
+                if tsel.size else np.zeros((0, 9)))
+            dims[tsel, 0] = np.arange(tsel.size)
+            hsel = np.flatnonzero(typ == 5)
+            dims[hsel, 0], dims[hsel, 1] = dims[hsel, 1].copy(), dims[hsel, 0].copy()
+            dims = np.ascontiguousarray(dims)
+        self._keep = (verts, tri, dims)
         self.L.ref_set_shapes(self.h, C.c_int(typ.size), _p(typ), _p(body), _p(fam), _p(oba), _p(obr), _p(dims),
-                              None, C.c_int(0), None)
+                              _p(tri) if tri.size else None, C.c_int(verts.size // 3),
+                              _p(verts) if verts.size else None)
 
     def set_settings(self, envelope, grid_type, res, bin_size, density, algorithm):
         res = np.ascontiguousarray(res, dtype=np.int32)

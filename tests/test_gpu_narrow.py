@@ -10,8 +10,8 @@ import pytest
 
 import chrono_wisc_b200 as cw
 from chrono_wisc_b200 import scenes
-from chrono_wisc_b200.system import (BOX, CAPSULE, CONE, CYLINDER, CYLSHELL, ELLIPSOID, ROUNDEDBOX, ROUNDEDCYL,
-                                     SPHERE)
+from chrono_wisc_b200.system import (BOX, CAPSULE, CONE, CONVEXHULL, CYLINDER, CYLSHELL, ELLIPSOID, ROUNDEDBOX,
+                                     ROUNDEDCYL, SPHERE, TRIANGLE)
 
 pytestmark = pytest.mark.gpu
 
@@ -53,7 +53,15 @@ def cluttered(kinds, n_side, spacing, seed, algorithm, envelope, aligned=False, 
                     q /= np.linalg.norm(q)
                 bid = b.add_bodies(1.0, (0.01, 0.01, 0.01), [p], rot=[q])
                 t = kinds[i % len(kinds)]
-                b.add_shapes(t, [bid], [DIMS[t]])
+                if t == TRIANGLE:  # three body-frame vertices around the body origin
+                    v = rng.uniform(-0.12, 0.12, (3, 3))
+                    b.add_triangle(bid, v[0], v[1], v[2])
+                elif t == CONVEXHULL:  # 4..12 shape-frame points, offset shape frame
+                    pts = rng.uniform(-0.09, 0.09, (int(rng.integers(4, 13)), 3))
+                    ql = rng.normal(size=4)
+                    b.add_convex_hull(bid, pts, pos=[rng.uniform(-0.02, 0.02, 3)], rot=[ql / np.linalg.norm(ql)])
+                else:
+                    b.add_shapes(t, [bid], [DIMS[t]])
                 i += 1
     # the SMC system runs with a zero envelope (ChSystemMulticoreSMC.cpp:27); a non-zero one is an NSC scene
     nsc = envelope > 0
@@ -122,6 +130,57 @@ def test_box_cylshell(ref, algorithm, aligned):
         types = scene["shape_type"]
         seen = set(zip(types[rk["shape_ids"] >> 32], types[rk["shape_ids"] & 0xFFFFFFFF]))
         assert (BOX, CYLSHELL) in seen or (CYLSHELL, BOX) in seen, seen
+
+
+@pytest.mark.parametrize("envelope", [0.0, 0.01])
+@pytest.mark.parametrize("algorithm", [MPR, PRIMS, HYBRID])
+def test_triangles_and_hulls(ref, algorithm, envelope):
+    """Triangles (triangle_sphere, ChNarrowphasePRIMS.cpp:379-434; GetSupportPoint_Triangle / GetCenter_Triangle under
+    MPR) and convex hulls (GetSupportPoint_Convex, GetCenter_Convex) among spheres, boxes and capsules.  A
+    triangle-box pair reserves 6 slots but PRIMSCollision reports it unsupported (:1590-1603): MPR decides it in
+    HYBRID mode, PRIMS mode gives no contact."""
+    scene = cluttered([SPHERE, TRIANGLE, BOX, CONVEXHULL, SPHERE, CAPSULE, TRIANGLE], 7, 0.14, 21, algorithm, envelope)
+    scene, rk = compare(scene, ref, 150)
+    types = scene["shape_type"]
+    seen = set(zip(types[rk["shape_ids"] >> 32], types[rk["shape_ids"] & 0xFFFFFFFF]))
+    assert (SPHERE, TRIANGLE) in seen or (TRIANGLE, SPHERE) in seen, seen
+    if algorithm != PRIMS:
+        assert any(CONVEXHULL in p for p in seen), seen
+        assert any(TRIANGLE in p and SPHERE not in p for p in seen), seen
+
+
+def test_triangle_mesh_floor_step(ref):
+    """A bed of spheres dropped on a triangulated floor (the tire-proxy / mesh-terrain use of triangle_sphere): contact
+    list vs the reference, then one SMC step vs the reference force function on that list (1e-10 relative)."""
+    from oracle import np_oracle
+
+    b = scenes.SceneBuilder()
+    rng = np.random.default_rng(5)
+    floor = b.add_bodies(1.0, (1, 1, 1), [[0, 0, 0]], active=0)
+    n, s = 8, 0.05
+    z = rng.uniform(-0.004, 0.004, (n + 1, n + 1))
+    for i in range(n):
+        for j in range(n):
+            p = lambda a, c: [a * s, c * s, z[a, c]]
+            b.add_triangle(floor, p(i, j), p(i + 1, j), p(i + 1, j + 1))
+            b.add_triangle(floor, p(i, j), p(i + 1, j + 1), p(i, j + 1))
+    r = 0.02
+    pos = [[(i + 0.5) * 0.041 + 0.02, (j + 0.5) * 0.041 + 0.02, r - 0.003 + 0.002 * rng.random()] for i in range(8)
+           for j in range(8)]
+    ids = b.add_bodies(0.01, (1e-5, 1e-5, 1e-5), pos) + np.arange(len(pos))
+    b.add_shapes(SPHERE, ids, [[r, 0, 0, 0]])
+    settings = dict(system_type=1, step_size=1e-4, gravity=(0, 0, -9.81), broadphase_grid=2, grid_density=5.0,
+                    narrowphase_algorithm=HYBRID, collision_envelope=0.0)
+    scene = b.finish([scenes.smc_material()], settings)
+    scene, rk = compare(scene, ref, 60)
+    sys = cw.load_scene(cw.ChSystemMulticoreSMC(), scene)
+    sys.DoStepDynamics()
+    _, _, vel = sys.GetBodyState()
+    ref.set_scene(scene)
+    p, q, v, info = np_oracle.smc_step(scene, ref, scene["pos"], scene["rot"], scene["vel"])
+    assert info["contacts"]["depth"].size == sys.GetNumContacts()
+    err = np.abs(vel - v).max() / np.abs(v).max()
+    assert err < 1e-10, err
 
 
 def test_spheres_only_under_mpr(ref):
