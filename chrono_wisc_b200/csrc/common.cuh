@@ -212,6 +212,13 @@ struct System {
     // ---- SMC (MC/solver/ChIterativeSolverMulticoreSMC.cpp) ----
     DevBuf<double> ct_force;    // 3 N_c  force on body 2 (body 1 gets the negative)
     DevBuf<double> ct_torque;   // 6 N_c  torque on body 1, torque on body 2 (body frames)
+    // MultiStep tangential displacement history, 20 slots per body (allocated on first use, smc.cu)
+    DevBuf<int32_t> sh_neigh;   // 3 x 20 nb
+    DevBuf<uint8_t> sh_touch;   // 20 nb
+    DevBuf<double> sh_disp;     // 3 x 20 nb
+    DevBuf<double> sh_relvel;   // 20 nb
+    DevBuf<double> sh_dur;      // 20 nb
+    uint32_t sh_bodies = 0;     // bodies the history arrays are initialised for
     DevBuf<uint32_t> b_deg;     // nb+1 incidence counts -> offsets
     DevBuf<uint32_t> b_cursor;  // nb
     DevBuf<uint32_t> b_inc;     // 2 N_c incidence list: contact << 1 | side
@@ -282,6 +289,7 @@ int enqueue_bins(System* S);                                             // broa
 int enqueue_broadphase(System* S, bool want_pairs, bool want_contacts);  // broadphase.cu
 int enqueue_pairs_only(System* S, bool want_pairs, bool want_contacts, bool defer_geometry = false);  // pairs.cu
 int ensure_contact_geometry(System* S);  // pairs.cu: contact records on demand
+int alloc_shear(System* S);                                              // smc.cu: MultiStep history arrays
 int enqueue_smc(System* S);                                              // smc.cu
 int enqueue_nsc(System* S);                                              // nsc.cu
 int nsc_contact_forces_inactive(System* S);                              // nsc.cu: on-demand part of CalculateContactForces

@@ -62,6 +62,18 @@ struct GenArgs {
     uint32_t* mats_out;
 };
 
+// MultiStep tangential displacement (ChSystemSMC::TangentialDisplacementModel::MultiStep): per body MAX_SHEAR history
+// slots (MC/ChDataManager.h:198, host_container::shear_neigh / shear_disp / contact_relvel_init / contact_duration)
+#define MAX_SHEAR 20
+struct ShearArgs {
+    const int64_t* keys;  // contact_shapeIDs: the shape pair of every contact
+    int32_t* neigh;       // 3 per slot: partner body, larger shape id, smaller shape id; x == -1: free
+    uint8_t* touch;       // slot used in this step
+    double* disp;         // 3 per slot
+    double* relvel0;      // |normal relative velocity| when the contact began
+    double* duration;
+};
+
 // cold path: a contact that involves a non-sphere
 __device__ __noinline__ void contact_general(uint32_t sA, int tA, double4 wA, uint32_t sB, int tB, double4 wB,
                                              double sep, const double* __restrict__ s_wrot,
@@ -69,8 +81,9 @@ __device__ __noinline__ void contact_general(uint32_t sA, int tA, double4 wA, ui
     prims_single(make_view(sA, tA, wA, s_wrot, s_dims), make_view(sB, tB, wB, s_wrot, s_dims), sep, c);
 }
 
-template <int FORCE_MODEL, bool USE_MAT, bool GEN>
-__global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, GenArgs G, const int32_t* __restrict__ bids,
+template <int FORCE_MODEL, bool USE_MAT, bool GEN, bool MULTI>
+__global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, GenArgs G, ShearArgs H,
+                                                   const int32_t* __restrict__ bids,
                                                    const uint32_t* __restrict__ c_mats,
                                                    const double* __restrict__ c_norm, const double* __restrict__ c_pta,
                                                    const double* __restrict__ c_ptb, const double* __restrict__ c_depth,
@@ -79,11 +92,22 @@ __global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, GenArgs G, co
                                                    const double* __restrict__ mass, const double* __restrict__ mat,
                                                    const uint8_t* __restrict__ heavy, uint32_t* __restrict__ deg,
                                                    double* __restrict__ ct_force, double* __restrict__ ct_torque,
-                                                   const DevCounters* __restrict__ cnt) {
+                                                   DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
     const uint32_t nc = cnt->n_contacts;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nc; i += gridDim.x * blockDim.x) {
+    for (uint32_t i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < nc; i0 += gridDim.x * blockDim.x) {
+    // MULTI: the contacts of one shape pair share one history slot; the reference's loop visits them in list order
+    // (they are adjacent), so the thread of the pair's first contact walks the whole run
+    uint32_t run = 1;
+    if (MULTI) {
+        const int64_t k0 = H.keys[i0];
+        if (i0 > 0 && H.keys[i0 - 1] == k0)
+            continue;
+        while (i0 + run < nc && H.keys[i0 + run] == k0)
+            run++;
+    }
+    for (uint32_t i = i0; i < i0 + run; i++) {
     d3 force = mk3(0), tq1 = mk3(0), tq2 = mk3(0);
     Contact C;
     uint32_t b1, b2, mm;
@@ -157,12 +181,72 @@ __global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, GenArgs G, co
         const double user_kn = M[9], user_kt = M[10], user_gn = M[11], user_gt = M[12];
 
         double kn = 0, kt = 0, gn = 0, gt = 0, kn_simple = 0, gn_simple = 0;
-        const double t_contact = 0;
+        double t_contact = 0;
+        double relvel_init = fabs(relvel_n_mag);
         const double delta_n = -depth;
         d3 delta_t = mk3(0);
         if (P.displ_mode == 1)
             delta_t = relvel_t * P.dT;
         double char_vel = P.char_vel;
+        size_t slot = 0;        // MULTI: this contact's history slot
+        bool hist_on_b1 = false;
+        if (MULTI) {
+            // contact history lives on the body with the larger id, keyed by (partner, larger shape, smaller shape)
+            // (:188-250).  Which of the MAX_SHEAR slots a contact gets has no effect on the forces, so slots are
+            // claimed with an atomic instead of the reference's first-free scan in contact order.
+            delta_t = relvel_t * P.dT;
+            const int64_t key = H.keys[i];
+            const int s1 = (int)(key >> 32), s2 = (int)(key & 0xffffffff);
+            const int sb1 = max((int)b1, (int)b2), sb2 = min((int)b1, (int)b2);
+            const int ss1 = max(s1, s2), ss2 = min(s1, s2);
+            int cid = -1;
+            int32_t* nb_ = H.neigh + 3 * (size_t)MAX_SHEAR * sb1;
+            for (int k = 0; k < MAX_SHEAR; k++) {
+                if (nb_[3 * k] == sb2 && nb_[3 * k + 1] == ss1 && nb_[3 * k + 2] == ss2) {
+                    H.duration[(size_t)MAX_SHEAR * sb1 + k] += P.dT;
+                    cid = k;
+                    break;
+                }
+            }
+            if (cid < 0) {
+                for (int k = 0; k < MAX_SHEAR; k++) {
+                    // -2 while the claimer fills the key: neither free nor a match for a concurrent search
+                    if (nb_[3 * k] == -1 && atomicCAS(&nb_[3 * k], -1, -2) == -1) {
+                        cid = k;
+                        const size_t sl = (size_t)MAX_SHEAR * sb1 + k;
+                        nb_[3 * k + 1] = ss1, nb_[3 * k + 2] = ss2;
+                        H.disp[3 * sl] = 0, H.disp[3 * sl + 1] = 0, H.disp[3 * sl + 2] = 0;
+                        H.relvel0[sl] = relvel_init;
+                        H.duration[sl] = 0;
+                        __threadfence();
+                        atomicExch(&nb_[3 * k], sb2);
+                        break;
+                    }
+                }
+            }
+            if (cid < 0) {
+                // more than MAX_SHEAR partners: the reference indexes slot -1 here (:232); reported as an error
+                atomicAdd(&cnt->unsupported, 1u);
+                cid = 0;
+            }
+            slot = (size_t)MAX_SHEAR * sb1 + cid;
+            H.touch[slot] = 1;
+            hist_on_b1 = sb1 == (int)b1;
+            d3 sd = mk3(H.disp[3 * slot], H.disp[3 * slot + 1], H.disp[3 * slot + 2]);
+            if (hist_on_b1) {
+                sd += delta_t;
+                sd -= dot3(sd, n) * n;
+                delta_t = sd;
+            } else {
+                sd -= delta_t;
+                sd -= dot3(sd, n) * n;
+                delta_t = -sd;
+            }
+            H.disp[3 * slot] = sd.x, H.disp[3 * slot + 1] = sd.y, H.disp[3 * slot + 2] = sd.z;
+            const double r0 = H.relvel0[slot];
+            relvel_init = (r0 < char_vel) ? char_vel : r0;
+            t_contact = H.duration[slot];
+        }
         const double eps = DBL_EPSILON;
         bool done = false;
         // kn_simple / gn_simple only decide whether rolling / spinning friction is switched off (:485-495);
@@ -173,6 +257,8 @@ __global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, GenArgs G, co
             case 0:  // Hooke (:259-281)
                 if (USE_MAT) {
                     const double tmp_k = (16.0 / 15) * sqrt(erad) * E_eff;
+                    if (MULTI)
+                        char_vel = relvel_init;  // :258
                     const double v2 = char_vel * char_vel;
                     double loge = (cr_eff < eps) ? log(eps) : log(cr_eff);
                     loge = (cr_eff > 1 - eps) ? log(1 - eps) : loge;
@@ -222,6 +308,8 @@ __global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, GenArgs G, co
                     const double St = 8 * G_eff * sqrt_Rd;
                     cr_eff = (cr_eff < 0.01) ? 0.01 : cr_eff;
                     cr_eff = (cr_eff > 1.0 - eps) ? 1.0 - eps : cr_eff;
+                    if (MULTI)
+                        char_vel = relvel_init;  // :312
                     const double loge = log(cr_eff);
                     const double beta = loge / sqrt(loge * loge + CH_PI_D * CH_PI_D);
                     kn = CH_2_3_D * Sn;
@@ -279,6 +367,11 @@ __global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, GenArgs G, co
                 if (delta_t_mag > eps) {
                     const double ratio = forceT_slide / forceT_mag;
                     forceT *= ratio;
+                    if (MULTI) {  // the stored displacement is rescaled to the Coulomb limit (:460-467)
+                        delta_t = (forceT - forceT_damp) / kt;
+                        const d3 sd = hist_on_b1 ? delta_t : -delta_t;
+                        H.disp[3 * slot] = sd.x, H.disp[3 * slot + 1] = sd.y, H.disp[3 * slot + 2] = sd.z;
+                    }
                 } else {
                     forceT = mk3(0);
                 }
@@ -335,6 +428,18 @@ __global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, GenArgs G, co
     double* t = ct_torque + 6 * (size_t)i;
     t[0] = tq1.x, t[1] = tq1.y, t[2] = tq1.z, t[3] = tq2.x, t[4] = tq2.y, t[5] = tq2.z;
     }
+    }
+}
+
+// MultiStep: history slots that saw no contact in this step are released (...SMC.cpp:687-695)
+__global__ void __launch_bounds__(256) k_shear_sweep(uint32_t nslots, const uint8_t* __restrict__ touch,
+                                                     int32_t* __restrict__ neigh,
+                                                     const DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nslots && !touch[i])
+        neigh[3 * (size_t)i] = -1;
 }
 
 // ---- body -> contact incidence lists (counting sort by body id) ------------------------------------------------
@@ -544,13 +649,47 @@ __global__ void __launch_bounds__(256) k_vel_update(uint32_t nb, const uint8_t* 
     v[5] = v[5] + inv_inertia[3 * b + 2] * f[5];
 }
 
+// History arrays for MultiStep: slots of new bodies start free with zero displacement
+// (ChSystemMulticoreSMC::AddMaterialSurfaceData, MC/physics/ChSystemMulticoreSMC.cpp:39-50).
+int alloc_shear(System* S) {
+    const size_t nb = S->nb, n0 = S->sh_bodies;
+    if (nb <= n0)
+        return CB200_OK;
+    if (S->capturing)
+        return set_error(CB200_ERR_STATE, "shear history must be allocated before a step is captured");
+    if (3 * MAX_SHEAR * nb > S->sh_neigh.cap)
+        invalidate_step_graph(S);
+    cudaStream_t st = S->stream;
+    CB_TRY(S->sh_neigh.reserve(3 * MAX_SHEAR * nb, true, st));
+    CB_TRY(S->sh_touch.reserve(MAX_SHEAR * nb, true, st));
+    CB_TRY(S->sh_disp.reserve(3 * MAX_SHEAR * nb, true, st));
+    CB_TRY(S->sh_relvel.reserve(MAX_SHEAR * nb, true, st));
+    CB_TRY(S->sh_dur.reserve(MAX_SHEAR * nb, true, st));
+    const size_t a = MAX_SHEAR * n0, n = MAX_SHEAR * (nb - n0);
+    CB_CUDA(cudaMemsetAsync(S->sh_neigh.p + 3 * a, 0xff, 3 * n * sizeof(int32_t), st));  // (-1, -1, -1)
+    CB_CUDA(cudaMemsetAsync(S->sh_disp.p + 3 * a, 0, 3 * n * sizeof(double), st));
+    CB_CUDA(cudaMemsetAsync(S->sh_relvel.p + a, 0, n * sizeof(double), st));
+    CB_CUDA(cudaMemsetAsync(S->sh_dur.p + a, 0, n * sizeof(double), st));
+    S->sh_bodies = (uint32_t)nb;
+    return CB200_OK;
+}
+
 int enqueue_smc(System* S) {
     if (S->nb == 0)
         return CB200_OK;
     const uint32_t nb = S->nb;
     const cb200_settings& st = S->set;
-    if (st.tangential_displ_mode == 2)
-        return set_error(CB200_ERR_UNSUPPORTED, "MultiStep tangential displacement history is not implemented");
+    const bool multi = st.tangential_displ_mode == 2;
+    if (multi && S->slab_on)
+        return set_error(CB200_ERR_UNSUPPORTED, "MultiStep contact history does not migrate between slabs yet");
+    ShearArgs H = {};
+    if (multi) {
+        CB_TRY(alloc_shear(S));
+        CB_TRY(ensure_contact_geometry(S));  // the history variant reads the contact records
+        H.keys = S->c_shapes.p, H.neigh = S->sh_neigh.p, H.touch = S->sh_touch.p, H.disp = S->sh_disp.p;
+        H.relvel0 = S->sh_relvel.p, H.duration = S->sh_dur.p;
+        CB_CUDA(cudaMemsetAsync(S->sh_touch.p, 0, (size_t)MAX_SHEAR * nb, S->stream));
+    }
     if (S->ns > 0 && S->nm_smc == 0)
         return set_error(CB200_ERR_STATE, "cb200_set_materials_smc was not called");
     SmcParams P;
@@ -574,18 +713,19 @@ int enqueue_smc(System* S) {
     G.s_dims = S->s_dims.p, G.c_src = use_complex(S) ? S->c_src.p : nullptr, G.cplx_out = S->cplx_out.p;
     G.sep = 2 * S->set.collision_envelope, G.bids_out = S->c_bids.p, G.mats_out = S->c_mats.p;
     const bool gen = !S->contacts_geom_valid;  // the step skipped k_contact_gen: evaluate the geometry here
-#define SMC_LAUNCH2(FM, UM, GN)                                                                                     \
-    k_smc_force<FM, UM, GN><<<fgrid, 128, 0, S->stream>>>(P, G, S->c_bids.p, S->c_mats.p, S->c_norm.p, S->c_pta.p, \
-                                                          S->c_ptb.p, S->c_depth.p, S->c_erad.p, S->pos.p,         \
-                                                          S->rot.p, S->vel.p, S->mass.p, S->mat_smc.p,             \
-                                                          S->heavy.p, S->b_deg.p, S->ct_force.p, S->ct_torque.p,   \
-                                                          S->d_cnt)
+#define SMC_LAUNCH2(FM, UM, GN, MS)                                                                       \
+    k_smc_force<FM, UM, GN, MS><<<fgrid, 128, 0, S->stream>>>(                                            \
+        P, G, H, S->c_bids.p, S->c_mats.p, S->c_norm.p, S->c_pta.p, S->c_ptb.p, S->c_depth.p, S->c_erad.p, \
+        S->pos.p, S->rot.p, S->vel.p, S->mass.p, S->mat_smc.p, S->heavy.p, S->b_deg.p, S->ct_force.p,     \
+        S->ct_torque.p, S->d_cnt)
 #define SMC_LAUNCH(FM, UM)         \
     do {                           \
-        if (gen)                   \
-            SMC_LAUNCH2(FM, UM, true);  \
+        if (multi)                 \
+            SMC_LAUNCH2(FM, UM, false, true); \
+        else if (gen)              \
+            SMC_LAUNCH2(FM, UM, true, false);  \
         else                       \
-            SMC_LAUNCH2(FM, UM, false); \
+            SMC_LAUNCH2(FM, UM, false, false); \
     } while (0)
     // one instantiation per force model: the runtime switch of the reference (...SMC.cpp:258-440) costs registers
     const bool um = P.use_mat_props != 0;
@@ -600,6 +740,11 @@ int enqueue_smc(System* S) {
 #undef SMC_LAUNCH2
     CB_TRY(timer_stop(S, "k_smc_force"));
     S->launches++;
+    if (multi) {
+        k_shear_sweep<<<blocks_for(MAX_SHEAR * nb, 256), 256, 0, S->stream>>>(MAX_SHEAR * nb, S->sh_touch.p,
+                                                                              S->sh_neigh.p, S->d_cnt);
+        S->launches++;
+    }
     CB_TRY(scan_u32(S, S->b_deg.p, S->b_deg.p, &S->d_cnt->n_bodies, nb));
     k_inc_fill<<<cgrid, 256, 0, S->stream>>>(S->c_bids.p, S->heavy.p, S->b_deg.p, S->b_cursor.p, S->b_inc.p, S->d_cnt);
     k_heavy_list<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->heavy.p, S->heavy_list.p, S->d_cnt);

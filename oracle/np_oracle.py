@@ -133,7 +133,7 @@ def integrate(pos, rot, vel, h, active):
     return p, q
 
 
-def smc_step(scene, ref, pos, rot, vel, fast=True):
+def smc_step(scene, ref, pos, rot, vel, fast=True, history=None):
     """One full SMC step on the CPU: reference collision + reference force function + the glue above.
     Returns (pos, rot, vel, info)."""
     st = scene["settings"]
@@ -151,12 +151,14 @@ def smc_step(scene, ref, pos, rot, vel, fast=True):
         sa = (c["shape_ids"] >> 32).astype(np.int64)
         sb = (c["shape_ids"] & 0xFFFFFFFF).astype(np.int64)
         mats = composite_smc(scene["materials"], scene["shape_mat"][sa], scene["shape_mat"][sb])
-        bid, cf, ct = ref.smc_contact_forces(c, mats, st, scene["mass"], pos, rot, vel)
+        bid, cf, ct = ref.smc_contact_forces(c, mats, st, scene["mass"], pos, rot, vel, history=history)
         acc = accumulate_fast if fast else accumulate_contact_forces
         F, T, cnt = acc(nb, bid, cf, ct)
         touched = cnt > 0
         hf[touched, :3] += (h * F)[touched]
         hf[touched, 3:] += (h * T)[touched]
+    elif history is not None:
+        history["neigh"][:, 0] = -1  # no contact touched any slot
     v2 = velocity_update(vel, hf, scene["mass"], inv_inertia, active)
     p2, q2 = integrate(pos, rot, v2, h, active)
     return p2, q2, v2, dict(contacts=c, hf=hf, body_force=F, body_torque=T)

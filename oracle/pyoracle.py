@@ -179,7 +179,16 @@ class Ref:
         return hit, dict(normal=n, pt_a=p1, pt_b=p2, depth=d[0])
 
     # ---- SMC per-contact forces through the reference's function_CalcContactForces ----
-    def smc_contact_forces(self, contacts, mats, settings, mass, pos, rot, vel):
+    @staticmethod
+    def new_shear_history(nb, max_shear=20):
+        """host_container::shear_neigh / shear_disp / contact_relvel_init / contact_duration as
+        ChSystemMulticoreSMC::AddMaterialSurfaceData initialises them (MC/physics/ChSystemMulticoreSMC.cpp:39-50)."""
+        return dict(neigh=np.full((max_shear * nb, 3), -1, np.int32), disp=np.zeros((max_shear * nb, 3)),
+                    relvel=np.zeros(max_shear * nb), duration=np.zeros(max_shear * nb))
+
+    def smc_contact_forces(self, contacts, mats, settings, mass, pos, rot, vel, history=None):
+        """history (MultiStep): updated in place, including the release of untouched slots
+        (ChIterativeSolverMulticoreSMC::ProcessContacts, ...SMC.cpp:687-695)."""
         nc = contacts["depth"].size
         nb = np.asarray(mass).size
         bids = np.ascontiguousarray(contacts["body_ids"], dtype=np.int32)
@@ -188,15 +197,24 @@ class Ref:
         ct_bid = np.zeros(2 * nc, np.int32)
         ct_f, ct_t = np.zeros((2 * nc, 3)), np.zeros((2 * nc, 3))
         g = lambda k, d: settings.get(k, d)
+        sp = touch = None
+        hp = [None] * 5
+        if history is not None:
+            sid = np.asarray(contacts["shape_ids"]).astype(np.int64)
+            sp = np.ascontiguousarray(np.stack([sid >> 32, sid & 0xFFFFFFFF], 1), dtype=np.int32)
+            touch = np.zeros(history["relvel"].size, np.int8)
+            hp = [_p(history["neigh"]), _p(touch), _p(history["disp"]), _p(history["relvel"]), _p(history["duration"])]
         self.L.ref_smc_contact_forces(
-            C.c_int(nc), _p(bids), None, C.c_int(g("contact_force_model", 1)), C.c_int(g("adhesion_force_model", 0)),
+            C.c_int(nc), _p(bids), _p(sp) if sp is not None else None, C.c_int(g("contact_force_model", 1)), C.c_int(g("adhesion_force_model", 0)),
             C.c_int(g("tangential_displ_mode", 1)), C.c_int(g("use_material_properties", 1)),
             C.c_double(g("characteristic_vel", 1.0)), C.c_double(g("min_slip_vel", 1e-4)),
             C.c_double(g("min_roll_vel", 1e-4)), C.c_double(g("min_spin_vel", 1e-4)), C.c_double(g("step_size", 1e-3)),
             C.c_int(nb), _p(_f64(mass)), _p(_f64(pos)), _p(_f64(rot)), _p(_f64(vel)), _p(fric), _p(mod), _p(adh),
             _p(cr), _p(smc), _p(_f64(contacts["pt_a"])), _p(_f64(contacts["pt_b"])), _p(_f64(contacts["normal"])),
-            _p(_f64(contacts["depth"])), _p(_f64(contacts["eff_radius"])), None, None, None, None, None, _p(ct_bid),
-            _p(ct_f), _p(ct_t))
+            _p(_f64(contacts["depth"])), _p(_f64(contacts["eff_radius"])), hp[0], hp[1], hp[2], hp[3], hp[4],
+            _p(ct_bid), _p(ct_f), _p(ct_t))
+        if history is not None:
+            history["neigh"][touch == 0, 0] = -1
         return ct_bid, ct_f, ct_t
 
     def rotate(self, v, q):

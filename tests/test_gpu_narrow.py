@@ -205,3 +205,30 @@ def test_mixed_step_matches_oracle_forces(ref):
     assert info["contacts"]["depth"].size == sys.GetNumContacts()
     err = np.abs(vel - v).max() / np.abs(v).max()
     assert err < 1e-10, err
+
+
+def test_multistep_history_with_multi_contact_pairs(ref):
+    """MultiStep history when one shape pair has several contacts (box-box, capsule pairs): they share one history
+    slot and the reference visits them in list order -- the CUDA kernel walks such a run in one thread."""
+    from oracle import np_oracle
+
+    scene = cluttered([SPHERE, BOX, CAPSULE, BOX], 5, 0.17, 8, HYBRID, 0.0, aligned=True)
+    scene["settings"].update(tangential_displ_mode=2, step_size=1e-4)
+    scene["materials"] = np.array([scenes.smc_material(young=2e6, friction=0.5, restitution=0.3)])
+    rng = np.random.default_rng(2)
+    scene["vel"][1:, :3] = rng.normal(scale=0.05, size=(scene["mass"].size - 1, 3))
+    sys = cw.load_scene(cw.ChSystemMulticoreSMC(), scene)
+    ref.set_scene(scene)
+    hist = ref.new_shear_history(scene["mass"].size)
+    p, q, v = scene["pos"].copy(), scene["rot"].copy(), scene["vel"].copy()
+    multi = 0
+    for step in range(8):
+        sys.SetBodyState(0, p, q, v)
+        sys.DoStepDynamics()
+        _, _, gv = sys.GetBodyState()
+        p, q, v, info = np_oracle.smc_step(scene, ref, p, q, v, history=hist)
+        _, counts = np.unique(info["contacts"]["shape_ids"], return_counts=True)
+        multi = max(multi, counts.max())
+        err = np.abs(gv - v).max() / np.abs(v).max()
+        assert err < 1e-10, (step, err)
+    assert multi >= 2
