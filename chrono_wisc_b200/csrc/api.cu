@@ -121,8 +121,7 @@ static int alloc_contacts(System* S, uint32_t n) {
     CB_TRY(S->c_bids.reserve(2 * c));
     CB_TRY(S->c_shapes.reserve(c));
     CB_TRY(S->c_mats.reserve(c));
-    CB_TRY(S->ct_force.reserve(3 * c));
-    CB_TRY(S->ct_torque.reserve(6 * c));
+    CB_TRY(S->ct_force.reserve(CT_STRIDE * (size_t)c));
     CB_TRY(S->b_inc.reserve(2 * c));
     CB_TRY(S->heavy_part.reserve((size_t)MAX_HEAVY * (c / 4096 + 2) * 7));
     S->cap_contacts = (uint32_t)c;
@@ -1104,19 +1103,18 @@ int cb200_download_contact_forces(cb200_system* sys, double* ct_force, double* c
     const size_t nc = S->h_cnt->n_contacts;
     if (nc == 0)
         return CB200_OK;
-    std::vector<double> f(3 * nc), t(6 * nc);
-    CB_TRY(download(S, S->ct_force.p, f.data(), 3 * nc));
-    CB_TRY(download(S, S->ct_torque.p, t.data(), 6 * nc));
+    std::vector<double> r(CT_STRIDE * nc);
+    CB_TRY(download(S, S->ct_force.p, r.data(), CT_STRIDE * nc));
     CB_CUDA(cudaStreamSynchronize(S->stream));
     for (size_t i = 0; i < nc; i++)
         for (int a = 0; a < 3; a++) {
             if (ct_force) {
-                ct_force[6 * i + a] = -f[3 * i + a];
-                ct_force[6 * i + 3 + a] = f[3 * i + a];
+                ct_force[6 * i + a] = -r[CT_STRIDE * i + a];
+                ct_force[6 * i + 3 + a] = r[CT_STRIDE * i + a];
             }
             if (ct_torque) {
-                ct_torque[6 * i + a] = t[6 * i + a];
-                ct_torque[6 * i + 3 + a] = t[6 * i + 3 + a];
+                ct_torque[6 * i + a] = r[CT_STRIDE * i + 4 + a];
+                ct_torque[6 * i + 3 + a] = r[CT_STRIDE * i + 8 + a];
             }
         }
     return CB200_OK;

@@ -127,7 +127,7 @@ struct Timer {
     bool armed = false;
 };
 
-enum { LARGE_BINS = 48, MAX_LARGE = 4096, MAX_HEAVY = 64, SMC_MAT_STRIDE = 14, NSC_MAT_STRIDE = 8, PAIR_TILE = 256,
+enum { CT_STRIDE = 12, LARGE_BINS = 48, MAX_LARGE = 4096, MAX_HEAVY = 64, SMC_MAT_STRIDE = 14, NSC_MAT_STRIDE = 8, PAIR_TILE = 256,
        PAIR_HALO = 64 };
 
 struct System {
@@ -210,8 +210,10 @@ struct System {
     DevBuf<uint32_t> c_src;      // cap_contacts  slot + 1 of a contact computed by the complex path, 0 otherwise
 
     // ---- SMC (MC/solver/ChIterativeSolverMulticoreSMC.cpp) ----
-    DevBuf<double> ct_force;    // 3 N_c  force on body 2 (body 1 gets the negative)
-    DevBuf<double> ct_torque;   // 6 N_c  torque on body 1, torque on body 2 (body frames)
+    // CT_STRIDE N_c: per contact (force on body 2 [body 1 gets the negative], pad) (torque on body 1, pad) (torque on
+    // body 2, pad), torques in the body frames -- three 32-byte sectors
+    DevBuf<double> ct_force;
+    DevBuf<double> ct_torque;   // unused (kept for the release list)
     // MultiStep tangential displacement history, 20 slots per body (allocated on first use, smc.cu)
     DevBuf<int32_t> sh_neigh;   // 3 x 20 nb
     DevBuf<uint8_t> sh_touch;   // 20 nb

@@ -424,9 +424,12 @@ __global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, GenArgs G, Sh
         tq1 = -torque1_loc + m_roll1 + m_spin1;
         tq2 = torque2_loc - m_roll2 - m_spin2;
     }
-    ct_force[3 * i] = force.x, ct_force[3 * i + 1] = force.y, ct_force[3 * i + 2] = force.z;
-    double* t = ct_torque + 6 * (size_t)i;
-    t[0] = tq1.x, t[1] = tq1.y, t[2] = tq1.z, t[3] = tq2.x, t[4] = tq2.y, t[5] = tq2.z;
+    // one 96-byte record per contact, three 32-byte sectors: (force, -) (torque on body 1, -) (torque on body 2, -);
+    // the per-body gather then touches exactly two whole sectors per incidence
+    double4* o = reinterpret_cast<double4*>(ct_force + CT_STRIDE * (size_t)i);
+    o[0] = make_double4(force.x, force.y, force.z, 0.0);
+    o[1] = make_double4(tq1.x, tq1.y, tq1.z, 0.0);
+    o[2] = make_double4(tq2.x, tq2.y, tq2.z, 0.0);
     }
     }
 }
@@ -484,14 +487,15 @@ __global__ void __launch_bounds__(256) k_body_reduce(uint32_t nb, const uint8_t*
             }
             last = best;
             const uint32_t ci = best >> 1, side = best & 1u;
-            const d3 f = mk3(ct_force[3 * ci], ct_force[3 * ci + 1], ct_force[3 * ci + 2]);
-            const double* t = ct_torque + 6 * (size_t)ci + 3 * side;
+            const double4* rec = reinterpret_cast<const double4*>(ct_force + CT_STRIDE * (size_t)ci);
+            const double4 f4 = rec[0], t4 = rec[1 + side];
+            const d3 f = mk3(f4.x, f4.y, f4.z);
             if (r == 0) {
                 F = side ? f : -f;
-                T = mk3(t[0], t[1], t[2]);
+                T = mk3(t4.x, t4.y, t4.z);
             } else {
                 F = F + (side ? f : -f);
-                T = T + mk3(t[0], t[1], t[2]);
+                T = T + mk3(t4.x, t4.y, t4.z);
             }
         }
         double* o = b_force + 6 * (size_t)b;
@@ -546,15 +550,16 @@ __global__ void __launch_bounds__(256) k_heavy_partial(const int32_t* __restrict
             const uint32_t c = c0 + k * 256 + threadIdx.x;
             if (c < nc) {
                 const uint32_t b1 = (uint32_t)bids[2 * c], b2 = (uint32_t)bids[2 * c + 1];
+                const double* rec = ct_force + CT_STRIDE * (size_t)c;
                 if (b1 == body) {
-                    acc[0] -= ct_force[3 * c], acc[1] -= ct_force[3 * c + 1], acc[2] -= ct_force[3 * c + 2];
-                    const double* t = ct_torque + 6 * (size_t)c;
+                    acc[0] -= rec[0], acc[1] -= rec[1], acc[2] -= rec[2];
+                    const double* t = rec + 4;
                     acc[3] += t[0], acc[4] += t[1], acc[5] += t[2];
                     acc[6] += 1;
                 }
                 if (b2 == body) {
-                    acc[0] += ct_force[3 * c], acc[1] += ct_force[3 * c + 1], acc[2] += ct_force[3 * c + 2];
-                    const double* t = ct_torque + 6 * (size_t)c + 3;
+                    acc[0] += rec[0], acc[1] += rec[1], acc[2] += rec[2];
+                    const double* t = rec + 8;
                     acc[3] += t[0], acc[4] += t[1], acc[5] += t[2];
                     acc[6] += 1;
                 }
