@@ -226,6 +226,24 @@ __device__ __noinline__ int narrow_complex(const ShapeView& A, const ShapeView& 
     return 0;
 }
 
+// What the long-bin paths (more than 64 entries in a bin: no masks, no records) need to run a complex pair in place.
+struct CplxArgs {
+    const double *s_lrot, *rot, *s_verts;
+    double* cplx_out;
+    uint32_t cap_slots;
+};
+
+__device__ __forceinline__ int narrow_complex_ids(uint32_t sA, uint32_t sB, const ShapeMeta* __restrict__ meta,
+                                                  const double* __restrict__ s_wpos, const double* __restrict__ s_wrot,
+                                                  const double* __restrict__ s_dims, const CplxArgs& X, int algorithm,
+                                                  double envelope, Contact* out) {
+    const ShapeView A = make_view_full(sA, meta[sA], s_wpos, s_wrot, s_dims, X.s_lrot, X.rot, X.s_verts);
+    const ShapeView B = make_view_full(sB, meta[sB], s_wpos, s_wrot, s_dims, X.s_lrot, X.rot, X.s_verts);
+    int n = narrow_complex(A, B, algorithm, envelope, out);
+    const int slots = (int)pair_slots(A.type, B.type, algorithm);
+    return n < 0 ? 0 : (n > slots ? slots : n);
+}
+
 // cold path of pair_hit (a non-sphere is involved): kept out of line so that the sphere-sphere loop stays lean
 __device__ __noinline__ int pair_hit_general(uint32_t idA, int tA, double4 wA, uint32_t idB, int tB, double4 wB,
                                              double sep, const double* __restrict__ s_wrot,
@@ -449,7 +467,7 @@ __global__ void __launch_bounds__(32 * SLOW_WARPS) k_pair_masks_slow(
     const double* __restrict__ s_dims, const uint32_t* __restrict__ ent_shape, const uint32_t* __restrict__ ent_bin,
     const uint64_t* __restrict__ bin_start, double envelope, int algorithm, int mode,
     uint64_t* __restrict__ ent_mask, uint64_t* __restrict__ ent_cmask, uint32_t* __restrict__ ent_cnt,
-    const uint32_t* __restrict__ slow_bins, DevCounters* __restrict__ cnt) {
+    const uint32_t* __restrict__ slow_bins, CplxArgs X, DevCounters* __restrict__ cnt) {
     __shared__ WindowT<SLOW_WIN> W[SLOW_WARPS];
     __shared__ unsigned long long smask[SLOW_WARPS][SLOW_WIN];
     __shared__ unsigned long long scmask[CPLX ? SLOW_WARPS : 1][SLOW_WIN];
@@ -528,7 +546,19 @@ __global__ void __launch_bounds__(32 * SLOW_WARPS) k_pair_masks_slow(
                             load_rec(RB, ent_shape[bs + j], meta, s_wpos, s_box, g.origin, envelope);
                         const int dec = pair_decide<false>(RA, RB, g, b, mode, sep, algorithm, s_wrot, s_dims, np);
                         hits += dec == 1 ? 1u : 0u;
-                        ncx += dec == 2 ? 1u : 0u;  // long bins have no complex path
+                        if (dec == 2) {
+                            // long bins keep no masks or records: a complex pair is evaluated here for its contact
+                            // count and once more by the store pass, which writes the contacts
+                            if (CPLX && mode == MODE_CONTACTS) {
+                                Contact tmp[MAX_PAIR_CONTACTS];
+                                hits += (uint32_t)narrow_complex_ids(RA.id, RB.id, meta, s_wpos, s_wrot, s_dims, X,
+                                                                     algorithm, envelope, tmp);
+                            } else if (CPLX) {
+                                hits++;  // pair-list mode: a candidate pair like any other
+                            } else {
+                                ncx++;
+                            }
+                        }
                     }
 #pragma unroll
                     for (int d = 16; d > 0; d >>= 1)
@@ -684,7 +714,7 @@ __global__ void __launch_bounds__(256) k_pair_store(const ShapeMeta* __restrict_
                                                     const uint32_t* __restrict__ ent_cbase,
                                                     const uint32_t* __restrict__ rec,
                                                     const uint32_t* __restrict__ cplx_n, uint32_t* __restrict__ c_src,
-                                                    DevCounters* __restrict__ cnt) {
+                                                    CplxArgs X, DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
     const uint32_t ni = cnt->n_intersections;
@@ -751,10 +781,38 @@ __global__ void __launch_bounds__(256) k_pair_store(const ShapeMeta* __restrict_
             for (uint32_t j = e + 1; j < s + k; j++) {
                 Rec B;
                 load_rec(B, ent_shape[j], meta, s_wpos, s_box, g.origin, envelope);
-                if (pair_decide<false>(A, B, g, bin, mode, 2 * envelope, algorithm, s_wrot, s_dims, np) == 1) {
+                const int dec = pair_decide<false>(A, B, g, bin, mode, 2 * envelope, algorithm, s_wrot, s_dims, np);
+                if (dec == 1) {
                     if (CPLX && mode == MODE_CONTACTS)
                         c_src[o] = 0;
                     out[o++] = hiA | (int64_t)B.id;
+                } else if (dec == 2 && CPLX) {
+                    if (mode != MODE_CONTACTS) {
+                        out[o++] = hiA | (int64_t)B.id;
+                        continue;
+                    }
+                    // complex pair in a long bin: evaluated in place, its contacts go to freshly reserved slots
+                    Contact tmp[MAX_PAIR_CONTACTS];
+                    const int n = narrow_complex_ids(A.id, B.id, meta, s_wpos, s_wrot, s_dims, X, algorithm, envelope,
+                                                     tmp);
+                    if (n == 0)
+                        continue;
+                    const uint32_t slot = atomicAdd(&cnt->n_cslots, (uint32_t)n);
+                    if (slot + n > X.cap_slots) {
+                        atomicMax(&cnt->need_cslots, slot + n);
+                        atomicMax(&cnt->need_complex, cnt->n_complex);
+                        atomicOr(&cnt->overflow, (uint32_t)OVF_COMPLEX);
+                        continue;
+                    }
+                    for (int t = 0; t < n; t++) {
+                        double* q = X.cplx_out + 11 * (size_t)(slot + t);
+                        q[0] = tmp[t].n.x, q[1] = tmp[t].n.y, q[2] = tmp[t].n.z;
+                        q[3] = tmp[t].p1.x, q[4] = tmp[t].p1.y, q[5] = tmp[t].p1.z;
+                        q[6] = tmp[t].p2.x, q[7] = tmp[t].p2.y, q[8] = tmp[t].p2.z;
+                        q[9] = tmp[t].depth, q[10] = tmp[t].erad;
+                        out[o] = hiA | (int64_t)B.id;
+                        c_src[o++] = slot + t + 1;
+                    }
                 }
             }
         }
@@ -820,6 +878,9 @@ static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
     const int gm = grid_for(S, S->cap_entries, PAIR_TILE, 4);
     CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_slow, 0, 4, S->stream));
     const int gs = S->num_sms * 8;
+    CplxArgs X = {};
+    X.s_lrot = S->s_lrot.p, X.rot = S->rot.p, X.s_verts = S->s_verts.p, X.cplx_out = S->cplx_out.p;
+    X.cap_slots = S->cap_cslots;
     CB_TRY(timer_start(S, "k_pair_masks"));
     if (cplx) {
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_complex, 0, 4, S->stream));
@@ -831,7 +892,7 @@ static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
         k_pair_masks_slow<true><<<gs, 32 * SLOW_WARPS, 0, S->stream>>>(
             S->s_meta.p, S->ent_m.p, S->ent_c.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p,
             S->ent_bin.p, S->bin_start.p, env, algorithm, mode, S->ent_mask.p, S->ent_cmask.p, S->ent_off.p,
-            S->slow_bins.p, S->d_cnt);
+            S->slow_bins.p, X, S->d_cnt);
         S->launches++;
         CB_TRY(timer_stop(S, "k_pair_masks"));
         k_cplx_collect<<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
@@ -850,7 +911,7 @@ static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
         k_pair_masks_slow<false><<<gs, 32 * SLOW_WARPS, 0, S->stream>>>(
             S->s_meta.p, S->ent_m.p, S->ent_c.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p,
             S->ent_bin.p, S->bin_start.p, env, algorithm, mode, S->ent_mask.p, nullptr, S->ent_off.p,
-            S->slow_bins.p, S->d_cnt);
+            S->slow_bins.p, X, S->d_cnt);
         S->launches++;
         CB_TRY(timer_stop(S, "k_pair_masks"));
         S->launches++;
@@ -861,12 +922,12 @@ static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
         k_pair_store<true><<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
             S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p,
             S->bin_start.p, env, algorithm, mode, S->ent_mask.p, S->ent_off.p, out, cap, S->ent_cmask.p,
-            S->ent_cbase.p, S->cplx_rec.p, S->cplx_n.p, S->c_src.p, S->d_cnt);
+            S->ent_cbase.p, S->cplx_rec.p, S->cplx_n.p, S->c_src.p, X, S->d_cnt);
     else
         k_pair_store<false><<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
             S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p,
             S->bin_start.p, env, algorithm, mode, S->ent_mask.p, S->ent_off.p, out, cap, nullptr, nullptr, nullptr,
-            nullptr, nullptr, S->d_cnt);
+            nullptr, nullptr, X, S->d_cnt);
     CB_TRY(timer_stop(S, "k_pair_store"));
     S->launches++;
     CB_CUDA(cudaGetLastError());

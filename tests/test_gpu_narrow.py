@@ -232,3 +232,15 @@ def test_multistep_history_with_multi_contact_pairs(ref):
         err = np.abs(gv - v).max() / np.abs(v).max()
         assert err < 1e-10, (step, err)
     assert multi >= 2
+
+
+@pytest.mark.parametrize("algorithm", [MPR, HYBRID])
+def test_complex_pairs_in_long_bins(ref, algorithm):
+    """Bins with more than 64 entries keep neither pair masks nor complex-pair records on the device: pairs without a
+    sphere are then evaluated in place by the count and store passes.  Same list as the reference, bit for bit."""
+    scene = cluttered([SPHERE, BOX, CAPSULE, BOX], 7, 0.15, 13, algorithm, 0.01, grid_density=0.2)
+    scene, rk = compare(scene, ref, 300)
+    _, _, _, start = ref.bins()
+    assert np.diff(start.astype(np.int64)).max() > 64
+    _, counts = np.unique(rk["shape_ids"], return_counts=True)
+    assert algorithm == MPR or counts.max() >= 2
