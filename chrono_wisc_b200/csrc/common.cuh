@@ -117,6 +117,7 @@ struct DevCounters {
     uint32_t n_cslots;           // contact slots reserved for the complex pairs (PreprocessCount's rule per pair)
     uint32_t need_cslots;
     uint32_t n_slow;             // bins queued for k_pair_masks_slow
+    uint32_t n_cls[4];           // complex pairs per narrowphase class (k_cplx_collect buckets them for k_cplx_narrow)
 };
 
 struct Timer {
@@ -206,6 +207,7 @@ struct System {
     DevBuf<uint32_t> ent_cbase;  // cap_entries  first complex record of the entry
     DevBuf<uint32_t> cplx_rec;   // 4 per record: entry, shape A, shape B, first slot
     DevBuf<uint32_t> cplx_n;     // contacts found per record
+    DevBuf<uint32_t> cplx_cls;   // 4 x cap_complex: record indices bucketed by narrowphase class
     DevBuf<double> cplx_out;     // 11 per slot: normal, point A, point B, depth, effective radius
     DevBuf<uint32_t> c_src;      // cap_contacts  slot + 1 of a contact computed by the complex path, 0 otherwise
 

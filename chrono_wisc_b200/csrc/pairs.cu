@@ -609,34 +609,79 @@ __global__ void __launch_bounds__(32 * SLOW_WARPS) k_pair_masks_slow(
 //   k_cplx_narrow   one thread per record: narrow_complex -> up to 8 contacts into the record's slots; adds the
 //                   number found to the entry's output count
 // --------------------------------------------------------------------------------------------------------------
+// Narrowphase class of a complex pair: pairs of one class run the same function, so k_cplx_narrow walks the records
+// class by class and its warps stay (mostly) convergent.  Has no effect on the results.
+__device__ __forceinline__ int pair_class(int tA, int tB, int algorithm) {
+    if (algorithm == 0)
+        return (tA == CB200_SPHERE || tB == CB200_SPHERE) ? 0 : ((tA == CB200_BOX && tB == CB200_BOX) ? 2 : 3);
+    const bool cA = tA == CB200_CAPSULE, cB = tB == CB200_CAPSULE, bA = tA == CB200_BOX, bB = tB == CB200_BOX;
+    if (cA && cB)
+        return 0;
+    if ((bA && cB) || (cA && bB))
+        return 1;
+    if (bA && bB)
+        return 2;
+    return 3;
+}
+
 __global__ void __launch_bounds__(256) k_cplx_collect(const ShapeMeta* __restrict__ meta,
                                                       const uint32_t* __restrict__ ent_shape,
                                                       const uint32_t* __restrict__ ent_bin,
                                                       const uint64_t* __restrict__ bin_start,
                                                       const uint64_t* __restrict__ ent_cmask, int algorithm,
                                                       uint32_t* __restrict__ ent_cbase, uint32_t* __restrict__ rec,
-                                                      uint32_t cap_rec, DevCounters* __restrict__ cnt) {
+                                                      uint32_t* __restrict__ cls_list, uint32_t cap_rec,
+                                                      DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
     const uint32_t ni = cnt->n_intersections;
-    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < ni; e += gridDim.x * blockDim.x) {
-        unsigned long long m = ent_cmask[e];
+    const int lane = threadIdx.x & 31;
+    // warp-uniform trip count: the record / slot ranges of a warp's entries are reserved with one atomic each
+    for (uint32_t e0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; e0 < ni; e0 += gridDim.x * blockDim.x) {
+        const uint32_t e = e0 + lane;
+        unsigned long long m = e < ni ? ent_cmask[e] : 0ull;
+        if (!__any_sync(0xffffffffu, m != 0ull))
+            continue;
+        uint32_t s = 0, sA = 0, count = 0, nslots = 0;
+        int tA = 0;
+        if (m) {
+            s = (uint32_t)bin_start[ent_bin[e]];
+            sA = ent_shape[e];
+            tA = (meta[sA].info >> 8) & 0xff;
+            count = (uint32_t)__popcll(m);
+            for (unsigned long long u = m; u; u &= u - 1) {
+                const int j = __ffsll((long long)u) - 1;
+                nslots += pair_slots(tA, (meta[ent_shape[s + j]].info >> 8) & 0xff, algorithm);
+            }
+        }
+        uint32_t pc = count, ps = nslots;  // inclusive warp scans
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t a = __shfl_up_sync(0xffffffffu, pc, d), b = __shfl_up_sync(0xffffffffu, ps, d);
+            if (lane >= d)
+                pc += a, ps += b;
+        }
+        uint32_t bc = 0, bs = 0;
+        if (lane == 31) {
+            bc = atomicAdd(&cnt->n_complex, pc);
+            bs = atomicAdd(&cnt->n_cslots, ps);
+        }
+        bc = __shfl_sync(0xffffffffu, bc, 31), bs = __shfl_sync(0xffffffffu, bs, 31);
         if (!m)
             continue;
-        const uint32_t count = (uint32_t)__popcll(m);
-        uint32_t base = atomicAdd(&cnt->n_complex, count);
+        uint32_t base = bc + pc - count, slot = bs + ps - nslots;
         ent_cbase[e] = base;
-        const uint32_t s = (uint32_t)bin_start[ent_bin[e]];
-        const uint32_t sA = ent_shape[e];
-        const int tA = (meta[sA].info >> 8) & 0xff;
         while (m) {
             const int j = __ffsll((long long)m) - 1;
             m &= m - 1;
             const uint32_t sB = ent_shape[s + j];
             const int tB = (meta[sB].info >> 8) & 0xff;
-            const uint32_t slot = atomicAdd(&cnt->n_cslots, pair_slots(tA, tB, algorithm));
-            if (base < cap_rec)
+            if (base < cap_rec) {
                 reinterpret_cast<uint4*>(rec)[base] = make_uint4(e, sA, sB, slot);
+                const int c = pair_class(tA, tB, algorithm);
+                cls_list[(size_t)c * cap_rec + atomicAdd(&cnt->n_cls[c], 1u)] = base;
+            }
+            slot += pair_slots(tA, tB, algorithm);
             base++;
         }
     }
@@ -649,7 +694,8 @@ __global__ void __launch_bounds__(128) k_cplx_narrow(const ShapeMeta* __restrict
                                                      const double* __restrict__ s_lrot,
                                                      const double* __restrict__ rot,
                                                      const double* __restrict__ s_verts, double envelope, int algorithm,
-                                                     const uint32_t* __restrict__ rec, uint32_t cap_rec,
+                                                     const uint32_t* __restrict__ rec,
+                                                     const uint32_t* __restrict__ cls_list, uint32_t cap_rec,
                                                      uint32_t cap_slots, uint32_t* __restrict__ cplx_n,
                                                      double* __restrict__ cplx_out, uint32_t* __restrict__ ent_cnt,
                                                      DevCounters* __restrict__ cnt) {
@@ -667,7 +713,15 @@ __global__ void __launch_bounds__(128) k_cplx_narrow(const ShapeMeta* __restrict
         return;
     }
     uint32_t bad = 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nrec; i += gridDim.x * blockDim.x) {
+    // thread t takes the t-th record of the class-by-class order (classes padded to whole warps)
+    const uint32_t c0 = (cnt->n_cls[0] + 31u) & ~31u, c1 = c0 + ((cnt->n_cls[1] + 31u) & ~31u);
+    const uint32_t c2 = c1 + ((cnt->n_cls[2] + 31u) & ~31u), c3 = c2 + ((cnt->n_cls[3] + 31u) & ~31u);
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < c3; t += gridDim.x * blockDim.x) {
+        const int cls = t < c0 ? 0 : (t < c1 ? 1 : (t < c2 ? 2 : 3));
+        const uint32_t k = t - (cls == 0 ? 0u : (cls == 1 ? c0 : (cls == 2 ? c1 : c2)));
+        if (k >= cnt->n_cls[cls])
+            continue;
+        const uint32_t i = cls_list[(size_t)cls * cap_rec + k];
         const uint4 r = reinterpret_cast<const uint4*>(rec)[i];
         const ShapeMeta mA = meta[r.y], mB = meta[r.z];
         const ShapeView A = make_view_full(r.y, mA, s_wpos, s_wrot, s_dims, s_lrot, rot, s_verts);
@@ -885,6 +939,7 @@ static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
     if (cplx) {
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_complex, 0, 4, S->stream));
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_cslots, 0, 4, S->stream));
+        CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_cls[0], 0, 16, S->stream));
         k_pair_masks<true><<<gm, PAIR_THREADS, 0, S->stream>>>(
             S->s_meta.p, S->ent_m.p, S->ent_c.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p,
             S->ent_bin.p, S->bin_start.p, env, algorithm, mode, S->ent_mask.p, S->ent_cmask.p, S->ent_off.p,
@@ -897,10 +952,10 @@ static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
         CB_TRY(timer_stop(S, "k_pair_masks"));
         k_cplx_collect<<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
             S->s_meta.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p, S->ent_cmask.p, algorithm, S->ent_cbase.p,
-            S->cplx_rec.p, S->cap_complex, S->d_cnt);
+            S->cplx_rec.p, S->cplx_cls.p, S->cap_complex, S->d_cnt);
         k_cplx_narrow<<<grid_for(S, S->cap_complex, 128), 128, 0, S->stream>>>(
             S->s_meta.p, S->s_wpos.p, S->s_wrot.p, S->s_dims.p, S->s_lrot.p, S->rot.p, S->s_verts.p, env, algorithm,
-            S->cplx_rec.p,
+            S->cplx_rec.p, S->cplx_cls.p,
             S->cap_complex, S->cap_cslots, S->cplx_n.p, S->cplx_out.p, S->ent_off.p, S->d_cnt);
         S->launches += 3;
     } else {

@@ -40,16 +40,22 @@ for k in range(3):
         first = b.add_bodies(m, I, pos[sel], rot=q[sel])
         b.add_shapes(CAPSULE, first + np.arange(sel.size), [[r, hl]])
 settings = dict(system_type=1, step_size=1e-3, gravity=(0.0, 0.0, -9.81), contact_force_model=HERTZ,
-                narrowphase_algorithm=alg, broadphase_grid=FIXED_BIN_SIZE, bin_size=(5 * radius,) * 3)
+                narrowphase_algorithm=alg, broadphase_grid=FIXED_BIN_SIZE, bin_size=(float(sys.argv[7]) * radius if len(sys.argv) > 7 else 3 * radius,) * 3)
 scene = b.finish([scenes.smc_material(young=2e5, friction=0.4, restitution=0.1)], settings)
 s = cw.load_scene(cw.ChSystemMulticoreSMC(), scene)
 t0 = time.time(); s.DoSteps(warm); s.Synchronize(); dt = time.time() - t0
 c = s.GetCounts()
 print(f"warm: {dt/warm*1e3:.3f} ms/step wall; N_b={n} N_i={c.num_bin_aabb_intersections} N_p={c.num_possible_collisions} N_c={c.num_rigid_contacts} bins={tuple(c.bins_per_axis)}")
+import os
+if os.environ.get("CB200_PROFILE"):  # ncu --profile-from-start off: one directly enqueued step
+    import ctypes
+    rt = ctypes.CDLL("libcudart.so.12")
+    rt.cudaProfilerStart(); s.DoSteps(1); s.Synchronize(); rt.cudaProfilerStop()
 t0 = time.time(); s.DoSteps(steps); s.Synchronize(); dt = time.time() - t0
 c = s.GetCounts()
 print(f"timed (algorithm {alg}): {dt/steps*1e3:.3f} ms/step wall, {n*steps/dt/1e6:.1f} M particle-steps/s; N_c={c.num_rigid_contacts}")
-for name in ("step", "update", "collision_broad", "collision_narrow", "advance", "integrate"):
+for name in ("step", "update", "collision_broad", "collision_narrow", "advance", "integrate", "k_pair_masks", "k_pair_store",
+             "k_smc_force", "k_body_reduce", "k_bin_sort"):
     print(f"  {name:18s} {s.GetTimer(name)*1e3:.4f} ms")
 p, _, v = s.GetBodyState()
 print("max z", p[1:, 2].max(), "mean z", p[1:, 2].mean(), "max |v|", np.abs(v[1:, :3]).max())
