@@ -643,6 +643,7 @@ __global__ void __launch_bounds__(256) k_cplx_collect(const ShapeMeta* __restric
         if (!__any_sync(0xffffffffu, m != 0ull))
             continue;
         uint32_t s = 0, sA = 0, count = 0, nslots = 0;
+        unsigned long long kk = 0ull;
         int tA = 0;
         if (m) {
             s = (uint32_t)bin_start[ent_bin[e]];
@@ -651,25 +652,40 @@ __global__ void __launch_bounds__(256) k_cplx_collect(const ShapeMeta* __restric
             count = (uint32_t)__popcll(m);
             for (unsigned long long u = m; u; u &= u - 1) {
                 const int j = __ffsll((long long)u) - 1;
-                nslots += pair_slots(tA, (meta[ent_shape[s + j]].info >> 8) & 0xff, algorithm);
+                const int tB = (meta[ent_shape[s + j]].info >> 8) & 0xff;
+                nslots += pair_slots(tA, tB, algorithm);
+                kk += 1ull << (16 * pair_class(tA, tB, algorithm));  // per-class counts, packed 4 x 16 bit
             }
         }
         uint32_t pc = count, ps = nslots;  // inclusive warp scans
+        unsigned long long pk = kk;        // 32 lanes x 64 pairs = 2048 < 65536: the packed counts cannot carry over
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             const uint32_t a = __shfl_up_sync(0xffffffffu, pc, d), b = __shfl_up_sync(0xffffffffu, ps, d);
+            const unsigned long long c = __shfl_up_sync(0xffffffffu, pk, d);
             if (lane >= d)
-                pc += a, ps += b;
+                pc += a, ps += b, pk += c;
         }
-        uint32_t bc = 0, bs = 0;
+        uint32_t bc = 0, bs = 0, b0 = 0, b1 = 0, b2 = 0, b3 = 0;
         if (lane == 31) {
             bc = atomicAdd(&cnt->n_complex, pc);
             bs = atomicAdd(&cnt->n_cslots, ps);
+            const uint32_t t0 = (uint32_t)(pk & 0xffff), t1 = (uint32_t)((pk >> 16) & 0xffff);
+            const uint32_t t2 = (uint32_t)((pk >> 32) & 0xffff), t3 = (uint32_t)((pk >> 48) & 0xffff);
+            if (t0) b0 = atomicAdd(&cnt->n_cls[0], t0);
+            if (t1) b1 = atomicAdd(&cnt->n_cls[1], t1);
+            if (t2) b2 = atomicAdd(&cnt->n_cls[2], t2);
+            if (t3) b3 = atomicAdd(&cnt->n_cls[3], t3);
         }
         bc = __shfl_sync(0xffffffffu, bc, 31), bs = __shfl_sync(0xffffffffu, bs, 31);
+        b0 = __shfl_sync(0xffffffffu, b0, 31), b1 = __shfl_sync(0xffffffffu, b1, 31);
+        b2 = __shfl_sync(0xffffffffu, b2, 31), b3 = __shfl_sync(0xffffffffu, b3, 31);
         if (!m)
             continue;
         uint32_t base = bc + pc - count, slot = bs + ps - nslots;
+        const unsigned long long ex = pk - kk;  // exclusive per-class prefix of this lane
+        b0 += (uint32_t)(ex & 0xffff), b1 += (uint32_t)((ex >> 16) & 0xffff);
+        b2 += (uint32_t)((ex >> 32) & 0xffff), b3 += (uint32_t)((ex >> 48) & 0xffff);
         ent_cbase[e] = base;
         while (m) {
             const int j = __ffsll((long long)m) - 1;
@@ -679,7 +695,13 @@ __global__ void __launch_bounds__(256) k_cplx_collect(const ShapeMeta* __restric
             if (base < cap_rec) {
                 reinterpret_cast<uint4*>(rec)[base] = make_uint4(e, sA, sB, slot);
                 const int c = pair_class(tA, tB, algorithm);
-                cls_list[(size_t)c * cap_rec + atomicAdd(&cnt->n_cls[c], 1u)] = base;
+                const uint32_t k = c == 0 ? b0 : (c == 1 ? b1 : (c == 2 ? b2 : b3));
+                if (k < cap_rec)
+                    cls_list[(size_t)c * cap_rec + k] = base;
+            }
+            {
+                const int c = pair_class(tA, tB, algorithm);
+                b0 += c == 0, b1 += c == 1, b2 += c == 2, b3 += c == 3;
             }
             slot += pair_slots(tA, tB, algorithm);
             base++;
