@@ -310,7 +310,7 @@ void cb200_destroy(cb200_system* sys) {
     cudaStreamSynchronize(S->stream);
 #define REL(x) S->x.release()
     REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(bflags); REL(heavy);
-    REL(s_type); REL(s_body); REL(s_fam); REL(s_mat); REL(s_lpos); REL(s_lrot); REL(s_dims); REL(s_verts); REL(sh_neigh); REL(sh_touch); REL(sh_disp); REL(sh_relvel); REL(sh_dur); REL(s_wpos); REL(s_wrot);
+    REL(s_type); REL(s_body); REL(s_fam); REL(s_mat); REL(s_lpos); REL(s_lrot); REL(s_dims); REL(general_ids); REL(s_verts); REL(sh_neigh); REL(sh_touch); REL(sh_disp); REL(sh_relvel); REL(sh_dur); REL(s_wpos); REL(s_wrot);
     REL(s_box); REL(s_meta); REL(mat_smc); REL(mat_nsc); REL(bin_intersections); REL(bin_start); REL(bin_cursor);
     REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_mask); REL(ent_c); REL(ent_m); REL(ent_off); REL(slow_bins); REL(large_list); REL(pairs);
     REL(c_norm); REL(c_pta); REL(c_ptb); REL(c_depth); REL(c_erad); REL(c_bids); REL(c_shapes); REL(c_mats);
@@ -468,6 +468,16 @@ int cb200_append_shapes(cb200_system* sys, int n, const int32_t* type, const uin
     CB_TRY(upload(S, S->s_lpos, 3 * ns0, pos_local, 3 * (size_t)n));
     CB_TRY(upload(S, S->s_lrot, 4 * ns0, rot_local, 4 * (size_t)n));
     CB_TRY(upload(S, S->s_dims, 4 * ns0, dims, 4 * (size_t)n));
+    // the shapes k_aabb<true> has to visit (same rule as k_build_meta's bit 2)
+    std::vector<uint32_t> gen;
+    for (int i = 0; i < n; i++)
+        if (!(type[i] == CB200_SPHERE && pos_local[3 * i] == 0 && pos_local[3 * i + 1] == 0 && pos_local[3 * i + 2] == 0))
+            gen.push_back((uint32_t)(ns0 + i));
+    if (!gen.empty()) {
+        CB_TRY(S->general_ids.reserve(S->n_general + gen.size(), true, st));
+        CB_TRY(upload(S, S->general_ids, S->n_general, gen.data(), gen.size()));
+        S->n_general += (uint32_t)gen.size();
+    }
     CB_CUDA(cudaStreamSynchronize(st));
     S->ns = (uint32_t)ns1;
     S->meta_dirty = true;

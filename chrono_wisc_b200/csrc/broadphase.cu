@@ -83,10 +83,96 @@ __global__ void k_reset_counters(DevCounters* cnt, uint32_t nb, uint32_t ns) {
     }
 }
 
+// Everything but a body-centred sphere: shape frame, box per type (GenerateAABB, :486-541).
+__device__ __forceinline__ bool aabb_general(uint32_t i, int type, uint32_t body, const d3& p, const double4& dm,
+                                          const double* __restrict__ s_lpos, const double* __restrict__ s_lrot,
+                                          double* s_dims, const double* __restrict__ s_verts,
+                                          const double* __restrict__ rot, double envelope,
+                                          double* __restrict__ s_wpos, double* __restrict__ s_wrot,
+                                          ShapeBox* __restrict__ s_box, d3& amin, d3& amax) {
+    bool ok = true;
+    const double4 qa = reinterpret_cast<const double4*>(rot)[body];
+    const q4 q = mkq(qa.x, qa.y, qa.z, qa.w);
+    const d3 lp = mk3(s_lpos[3 * i], s_lpos[3 * i + 1], s_lpos[3 * i + 2]);
+    const double4 la = reinterpret_cast<const double4*>(s_lrot)[i];
+    const q4 lq = mkq(la.x, la.y, la.z, la.w);
+    const d3 wp = rotate(lp, q) + p;  // == TransformLocalToParent(p, q, lp): IEEE addition commutes
+    const q4 wq = qmul(q, lq);
+    if (type == CB200_TRIANGLE) {
+        // GenerateAABB :524-535 and PreprocessLocalToParent (CMC/ChNarrowphase.cpp:186-194): the vertices are
+        // given in the BODY frame; no envelope on a triangle's box.  The world vertices (triangle_global) take
+        // the shape's wpos / wrot / dims.yzw slots, which a triangle has no other use for (mpr.cuh ShapeView).
+        const double* t = s_verts + 3 * (size_t)dm.x;
+        const d3 A = rotate(mk3(t[0], t[1], t[2]), q) + p;
+        const d3 B = rotate(mk3(t[3], t[4], t[5]), q) + p;
+        const d3 C = rotate(mk3(t[6], t[7], t[8]), q) + p;
+        reinterpret_cast<double4*>(s_wpos)[i] = make_double4(A.x, A.y, A.z, dm.x);
+        reinterpret_cast<double4*>(s_wrot)[i] = make_double4(B.x, B.y, B.z, 0.0);
+        s_dims[4 * i + 1] = C.x, s_dims[4 * i + 2] = C.y, s_dims[4 * i + 3] = C.z;
+        amin = min3(A, min3(B, C));
+        amax = max3(A, max3(B, C));
+        ShapeBox b;
+        b.mn[0] = amin.x, b.mn[1] = amin.y, b.mn[2] = amin.z;
+        b.mx[0] = amax.x, b.mx[1] = amax.y, b.mx[2] = amax.z;
+        s_box[i] = b;
+        return true;
+    }
+    reinterpret_cast<double4*>(s_wpos)[i] = make_double4(wp.x, wp.y, wp.z, dm.x);
+    reinterpret_cast<double4*>(s_wrot)[i] = make_double4(wq.w, wq.x, wq.y, wq.z);
+    if (type == CB200_SPHERE) {
+        const double r = dm.x + envelope;
+        amin = wp - r;
+        amax = wp + r;
+    } else {
+        d3 t = mk3(0);
+        if (type == CB200_ELLIPSOID || type == CB200_BOX || type == CB200_CYLINDER ||
+            type == CB200_CYLSHELL || type == CB200_CONE) {
+            t = abs_rotate(wq, mk3(dm.x, dm.y, dm.z) + envelope);
+        } else if (type == CB200_ROUNDEDBOX || type == CB200_ROUNDEDCYL) {
+            t = abs_rotate(wq, mk3(dm.x, dm.y, dm.z) + dm.w + envelope);
+        } else if (type == CB200_CAPSULE) {
+            t = abs_rotate(wq, mk3(dm.x, dm.x + dm.y, dm.x) + envelope);
+        } else if (type == CB200_CONVEXHULL) {
+            // ComputeAABBConvex, CMC/ChCollisionSystemMulticore.cpp:424-456: Rotate(point + lpos, body*local)
+            const double* h = s_verts + 3 * (size_t)dm.x;
+            const int nv = (int)dm.y;
+            d3 lo = rotate(mk3(h[0], h[1], h[2]) + lp, wq) + p, hi = lo;
+            for (int k = 0; k < nv; k++) {
+                const d3 c = rotate(mk3(h[3 * k], h[3 * k + 1], h[3 * k + 2]) + lp, wq) + p;
+                lo = min3(lo, c);
+                hi = max3(hi, c);
+            }
+            amin = lo - envelope;
+            amax = hi + envelope;
+            ShapeBox b;
+            b.mn[0] = amin.x, b.mn[1] = amin.y, b.mn[2] = amin.z;
+            b.mx[0] = amax.x, b.mx[1] = amax.y, b.mx[2] = amax.z;
+            s_box[i] = b;
+            return true;
+        } else {
+            ok = false;  // type without an AABB rule: the reference `continue`s and keeps stale values
+        }
+        amin = wp - t;
+        amax = wp + t;
+        if (!ok)
+            amin = amax = mk3(0);
+        ShapeBox b;
+        b.mn[0] = amin.x, b.mn[1] = amin.y, b.mn[2] = amin.z;
+        b.mx[0] = amax.x, b.mx[1] = amax.y, b.mx[2] = amax.z;
+        s_box[i] = b;
+    }
+    return ok;
+}
+
 // --------------------------------------------------------------------------------------------------------------
-// k_aabb: one thread per shape (grid-stride).
+// k_aabb: one thread per shape (grid-stride).  Two instantiations, two launches: <false> takes the body-centred
+// spheres and nothing else (a lean, latency-bound gather that wants its occupancy), <true> everything else --
+// through the list of such shapes kept by cb200_append_shapes, or (ids == nullptr, slab systems, whose shapes are
+// written by the device) by scanning all shapes.
 // --------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_aabb(uint32_t ns, const ShapeMeta* __restrict__ meta,
+template <bool GENERAL>
+__global__ void __launch_bounds__(256) k_aabb(uint32_t ns, const uint32_t* __restrict__ ids,
+                                              const ShapeMeta* __restrict__ meta,
                                               const double* __restrict__ s_lpos, const double* __restrict__ s_lrot,
                                               double* s_dims, const double* __restrict__ s_verts,
                                               const double* __restrict__ pos,
@@ -97,9 +183,10 @@ __global__ void __launch_bounds__(256) k_aabb(uint32_t ns, const ShapeMeta* __re
         return;
     d3 mn = mk3(DBL_MAX), mx = mk3(-DBL_MAX);
     bool counted = false;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ns; i += gridDim.x * blockDim.x) {
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < ns; t += gridDim.x * blockDim.x) {
+        const uint32_t i = (GENERAL && ids) ? ids[t] : t;
         const ShapeMeta m = meta[i];
-        if (m.body == UINT_MAX)
+        if (m.body == UINT_MAX || ((m.info & 4u) != 0) == GENERAL)
             continue;
         const int type = (m.info >> 8) & 0xff;
         const uint32_t body = m.body;
@@ -107,93 +194,17 @@ __global__ void __launch_bounds__(256) k_aabb(uint32_t ns, const ShapeMeta* __re
         const double4 dm = reinterpret_cast<const double4*>(s_dims)[i];
         d3 amin, amax;
         bool ok = true;
-        if (m.info & 4u) {
+        if (!GENERAL) {
             // centred sphere: Rotate(0, q) + p == p
             reinterpret_cast<double4*>(s_wpos)[i] = make_double4(p.x, p.y, p.z, dm.x);
             const double r = dm.x + envelope;
             amin = p - r;
             amax = p + r;
         } else {
-            const double4 qa = reinterpret_cast<const double4*>(rot)[body];
-            const q4 q = mkq(qa.x, qa.y, qa.z, qa.w);
-            const d3 lp = mk3(s_lpos[3 * i], s_lpos[3 * i + 1], s_lpos[3 * i + 2]);
-            const double4 la = reinterpret_cast<const double4*>(s_lrot)[i];
-            const q4 lq = mkq(la.x, la.y, la.z, la.w);
-            const d3 wp = rotate(lp, q) + p;  // == TransformLocalToParent(p, q, lp): IEEE addition commutes
-            const q4 wq = qmul(q, lq);
-            if (type == CB200_TRIANGLE) {
-                // GenerateAABB :524-535 and PreprocessLocalToParent (CMC/ChNarrowphase.cpp:186-194): the vertices are
-                // given in the BODY frame; no envelope on a triangle's box.  The world vertices (triangle_global) take
-                // the shape's wpos / wrot / dims.yzw slots, which a triangle has no other use for (mpr.cuh ShapeView).
-                const double* t = s_verts + 3 * (size_t)dm.x;
-                const d3 A = rotate(mk3(t[0], t[1], t[2]), q) + p;
-                const d3 B = rotate(mk3(t[3], t[4], t[5]), q) + p;
-                const d3 C = rotate(mk3(t[6], t[7], t[8]), q) + p;
-                reinterpret_cast<double4*>(s_wpos)[i] = make_double4(A.x, A.y, A.z, dm.x);
-                reinterpret_cast<double4*>(s_wrot)[i] = make_double4(B.x, B.y, B.z, 0.0);
-                s_dims[4 * i + 1] = C.x, s_dims[4 * i + 2] = C.y, s_dims[4 * i + 3] = C.z;
-                amin = min3(A, min3(B, C));
-                amax = max3(A, max3(B, C));
-                ShapeBox b;
-                b.mn[0] = amin.x, b.mn[1] = amin.y, b.mn[2] = amin.z;
-                b.mx[0] = amax.x, b.mx[1] = amax.y, b.mx[2] = amax.z;
-                s_box[i] = b;
-                if (m.info & 2u) {
-                    mn = min3(mn, amin);
-                    mx = max3(mx, amax);
-                    counted = true;
-                }
-                continue;
-            }
-            reinterpret_cast<double4*>(s_wpos)[i] = make_double4(wp.x, wp.y, wp.z, dm.x);
-            reinterpret_cast<double4*>(s_wrot)[i] = make_double4(wq.w, wq.x, wq.y, wq.z);
-            if (type == CB200_SPHERE) {
-                const double r = dm.x + envelope;
-                amin = wp - r;
-                amax = wp + r;
-            } else {
-                d3 t = mk3(0);
-                if (type == CB200_ELLIPSOID || type == CB200_BOX || type == CB200_CYLINDER ||
-                    type == CB200_CYLSHELL || type == CB200_CONE) {
-                    t = abs_rotate(wq, mk3(dm.x, dm.y, dm.z) + envelope);
-                } else if (type == CB200_ROUNDEDBOX || type == CB200_ROUNDEDCYL) {
-                    t = abs_rotate(wq, mk3(dm.x, dm.y, dm.z) + dm.w + envelope);
-                } else if (type == CB200_CAPSULE) {
-                    t = abs_rotate(wq, mk3(dm.x, dm.x + dm.y, dm.x) + envelope);
-                } else if (type == CB200_CONVEXHULL) {
-                    // ComputeAABBConvex, CMC/ChCollisionSystemMulticore.cpp:424-456: Rotate(point + lpos, body*local)
-                    const double* h = s_verts + 3 * (size_t)dm.x;
-                    const int nv = (int)dm.y;
-                    d3 lo = rotate(mk3(h[0], h[1], h[2]) + lp, wq) + p, hi = lo;
-                    for (int k = 0; k < nv; k++) {
-                        const d3 c = rotate(mk3(h[3 * k], h[3 * k + 1], h[3 * k + 2]) + lp, wq) + p;
-                        lo = min3(lo, c);
-                        hi = max3(hi, c);
-                    }
-                    amin = lo - envelope;
-                    amax = hi + envelope;
-                    ShapeBox b;
-                    b.mn[0] = amin.x, b.mn[1] = amin.y, b.mn[2] = amin.z;
-                    b.mx[0] = amax.x, b.mx[1] = amax.y, b.mx[2] = amax.z;
-                    s_box[i] = b;
-                    if (m.info & 2u) {
-                        mn = min3(mn, amin);
-                        mx = max3(mx, amax);
-                        counted = true;
-                    }
-                    continue;
-                } else {
-                    ok = false;  // type without an AABB rule: the reference `continue`s and keeps stale values
-                }
-                amin = wp - t;
-                amax = wp + t;
-                if (!ok)
-                    amin = amax = mk3(0);
-                ShapeBox b;
-                b.mn[0] = amin.x, b.mn[1] = amin.y, b.mn[2] = amin.z;
-                b.mx[0] = amax.x, b.mx[1] = amax.y, b.mx[2] = amax.z;
-                s_box[i] = b;
-            }
+            d3 lo, hi;  // only these have their address taken: the sphere path stays in registers
+            ok = aabb_general(i, type, body, p, dm, s_lpos, s_lrot, s_dims, s_verts, rot, envelope, s_wpos, s_wrot, s_box,
+                              lo, hi);
+            amin = lo, amax = hi;
         }
         if (ok && (m.info & 2u)) {
             mn = min3(mn, amin);
@@ -560,10 +571,16 @@ int enqueue_aabb(System* S) {
     }
     k_reset_counters<<<1, 32, 0, S->stream>>>(S->d_cnt, S->nb, S->ns);
     CB_CUDA(cudaMemsetAsync(S->heavy.p, 0, S->nb, S->stream));
-    k_aabb<<<grid_for(S, S->ns, 256), 256, 0, S->stream>>>(S->ns, S->s_meta.p, S->s_lpos.p, S->s_lrot.p, S->s_dims.p, S->s_verts.p,
-                                                           S->pos.p, S->rot.p, S->set.collision_envelope, S->s_wpos.p,
-                                                           S->s_wrot.p, S->s_box.p, S->d_cnt);
-    S->launches += 2;
+    k_aabb<false><<<grid_for(S, S->ns, 256), 256, 0, S->stream>>>(
+        S->ns, nullptr, S->s_meta.p, S->s_lpos.p, S->s_lrot.p, S->s_dims.p, S->s_verts.p, S->pos.p, S->rot.p,
+        S->set.collision_envelope, S->s_wpos.p, S->s_wrot.p, S->s_box.p, S->d_cnt);
+    const bool listed = !S->slab_on && S->general_ids.p;
+    const uint32_t ng = listed ? S->n_general : S->ns;
+    if (ng)
+        k_aabb<true><<<grid_for(S, ng, 256), 256, 0, S->stream>>>(
+            ng, listed ? S->general_ids.p : nullptr, S->s_meta.p, S->s_lpos.p, S->s_lrot.p, S->s_dims.p, S->s_verts.p,
+            S->pos.p, S->rot.p, S->set.collision_envelope, S->s_wpos.p, S->s_wrot.p, S->s_box.p, S->d_cnt);
+    S->launches += 3;
     S->pairs_valid = false;
     S->box_relative = false;
     CB_CUDA(cudaGetLastError());

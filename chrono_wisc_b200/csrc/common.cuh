@@ -161,6 +161,8 @@ struct System {
     DevBuf<double> s_lpos;   // 3 ns  ObA
     DevBuf<double> s_lrot;   // 4 ns  ObR
     DevBuf<double> s_dims;   // 4 ns
+    DevBuf<uint32_t> general_ids;  // shapes that are not body-centred spheres (k_aabb<true> walks this list)
+    uint32_t n_general = 0;
     DevBuf<double> s_verts;  // 3 n_verts: vertex pool of triangles (body frame) and convex hulls (shape frame)
     uint32_t n_verts = 0;
     DevBuf<double> s_wpos;   // 4 ns  world position + dims[0]  (obj_data_A_global)

@@ -772,6 +772,58 @@ __global__ void __launch_bounds__(128) k_cplx_narrow(const ShapeMeta* __restrict
         atomicAdd(&cnt->unsupported, bad);
 }
 
+// Row of a bin with more than 64 entries (no masks): re-walk and re-test (k_pair_store_long).
+template <bool CPLX>
+__device__ __forceinline__ void store_long_row(uint32_t e, uint32_t o, uint32_t s, uint32_t k, uint32_t bin, int64_t hiA,
+                                            const ShapeMeta* __restrict__ meta, const double* __restrict__ s_wpos,
+                                            const ShapeBox* __restrict__ s_box, const double* __restrict__ s_wrot,
+                                            const double* __restrict__ s_dims,
+                                            const uint32_t* __restrict__ ent_shape, double envelope, int algorithm,
+                                            int mode, int64_t* __restrict__ out, uint32_t* __restrict__ c_src,
+                                            const CplxArgs& X, DevCounters* __restrict__ cnt) {
+    const GridParams g = load_grid(cnt);
+    Rec A;
+    load_rec(A, ent_shape[e], meta, s_wpos, s_box, g.origin, envelope);
+    uint32_t np = 0;
+    for (uint32_t j = e + 1; j < s + k; j++) {
+        Rec B;
+        load_rec(B, ent_shape[j], meta, s_wpos, s_box, g.origin, envelope);
+        const int dec = pair_decide<false>(A, B, g, bin, mode, 2 * envelope, algorithm, s_wrot, s_dims, np);
+        if (dec == 1) {
+            if (CPLX && mode == MODE_CONTACTS)
+                c_src[o] = 0;
+            out[o++] = hiA | (int64_t)B.id;
+        } else if (dec == 2 && CPLX) {
+            if (mode != MODE_CONTACTS) {
+                out[o++] = hiA | (int64_t)B.id;
+                continue;
+            }
+            // complex pair in a long bin: evaluated in place, its contacts go to freshly reserved slots
+            Contact tmp[MAX_PAIR_CONTACTS];
+            const int n = narrow_complex_ids(A.id, B.id, meta, s_wpos, s_wrot, s_dims, X, algorithm, envelope,
+                                             tmp);
+            if (n == 0)
+                continue;
+            const uint32_t slot = atomicAdd(&cnt->n_cslots, (uint32_t)n);
+            if (slot + n > X.cap_slots) {
+                atomicMax(&cnt->need_cslots, slot + n);
+                atomicMax(&cnt->need_complex, cnt->n_complex);
+                atomicOr(&cnt->overflow, (uint32_t)OVF_COMPLEX);
+                continue;
+            }
+            for (int t = 0; t < n; t++) {
+                double* q = X.cplx_out + 11 * (size_t)(slot + t);
+                q[0] = tmp[t].n.x, q[1] = tmp[t].n.y, q[2] = tmp[t].n.z;
+                q[3] = tmp[t].p1.x, q[4] = tmp[t].p1.y, q[5] = tmp[t].p1.z;
+                q[6] = tmp[t].p2.x, q[7] = tmp[t].p2.y, q[8] = tmp[t].p2.z;
+                q[9] = tmp[t].depth, q[10] = tmp[t].erad;
+                out[o] = hiA | (int64_t)B.id;
+                c_src[o++] = slot + t + 1;
+            }
+        }
+    }
+}
+
 // k_pair_store: one thread per entry; turns masks (or, for long bins, a re-walk of the row) into 64-bit shape-pair
 // keys at their final, compacted positions.  With CPLX the contacts of complex pairs are interleaved in (j, contact)
 // order -- the order the reference's slot layout + stable compaction leaves -- and c_src points at their records.
@@ -849,48 +901,48 @@ __global__ void __launch_bounds__(256) k_pair_store(const ShapeMeta* __restrict_
                     out[o++] = hiA | (int64_t)ent_shape[s + j];
                 }
             }
-        } else {
-            const GridParams g = load_grid(cnt);
-            Rec A;
-            load_rec(A, ent_shape[e], meta, s_wpos, s_box, g.origin, envelope);
-            uint32_t np = 0;
-            for (uint32_t j = e + 1; j < s + k; j++) {
-                Rec B;
-                load_rec(B, ent_shape[j], meta, s_wpos, s_box, g.origin, envelope);
-                const int dec = pair_decide<false>(A, B, g, bin, mode, 2 * envelope, algorithm, s_wrot, s_dims, np);
-                if (dec == 1) {
-                    if (CPLX && mode == MODE_CONTACTS)
-                        c_src[o] = 0;
-                    out[o++] = hiA | (int64_t)B.id;
-                } else if (dec == 2 && CPLX) {
-                    if (mode != MODE_CONTACTS) {
-                        out[o++] = hiA | (int64_t)B.id;
-                        continue;
-                    }
-                    // complex pair in a long bin: evaluated in place, its contacts go to freshly reserved slots
-                    Contact tmp[MAX_PAIR_CONTACTS];
-                    const int n = narrow_complex_ids(A.id, B.id, meta, s_wpos, s_wrot, s_dims, X, algorithm, envelope,
-                                                     tmp);
-                    if (n == 0)
-                        continue;
-                    const uint32_t slot = atomicAdd(&cnt->n_cslots, (uint32_t)n);
-                    if (slot + n > X.cap_slots) {
-                        atomicMax(&cnt->need_cslots, slot + n);
-                        atomicMax(&cnt->need_complex, cnt->n_complex);
-                        atomicOr(&cnt->overflow, (uint32_t)OVF_COMPLEX);
-                        continue;
-                    }
-                    for (int t = 0; t < n; t++) {
-                        double* q = X.cplx_out + 11 * (size_t)(slot + t);
-                        q[0] = tmp[t].n.x, q[1] = tmp[t].n.y, q[2] = tmp[t].n.z;
-                        q[3] = tmp[t].p1.x, q[4] = tmp[t].p1.y, q[5] = tmp[t].p1.z;
-                        q[6] = tmp[t].p2.x, q[7] = tmp[t].p2.y, q[8] = tmp[t].p2.z;
-                        q[9] = tmp[t].depth, q[10] = tmp[t].erad;
-                        out[o] = hiA | (int64_t)B.id;
-                        c_src[o++] = slot + t + 1;
-                    }
-                }
-            }
+        }
+        // rows of bins with more than 64 entries: k_pair_store_long
+    }
+}
+
+// The rows k_pair_store leaves out: a warp per queued bin (k_pair_masks queued every bin of more than 64 entries),
+// lanes across its rows.  A kernel of its own because its registers (pair_decide, narrow_complex) would set the
+// occupancy of the store kernel, which is a latency-bound gather.
+template <bool CPLX>
+__global__ void __launch_bounds__(128) k_pair_store_long(const ShapeMeta* __restrict__ meta,
+                                                         const double* __restrict__ s_wpos,
+                                                         const ShapeBox* __restrict__ s_box,
+                                                         const double* __restrict__ s_wrot,
+                                                         const double* __restrict__ s_dims,
+                                                         const uint32_t* __restrict__ ent_shape,
+                                                         const uint32_t* __restrict__ ent_bin,
+                                                         const uint64_t* __restrict__ bin_start, double envelope,
+                                                         int algorithm, int mode,
+                                                         const uint32_t* __restrict__ ent_off,
+                                                         int64_t* __restrict__ out, uint32_t cap,
+                                                         uint32_t* __restrict__ c_src,
+                                                         const uint32_t* __restrict__ slow_bins, CplxArgs X,
+                                                         DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    if (ent_off[cnt->n_intersections] > cap)
+        return;  // k_pair_store raises the flag
+    const uint32_t nslow = cnt->n_slow;
+    const int lane = threadIdx.x & 31;
+    const uint32_t nw = gridDim.x * (blockDim.x >> 5);
+    for (uint32_t q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); q < nslow; q += nw) {
+        const uint32_t s = slow_bins[q];
+        const uint32_t bin = ent_bin[s];
+        const uint32_t k = (uint32_t)bin_start[bin + 1] - s;
+        if (k <= 64)
+            continue;
+        for (uint32_t e = s + lane; e < s + k; e += 32) {
+            const uint32_t o = ent_off[e];
+            if (ent_off[e + 1] == o)
+                continue;
+            store_long_row<CPLX>(e, o, s, k, bin, (int64_t)ent_shape[e] << 32, meta, s_wpos, s_box, s_wrot, s_dims,
+                                 ent_shape, envelope, algorithm, mode, out, c_src, X, cnt);
         }
     }
 }
@@ -1005,8 +1057,16 @@ static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
             S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p,
             S->bin_start.p, env, algorithm, mode, S->ent_mask.p, S->ent_off.p, out, cap, nullptr, nullptr, nullptr,
             nullptr, nullptr, X, S->d_cnt);
+    if (cplx)
+        k_pair_store_long<true><<<S->num_sms * 2, 128, 0, S->stream>>>(
+            S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p,
+            S->bin_start.p, env, algorithm, mode, S->ent_off.p, out, cap, S->c_src.p, S->slow_bins.p, X, S->d_cnt);
+    else
+        k_pair_store_long<false><<<S->num_sms * 2, 128, 0, S->stream>>>(
+            S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p,
+            S->bin_start.p, env, algorithm, mode, S->ent_off.p, out, cap, nullptr, S->slow_bins.p, X, S->d_cnt);
     CB_TRY(timer_stop(S, "k_pair_store"));
-    S->launches++;
+    S->launches += 2;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;
 }
