@@ -161,62 +161,73 @@ __global__ void __launch_bounds__(256) k_slab_pack(SlabGeom G, SlabArrays A, con
     }
 }
 
-// One CTA: rebuild one ghost region from a received buffer; arrivals take vacant owned slots in record order.
+// Rebuild one ghost region from a received buffer; arrivals take vacant owned slots in record order.  One CTA per
+// 1024 records: a CTA first counts the arrivals among the records before its chunk (one coordinate each, a few KB),
+// which is the rank offset a single sequential CTA would have carried along, then handles its own chunk.
+__device__ __forceinline__ bool slab_is_arrival(const SlabGeom& G, const double* __restrict__ recv, uint32_t j) {
+    const double p = recv[SLAB_HDR + (size_t)SLAB_REC * j + 1 + G.axis];
+    return (!G.has_left || p >= G.lo) && (!G.has_right || p < G.hi);
+}
+
 __global__ void __launch_bounds__(1024) k_slab_unpack(SlabGeom G, SlabArrays A, const double* __restrict__ recv,
                                                       uint32_t ghost_base, const uint32_t* __restrict__ vacant,
                                                       uint32_t* __restrict__ scnt, int first_side,
                                                       DevCounters* __restrict__ cnt) {
     __shared__ uint32_t warp_tot[32];
-    __shared__ uint32_t base;
     if (cnt->overflow)
         return;
     const uint32_t n = recv ? (uint32_t)recv[0] : 0u;
     const uint32_t n_vac = scnt[1];
-    if (threadIdx.x == 0)
-        base = first_side ? 0u : scnt[2];
-    __syncthreads();
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    for (uint32_t j0 = 0; j0 < G.ghost_cap; j0 += blockDim.x) {
-        const uint32_t j = j0 + threadIdx.x;
-        bool arrival = false;
-        const double* r = nullptr;
-        if (j < n) {
-            r = recv + SLAB_HDR + (size_t)SLAB_REC * j;
-            const double p = r[1 + G.axis];
-            arrival = (!G.has_left || p >= G.lo) && (!G.has_right || p < G.hi);
-        }
-        const unsigned m = __ballot_sync(0xffffffffu, arrival);
-        if (lane == 0)
-            warp_tot[wid] = (uint32_t)__popc(m);
-        __syncthreads();
-        uint32_t before = base;
-        for (int w = 0; w < wid; w++)
-            before += warp_tot[w];
-        const uint32_t rank = before + (uint32_t)__popc(m & ((1u << lane) - 1));
-        uint32_t chunk_total = 0;
-        for (int w = 0; w < (int)(blockDim.x >> 5); w++)
-            chunk_total += warp_tot[w];
-        if (j < G.ghost_cap) {
-            const uint32_t gslot = ghost_base + j;
-            if (j < n && !arrival) {
-                slab_read_record(A, gslot, r, 2);  // ghost: collides, not integrated
-            } else {
-                A.bflags[gslot] = 4;
-                if (arrival) {
-                    if (rank < n_vac)
-                        slab_read_record(A, vacant[rank], r, 3);
-                    else
-                        atomicOr(&cnt->overflow, (uint32_t)OVF_SLAB);
-                }
+    const uint32_t j0 = blockIdx.x * blockDim.x;
+    // arrivals before this chunk (CTA 0 counts all of them instead, for the other side's kernel)
+    const uint32_t upto = blockIdx.x == 0 ? n : min(j0, n);
+    uint32_t mine = 0;
+    for (uint32_t i = threadIdx.x; i < ((upto + 31u) & ~31u); i += blockDim.x) {
+        const bool a = i < upto && slab_is_arrival(G, recv, i);
+        mine += (uint32_t)__popc(__ballot_sync(0xffffffffu, a));  // warp-uniform
+    }
+    if (lane == 0)
+        warp_tot[wid] = mine;
+    __syncthreads();
+    uint32_t counted = 0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); w++)
+        counted += warp_tot[w];
+    __syncthreads();
+    const uint32_t side_base = first_side ? 0u : scnt[2];  // arrivals of the side unpacked first
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+        scnt[first_side ? 2 : 3] = first_side ? counted : side_base + counted;
+    const uint32_t base = side_base + (blockIdx.x == 0 ? 0u : counted);
+
+    const uint32_t j = j0 + threadIdx.x;
+    bool arrival = false;
+    const double* r = nullptr;
+    if (j < n) {
+        r = recv + SLAB_HDR + (size_t)SLAB_REC * j;
+        arrival = slab_is_arrival(G, recv, j);
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, arrival);
+    if (lane == 0)
+        warp_tot[wid] = (uint32_t)__popc(m);
+    __syncthreads();
+    uint32_t before = base;
+    for (int w = 0; w < wid; w++)
+        before += warp_tot[w];
+    const uint32_t rank = before + (uint32_t)__popc(m & ((1u << lane) - 1));
+    if (j < G.ghost_cap) {
+        const uint32_t gslot = ghost_base + j;
+        if (j < n && !arrival) {
+            slab_read_record(A, gslot, r, 2);  // ghost: collides, not integrated
+        } else {
+            A.bflags[gslot] = 4;
+            if (arrival) {
+                if (rank < n_vac)
+                    slab_read_record(A, vacant[rank], r, 3);
+                else
+                    atomicOr(&cnt->overflow, (uint32_t)OVF_SLAB);
             }
         }
-        __syncthreads();
-        if (threadIdx.x == 0)
-            base += chunk_total;
-        __syncthreads();
     }
-    if (threadIdx.x == 0)
-        scnt[2] = base;
 }
 
 static SlabArrays slab_arrays(System* S) {
@@ -376,10 +387,11 @@ int cb200_slab_unpack_dev(cb200_system* sys, const void* recv_left_dev, const vo
     const SlabGeom G = slab_geom(S);
     const SlabArrays A = slab_arrays(S);
     const uint32_t gl = S->slab_nb_static + G.owned_cap, gr = gl + G.ghost_cap;
-    k_slab_unpack<<<1, 1024, 0, S->stream>>>(G, A, S->slab_has_left ? (const double*)recv_left_dev : nullptr, gl,
-                                             S->slab_vacant.p, S->slab_cnt, 1, S->d_cnt);
-    k_slab_unpack<<<1, 1024, 0, S->stream>>>(G, A, S->slab_has_right ? (const double*)recv_right_dev : nullptr, gr,
-                                             S->slab_vacant.p, S->slab_cnt, 0, S->d_cnt);
+    const uint32_t ug = (G.ghost_cap + 1023u) / 1024u;
+    k_slab_unpack<<<ug, 1024, 0, S->stream>>>(G, A, S->slab_has_left ? (const double*)recv_left_dev : nullptr, gl,
+                                              S->slab_vacant.p, S->slab_cnt, 1, S->d_cnt);
+    k_slab_unpack<<<ug, 1024, 0, S->stream>>>(G, A, S->slab_has_right ? (const double*)recv_right_dev : nullptr, gr,
+                                              S->slab_vacant.p, S->slab_cnt, 0, S->d_cnt);
     S->launches += 2;
     CB_CUDA(cudaGetLastError());
     S->meta_dirty = true;
