@@ -117,6 +117,7 @@ struct DevCounters {
     uint32_t n_cslots;           // contact slots reserved for the complex pairs (PreprocessCount's rule per pair)
     uint32_t need_cslots;
     uint32_t n_slow;             // bins queued for k_pair_masks_slow
+    uint32_t n_long;             // ... of which have more than 64 entries (kept right behind n_slow: one memset)
     uint32_t n_cls[4];           // complex pairs per narrowphase class (k_cplx_collect buckets them for k_cplx_narrow)
 };
 

@@ -428,8 +428,11 @@ __global__ void __launch_bounds__(PAIR_THREADS, 2) k_pair_masks(const ShapeMeta*
         // ---- the rest (a non-sphere in the bin, MPR for everything, or more than 64 entries) is queued for
         // k_pair_masks_slow, a warp per bin: kept out of this kernel so that a tile along a wall does not hold
         // its CTA at the barrier below while the other warps idle
-        if (own && s == e && (k > 64 || (k >= 2 && !fast)))
+        if (own && s == e && (k > 64 || (k >= 2 && !fast))) {
             slow_bins[atomicAdd(&cnt->n_slow, 1u)] = s;
+            if (k > 64)
+                atomicAdd(&cnt->n_long, 1u);
+        }
         __syncthreads();
         // masks of the rows this tile owns and has decided
         if (own && (k < 2 || (k <= 64 && fast))) {
@@ -928,6 +931,8 @@ __global__ void __launch_bounds__(128) k_pair_store_long(const ShapeMeta* __rest
         return;
     if (ent_off[cnt->n_intersections] > cap)
         return;  // k_pair_store raises the flag
+    if (cnt->n_long == 0)
+        return;
     const uint32_t nslow = cnt->n_slow;
     const int lane = threadIdx.x & 31;
     const uint32_t nw = gridDim.x * (blockDim.x >> 5);
@@ -1004,7 +1009,7 @@ static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
     if (mode == MODE_CONTACTS)
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_pairs, 0, 4, S->stream));
     const int gm = grid_for(S, S->cap_entries, PAIR_TILE, 4);
-    CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_slow, 0, 4, S->stream));
+    CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_slow, 0, 8, S->stream));  // n_slow, n_long
     const int gs = S->num_sms * 8;
     CplxArgs X = {};
     X.s_lrot = S->s_lrot.p, X.rot = S->rot.p, X.s_verts = S->s_verts.p, X.cplx_out = S->cplx_out.p;
