@@ -244,3 +244,43 @@ def test_complex_pairs_in_long_bins(ref, algorithm):
     assert np.diff(start.astype(np.int64)).max() > 64
     _, counts = np.unique(rk["shape_ids"], return_counts=True)
     assert algorithm == MPR or counts.max() >= 2
+
+
+def test_bodies_and_shapes_added_between_steps():
+    """ChSystemMulticore::AddBody after the system has stepped (MC/physics/ChSystemMulticore.cpp:205-226): a system
+    that receives its bodies and shapes in two batches, with a collision pass in between, ends up with the same
+    contact list and takes the same step as one that got them all at once."""
+    scene = cluttered([SPHERE, BOX, CAPSULE, TRIANGLE, CONVEXHULL, SPHERE], 6, 0.15, 17, HYBRID, 0.0)
+    whole = cw.load_scene(cw.ChSystemMulticoreSMC(), scene)
+    nb = scene["mass"].size
+    nb1 = nb // 2
+    sel1, sel2 = scene["shape_body"] < nb1, scene["shape_body"] >= nb1
+    part = cw.ChSystemMulticoreSMC()
+    st = part.GetSettings()
+    for k, v in scene["settings"].items():
+        cur = getattr(st, k)
+        if hasattr(cur, "__len__"):
+            cur[:] = list(v)
+        else:
+            setattr(st, k, v)
+    part.SetMaterials(scene["materials"])
+    part.AddShapeVertices(scene["shape_verts"])
+    for lo, hi, sel in ((0, nb1, sel1), (nb1, nb, sel2)):
+        part.AddBodies(scene["mass"][lo:hi], scene["inertia"][lo:hi], scene["pos"][lo:hi], scene["rot"][lo:hi],
+                       scene["vel"][lo:hi], scene["active"][lo:hi], scene["collide"][lo:hi])
+        part.AddShapes(scene["shape_type"][sel], scene["shape_body"][sel], scene["shape_dims"][sel],
+                       scene["shape_pos"][sel], scene["shape_rot"][sel], scene["shape_fam"][sel], scene["shape_mat"][sel])
+        if lo == 0:  # the system steps with the first batch only, which is then put back where it started
+            part.DoStepDynamics()
+            part.SetBodyState(0, scene["pos"][:nb1], scene["rot"][:nb1], scene["vel"][:nb1])
+    whole.RunCollision(7)
+    part.SetBodyState(0, scene["pos"], scene["rot"], scene["vel"])
+    part.RunCollision(7)
+    a, b = whole.GetContacts(), part.GetContacts()
+    assert a["depth"].size > 200
+    for key in KEYS:
+        assert np.array_equal(a[key], b[key]), key
+    whole.DoStepDynamics()
+    part.DoStepDynamics()
+    for x, y in zip(whole.GetBodyState(), part.GetBodyState()):
+        assert np.array_equal(x, y)
