@@ -706,13 +706,15 @@ static int enqueue_one_step(System* S) {
     CB_TRY(timer_stop(S, "collision_narrow"));
     CB_TRY(timer_stop(S, "collision"));
     CB_TRY(timer_start(S, "advance"));
-    if (S->set.system_type == 1)
-        CB_TRY(enqueue_smc(S));
-    else
-        CB_TRY(enqueue_nsc(S));
-    CB_TRY(timer_stop(S, "advance"));
-    CB_TRY(timer_start(S, "integrate"));
-    CB_TRY(enqueue_integrate(S));
+    S->defer_vel_update = S->set.system_type == 1;  // SMC: k_integrate<true> also does v += M^-1 hf
+    int rc = S->set.system_type == 1 ? enqueue_smc(S) : enqueue_nsc(S);
+    if (rc == CB200_OK) {
+        CB_TRY(timer_stop(S, "advance"));
+        CB_TRY(timer_start(S, "integrate"));
+        rc = enqueue_integrate(S);
+    }
+    S->defer_vel_update = false;
+    CB_TRY(rc);
     CB_TRY(timer_stop(S, "integrate"));
     CB_TRY(timer_stop(S, "step"));
     return CB200_OK;
@@ -859,11 +861,12 @@ int cb200_step_host(cb200_system* sys, double* pos, double* rot, double* vel) {
         CB_TRY(enqueue_pairs_only(S, false, true, /*defer_geometry=*/S->set.system_type == 1));
         CB_CUDA(cudaStreamWaitEvent(S->stream, S->ev_copy, 0));
         CB_TRY(enqueue_update_forces(S));
-        if (S->set.system_type == 1)
-            CB_TRY(enqueue_smc(S));
-        else
-            CB_TRY(enqueue_nsc(S));
-        CB_TRY(enqueue_integrate(S));
+        S->defer_vel_update = S->set.system_type == 1;
+        int rc = S->set.system_type == 1 ? enqueue_smc(S) : enqueue_nsc(S);
+        if (rc == CB200_OK)
+            rc = enqueue_integrate(S);
+        S->defer_vel_update = false;
+        CB_TRY(rc);
         CB_CUDA(cudaMemcpyAsync(pos, S->pos.p, 3 * nb * sizeof(double), cudaMemcpyDeviceToHost, S->stream));
         CB_CUDA(cudaMemcpyAsync(rot, S->rot.p, 4 * nb * sizeof(double), cudaMemcpyDeviceToHost, S->stream));
         CB_CUDA(cudaMemcpyAsync(vel, S->vel.p, 6 * nb * sizeof(double), cudaMemcpyDeviceToHost, S->stream));

@@ -45,9 +45,14 @@ __global__ void __launch_bounds__(256) k_update_forces(uint32_t nb, double h, d3
 }
 
 // x += h v ;  q <- dq(h R w) * q   (ChBody::VariablesQbIncrementPosition), active bodies only
+// VEL: the velocity update of the SMC solve (k_vel_update, smc.cu: v += M^-1 hf, same operations) is done here, in
+// the same pass over the bodies -- used by the whole-step paths, where nothing reads the velocities in between.
+template <bool VEL>
 __global__ void __launch_bounds__(256) k_integrate(uint32_t nb, double h, const uint8_t* __restrict__ bflags,
-                                                   const double* __restrict__ vel, double* __restrict__ pos,
-                                                   double* __restrict__ rot, DevCounters* __restrict__ cnt) {
+                                                   double* __restrict__ vel, double* __restrict__ pos,
+                                                   double* __restrict__ rot, const double* __restrict__ mass,
+                                                   const double* __restrict__ inv_inertia,
+                                                   const double* __restrict__ hf, DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -55,7 +60,17 @@ __global__ void __launch_bounds__(256) k_integrate(uint32_t nb, double h, const 
         cnt->steps_done++;  // this step was applied in full (nothing upstream overflowed)
     if (b >= nb || !(bflags[b] & 1u))
         return;
-    const double* v = vel + 6 * (size_t)b;
+    double* v = vel + 6 * (size_t)b;
+    if (VEL) {
+        const double inv_mass = 1.0 / mass[b];
+        const double* f = hf + 6 * (size_t)b;
+        v[0] = v[0] + inv_mass * f[0];
+        v[1] = v[1] + inv_mass * f[1];
+        v[2] = v[2] + inv_mass * f[2];
+        v[3] = v[3] + inv_inertia[3 * b] * f[3];
+        v[4] = v[4] + inv_inertia[3 * b + 1] * f[4];
+        v[5] = v[5] + inv_inertia[3 * b + 2] * f[5];
+    }
     double* p = pos + 3 * (size_t)b;
     p[0] = p[0] + v[0] * h;
     p[1] = p[1] + v[1] * h;
@@ -107,8 +122,13 @@ int enqueue_update_forces(System* S) {
 int enqueue_integrate(System* S) {
     if (S->nb == 0)
         return CB200_OK;
-    k_integrate<<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(S->nb, S->set.step_size, S->bflags.p, S->vel.p, S->pos.p,
-                                                               S->rot.p, S->d_cnt);
+    if (S->defer_vel_update)
+        k_integrate<true><<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(
+            S->nb, S->set.step_size, S->bflags.p, S->vel.p, S->pos.p, S->rot.p, S->mass.p, S->inv_inertia.p, S->hf.p,
+            S->d_cnt);
+    else
+        k_integrate<false><<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(
+            S->nb, S->set.step_size, S->bflags.p, S->vel.p, S->pos.p, S->rot.p, nullptr, nullptr, nullptr, S->d_cnt);
     S->launches++;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;

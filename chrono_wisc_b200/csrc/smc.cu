@@ -762,9 +762,10 @@ int enqueue_smc(System* S) {
         S->c_bids.p, S->ct_force.p, S->ct_torque.p, S->heavy_list.p, S->d_cnt, chunk_cap, S->heavy_part.p);
     k_heavy_final<<<MAX_HEAVY, 256, 0, S->stream>>>(S->heavy_list.p, S->d_cnt, chunk_cap, S->heavy_part.p,
                                                     st.step_size, S->b_force.p, S->hf.p, S->d_cnt);
-    k_vel_update<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->bflags.p, S->mass.p, S->inv_inertia.p, S->hf.p,
-                                                             S->vel.p, S->d_cnt);
-    S->launches += 6;
+    if (!S->defer_vel_update)
+        k_vel_update<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->bflags.p, S->mass.p, S->inv_inertia.p, S->hf.p,
+                                                                 S->vel.p, S->d_cnt);
+    S->launches += S->defer_vel_update ? 5 : 6;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;
 }
