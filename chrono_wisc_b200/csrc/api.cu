@@ -694,7 +694,8 @@ int cb200_integrate(cb200_system* sys) {
 static int enqueue_one_step(System* S) {
     CB_TRY(timer_start(S, "step"));
     CB_TRY(timer_start(S, "update"));
-    CB_TRY(enqueue_update_forces(S));
+    if (S->set.system_type != 1)  // SMC: formed in k_body_reduce<true> (defer_update_forces below)
+        CB_TRY(enqueue_update_forces(S));
     CB_TRY(timer_stop(S, "update"));
     CB_TRY(timer_start(S, "collision"));
     CB_TRY(timer_start(S, "collision_broad"));
@@ -706,14 +707,14 @@ static int enqueue_one_step(System* S) {
     CB_TRY(timer_stop(S, "collision_narrow"));
     CB_TRY(timer_stop(S, "collision"));
     CB_TRY(timer_start(S, "advance"));
-    S->defer_vel_update = S->set.system_type == 1;  // SMC: k_integrate<true> also does v += M^-1 hf
+    S->defer_vel_update = S->defer_update_forces = S->set.system_type == 1;  // SMC: done in k_integrate<true> / k_body_reduce<true>
     int rc = S->set.system_type == 1 ? enqueue_smc(S) : enqueue_nsc(S);
     if (rc == CB200_OK) {
         CB_TRY(timer_stop(S, "advance"));
         CB_TRY(timer_start(S, "integrate"));
         rc = enqueue_integrate(S);
     }
-    S->defer_vel_update = false;
+    S->defer_vel_update = S->defer_update_forces = false;
     CB_TRY(rc);
     CB_TRY(timer_stop(S, "integrate"));
     CB_TRY(timer_stop(S, "step"));
@@ -860,12 +861,14 @@ int cb200_step_host(cb200_system* sys, double* pos, double* rot, double* vel) {
         CB_TRY(enqueue_bins(S));
         CB_TRY(enqueue_pairs_only(S, false, true, /*defer_geometry=*/S->set.system_type == 1));
         CB_CUDA(cudaStreamWaitEvent(S->stream, S->ev_copy, 0));
-        CB_TRY(enqueue_update_forces(S));
+        if (S->set.system_type != 1)
+            CB_TRY(enqueue_update_forces(S));
+        S->defer_update_forces = S->set.system_type == 1;
         S->defer_vel_update = S->set.system_type == 1;
         int rc = S->set.system_type == 1 ? enqueue_smc(S) : enqueue_nsc(S);
         if (rc == CB200_OK)
             rc = enqueue_integrate(S);
-        S->defer_vel_update = false;
+        S->defer_vel_update = S->defer_update_forces = false;
         CB_TRY(rc);
         CB_CUDA(cudaMemcpyAsync(pos, S->pos.p, 3 * nb * sizeof(double), cudaMemcpyDeviceToHost, S->stream));
         CB_CUDA(cudaMemcpyAsync(rot, S->rot.p, 4 * nb * sizeof(double), cudaMemcpyDeviceToHost, S->stream));

@@ -266,6 +266,7 @@ struct System {
 
     std::map<std::string, Timer> timers;
     int timed_steps = 0;
+    bool defer_update_forces = false;  // whole-step paths (SMC): hf is formed in k_body_reduce<true>, k_update_forces is skipped
     bool defer_vel_update = false;   // whole-step paths (SMC): v += M^-1 hf is done by k_integrate<true>, not k_vel_update
     bool capturing = false;          // a step is being captured into a CUDA graph: timers are skipped
     cudaGraphExec_t step_graph = nullptr;

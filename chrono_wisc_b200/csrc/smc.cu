@@ -462,17 +462,46 @@ __global__ void __launch_bounds__(256) k_inc_fill(const int32_t* __restrict__ bi
     }
 }
 
+// What k_update_forces (integrate.cu) reads: with UPD the body's hf = h (m g + F_applied, T_applied - w x J w) is
+// formed here, by the same operations, instead of being written by that kernel and read back.
+struct UpdArgs {
+    d3 g;
+    const double *mass, *inertia, *vel, *fapp;
+};
+
 // one thread per body: add the body's contacts in ascending contact index, then hf += h * (F, T)
+template <bool UPD>
 __global__ void __launch_bounds__(256) k_body_reduce(uint32_t nb, const uint8_t* __restrict__ heavy,
                                                      const uint32_t* __restrict__ off, const uint32_t* __restrict__ inc,
                                                      const double* __restrict__ ct_force,
                                                      const double* __restrict__ ct_torque, double h,
                                                      double* __restrict__ b_force, double* __restrict__ hf,
-                                                     DevCounters* __restrict__ cnt) {
+                                                     UpdArgs U, DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     bool touched = false;
+    d3 bF = mk3(0), bT = mk3(0);
+    if (UPD && b < nb) {
+        const double m = U.mass[b];
+        const double* v = U.vel + 6 * (size_t)b;
+        const d3 w = mk3(v[3], v[4], v[5]);
+        const d3 Jw = mk3(U.inertia[3 * b] * w.x, U.inertia[3 * b + 1] * w.y, U.inertia[3 * b + 2] * w.z);
+        const d3 gyro = cross3(w, Jw);
+        d3 F = U.g * m;
+        d3 T = mk3(0);
+        if (U.fapp) {
+            const double* a = U.fapp + 6 * (size_t)b;
+            F += mk3(a[0], a[1], a[2]);
+            T += mk3(a[3], a[4], a[5]);
+        }
+        bF = h * F;
+        bT = h * (T - gyro);
+        if (heavy[b]) {  // its contacts are added by k_heavy_final
+            double* q = hf + 6 * (size_t)b;
+            q[0] = bF.x, q[1] = bF.y, q[2] = bF.z, q[3] = bT.x, q[4] = bT.y, q[5] = bT.z;
+        }
+    }
     if (b < nb && !heavy[b]) {
         const uint32_t s = off[b], d = off[b + 1] - s;
         d3 F = mk3(0), T = mk3(0);
@@ -500,11 +529,18 @@ __global__ void __launch_bounds__(256) k_body_reduce(uint32_t nb, const uint8_t*
         }
         double* o = b_force + 6 * (size_t)b;
         o[0] = F.x, o[1] = F.y, o[2] = F.z, o[3] = T.x, o[4] = T.y, o[5] = T.z;
+        double* q = hf + 6 * (size_t)b;
         if (d) {
             touched = true;
             const d3 hF = h * F, hT = h * T;
-            double* q = hf + 6 * (size_t)b;
-            q[0] += hF.x, q[1] += hF.y, q[2] += hF.z, q[3] += hT.x, q[4] += hT.y, q[5] += hT.z;
+            if (UPD) {
+                q[0] = bF.x + hF.x, q[1] = bF.y + hF.y, q[2] = bF.z + hF.z;
+                q[3] = bT.x + hT.x, q[4] = bT.y + hT.y, q[5] = bT.z + hT.z;
+            } else {
+                q[0] += hF.x, q[1] += hF.y, q[2] += hF.z, q[3] += hT.x, q[4] += hT.y, q[5] += hT.z;
+            }
+        } else if (UPD) {
+            q[0] = bF.x, q[1] = bF.y, q[2] = bF.z, q[3] = bT.x, q[4] = bT.y, q[5] = bT.z;
         }
     }
     const unsigned m = __ballot_sync(0xffffffffu, touched);
@@ -754,9 +790,17 @@ int enqueue_smc(System* S) {
     k_inc_fill<<<cgrid, 256, 0, S->stream>>>(S->c_bids.p, S->heavy.p, S->b_deg.p, S->b_cursor.p, S->b_inc.p, S->d_cnt);
     k_heavy_list<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->heavy.p, S->heavy_list.p, S->d_cnt);
     CB_TRY(timer_start(S, "k_body_reduce"));
-    k_body_reduce<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->heavy.p, S->b_deg.p, S->b_inc.p, S->ct_force.p,
-                                                              S->ct_torque.p, st.step_size, S->b_force.p, S->hf.p,
-                                                              S->d_cnt);
+    UpdArgs U;
+    U.g = mk3(st.gravity[0], st.gravity[1], st.gravity[2]);
+    U.mass = S->mass.p, U.inertia = S->inertia.p, U.vel = S->vel.p, U.fapp = S->has_fapp ? S->fapp.p : nullptr;
+    if (S->defer_update_forces)
+        k_body_reduce<true><<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->heavy.p, S->b_deg.p, S->b_inc.p,
+                                                                        S->ct_force.p, S->ct_torque.p, st.step_size,
+                                                                        S->b_force.p, S->hf.p, U, S->d_cnt);
+    else
+        k_body_reduce<false><<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->heavy.p, S->b_deg.p, S->b_inc.p,
+                                                                         S->ct_force.p, S->ct_torque.p, st.step_size,
+                                                                         S->b_force.p, S->hf.p, U, S->d_cnt);
     CB_TRY(timer_stop(S, "k_body_reduce"));
     k_heavy_partial<<<dim3(grid_for(S, chunk_cap, 1, 4), 4), 256, 0, S->stream>>>(
         S->c_bids.p, S->ct_force.p, S->ct_torque.p, S->heavy_list.p, S->d_cnt, chunk_cap, S->heavy_part.p);
