@@ -66,6 +66,13 @@ void invalidate_step_graph(System* S) {
     S->direct_steps = 0;
 }
 
+// `unsupported` is sticky on the device (a step in the middle of a chunk must not hide it): the host clears it at the
+// start of a synchronising call, i.e. right after the previous call has read and reported it.
+static int clear_unsupported(System* S) {
+    CB_CUDA(cudaMemsetAsync(&S->d_cnt->unsupported, 0, 4, S->stream));
+    return CB200_OK;
+}
+
 int fetch_counters(System* S) {
     CB_CUDA(cudaMemcpyAsync(S->h_cnt, S->d_cnt, sizeof(DevCounters), cudaMemcpyDeviceToHost, S->stream));
     CB_CUDA(cudaStreamSynchronize(S->stream));
@@ -93,17 +100,24 @@ static int alloc_bins(System* S, uint32_t n) {
     S->cap_bins = (uint32_t)std::min<size_t>(S->bin_cursor.cap - 1, S->bin_start.cap - 2);
     return CB200_OK;
 }
+static int alloc_pairq(System* S, uint32_t n) {
+    invalidate_step_graph(S);
+    CB_TRY(S->pair_q.reserve(n));
+    S->cap_pairq = (uint32_t)S->pair_q.cap;
+    return CB200_OK;
+}
 static int alloc_entries(System* S, uint32_t n) {
     invalidate_step_graph(S);
     CB_TRY(S->ent_tmp.reserve(n));
     CB_TRY(S->ent_bin.reserve(n));
     CB_TRY(S->ent_shape.reserve(n));
     CB_TRY(S->ent_mask.reserve(n));
-    CB_TRY(S->ent_c.reserve(4 * (size_t)S->ent_tmp.cap));
-    CB_TRY(S->ent_m.reserve(S->ent_tmp.cap));
     S->cap_entries = (uint32_t)S->ent_tmp.cap;
     CB_TRY(S->ent_off.reserve((size_t)S->cap_entries + 4));
     CB_TRY(S->slow_bins.reserve((size_t)S->cap_entries + 4));
+    CB_TRY(S->long_bins.reserve((size_t)S->cap_entries / 64 + 4));
+    if (S->cap_pairq == 0)
+        CB_TRY(alloc_pairq(S, S->cap_entries / 4 + 1024));
     if (use_complex(S)) {
         CB_TRY(S->ent_cmask.reserve(S->cap_entries));
         CB_TRY(S->ent_cbase.reserve(S->cap_entries));
@@ -183,6 +197,9 @@ int grow_after_overflow(System* S) {
         return set_error(CB200_ERR_UNSUPPORTED, "more than 4096 shapes span more than 48 bins each");
     if (c.overflow & OVF_HEAVY)
         return set_error(CB200_ERR_UNSUPPORTED, "more than 64 bodies own a shape spanning more than 48 bins");
+    if (c.overflow & OVF_SLAB)
+        return set_error(CB200_ERR_STATE, "slab ghost / arrival capacity exceeded: bodies that crossed into this slab "
+                                          "were dropped (recreate the slab system with larger owned_cap / ghost_cap)");
     if (c.overflow & OVF_BINS) {
         if (c.need_bins > (1u << 28))
             return set_error(CB200_ERR_UNSUPPORTED, "broadphase grid has more than 2^28 bins");
@@ -196,6 +213,8 @@ int grow_after_overflow(System* S) {
         CB_TRY(alloc_pairs(S, c.need_pairs + c.need_pairs / 8));
     if (c.overflow & OVF_COMPLEX)
         CB_TRY(alloc_complex(S, c.need_complex + c.need_complex / 4, c.need_cslots + c.need_cslots / 4));
+    if (c.overflow & OVF_PAIRQ)
+        CB_TRY(alloc_pairq(S, c.need_pairq + c.need_pairq / 4));
     if (c.overflow & OVF_NSC)
         S->nsc_extra_slots = 2 * S->nsc_extra_slots + 32 + (int)c.need_nsc_slots / 4;
     CB_CUDA(cudaMemsetAsync(&S->d_cnt->overflow, 0, 4, S->stream));
@@ -312,7 +331,7 @@ void cb200_destroy(cb200_system* sys) {
     REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(bflags); REL(heavy);
     REL(s_type); REL(s_body); REL(s_fam); REL(s_mat); REL(s_lpos); REL(s_lrot); REL(s_dims); REL(general_ids); REL(s_verts); REL(sh_neigh); REL(sh_touch); REL(sh_disp); REL(sh_relvel); REL(sh_dur); REL(s_wpos); REL(s_wrot);
     REL(s_box); REL(s_meta); REL(mat_smc); REL(mat_nsc); REL(bin_intersections); REL(bin_start); REL(bin_cursor);
-    REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_mask); REL(ent_c); REL(ent_m); REL(ent_off); REL(slow_bins); REL(large_list); REL(pairs);
+    REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_mask); REL(ent_off); REL(slow_bins); REL(long_bins); REL(pair_q); REL(large_list); REL(pairs);
     REL(c_norm); REL(c_pta); REL(c_ptb); REL(c_depth); REL(c_erad); REL(c_bids); REL(c_shapes); REL(c_mats);
     REL(ent_cmask); REL(ent_cbase); REL(cplx_rec); REL(cplx_n); REL(cplx_cls); REL(cplx_out); REL(c_src);
     REL(ct_force); REL(ct_torque); REL(b_deg); REL(b_cursor); REL(b_inc); REL(b_force); REL(heavy_list);
@@ -658,6 +677,7 @@ int cb200_update_forces(cb200_system* sys) {
 int cb200_run_collision(cb200_system* sys, int stages) {
     System* S = SYS(sys);
     CB_CUDA(cudaSetDevice(S->device));
+    CB_TRY(clear_unsupported(S));
     return run_stage(S, [&]() -> int {
         // a retry after a capacity overflow restarts from the AABBs (OffsetAABB rewrites the boxes in place)
         if ((stages & 1) || ((stages & 2) && S->box_relative))
@@ -770,6 +790,7 @@ static int replay_or_enqueue_step(System* S) {
     if (S->step_graph_meta)
         S->meta_dirty = false;
     S->pairs_valid = false;
+    S->contacts_geom_valid = false;  // the replayed step made a new key list; the records are those of an older one
     S->box_relative = true;
     return CB200_OK;
 }
@@ -799,6 +820,7 @@ int cb200_do_steps(cb200_system* sys, int nsteps) {
         const int chunk = remaining < 64 ? remaining : 64;
         CB_TRY(timer_start(S, "do_steps"));
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->steps_done, 0, 4, S->stream));
+        CB_TRY(clear_unsupported(S));
         CB_TRY(enqueue_one_step(S));
         S->direct_steps++;
         for (int s = 1; s < chunk; s++)
@@ -849,6 +871,7 @@ int cb200_step_host(cb200_system* sys, double* pos, double* rot, double* vel) {
     const size_t nb = S->nb;
     for (int attempt = 0; attempt < 8; attempt++) {
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->steps_done, 0, 4, S->stream));
+        CB_TRY(clear_unsupported(S));
         CB_CUDA(cudaMemcpyAsync(S->pos.p, pos, 3 * nb * sizeof(double), cudaMemcpyHostToDevice, S->stream));
         CB_CUDA(cudaMemcpyAsync(S->rot.p, rot, 4 * nb * sizeof(double), cudaMemcpyHostToDevice, S->stream));
         // the velocities follow the pose over the link (not beside it: both would share the bandwidth and the
@@ -922,9 +945,11 @@ int cb200_check(cb200_system* sys) {
     if (S->h_cnt->overflow)
         return set_error(CB200_ERR_STATE, "a device capacity was exceeded during asynchronous stepping (overflow mask " +
                                               std::to_string(S->h_cnt->overflow) + "); steps after it did not run");
-    if (S->h_cnt->unsupported)
+    if (S->h_cnt->unsupported) {
+        CB_TRY(clear_unsupported(S));  // read and reported: the next check starts clean
         return set_error(CB200_ERR_UNSUPPORTED, std::to_string(S->h_cnt->unsupported) +
                                                     " candidate pairs have a shape combination this backend cannot test yet");
+    }
     return CB200_OK;
 }
 

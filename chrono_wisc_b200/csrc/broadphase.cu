@@ -7,7 +7,8 @@
 //                                       (on the device, so the step needs no host round trip)
 //   OffsetAABB + f_Count_AABB_BIN     CMC/ChBroadphase.cpp:168-176,261-268         -> k_bin_count
 //   exclusive_scan / sort_by_key / RLE CMC/ChBroadphase.cpp:271-301                -> counting sort: histogram with
-//                                       warp-aggregated atomics, packed u64 scan, scatter, in-bin rank sort
+//                                       warp-aggregated atomics, packed u64 scan, scatter; the in-bin rank sort is
+//                                       done by the pair kernel on its staged tile (pairs.cu)
 //   f_Count/Store_AABB_AABB_Intersection  CMC/ChCollisionUtilsBroadphase.cpp:86-217
 //   + PreprocessCount / DispatchPRIMS / remove_if  CMC/ChNarrowphase.cpp:94-155,264-320,366-385
 //                                                                                  -> k_pairs<COUNT>, k_pairs<STORE>
@@ -79,7 +80,7 @@ __global__ void k_reset_counters(DevCounters* cnt, uint32_t nb, uint32_t ns) {
         cnt->n_large = 0;
         cnt->n_heavy = 0;
         cnt->ct_body_count = 0;
-        cnt->unsupported = 0;
+        // cnt->unsupported is sticky: only the host clears it, after it has read it (api.cu clear_unsupported)
     }
 }
 
@@ -388,17 +389,19 @@ __global__ void __launch_bounds__(256) k_bin_count(GridSettings st, double envel
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1)
             wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, d));
-        const int ny = hi[1] - lo[1] + 1, nz = hi[2] - lo[2] + 1;
+        // the shape's bins, x slowest / z fastest, walked with counters (no division per bin)
+        int ix = lo[0], iy = lo[1], iz = lo[2];
         for (uint32_t it = 0; it < wmax; it++) {
             const bool valid = it < mine;
-            uint32_t b = 0;
-            if (valid) {
-                const int ix = lo[0] + (int)(it / (uint32_t)(ny * nz));
-                const int rem = (int)(it % (uint32_t)(ny * nz));
-                const int iy = lo[1] + rem / nz, iz = lo[2] + rem % nz;
-                b = (uint32_t)((iz * g.bins[1]) * g.bins[0] + iy * g.bins[0] + ix);  // Hash_Index
-            }
+            const uint32_t b = (uint32_t)((iz * g.bins[1]) * g.bins[0] + iy * g.bins[0] + ix);  // Hash_Index
             warp_agg<1>(hist, b, valid);
+            if (++iz > hi[2]) {
+                iz = lo[2];
+                if (++iy > hi[1]) {
+                    iy = lo[1];
+                    ++ix;
+                }
+            }
         }
     }
 }
@@ -490,15 +493,16 @@ __global__ void __launch_bounds__(256) k_bin_fill(uint32_t ns, double envelope, 
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1)
             wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, d));
-        const int ny = hi[1] - lo[1] + 1, nz = hi[2] - lo[2] + 1;
+        int ix = lo[0], iy = lo[1], iz = lo[2];
         for (uint32_t it = 0; it < wmax; it++) {
             const bool valid = it < mine;
-            uint32_t b = 0;
-            if (valid) {
-                const int ix = lo[0] + (int)(it / (uint32_t)(ny * nz));
-                const int rem = (int)(it % (uint32_t)(ny * nz));
-                const int iy = lo[1] + rem / nz, iz = lo[2] + rem % nz;
-                b = (uint32_t)((iz * g.bins[1]) * g.bins[0] + iy * g.bins[0] + ix);
+            const uint32_t b = (uint32_t)((iz * g.bins[1]) * g.bins[0] + iy * g.bins[0] + ix);
+            if (++iz > hi[2]) {
+                iz = lo[2];
+                if (++iy > hi[1]) {
+                    iy = lo[1];
+                    ++ix;
+                }
             }
             const uint32_t slot = warp_agg<-1>(cursor, b, valid);
             if (valid) {
@@ -507,52 +511,6 @@ __global__ void __launch_bounds__(256) k_bin_fill(uint32_t ns, double envelope, 
                 ent_bin[e] = b;
             }
         }
-    }
-}
-
-// rank sort of every bin's entries by shape id (ids are unique inside a bin): what the reference gets from its
-// stable sort_by_key on the bin number
-__global__ void __launch_bounds__(256) k_bin_sort(const uint32_t* __restrict__ ent_tmp,
-                                                  const uint32_t* __restrict__ ent_bin,
-                                                  const uint64_t* __restrict__ bin_start,
-                                                  const ShapeMeta* __restrict__ meta,
-                                                  const double* __restrict__ s_wpos,
-                                                  const ShapeBox* __restrict__ s_box, double envelope,
-                                                  uint32_t* __restrict__ ent_shape, double* __restrict__ ent_c,
-                                                  ShapeMeta* __restrict__ ent_m, const DevCounters* __restrict__ cnt) {
-    if (cnt->overflow)
-        return;
-    const uint32_t ni = cnt->n_intersections;
-    const GridParams g = load_grid(cnt);
-    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < ni; e += gridDim.x * blockDim.x) {
-        const uint32_t b = ent_bin[e];
-        const uint32_t s = (uint32_t)bin_start[b], t = (uint32_t)bin_start[b + 1];
-        const uint32_t id = ent_tmp[e];
-        // the gathers of the per-shape records happen here, in a cheap, latency-tolerant kernel; the pair kernel
-        // then streams the bin-sorted copies
-        ShapeMeta m = meta[id];
-        const double4 w = reinterpret_cast<const double4*>(s_wpos)[id];
-        uint32_t rank = 0;
-        for (uint32_t j = s; j < t; j++)
-            rank += ent_tmp[j] < id;
-        const uint32_t o = s + rank;
-        ent_shape[o] = id;
-        m.pad = id;
-        // info bits 3..5: the shape's lower corner hashes to this bin's x / y / z coordinate.  HashMin is monotone, so
-        // current_bin(A, B) (CMC/ChCollisionUtils.h:97-110), i.e. Hash(max(Amin, Bmin)) == bin, holds iff on every
-        // axis at least one of the two entries carries the flag (both lower corners hash to <= the bin coordinate).
-        {
-            double mn[3], mx[3];
-            shape_box_rel(id, m.info, s_wpos, s_box, g.origin, envelope, mn, mx);
-            const int bx = (int)(b % (uint32_t)g.bins[0]), by = (int)((b / (uint32_t)g.bins[0]) % (uint32_t)g.bins[1]),
-                      bz = (int)(b / ((uint32_t)g.bins[0] * (uint32_t)g.bins[1]));
-            const uint32_t f = ((int)floor(mn[0] * g.inv[0]) == bx ? 8u : 0u) |
-                               ((int)floor(mn[1] * g.inv[1]) == by ? 16u : 0u) |
-                               ((int)floor(mn[2] * g.inv[2]) == bz ? 32u : 0u);
-            m.info = (m.info & ~56u) | f;
-        }
-        ent_m[o] = m;
-        reinterpret_cast<double4*>(ent_c)[o] = w;
     }
 }
 
@@ -617,12 +575,8 @@ int enqueue_bins(System* S) {
     k_bin_large<true><<<S->num_sms * 4, 256, 0, S->stream>>>(S->s_meta.p, S->s_wpos.p, S->s_box.p, env, S->large_list.p, S->d_cnt,
                                                  S->cap_entries, S->bin_cursor.p, S->bin_start.p, S->ent_tmp.p,
                                                  S->ent_bin.p);
-    CB_TRY(timer_start(S, "k_bin_sort"));
-    k_bin_sort<<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(S->ent_tmp.p, S->ent_bin.p, S->bin_start.p,
-                                                                        S->s_meta.p, S->s_wpos.p, S->s_box.p, env,
-                                                                        S->ent_shape.p, S->ent_c.p, S->ent_m.p, S->d_cnt);
-    CB_TRY(timer_stop(S, "k_bin_sort"));
-    S->launches += 3;
+    // the in-bin sort by shape id happens in the pair kernel, on the staged tile (pairs.cu)
+    S->launches += 2;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;
 }

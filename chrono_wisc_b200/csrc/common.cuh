@@ -87,7 +87,7 @@ struct __align__(16) ShapeMeta {
 
 // overflow mask bits
 enum { OVF_BINS = 1, OVF_ENTRIES = 2, OVF_CONTACTS = 4, OVF_PAIRS = 8, OVF_LARGE = 16, OVF_HEAVY = 32, OVF_COMPLEX = 64,
-       OVF_NSC = 128, OVF_SLAB = 256 };
+       OVF_NSC = 128, OVF_SLAB = 256, OVF_PAIRQ = 512 };
 
 // Device-side counters and the broadphase grid (one pinned-host mirror, read back at the single sync of a call).
 struct DevCounters {
@@ -118,6 +118,8 @@ struct DevCounters {
     uint32_t need_cslots;
     uint32_t n_slow;             // bins queued for k_pair_masks_slow
     uint32_t n_long;             // ... of which have more than 64 entries (kept right behind n_slow: one memset)
+    uint32_t n_pairq;            // (wall-bin pairs with a non-sphere) queued for k_pair_queue (right behind n_long)
+    uint32_t need_pairq;
     uint32_t n_cls[4];           // complex pairs per narrowphase class (k_cplx_collect buckets them for k_cplx_narrow)
 };
 
@@ -186,12 +188,13 @@ struct System {
     DevBuf<uint32_t> bin_cursor;         // cap_bins (histogram, then countdown cursor of the scatter)
     DevBuf<uint32_t> ent_tmp;            // cap_entries  shape ids, unsorted inside a bin
     DevBuf<uint32_t> ent_bin;            // cap_entries  bin of every entry
-    DevBuf<uint32_t> ent_shape;          // cap_entries  shape ids sorted inside a bin == bin_aabb_number
-    DevBuf<double> ent_c;                // 4 per entry: world position + dims[0] of the entry's shape, bin-sorted
-    DevBuf<ShapeMeta> ent_m;             // per entry: integer record of the shape (pad = shape id), bin-sorted
+    DevBuf<uint32_t> ent_shape;          // cap_entries  shape ids sorted inside a bin == bin_aabb_number (written by the pair kernels)
     DevBuf<uint64_t> ent_mask;           // cap_entries  bit j set: the entry pairs with the j-th entry of its bin
     DevBuf<uint32_t> ent_off;            // cap_entries+2 outputs per entry -> exclusive offsets
     DevBuf<uint32_t> slow_bins;          // cap_entries  first entries of the bins the warp-per-bin pair kernel takes
+    DevBuf<uint32_t> long_bins;          // cap_entries / 64 + 1  ... of those with more than 64 entries
+    DevBuf<uint64_t> pair_q;             // cap_pairq  (entry, entry) pairs of wall bins that involve a non-sphere
+    uint32_t cap_pairq = 0;
     DevBuf<uint32_t> large_list;         // MAX_LARGE
     DevBuf<int64_t> pairs;               // cap_pairs (materialised on demand only)
     bool pairs_valid = false;

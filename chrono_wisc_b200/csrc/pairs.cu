@@ -31,15 +31,32 @@ namespace cb200 {
 
 constexpr int WIN = PAIR_TILE + PAIR_HALO;
 constexpr int PAIR_THREADS = WIN;  // one thread per window entry
+constexpr int PAIR_WARPS = PAIR_THREADS / 32;
+constexpr int QCAP = 128;    // candidate queue of a warp: 32 rows x 4 candidates per round
+constexpr int NNS_MAX = 4;   // non-spheres in a bin up to which the tile kernel keeps the bin's sphere-sphere pairs
 
-// Shared-memory window, struct-of-arrays: lane-consecutive entries are word-consecutive in every array.
+// Shared-memory window of the slow (warp-per-bin) kernel, struct-of-arrays: lane-consecutive entries are
+// word-consecutive in every array.
 template <int N>
 struct WindowT {
     double mn[3][N], mx[3][N];  // origin-relative AABB
     double c[4][N];             // world position + dims[0] (sphere: centre, radius)
     uint32_t body[N], fam[N], info[N], id[N];
 };
-using Window = WindowT<WIN>;
+
+// Window of the tile kernel.  Sphere records only (centre, radius: the AABB is recomputed from them with the very
+// operations that produced it), plus a float copy for the conservative pre-test and the float classification.
+struct TileSmem {
+    double c[4][WIN];
+    float4 f[WIN];   // centre relative to the bin's lower corner, in float; .w = upper bound of radius + envelope
+                     // (margin included), its low 4 mantissa bits replaced by flags: bits 0..2 "lower corner hashes
+                     // to this bin's x / y / z", bit 3 "sphere that can collide"
+    float rm[WIN];   // lower bound of radius + envelope (margin subtracted)
+    uint32_t body[WIN], fam[WIN], info[WIN], sid[WIN];
+    unsigned long long smask[WIN];
+    unsigned long long nsm[WIN];  // at the slot where a bin starts: which (sorted) slots of the bin hold non-spheres
+    uint32_t queue[PAIR_WARPS][QCAP];
+};
 
 struct Rec {
     double mn[3], mx[3];
@@ -57,22 +74,27 @@ __device__ __forceinline__ void load_rec(Rec& R, uint32_t id, const ShapeMeta* _
     shape_box_rel(id, m.info, s_wpos, s_box, origin, envelope, R.mn, R.mx);
 }
 
-// record of entry e from the bin-sorted copies (coalesced); boxes of non-spheres are gathered
-__device__ __forceinline__ void load_rec_sorted(Rec& R, uint32_t e, const ShapeMeta* __restrict__ ent_m,
-                                                const double* __restrict__ ent_c, const double* __restrict__ s_wpos,
-                                                const ShapeBox* __restrict__ s_box, const double* origin,
-                                                double envelope) {
-    const ShapeMeta m = ent_m[e];
-    const double4 w = reinterpret_cast<const double4*>(ent_c)[e];
-    R.cx = w.x, R.cy = w.y, R.cz = w.z, R.r = w.w;
-    R.body = m.body, R.fam = m.fam, R.info = m.info, R.id = m.pad;
-    if (((m.info >> 8) & 0xff) == CB200_SPHERE) {
-        const double r = w.w + envelope;
-        R.mn[0] = (w.x - r) - origin[0], R.mn[1] = (w.y - r) - origin[1], R.mn[2] = (w.z - r) - origin[2];
-        R.mx[0] = (w.x + r) - origin[0], R.mx[1] = (w.y + r) - origin[1], R.mx[2] = (w.z + r) - origin[2];
-    } else {
-        shape_box_rel(m.pad, m.info, s_wpos, s_box, origin, envelope, R.mn, R.mx);
-    }
+// info bits 3..5 of a record staged for bin (bx, by, bz): the shape's lower corner hashes to the bin's x / y / z
+// coordinate.  HashMin is monotone, so current_bin(A, B) (CMC/ChCollisionUtils.h:97-110), i.e.
+// Hash(max(Amin, Bmin)) == bin, holds iff on every axis at least one of the two entries carries the flag (both
+// lower corners hash to <= the bin coordinate).
+__device__ __forceinline__ uint32_t corner_flags(const double* mn, const GridParams& g, int bx, int by, int bz) {
+    return ((int)floor(mn[0] * g.inv[0]) == bx ? 8u : 0u) | ((int)floor(mn[1] * g.inv[1]) == by ? 16u : 0u) |
+           ((int)floor(mn[2] * g.inv[2]) == bz ? 32u : 0u);
+}
+
+__device__ __forceinline__ void bin_coords(uint32_t b, const GridParams& g, int& bx, int& by, int& bz) {
+    bx = (int)(b % (uint32_t)g.bins[0]);
+    by = (int)((b / (uint32_t)g.bins[0]) % (uint32_t)g.bins[1]);
+    bz = (int)(b / ((uint32_t)g.bins[0] * (uint32_t)g.bins[1]));
+}
+
+// record of shape id as an entry of bin (bx, by, bz): gathered (the per-shape arrays sit in L2), corner flags set
+__device__ __forceinline__ void load_rec_bin(Rec& R, uint32_t id, const ShapeMeta* __restrict__ meta,
+                                             const double* __restrict__ s_wpos, const ShapeBox* __restrict__ s_box,
+                                             const GridParams& g, int bx, int by, int bz, double envelope) {
+    load_rec(R, id, meta, s_wpos, s_box, g.origin, envelope);
+    R.info = (R.info & ~56u) | corner_flags(R.mn, g, bx, by, bz);
 }
 
 template <int N>
@@ -282,16 +304,28 @@ __device__ __forceinline__ T warp_incl_scan_bp(T v, int lane) {
 
 
 // --------------------------------------------------------------------------------------------------------------
-// k_pair_masks: all unordered pairs of a bin, spread evenly over the lanes of the warp that owns the bin.
+// k_pair_masks: the tile kernel.  A CTA takes a 256-entry tile of the (bin, shape) entry list plus a 64-entry forward
+// halo and owns the bins that start in the tile; one thread per window entry.
 //
-// A warp owns the bins whose first entry lies in its 32-entry chunk.  For a bin of k <= 64 entries it walks the
-// k(k-1)/2 pairs in the cyclic order (i, i+d mod k), d = 1..(k-1)/2 (+ half a diagonal when k is even): every
-// lane always has a pair, whatever its position in the bin.  A pair that passes (the broadphase filter alone in
-// PAIRS mode, filter + contact decision in CONTACTS mode) sets bit max(i,j) in the 64-bit mask of entry min(i,j).
-// The masks are all the store pass needs: its output slot for (i, j) is offset[i] + popc(mask[i] below bit j),
-// i.e. the reference's emission order (bin, shape A, shape B), without re-running a single test.
-// Bins with more than 64 entries (coarse grids) are walked row by row by the owning warp and only counted; the
-// store pass re-tests those rows.
+//   stage    every thread fetches one entry (unsorted inside its bin, as the scatter left it), gathers the shape's
+//            records (L2-resident), ranks its shape id among the bin's ids in shared memory and drops the record at
+//            its sorted slot: the in-bin sort by shape id costs no pass of its own, and ent_shape (bin_aabb_number)
+//            is written from here.
+//   phase 1  thread t = row t of the sorted window.  Row i meets its partners j = i + d (mod k), d = 1..(k-1)/2
+//            (+ half a diagonal when k is even): every unordered pair once, the same work for every row.  The test
+//            is a CONSERVATIVE float test (|dc| <= rA + rB + margin on every axis, corner flags, both can collide): it
+//            can only say "certainly not", so list membership is still decided by the exact test alone.  ~7 of 8 pairs
+//            end here after one 16-byte shared load and a dozen FP32 / integer instructions.
+//   phase 2  the survivors of a warp's 32 rows are compacted through a shared queue and spread over all lanes; each
+//            gets the reference's test in FP64, operation for operation: AABB overlap
+//            (f_Count_AABB_AABB_Intersection, CMC/ChCollisionUtilsBroadphase.cpp:114-140), current_bin, the body /
+//            family filters and -- in CONTACTS mode -- the deciding lines of sphere_sphere (ChNarrowphasePRIMS.cpp:52-60).
+//            A hit sets bit max(i,j) in the 64-bit mask of entry min(i,j).
+// The masks are all the store pass needs: its output slot for (i, j) is offset[i] + popc(mask[i] below bit j), i.e.
+// the reference's emission order (bin, shape A, shape B), without re-running a single test.
+// Bins with a few non-spheres (container walls): the sphere-sphere pairs stay here, the rows of the non-spheres are
+// queued for k_pair_masks_slow.  Bins with many non-spheres, with more than 64 entries, or all bins when MPR is
+// requested for everything are queued as a whole.
 // --------------------------------------------------------------------------------------------------------------
 enum { MODE_PAIRS = 0, MODE_CONTACTS = 1 };
 
@@ -312,144 +346,301 @@ __device__ __forceinline__ int pair_decide(const Rec& A, const Rec& B, const Gri
     return n < 0 ? 2 : n;
 }
 
+// rank += (v < id): one compare + one predicated add (the compiler's own select sequence is a third longer, and this
+// is the inner statement of the in-bin sort)
+__device__ __forceinline__ void count_less(uint32_t& rank, uint32_t v, uint32_t id) {
+    asm("{ .reg .pred p; setp.lt.u32 p, %1, %2; @p add.u32 %0, %0, 1; }" : "+r"(rank) : "r"(v), "r"(id));
+}
+
 template <bool CPLX>
-__global__ void __launch_bounds__(PAIR_THREADS, 2) k_pair_masks(const ShapeMeta* __restrict__ meta,
-                                                             const ShapeMeta* __restrict__ ent_m,
-                                                             const double* __restrict__ ent_c,
+__global__ void __launch_bounds__(PAIR_THREADS, 4) k_pair_masks(const ShapeMeta* __restrict__ meta,
                                                              const double* __restrict__ s_wpos,
                                                              const ShapeBox* __restrict__ s_box,
-                                                             const double* __restrict__ s_wrot,
-                                                             const double* __restrict__ s_dims,
-                                                             const uint32_t* __restrict__ ent_shape,
+                                                             const uint32_t* __restrict__ ent_tmp,
                                                              const uint32_t* __restrict__ ent_bin,
                                                              const uint64_t* __restrict__ bin_start, double envelope,
-                                                             int algorithm, int mode, uint64_t* __restrict__ ent_mask,
+                                                             int algorithm, int mode, uint32_t* __restrict__ ent_shape,
+                                                             uint64_t* __restrict__ ent_mask,
                                                              uint64_t* __restrict__ ent_cmask,
                                                              uint32_t* __restrict__ ent_cnt,
                                                              uint32_t* __restrict__ slow_bins,
+                                                             uint32_t* __restrict__ long_bins,
+                                                             uint2* __restrict__ pair_q, uint32_t cap_pairq,
                                                              DevCounters* __restrict__ cnt) {
-    __shared__ Window W;
-    __shared__ unsigned long long smask[WIN];
-    __shared__ unsigned long long scmask[CPLX ? WIN : 1];
-    __shared__ uint8_t mixed[WIN];  // the row's bin holds a non-sphere
+    __shared__ TileSmem T;
     if (cnt->overflow)
         return;
     const GridParams g = load_grid(cnt);
     const uint32_t ni = cnt->n_intersections;
     const uint32_t ntiles = cnt->n_tiles;
     const double sep = 2 * envelope;
-    const int lane = threadIdx.x & 31;
-    const uint32_t t = threadIdx.x;  // window index == row of this thread (WIN == blockDim.x)
-    uint32_t np = 0, ncx = 0;
+    // Margins of the float tests.  A centre is kept relative to its bin's lower corner, |coordinate| <= B + R (B the
+    // largest bin edge, R = radius + envelope), so with u = 2^-24: a float centre is off by <= u (B + R), a float
+    // difference of two by another u |d|, the float norm of the difference by <= 7u (2B + RA + RB) in all.  Each
+    // entry carries the margin m = 16u (B + R) + 2^-45 Eabs (Eabs: largest absolute coordinate of the grid; covers the
+    // FP64 roundings of the exact tests themselves): a float comparison against RA + RB + mA + mB can only say
+    // "certainly not", one against RA + RB - mA - mB only "certainly yes" (error analysis in DESIGN.md section 4.1).
+    const double Bmax = fmax(fmax(cnt->bin_size[0], cnt->bin_size[1]), cnt->bin_size[2]);
+    const double Eabs = fmax(fmax(fmax(fabs(cnt->origin[0]), fabs(cnt->maxpt[0])), fmax(fabs(cnt->origin[1]), fabs(cnt->maxpt[1]))),
+                             fmax(fabs(cnt->origin[2]), fabs(cnt->maxpt[2])));
+    const double m_abs = Eabs * (1.0 / 35184372088832.0);  // 2^-45
+    const double m_rel = 16.0 / 16777216.0;                // 16 u
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const uint32_t t = threadIdx.x;  // window index (WIN == blockDim.x)
+    uint32_t np = 0;
 
     for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const uint32_t e0 = tile * PAIR_TILE;
         const uint32_t wend = min(ni, e0 + WIN);
         const uint32_t e = e0 + t;
         __syncthreads();  // previous tile's readers are done with the window
-        smask[t] = 0ull;
-        if (CPLX)
-            scmask[t] = 0ull;
-        mixed[t] = 0;
-        __syncthreads();
-        // every thread stages one entry and learns its bin (first entry s, length k)
-        Rec A;
-        uint32_t bin = 0, s = 0, k = 0;
-        if (e < wend) {
-            load_rec_sorted(A, e, ent_m, ent_c, s_wpos, s_box, g.origin, envelope);
-            win_put(W, (int)t, A);
+        T.smask[t] = 0ull;
+        T.nsm[t] = 0ull;
+        // ---- stage: one entry per thread, unsorted inside its bin
+        uint32_t id = 0, bin = 0, s = 0, k = 0;
+        ShapeMeta m = {};
+        double4 w = make_double4(0, 0, 0, 0);
+        const bool have = e < wend;
+        if (have) {
+            id = ent_tmp[e];
             bin = ent_bin[e];
             s = (uint32_t)bin_start[bin];
             k = (uint32_t)bin_start[bin + 1] - s;
-            if (((A.info >> 8) & 0xff) != CB200_SPHERE) {
-                const uint32_t lo = max(s, e0), hi = min(s + k, wend);
-                for (uint32_t x = lo; x < hi; x++)
-                    mixed[x - e0] = 1;
+            T.sid[t] = id;
+            m = meta[id];
+            w = reinterpret_cast<const double4*>(s_wpos)[id];
+        }
+        // the tile owns the bins that start in its first PAIR_TILE entries, including their rows in the halo
+        const bool own = have && s >= e0 && s < e0 + PAIR_TILE;
+        const bool sphere = ((m.info >> 8) & 0xff) == CB200_SPHERE;
+        const uint32_t w0 = own ? s - e0 : 0u;
+        __syncthreads();
+        if (own && k <= 64) {
+            // rank of this shape id among the bin's ids == its position in the reference's sorted (bin, shape) list
+            uint32_t rank = 0, x = w0;
+            const uint32_t xe = w0 + k;
+            for (; (x & 3u) && x < xe; x++)
+                count_less(rank, T.sid[x], id);
+            for (; x + 4 <= xe; x += 4) {
+                const uint4 v = *reinterpret_cast<const uint4*>(&T.sid[x]);
+                count_less(rank, v.x, id);
+                count_less(rank, v.y, id);
+                count_less(rank, v.z, id);
+                count_less(rank, v.w, id);
             }
+            for (; x < xe; x++)
+                count_less(rank, T.sid[x], id);
+            const uint32_t p = w0 + rank;
+            ent_shape[s + rank] = id;
+            if (!sphere)
+                atomicOr(&T.nsm[w0], 1ull << rank);
+            double mn[3], mx[3];
+            shape_box_rel(id, m.info, s_wpos, s_box, g.origin, envelope, mn, mx);
+            int bx, by, bz;
+            bin_coords(bin, g, bx, by, bz);
+            const uint32_t fl = corner_flags(mn, g, bx, by, bz);
+            T.c[0][p] = w.x, T.c[1][p] = w.y, T.c[2][p] = w.z, T.c[3][p] = w.w;
+            T.body[p] = m.body, T.fam[p] = m.fam, T.info[p] = (m.info & ~56u) | fl;
+            const bool ok = sphere && m.body != UINT_MAX && (m.info & 2u);
+            const double R = w.w + envelope;
+            const double me = m_rel * (Bmax + R) + m_abs;
+            // upper bound of R + me that survives the replacement of its 4 low mantissa bits by the flags
+            const uint32_t rp = ((__float_as_uint(__double2float_ru(R + me)) & ~15u) + 16u) | (fl >> 3) | (ok ? 8u : 0u);
+            T.rm[p] = __double2float_rd(R - me);
+            T.f[p] = make_float4(__double2float_rn(w.x - (g.origin[0] + bx * cnt->bin_size[0])),
+                                 __double2float_rn(w.y - (g.origin[1] + by * cnt->bin_size[1])),
+                                 __double2float_rn(w.z - (g.origin[2] + bz * cnt->bin_size[2])), __uint_as_float(rp));
         }
         __syncthreads();
-        // the tile owns the bins that start in its first PAIR_TILE entries, including their rows in the halo
-        const bool own = e < wend && s >= e0 && s < e0 + PAIR_TILE;
-        const bool fast = !mixed[t] && algorithm != 0;
-
-        // ---- phase A: one thread per row of a sphere-only bin of 2..64 entries.  Row i meets its partners
-        // j = i + d (mod k), d = 1..(k-1)/2 (+ half a diagonal when k is even): every unordered pair exactly once,
-        // the same amount of work for every row of a bin, no idle lanes whatever k is.  The partner's AABB is
-        // recomputed from (centre, radius) -- the very operations that produced the stored one -- because FP64
-        // adds are cheaper here than 64-bit shared-memory loads.
-        if (own && fast && k >= 2 && k <= 64 && A.body != UINT_MAX && (A.info & 2u)) {
-            const uint32_t i = e - s;
-            const int w0 = (int)(s - e0);
-            const uint32_t h = (k - 1) >> 1;
-            const uint32_t nd = h + (((k & 1u) || i >= (k >> 1)) ? 0u : 1u);
-            unsigned long long mym = 0ull;
-            const uint32_t gA = A.fam & 0xffffu, mA = A.fam >> 16;
-            // Straight-line body: with ~1 pair in 8 passing, a warp never skips a section as a whole, so early
-            // exits only add branches; all loads are issued up front and two partners are in flight per trip.
+        // ---- from here on thread t is row t of the sorted window (same bin, hence same s and k, as its staged entry)
+        const unsigned long long nsm = (own && k <= 64) ? T.nsm[w0] : 0ull;
+        const uint32_t nn = (uint32_t)__popcll(nsm);
+        const bool bin_here = algorithm != 0 && nn <= NNS_MAX && k >= 2 && k <= 64;  // sphere-sphere pairs done here
+        const bool whole_slow = own && (k > 64 || (k >= 2 && !bin_here));
+        const uint32_t i = e - s;
+        uint32_t cand = 0u, nd = 0u;  // bit (nd - d) of cand: partner j = i + d (mod k) may pair with this row
+        if (own && bin_here) {
+            const float4 A = T.f[t];
+            const uint32_t ab = __float_as_uint(A.w);
+            if (ab & 8u) {
+                const uint32_t am = ab & 7u;
+                nd = ((k - 1) >> 1) + (((k & 1u) || i >= (k >> 1)) ? 0u : 1u);
+                const float4* Fb = &T.f[w0];
 #pragma unroll 2
-            for (uint32_t d = 1; d <= nd; d++) {
+                for (uint32_t d = 1; d <= nd; d++) {
+                    uint32_t j = i + d;
+                    if (j >= k)
+                        j -= k;
+                    const float4 B = Fb[j];
+                    const float rs = A.w + B.w;
+                    const bool maybe = fabsf(B.x - A.x) <= rs && fabsf(B.y - A.y) <= rs && fabsf(B.z - A.z) <= rs &&
+                                       ((__float_as_uint(B.w) | am) & 15u) == 15u;
+                    cand = (cand << 1) | (maybe ? 1u : 0u);
+                }
+            }
+        }
+        // ---- phase 2: the candidates of the warp's rows, compacted and spread over the lanes
+        while (__any_sync(0xffffffffu, cand != 0u)) {
+            const uint32_t c = min((uint32_t)__popc(cand), (uint32_t)(QCAP / 32));
+            const uint32_t incl = warp_incl_scan_bp(c, lane);
+            const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+            uint32_t q = incl - c;
+            for (uint32_t x = 0; x < c; x++) {
+                const uint32_t d = nd - ((uint32_t)__ffs((int)cand) - 1u);
+                cand &= cand - 1u;
                 uint32_t j = i + d;
                 if (j >= k)
                     j -= k;
-                const int wj = w0 + (int)j;
-                const double bx = W.c[0][wj], by = W.c[1][wj], bz = W.c[2][wj], br = W.c[3][wj];
-                const uint32_t bbody = W.body[wj], bfam = W.fam[wj], binfo = W.info[wj];
-                const double rr = br + envelope;
-                const double n0 = (bx - rr) - g.origin[0], n1 = (by - rr) - g.origin[1], n2 = (bz - rr) - g.origin[2];
-                const double x0 = (bx + rr) - g.origin[0], x1 = (by + rr) - g.origin[1], x2 = (bz + rr) - g.origin[2];
-                // f_Count_AABB_AABB_Intersection's conjunction, CMC/ChCollisionUtilsBroadphase.cpp:114-140
-                const bool ov = (A.mn[0] <= x0) & (n0 <= A.mx[0]) & (A.mn[1] <= x1) & (n1 <= A.mx[1]) &
-                                (A.mn[2] <= x2) & (n2 <= A.mx[2]);
-                const uint32_t both = A.info | binfo;
-                const bool ok = ((both & 56u) == 56u) & (bbody != UINT_MAX) & (bbody != A.body) &
-                                ((binfo & 2u) != 0) & ((both & 1u) != 0) & ((mA & (bfam & 0xffffu)) != 0) &
-                                (((bfam >> 16) & gA) != 0);
+                T.queue[wid][q++] = (w0 << 12) | (i << 6) | j;
+            }
+            __syncwarp();
+            for (uint32_t x = lane; x < total; x += 32) {
+                const uint32_t item = T.queue[wid][x];
+                const uint32_t bw = item >> 12, pi = (item >> 6) & 63u, pj = item & 63u;
+                const uint32_t lo = min(pi, pj), hi = max(pi, pj);
+                const uint32_t sa = bw + lo, sb = bw + hi;
+                // float classification: certainly overlapping boxes?  certainly touching / certainly apart spheres?
+                const float4 FA = T.f[sa], FB = T.f[sb];
+                const float dx = FB.x - FA.x, dy = FB.y - FA.y, dz = FB.z - FA.z;
+                const float rsM = T.rm[sa] + T.rm[sb], rsP = FA.w + FB.w;
+                const float d2 = dx * dx + dy * dy + dz * dz;
+                const bool sure_box = fmaxf(fmaxf(fabsf(dx), fabsf(dy)), fabsf(dz)) <= rsM;
+                const bool sure_hit = d2 <= rsM * rsM * 0.99999904f && d2 >= 1e-10f && rsM > 0.f;
+                const bool sure_miss = d2 >= rsP * rsP * 1.00000096f;
+                bool ov = true, touch = sure_hit;
+                if (!sure_box || (mode == MODE_CONTACTS && !sure_hit && !sure_miss)) {
+                    // the reference's tests in FP64, operation for operation.  Both boxes exactly as GenerateAABB +
+                    // OffsetAABB leave them: (c -/+ (r + envelope)) - global_origin
+                    const double ax = T.c[0][sa], ay = T.c[1][sa], az = T.c[2][sa], ar = T.c[3][sa];
+                    const double bx = T.c[0][sb], by = T.c[1][sb], bz = T.c[2][sb], br = T.c[3][sb];
+                    const double ra = ar + envelope, rb = br + envelope;
+                    const double an0 = (ax - ra) - g.origin[0], an1 = (ay - ra) - g.origin[1], an2 = (az - ra) - g.origin[2];
+                    const double ax0 = (ax + ra) - g.origin[0], ax1 = (ay + ra) - g.origin[1], ax2 = (az + ra) - g.origin[2];
+                    const double bn0 = (bx - rb) - g.origin[0], bn1 = (by - rb) - g.origin[1], bn2 = (bz - rb) - g.origin[2];
+                    const double bx0 = (bx + rb) - g.origin[0], bx1 = (by + rb) - g.origin[1], bx2 = (bz + rb) - g.origin[2];
+                    // f_Count_AABB_AABB_Intersection, CMC/ChCollisionUtilsBroadphase.cpp:114-140
+                    ov = (an0 <= bx0) & (bn0 <= ax0) & (an1 <= bx1) & (bn1 <= ax1) & (an2 <= bx2) & (bn2 <= ax2);
+                    // the deciding lines of sphere_sphere, ChNarrowphasePRIMS.cpp:52-60 (symmetric in the two shapes)
+                    const d3 delta = mk3(bx, by, bz) - mk3(ax, ay, az);
+                    const double dist2 = dot3(delta, delta);
+                    const double radSum_s = (ar + br) + sep;
+                    touch = !((dist2 >= radSum_s * radSum_s) | (dist2 < 1e-12));
+                }
+                const uint32_t ia = T.info[sa], ib = T.info[sb], fa = T.fam[sa], fb = T.fam[sb];
+                const uint32_t both = ia | ib;
+                // "can collide" and "not removed" were part of the pre-test (exact there: plain bits)
+                const bool ok = ((both & 56u) == 56u) & (T.body[sa] != T.body[sb]) & ((both & 1u) != 0u) &
+                                (((fa >> 16) & (fb & 0xffffu)) != 0u) & (((fb >> 16) & (fa & 0xffffu)) != 0u);
                 bool hit = ov & ok;
                 np += hit ? 1u : 0u;
-                if (mode == MODE_CONTACTS) {
-                    // the deciding lines of sphere_sphere, ChNarrowphasePRIMS.cpp:52-60 (symmetric in the two
-                    // shapes bit for bit)
-                    const d3 delta = mk3(bx, by, bz) - mk3(A.cx, A.cy, A.cz);
-                    const double dist2 = dot3(delta, delta);
-                    const double radSum_s = (A.r + br) + sep;
-                    hit = hit & !((dist2 >= radSum_s * radSum_s) | (dist2 < 1e-12));
-                }
-                if (hit) {
-                    if (j > i)
-                        mym |= 1ull << j;
-                    else
-                        atomicOr(&smask[wj], 1ull << i);
+                if (mode == MODE_CONTACTS)
+                    hit = hit & touch;
+                if (hit)
+                    atomicOr(&T.smask[sa], 1ull << hi);
+            }
+            __syncwarp();
+        }
+        // ---- pairs with one of the few non-spheres of a wall bin: queued one by one for k_pair_queue (a thread per
+        // pair).  A sphere row queues itself against every non-sphere, a non-sphere row against the non-spheres after it.
+        {
+            unsigned long long mine = 0ull;
+            if (own && bin_here && nn > 0) {
+                const bool row_ns = (nsm >> i) & 1ull;
+                mine = row_ns ? (nsm & ~((2ull << i) - 1ull)) : nsm;
+            }
+            const uint32_t c = (uint32_t)__popcll(mine);
+            if (__any_sync(0xffffffffu, c != 0u)) {
+                const uint32_t incl = warp_incl_scan_bp(c, lane);
+                uint32_t base = 0;
+                if (lane == 31)
+                    base = atomicAdd(&cnt->n_pairq, incl);
+                base = __shfl_sync(0xffffffffu, base, 31) + incl - c;
+                for (; mine; mine &= mine - 1ull) {
+                    const uint32_t a = (uint32_t)__ffsll((long long)mine) - 1u;
+                    if (base < cap_pairq)
+                        pair_q[base] = make_uint2(s + min(i, a), s + max(i, a));
+                    base++;
                 }
             }
-            if (mym)
-                atomicOr(&smask[t], mym);
         }
-
-        // ---- the rest (a non-sphere in the bin, MPR for everything, or more than 64 entries) is queued for
-        // k_pair_masks_slow, a warp per bin: kept out of this kernel so that a tile along a wall does not hold
-        // its CTA at the barrier below while the other warps idle
-        if (own && s == e && (k > 64 || (k >= 2 && !fast))) {
-            slow_bins[atomicAdd(&cnt->n_slow, 1u)] = s;
+        // ---- bins left as a whole to k_pair_masks_slow (a warp per bin)
+        if (own && s == e && whole_slow) {
             if (k > 64)
-                atomicAdd(&cnt->n_long, 1u);
+                long_bins[atomicAdd(&cnt->n_long, 1u)] = s;  // k_long_sort / k_long_count / k_long_store
+            else
+                slow_bins[atomicAdd(&cnt->n_slow, 1u)] = s;
         }
         __syncthreads();
         // masks of the rows this tile owns and has decided
-        if (own && (k < 2 || (k <= 64 && fast))) {
-            const unsigned long long m = smask[t];
-            ent_mask[e] = m;
-            ent_cnt[e] = (uint32_t)__popcll(m);
+        if (own && !whole_slow) {
+            const unsigned long long mk = T.smask[t];
+            ent_mask[e] = mk;
+            ent_cnt[e] = (uint32_t)__popcll(mk);
             if (CPLX)
-                ent_cmask[e] = scmask[t];
+                ent_cmask[e] = 0ull;
         }
     }
-    // totals that are not tied to an entry: N_p (contacts mode) and the pairs this backend cannot test
+    // N_p (contacts mode; in pairs mode the store pass sets it from the scanned counts)
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1)
+        np += __shfl_xor_sync(0xffffffffu, np, d);
+    if (lane == 0 && mode == MODE_CONTACTS && np)
+        atomicAdd(&cnt->n_pairs, np);
+}
+
+// k_pair_queue: the pairs of wall bins that involve a non-sphere, a thread per pair; the result joins the masks the tile
+// kernel wrote for those rows (global atomics: two pairs of one row may be decided by different threads).
+template <bool CPLX>
+__global__ void __launch_bounds__(128) k_pair_queue(const ShapeMeta* __restrict__ meta,
+                                                    const double* __restrict__ s_wpos,
+                                                    const ShapeBox* __restrict__ s_box,
+                                                    const double* __restrict__ s_wrot,
+                                                    const double* __restrict__ s_dims,
+                                                    const uint32_t* __restrict__ ent_shape,
+                                                    const uint32_t* __restrict__ ent_bin,
+                                                    const uint64_t* __restrict__ bin_start, double envelope,
+                                                    int algorithm, int mode, const uint2* __restrict__ pair_q,
+                                                    uint32_t cap_pairq, unsigned long long* __restrict__ ent_mask,
+                                                    unsigned long long* __restrict__ ent_cmask,
+                                                    uint32_t* __restrict__ ent_cnt, DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    const uint32_t nq = cnt->n_pairq;
+    if (nq > cap_pairq) {
+        if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) {
+            cnt->need_pairq = nq;
+            __threadfence();
+            atomicOr(&cnt->overflow, (uint32_t)OVF_PAIRQ);
+        }
+        return;
+    }
+    const GridParams g = load_grid(cnt);
+    const double sep = 2 * envelope;
+    uint32_t np = 0, ncx = 0;
+    for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < nq; q += gridDim.x * blockDim.x) {
+        const uint2 it = pair_q[q];
+        const uint32_t bin = ent_bin[it.x];
+        const uint32_t s = (uint32_t)bin_start[bin];
+        Rec A, B;
+        load_rec(A, ent_shape[it.x], meta, s_wpos, s_box, g.origin, envelope);
+        load_rec(B, ent_shape[it.y], meta, s_wpos, s_box, g.origin, envelope);
+        const int dec = pair_decide<false>(A, B, g, bin, mode, sep, algorithm, s_wrot, s_dims, np);
+        if (dec == 1) {
+            atomicOr(&ent_mask[it.x], 1ull << (it.y - s));
+            atomicAdd(&ent_cnt[it.x], 1u);
+        } else if (dec == 2) {
+            if (CPLX)
+                atomicOr(&ent_cmask[it.x], 1ull << (it.y - s));
+            else
+                ncx++;
+        }
+    }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
         np += __shfl_xor_sync(0xffffffffu, np, d);
         ncx += __shfl_xor_sync(0xffffffffu, ncx, d);
     }
-    if (lane == 0) {
+    if ((threadIdx.x & 31) == 0) {
         if (mode == MODE_CONTACTS && np)
             atomicAdd(&cnt->n_pairs, np);
         if (ncx)
@@ -458,18 +649,18 @@ __global__ void __launch_bounds__(PAIR_THREADS, 2) k_pair_masks(const ShapeMeta*
 }
 
 // --------------------------------------------------------------------------------------------------------------
-// k_pair_masks_slow: a warp per queued bin (non-sphere in the bin, MPR for everything, or more than 64 entries);
-// the warp stages up to 64 of the bin's entries in its own shared-memory window.
+// k_pair_masks_slow: a warp per queued bin; the warp stages up to 64 of the bin's entries in its own shared-memory
+// window: all pairs of a bin of <= 64 entries that the tile kernel left as a whole (many non-spheres, or MPR for
+// everything).  Bins of more than 64 entries: k_long_sort / k_long_count / k_long_store.
 // --------------------------------------------------------------------------------------------------------------
 constexpr int SLOW_WIN = 64, SLOW_WARPS = 4;
 
 template <bool CPLX>
 __global__ void __launch_bounds__(32 * SLOW_WARPS) k_pair_masks_slow(
-    const ShapeMeta* __restrict__ meta, const ShapeMeta* __restrict__ ent_m, const double* __restrict__ ent_c,
-    const double* __restrict__ s_wpos, const ShapeBox* __restrict__ s_box, const double* __restrict__ s_wrot,
-    const double* __restrict__ s_dims, const uint32_t* __restrict__ ent_shape, const uint32_t* __restrict__ ent_bin,
-    const uint64_t* __restrict__ bin_start, double envelope, int algorithm, int mode,
-    uint64_t* __restrict__ ent_mask, uint64_t* __restrict__ ent_cmask, uint32_t* __restrict__ ent_cnt,
+    const ShapeMeta* __restrict__ meta, const double* __restrict__ s_wpos, const ShapeBox* __restrict__ s_box,
+    const double* __restrict__ s_wrot, const double* __restrict__ s_dims, const uint32_t* __restrict__ ent_tmp,
+    uint32_t* ent_shape, const uint32_t* __restrict__ ent_bin, const uint64_t* __restrict__ bin_start,
+    double envelope, int algorithm, int mode, uint64_t* ent_mask, uint64_t* ent_cmask, uint32_t* ent_cnt,
     const uint32_t* __restrict__ slow_bins, CplxArgs X, DevCounters* __restrict__ cnt) {
     __shared__ WindowT<SLOW_WIN> W[SLOW_WARPS];
     __shared__ unsigned long long smask[SLOW_WARPS][SLOW_WIN];
@@ -480,112 +671,64 @@ __global__ void __launch_bounds__(32 * SLOW_WARPS) k_pair_masks_slow(
     const uint32_t nslow = cnt->n_slow;
     const double sep = 2 * envelope;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const uint32_t w0 = 0;
     uint32_t np = 0, ncx = 0;
     for (uint32_t q = blockIdx.x * SLOW_WARPS + wid; q < nslow; q += gridDim.x * SLOW_WARPS) {
         const uint32_t bs = slow_bins[q];
         const uint32_t b = ent_bin[bs];
         const uint32_t bk = (uint32_t)bin_start[b + 1] - bs;
+        int bx, by, bz;
+        bin_coords(b, g, bx, by, bz);
         __syncwarp();
         for (uint32_t x = lane; x < min(bk, (uint32_t)SLOW_WIN); x += 32) {
             Rec R;
-            load_rec_sorted(R, bs + x, ent_m, ent_c, s_wpos, s_box, g.origin, envelope);
+            load_rec_bin(R, ent_shape[bs + x], meta, s_wpos, s_box, g, bx, by, bz, envelope);
             win_put(W[wid], (int)x, R);
             smask[wid][x] = 0ull;
             if (CPLX)
                 scmask[wid][x] = 0ull;
         }
         __syncwarp();
-            if (bk <= 64) {
-                // pairs spread evenly over the lanes in the cyclic order (i, i+d mod k); both records from the
-                // window, ordered (lower entry, higher entry) for the shape functions
-                const uint32_t h = (bk - 1) >> 1;
-                const uint32_t full = bk * h;
-                const uint32_t total = full + ((bk & 1u) ? 0u : (bk >> 1));
-                const uint32_t M = ((1u << 20) + bk - 1) / bk;  // p / k == (p * M) >> 20 for p < 2048, k <= 64
-                for (uint32_t p0 = 0; p0 < total; p0 += 32) {
-                    const uint32_t p = p0 + lane;
-                    if (p < total) {
-                        uint32_t i, j;
-                        if (p < full) {
-                            const uint32_t d = (p * M) >> 20;
-                            i = p - d * bk;
-                            j = i + d + 1;
-                            if (j >= bk)
-                                j -= bk;
-                        } else {
-                            i = p - full;
-                            j = i + (bk >> 1);
-                        }
-                        const uint32_t a = min(i, j), c = max(i, j);
-                        Rec RA, RB;
-                        win_get(W[wid], (int)(w0 + a), RA);
-                        win_get(W[wid], (int)(w0 + c), RB);
-                        const int dec = pair_decide<true>(RA, RB, g, b, mode, sep, algorithm, s_wrot, s_dims, np);
-                        if (dec == 1)
-                            atomicOr(&smask[wid][w0 + a], 1ull << c);
-                        else if (dec == 2) {
-                            if (CPLX)
-                                atomicOr(&scmask[CPLX ? wid : 0][w0 + a], 1ull << c);
-                            else
-                                ncx++;
-                        }
+        if (bk <= 64) {
+            // pairs spread evenly over the lanes in the cyclic order (i, i+d mod k); both records from the
+            // window, ordered (lower entry, higher entry) for the shape functions
+            const uint32_t h = (bk - 1) >> 1;
+            const uint32_t full = bk * h;
+            const uint32_t total = full + ((bk & 1u) ? 0u : (bk >> 1));
+            const uint32_t M = ((1u << 20) + bk - 1) / bk;  // p / k == (p * M) >> 20 for p < 2048, k <= 64
+            for (uint32_t p0 = 0; p0 < total; p0 += 32) {
+                const uint32_t p = p0 + lane;
+                if (p < total) {
+                    uint32_t i, j;
+                    if (p < full) {
+                        const uint32_t d = (p * M) >> 20;
+                        i = p - d * bk;
+                        j = i + d + 1;
+                        if (j >= bk)
+                            j -= bk;
+                    } else {
+                        i = p - full;
+                        j = i + (bk >> 1);
                     }
-                }
-            } else {
-                // long bin: rows one after the other, lanes across the row; count only (the store pass re-tests)
-                for (uint32_t i = 0; i + 1 < bk; i++) {
-                    Rec RA;
-                    if (i < SLOW_WIN)
-                        win_get(W[wid], (int)(w0 + i), RA);
-                    else
-                        load_rec(RA, ent_shape[bs + i], meta, s_wpos, s_box, g.origin, envelope);
-                    uint32_t hits = 0;
-                    for (uint32_t j = i + 1 + lane; j < bk; j += 32) {
-                        Rec RB;
-                        if (j < SLOW_WIN)
-                            win_get(W[wid], (int)(w0 + j), RB);
-                        else
-                            load_rec(RB, ent_shape[bs + j], meta, s_wpos, s_box, g.origin, envelope);
-                        const int dec = pair_decide<false>(RA, RB, g, b, mode, sep, algorithm, s_wrot, s_dims, np);
-                        hits += dec == 1 ? 1u : 0u;
-                        if (dec == 2) {
-                            // long bins keep no masks or records: a complex pair is evaluated here for its contact
-                            // count and once more by the store pass, which writes the contacts
-                            if (CPLX && mode == MODE_CONTACTS) {
-                                Contact tmp[MAX_PAIR_CONTACTS];
-                                hits += (uint32_t)narrow_complex_ids(RA.id, RB.id, meta, s_wpos, s_wrot, s_dims, X,
-                                                                     algorithm, envelope, tmp);
-                            } else if (CPLX) {
-                                hits++;  // pair-list mode: a candidate pair like any other
-                            } else {
-                                ncx++;
-                            }
-                        }
-                    }
-#pragma unroll
-                    for (int d = 16; d > 0; d >>= 1)
-                        hits += __shfl_xor_sync(0xffffffffu, hits, d);
-                    if (lane == 0) {
-                        ent_mask[bs + i] = 0ull;
-                        ent_cnt[bs + i] = hits;
+                    const uint32_t a = min(i, j), c = max(i, j);
+                    Rec RA, RB;
+                    win_get(W[wid], (int)a, RA);
+                    win_get(W[wid], (int)c, RB);
+                    const int dec = pair_decide<true>(RA, RB, g, b, mode, sep, algorithm, s_wrot, s_dims, np);
+                    if (dec == 1)
+                        atomicOr(&smask[wid][a], 1ull << c);
+                    else if (dec == 2) {
                         if (CPLX)
-                            ent_cmask[bs + i] = 0ull;
+                            atomicOr(&scmask[CPLX ? wid : 0][a], 1ull << c);
+                        else
+                            ncx++;
                     }
-                }
-                if (lane == 0) {
-                    ent_mask[bs + bk - 1] = 0ull;
-                    ent_cnt[bs + bk - 1] = 0;
-                    if (CPLX)
-                        ent_cmask[bs + bk - 1] = 0ull;
                 }
             }
-        if (bk <= 64) {
             __syncwarp();
             for (uint32_t x = lane; x < bk; x += 32) {
-                const unsigned long long m = smask[wid][x];
-                ent_mask[bs + x] = m;
-                ent_cnt[bs + x] = (uint32_t)__popcll(m);
+                const unsigned long long mk = smask[wid][x];
+                ent_mask[bs + x] = mk;
+                ent_cnt[bs + x] = (uint32_t)__popcll(mk);
                 if (CPLX)
                     ent_cmask[bs + x] = scmask[CPLX ? wid : 0][x];
             }
@@ -728,13 +871,14 @@ __global__ void __launch_bounds__(128) k_cplx_narrow(const ShapeMeta* __restrict
         return;
     const uint32_t nrec = cnt->n_complex, nslots = cnt->n_cslots;
     if (nrec > cap_rec || nslots > cap_slots) {
-        if (blockIdx.x == 0 && threadIdx.x == 0) {
+        // every CTA sees the same counters, so all of them leave; the last CTA of the grid records what was needed
+        // and only then raises the flag (the CTAs before it may still be about to read `overflow`)
+        if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) {
             cnt->need_complex = nrec;
             cnt->need_cslots = nslots;
-        }
-        // every CTA sees the same counters, so all of them leave; the flag is raised by the last line of the grid
-        if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0)
+            __threadfence();
             atomicOr(&cnt->overflow, (uint32_t)OVF_COMPLEX);
+        }
         return;
     }
     uint32_t bad = 0;
@@ -773,58 +917,6 @@ __global__ void __launch_bounds__(128) k_cplx_narrow(const ShapeMeta* __restrict
     }
     if (bad)
         atomicAdd(&cnt->unsupported, bad);
-}
-
-// Row of a bin with more than 64 entries (no masks): re-walk and re-test (k_pair_store_long).
-template <bool CPLX>
-__device__ __forceinline__ void store_long_row(uint32_t e, uint32_t o, uint32_t s, uint32_t k, uint32_t bin, int64_t hiA,
-                                            const ShapeMeta* __restrict__ meta, const double* __restrict__ s_wpos,
-                                            const ShapeBox* __restrict__ s_box, const double* __restrict__ s_wrot,
-                                            const double* __restrict__ s_dims,
-                                            const uint32_t* __restrict__ ent_shape, double envelope, int algorithm,
-                                            int mode, int64_t* __restrict__ out, uint32_t* __restrict__ c_src,
-                                            const CplxArgs& X, DevCounters* __restrict__ cnt) {
-    const GridParams g = load_grid(cnt);
-    Rec A;
-    load_rec(A, ent_shape[e], meta, s_wpos, s_box, g.origin, envelope);
-    uint32_t np = 0;
-    for (uint32_t j = e + 1; j < s + k; j++) {
-        Rec B;
-        load_rec(B, ent_shape[j], meta, s_wpos, s_box, g.origin, envelope);
-        const int dec = pair_decide<false>(A, B, g, bin, mode, 2 * envelope, algorithm, s_wrot, s_dims, np);
-        if (dec == 1) {
-            if (CPLX && mode == MODE_CONTACTS)
-                c_src[o] = 0;
-            out[o++] = hiA | (int64_t)B.id;
-        } else if (dec == 2 && CPLX) {
-            if (mode != MODE_CONTACTS) {
-                out[o++] = hiA | (int64_t)B.id;
-                continue;
-            }
-            // complex pair in a long bin: evaluated in place, its contacts go to freshly reserved slots
-            Contact tmp[MAX_PAIR_CONTACTS];
-            const int n = narrow_complex_ids(A.id, B.id, meta, s_wpos, s_wrot, s_dims, X, algorithm, envelope,
-                                             tmp);
-            if (n == 0)
-                continue;
-            const uint32_t slot = atomicAdd(&cnt->n_cslots, (uint32_t)n);
-            if (slot + n > X.cap_slots) {
-                atomicMax(&cnt->need_cslots, slot + n);
-                atomicMax(&cnt->need_complex, cnt->n_complex);
-                atomicOr(&cnt->overflow, (uint32_t)OVF_COMPLEX);
-                continue;
-            }
-            for (int t = 0; t < n; t++) {
-                double* q = X.cplx_out + 11 * (size_t)(slot + t);
-                q[0] = tmp[t].n.x, q[1] = tmp[t].n.y, q[2] = tmp[t].n.z;
-                q[3] = tmp[t].p1.x, q[4] = tmp[t].p1.y, q[5] = tmp[t].p1.z;
-                q[6] = tmp[t].p2.x, q[7] = tmp[t].p2.y, q[8] = tmp[t].p2.z;
-                q[9] = tmp[t].depth, q[10] = tmp[t].erad;
-                out[o] = hiA | (int64_t)B.id;
-                c_src[o++] = slot + t + 1;
-            }
-        }
-    }
 }
 
 // k_pair_store: one thread per entry; turns masks (or, for long bins, a re-walk of the row) into 64-bit shape-pair
@@ -909,48 +1001,163 @@ __global__ void __launch_bounds__(256) k_pair_store(const ShapeMeta* __restrict_
     }
 }
 
-// The rows k_pair_store leaves out: a warp per queued bin (k_pair_masks queued every bin of more than 64 entries),
-// lanes across its rows.  A kernel of its own because its registers (pair_decide, narrow_complex) would set the
-// occupancy of the store kernel, which is a latency-bound gather.
-template <bool CPLX>
-__global__ void __launch_bounds__(128) k_pair_store_long(const ShapeMeta* __restrict__ meta,
-                                                         const double* __restrict__ s_wpos,
-                                                         const ShapeBox* __restrict__ s_box,
-                                                         const double* __restrict__ s_wrot,
-                                                         const double* __restrict__ s_dims,
-                                                         const uint32_t* __restrict__ ent_shape,
-                                                         const uint32_t* __restrict__ ent_bin,
-                                                         const uint64_t* __restrict__ bin_start, double envelope,
-                                                         int algorithm, int mode,
-                                                         const uint32_t* __restrict__ ent_off,
-                                                         int64_t* __restrict__ out, uint32_t cap,
-                                                         uint32_t* __restrict__ c_src,
-                                                         const uint32_t* __restrict__ slow_bins, CplxArgs X,
-                                                         DevCounters* __restrict__ cnt) {
+// --------------------------------------------------------------------------------------------------------------
+// Bins with more than 64 entries (coarse grids; a dense 4 x 4 x 4 bin plus its walls): no masks.  Three small kernels,
+// all of which leave at once when there is no such bin:
+//   k_long_sort   rank sort of the bin's entries by shape id (a CTA per bin)
+//   k_long_count  outputs per row: a warp per row, lanes across the partners (rows of one bin spread over many CTAs)
+//   k_long_store  the same walk again after the scan; a lane's slot = row offset + hits of the lanes before it, i.e.
+//                 the reference's (shape A, shape B) order
+// --------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_long_sort(const uint32_t* __restrict__ ent_tmp, uint32_t* __restrict__ ent_shape,
+                                                   const uint32_t* __restrict__ ent_bin,
+                                                   const uint64_t* __restrict__ bin_start,
+                                                   const uint32_t* __restrict__ long_bins,
+                                                   const DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
-    if (ent_off[cnt->n_intersections] > cap)
-        return;  // k_pair_store raises the flag
-    if (cnt->n_long == 0)
-        return;
-    const uint32_t nslow = cnt->n_slow;
-    const int lane = threadIdx.x & 31;
-    const uint32_t nw = gridDim.x * (blockDim.x >> 5);
-    for (uint32_t q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); q < nslow; q += nw) {
-        const uint32_t s = slow_bins[q];
-        const uint32_t bin = ent_bin[s];
-        const uint32_t k = (uint32_t)bin_start[bin + 1] - s;
-        if (k <= 64)
-            continue;
-        for (uint32_t e = s + lane; e < s + k; e += 32) {
-            const uint32_t o = ent_off[e];
-            if (ent_off[e + 1] == o)
-                continue;
-            store_long_row<CPLX>(e, o, s, k, bin, (int64_t)ent_shape[e] << 32, meta, s_wpos, s_box, s_wrot, s_dims,
-                                 ent_shape, envelope, algorithm, mode, out, c_src, X, cnt);
+    const uint32_t nl = cnt->n_long;
+    for (uint32_t q = blockIdx.x; q < nl; q += gridDim.x) {
+        const uint32_t s = long_bins[q];
+        const uint32_t k = (uint32_t)bin_start[ent_bin[s] + 1] - s;
+        for (uint32_t x = threadIdx.x; x < k; x += blockDim.x) {
+            const uint32_t id = ent_tmp[s + x];
+            uint32_t rank = 0;
+            for (uint32_t y = 0; y < k; y++)
+                rank += ent_tmp[s + y] < id ? 1u : 0u;
+            ent_shape[s + rank] = id;
         }
     }
 }
+
+// decision for the lane's partner j of row A, and the number of outputs it gives (contacts, or 1 in pair-list mode)
+template <bool CPLX>
+__device__ __forceinline__ int long_pair(const Rec& A, uint32_t idB, const GridParams& g, uint32_t bin, int mode,
+                                         double envelope, int algorithm, const ShapeMeta* __restrict__ meta,
+                                         const double* __restrict__ s_wpos, const ShapeBox* __restrict__ s_box,
+                                         const double* __restrict__ s_wrot, const double* __restrict__ s_dims,
+                                         const CplxArgs& X, Contact* tmp, uint32_t& n, uint32_t& np, uint32_t& ncx) {
+    Rec B;
+    load_rec(B, idB, meta, s_wpos, s_box, g.origin, envelope);
+    const int dec = pair_decide<false>(A, B, g, bin, mode, 2 * envelope, algorithm, s_wrot, s_dims, np);
+    n = dec == 1 ? 1u : 0u;
+    if (dec == 2) {
+        if (!CPLX)
+            ncx++;
+        else if (mode != MODE_CONTACTS)
+            n = 1;  // pair-list mode: a candidate pair like any other
+        else  // long bins keep no records: a complex pair is evaluated in place, by the count and by the store pass
+            n = (uint32_t)narrow_complex_ids(A.id, idB, meta, s_wpos, s_wrot, s_dims, X, algorithm, envelope, tmp);
+    }
+    return dec;
+}
+
+template <bool CPLX, bool STORE>
+__global__ void __launch_bounds__(128) k_long_rows(const ShapeMeta* __restrict__ meta, const double* __restrict__ s_wpos,
+                                                   const ShapeBox* __restrict__ s_box,
+                                                   const double* __restrict__ s_wrot,
+                                                   const double* __restrict__ s_dims,
+                                                   const uint32_t* __restrict__ ent_shape,
+                                                   const uint32_t* __restrict__ ent_bin,
+                                                   const uint64_t* __restrict__ bin_start, double envelope,
+                                                   int algorithm, int mode, uint64_t* __restrict__ ent_mask,
+                                                   uint64_t* __restrict__ ent_cmask, uint32_t* __restrict__ ent_cnt,
+                                                   const uint32_t* __restrict__ ent_off, int64_t* __restrict__ out,
+                                                   uint32_t cap, uint32_t* __restrict__ c_src,
+                                                   const uint32_t* __restrict__ long_bins, CplxArgs X,
+                                                   DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    const uint32_t nl = cnt->n_long;
+    if (nl == 0)
+        return;
+    if (STORE && ent_off[cnt->n_intersections] > cap)
+        return;  // k_pair_store raises the flag
+    const GridParams g = load_grid(cnt);
+    const int lane = threadIdx.x & 31;
+    const uint32_t wpb = blockDim.x >> 5;
+    uint32_t np = 0, ncx = 0;
+    for (uint32_t q = blockIdx.y; q < nl; q += gridDim.y) {
+        const uint32_t s = long_bins[q];
+        const uint32_t bin = ent_bin[s];
+        const uint32_t k = (uint32_t)bin_start[bin + 1] - s;
+        for (uint32_t i = blockIdx.x * wpb + (threadIdx.x >> 5); i < k; i += gridDim.x * wpb) {
+            const uint32_t e = s + i;
+            uint32_t o = 0;
+            if (STORE) {
+                o = ent_off[e];
+                if (ent_off[e + 1] == o)
+                    continue;
+            }
+            Rec A;
+            load_rec(A, ent_shape[e], meta, s_wpos, s_box, g.origin, envelope);
+            const int64_t hiA = (int64_t)A.id << 32;
+            uint32_t hits = 0;
+            for (uint32_t j0 = i + 1; j0 < k; j0 += 32) {
+                const uint32_t j = j0 + lane;
+                Contact tmp[CPLX ? MAX_PAIR_CONTACTS : 1];
+                uint32_t n = 0, idB = 0;
+                int dec = 0;
+                if (j < k) {
+                    idB = ent_shape[s + j];
+                    dec = long_pair<CPLX>(A, idB, g, bin, mode, envelope, algorithm, meta, s_wpos, s_box, s_wrot, s_dims, X,
+                                          tmp, n, np, ncx);
+                }
+                const uint32_t incl = warp_incl_scan_bp(n, lane);
+                hits += __shfl_sync(0xffffffffu, incl, 31);
+                if (STORE && n) {
+                    uint32_t p = o + incl - n;
+                    const int64_t key = hiA | (int64_t)idB;
+                    if (dec == 1 || mode != MODE_CONTACTS) {
+                        if (CPLX && mode == MODE_CONTACTS)
+                            c_src[p] = 0;
+                        out[p] = key;
+                    } else if (CPLX) {
+                        // contacts of a complex pair go to freshly reserved slots
+                        const uint32_t slot = atomicAdd(&cnt->n_cslots, n);
+                        if (slot + n > X.cap_slots) {
+                            atomicMax(&cnt->need_cslots, slot + n);
+                            atomicMax(&cnt->need_complex, cnt->n_complex);
+                            atomicOr(&cnt->overflow, (uint32_t)OVF_COMPLEX);
+                        } else {
+                            for (uint32_t t = 0; t < n; t++) {
+                                double* qd = X.cplx_out + 11 * (size_t)(slot + t);
+                                qd[0] = tmp[t].n.x, qd[1] = tmp[t].n.y, qd[2] = tmp[t].n.z;
+                                qd[3] = tmp[t].p1.x, qd[4] = tmp[t].p1.y, qd[5] = tmp[t].p1.z;
+                                qd[6] = tmp[t].p2.x, qd[7] = tmp[t].p2.y, qd[8] = tmp[t].p2.z;
+                                qd[9] = tmp[t].depth, qd[10] = tmp[t].erad;
+                                out[p] = key;
+                                c_src[p++] = slot + t + 1;
+                            }
+                        }
+                    }
+                }
+                if (STORE)
+                    o += __shfl_sync(0xffffffffu, incl, 31);
+            }
+            if (!STORE && lane == 0) {
+                ent_mask[e] = 0ull;
+                ent_cnt[e] = hits;
+                if (CPLX)
+                    ent_cmask[e] = 0ull;
+            }
+        }
+    }
+    if (!STORE) {
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            np += __shfl_xor_sync(0xffffffffu, np, d);
+            ncx += __shfl_xor_sync(0xffffffffu, ncx, d);
+        }
+        if (lane == 0) {
+            if (mode == MODE_CONTACTS && np)
+                atomicAdd(&cnt->n_pairs, np);
+            if (ncx)
+                atomicAdd(&cnt->unsupported, ncx);
+        }
+    }
+}
+
 // --------------------------------------------------------------------------------------------------------------
 // k_contact_gen: one thread per contact key -> the contact record (DispatchPRIMS on the compacted list).
 // --------------------------------------------------------------------------------------------------------------
@@ -1002,78 +1209,77 @@ __global__ void __launch_bounds__(256) k_contact_gen(const ShapeMeta* __restrict
 // --------------------------------------------------------------------------------------------------------------
 // host side: enqueue only, no synchronisation
 // --------------------------------------------------------------------------------------------------------------
-static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
+template <bool CPLX>
+static int enqueue_pair_pass_t(System* S, int mode, int64_t* out, uint32_t cap) {
     const double env = S->set.collision_envelope;
     const int algorithm = S->set.narrowphase_algorithm;
-    const bool cplx = mode == MODE_CONTACTS && use_complex(S);
     if (mode == MODE_CONTACTS)
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_pairs, 0, 4, S->stream));
-    const int gm = grid_for(S, S->cap_entries, PAIR_TILE, 4);
-    CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_slow, 0, 8, S->stream));  // n_slow, n_long
+    const int gm = grid_for(S, S->cap_entries, PAIR_TILE, 4);  // 4 resident CTAs per SM, tiles grid-stride
+    CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_slow, 0, 12, S->stream));  // n_slow, n_long, n_pairq
     const int gs = S->num_sms * 8;
     CplxArgs X = {};
     X.s_lrot = S->s_lrot.p, X.rot = S->rot.p, X.s_verts = S->s_verts.p, X.cplx_out = S->cplx_out.p;
     X.cap_slots = S->cap_cslots;
-    CB_TRY(timer_start(S, "k_pair_masks"));
-    if (cplx) {
+    uint64_t* cmask = CPLX ? S->ent_cmask.p : nullptr;
+    if (CPLX) {
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_complex, 0, 4, S->stream));
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_cslots, 0, 4, S->stream));
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_cls[0], 0, 16, S->stream));
-        k_pair_masks<true><<<gm, PAIR_THREADS, 0, S->stream>>>(
-            S->s_meta.p, S->ent_m.p, S->ent_c.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p,
-            S->ent_bin.p, S->bin_start.p, env, algorithm, mode, S->ent_mask.p, S->ent_cmask.p, S->ent_off.p,
-            S->slow_bins.p, S->d_cnt);
-        k_pair_masks_slow<true><<<gs, 32 * SLOW_WARPS, 0, S->stream>>>(
-            S->s_meta.p, S->ent_m.p, S->ent_c.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p,
-            S->ent_bin.p, S->bin_start.p, env, algorithm, mode, S->ent_mask.p, S->ent_cmask.p, S->ent_off.p,
-            S->slow_bins.p, X, S->d_cnt);
-        S->launches++;
-        CB_TRY(timer_stop(S, "k_pair_masks"));
+    }
+    CB_TRY(timer_start(S, "k_pair_masks"));
+    k_pair_masks<CPLX><<<gm, PAIR_THREADS, 0, S->stream>>>(
+        S->s_meta.p, S->s_wpos.p, S->s_box.p, S->ent_tmp.p, S->ent_bin.p, S->bin_start.p, env, algorithm, mode,
+        S->ent_shape.p, S->ent_mask.p, cmask, S->ent_off.p, S->slow_bins.p, S->long_bins.p,
+        reinterpret_cast<uint2*>(S->pair_q.p), S->cap_pairq, S->d_cnt);
+    CB_TRY(timer_stop(S, "k_pair_masks"));
+    CB_TRY(timer_start(S, "k_pair_masks_slow"));
+    k_pair_queue<CPLX><<<grid_for(S, S->cap_pairq, 128, 8), 128, 0, S->stream>>>(
+        S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
+        env, algorithm, mode, reinterpret_cast<const uint2*>(S->pair_q.p), S->cap_pairq,
+        reinterpret_cast<unsigned long long*>(S->ent_mask.p), reinterpret_cast<unsigned long long*>(cmask),
+        S->ent_off.p, S->d_cnt);
+    k_pair_masks_slow<CPLX><<<gs, 32 * SLOW_WARPS, 0, S->stream>>>(
+        S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_tmp.p, S->ent_shape.p, S->ent_bin.p,
+        S->bin_start.p, env, algorithm, mode, S->ent_mask.p, cmask, S->ent_off.p, S->slow_bins.p, X, S->d_cnt);
+    k_long_sort<<<64, 256, 0, S->stream>>>(S->ent_tmp.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p, S->long_bins.p,
+                                           S->d_cnt);
+    k_long_rows<CPLX, false><<<dim3(8, 64), 128, 0, S->stream>>>(
+        S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
+        env, algorithm, mode, S->ent_mask.p, cmask, S->ent_off.p, nullptr, nullptr, 0, nullptr, S->long_bins.p, X,
+        S->d_cnt);
+    CB_TRY(timer_stop(S, "k_pair_masks_slow"));
+    S->launches += 5;
+    if (CPLX) {
         k_cplx_collect<<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
             S->s_meta.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p, S->ent_cmask.p, algorithm, S->ent_cbase.p,
             S->cplx_rec.p, S->cplx_cls.p, S->cap_complex, S->d_cnt);
         k_cplx_narrow<<<grid_for(S, S->cap_complex, 128), 128, 0, S->stream>>>(
             S->s_meta.p, S->s_wpos.p, S->s_wrot.p, S->s_dims.p, S->s_lrot.p, S->rot.p, S->s_verts.p, env, algorithm,
-            S->cplx_rec.p, S->cplx_cls.p,
-            S->cap_complex, S->cap_cslots, S->cplx_n.p, S->cplx_out.p, S->ent_off.p, S->d_cnt);
-        S->launches += 3;
-    } else {
-        k_pair_masks<false><<<gm, PAIR_THREADS, 0, S->stream>>>(
-            S->s_meta.p, S->ent_m.p, S->ent_c.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p,
-            S->ent_bin.p, S->bin_start.p, env, algorithm, mode, S->ent_mask.p, nullptr, S->ent_off.p,
-            S->slow_bins.p, S->d_cnt);
-        k_pair_masks_slow<false><<<gs, 32 * SLOW_WARPS, 0, S->stream>>>(
-            S->s_meta.p, S->ent_m.p, S->ent_c.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p,
-            S->ent_bin.p, S->bin_start.p, env, algorithm, mode, S->ent_mask.p, nullptr, S->ent_off.p,
-            S->slow_bins.p, X, S->d_cnt);
-        S->launches++;
-        CB_TRY(timer_stop(S, "k_pair_masks"));
-        S->launches++;
+            S->cplx_rec.p, S->cplx_cls.p, S->cap_complex, S->cap_cslots, S->cplx_n.p, S->cplx_out.p, S->ent_off.p,
+            S->d_cnt);
+        S->launches += 2;
     }
     CB_TRY(scan_u32(S, S->ent_off.p, S->ent_off.p, &S->d_cnt->n_intersections, S->cap_entries));
     CB_TRY(timer_start(S, "k_pair_store"));
-    if (cplx)
-        k_pair_store<true><<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
-            S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p,
-            S->bin_start.p, env, algorithm, mode, S->ent_mask.p, S->ent_off.p, out, cap, S->ent_cmask.p,
-            S->ent_cbase.p, S->cplx_rec.p, S->cplx_n.p, S->c_src.p, X, S->d_cnt);
-    else
-        k_pair_store<false><<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
-            S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p,
-            S->bin_start.p, env, algorithm, mode, S->ent_mask.p, S->ent_off.p, out, cap, nullptr, nullptr, nullptr,
-            nullptr, nullptr, X, S->d_cnt);
-    if (cplx)
-        k_pair_store_long<true><<<S->num_sms * 2, 128, 0, S->stream>>>(
-            S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p,
-            S->bin_start.p, env, algorithm, mode, S->ent_off.p, out, cap, S->c_src.p, S->slow_bins.p, X, S->d_cnt);
-    else
-        k_pair_store_long<false><<<S->num_sms * 2, 128, 0, S->stream>>>(
-            S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p,
-            S->bin_start.p, env, algorithm, mode, S->ent_off.p, out, cap, nullptr, S->slow_bins.p, X, S->d_cnt);
+    k_pair_store<CPLX><<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
+        S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
+        env, algorithm, mode, S->ent_mask.p, S->ent_off.p, out, cap, cmask, CPLX ? S->ent_cbase.p : nullptr,
+        CPLX ? S->cplx_rec.p : nullptr, CPLX ? S->cplx_n.p : nullptr, CPLX ? S->c_src.p : nullptr, X, S->d_cnt);
+    k_long_rows<CPLX, true><<<dim3(8, 64), 128, 0, S->stream>>>(
+        S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
+        env, algorithm, mode, nullptr, nullptr, nullptr, S->ent_off.p, out, cap, CPLX ? S->c_src.p : nullptr,
+        S->long_bins.p, X, S->d_cnt);
     CB_TRY(timer_stop(S, "k_pair_store"));
     S->launches += 2;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;
+}
+
+static int enqueue_pair_pass(System* S, int mode, int64_t* out, uint32_t cap) {
+    if (mode == MODE_CONTACTS && use_complex(S))
+        return enqueue_pair_pass_t<true>(S, mode, out, cap);
+    return enqueue_pair_pass_t<false>(S, mode, out, cap);
 }
 
 // k_contact_gen over the current key list: the contact records (CMC/ChCollisionData.h:159-183).  The shape frames

@@ -4,13 +4,13 @@
 //
 // The element count lives in device memory (*n_dev): the launch geometry is fixed by the capacity and the kernels
 // walk the tiles grid-stride, so a scan can be enqueued before its extent is known on the host.
-// Three launches (tile reduce -> scan of tile sums in one CTA -> tile scan with carry-in); each tile is
-// 256 threads x 16 items, staged through shared memory so that global loads and stores are coalesced.
+// One launch per scan (decoupled look-back, below); each tile is 512 threads x 16 consecutive items per
+// thread, moved as 16-byte vectors.
 #include "common.cuh"
 
 namespace cb200 {
 
-constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_THREADS = 512;
 constexpr int SCAN_ITEMS = 16;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
@@ -64,99 +64,156 @@ __device__ __forceinline__ T block_excl_scan(T v, T* total, T* smem /* >= 33 ent
     return off + incl - v;
 }
 
+// Single-pass scan with decoupled look-back: every tile publishes its aggregate (flag 1), then walks back over its
+// predecessors' status words until it meets an inclusive prefix (flag 2), and publishes its own.  Tiles are handed
+// out by an atomic ticket, so a tile only ever waits for tiles that are already running (no deadlock whatever the
+// number of resident CTAs).  One launch, each input read once and each output written once.
+struct TileState {           // 32 bytes
+    uint32_t flag, pad;      // 0 nothing yet, 1 aggregate published, 2 inclusive prefix published
+    uint64_t agg, incl, pad2;
+};
+
+// 16 consecutive items of a thread, moved as 16-byte vectors (a tile starts on a 16-byte boundary: the arrays come
+// from cudaMalloc and a tile holds a multiple of 4 items)
+template <typename V>
+__device__ __forceinline__ void load_items(const V* __restrict__ p, size_t i0, size_t n, V* v) {
+    constexpr int PER = 16 / sizeof(V);
+    if (i0 + SCAN_ITEMS <= n) {
+#pragma unroll
+        for (int k = 0; k < SCAN_ITEMS / PER; k++) {
+            const uint4 q = reinterpret_cast<const uint4*>(p + i0)[k];
+            if (sizeof(V) == 4) {
+                v[4 * k] = (V)q.x, v[4 * k + 1] = (V)q.y, v[4 * k + 2] = (V)q.z, v[4 * k + 3] = (V)q.w;
+            } else {
+                v[2 * k] = (V)((uint64_t)q.x | ((uint64_t)q.y << 32));
+                v[2 * k + 1] = (V)((uint64_t)q.z | ((uint64_t)q.w << 32));
+            }
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < SCAN_ITEMS; k++)
+            v[k] = i0 + k < n ? p[i0 + k] : V(0);
+    }
+}
+template <typename V>
+__device__ __forceinline__ void store_items(V* __restrict__ p, size_t i0, size_t n, const V* v) {
+    constexpr int PER = 16 / sizeof(V);
+    if (i0 + SCAN_ITEMS <= n) {
+#pragma unroll
+        for (int k = 0; k < SCAN_ITEMS / PER; k++) {
+            uint4 q;
+            if (sizeof(V) == 4) {
+                q = make_uint4((uint32_t)v[4 * k], (uint32_t)v[4 * k + 1], (uint32_t)v[4 * k + 2], (uint32_t)v[4 * k + 3]);
+            } else {
+                const uint64_t a = (uint64_t)v[2 * k], b = (uint64_t)v[2 * k + 1];
+                q = make_uint4((uint32_t)a, (uint32_t)(a >> 32), (uint32_t)b, (uint32_t)(b >> 32));
+            }
+            reinterpret_cast<uint4*>(p + i0)[k] = q;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < SCAN_ITEMS; k++)
+            if (i0 + k < n)
+                p[i0 + k] = v[k];
+    }
+}
+
 template <typename L>
-__global__ void __launch_bounds__(SCAN_THREADS) k_scan_reduce(const typename L::in_t* __restrict__ in,
-                                                             typename L::out_t* __restrict__ tile_sums,
-                                                             const uint32_t* __restrict__ n_dev,
-                                                             const DevCounters* __restrict__ cnt) {
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_onepass(const typename L::in_t* in, typename L::out_t* out,
+                                                              uint64_t* __restrict__ state_raw,
+                                                              const uint32_t* __restrict__ n_dev,
+                                                              const DevCounters* __restrict__ cnt) {
     typedef typename L::out_t T;
+    typedef typename L::in_t I;
     __shared__ T sm[33];
+    __shared__ uint32_t s_ticket;
+    __shared__ T s_prefix;
     if (cnt->overflow)
         return;
     const size_t n = *n_dev;
-    const size_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
-    for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const size_t base = tile * SCAN_TILE;
-        T s = 0;
-#pragma unroll
-        for (int k = 0; k < SCAN_ITEMS; k++) {
-            size_t i = base + (size_t)k * SCAN_THREADS + threadIdx.x;
-            if (i < n)
-                s += L::load(in[i]);
-        }
-        T total;
-        block_excl_scan(s, &total, sm);
+    if (n == 0) {
+        if (blockIdx.x == 0 && threadIdx.x == 0)
+            out[0] = T(0);
+        return;
+    }
+    const uint32_t ntiles = (uint32_t)((n + SCAN_TILE - 1) / SCAN_TILE);
+    uint32_t* ticket = reinterpret_cast<uint32_t*>(state_raw);
+    volatile TileState* st = reinterpret_cast<volatile TileState*>(state_raw + 4);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    while (true) {
         if (threadIdx.x == 0)
-            tile_sums[tile] = total;
-    }
-}
-
-template <typename T>
-__global__ void __launch_bounds__(1024) k_scan_tiles(T* __restrict__ tile_sums, const uint32_t* __restrict__ n_dev,
-                                                     T* __restrict__ out, const DevCounters* __restrict__ cnt) {
-    __shared__ T sm[33];
-    if (cnt->overflow)
-        return;
-    const size_t n = *n_dev;
-    const size_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
-    T carry = 0;
-    for (size_t base = 0; base < ntiles; base += blockDim.x) {
-        size_t i = base + threadIdx.x;
-        T v = (i < ntiles) ? tile_sums[i] : T(0);
-        T total;
-        T ex = block_excl_scan(v, &total, sm);
-        if (i < ntiles)
-            tile_sums[i] = carry + ex;
-        carry += total;
-    }
-    if (threadIdx.x == 0)
-        out[n] = carry;
-}
-
-template <typename L>
-__global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(const typename L::in_t* __restrict__ in,
-                                                            typename L::out_t* __restrict__ out,
-                                                            const typename L::out_t* __restrict__ tile_offsets,
-                                                            const uint32_t* __restrict__ n_dev,
-                                                            const DevCounters* __restrict__ cnt) {
-    typedef typename L::out_t T;
-    __shared__ T sm[33];
-    __shared__ T stage[SCAN_TILE];
-    if (cnt->overflow)
-        return;
-    const size_t n = *n_dev;
-    const size_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
-    for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const size_t base = tile * SCAN_TILE;
-        // coalesced load into shared, then each thread owns SCAN_ITEMS consecutive items
-#pragma unroll
-        for (int k = 0; k < SCAN_ITEMS; k++) {
-            size_t i = base + (size_t)k * SCAN_THREADS + threadIdx.x;
-            stage[k * SCAN_THREADS + threadIdx.x] = (i < n) ? L::load(in[i]) : T(0);
-        }
+            s_ticket = atomicAdd(ticket, 1u);
         __syncthreads();
+        const uint32_t tile = s_ticket;
+        if (tile >= ntiles)
+            break;
+        const size_t i0 = (size_t)tile * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
+        I raw[SCAN_ITEMS];
+        load_items<I>(in, i0, n, raw);
         T loc[SCAN_ITEMS];
         T s = 0;
 #pragma unroll
         for (int k = 0; k < SCAN_ITEMS; k++) {
-            loc[k] = stage[threadIdx.x * SCAN_ITEMS + k];
+            loc[k] = i0 + k < n ? L::load(raw[k]) : T(0);
             s += loc[k];
         }
         T total;
-        T ex = block_excl_scan(s, &total, sm) + tile_offsets[tile];
+        T ex = block_excl_scan(s, &total, sm);
+        if (threadIdx.x == 0) {
+            if (tile == 0) {
+                st[0].incl = (uint64_t)total;
+                __threadfence();
+                st[0].flag = 2u;
+            } else {
+                st[tile].agg = (uint64_t)total;
+                __threadfence();
+                st[tile].flag = 1u;
+            }
+        }
+        if (tile > 0 && wid == 0) {
+            T prefix = 0;
+            int look = (int)tile - 1;
+            while (true) {
+                const int idx = look - lane;
+                uint32_t f = 2u;  // lanes before tile 0 act as a zero-valued terminator
+                T v = 0;
+                if (idx >= 0) {
+                    do {
+                        f = st[idx].flag;
+                    } while (f == 0u);
+                    __threadfence();
+                    v = (T)(f == 2u ? st[idx].incl : st[idx].agg);
+                }
+                const unsigned pm = __ballot_sync(0xffffffffu, f == 2u);
+                const int first = pm ? __ffs(pm) - 1 : 31;  // nearest predecessor holding an inclusive prefix
+                T c = lane <= first ? v : T(0);
 #pragma unroll
-        for (int k = 0; k < SCAN_ITEMS; k++) {
-            T v = loc[k];
-            stage[threadIdx.x * SCAN_ITEMS + k] = ex;
-            ex += v;
+                for (int d = 16; d > 0; d >>= 1)
+                    c += __shfl_xor_sync(0xffffffffu, c, d);
+                prefix += c;
+                if (pm)
+                    break;
+                look -= 32;
+            }
+            if (lane == 0) {
+                s_prefix = prefix;
+                st[tile].incl = (uint64_t)(prefix + total);
+                __threadfence();
+                st[tile].flag = 2u;
+            }
         }
         __syncthreads();
+        const T carry = tile > 0 ? s_prefix : T(0);
+        ex += carry;
+        T o[SCAN_ITEMS];
 #pragma unroll
         for (int k = 0; k < SCAN_ITEMS; k++) {
-            size_t i = base + (size_t)k * SCAN_THREADS + threadIdx.x;
-            if (i < n)
-                out[i] = stage[k * SCAN_THREADS + threadIdx.x];
+            o[k] = ex;
+            ex += loc[k];
         }
+        store_items<T>(out, i0, n, o);
+        if (tile == ntiles - 1 && threadIdx.x == 0)
+            out[n] = carry + total;
         __syncthreads();
     }
 }
@@ -164,17 +221,20 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(const typename L::i
 template <typename L>
 static int scan_impl(System* S, const typename L::in_t* in, typename L::out_t* out, const uint32_t* n_dev,
                      size_t n_cap) {
-    typedef typename L::out_t T;
     size_t ntiles = (n_cap + SCAN_TILE - 1) / SCAN_TILE;
     if (ntiles == 0)
         ntiles = 1;
-    CB_TRY(S->scan_tmp.reserve(ntiles + 2));
-    T* tiles = reinterpret_cast<T*>(S->scan_tmp.p);
-    const int grid = grid_for(S, n_cap, SCAN_TILE, 4);
-    k_scan_reduce<L><<<grid, SCAN_THREADS, 0, S->stream>>>(in, tiles, n_dev, S->d_cnt);
-    k_scan_tiles<T><<<1, 1024, 0, S->stream>>>(tiles, n_dev, out, S->d_cnt);
-    k_scan_apply<L><<<grid, SCAN_THREADS, 0, S->stream>>>(in, out, tiles, n_dev, S->d_cnt);
-    S->launches += 3;
+    const size_t words = 4 + 4 * (ntiles + 1);  // ticket block + one 32-byte status record per tile
+    if (S->scan_tmp.cap < words) {
+        if (S->capturing)
+            return set_error(CB200_ERR_STATE, "scan scratch must be allocated before a step is captured");
+        invalidate_step_graph(S);
+        CB_TRY(S->scan_tmp.reserve(words));
+    }
+    CB_CUDA(cudaMemsetAsync(S->scan_tmp.p, 0, words * sizeof(uint64_t), S->stream));
+    const int grid = grid_for(S, n_cap, SCAN_TILE, 2);
+    k_scan_onepass<L><<<grid, SCAN_THREADS, 0, S->stream>>>(in, out, S->scan_tmp.p, n_dev, S->d_cnt);
+    S->launches += 1;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;
 }

@@ -189,7 +189,7 @@ __global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, GenArgs G, Sh
             delta_t = relvel_t * P.dT;
         double char_vel = P.char_vel;
         size_t slot = 0;        // MULTI: this contact's history slot
-        bool hist_on_b1 = false;
+        bool hist_on_b1 = false, have_slot = false;
         if (MULTI) {
             // contact history lives on the body with the larger id, keyed by (partner, larger shape, smaller shape)
             // (:188-250).  Which of the MAX_SHEAR slots a contact gets has no effect on the forces, so slots are
@@ -224,28 +224,31 @@ __global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, GenArgs G, Sh
                     }
                 }
             }
-            if (cid < 0) {
-                // more than MAX_SHEAR partners: the reference indexes slot -1 here (:232); reported as an error
+            have_slot = cid >= 0;
+            if (!have_slot) {
+                // more than MAX_SHEAR partners: the reference indexes slot -1 here (:232).  Reported as an error (the
+                // counter is sticky); nobody else's history is touched: the contact is treated as a new one.
                 atomicAdd(&cnt->unsupported, 1u);
-                cid = 0;
-            }
-            slot = (size_t)MAX_SHEAR * sb1 + cid;
-            H.touch[slot] = 1;
-            hist_on_b1 = sb1 == (int)b1;
-            d3 sd = mk3(H.disp[3 * slot], H.disp[3 * slot + 1], H.disp[3 * slot + 2]);
-            if (hist_on_b1) {
-                sd += delta_t;
-                sd -= dot3(sd, n) * n;
-                delta_t = sd;
+                relvel_init = (relvel_init < char_vel) ? char_vel : relvel_init;
             } else {
-                sd -= delta_t;
-                sd -= dot3(sd, n) * n;
-                delta_t = -sd;
+                slot = (size_t)MAX_SHEAR * sb1 + cid;
+                H.touch[slot] = 1;
+                hist_on_b1 = sb1 == (int)b1;
+                d3 sd = mk3(H.disp[3 * slot], H.disp[3 * slot + 1], H.disp[3 * slot + 2]);
+                if (hist_on_b1) {
+                    sd += delta_t;
+                    sd -= dot3(sd, n) * n;
+                    delta_t = sd;
+                } else {
+                    sd -= delta_t;
+                    sd -= dot3(sd, n) * n;
+                    delta_t = -sd;
+                }
+                H.disp[3 * slot] = sd.x, H.disp[3 * slot + 1] = sd.y, H.disp[3 * slot + 2] = sd.z;
+                const double r0 = H.relvel0[slot];
+                relvel_init = (r0 < char_vel) ? char_vel : r0;
+                t_contact = H.duration[slot];
             }
-            H.disp[3 * slot] = sd.x, H.disp[3 * slot + 1] = sd.y, H.disp[3 * slot + 2] = sd.z;
-            const double r0 = H.relvel0[slot];
-            relvel_init = (r0 < char_vel) ? char_vel : r0;
-            t_contact = H.duration[slot];
         }
         const double eps = DBL_EPSILON;
         bool done = false;
@@ -367,7 +370,7 @@ __global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, GenArgs G, Sh
                 if (delta_t_mag > eps) {
                     const double ratio = forceT_slide / forceT_mag;
                     forceT *= ratio;
-                    if (MULTI) {  // the stored displacement is rescaled to the Coulomb limit (:460-467)
+                    if (MULTI && have_slot) {  // the stored displacement is rescaled to the Coulomb limit (:460-467)
                         delta_t = (forceT - forceT_damp) / kt;
                         const d3 sd = hist_on_b1 ? delta_t : -delta_t;
                         H.disp[3 * slot] = sd.x, H.disp[3 * slot + 1] = sd.y, H.disp[3 * slot + 2] = sd.z;

@@ -1,4 +1,4 @@
-"""Summarise an ncu --csv launch list (gpu__time_duration.sum) per kernel: tools_launch_summary.py file.csv nsteps"""
+"""Summarise an ncu --csv launch list (gpu__time_duration.sum) per kernel: tools/launch_summary.py file.csv nsteps"""
 import collections
 import csv
 import sys

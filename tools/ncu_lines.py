@@ -1,5 +1,5 @@
 """Per-source-line instruction / stall-sample totals from
-`ncu -i X.ncu-rep --page source --csv --print-source cuda,sass > src.csv`.   usage: tools_ncu_lines.py src.csv [substr-of-function]"""
+`ncu -i X.ncu-rep --page source --csv --print-source cuda,sass > src.csv`.   usage: tools/ncu_lines.py src.csv [substr-of-function]"""
 import csv
 import sys
 

@@ -1,5 +1,7 @@
 """Scratch profiling helper: warm up, then run a few steps inside a cudaProfilerStart/Stop range
 (use with: ncu --profile-from-start off ...)."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import ctypes, sys
 import chrono_wisc_b200 as cw
 from chrono_wisc_b200 import scenes

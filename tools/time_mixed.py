@@ -1,6 +1,8 @@
 """Scratch timing helper (not part of the product): BASELINE.json configs[4] flavour -- a bed of mixed spheres / boxes /
 capsules (demo_MCORE_mixerSMC.cpp:118-168 shape families) settling in an open box, without the mixer blade (its motor is
-a bilateral constraint).  usage: tools_time_mixed.py nx ny nz warm steps algorithm(0 MPR, 2 HYBRID)"""
+a bilateral constraint).  usage: tools/time_mixed.py nx ny nz warm steps algorithm(0 MPR, 2 HYBRID)"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import sys, time
 import numpy as np
 import chrono_wisc_b200 as cw

@@ -1,5 +1,7 @@
 """Scratch timing helper (not part of the product): NSC APGD step on a ball bed (BASELINE.json configs[3]).
-usage: tools_time_nsc.py nx ny nz warm steps [iterations]"""
+usage: tools/time_nsc.py nx ny nz warm steps [iterations]"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import sys, time
 import numpy as np
 import chrono_wisc_b200 as cw

@@ -1,4 +1,6 @@
 """Scratch timing helper (not part of the product): per-stage GPU timers on a settling bed."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import sys, time
 import numpy as np
 import chrono_wisc_b200 as cw
