@@ -59,10 +59,11 @@ int flush_timers(System* S) {
 }
 
 void invalidate_step_graph(System* S) {
-    if (S->step_graph) {
-        cudaGraphExecDestroy(S->step_graph);
-        S->step_graph = nullptr;
-    }
+    for (int p = 0; p < 2; p++)
+        if (S->step_graph[p]) {
+            cudaGraphExecDestroy(S->step_graph[p]);
+            S->step_graph[p] = nullptr;
+        }
     S->direct_steps = 0;
 }
 
@@ -328,8 +329,8 @@ void cb200_destroy(cb200_system* sys) {
     cudaSetDevice(S->device);
     cudaStreamSynchronize(S->stream);
 #define REL(x) S->x.release()
-    REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(bflags); REL(heavy);
-    REL(s_type); REL(s_body); REL(s_fam); REL(s_mat); REL(s_lpos); REL(s_lrot); REL(s_dims); REL(general_ids); REL(s_verts); REL(sh_neigh); REL(sh_touch); REL(sh_disp); REL(sh_relvel); REL(sh_dur); REL(s_wpos); REL(s_wrot);
+    REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(bflags); REL(heavy); REL(b_sphere); REL(b_rad);
+    REL(s_type); REL(s_body); REL(s_fam); REL(s_mat); REL(s_lpos); REL(s_lrot); REL(s_dims); REL(general_ids); REL(s_verts); REL(sh_neigh); REL(sh_touch); REL(sh_disp); REL(sh_relvel); REL(sh_dur); REL(s_wpos); REL(s_wpos_alt); REL(s_wrot);
     REL(s_box); REL(s_meta); REL(mat_smc); REL(mat_nsc); REL(bin_intersections); REL(bin_start); REL(bin_cursor);
     REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_mask); REL(ent_off); REL(slow_bins); REL(long_bins); REL(pair_q); REL(large_list); REL(pairs);
     REL(c_norm); REL(c_pta); REL(c_ptb); REL(c_depth); REL(c_erad); REL(c_bids); REL(c_shapes); REL(c_mats);
@@ -337,8 +338,7 @@ void cb200_destroy(cb200_system* sys) {
     REL(ct_force); REL(ct_torque); REL(b_deg); REL(b_cursor); REL(b_inc); REL(b_force); REL(heavy_list);
     REL(heavy_part); REL(n_frame); REL(n_aux); REL(gamma); REL(n_gamma_hat); REL(n_y); REL(n_gn); REL(n_g); REL(n_rfull);
     REL(n_w); REL(n_w0); REL(n_mk); REL(n_part); REL(n_hist); REL(n_rows);
-    if (S->step_graph)
-        cudaGraphExecDestroy(S->step_graph);
+    invalidate_step_graph(S);
     if (S->copy_stream) {
         cudaStreamDestroy(S->copy_stream);
         cudaEventDestroy(S->ev_copy);
@@ -380,6 +380,7 @@ int cb200_set_settings(cb200_system* sys, const cb200_settings* s) {
     if (s->narrowphase_algorithm < 0 || s->narrowphase_algorithm > 2)
         return set_error(CB200_ERR_ARG, "narrowphase_algorithm must be 0, 1 or 2");
     S->set = *s;
+    S->sphere_aabb_valid = false;
     // ChSystemMulticoreSMC forces a zero envelope every step (MC/physics/ChSystemMulticoreSMC.cpp:27,56-67)
     if (S->set.system_type == 1)
         S->set.collision_envelope = 0;
@@ -424,10 +425,17 @@ int cb200_append_bodies(cb200_system* sys, int n, const double* mass, const doub
     CB_CUDA(cudaMemsetAsync(S->hf.p + 6 * nb0, 0, 6 * (size_t)n * 8, st));
     CB_CUDA(cudaMemsetAsync(S->fapp.p + 6 * nb0, 0, 6 * (size_t)n * 8, st));
     CB_CUDA(cudaMemsetAsync(S->heavy.p + nb0, 0, (size_t)n, st));
+    S->h_b_sphere.resize(nb1, -1);
+    S->h_b_rad.resize(nb1, 0.0);
+    CB_TRY(S->b_sphere.reserve(nb1, true, st));
+    CB_TRY(S->b_rad.reserve(nb1, true, st));
+    CB_TRY(upload(S, S->b_sphere, nb0, S->h_b_sphere.data() + nb0, (size_t)n));
+    CB_TRY(upload(S, S->b_rad, nb0, S->h_b_rad.data() + nb0, (size_t)n));
     CB_CUDA(cudaStreamSynchronize(st));  // host staging buffers go out of scope
     if (first)
         *first = (int)nb0;
     S->nb = (uint32_t)nb1;
+    S->sphere_aabb_valid = false;
     return CB200_OK;
 }
 
@@ -470,6 +478,7 @@ int cb200_append_shapes(cb200_system* sys, int n, const int32_t* type, const uin
     CB_TRY(S->s_lrot.reserve(4 * ns1, true, st));
     CB_TRY(S->s_dims.reserve(4 * ns1, true, st));
     CB_TRY(S->s_wpos.reserve(4 * ns1, true, st));
+    CB_TRY(S->s_wpos_alt.reserve(4 * ns1, true, st));
     CB_TRY(S->s_wrot.reserve(4 * ns1, true, st));
     CB_TRY(S->s_box.reserve(ns1, true, st));
     CB_TRY(S->s_meta.reserve(ns1, true, st));
@@ -487,11 +496,26 @@ int cb200_append_shapes(cb200_system* sys, int n, const int32_t* type, const uin
     CB_TRY(upload(S, S->s_lpos, 3 * ns0, pos_local, 3 * (size_t)n));
     CB_TRY(upload(S, S->s_lrot, 4 * ns0, rot_local, 4 * (size_t)n));
     CB_TRY(upload(S, S->s_dims, 4 * ns0, dims, 4 * (size_t)n));
-    // the shapes k_aabb<true> has to visit (same rule as k_build_meta's bit 2)
+    // A body's first centred sphere is "its" sphere (b_sphere): k_aabb<false> / the integration kernel write its world
+    // record.  Everything else is visited by k_aabb<true> through this list (same rule as k_build_meta's bit 2).
     std::vector<uint32_t> gen;
-    for (int i = 0; i < n; i++)
-        if (!(type[i] == CB200_SPHERE && pos_local[3 * i] == 0 && pos_local[3 * i + 1] == 0 && pos_local[3 * i + 2] == 0))
+    bool own_changed = false;
+    for (int i = 0; i < n; i++) {
+        const bool centred = type[i] == CB200_SPHERE && pos_local[3 * i] == 0 && pos_local[3 * i + 1] == 0 &&
+                             pos_local[3 * i + 2] == 0 && body_id[i] != UINT_MAX;
+        if (centred && S->h_b_sphere[body_id[i]] < 0) {
+            S->h_b_sphere[body_id[i]] = (int32_t)(ns0 + i);
+            S->h_b_rad[body_id[i]] = dims[4 * i];
+            own_changed = true;
+        } else {
             gen.push_back((uint32_t)(ns0 + i));
+        }
+    }
+    if (own_changed) {
+        CB_TRY(upload(S, S->b_sphere, 0, S->h_b_sphere.data(), (size_t)S->nb));
+        CB_TRY(upload(S, S->b_rad, 0, S->h_b_rad.data(), (size_t)S->nb));
+    }
+    S->sphere_aabb_valid = false;
     if (!gen.empty()) {
         CB_TRY(S->general_ids.reserve(S->n_general + gen.size(), true, st));
         CB_TRY(upload(S, S->general_ids, S->n_general, gen.data(), gen.size()));
@@ -629,6 +653,8 @@ int cb200_upload_state(cb200_system* sys, int first, int n, const double* pos, c
         return set_error(CB200_ERR_ARG, "body range out of bounds");
     CB_CUDA(cudaSetDevice(S->device));
     if (pos)
+        S->sphere_aabb_valid = false;
+    if (pos)
         CB_TRY(upload(S, S->pos, 3 * (size_t)first, pos, 3 * (size_t)n));
     if (rot)
         CB_TRY(upload(S, S->rot, 4 * (size_t)first, rot, 4 * (size_t)n));
@@ -665,6 +691,7 @@ int cb200_set_body_flags(cb200_system* sys, int first, int n, const char* active
     CB_TRY(upload(S, S->bflags, (size_t)first, fl.data(), (size_t)n));
     CB_CUDA(cudaStreamSynchronize(S->stream));
     S->meta_dirty = true;
+    S->sphere_aabb_valid = false;
     return CB200_OK;
 }
 
@@ -732,7 +759,9 @@ static int enqueue_one_step(System* S) {
     if (rc == CB200_OK) {
         CB_TRY(timer_stop(S, "advance"));
         CB_TRY(timer_start(S, "integrate"));
+        S->fuse_aabb = !S->slab_on;  // back-to-back steps: this integration also prepares the next step's sphere boxes
         rc = enqueue_integrate(S);
+        S->fuse_aabb = false;
     }
     S->defer_vel_update = S->defer_update_forces = false;
     CB_TRY(rc);
@@ -743,17 +772,19 @@ static int enqueue_one_step(System* S) {
 
 // One step captured into an executable graph (stage timers are skipped while capturing; every allocation a step can
 // need was made by the directly enqueued step before it).
-static int capture_step_graph(System* S) {
+static int capture_step_graph(System* S, int par) {
     cudaGraph_t g = nullptr;
     const int64_t l0 = S->launches;
-    invalidate_step_graph(S);
-    S->step_graph_meta = S->meta_dirty;
+    if (S->step_graph[par]) {
+        cudaGraphExecDestroy(S->step_graph[par]);
+        S->step_graph[par] = nullptr;
+    }
     CB_CUDA(cudaStreamBeginCapture(S->stream, cudaStreamCaptureModeThreadLocal));
     S->capturing = true;
     const int rc = enqueue_one_step(S);
     S->capturing = false;
     const cudaError_t e = cudaStreamEndCapture(S->stream, &g);
-    S->step_graph_launches = (int)(S->launches - l0);
+    S->step_graph_launches[par] = (int)(S->launches - l0);
     S->launches = l0;
     if (rc != CB200_OK) {
         if (g)
@@ -762,10 +793,10 @@ static int capture_step_graph(System* S) {
     }
     if (e != cudaSuccess)
         return set_error(CB200_ERR_CUDA, std::string("cudaStreamEndCapture: ") + cudaGetErrorString(e));
-    const cudaError_t e2 = cudaGraphInstantiate(&S->step_graph, g, 0);
+    const cudaError_t e2 = cudaGraphInstantiate(&S->step_graph[par], g, 0);
     cudaGraphDestroy(g);
     if (e2 != cudaSuccess) {
-        S->step_graph = nullptr;
+        S->step_graph[par] = nullptr;
         return set_error(CB200_ERR_CUDA, std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e2));
     }
     return CB200_OK;
@@ -779,19 +810,25 @@ static bool graph_capable(const System* S) {
 
 // A step through the cached graph (captured once a directly enqueued step has made every lazy allocation).
 static int replay_or_enqueue_step(System* S) {
-    if (S->direct_steps < 1) {
+    // the captured step relies on the previous step's integration for the spheres' records and on clean shape records
+    if (S->direct_steps < 1 || !S->sphere_aabb_valid || S->meta_dirty) {
         S->direct_steps++;
         return enqueue_one_step(S);
     }
-    if (!S->step_graph || (S->meta_dirty && !S->step_graph_meta))
-        CB_TRY(capture_step_graph(S));
-    CB_CUDA(cudaGraphLaunch(S->step_graph, S->stream));
-    S->launches += S->step_graph_launches;
-    if (S->step_graph_meta)
-        S->meta_dirty = false;
+    const int par = S->wpos_parity;
+    if (!S->step_graph[par]) {
+        CB_TRY(capture_step_graph(S, par));  // leaves the host-side state as if the step had been enqueued
+    } else {
+        // what enqueue_one_step does on the host side for such a step
+        std::swap(S->s_wpos, S->s_wpos_alt);
+        S->wpos_parity ^= 1;
+    }
+    CB_CUDA(cudaGraphLaunch(S->step_graph[par], S->stream));
+    S->launches += S->step_graph_launches[par];
     S->pairs_valid = false;
     S->contacts_geom_valid = false;  // the replayed step made a new key list; the records are those of an older one
     S->box_relative = true;
+    S->sphere_aabb_valid = true;
     return CB200_OK;
 }
 
@@ -870,6 +907,7 @@ int cb200_step_host(cb200_system* sys, double* pos, double* rot, double* vel) {
     CB_TRY(ensure_capacity(S));
     const size_t nb = S->nb;
     for (int attempt = 0; attempt < 8; attempt++) {
+        S->sphere_aabb_valid = false;  // the pose comes from the host
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->steps_done, 0, 4, S->stream));
         CB_TRY(clear_unsupported(S));
         CB_CUDA(cudaMemcpyAsync(S->pos.p, pos, 3 * nb * sizeof(double), cudaMemcpyHostToDevice, S->stream));

@@ -7,7 +7,7 @@
 //                                       (on the device, so the step needs no host round trip)
 //   OffsetAABB + f_Count_AABB_BIN     CMC/ChBroadphase.cpp:168-176,261-268         -> k_bin_count
 //   exclusive_scan / sort_by_key / RLE CMC/ChBroadphase.cpp:271-301                -> counting sort: histogram with
-//                                       warp-aggregated atomics, packed u64 scan, scatter; the in-bin rank sort is
+//                                       L2 atomics, packed u64 scan, scatter; the in-bin rank sort is
 //                                       done by the pair kernel on its staged tile (pairs.cu)
 //   f_Count/Store_AABB_AABB_Intersection  CMC/ChCollisionUtilsBroadphase.cpp:86-217
 //   + PreprocessCount / DispatchPRIMS / remove_if  CMC/ChNarrowphase.cpp:94-155,264-320,366-385
@@ -50,7 +50,9 @@ __global__ void __launch_bounds__(256) k_build_meta(uint32_t ns, const int32_t* 
                                                     const uint32_t* __restrict__ s_fam,
                                                     const int32_t* __restrict__ s_mat,
                                                     const double* __restrict__ s_lpos,
-                                                    const uint8_t* __restrict__ bflags, ShapeMeta* __restrict__ meta) {
+                                                    const uint8_t* __restrict__ bflags,
+                                                    const int32_t* __restrict__ b_sphere /* null: slab systems */,
+                                                    ShapeMeta* __restrict__ meta) {
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ns; i += gridDim.x * blockDim.x) {
         ShapeMeta m;
         m.body = s_body[i];
@@ -58,25 +60,33 @@ __global__ void __launch_bounds__(256) k_build_meta(uint32_t ns, const int32_t* 
         m.pad = 0;
         const uint32_t type = (uint32_t)s_type[i] & 0xff;
         m.info = type << 8 | ((uint32_t)s_mat[i] & 0xffff) << 16;
+        bool own = true;  // the body's own centred sphere (the first one it was given)
         if (m.body != UINT_MAX) {
             const uint32_t fl = bflags[m.body];
             m.info |= fl & 3u;
+            if (b_sphere)
+                own = b_sphere[m.body] == (int32_t)i;
             if (fl & 4u)
                 m.body = UINT_MAX;  // vacant slot of a slab system: treated like a removed shape
+        } else if (b_sphere) {
+            own = false;
         }
-        // bit 2: sphere centred on its body (ObA == 0): world centre == body position, no rotation needed
-        if (type == CB200_SPHERE && s_lpos[3 * i] == 0 && s_lpos[3 * i + 1] == 0 && s_lpos[3 * i + 2] == 0)
+        // bit 2: the body's sphere, centred on it (ObA == 0): world centre == body position, no rotation needed
+        if (own && type == CB200_SPHERE && s_lpos[3 * i] == 0 && s_lpos[3 * i + 1] == 0 && s_lpos[3 * i + 2] == 0)
             m.info |= 4u;
         meta[i] = m;
     }
 }
 
-__global__ void k_reset_counters(DevCounters* cnt, uint32_t nb, uint32_t ns) {
+// keep_bbox: the integration kernel that ended the previous step has already put the bodies' own spheres into the box
+__global__ void k_reset_counters(DevCounters* cnt, uint32_t nb, uint32_t ns, bool keep_bbox) {
     if (threadIdx.x == 0) {
         cnt->n_bodies = nb;
         cnt->n_shapes = ns;
-        cnt->bbox[0] = cnt->bbox[1] = cnt->bbox[2] = ~0ull;
-        cnt->bbox[3] = cnt->bbox[4] = cnt->bbox[5] = 0ull;
+        if (!keep_bbox) {
+            cnt->bbox[0] = cnt->bbox[1] = cnt->bbox[2] = ~0ull;
+            cnt->bbox[3] = cnt->bbox[4] = cnt->bbox[5] = 0ull;
+        }
         cnt->n_large = 0;
         cnt->n_heavy = 0;
         cnt->ct_body_count = 0;
@@ -213,28 +223,8 @@ __global__ void __launch_bounds__(256) k_aabb(uint32_t ns, const uint32_t* __res
             counted = true;
         }
     }
-    // union of the AABBs of colliding shapes (BoxInvert/BoxReduce, CMC/ChBroadphase.cpp:38-100): min/max are exact
-    // and order-free, so warp shuffles + ordered-integer atomics give the reference's result bit for bit.
-    const unsigned any = __ballot_sync(0xffffffffu, counted);
-    if (any) {
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) {
-            mn.x = fmin(mn.x, __shfl_xor_sync(0xffffffffu, mn.x, d));
-            mn.y = fmin(mn.y, __shfl_xor_sync(0xffffffffu, mn.y, d));
-            mn.z = fmin(mn.z, __shfl_xor_sync(0xffffffffu, mn.z, d));
-            mx.x = fmax(mx.x, __shfl_xor_sync(0xffffffffu, mx.x, d));
-            mx.y = fmax(mx.y, __shfl_xor_sync(0xffffffffu, mx.y, d));
-            mx.z = fmax(mx.z, __shfl_xor_sync(0xffffffffu, mx.z, d));
-        }
-        if ((threadIdx.x & 31) == 0) {
-            atomicMin(&cnt->bbox[0], enc_ordered(mn.x));
-            atomicMin(&cnt->bbox[1], enc_ordered(mn.y));
-            atomicMin(&cnt->bbox[2], enc_ordered(mn.z));
-            atomicMax(&cnt->bbox[3], enc_ordered(mx.x));
-            atomicMax(&cnt->bbox[4], enc_ordered(mx.y));
-            atomicMax(&cnt->bbox[5], enc_ordered(mx.z));
-        }
-    }
+    // union of the AABBs of colliding shapes (BoxInvert/BoxReduce, CMC/ChBroadphase.cpp:38-100)
+    bbox_block_merge(cnt, mn, mx, counted);
 }
 
 // DetermineBoundingBox + ComputeTopLevelResolution (CMC/ChBroadphase.cpp:142-208) and Compute_Grid_Resolution
@@ -302,24 +292,6 @@ __device__ __forceinline__ bool bin_range(const double* mn, const double* mx, co
            hi[0] >= lo[0] && hi[1] >= lo[1] && hi[2] >= lo[2];
 }
 
-// Warp-aggregated counter update: lanes that target the same counter elect a leader that applies the group size
-// once; every lane gets its own slot.  All 32 lanes must call (valid=false lanes pass through).
-// DIR = +1: counter counts up from 0 (histogram);  DIR = -1: counts down from the histogram value (scatter).
-template <int DIR>
-__device__ __forceinline__ uint32_t warp_agg(uint32_t* counters, uint32_t key, bool valid) {
-    const unsigned lane = threadIdx.x & 31;
-    const unsigned grp = __match_any_sync(0xffffffffu, valid ? key : 0xffffffffu);
-    const int leader = __ffs(grp) - 1;
-    const unsigned rank = __popc(grp & ((1u << lane) - 1));
-    uint32_t base = 0;
-    if (valid && (int)lane == leader) {
-        const uint32_t n = (uint32_t)__popc(grp);
-        base = DIR > 0 ? atomicAdd(&counters[key], n) : atomicSub(&counters[key], n) - n;
-    }
-    base = __shfl_sync(0xffffffffu, base, leader);
-    return base + rank;
-}
-
 // --------------------------------------------------------------------------------------------------------------
 // k_bin_count: grid of this step + OffsetAABB (in place, non-spheres) + bins touched per shape + dense histogram.
 // --------------------------------------------------------------------------------------------------------------
@@ -353,8 +325,7 @@ __global__ void __launch_bounds__(256) k_bin_count(GridSettings st, double envel
     if (g.num_bins > st.cap_bins)
         return;
     const uint32_t ns = st.ns;
-    const uint32_t nround = (ns + 31u) & ~31u;  // whole warps stay together for the aggregated atomics
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nround; i += gridDim.x * blockDim.x) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ns; i += gridDim.x * blockDim.x) {
         int lo[3] = {0, 0, 0}, hi[3] = {-1, -1, -1};
         uint32_t n = 0;
         if (i < ns) {
@@ -385,16 +356,12 @@ __global__ void __launch_bounds__(256) k_bin_count(GridSettings st, double envel
             bin_intersections[i] = n;
         }
         const uint32_t mine = (n <= LARGE_BINS) ? n : 0;
-        uint32_t wmax = mine;
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1)
-            wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, d));
-        // the shape's bins, x slowest / z fastest, walked with counters (no division per bin)
+        // the shape's bins, x slowest / z fastest, walked with counters (no division per bin).  Plain atomics: they
+        // resolve in L2 at a few entries per bin; warp aggregation (match.any) cost more than it saved (measured).
         int ix = lo[0], iy = lo[1], iz = lo[2];
-        for (uint32_t it = 0; it < wmax; it++) {
-            const bool valid = it < mine;
+        for (uint32_t it = 0; it < mine; it++) {
             const uint32_t b = (uint32_t)((iz * g.bins[1]) * g.bins[0] + iy * g.bins[0] + ix);  // Hash_Index
-            warp_agg<1>(hist, b, valid);
+            atomicAdd(&hist[b], 1u);
             if (++iz > hi[2]) {
                 iz = lo[2];
                 if (++iy > hi[1]) {
@@ -476,8 +443,7 @@ __global__ void __launch_bounds__(256) k_bin_fill(uint32_t ns, double envelope, 
     }
     if (ni > cap_entries)
         return;
-    const uint32_t nround = (ns + 31u) & ~31u;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nround; i += gridDim.x * blockDim.x) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ns; i += gridDim.x * blockDim.x) {
         int lo[3] = {0, 0, 0}, hi[3] = {-1, -1, -1};
         uint32_t mine = 0;
         if (i < ns) {
@@ -489,13 +455,8 @@ __global__ void __launch_bounds__(256) k_bin_fill(uint32_t ns, double envelope, 
                 mine = n;
             }
         }
-        uint32_t wmax = mine;
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1)
-            wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, d));
         int ix = lo[0], iy = lo[1], iz = lo[2];
-        for (uint32_t it = 0; it < wmax; it++) {
-            const bool valid = it < mine;
+        for (uint32_t it = 0; it < mine; it++) {
             const uint32_t b = (uint32_t)((iz * g.bins[1]) * g.bins[0] + iy * g.bins[0] + ix);
             if (++iz > hi[2]) {
                 iz = lo[2];
@@ -504,12 +465,10 @@ __global__ void __launch_bounds__(256) k_bin_fill(uint32_t ns, double envelope, 
                     ++ix;
                 }
             }
-            const uint32_t slot = warp_agg<-1>(cursor, b, valid);
-            if (valid) {
-                const uint32_t e = (uint32_t)bin_start[b] + slot;
-                ent_tmp[e] = i;
-                ent_bin[e] = b;
-            }
+            const uint32_t slot = atomicSub(&cursor[b], 1u) - 1u;
+            const uint32_t e = (uint32_t)bin_start[b] + slot;
+            ent_tmp[e] = i;
+            ent_bin[e] = b;
         }
     }
 }
@@ -523,22 +482,35 @@ int enqueue_aabb(System* S) {
     if (S->meta_dirty) {
         k_build_meta<<<grid_for(S, S->ns, 256), 256, 0, S->stream>>>(S->ns, S->s_type.p, S->s_body.p, S->s_fam.p,
                                                                      S->s_mat.p, S->s_lpos.p, S->bflags.p,
-                                                                     S->s_meta.p);
+                                                                     S->slab_on ? nullptr : S->b_sphere.p, S->s_meta.p);
         S->meta_dirty = false;
+        S->sphere_aabb_valid = false;
         S->launches++;
     }
-    k_reset_counters<<<1, 32, 0, S->stream>>>(S->d_cnt, S->nb, S->ns);
+    // the bodies' own spheres: done by the integration that ended the previous step, unless something touched the
+    // state since (uploads, new bodies / shapes, flags, settings)
+    const bool spheres_done = S->sphere_aabb_valid && !S->slab_on;
+    if (spheres_done) {
+        // their records were written to the other buffer (the previous step's stayed readable until now)
+        std::swap(S->s_wpos, S->s_wpos_alt);
+        S->wpos_parity ^= 1;
+    }
+    k_reset_counters<<<1, 32, 0, S->stream>>>(S->d_cnt, S->nb, S->ns, spheres_done);
     CB_CUDA(cudaMemsetAsync(S->heavy.p, 0, S->nb, S->stream));
-    k_aabb<false><<<grid_for(S, S->ns, 256), 256, 0, S->stream>>>(
-        S->ns, nullptr, S->s_meta.p, S->s_lpos.p, S->s_lrot.p, S->s_dims.p, S->s_verts.p, S->pos.p, S->rot.p,
-        S->set.collision_envelope, S->s_wpos.p, S->s_wrot.p, S->s_box.p, S->d_cnt);
+    if (!spheres_done) {
+        k_aabb<false><<<grid_for(S, S->ns, 256), 256, 0, S->stream>>>(
+            S->ns, nullptr, S->s_meta.p, S->s_lpos.p, S->s_lrot.p, S->s_dims.p, S->s_verts.p, S->pos.p, S->rot.p,
+            S->set.collision_envelope, S->s_wpos.p, S->s_wrot.p, S->s_box.p, S->d_cnt);
+        S->launches++;
+    }
+    S->sphere_aabb_valid = false;  // consumed; the integration of a whole step sets it again
     const bool listed = !S->slab_on && S->general_ids.p;
     const uint32_t ng = listed ? S->n_general : S->ns;
     if (ng)
         k_aabb<true><<<grid_for(S, ng, 256), 256, 0, S->stream>>>(
             ng, listed ? S->general_ids.p : nullptr, S->s_meta.p, S->s_lpos.p, S->s_lrot.p, S->s_dims.p, S->s_verts.p,
             S->pos.p, S->rot.p, S->set.collision_envelope, S->s_wpos.p, S->s_wrot.p, S->s_box.p, S->d_cnt);
-    S->launches += 3;
+    S->launches += 2;
     S->pairs_valid = false;
     S->box_relative = false;
     CB_CUDA(cudaGetLastError());

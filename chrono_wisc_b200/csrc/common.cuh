@@ -154,6 +154,14 @@ struct System {
     DevBuf<double> inv_inertia;  // 3 nb
     DevBuf<uint8_t> bflags;  // bit0 active, bit1 collide, bit2 vacant slot (slab decomposition: no body lives here)
     DevBuf<uint8_t> heavy;   // body owns a large shape this step
+    // a body's own centred sphere (the first sphere shape with ObA == 0 added for it; -1: none) and its radius: the
+    // integration kernel writes that shape's world record and box itself (integrate.cu, k_integrate<.., true>)
+    DevBuf<int32_t> b_sphere;
+    DevBuf<double> b_rad;
+    std::vector<int32_t> h_b_sphere;
+    std::vector<double> h_b_rad;
+    bool sphere_aabb_valid = false;  // s_wpos of those spheres and their share of the global box match `pos`
+    bool fuse_aabb = false;          // whole-step paths: the integration that ends this step prepares the next one
 
     // ---- shapes (shape_container, CMC/ChCollisionData.h:35-59) ----
     uint32_t ns = 0;
@@ -169,6 +177,8 @@ struct System {
     DevBuf<double> s_verts;  // 3 n_verts: vertex pool of triangles (body frame) and convex hulls (shape frame)
     uint32_t n_verts = 0;
     DevBuf<double> s_wpos;   // 4 ns  world position + dims[0]  (obj_data_A_global)
+    DevBuf<double> s_wpos_alt;  // the records of the NEXT step's own spheres, written by the integration of a whole
+                                // step; the collision stage's records stay readable until the next step starts
     DevBuf<double> s_wrot;   // 4 ns  world rotation            (obj_data_R_global)
     DevBuf<ShapeBox> s_box;  // ns    AABB
     DevBuf<ShapeMeta> s_meta;  // ns
@@ -272,9 +282,11 @@ struct System {
     bool defer_update_forces = false;  // whole-step paths (SMC): hf is formed in k_body_reduce<true>, k_update_forces is skipped
     bool defer_vel_update = false;   // whole-step paths (SMC): v += M^-1 hf is done by k_integrate<true>, not k_vel_update
     bool capturing = false;          // a step is being captured into a CUDA graph: timers are skipped
-    cudaGraphExec_t step_graph = nullptr;
-    int step_graph_launches = 0;     // kernel / memset nodes of one captured step
-    bool step_graph_meta = false;    // the captured step rebuilds the per-shape records (meta_dirty at capture)
+    // Two graphs: the world records of the bodies' own spheres are double-buffered (s_wpos / s_wpos_alt swap every
+    // whole step, see integrate.cu), so consecutive steps capture different pointers.
+    cudaGraphExec_t step_graph[2] = {nullptr, nullptr};
+    int step_graph_launches[2] = {0, 0};  // kernel / memset nodes of one captured step
+    int wpos_parity = 0;             // flips with every s_wpos / s_wpos_alt swap
     int direct_steps = 0;            // steps enqueued directly since the graph was last invalidated
     unsigned async_calls = 0;
     cudaStream_t copy_stream = nullptr;  // second copy engine queue of cb200_step_host
@@ -343,5 +355,58 @@ HD double dec_ordered(unsigned long long u) {
     return d;
 #endif
 }
+
+
+#ifdef __CUDACC__
+// The boxes of a CTA's threads (counted == false: none) join the global bounding box (BoxInvert / BoxReduce,
+// CMC/ChBroadphase.cpp:38-100: min and max are exact and order-free, so any reduction tree gives the reference's bits).
+// Keys are the order-preserving 64-bit encodings; a warp reduces them with two 32-bit hardware reductions per value
+// (high word, then the low words of the lanes that hold that high word), the CTA combines its warps in shared memory and
+// issues at most six atomics, and only those that still improve on a fresh read of the global value.
+// Must be called by all threads of the CTA.
+__device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v) {
+    const uint32_t hi = (uint32_t)(v >> 32), lo = (uint32_t)v;
+    const uint32_t mh = __reduce_min_sync(0xffffffffu, hi);
+    const uint32_t ml = __reduce_min_sync(0xffffffffu, hi == mh ? lo : 0xffffffffu);
+    return ((unsigned long long)mh << 32) | ml;
+}
+__device__ __forceinline__ unsigned long long warp_max_u64(unsigned long long v) {
+    const uint32_t hi = (uint32_t)(v >> 32), lo = (uint32_t)v;
+    const uint32_t mh = __reduce_max_sync(0xffffffffu, hi);
+    const uint32_t ml = __reduce_max_sync(0xffffffffu, hi == mh ? lo : 0u);
+    return ((unsigned long long)mh << 32) | ml;
+}
+__device__ __forceinline__ void bbox_block_merge(DevCounters* cnt, const d3& mn, const d3& mx, bool counted) {
+    __shared__ unsigned long long part[32][6];
+    unsigned long long k[6];
+    k[0] = counted ? enc_ordered(mn.x) : ~0ull, k[1] = counted ? enc_ordered(mn.y) : ~0ull;
+    k[2] = counted ? enc_ordered(mn.z) : ~0ull, k[3] = counted ? enc_ordered(mx.x) : 0ull;
+    k[4] = counted ? enc_ordered(mx.y) : 0ull, k[5] = counted ? enc_ordered(mx.z) : 0ull;
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        k[a] = warp_min_u64(k[a]);
+        k[3 + a] = warp_max_u64(k[3 + a]);
+    }
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    if (lane == 0)
+#pragma unroll
+        for (int a = 0; a < 6; a++)
+            part[wid][a] = k[a];
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        const int a = threadIdx.x;
+        unsigned long long v = part[0][a];
+        for (int w = 1; w < nw; w++)
+            v = a < 3 ? min(v, part[w][a]) : max(v, part[w][a]);
+        const unsigned long long cur = reinterpret_cast<volatile unsigned long long*>(cnt->bbox)[a];
+        if (a < 3 ? v < cur : v > cur) {
+            if (a < 3)
+                atomicMin(&cnt->bbox[a], v);
+            else
+                atomicMax(&cnt->bbox[a], v);
+        }
+    }
+}
+#endif
 
 }  // namespace cb200

@@ -47,64 +47,102 @@ __global__ void __launch_bounds__(256) k_update_forces(uint32_t nb, double h, d3
 // x += h v ;  q <- dq(h R w) * q   (ChBody::VariablesQbIncrementPosition), active bodies only
 // VEL: the velocity update of the SMC solve (k_vel_update, smc.cu: v += M^-1 hf, same operations) is done here, in
 // the same pass over the bodies -- used by the whole-step paths, where nothing reads the velocities in between.
-template <bool VEL>
+// AABB: whole-step paths again -- the body's own centred sphere gets its world record (obj_data_A_global + radius) and
+// its box joins the global bounding box of the NEXT step right here, with the operations of k_aabb<false>
+// (broadphase.cu), so that step does not read the positions once more just for that.
+struct AabbArgs {
+    const int32_t* b_sphere;
+    const double* b_rad;
+    double* s_wpos;
+    double envelope;
+};
+
+template <bool VEL, bool AABB>
 __global__ void __launch_bounds__(256) k_integrate(uint32_t nb, double h, const uint8_t* __restrict__ bflags,
                                                    double* __restrict__ vel, double* __restrict__ pos,
                                                    double* __restrict__ rot, const double* __restrict__ mass,
                                                    const double* __restrict__ inv_inertia,
-                                                   const double* __restrict__ hf, DevCounters* __restrict__ cnt) {
+                                                   const double* __restrict__ hf, AabbArgs A,
+                                                   DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b == 0)
         cnt->steps_done++;  // this step was applied in full (nothing upstream overflowed)
-    if (b >= nb || !(bflags[b] & 1u))
-        return;
-    double* v = vel + 6 * (size_t)b;
-    if (VEL) {
-        const double inv_mass = 1.0 / mass[b];
-        const double* f = hf + 6 * (size_t)b;
-        v[0] = v[0] + inv_mass * f[0];
-        v[1] = v[1] + inv_mass * f[1];
-        v[2] = v[2] + inv_mass * f[2];
-        v[3] = v[3] + inv_inertia[3 * b] * f[3];
-        v[4] = v[4] + inv_inertia[3 * b + 1] * f[4];
-        v[5] = v[5] + inv_inertia[3 * b + 2] * f[5];
-    }
-    double* p = pos + 3 * (size_t)b;
-    p[0] = p[0] + v[0] * h;
-    p[1] = p[1] + v[1] * h;
-    p[2] = p[2] + v[2] * h;
+    const uint32_t fl = b < nb ? bflags[b] : 0u;
+    d3 bmn = mk3(DBL_MAX), bmx = mk3(-DBL_MAX);
+    bool counted = false;
+    if (b < nb) {
+        double* p = pos + 3 * (size_t)b;
+        d3 pn = mk3(p[0], p[1], p[2]);
+        if (fl & 1u) {
+            double* v = vel + 6 * (size_t)b;
+            if (VEL) {
+                const double inv_mass = 1.0 / mass[b];
+                const double* f = hf + 6 * (size_t)b;
+                v[0] = v[0] + inv_mass * f[0];
+                v[1] = v[1] + inv_mass * f[1];
+                v[2] = v[2] + inv_mass * f[2];
+                v[3] = v[3] + inv_inertia[3 * b] * f[3];
+                v[4] = v[4] + inv_inertia[3 * b + 1] * f[4];
+                v[5] = v[5] + inv_inertia[3 * b + 2] * f[5];
+            }
+            pn = mk3(pn.x + v[0] * h, pn.y + v[1] * h, pn.z + v[2] * h);
+            p[0] = pn.x, p[1] = pn.y, p[2] = pn.z;
 
-    const double4 qa = reinterpret_cast<const double4*>(rot)[b];
-    const double e0 = qa.x, e1 = qa.y, e2 = qa.z, e3 = qa.w;
-    // ChMatrix33::SetFromQuaternion (src/chrono/core/ChMatrix33.h:253-274) times the local angular velocity
-    const double e0e0 = e0 * e0, e1e1 = e1 * e1, e2e2 = e2 * e2, e3e3 = e3 * e3;
-    const double e0e1 = e0 * e1, e0e2 = e0 * e2, e0e3 = e0 * e3, e1e2 = e1 * e2, e1e3 = e1 * e3, e2e3 = e2 * e3;
-    const double wx = v[3], wy = v[4], wz = v[5];
-    double ax = ((e0e0 + e1e1) * 2 - 1) * wx + ((e1e2 - e0e3) * 2) * wy + ((e1e3 + e0e2) * 2) * wz;
-    double ay = ((e1e2 + e0e3) * 2) * wx + ((e0e0 + e2e2) * 2 - 1) * wy + ((e2e3 - e0e1) * 2) * wz;
-    double az = ((e1e3 - e0e2) * 2) * wx + ((e2e3 + e0e1) * 2) * wy + ((e0e0 + e3e3) * 2 - 1) * wz;
-    const double len = sqrt(ax * ax + ay * ay + az * az);
-    const double angle = len * h;
-    // ChVector3::Normalize (src/chrono/core/ChVector3.h:873-883)
-    if (len < DBL_MIN) {
-        ax = 1, ay = 0, az = 0;
-    } else {
-        const double s = 1 / len;
-        ax *= s, ay *= s, az *= s;
+            const double4 qa = reinterpret_cast<const double4*>(rot)[b];
+            const double e0 = qa.x, e1 = qa.y, e2 = qa.z, e3 = qa.w;
+            // ChMatrix33::SetFromQuaternion (src/chrono/core/ChMatrix33.h:253-274) times the local angular velocity
+            const double e0e0 = e0 * e0, e1e1 = e1 * e1, e2e2 = e2 * e2, e3e3 = e3 * e3;
+            const double e0e1 = e0 * e1, e0e2 = e0 * e2, e0e3 = e0 * e3, e1e2 = e1 * e2, e1e3 = e1 * e3, e2e3 = e2 * e3;
+            const double wx = v[3], wy = v[4], wz = v[5];
+            double ax = ((e0e0 + e1e1) * 2 - 1) * wx + ((e1e2 - e0e3) * 2) * wy + ((e1e3 + e0e2) * 2) * wz;
+            double ay = ((e1e2 + e0e3) * 2) * wx + ((e0e0 + e2e2) * 2 - 1) * wy + ((e2e3 - e0e1) * 2) * wz;
+            double az = ((e1e3 - e0e2) * 2) * wx + ((e2e3 + e0e1) * 2) * wy + ((e0e0 + e3e3) * 2 - 1) * wz;
+            const double len = sqrt(ax * ax + ay * ay + az * az);
+            const double angle = len * h;
+            // ChVector3::Normalize (src/chrono/core/ChVector3.h:873-883)
+            if (len < DBL_MIN) {
+                ax = 1, ay = 0, az = 0;
+            } else {
+                const double s = 1 / len;
+                ax *= s, ay *= s, az *= s;
+            }
+            // SetFromAngleAxis (ChQuaternion.h:1052-1059)
+            const double half = angle / 2;
+            const double sh = sin(half);
+            const double d0 = cos(half), d1 = ax * sh, d2 = ay * sh, d3_ = az * sh;
+            // mdeltarot * moldrot, ChQuaternion::Cross (ChQuaternion.h:891-903)
+            double4 qn;
+            qn.x = d0 * e0 - d1 * e1 - d2 * e2 - d3_ * e3;
+            qn.y = d0 * e1 + d1 * e0 - d3_ * e2 + d2 * e3;
+            qn.z = d0 * e2 + d2 * e0 + d3_ * e1 - d1 * e3;
+            qn.w = d0 * e3 + d3_ * e0 - d2 * e1 + d1 * e2;
+            reinterpret_cast<double4*>(rot)[b] = qn;
+        }
+        if (AABB) {
+            const int32_t si = A.b_sphere[b];
+            if (si >= 0) {
+                // k_aabb<false>: centred sphere, Rotate(0, q) + p == p
+                const double rad = A.b_rad[b];
+                reinterpret_cast<double4*>(A.s_wpos)[si] = make_double4(pn.x, pn.y, pn.z, rad);
+                if (fl & 2u) {
+                    const double r = rad + A.envelope;
+                    bmn = pn - r, bmx = pn + r;
+                    counted = true;
+                }
+            }
+        }
     }
-    // SetFromAngleAxis (ChQuaternion.h:1052-1059)
-    const double half = angle / 2;
-    const double sh = sin(half);
-    const double d0 = cos(half), d1 = ax * sh, d2 = ay * sh, d3_ = az * sh;
-    // mdeltarot * moldrot, ChQuaternion::Cross (ChQuaternion.h:891-903)
-    double4 qn;
-    qn.x = d0 * e0 - d1 * e1 - d2 * e2 - d3_ * e3;
-    qn.y = d0 * e1 + d1 * e0 - d3_ * e2 + d2 * e3;
-    qn.z = d0 * e2 + d2 * e0 + d3_ * e1 - d1 * e3;
-    qn.w = d0 * e3 + d3_ * e0 - d2 * e1 + d1 * e2;
-    reinterpret_cast<double4*>(rot)[b] = qn;
+    if (AABB)
+        bbox_block_merge(cnt, bmn, bmx, counted);  // union of the boxes of colliding shapes, as in k_aabb
+}
+
+__global__ void k_reset_bbox(DevCounters* cnt) {
+    if (threadIdx.x == 0 && !cnt->overflow) {
+        cnt->bbox[0] = cnt->bbox[1] = cnt->bbox[2] = ~0ull;
+        cnt->bbox[3] = cnt->bbox[4] = cnt->bbox[5] = 0ull;
+    }
 }
 
 int enqueue_update_forces(System* S) {
@@ -122,13 +160,26 @@ int enqueue_update_forces(System* S) {
 int enqueue_integrate(System* S) {
     if (S->nb == 0)
         return CB200_OK;
-    if (S->defer_vel_update)
-        k_integrate<true><<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(
-            S->nb, S->set.step_size, S->bflags.p, S->vel.p, S->pos.p, S->rot.p, S->mass.p, S->inv_inertia.p, S->hf.p,
-            S->d_cnt);
-    else
-        k_integrate<false><<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(
-            S->nb, S->set.step_size, S->bflags.p, S->vel.p, S->pos.p, S->rot.p, nullptr, nullptr, nullptr, S->d_cnt);
+    const int grid = blocks_for(S->nb, 256);
+    const bool fuse = S->fuse_aabb && S->b_sphere.p && S->s_wpos_alt.p && S->ns > 0 && !S->meta_dirty;
+    AabbArgs A = {S->b_sphere.p, S->b_rad.p, S->s_wpos_alt.p, S->set.collision_envelope};
+#define INTEGRATE(VEL, AABB)                                                                                          \
+    k_integrate<VEL, AABB><<<grid, 256, 0, S->stream>>>(S->nb, S->set.step_size, S->bflags.p, S->vel.p, S->pos.p,      \
+                                                        S->rot.p, S->mass.p, S->inv_inertia.p, S->hf.p, A, S->d_cnt)
+    if (fuse) {
+        k_reset_bbox<<<1, 32, 0, S->stream>>>(S->d_cnt);
+        S->launches++;
+        if (S->defer_vel_update)
+            INTEGRATE(true, true);
+        else
+            INTEGRATE(false, true);
+    } else if (S->defer_vel_update) {
+        INTEGRATE(true, false);
+    } else {
+        INTEGRATE(false, false);
+    }
+#undef INTEGRATE
+    S->sphere_aabb_valid = fuse;
     S->launches++;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;

@@ -937,6 +937,7 @@ __global__ void __launch_bounds__(256) k_pair_store(const ShapeMeta* __restrict_
                                                     const uint32_t* __restrict__ ent_cbase,
                                                     const uint32_t* __restrict__ rec,
                                                     const uint32_t* __restrict__ cplx_n, uint32_t* __restrict__ c_src,
+                                                    int32_t* __restrict__ c_bids, uint32_t* __restrict__ c_mats,
                                                     CplxArgs X, DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
@@ -965,7 +966,14 @@ __global__ void __launch_bounds__(256) k_pair_store(const ShapeMeta* __restrict_
             continue;
         const uint32_t bin = ent_bin[e];
         const uint32_t s = (uint32_t)bin_start[bin], k = (uint32_t)bin_start[bin + 1] - s;
-        const int64_t hiA = (int64_t)ent_shape[e] << 32;
+        const uint32_t idA = ent_shape[e];
+        const int64_t hiA = (int64_t)idA << 32;
+        // contacts mode: body and material ids of every contact are written beside its key (bids, per-contact material
+        // pair), so that the force kernel can start its body gathers without waiting for the shape records
+        const bool ids = mode == MODE_CONTACTS && c_bids != nullptr;
+        ShapeMeta mA = {};
+        if (ids)
+            mA = meta[idA];
         if (k <= 64) {
             unsigned long long m = ent_mask[e];
             if (CPLX && mode == MODE_CONTACTS) {
@@ -975,17 +983,25 @@ __global__ void __launch_bounds__(256) k_pair_store(const ShapeMeta* __restrict_
                 while (u) {
                     const int j = __ffsll((long long)u) - 1;
                     u &= u - 1;
-                    const int64_t key = hiA | (int64_t)ent_shape[s + j];
+                    const uint32_t idB = ent_shape[s + j];
+                    const int64_t key = hiA | (int64_t)idB;
+                    const ShapeMeta mB = meta[idB];
+                    const int2 bb = make_int2((int)mA.body, (int)mB.body);
+                    const uint32_t mm = (mA.info >> 16) | (mB.info >> 16) << 16;
                     if ((cm >> j) & 1ull) {
                         const uint32_t n = cplx_n[ci];
                         const uint32_t slot = rec[4 * (size_t)ci + 3];
                         for (uint32_t t = 0; t < n; t++) {
                             out[o] = key;
+                            reinterpret_cast<int2*>(c_bids)[o] = bb;
+                            c_mats[o] = mm;
                             c_src[o++] = slot + t + 1;
                         }
                         ci++;
                     } else {
                         out[o] = key;
+                        reinterpret_cast<int2*>(c_bids)[o] = bb;
+                        c_mats[o] = mm;
                         c_src[o++] = 0;
                     }
                 }
@@ -993,7 +1009,13 @@ __global__ void __launch_bounds__(256) k_pair_store(const ShapeMeta* __restrict_
                 while (m) {
                     const int j = __ffsll((long long)m) - 1;
                     m &= m - 1;
-                    out[o++] = hiA | (int64_t)ent_shape[s + j];
+                    const uint32_t idB = ent_shape[s + j];
+                    if (ids) {
+                        const ShapeMeta mB = meta[idB];
+                        reinterpret_cast<int2*>(c_bids)[o] = make_int2((int)mA.body, (int)mB.body);
+                        c_mats[o] = (mA.info >> 16) | (mB.info >> 16) << 16;
+                    }
+                    out[o++] = hiA | (int64_t)idB;
                 }
             }
         }
@@ -1064,6 +1086,7 @@ __global__ void __launch_bounds__(128) k_long_rows(const ShapeMeta* __restrict__
                                                    uint64_t* __restrict__ ent_cmask, uint32_t* __restrict__ ent_cnt,
                                                    const uint32_t* __restrict__ ent_off, int64_t* __restrict__ out,
                                                    uint32_t cap, uint32_t* __restrict__ c_src,
+                                                   int32_t* __restrict__ c_bids, uint32_t* __restrict__ c_mats,
                                                    const uint32_t* __restrict__ long_bins, CplxArgs X,
                                                    DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
@@ -1108,6 +1131,13 @@ __global__ void __launch_bounds__(128) k_long_rows(const ShapeMeta* __restrict__
                 if (STORE && n) {
                     uint32_t p = o + incl - n;
                     const int64_t key = hiA | (int64_t)idB;
+                    if (mode == MODE_CONTACTS && c_bids) {
+                        const ShapeMeta mB = meta[idB];
+                        for (uint32_t t = 0; t < n; t++) {
+                            reinterpret_cast<int2*>(c_bids)[p + t] = make_int2((int)A.body, (int)mB.body);
+                            c_mats[p + t] = (A.info >> 16) | (mB.info >> 16) << 16;
+                        }
+                    }
                     if (dec == 1 || mode != MODE_CONTACTS) {
                         if (CPLX && mode == MODE_CONTACTS)
                             c_src[p] = 0;
@@ -1246,8 +1276,8 @@ static int enqueue_pair_pass_t(System* S, int mode, int64_t* out, uint32_t cap) 
                                            S->d_cnt);
     k_long_rows<CPLX, false><<<dim3(8, 64), 128, 0, S->stream>>>(
         S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
-        env, algorithm, mode, S->ent_mask.p, cmask, S->ent_off.p, nullptr, nullptr, 0, nullptr, S->long_bins.p, X,
-        S->d_cnt);
+        env, algorithm, mode, S->ent_mask.p, cmask, S->ent_off.p, nullptr, nullptr, 0, nullptr, nullptr, nullptr,
+        S->long_bins.p, X, S->d_cnt);
     CB_TRY(timer_stop(S, "k_pair_masks_slow"));
     S->launches += 5;
     if (CPLX) {
@@ -1265,11 +1295,12 @@ static int enqueue_pair_pass_t(System* S, int mode, int64_t* out, uint32_t cap) 
     k_pair_store<CPLX><<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
         S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
         env, algorithm, mode, S->ent_mask.p, S->ent_off.p, out, cap, cmask, CPLX ? S->ent_cbase.p : nullptr,
-        CPLX ? S->cplx_rec.p : nullptr, CPLX ? S->cplx_n.p : nullptr, CPLX ? S->c_src.p : nullptr, X, S->d_cnt);
+        CPLX ? S->cplx_rec.p : nullptr, CPLX ? S->cplx_n.p : nullptr, CPLX ? S->c_src.p : nullptr, S->c_bids.p,
+        S->c_mats.p, X, S->d_cnt);
     k_long_rows<CPLX, true><<<dim3(8, 64), 128, 0, S->stream>>>(
         S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
         env, algorithm, mode, nullptr, nullptr, nullptr, S->ent_off.p, out, cap, CPLX ? S->c_src.p : nullptr,
-        S->long_bins.p, X, S->d_cnt);
+        S->c_bids.p, S->c_mats.p, S->long_bins.p, X, S->d_cnt);
     CB_TRY(timer_stop(S, "k_pair_store"));
     S->launches += 2;
     CB_CUDA(cudaGetLastError());

@@ -48,6 +48,20 @@ __device__ __forceinline__ BodyView load_body(uint32_t b, const double* __restri
     return B;
 }
 
+__device__ __forceinline__ BodyView load_body_nopos(uint32_t b, const double* __restrict__ rot,
+                                                    const double* __restrict__ vel, const double* __restrict__ mass) {
+    BodyView B;
+    B.pos = mk3(0);
+    const double4 q = reinterpret_cast<const double4*>(rot)[b];
+    B.rot = mkq(q.x, q.y, q.z, q.w);
+    const double2* v = reinterpret_cast<const double2*>(vel + 6 * (size_t)b);
+    const double2 v0 = v[0], v1 = v[1], v2 = v[2];
+    B.v = mk3(v0.x, v0.y, v1.x);
+    B.w = mk3(v1.y, v2.x, v2.y);
+    B.mass = mass[b];
+    return B;
+}
+
 // Contact geometry evaluated inside the force kernel (GEN): in a step nobody reads the contact records, so writing
 // them in k_contact_gen and reading them back here would be 200 bytes of traffic per contact for nothing.  The
 // records are produced on demand instead (ensure_contact_geometry, pairs.cu).
@@ -58,8 +72,6 @@ struct GenArgs {
     const uint32_t* c_src;
     const double* cplx_out;
     double sep;
-    int32_t* bids_out;
-    uint32_t* mats_out;
 };
 
 // MultiStep tangential displacement (ChSystemSMC::TangentialDisplacementModel::MultiStep): per body MAX_SHEAR history
@@ -111,6 +123,15 @@ __global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, GenArgs G, Sh
     d3 force = mk3(0), tq1 = mk3(0), tq2 = mk3(0);
     Contact C;
     uint32_t b1, b2, mm;
+    // body and material ids: written beside the key by the store pass of the collision stage (or by k_contact_gen)
+    const int2 bb = reinterpret_cast<const int2*>(bids)[i];
+    b1 = (uint32_t)bb.x, b2 = (uint32_t)bb.y;
+    mm = c_mats[i];
+    // everything the force needs from the two bodies but the position, requested before the geometry is known (an
+    // SMC contact list holds penetrating contacts almost exclusively)
+    BodyView B1 = load_body_nopos(b1, rot, vel, mass), B2 = load_body_nopos(b2, rot, vel, mass);
+    const bool hv1 = heavy[b1], hv2 = heavy[b2];
+    bool cen1 = false, cen2 = false;  // body-centred sphere: the shape's world position IS the body position
     if (GEN) {
         // DispatchPRIMS on the compacted key list, as k_contact_gen does it
         const int64_t key = G.c_shapes[i];
@@ -131,25 +152,26 @@ __global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, GenArgs G, Sh
             contact_general(sA, tA, wA, sB, tB, wB, G.sep, G.s_wrot, G.s_dims, cg);
             C.n = cg.n, C.p1 = cg.p1, C.p2 = cg.p2, C.depth = cg.depth, C.erad = cg.erad;
         }
-        b1 = mA.body, b2 = mB.body;
-        mm = (mA.info >> 16) | (mB.info >> 16) << 16;
-        reinterpret_cast<int2*>(G.bids_out)[i] = make_int2((int)b1, (int)b2);
-        G.mats_out[i] = mm;
+        cen1 = (mA.info & 4u) != 0, cen2 = (mB.info & 4u) != 0;
+        if (cen1)
+            B1.pos = mk3(wA.x, wA.y, wA.z);
+        if (cen2)
+            B2.pos = mk3(wB.x, wB.y, wB.z);
     } else {
         C.depth = c_depth[i];
-        b1 = (uint32_t)bids[2 * i], b2 = (uint32_t)bids[2 * i + 1];
-        mm = c_mats[i];
     }
     const double depth = C.depth;
     // body -> contact incidence counts (first half of the counting sort by body that replaces the reference's
     // sort_by_key, ...SMC.cpp:702-703)
-    if (!heavy[b1])
+    if (!hv1)
         atomicAdd(&deg[b1], 1u);
-    if (!heavy[b2])
+    if (!hv2)
         atomicAdd(&deg[b2], 1u);
     if (depth < 0) {
-        const BodyView B1 = load_body(b1, pos, rot, vel, mass);
-        const BodyView B2 = load_body(b2, pos, rot, vel, mass);
+        if (!cen1)
+            B1.pos = mk3(pos[3 * b1], pos[3 * b1 + 1], pos[3 * b1 + 2]);
+        if (!cen2)
+            B2.pos = mk3(pos[3 * b2], pos[3 * b2 + 1], pos[3 * b2 + 2]);
         if (!GEN) {
             C.n = mk3(c_norm[3 * i], c_norm[3 * i + 1], c_norm[3 * i + 2]);
             C.p1 = mk3(c_pta[3 * i], c_pta[3 * i + 1], c_pta[3 * i + 2]);
@@ -472,6 +494,47 @@ struct UpdArgs {
     const double *mass, *inertia, *vel, *fapp;
 };
 
+// F, T (+)= the record of incidence `code` (contact << 1 | side): force on body 2 of the contact (body 1 gets the
+// negative), torque on the coded side
+__device__ __forceinline__ void add_record(const double* __restrict__ ct_force, uint32_t code, bool first, d3& F, d3& T) {
+    const double4* rec = reinterpret_cast<const double4*>(ct_force + CT_STRIDE * (size_t)(code >> 1));
+    const double4 f4 = rec[0], t4 = rec[1 + (code & 1u)];
+    const d3 f = mk3(f4.x, f4.y, f4.z);
+    if (first) {
+        F = (code & 1u) ? f : -f;
+        T = mk3(t4.x, t4.y, t4.z);
+    } else {
+        F = F + ((code & 1u) ? f : -f);
+        T = T + mk3(t4.x, t4.y, t4.z);
+    }
+}
+
+// Batcher's odd-even merge sort as a fixed network over registers (N a power of two; all indices are compile-time)
+template <int N>
+__device__ __forceinline__ void reduce_sorted(const uint32_t* __restrict__ codes, uint32_t d,
+                                              const double* __restrict__ ct_force, d3& F, d3& T) {
+    uint32_t c[N];
+#pragma unroll
+    for (int k = 0; k < N; k++)
+        c[k] = (uint32_t)k < d ? codes[k] : 0xffffffffu;
+#pragma unroll
+    for (int p = 1; p < N; p <<= 1)
+#pragma unroll
+        for (int k = p; k >= 1; k >>= 1)
+#pragma unroll
+            for (int j = k % p; j + k < N; j += 2 * k)
+#pragma unroll
+                for (int i = 0; i < k; i++)
+                    if (i + j + k < N && (i + j) / (2 * p) == (i + j + k) / (2 * p)) {
+                        const uint32_t lo = min(c[i + j], c[i + j + k]), hi = max(c[i + j], c[i + j + k]);
+                        c[i + j] = lo, c[i + j + k] = hi;
+                    }
+#pragma unroll
+    for (int r = 0; r < N; r++)
+        if ((uint32_t)r < d)
+            add_record(ct_force, c[r], r == 0, F, T);
+}
+
 // one thread per body: add the body's contacts in ascending contact index, then hf += h * (F, T)
 template <bool UPD>
 __global__ void __launch_bounds__(256) k_body_reduce(uint32_t nb, const uint8_t* __restrict__ heavy,
@@ -508,26 +571,24 @@ __global__ void __launch_bounds__(256) k_body_reduce(uint32_t nb, const uint8_t*
     if (b < nb && !heavy[b]) {
         const uint32_t s = off[b], d = off[b + 1] - s;
         d3 F = mk3(0), T = mk3(0);
-        // selection walk: next smallest code each round (d is ~6..12 for sphere beds; lists sit in L1)
-        uint32_t last = 0;
-        for (uint32_t r = 0; r < d; r++) {
-            uint32_t best = 0xffffffffu;
-            for (uint32_t k = 0; k < d; k++) {
-                const uint32_t c = inc[s + k];
-                if ((r == 0 || c > last) && c < best)
-                    best = c;
-            }
-            last = best;
-            const uint32_t ci = best >> 1, side = best & 1u;
-            const double4* rec = reinterpret_cast<const double4*>(ct_force + CT_STRIDE * (size_t)ci);
-            const double4 f4 = rec[0], t4 = rec[1 + side];
-            const d3 f = mk3(f4.x, f4.y, f4.z);
-            if (r == 0) {
-                F = side ? f : -f;
-                T = mk3(t4.x, t4.y, t4.z);
-            } else {
-                F = F + (side ? f : -f);
-                T = T + mk3(t4.x, t4.y, t4.z);
+        // ascending contact code == the order the reference's stable sort leaves.  Up to 16 incidences (every sphere
+        // of a bed): the codes are read once, sorted in registers by a fixed network, and the records gathered with
+        // constant register indices (the compiler keeps several gathers in flight).  Longer lists: selection walk.
+        if (d <= 8)
+            reduce_sorted<8>(inc + s, d, ct_force, F, T);
+        else if (d <= 16)
+            reduce_sorted<16>(inc + s, d, ct_force, F, T);
+        else {
+            uint32_t last = 0;
+            for (uint32_t r = 0; r < d; r++) {
+                uint32_t best = 0xffffffffu;
+                for (uint32_t k = 0; k < d; k++) {
+                    const uint32_t c = inc[s + k];
+                    if ((r == 0 || c > last) && c < best)
+                        best = c;
+                }
+                last = best;
+                add_record(ct_force, best, r == 0, F, T);
             }
         }
         double* o = b_force + 6 * (size_t)b;
@@ -585,10 +646,18 @@ __global__ void __launch_bounds__(256) k_heavy_partial(const int32_t* __restrict
         const uint32_t body = list[hI];
         double acc[7] = {0, 0, 0, 0, 0, 0, 0};
         const uint32_t c0 = chunk * HEAVY_CHUNK;
+        // all body-id pairs of the thread first (16 independent coalesced loads), then the few matching records
+        int2 bb[HEAVY_CHUNK / 256];
+#pragma unroll
+        for (int k = 0; k < HEAVY_CHUNK / 256; k++) {
+            const uint32_t c = c0 + k * 256 + threadIdx.x;
+            bb[k] = c < nc ? reinterpret_cast<const int2*>(bids)[c] : make_int2(-1, -1);
+        }
+#pragma unroll
         for (int k = 0; k < HEAVY_CHUNK / 256; k++) {
             const uint32_t c = c0 + k * 256 + threadIdx.x;
             if (c < nc) {
-                const uint32_t b1 = (uint32_t)bids[2 * c], b2 = (uint32_t)bids[2 * c + 1];
+                const uint32_t b1 = (uint32_t)bb[k].x, b2 = (uint32_t)bb[k].y;
                 const double* rec = ct_force + CT_STRIDE * (size_t)c;
                 if (b1 == body) {
                     acc[0] -= rec[0], acc[1] -= rec[1], acc[2] -= rec[2];
@@ -755,7 +824,7 @@ int enqueue_smc(System* S) {
     GenArgs G;
     G.c_shapes = S->c_shapes.p, G.meta = S->s_meta.p, G.s_wpos = S->s_wpos.p, G.s_wrot = S->s_wrot.p;
     G.s_dims = S->s_dims.p, G.c_src = use_complex(S) ? S->c_src.p : nullptr, G.cplx_out = S->cplx_out.p;
-    G.sep = 2 * S->set.collision_envelope, G.bids_out = S->c_bids.p, G.mats_out = S->c_mats.p;
+    G.sep = 2 * S->set.collision_envelope;
     const bool gen = !S->contacts_geom_valid;  // the step skipped k_contact_gen: evaluate the geometry here
 #define SMC_LAUNCH2(FM, UM, GN, MS)                                                                       \
     k_smc_force<FM, UM, GN, MS><<<fgrid, 128, 0, S->stream>>>(                                            \

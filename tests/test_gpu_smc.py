@@ -240,3 +240,33 @@ def test_multistep_graph_replay_equals_single_steps():
         b.DoStepDynamics()
     for x, y in zip(a.GetBodyState(), b.GetBodyState()):
         assert np.array_equal(x, y)
+
+
+def test_contacts_after_graph_replay_are_current(monkeypatch):
+    """A contact download between graph-replayed steps returns the records of the LAST step's key list (the records are
+    produced on demand from the collision stage's shape records, which the next step's preparation must not touch),
+    and stepping through the graph equals stepping without it bit for bit."""
+    def run(no_graph):
+        if no_graph:
+            monkeypatch.setenv("CB200_NO_GRAPH", "1")
+        else:
+            monkeypatch.delenv("CB200_NO_GRAPH", raising=False)
+        scene = scenes.settling_smc(14, 14, 5, spacing_factor=1.98, jitter_factor=0.03)
+        s = cw.load_scene(cw.ChSystemMulticoreSMC(), scene)
+        out = []
+        for n in (12, 1, 9):
+            s.DoSteps(n)
+            k = s.GetContacts()
+            out.append({key: np.array(v, copy=True) for key, v in k.items()})
+            out.append(s.GetBodyState())
+        return out
+
+    a, b = run(False), run(True)
+    for x, y in zip(a, b):
+        if isinstance(x, dict):
+            assert x["depth"].size > 0
+            for key in x:
+                assert np.array_equal(x[key], y[key]), key
+        else:
+            for u, v in zip(x, y):
+                assert np.array_equal(u, v)
