@@ -45,6 +45,8 @@ def measured_peak_gbs():
 def make_scene(args, rank=0, world=1):
     from chrono_wisc_b200 import scenes
 
+    if args.config == "mixed":
+        return scenes.mixed_bed(args.mixed_nx, args.mixed_ny, args.mixed_nz)
     # near-touching jittered lattice: the bed forms its contact network within the settle window
     if args.bin_edge > 0:  # FIXED_BIN_SIZE, cubic bins of --bin-edge sphere diameters
         return scenes.settling_smc(args.nx, args.ny, args.nz, seed=12345 + rank, spacing_factor=args.spacing,
@@ -121,31 +123,48 @@ def algorithmic_bytes(nb, c):
             c.num_rigid_contacts * 192 + nb * 96)
 
 
-KERNEL_TIMERS = ("k_pair_masks", "k_smc_force", "k_body_reduce", "k_contact_gen", "k_pair_store", "k_bin_sort")
-
-
-def kernel_rooflines(sys_, nb, c, peak):
-    """Per-kernel roofline entries for the heaviest kernels: live CUDA-event durations (events around the launch, on
-    the library stream, in the directly enqueued steps of the timed region) against each kernel's own share of the
-    SURVEY.md 8(d) algorithmic bytes.  `traffic` = DRAM bytes per launch from the committed
-    ncu --set full capture (profiles/r1_traffic.json), when the capture holds that kernel."""
-    ni, np_, nc = c.num_bin_aabb_intersections, c.num_possible_collisions, c.num_rigid_contacts
-    alg = {
-        "k_pair_masks": ni * 16 + np_ * 16,          # entries read; the pair list it decides but never materialises
-        # pair key + two shape poses (centre, radius) + two body states in; body/material ids, force, torques out
-        # (the contact geometry is evaluated in the kernel, no contact record is read in the step)
-        "k_smc_force": nc * (8 + 2 * 32 + 2 * 112 + 16 + 72),
-        "k_body_reduce": nb * 96 + nc * 2 * 56,      # per-body accumulators + (index, force, torque) per incidence
-        "k_contact_gen": nc * (8 + 96),              # key in, contact record out
-        "k_pair_store": ni * 16 + nc * 8,            # masks + offsets in, keys out
-        "k_bin_sort": ni * 16,                       # (bin, shape) key/value moved once
+def kernel_algorithmic_bytes(nb, ns, c):
+    """Per-kernel algorithmic bytes: what the kernel must move given its inputs and outputs, unpadded, every logical
+    array once (a body or shape record gathered by many contacts counts once per body).  DESIGN.md
+    section 4 has the same table."""
+    ni, nc = c.num_bin_aabb_intersections, c.num_rigid_contacts
+    return {
+        "k_bin_count": ns * (32 + 16 + 4),                    # shape world record + integer record in, bins touched out
+        "k_bin_fill": ns * (32 + 16 + 4) + ni * 8,            # same in, (shape, bin) per entry out
+        "k_pair_masks": ni * 8 + ns * 48 + ni * (4 + 8 + 4),  # entries in, shape records once, sorted id + mask + count out
+        "k_pair_queue": 0,                                    # wall-bin pairs: latency-bound, no streaming term of its own
+        "k_pair_store": ni * (8 + 4 + 4 + 4) + ns * 16 + nc * (8 + 8 + 4),  # mask, offset, id, bin in; key, body ids, materials out
+        "k_smc_force": nc * (8 + 8 + 4) + ns * (32 + 16) + nb * (32 + 48 + 8) + nc * 96,  # keys/ids in, shape + body state once, record out
+        "k_inc_fill": nc * 8 + nb * 4 + nc * 8,               # body ids + offsets in, two incidence codes out
+        "k_body_reduce": nc * (96 + 8) + nb * (4 + 48 + 8 + 24) + nb * 96,  # records + codes in, body state in, sums + hf out
+        "k_integrate": nb * (48 + 48 + 24 + 32 + 8 + 24 + 1) + nb * 104 + nb * (4 + 8 + 32),  # + the next step's sphere records
+        "k_contact_gen": nc * (8 + 96),
     }
-    traffic = {}
-    try:
-        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")) as f:
-            traffic = json.load(f).get("dram_bytes_per_launch", {})
-    except Exception:
-        pass
+
+
+KERNEL_TIMERS = ("k_bin_count", "k_bin_fill", "k_pair_masks", "k_pair_queue", "k_pair_store", "k_smc_force", "k_inc_fill",
+                 "k_body_reduce", "k_integrate", "k_contact_gen")
+
+
+def load_traffic():
+    """DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of this round's build, from the committed
+    ncu --set full capture (profiles/r2_traffic.json; tools/ncu_traffic.py makes it)."""
+    for name in ("r2_traffic.json",):
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as f:
+                return json.load(f).get("dram_bytes_per_launch", {}), name
+        except Exception:
+            pass
+    return {}, None
+
+
+def kernel_rooflines(sys_, nb, ns, c, peak):
+    """Per-kernel roofline entries: live CUDA-event durations (events around the launch, on the library stream, in the
+    directly enqueued steps of the timed region) against each kernel's algorithmic bytes.  `traffic` = measured DRAM
+    bytes per launch (ncu); algorithmic bytes above the measured traffic would claim bandwidth DRAM never delivered, so
+    `achieved` then uses the traffic and the entry says so."""
+    alg = kernel_algorithmic_bytes(nb, ns, c)
+    traffic, src = load_traffic()
     out = {}
     for k in KERNEL_TIMERS:
         try:
@@ -154,30 +173,63 @@ def kernel_rooflines(sys_, nb, c, peak):
             continue
         if ms <= 0:
             continue
-        a = alg[k] / (ms * 1e-3) / 1e9
-        out[k] = {"ms": ms, "algorithmic_bytes": alg[k], "achieved": a, "frac": a / peak, "traffic": traffic.get(k)}
-    return out
+        t = traffic.get(k)
+        used = alg[k]
+        capped = t is not None and used > t
+        if capped:
+            used = t
+        a = used / (ms * 1e-3) / 1e9
+        out[k] = {"ms": ms, "algorithmic_bytes": alg[k], "achieved": a, "frac": a / peak, "traffic": t,
+                  "capped_to_traffic": capped}
+    return out, src
 
 
-def cpu_baseline_sample(scene, seconds_budget=20.0):
-    """Oracle ("port": oracle/liboracle.so, OpenMP over the host cores) on a bounded sample: the same bed state,
-    as many whole steps as fit the budget (at least 1)."""
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def ref_cpu_steps(scene, state, n_settle, n_warm, n_steps, seconds):
+    """The reference's CPU path on the host cores ("_ref+glue": oracle/_ref = the reference's own collision translation
+    units + its extracted force function under the reference's OpenMP loop + Thrust-OMP sort/reduce, restated glue for
+    the Eigen/ChBody parts; oracle/ref_driver.cpp ref_smc_step).  Bounded: the step counts shrink to the time budget."""
     from oracle import pyoracle
 
-    orc = pyoracle.Oracle(scene)
-    cores = orc.max_threads()
-    orc.set_threads(cores)
-    nb = scene["mass"].size
+    ref = pyoracle.Ref()
+    cores = host_threads()
+    ref.set_num_threads(cores)  # (torchrun exports OMP_NUM_THREADS=1: the arm sets its own team size)
+    sc = dict(scene)
+    if state is not None:
+        sc["pos"], sc["rot"], sc["vel"] = state
+    ref.smc_setup(sc)
     t0 = time.time()
-    orc.step(1)
-    t1 = time.time() - t0
-    n = int(max(1, min(50, seconds_budget / max(t1, 1e-6) - 1)))
+    ref.smc_step(1)
+    t1 = max(time.time() - t0, 1e-6)
+    settle = int(max(0, min(n_settle, 0.35 * seconds / t1 - 1)))
+    warm = int(max(1, min(n_warm, 0.15 * seconds / t1)))
+    steps = int(max(2, min(n_steps, 0.5 * seconds / t1)))
+    ref.smc_step(settle)
+    ref.smc_step(warm)
+    ref.smc_setup(dict(sc, **dict(zip(("pos", "rot", "vel"), ref.smc_state()))))  # (resets the phase timers)
     t0 = time.time()
-    orc.step(n)
+    ref.smc_step(steps)
     dt = time.time() - t0
-    return {"value": nb * n / dt, "unit": METRIC, "cores": cores, "kind": "port",
-            "sample": f"{n} steps of the same {nb}-body bed state (oracle/liboracle.so, OpenMP {cores} threads), "
-                      f"{dt / n * 1e3:.1f} ms/step", "ms_per_step": dt / n * 1e3}
+    nb = scene["mass"].size
+    phases = {k: v * 1e3 for k, v in ref.smc_timers().items()}
+    cn = ref.counts()
+    return {"value": nb * steps / dt, "unit": METRIC, "cores": cores, "kind": "_ref+glue", "ms_per_step": dt / steps * 1e3,
+            "phase_ms": phases, "steps": steps, "settle_steps": 1 + settle + warm, "N_c": cn["N_c"], "N_p": cn["N_p"],
+            "N_i": cn["N_i"]}
+
+
+def cpu_baseline_sample(scene, state, seconds_budget=25.0):
+    r = ref_cpu_steps(scene, state, 0, 1, 20, seconds_budget)
+    r["sample"] = (f"{r['steps']} steps from the same {scene['mass'].size}-body bed state as the timed window "
+                   f"(reference collision TUs + extracted force function + Thrust-OMP accumulation, OpenMP {r['cores']} "
+                   f"threads), {r['ms_per_step']:.0f} ms/step")
+    return r
 
 
 def run_reference(args):
@@ -185,48 +237,96 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from oracle import pyoracle
-
+    if args.config == "nsc":
+        return run_reference_nsc(args)
     scene = make_scene(args)
-    # the reference arm times a bounded sample: a bed of --ref-nx x --ref-ny x nz spheres (same materials, spacing,
-    # grid rule and step) so that W + K steps end within minutes on the host cores
-    small = dict(vars(args))
-    sargs = argparse.Namespace(**small)
-    sargs.nx, sargs.ny = args.ref_nx, args.ref_ny
-    scene = make_scene(sargs)
     nb = scene["mass"].size
-    orc = pyoracle.Oracle(scene)
-    cores = orc.max_threads()
-    orc.set_threads(cores)
-    orc.step(min(args.settle, args.ref_settle))
-    orc.step(args.warmup)
-    t0 = time.time()
-    orc.step(args.steps)
-    dt = time.time() - t0
-    value = nb * args.steps / dt
-    sample = (f"{args.steps} steps of a {sargs.nx}x{sargs.ny}x{sargs.nz} = {nb - 1}-sphere bed (same materials/grid rule "
-              f"as the {args.nx}x{args.ny}x{args.nz} workload), oracle/liboracle.so OpenMP {cores} threads")
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+    r = ref_cpu_steps(scene, None, args.settle, args.warmup, args.steps, args.ref_seconds)
+    sample = (f"{r['steps']} timed steps after {r['settle_steps']} settle + warm-up steps of the SAME {workload_name(args)} bed "
+              f"(step counts bounded by --ref-seconds {args.ref_seconds:.0f}; N_c = {r['N_c']} in the window), "
+              f"reference collision TUs + extracted function_CalcContactForces + Thrust-OMP sort/reduce + restated glue, "
+              f"OpenMP {r['cores']} threads")
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": METRIC, "n_gpus": args.gpus,
+            "steps": r["steps"], "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(args, None, nb),
-            "cpu_baseline": {"value": value, "unit": METRIC, "cores": cores, "kind": "port", "sample": sample},
-            "e2e": {"value": value, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "config": dict(workload_config(args, None, nb), N_i=r["N_i"], N_p=r["N_p"], N_c=r["N_c"]),
+            "cpu_baseline": {"value": r["value"], "unit": METRIC, "cores": r["cores"], "kind": "_ref+glue", "sample": sample,
+                             "phase_ms": r["phase_ms"]},
+            "e2e": {"value": r["value"], "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
 
 
+def run_reference_nsc(args):
+    """configs[3] on the host cores.  The NSC linear algebra of the reference is Eigen (absent here), so this
+    arm is the CPU restatement (oracle/liboracle.so, kind "port") over the same scene."""
+    from chrono_wisc_b200 import scenes
+    from oracle import pyoracle
+
+    scene = scenes.balls_nsc(args.nsc_nx, args.nsc_ny, args.nsc_nz, iterations=args.nsc_iters)
+    nb = scene["mass"].size
+    orc = pyoracle.Oracle(scene)
+    cores = host_threads()
+    orc.set_threads(cores)
+    t0 = time.time()
+    orc.step(1)
+    t1 = max(time.time() - t0, 1e-6)
+    steps = int(max(1, min(args.steps, 0.6 * args.ref_seconds / t1)))
+    t0 = time.time()
+    orc.step(steps)
+    dt = time.time() - t0
+    value = nb * steps / dt
+    sample = (f"{steps} steps of the same {nb - 1}-sphere NSC bed, APGD {args.nsc_iters} iterations/step, CPU restatement "
+              f"(Eigen absent: the reference's own NSC code cannot be built), OpenMP {cores} threads")
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": args.gpus, "steps": steps,
+            "warmup": 1, "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": nsc_config(args, nb, None),
+            "cpu_baseline": {"value": value, "unit": METRIC, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def workload_name(args):
+    if args.config == "mixed":
+        return f"{args.mixed_nx}x{args.mixed_ny}x{args.mixed_nz} mixed sphere/box/capsule"
+    return f"{args.nx}x{args.ny}x{args.nz} = {args.nx * args.ny * args.nz}-sphere"
+
+
 def workload_config(args, counts, nb):
-    cfg = {"workload": f"{args.nx}x{args.ny}x{args.nz} = {args.nx * args.ny * args.nz} monodisperse spheres r=0.02, "
-                       "Hertz SMC settling in a 5-wall box, FP64, h=1e-3, " +
-                       (f"FIXED_BIN_SIZE {args.bin_edge} diameters" if args.bin_edge > 0 else
-                        "FIXED_DENSITY 5 shapes/bin") + " (BASELINE.json configs[1])",
-           "bodies_per_gpu": nb, "settle_steps": args.settle,
+    if args.config == "mixed":
+        wl = (f"{args.mixed_nx}x{args.mixed_ny}x{args.mixed_nz} = {nb - 1} bodies, one third spheres r=0.1 / boxes "
+              "(0.1,0.08,0.06) / capsules r=0.06, Hertz SMC, E=2e5, mu=0.4, cr=0.1, settling in a 5-wall box, HYBRID "
+              "narrowphase (PRIMS + MPR), FP64, h=1e-3, FIXED_BIN_SIZE 3 radii (BASELINE.json configs[4] without the "
+              "motor-driven blade)")
+    else:
+        wl = (f"{args.nx}x{args.ny}x{args.nz} = {args.nx * args.ny * args.nz} monodisperse spheres r=0.02 on a jittered "
+              f"lattice (spacing {args.spacing} r, jitter 0.005 r, seed 12345), Hertz SMC settling in a 5-wall box, FP64, "
+              "h=1e-3, " + (f"FIXED_BIN_SIZE {args.bin_edge} diameters" if args.bin_edge > 0 else
+                            "FIXED_DENSITY 5 shapes/bin") + " (BASELINE.json configs[1])")
+    cfg = {"workload": wl, "bodies_per_gpu": nb, "settle_steps": args.settle,
            "l2": "inputs larger than L2 (body+contact state >> 126 MB); no flush needed"}
     if counts is not None:
         cfg.update({"N_i": counts.num_bin_aabb_intersections, "N_p": counts.num_possible_collisions,
                     "N_c": counts.num_rigid_contacts, "bins": list(counts.bins_per_axis)})
     return cfg
+
+
+def nsc_config(args, nb, counts):
+    cfg = {"workload": f"{args.nsc_nx}x{args.nsc_ny}x{args.nsc_nz} = {nb - 1} spheres r=0.15, m=1, mu=0.4, envelope 0.01, "
+                       f"NSC DVI, SLIDING, alpha=0, recovery speed 1e4, APGD exactly {args.nsc_iters} iterations/step, "
+                       "h=1e-2, FIXED_DENSITY 5 shapes/bin (BASELINE.json configs[3], demo_MCORE_ballsNSC-style)",
+           "bodies_per_gpu": nb, "settle_steps": args.nsc_settle,
+           "l2": "the iteration's working set (contact frames + vectors) is larger than L2 at this size"}
+    if counts is not None:
+        cfg.update({"N_c": counts.num_rigid_contacts, "iterations": counts.solver_iterations,
+                    "residual": counts.solver_residual})
+    return cfg
+
+
+def kinetic_energy_per_particle(scene, vel):
+    m, I = scene["mass"][1:], scene["inertia"][1:]
+    v = vel[1:]
+    return float((0.5 * m * (v[:, :3] ** 2).sum(1) + 0.5 * (I * v[:, 3:] ** 2).sum(1)).mean())
 
 
 def run_b200(args):
@@ -251,16 +351,29 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     lib = _lib.load()
+    if args.config == "nsc":
+        return run_b200_nsc(args, rank, world, local, barrier)
     if world > 1:
+        if args.config != "smc":
+            raise SystemExit("bench.py: --config mixed is a single-GPU workload")
         return run_b200_slabs(args, rank, world, local, barrier)
     scene = make_scene(args, rank, world)
-    nb = scene["mass"].size
+    nb, ns = scene["mass"].size, scene["shape_type"].size
     sys_ = cw.load_scene(cw.ChSystemMulticoreSMC(local), scene)
-    sys_.DoSteps(args.settle)
+
+    # ---- window 1: the falling / colliding transient, from step 0 --------------------------------
+    sys_.DoSteps(args.warmup)
+    sys_.Synchronize()
+    n_tr = max(1, min(args.steps, args.settle))
+    sys_.DoSteps(n_tr)
+    sys_.Synchronize()
+    tr_ms = sys_.GetTimer("do_steps") * 1e3
+    tr_counts = sys_.GetCounts()
+    sys_.DoSteps(max(0, args.settle - n_tr))
     sys_.DoSteps(args.warmup)
     sys_.Synchronize()
 
-    # ---- device-resident timed region: K steps, CUDA events on the library's own stream ("step" timer) ----------
+    # ---- window 2, the headline: K steps of the contact-rich bed, CUDA events on the library's own stream --------
     sampler = ClockSampler(local)
     sampler.start()
     l0 = sys_.KernelLaunches()
@@ -276,12 +389,7 @@ def run_b200(args):
     counts = sys_.GetCounts()
     stage_ms = {n: sys_.GetTimer(n) * 1e3 for n in ("update", "collision_broad", "collision_narrow", "advance",
                                                    "integrate")}
-    # the job's time is the slowest rank's device time over the K steps (CUDA events, host sync gaps included)
-    t = torch.tensor([dev_ms, wall], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms, wall = float(t[0].item()), float(t[1].item())
-    value = nb * world * args.steps / (dev_ms * 1e-3 * args.steps)
+    value = nb * args.steps / (dev_ms * 1e-3 * args.steps)
 
     # ---- e2e: same steps through the public API with HOST state: upload pose+velocity, step, download ----------
     n_e2e = max(1, min(args.steps, args.e2e_steps))
@@ -303,45 +411,145 @@ def run_b200(args):
         sys_.StepHost(hp, hq, hv)  # cb200_step_host: H2D pose + velocity, one step, D2H pose + velocity
     barrier()
     e2e_wall = time.perf_counter() - t0
-    t = torch.tensor([e2e_wall], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = nb * world * n_e2e / float(t.item())
+    e2e_value = nb * n_e2e / e2e_wall
     for p in pin:
         lib.cb200_host_free(p)
 
-    if rank == 0:
-        peak, peak_kind = measured_peak_gbs()
-        bytes_step = algorithmic_bytes(nb, counts)
-        achieved = bytes_step / (dev_ms * 1e-3) / 1e9
-        line = {
-            "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": dev_ms, "wall_ms_per_step": wall / args.steps * 1e3, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(args, counts, nb),
-            "stage_ms": stage_ms, "clocks": clocks,
-            "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": nb * 13 * 8,
-                    "d2h_bytes_per_step": nb * 13 * 8, "steps": n_e2e},
-            "gpu_launches": int(launches),
-            "roofline_step": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                              "frac": achieved / peak, "peak_kind": peak_kind, "kernel": "whole step (all kernels)",
-                              "algorithmic_bytes_per_step": bytes_step},
-        }
-        kr = kernel_rooflines(sys_, nb, counts, peak)
-        line["kernels"] = kr
-        if kr:
-            dom = max(kr, key=lambda k: kr[k]["ms"])
-            line["roofline"] = {"bound": "hbm", "achieved": kr[dom]["achieved"], "peak": peak, "unit": "GB/s",
-                                "frac": kr[dom]["frac"], "traffic": kr[dom]["traffic"], "peak_kind": peak_kind,
-                                "kernel": dom, "ms_per_launch": kr[dom]["ms"],
-                                "algorithmic_bytes_per_launch": kr[dom]["algorithmic_bytes"]}
-        else:
-            line["roofline"] = dict(line["roofline_step"], traffic=None)
-        if world == 1 and not args.no_cpu:
-            line["cpu_baseline"] = cpu_baseline_sample(dict(scene, pos=p0, rot=q0, vel=v0), args.cpu_seconds)
-        print(json.dumps(line))
+    peak, peak_kind = measured_peak_gbs()
+    bytes_step = algorithmic_bytes(nb, counts)
+    achieved = bytes_step / (dev_ms * 1e-3) / 1e9
+    ke = kinetic_energy_per_particle(scene, v0)
+    line = {
+        "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dev_ms, "wall_ms_per_step": wall / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, counts, nb),
+        "windows": {
+            "transient": {"steps": f"{args.warmup}..{args.warmup + n_tr}", "ms_per_step": tr_ms,
+                          "value": nb / (tr_ms * 1e-3), "N_c": tr_counts.num_rigid_contacts},
+            "timed": {"steps": f"{2 * args.warmup + args.settle}..{2 * args.warmup + args.settle + args.steps}",
+                      "ms_per_step": dev_ms, "N_c": counts.num_rigid_contacts, "ke_per_particle_J": ke,
+                      "settled_by_SURVEY_8d_criterion": bool(ke < 1e-9)}},
+        "stage_ms": stage_ms,
+        "stage_ms_note": "stage and kernel timers are CUDA-event pairs of the directly enqueued (non-graph) steps only, "
+                         "one per 64-step chunk; ms_per_step covers all K steps, graph replays included",
+        "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": nb * 13 * 8,
+                "d2h_bytes_per_step": nb * 13 * 8, "steps": n_e2e},
+        "gpu_launches": int(launches),
+        "roofline_step": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                          "frac": achieved / peak, "peak_kind": peak_kind, "kernel": "whole step (all kernels)",
+                          "algorithmic_bytes_per_step": bytes_step},
+    }
+    kr, traffic_src = kernel_rooflines(sys_, nb, ns, counts, peak)
+    line["kernels"] = kr
+    line["kernels_traffic_source"] = traffic_src
+    if kr:
+        dom = max(kr, key=lambda k: kr[k]["ms"])
+        line["roofline"] = {"bound": "hbm", "achieved": kr[dom]["achieved"], "peak": peak, "unit": "GB/s",
+                            "frac": kr[dom]["frac"], "traffic": kr[dom]["traffic"], "peak_kind": peak_kind,
+                            "kernel": dom, "ms_per_launch": kr[dom]["ms"],
+                            "algorithmic_bytes_per_launch": kr[dom]["algorithmic_bytes"]}
+    else:
+        line["roofline"] = dict(line["roofline_step"], traffic=None)
+    if not args.no_cpu:
+        line["cpu_baseline"] = cpu_baseline_sample(scene, (p0, q0, v0), args.cpu_seconds)
+    print(json.dumps(line))
+
+
+def run_b200_nsc(args, rank, world, local, barrier):
+    """BASELINE.json configs[3]: NSC DVI ball bed, APGD with a fixed iteration count per step."""
+    import chrono_wisc_b200 as cw
+    from chrono_wisc_b200 import _lib, scenes
+
     if world > 1:
-        dist.destroy_process_group()
+        return run_b200_nsc_slabs(args, rank, world, local, barrier)
+    lib = _lib.load()
+    scene = scenes.balls_nsc(args.nsc_nx, args.nsc_ny, args.nsc_nz, iterations=args.nsc_iters)
+    nb = scene["mass"].size
+    sys_ = cw.load_scene(cw.ChSystemMulticoreNSC(local), scene)
+    sys_.DoSteps(args.nsc_settle)
+    sys_.DoSteps(min(args.warmup, 5))
+    sys_.Synchronize()
+    sampler = ClockSampler(local)
+    sampler.start()
+    steps = max(1, min(args.steps, args.nsc_steps))
+    l0 = sys_.KernelLaunches()
+    barrier()
+    t0 = time.perf_counter()
+    sys_.DoSteps(steps)
+    sys_.Synchronize()
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.result()
+    launches = sys_.KernelLaunches() - l0
+    dev_ms = sys_.GetTimer("do_steps") * 1e3
+    counts = sys_.GetCounts()
+    adv_ms = sys_.GetTimer("advance") * 1e3
+    nc, it = counts.num_rigid_contacts, max(1, counts.solver_iterations)
+    # e2e: host pose + velocity in, one step, out
+    pin = []
+
+    def pinned(shape):
+        n = int(np.prod(shape)) * 8
+        p = C.c_void_p()
+        _lib.check(lib.cb200_host_alloc(n, C.byref(p)))
+        pin.append(p)
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_double)), shape=(int(np.prod(shape)),)).reshape(shape)
+
+    hp, hq, hv = pinned((nb, 3)), pinned((nb, 4)), pinned((nb, 6))
+    p0, q0, v0 = sys_.GetBodyState()
+    hp[:], hq[:], hv[:] = p0, q0, v0
+    n_e2e = max(1, min(steps, 5))
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(n_e2e):
+        sys_.StepHost(hp, hq, hv)
+    barrier()
+    e2e_value = nb * n_e2e / (time.perf_counter() - t0)
+    for p in pin:
+        lib.cb200_host_free(p)
+    peak, peak_kind = measured_peak_gbs()
+    # SURVEY 8(d): per APGD iteration 2 Schur products + the fused vector algebra; per step the setup on top
+    bytes_it = 2 * (nc * (2 * 144 + 48) + nb * 96) + 240 * nc
+    bytes_step = it * bytes_it + nc * (96 + 144 + 72)
+    ach_it = bytes_it / (adv_ms * 1e-3 / it) / 1e9
+    line = {"metric": METRIC, "value": nb * steps / (dev_ms * 1e-3 * steps), "unit": METRIC, "n_gpus": 1, "steps": steps,
+            "warmup": min(args.warmup, 5), "ms_per_step": dev_ms, "wall_ms_per_step": wall / steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": nsc_config(args, nb, counts), "clocks": clocks,
+            "stage_ms": {n: sys_.GetTimer(n) * 1e3 for n in ("update", "collision_broad", "collision_narrow", "advance",
+                                                           "integrate")},
+            "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": nb * 13 * 8, "d2h_bytes_per_step": nb * 13 * 8,
+                    "steps": n_e2e},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": ach_it, "peak": peak, "unit": "GB/s", "frac": ach_it / peak,
+                         "traffic": None, "peak_kind": peak_kind,
+                         "kernel": "one APGD iteration (k_nsc_scatter/gather x2 + fused vector kernels)",
+                         "us_per_iteration": adv_ms * 1e3 / it, "algorithmic_bytes_per_iteration": bytes_it},
+            "roofline_step": {"bound": "hbm", "achieved": bytes_step / (dev_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                              "frac": bytes_step / (dev_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_step": bytes_step}}
+    if not args.no_cpu:
+        from oracle import pyoracle
+
+        orc = pyoracle.Oracle(dict(scene, pos=p0, rot=q0, vel=v0))
+        cores = host_threads()
+        orc.set_threads(cores)
+        t0 = time.time()
+        orc.step(1)
+        t1 = time.time() - t0
+        n = int(max(1, min(5, args.cpu_seconds / max(t1, 1e-6) - 1)))
+        t0 = time.time()
+        orc.step(n)
+        dt = time.time() - t0
+        line["cpu_baseline"] = {"value": nb * n / dt, "unit": METRIC, "cores": cores, "kind": "port",
+                                "sample": f"{n} steps of the same bed state, CPU restatement of the NSC path (Eigen absent), "
+                                          f"OpenMP {cores} threads, {dt / n * 1e3:.0f} ms/step"}
+    print(json.dumps(line))
+
+
+def run_b200_nsc_slabs(args, rank, world, local, barrier):
+    raise SystemExit("bench.py: --config nsc at N > 1 needs the NSC slab path (see DESIGN.md section 7)")
 
 
 def run_b200_slabs(args, rank, world, local, barrier):
@@ -463,6 +671,8 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="smc", choices=["smc", "nsc", "mixed"],
+                    help="smc: BASELINE.json configs[1]/[2] (the metric's config); nsc: configs[3]; mixed: configs[4]")
     ap.add_argument("--nx", type=int, default=250)
     ap.add_argument("--ny", type=int, default=250)
     ap.add_argument("--nz", type=int, default=16)
@@ -471,12 +681,21 @@ def main():
                     help="0: FIXED_DENSITY 5 shapes/bin; >0: FIXED_BIN_SIZE with this edge in sphere diameters")
     ap.add_argument("--settle", type=int, default=300, help="untimed steps before warm-up (bed forms its contacts)")
     ap.add_argument("--e2e-steps", type=int, default=20)
-    ap.add_argument("--cpu-seconds", type=float, default=20.0)
+    ap.add_argument("--cpu-seconds", type=float, default=25.0)
+    ap.add_argument("--ref-seconds", type=float, default=150.0, help="--impl reference: wall-clock budget of the arm")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--ref-nx", type=int, default=100)
-    ap.add_argument("--ref-ny", type=int, default=100)
-    ap.add_argument("--ref-settle", type=int, default=50)
+    ap.add_argument("--nsc-nx", type=int, default=128)
+    ap.add_argument("--nsc-ny", type=int, default=128)
+    ap.add_argument("--nsc-nz", type=int, default=16)
+    ap.add_argument("--nsc-iters", type=int, default=100)
+    ap.add_argument("--nsc-settle", type=int, default=20)
+    ap.add_argument("--nsc-steps", type=int, default=20, help="cap on the timed NSC steps (25 ms each)")
+    ap.add_argument("--mixed-nx", type=int, default=180)
+    ap.add_argument("--mixed-ny", type=int, default=180)
+    ap.add_argument("--mixed-nz", type=int, default=16)
     args = ap.parse_args()
+    if args.config == "mixed" and args.settle == 300:
+        args.settle = 2500  # the mixed bed needs longer to come to rest on the floor
     if args.impl == "reference":
         run_reference(args)
     else:

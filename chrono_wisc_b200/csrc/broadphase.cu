@@ -535,15 +535,19 @@ int enqueue_bins(System* S) {
     S->box_relative = true;
 
     CB_CUDA(cudaMemsetAsync(S->bin_cursor.p, 0, (size_t)S->cap_bins * 4, S->stream));
+    CB_TRY(timer_start(S, "k_bin_count"));
     k_bin_count<<<sgrid, 256, 0, S->stream>>>(gs, env, S->s_meta.p, S->s_wpos.p, S->s_box.p, S->bin_intersections.p,
                                               S->bin_cursor.p, S->large_list.p, S->heavy.p, S->d_cnt);
+    CB_TRY(timer_stop(S, "k_bin_count"));
     k_bin_large<false><<<S->num_sms * 4, 256, 0, S->stream>>>(S->s_meta.p, S->s_wpos.p, S->s_box.p, env, S->large_list.p, S->d_cnt,
                                                   S->cap_entries, S->bin_cursor.p, nullptr, nullptr, nullptr);
     S->launches += 2;
     CB_TRY(scan_bins(S, S->bin_cursor.p, S->bin_start.p, &S->d_cnt->num_bins, S->cap_bins));
+    CB_TRY(timer_start(S, "k_bin_fill"));
     k_bin_fill<<<sgrid, 256, 0, S->stream>>>(S->ns, env, S->s_meta.p, S->s_wpos.p, S->s_box.p, S->bin_intersections.p,
                                              S->bin_start.p, S->cap_entries, S->bin_cursor.p, S->ent_tmp.p,
                                              S->ent_bin.p, S->d_cnt);
+    CB_TRY(timer_stop(S, "k_bin_fill"));
     k_bin_large<true><<<S->num_sms * 4, 256, 0, S->stream>>>(S->s_meta.p, S->s_wpos.p, S->s_box.p, env, S->large_list.p, S->d_cnt,
                                                  S->cap_entries, S->bin_cursor.p, S->bin_start.p, S->ent_tmp.p,
                                                  S->ent_bin.p);

@@ -169,6 +169,9 @@ int enqueue_integrate(System* S) {
     if (fuse) {
         k_reset_bbox<<<1, 32, 0, S->stream>>>(S->d_cnt);
         S->launches++;
+    }
+    CB_TRY(timer_start(S, "k_integrate"));
+    if (fuse) {
         if (S->defer_vel_update)
             INTEGRATE(true, true);
         else
@@ -179,6 +182,7 @@ int enqueue_integrate(System* S) {
         INTEGRATE(false, false);
     }
 #undef INTEGRATE
+    CB_TRY(timer_stop(S, "k_integrate"));
     S->sphere_aabb_valid = fuse;
     S->launches++;
     CB_CUDA(cudaGetLastError());

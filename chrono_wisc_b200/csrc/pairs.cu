@@ -1263,12 +1263,14 @@ static int enqueue_pair_pass_t(System* S, int mode, int64_t* out, uint32_t cap) 
         S->ent_shape.p, S->ent_mask.p, cmask, S->ent_off.p, S->slow_bins.p, S->long_bins.p,
         reinterpret_cast<uint2*>(S->pair_q.p), S->cap_pairq, S->d_cnt);
     CB_TRY(timer_stop(S, "k_pair_masks"));
-    CB_TRY(timer_start(S, "k_pair_masks_slow"));
+    CB_TRY(timer_start(S, "k_pair_queue"));
     k_pair_queue<CPLX><<<grid_for(S, S->cap_pairq, 128, 8), 128, 0, S->stream>>>(
         S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
         env, algorithm, mode, reinterpret_cast<const uint2*>(S->pair_q.p), S->cap_pairq,
         reinterpret_cast<unsigned long long*>(S->ent_mask.p), reinterpret_cast<unsigned long long*>(cmask),
         S->ent_off.p, S->d_cnt);
+    CB_TRY(timer_stop(S, "k_pair_queue"));
+    CB_TRY(timer_start(S, "k_pair_masks_slow"));
     k_pair_masks_slow<CPLX><<<gs, 32 * SLOW_WARPS, 0, S->stream>>>(
         S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_tmp.p, S->ent_shape.p, S->ent_bin.p,
         S->bin_start.p, env, algorithm, mode, S->ent_mask.p, cmask, S->ent_off.p, S->slow_bins.p, X, S->d_cnt);

@@ -859,7 +859,9 @@ int enqueue_smc(System* S) {
         S->launches++;
     }
     CB_TRY(scan_u32(S, S->b_deg.p, S->b_deg.p, &S->d_cnt->n_bodies, nb));
+    CB_TRY(timer_start(S, "k_inc_fill"));
     k_inc_fill<<<cgrid, 256, 0, S->stream>>>(S->c_bids.p, S->heavy.p, S->b_deg.p, S->b_cursor.p, S->b_inc.p, S->d_cnt);
+    CB_TRY(timer_stop(S, "k_inc_fill"));
     k_heavy_list<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->heavy.p, S->heavy_list.p, S->d_cnt);
     CB_TRY(timer_start(S, "k_body_reduce"));
     UpdArgs U;

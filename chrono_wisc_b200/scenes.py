@@ -204,6 +204,48 @@ def mixed_smc(n_side=6, seed=7, radius=0.1, step=1e-3, shapes=("sphere", "box", 
     return b.finish([smc_material(young=2e5, friction=0.4, restitution=0.1)], settings)
 
 
+def mixed_bed(nx=180, ny=180, nz=16, radius=0.1, seed=7, step=1e-3, algorithm=HYBRID, bin_edge=3.0):
+    """Large mixed-shape SMC bed (BASELINE.json configs[4] flavour, shape families of
+    src/demos/multicore/demo_MCORE_mixerSMC.cpp:118-168): one third spheres (r), boxes (r, 0.8 r, 0.6 r) and capsules
+    (0.6 r, stored half-length as Appendix A.1 of the survey), E = 2e5, mu = 0.4, cr = 0.1, settling in an open box;
+    FIXED_BIN_SIZE with a cubic bin of `bin_edge` radii.  518,400 bodies = mixed_bed(180, 180, 16).  The mixer blade of
+    the demo is a motor-driven body (bilateral constraint) and is not part of this scene."""
+    b = SceneBuilder()
+    rho = 1000.0
+    spacing = 2.4 * radius
+    sx, sy, sz = nx * spacing + radius, ny * spacing + radius, (nz + 2) * spacing
+    bin_body = b.add_bodies(1.0, (1.0, 1.0, 1.0), [[0.0, 0.0, 0.0]], active=0, collide=1)
+    b.add_box_container(bin_body, (0, 0, sz / 2), (sx, sy, sz), 0.2, faces=(2, 2, -1))
+    pos = lattice_positions(nx, ny, nz, spacing, 0.02 * radius, 1.2 * radius, seed)
+    rng = np.random.Generator(np.random.MT19937(seed + 1))
+    n = pos.shape[0]
+    q = rng.normal(size=(n, 4))
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    kind = np.arange(n) % 3
+    for k in range(3):
+        sel = np.flatnonzero(kind == k)
+        if k == 0:
+            m = rho * 4 / 3 * np.pi * radius ** 3
+            I = (0.4 * m * radius ** 2,) * 3
+            first = b.add_bodies(m, I, pos[sel], rot=q[sel])
+            b.add_shapes(SPHERE, first + np.arange(sel.size), [[radius]])
+        elif k == 1:
+            h = np.array([radius, 0.8 * radius, 0.6 * radius])
+            m = rho * 8 * h.prod()
+            I = m / 3 * np.array([h[1] ** 2 + h[2] ** 2, h[0] ** 2 + h[2] ** 2, h[0] ** 2 + h[1] ** 2])
+            first = b.add_bodies(m, I, pos[sel], rot=q[sel])
+            b.add_shapes(BOX, first + np.arange(sel.size), [h])
+        else:
+            r, hl = 0.6 * radius, 0.6 * radius
+            m = rho * (np.pi * r * r * 2 * hl + 4 / 3 * np.pi * r ** 3)
+            I = (0.5 * m * r * r,) * 3
+            first = b.add_bodies(m, I, pos[sel], rot=q[sel])
+            b.add_shapes(CAPSULE, first + np.arange(sel.size), [[r, hl]])
+    settings = dict(system_type=1, step_size=step, gravity=(0.0, 0.0, -9.81), contact_force_model=HERTZ,
+                    narrowphase_algorithm=algorithm, broadphase_grid=FIXED_BIN_SIZE, bin_size=(bin_edge * radius,) * 3)
+    return b.finish([smc_material(young=2e5, friction=0.4, restitution=0.1)], settings)
+
+
 def balls_nsc(nx=16, ny=16, nz=4, radius=0.15, seed=3, step=1e-2, envelope=0.01, iterations=100, mu=0.4):
     """NSC ball bed (config D, after src/demos/multicore/demo_MCORE_ballsNSC.cpp:121-149): unit-mass spheres with
     I = 0.4 m r^2, friction 0.4, SLIDING mode, alpha = 0, recovery speed 1e4, APGD with a fixed iteration count.

@@ -726,6 +726,38 @@ void orc_set_threads(int n) { omp_set_num_threads(n > 0 ? n : 1); }
 int orc_max_threads(void) { return omp_get_max_threads(); }
 void orc_set_settings(orc_system* S, const cb200_settings* s) { S->st = *s; }
 
+// The reference's defaults (collision_settings / solver_settings constructors, src/chrono_multicore/ChSettings.h:39-246)
+// for the fields the boundary struct carries; the checkers keep their own table (they never load the product library).
+void orc_default_settings(cb200_settings* s) {
+    memset(s, 0, sizeof(*s));
+    s->collision_envelope = 0;
+    s->broadphase_grid = 0;  // FIXED_RESOLUTION, 10 x 10 x 10
+    s->bins_per_axis[0] = s->bins_per_axis[1] = s->bins_per_axis[2] = 10;
+    s->bin_size[0] = s->bin_size[1] = s->bin_size[2] = 1;
+    s->grid_density = 5;
+    s->narrowphase_algorithm = 2;  // HYBRID
+    s->system_type = 0;
+    s->step_size = 0.01;
+    s->contact_force_model = 1;    // Hertz
+    s->adhesion_force_model = 0;   // Constant
+    s->tangential_displ_mode = 1;  // OneStep
+    s->use_material_properties = 1;
+    s->characteristic_vel = 1;
+    s->min_slip_vel = 1e-4;
+    s->min_roll_vel = 1e-4;
+    s->min_spin_vel = 1e-4;
+    s->solver_type = 0;            // APGD
+    s->solver_mode = 1;            // SLIDING
+    s->max_iteration_normal = 0;
+    s->max_iteration_sliding = 100;
+    s->max_iteration_spinning = 0;
+    s->cache_step_length = 0;
+    s->alpha = .2;
+    s->contact_recovery_speed = .6;
+    s->tolerance = 1e-4;
+    s->deterministic = 1;
+}
+
 void orc_set_bodies(orc_system* S, int nb, const double* mass, const double* inertia, const char* active,
                     const char* collide) {
     S->nb = nb;

@@ -23,6 +23,7 @@ void orc_destroy(orc_system*);
 void orc_set_threads(int n); /* OpenMP threads for the embarrassingly parallel loops; 1 = scalar port */
 int orc_max_threads(void);
 void orc_set_settings(orc_system*, const cb200_settings*);
+void orc_default_settings(cb200_settings*);
 void orc_set_bodies(orc_system*, int nb, const double* mass, const double* inertia_xx, const char* active,
                     const char* collide);
 void orc_set_shapes(orc_system*, int ns, const int32_t* type, const uint32_t* body, const int16_t* fam,

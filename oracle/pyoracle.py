@@ -38,6 +38,24 @@ def have_ref():
     return os.path.exists(REF_LIB)
 
 
+class OrcSettings(C.Structure):
+    """The checkers' own mirror of ``cb200_settings`` (include/chrono_b200.h -- the boundary contract, a header; the
+    oracle never loads the product library).  tests/test_abi.py checks it field by field against the product's mirror."""
+
+    _fields_ = [
+        ("collision_envelope", C.c_double), ("broadphase_grid", C.c_int32), ("bins_per_axis", C.c_int32 * 3),
+        ("bin_size", C.c_double * 3), ("grid_density", C.c_double), ("narrowphase_algorithm", C.c_int32),
+        ("system_type", C.c_int32), ("step_size", C.c_double), ("gravity", C.c_double * 3),
+        ("contact_force_model", C.c_int32), ("adhesion_force_model", C.c_int32), ("tangential_displ_mode", C.c_int32),
+        ("use_material_properties", C.c_int32), ("characteristic_vel", C.c_double), ("min_slip_vel", C.c_double),
+        ("min_roll_vel", C.c_double), ("min_spin_vel", C.c_double), ("solver_type", C.c_int32),
+        ("solver_mode", C.c_int32), ("max_iteration_normal", C.c_int32), ("max_iteration_sliding", C.c_int32),
+        ("max_iteration_spinning", C.c_int32), ("cache_step_length", C.c_int32), ("alpha", C.c_double),
+        ("contact_recovery_speed", C.c_double), ("tolerance", C.c_double), ("deterministic", C.c_int32),
+        ("reserved", C.c_int32 * 7),
+    ]
+
+
 class Ref:
     """The reference collision pipeline (GenerateAABB + ChBroadphase + ChNarrowphase) and helpers."""
 
@@ -50,7 +68,8 @@ class Ref:
                      "ref_run_collision", "ref_get_counts", "ref_get_grid", "ref_get_aabb", "ref_get_bins",
                      "ref_get_pairs", "ref_get_contacts", "ref_smc_contact_forces", "ref_orthogonalize",
                      "ref_compute_jacobian", "ref_rotate", "ref_rotate_t", "ref_abs_rotate", "ref_quat_mult",
-                     "ref_set_num_threads"):
+                     "ref_set_num_threads", "ref_smc_setup", "ref_smc_step", "ref_smc_get_state",
+                     "ref_smc_get_timers"):
             getattr(L, name).restype = None
         L.ref_prims_pair.restype = C.c_int
         L.ref_mpr_pair.restype = C.c_int
@@ -120,6 +139,44 @@ class Ref:
 
     def run(self, stages=7):
         self.L.ref_run_collision(self.h, C.c_int(stages))
+
+    # ---- whole SMC step: reference collision + reference force function + restated glue, all in C++ / OpenMP ----
+    SMC_PHASES = ("update", "collision_broad", "collision_narrow", "materials", "forces", "accumulate", "velocity",
+                  "integrate")
+
+    def smc_setup(self, scene):
+        """set_scene + everything the step needs beside the collision data (ref_smc_setup)."""
+        self.set_scene(scene)
+        st = scene["settings"]
+        g = lambda k, d: st.get(k, d)
+        iset = np.array([g("contact_force_model", 1), g("adhesion_force_model", 0), g("tangential_displ_mode", 1),
+                         g("use_material_properties", 1)], dtype=np.int32)
+        if iset[2] == 2:
+            raise ValueError("the whole-step reference driver keeps no MultiStep history")
+        grav = g("gravity", (0, 0, -9.81))
+        dset = np.array([g("characteristic_vel", 1.0), g("min_slip_vel", 1e-4), g("min_roll_vel", 1e-4),
+                         g("min_spin_vel", 1e-4), g("step_size", 1e-3), grav[0], grav[1], grav[2]], dtype=np.float64)
+        mats = np.ascontiguousarray(scene["materials"], dtype=np.float32)
+        smat = np.ascontiguousarray(scene["shape_mat"], dtype=np.int32)
+        self.nb = scene["mass"].size
+        self.L.ref_smc_setup(self.h, C.c_int(self.nb), _p(_f64(scene["mass"])), _p(_f64(scene["inertia"])),
+                             _p(_f64(scene["vel"])), C.c_int(mats.shape[0]), _p(mats), C.c_int(smat.size), _p(smat),
+                             _p(iset), _p(dset))
+
+    def smc_step(self, n=1):
+        self.L.ref_smc_step(self.h, C.c_int(int(n)))
+
+    def smc_state(self):
+        pos, rot, vel = np.empty((self.nb, 3)), np.empty((self.nb, 4)), np.empty((self.nb, 6))
+        self.L.ref_smc_get_state(self.h, _p(pos), _p(rot), _p(vel))
+        return pos, rot, vel
+
+    def smc_timers(self):
+        """seconds per step and phase since smc_setup"""
+        t, n = np.zeros(8), C.c_long(0)
+        self.L.ref_smc_get_timers(self.h, _p(t), C.byref(n))
+        k = max(n.value, 1)
+        return {name: float(v) / k for name, v in zip(self.SMC_PHASES, t)}
 
     def counts(self):
         c = np.zeros(8, dtype=np.uint32)
@@ -253,7 +310,7 @@ class Oracle:
         L = C.CDLL(ORACLE_LIB)
         L.orc_create.restype = P
         L.orc_max_threads.restype = C.c_int
-        for name in ("orc_destroy", "orc_set_threads", "orc_set_settings", "orc_set_bodies", "orc_set_shapes",
+        for name in ("orc_destroy", "orc_default_settings", "orc_set_threads", "orc_set_settings", "orc_set_bodies", "orc_set_shapes",
                      "orc_set_materials_smc", "orc_set_state", "orc_get_state", "orc_collide", "orc_smc_step",
                      "orc_get_counts", "orc_get_grid", "orc_get_aabb", "orc_get_pairs", "orc_get_contacts",
                      "orc_get_contact_forces", "orc_get_body_forces", "orc_get_hf", "orc_get_timers",
@@ -282,10 +339,8 @@ class Oracle:
         return int(self.L.orc_max_threads())
 
     def set_scene(self, scene):
-        from chrono_wisc_b200._lib import cb200_settings, load  # struct layout + defaults of the boundary only
-
-        st = cb200_settings()
-        load().cb200_default_settings(C.byref(st))
+        st = OrcSettings()
+        self.L.orc_default_settings(C.byref(st))
         for k, v in scene["settings"].items():
             cur = getattr(st, k)
             if hasattr(cur, "__len__"):

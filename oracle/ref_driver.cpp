@@ -24,6 +24,8 @@
 #include <limits>
 #include <memory>
 #include <vector>
+#include <cmath>
+#include <omp.h>
 
 #include "chrono/multicore_math/thrust.h"
 #include "chrono/collision/ChCollisionModel.h"
@@ -83,8 +85,34 @@ namespace chrono {
 
 namespace {
 
+// State of the whole-step driver (ref_smc_step): what host_container holds beside the collision data
+// (MC/ChDataManager.h:228-262) in the reference's own types.
+struct StepState {
+    int nb = 0;
+    std::vector<real> mass, v, hf;          // v, hf: 6 per body (MC/physics/ChSystemMulticore.cpp:350-362)
+    std::vector<real3> inertia, inv_inertia;
+    std::vector<float> materials;           // nm x 14 (ChContactMaterialSMC fields, see chrono_b200.h)
+    std::vector<int> shape_mat;
+    int force_model = 1, adhesion_model = 0, displ_mode = 1, use_mat_props = 1;
+    real char_vel = 1, min_slip_vel = 1e-4, min_roll_vel = 1e-4, min_spin_vel = 1e-4, h = 1e-3;
+    real3 gravity = real3(0, 0, -9.81);
+    double t[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // seconds: update, broad, narrow, materials, forces, accumulate, velocity, integrate
+    long steps = 0;
+    unsigned ct_body_count = 0;
+};
+
 struct RefSystem {
     chrono::ChCollisionSystemMulticore cs;
+    StepState st;
+};
+
+// thrust::reduce_by_key functor over (force, torque) tuples, as sum_tuples in
+// MC/solver/ChIterativeSolverMulticoreSMC.cpp:639-648
+struct add_pairs {
+    template <typename A, typename B>
+    thrust::tuple<real3, real3> operator()(const A& a, const B& b) const {
+        return thrust::tuple<real3, real3>(thrust::get<0>(a) + thrust::get<0>(b), thrust::get<1>(a) + thrust::get<1>(b));
+    }
 };
 
 inline real3 r3(const double* p) { return real3(p[0], p[1], p[2]); }
@@ -375,6 +403,195 @@ void ref_smc_contact_forces(int nc, const int* bids, const int* shape_pairs, int
             shear_disp[3 * i] = sd[i].x, shear_disp[3 * i + 1] = sd[i].y, shear_disp[3 * i + 2] = sd[i].z;
         }
     }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Whole SMC step on the host cores the way the reference runs it: the reference's own collision translation units
+// (GenerateAABB, ChBroadphase::Process, ChNarrowphase::Process -- Thrust with the OpenMP backend), its own
+// function_CalcContactForces under the OpenMP loop of host_CalcContactForces, Thrust sort_by_key / reduce_by_key for
+// ProcessContacts; the parts that live in Eigen / ChBody translation units are restated beside them ("glue"), each
+// with the threading the reference gives it.  This is the timed CPU arm of bench.py (kind "_ref+glue").
+// ---------------------------------------------------------------------------------------------------------------
+void ref_smc_setup(void* h, int nb, const double* mass, const double* inertia, const double* vel, int nm,
+                   const float* materials, int ns, const int* shape_mat, const int* isettings, const double* dsettings) {
+    auto& st = static_cast<RefSystem*>(h)->st;
+    st.nb = nb;
+    st.mass.assign(mass, mass + nb);
+    st.v.assign(vel, vel + 6 * (size_t)nb);
+    st.hf.assign(6 * (size_t)nb, 0.0);
+    st.inertia.resize(nb);
+    st.inv_inertia.resize(nb);
+    for (int i = 0; i < nb; i++) {
+        st.inertia[i] = r3(inertia + 3 * i);
+        st.inv_inertia[i] = real3(1.0 / inertia[3 * i], 1.0 / inertia[3 * i + 1], 1.0 / inertia[3 * i + 2]);
+    }
+    st.materials.assign(materials, materials + 14 * (size_t)nm);
+    st.shape_mat.assign(shape_mat, shape_mat + ns);
+    st.force_model = isettings[0], st.adhesion_model = isettings[1], st.displ_mode = isettings[2];
+    st.use_mat_props = isettings[3];
+    st.char_vel = dsettings[0], st.min_slip_vel = dsettings[1], st.min_roll_vel = dsettings[2];
+    st.min_spin_vel = dsettings[3], st.h = dsettings[4];
+    st.gravity = real3(dsettings[5], dsettings[6], dsettings[7]);
+    for (double& x : st.t)
+        x = 0;
+    st.steps = 0;
+}
+
+void ref_smc_step(void* hh, int nsteps) {
+    auto* sys = static_cast<RefSystem*>(hh);
+    auto& st = sys->st;
+    auto& cd = *sys->cs.cd_data;
+    const int nb = st.nb;
+    const real h = st.h;
+    std::vector<real3>& pos = *cd.state_data.pos_rigid;
+    std::vector<quaternion>& rot = *cd.state_data.rot_rigid;
+    std::vector<char>& active = *cd.state_data.active_rigid;
+    for (int step = 0; step < nsteps; step++) {
+        double t0 = omp_get_wtime(), t1;
+        // UpdateRigidBodies (MC/physics/ChSystemMulticore.cpp:329-377, omp over bodies) with ChBody::UpdateForces /
+        // ComputeGyro / VariablesFbLoadForces (src/chrono/physics/ChBody.cpp:552-574,423-426,247-257)
+#pragma omp parallel for
+        for (int i = 0; i < nb; i++) {
+            const real3 w(st.v[6 * i + 3], st.v[6 * i + 4], st.v[6 * i + 5]);
+            const real3 gyro = Cross(w, st.inertia[i] * w);
+            const real3 F = st.gravity * st.mass[i];
+            const real3 hF = h * F, hT = h * (real3(0) - gyro);
+            st.hf[6 * i] = hF.x, st.hf[6 * i + 1] = hF.y, st.hf[6 * i + 2] = hF.z;
+            st.hf[6 * i + 3] = hT.x, st.hf[6 * i + 4] = hT.y, st.hf[6 * i + 5] = hT.z;
+        }
+        t1 = omp_get_wtime(), st.t[0] += t1 - t0, t0 = t1;
+        // ChCollisionSystemMulticore::Run (CMC/ChCollisionSystemMulticore.cpp:289-345): the reference's own code
+        sys->cs.GenerateAABB();
+        sys->cs.broadphase.Process();
+        t1 = omp_get_wtime(), st.t[1] += t1 - t0, t0 = t1;
+        sys->cs.narrowphase.Process();
+        t1 = omp_get_wtime(), st.t[2] += t1 - t0, t0 = t1;
+        const int nc = (int)cd.num_rigid_contacts;
+        // composite materials per contact, float arithmetic (ChContactContainerMulticoreSMC::AddContact,
+        // MC/collision/ChContactContainerMulticoreSMC.cpp:123-174 + ChContactMaterialCompositeSMC's constructor,
+        // src/chrono/physics/ChContactMaterialSMC.cpp:107-130)
+        std::vector<real3> fric(nc), adhesion(nc);
+        std::vector<real2> modulus(nc);
+        std::vector<real> cr(nc);
+        std::vector<real4> smc(nc);
+#pragma omp parallel for
+        for (int i = 0; i < nc; i++) {
+            const long long key = cd.contact_shapeIDs[i];
+            const float* m1 = st.materials.data() + 14 * st.shape_mat[(int)(key >> 32)];
+            const float* m2 = st.materials.data() + 14 * st.shape_mat[(int)(key & 0xffffffff)];
+            const float E1 = m1[0], nu1 = m1[1], E2 = m2[0], nu2 = m2[1];
+            const float inv_E = (1 - nu1 * nu1) / E1 + (1 - nu2 * nu2) / E2;
+            const float inv_G = 2 * (2 - nu1) * (1 + nu1) / E1 + 2 * (2 - nu2) * (1 + nu2) / E2;
+            const float E_eff = 1 / inv_E, G_eff = 1 / inv_G;
+            fric[i] = real3(std::min(m1[2], m2[2]), std::min(m1[4], m2[4]), std::min(m1[5], m2[5]));
+            modulus[i] = real2(E_eff, G_eff);
+            adhesion[i] = real3(std::min(m1[7], m2[7]), std::min(m1[8], m2[8]), std::min(m1[9], m2[9]));
+            cr[i] = std::min(m1[6], m2[6]);
+            smc[i] = real4((float)((m1[10] + m2[10]) / 2), (float)((m1[11] + m2[11]) / 2), (float)((m1[12] + m2[12]) / 2),
+                           (float)((m1[13] + m2[13]) / 2));
+        }
+        t1 = omp_get_wtime(), st.t[3] += t1 - t0, t0 = t1;
+        // ProcessContacts step 1 = host_CalcContactForces (MC/solver/ChIterativeSolverMulticoreSMC.cpp:558-602)
+        std::vector<int> ct_bid(2 * nc);
+        std::vector<real3> ct_force(2 * nc), ct_torque(2 * nc);
+        std::vector<vec2> shape_pairs(1);
+#pragma omp parallel for
+        for (int i = 0; i < nc; i++) {
+            function_CalcContactForces(
+                i, cd.bids_rigid_rigid.data(), shape_pairs.data(), (ChSystemSMC::ContactForceModel)st.force_model,
+                (ChSystemSMC::AdhesionForceModel)st.adhesion_model, (ChSystemSMC::TangentialDisplacementModel)st.displ_mode,
+                st.use_mat_props != 0, st.char_vel, st.min_slip_vel, st.min_roll_vel, st.min_spin_vel, h, st.mass.data(),
+                pos.data(), rot.data(), st.v.data(), fric.data(), modulus.data(), adhesion.data(), cr.data(), smc.data(),
+                cd.cpta_rigid_rigid.data(), cd.cptb_rigid_rigid.data(), cd.norm_rigid_rigid.data(),
+                cd.dpth_rigid_rigid.data(), cd.erad_rigid_rigid.data(), nullptr, nullptr, nullptr, nullptr, nullptr,
+                ct_bid.data(), ct_force.data(), ct_torque.data());
+        }
+        t1 = omp_get_wtime(), st.t[4] += t1 - t0, t0 = t1;
+        // ProcessContacts steps 2-3 (:696-736): sort by body, reduce by body, hf += h (F, T)
+        std::vector<int> ct_body_id(nb);
+        std::vector<real3> ct_body_force(nb), ct_body_torque(nb);
+        unsigned count = 0;
+        if (nc) {
+            thrust::sort_by_key(THRUST_PAR ct_bid.begin(), ct_bid.end(),
+                                thrust::make_zip_iterator(thrust::make_tuple(ct_force.begin(), ct_torque.begin())));
+            auto end_range = thrust::reduce_by_key(
+                THRUST_PAR ct_bid.begin(), ct_bid.end(),
+                thrust::make_zip_iterator(thrust::make_tuple(ct_force.begin(), ct_torque.begin())), ct_body_id.begin(),
+                thrust::make_zip_iterator(thrust::make_tuple(ct_body_force.begin(), ct_body_torque.begin())),
+                thrust::equal_to<int>(), add_pairs());
+            count = (unsigned)(end_range.first - ct_body_id.begin());
+        }
+        st.ct_body_count = count;
+#pragma omp parallel for
+        for (int k = 0; k < (int)count; k++) {  // host_AddContactForces (:611-626)
+            const int b = ct_body_id[k];
+            const real3 F = h * ct_body_force[k], T = h * ct_body_torque[k];
+            st.hf[6 * b] += F.x, st.hf[6 * b + 1] += F.y, st.hf[6 * b + 2] += F.z;
+            st.hf[6 * b + 3] += T.x, st.hf[6 * b + 4] += T.y, st.hf[6 * b + 5] += T.z;
+        }
+        t1 = omp_get_wtime(), st.t[5] += t1 - t0, t0 = t1;
+        // ComputeInvMassMatrix + ComputeImpulses (MC/solver/ChIterativeSolverMulticore.cpp:61-147, ...SMC.cpp:854-868):
+        // a serial loop over the bodies and a serial (EIGEN_DONT_PARALLELIZE) block-diagonal product in the reference
+        for (int i = 0; i < nb; i++) {
+            if (!active[i])
+                continue;
+            const real im = 1.0 / st.mass[i];
+            st.v[6 * i] = st.v[6 * i] + im * st.hf[6 * i];
+            st.v[6 * i + 1] = st.v[6 * i + 1] + im * st.hf[6 * i + 1];
+            st.v[6 * i + 2] = st.v[6 * i + 2] + im * st.hf[6 * i + 2];
+            st.v[6 * i + 3] = st.v[6 * i + 3] + st.inv_inertia[i].x * st.hf[6 * i + 3];
+            st.v[6 * i + 4] = st.v[6 * i + 4] + st.inv_inertia[i].y * st.hf[6 * i + 4];
+            st.v[6 * i + 5] = st.v[6 * i + 5] + st.inv_inertia[i].z * st.hf[6 * i + 5];
+        }
+        t1 = omp_get_wtime(), st.t[6] += t1 - t0, t0 = t1;
+        // scatter + ChBody::VariablesQbIncrementPosition (MC/physics/ChSystemMulticore.cpp:134-153, omp over bodies;
+        // src/chrono/physics/ChBody.cpp:288-310; ChMatrix33::SetFromQuaternion, ChQuaternion::SetFromAngleAxis / Cross)
+#pragma omp parallel for
+        for (int i = 0; i < nb; i++) {
+            if (!active[i])
+                continue;
+            const real* v = &st.v[6 * i];
+            pos[i] = real3(pos[i].x + v[0] * h, pos[i].y + v[1] * h, pos[i].z + v[2] * h);
+            const real e0 = rot[i].w, e1 = rot[i].x, e2 = rot[i].y, e3 = rot[i].z;
+            real ax = ((e0 * e0 + e1 * e1) * 2 - 1) * v[3] + ((e1 * e2 - e0 * e3) * 2) * v[4] + ((e1 * e3 + e0 * e2) * 2) * v[5];
+            real ay = ((e1 * e2 + e0 * e3) * 2) * v[3] + ((e0 * e0 + e2 * e2) * 2 - 1) * v[4] + ((e2 * e3 - e0 * e1) * 2) * v[5];
+            real az = ((e1 * e3 - e0 * e2) * 2) * v[3] + ((e2 * e3 + e0 * e1) * 2) * v[4] + ((e0 * e0 + e3 * e3) * 2 - 1) * v[5];
+            const real len = sqrt(ax * ax + ay * ay + az * az);
+            const real angle = len * h;
+            if (len < std::numeric_limits<real>::min()) {
+                ax = 1, ay = 0, az = 0;
+            } else {
+                const real s = 1 / len;
+                ax *= s, ay *= s, az *= s;
+            }
+            const real half = angle / 2, sh = sin(half);
+            const real d0 = cos(half), d1 = ax * sh, d2 = ay * sh, d3 = az * sh;
+            rot[i] = quaternion(d0 * e0 - d1 * e1 - d2 * e2 - d3 * e3, d0 * e1 + d1 * e0 - d3 * e2 + d2 * e3,
+                                d0 * e2 + d2 * e0 + d3 * e1 - d1 * e3, d0 * e3 + d3 * e0 - d2 * e1 + d1 * e2);
+        }
+        t1 = omp_get_wtime(), st.t[7] += t1 - t0;
+        st.steps++;
+    }
+}
+
+void ref_smc_get_state(void* hh, double* pos, double* rot, double* vel) {
+    auto* sys = static_cast<RefSystem*>(hh);
+    auto& cd = *sys->cs.cd_data;
+    for (int i = 0; i < sys->st.nb; i++) {
+        const real3 p = (*cd.state_data.pos_rigid)[i];
+        const quaternion q = (*cd.state_data.rot_rigid)[i];
+        pos[3 * i] = p.x, pos[3 * i + 1] = p.y, pos[3 * i + 2] = p.z;
+        rot[4 * i] = q.w, rot[4 * i + 1] = q.x, rot[4 * i + 2] = q.y, rot[4 * i + 3] = q.z;
+    }
+    memcpy(vel, sys->st.v.data(), sizeof(double) * 6 * (size_t)sys->st.nb);
+}
+
+// seconds per phase accumulated since ref_smc_setup (8 values, see StepState::t) and the step count
+void ref_smc_get_timers(void* hh, double* t, long* steps) {
+    auto& st = static_cast<RefSystem*>(hh)->st;
+    for (int i = 0; i < 8; i++)
+        t[i] = st.t[i];
+    *steps = st.steps;
 }
 
 // Contact frame and Jacobian blocks (ChConstraintUtils.cpp:22-51), cone projection (:69-92).

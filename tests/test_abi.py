@@ -51,3 +51,16 @@ def test_no_cpu_fallback_without_device():
     h = ctypes.c_void_p()
     rc = lib.cb200_create(0, ctypes.byref(h))
     assert rc != 0 and b"no CUDA device" in lib.cb200_last_error()
+
+
+def test_oracle_settings_mirror_matches_the_boundary_struct():
+    """The checkers keep their own ctypes mirror of cb200_settings (they never load the product library); it must stay
+    field-for-field identical to the product's."""
+    from chrono_wisc_b200 import _lib
+    from oracle import pyoracle
+
+    a, b = _lib.cb200_settings, pyoracle.OrcSettings
+    assert [(n, t._type_ if hasattr(t, "_length_") else t, getattr(t, "_length_", 1)) for n, t in a._fields_] == \
+           [(n, t._type_ if hasattr(t, "_length_") else t, getattr(t, "_length_", 1)) for n, t in b._fields_]
+    import ctypes as C
+    assert C.sizeof(a) == C.sizeof(b)
