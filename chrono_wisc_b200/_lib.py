@@ -127,6 +127,11 @@ _SIGNATURES = {
     "cb200_slab_buffer_doubles": (C.c_int64, [_P]),
     "cb200_slab_pack_dev": (C.c_int, [_P, _P, _P]),
     "cb200_slab_unpack_dev": (C.c_int, [_P, _P, _P]),
+    "cb200_comm_unique_id": (C.c_int, [C.c_char_p, _P]),
+    "cb200_comm_init_nccl": (C.c_int, [_P, C.c_char_p, C.c_int, C.c_int, _P]),
+    "cb200_comm_init_local": (C.c_int, [_P, C.c_int]),
+    "cb200_comm_exchange": (C.c_int, [_P, C.c_int]),
+    "cb200_comm_steps": (C.c_int, [_P, C.c_int, C.c_int]),
 }
 
 _lib = None

@@ -194,6 +194,9 @@ int ensure_capacity(System* S) {
 // Called after fetch_counters() found the overflow mask set: grow what was too small and clear the mask.
 int grow_after_overflow(System* S) {
     const DevCounters& c = *S->h_cnt;
+    // the steps enqueued behind the overflow were no-ops on the device (their integration prepared nothing) while the
+    // host-side bookkeeping went on: the next step computes the spheres' records itself
+    S->sphere_aabb_valid = false;
     if (c.overflow & OVF_LARGE)
         return set_error(CB200_ERR_UNSUPPORTED, "more than 4096 shapes span more than 48 bins each");
     if (c.overflow & OVF_HEAVY)
@@ -328,8 +331,9 @@ void cb200_destroy(cb200_system* sys) {
         return;
     cudaSetDevice(S->device);
     cudaStreamSynchronize(S->stream);
+    comm_release(S);
 #define REL(x) S->x.release()
-    REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(bflags); REL(heavy); REL(b_sphere); REL(b_rad);
+    REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(bflags); REL(heavy); REL(b_sphere); REL(b_rad); REL(c_own);
     REL(s_type); REL(s_body); REL(s_fam); REL(s_mat); REL(s_lpos); REL(s_lrot); REL(s_dims); REL(general_ids); REL(s_verts); REL(sh_neigh); REL(sh_touch); REL(sh_disp); REL(sh_relvel); REL(sh_dur); REL(s_wpos); REL(s_wpos_alt); REL(s_wrot);
     REL(s_box); REL(s_meta); REL(mat_smc); REL(mat_nsc); REL(bin_intersections); REL(bin_start); REL(bin_cursor);
     REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_mask); REL(ent_off); REL(slow_bins); REL(long_bins); REL(pair_q); REL(large_list); REL(pairs);

@@ -261,7 +261,9 @@ struct System {
     int nsc_hist_cap = 0;
     bool nsc_fc_current = false;  // b_force also holds the contact forces on inactive bodies (Fc_current)
 
-    // ---- slab decomposition (slab.cu) ----
+    // ---- slab decomposition (slab.cu, comm.cu) ----
+    struct Comm* comm = nullptr;    // communicator / local group this slab belongs to (comm.cu); null: single system
+    DevBuf<uint8_t> c_own;          // NSC: contact enters the global sums on this rank (its first dynamic body is owned)
     bool slab_on = false;
     int slab_axis = 0, slab_has_left = 0, slab_has_right = 0;
     double slab_lo = 0, slab_hi = 0, slab_w = 0;
@@ -317,6 +319,18 @@ int alloc_shear(System* S);                                              // smc.
 int enqueue_smc(System* S);                                              // smc.cu
 int enqueue_nsc(System* S);                                              // nsc.cu
 int nsc_contact_forces_inactive(System* S);                              // nsc.cu: on-demand part of CalculateContactForces
+
+// ---- decomposed systems (comm.cu): systems that step in lockstep in this process.  One system per process over NCCL;
+// several only when ranks are emulated on one GPU (tests), all on one stream ----
+struct Group {
+    std::vector<System*> sys;
+};
+void comm_release(System* S);         // frees the communicator (cb200_destroy)
+bool comm_multi(const System* S);     // S is one slab of a decomposed system (has a communicator or a local group)
+double* comm_gsum(System* S);         // 24 doubles of device scratch for sums over all ranks
+int comm_halo6(Group& g, int which);  // owners' 6 doubles per body (0: n_w, 1: n_w0) -> the neighbours' ghost copies
+int comm_allreduce(Group& g, int first, int n);  // gsum[first..first+n) summed over all ranks, in place
+int enqueue_nsc_group(Group& g);      // nsc.cu: the NSC solve of all systems of the group, slot by slot
 
 // exclusive scans (scan.cu) over a device-side element count (*n_dev <= n_cap). n+1 outputs: out[n] = total.
 // In-place allowed.

@@ -34,7 +34,7 @@
 
 namespace cb200 {
 
-enum { NSC_FRAME = 10, NSC_PART = 8, NSC_THREADS = 256 };
+enum { NSC_FRAME = 10, NSC_PART = 8, NSC_THREADS = 256, NSC_NGLOB = 16 /* slot of comm_gsum */ };
 
 struct NscCtl {
     double L, t, theta, theta_new, beta, obj2, residual, objective, g_diff, tol_speed, norm_temp, dot_g_temp;
@@ -479,6 +479,7 @@ __global__ void __launch_bounds__(256) k_nsc_scatter(uint32_t nb, const NscCtl* 
 template <int ROWS>
 __global__ void __launch_bounds__(NSC_THREADS) k_nsc_init_temp(const double* __restrict__ gamma,
                                                                double* __restrict__ temp, double* __restrict__ part,
+                                                               const uint8_t* __restrict__ own,
                                                                const DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
@@ -487,10 +488,12 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_init_temp(const double* __r
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nc; i += gridDim.x * blockDim.x) {
         double g[ROWS];
         load_vec<ROWS>(gamma, i, g);
+        const bool mine = !own || own[i];  // decomposed systems: a contact enters the global sums on one rank only
 #pragma unroll
         for (int k = 0; k < ROWS; k++) {
             g[k] = g[k] - 1.0;
-            acc[0] += g[k] * g[k];
+            if (mine)
+                acc[0] += g[k] * g[k];
         }
         store_vec<ROWS>(temp, i, g);
     }
@@ -506,6 +509,7 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_gather_norm(const NscCtl* _
                                                                  const double* __restrict__ w,
                                                                  const double* __restrict__ x, double* __restrict__ out,
                                                                  double* __restrict__ part,
+                                                                 const uint8_t* __restrict__ own,
                                                                  const DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
@@ -526,9 +530,10 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_gather_norm(const NscCtl* _
                 if (k < act)
                     o[k] += aux_E<ROWS>(A, k) * xv[k];
         }
+        if (!own || own[i])
 #pragma unroll
-        for (int k = 0; k < ROWS; k++)
-            acc[1] += o[k] * o[k];
+            for (int k = 0; k < ROWS; k++)
+                acc[1] += o[k] * o[k];
         if (out)
             store_vec<ROWS>(out, i, o);
     }
@@ -569,15 +574,18 @@ __device__ __forceinline__ void reduce_partials(const double* __restrict__ part,
 }
 
 // start of a phase (one Solve call): scalars of :74-83
+// nglob: decomposed systems -- the number of contacts of the whole system (every contact counted on one rank)
 __global__ void k_nsc_phase_begin(NscCtl* __restrict__ ctl, int act, int max_iter, int rows, int ref_variant,
-                                  double tol_speed, int first_phase, int hist_cap, const DevCounters* __restrict__ cnt) {
+                                  double tol_speed, int first_phase, int hist_cap, const double* __restrict__ nglob,
+                                  const DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
-    const double size = (double)rows * (double)cnt->n_contacts;
+    const double ncg = nglob ? *nglob : (double)cnt->n_contacts;
+    const double size = (double)rows * ncg;
     ctl->act = act;
     ctl->max_iter = max_iter;
     ctl->iter = 0;
-    ctl->done = (max_iter <= 0 || cnt->n_contacts == 0) ? 1 : 0;
+    ctl->done = (max_iter <= 0 || ncg == 0) ? 1 : 0;
     ctl->redo = 0;
     ctl->accepted = 0;
     ctl->improved = 0;
@@ -652,6 +660,7 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_grad(const NscCtl* __restri
                                                           const double* __restrict__ w, const double* __restrict__ y,
                                                           const double* __restrict__ rfull, double* __restrict__ g,
                                                           double* __restrict__ gn, double* __restrict__ part,
+                                                          const uint8_t* __restrict__ own,
                                                           const DevCounters* __restrict__ cnt) {
     if (cnt->overflow || ctl->done)
         return;
@@ -670,13 +679,14 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_grad(const NscCtl* __restri
             double tmp[ROWS], rv[ROWS];
             rows_dot<ROWS>(F, act, w, (uint32_t)bb.x, (uint32_t)bb.y, tmp);
             load_vec<ROWS>(rfull, i, rv);
+            const double mine = (!own || own[i]) ? 1.0 : 0.0;
 #pragma unroll
             for (int k = 0; k < ROWS; k++) {
                 if (k < act) {
                     if (has_aux)
                         tmp[k] += aux_E<ROWS>(A, k) * yv[k];
-                    acc[0] += yv[k] * tmp[k];
-                    acc[1] += yv[k] * rv[k];
+                    acc[0] += mine * (yv[k] * tmp[k]);
+                    acc[1] += mine * (yv[k] * rv[k]);
                     gv[k] = tmp[k] - rv[k];
                 } else {
                     gv[k] = 0;
@@ -707,6 +717,7 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_eval(const NscCtl* __restri
                                                           const double* __restrict__ rfull,
                                                           const double* __restrict__ g, const double* __restrict__ gn,
                                                           const double* __restrict__ gamma, double* __restrict__ part,
+                                                          const uint8_t* __restrict__ own,
                                                           const DevCounters* __restrict__ cnt) {
     if (cnt->overflow || ctl->done)
         return;
@@ -725,25 +736,26 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_eval(const NscCtl* __restri
         load_vec<ROWS>(g, i, gv);
         load_vec<ROWS>(gamma, i, gam);
         load_vec<ROWS>(rfull, i, rv);
+        const double mine = (!own || own[i]) ? 1.0 : 0.0;
 #pragma unroll
         for (int k = 0; k < ROWS; k++) {
             if (k >= act)
                 n[k] = 0, rv[k] = 0;
             else if (has_aux)
                 n[k] += aux_E<ROWS>(A, k) * gnv[k];
-            acc[0] += gnv[k] * n[k];
-            acc[1] += gnv[k] * rv[k];
+            acc[0] += mine * (gnv[k] * n[k]);
+            acc[1] += mine * (gnv[k] * rv[k]);
             const double d = gnv[k] - yv[k];
-            acc[2] += d * gv[k];
-            acc[3] += d * d;
-            acc[4] += gv[k] * (gnv[k] - gam[k]);
+            acc[2] += mine * (d * gv[k]);
+            acc[3] += mine * (d * d);
+            acc[4] += mine * (gv[k] * (gnv[k] - gam[k]));
             tmp[k] = gnv[k] - g_diff * (n[k] - rv[k]);
         }
         project_contact<ROWS>(tmp, act, F.mu, A.coh, A.roll, A.spin);
 #pragma unroll
         for (int k = 0; k < ROWS; k++) {
             const double e = inv_g_diff * (gnv[k] - tmp[k]);
-            acc[5] += e * e;
+            acc[5] += mine * (e * e);
         }
     }
     block_partials<6>(acc, part);
@@ -1033,119 +1045,243 @@ static int nsc_reserve(System* S) {
     return CB200_OK;
 }
 
+// ---- decomposed systems: which contacts this rank sums, and sums over all ranks -----------------------------------
+// A contact of a slab system exists on every rank that sees both bodies (same state, same arithmetic, so its multipliers
+// stay identical everywhere); it enters the dot products on the rank that OWNS (integrates) its dynamic body with the
+// smaller GLOBAL id -- a rule every rank evaluates the same way, whatever its local slot order.
+__global__ void __launch_bounds__(256) k_nsc_own(const int32_t* __restrict__ bids, const uint8_t* __restrict__ bflags,
+                                                 const int64_t* __restrict__ gid, uint32_t nb_static,
+                                                 uint8_t* __restrict__ own, double* __restrict__ gsum,
+                                                 const DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    const uint32_t nc = cnt->n_contacts;
+    uint32_t mine = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nc; i += gridDim.x * blockDim.x) {
+        const int2 bb = reinterpret_cast<const int2*>(bids)[i];
+        const uint32_t a = (uint32_t)bb.x, b = (uint32_t)bb.y;
+        uint32_t ref = a >= nb_static ? a : b;
+        if (a >= nb_static && b >= nb_static && gid[b] < gid[a])
+            ref = b;
+        const uint8_t o = (ref >= nb_static && (bflags[ref] & 1u)) ? 1 : 0;
+        own[i] = o;
+        mine += o;
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1)
+        mine += __shfl_xor_sync(0xffffffffu, mine, d);
+    if ((threadIdx.x & 31) == 0 && mine)
+        atomicAdd(&gsum[0], (double)mine);  // whole numbers: exact whatever the order
+}
+
+// the per-CTA partials of two reductions -> gsum[0..8), gsum[8..16) (fixed order), ready for the sum over the ranks
+__global__ void __launch_bounds__(NSC_THREADS) k_nsc_fold(const NscCtl* __restrict__ ctl, const double* __restrict__ partA,
+                                                          const double* __restrict__ partB, int nblocks,
+                                                          double* __restrict__ gsum, const DevCounters* __restrict__ cnt) {
+    if (cnt->overflow || ctl->done)
+        return;
+    double a[NSC_PART], b[NSC_PART];
+    reduce_partials<NSC_PART>(partA, nblocks, a);
+    __syncthreads();
+    reduce_partials<NSC_PART>(partB, nblocks, b);
+    if (threadIdx.x < NSC_PART) {
+        gsum[threadIdx.x] = a[threadIdx.x];
+        gsum[NSC_PART + threadIdx.x] = b[threadIdx.x];
+    }
+}
+
 template <int ROWS>
-static int nsc_schur_pass(System* S, const double* x, int skip_on_redo) {
-    NscCtl* ctl = (NscCtl*)S->n_ctl;
-    k_nsc_scatter<ROWS, 0><<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(
-        S->nb, ctl, skip_on_redo, S->bflags.p, S->mass.p, S->inv_inertia.p, S->rot.p, S->b_deg.p, S->b_inc.p,
-        S->n_frame.p, x, S->n_w.p, nullptr, nullptr, nullptr, 0.0, S->d_cnt);
-    S->launches++;
+static int nsc_schur_pass(Group& g, int xsel /* 0: gamma_new, 1: y */, int skip_on_redo) {
+    for (System* S : g.sys) {
+        NscCtl* ctl = (NscCtl*)S->n_ctl;
+        const double* x = xsel == 0 ? S->n_gn.p : S->n_y.p;
+        k_nsc_scatter<ROWS, 0><<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(
+            S->nb, ctl, skip_on_redo, S->bflags.p, S->mass.p, S->inv_inertia.p, S->rot.p, S->b_deg.p, S->b_inc.p,
+            S->n_frame.p, x, S->n_w.p, nullptr, nullptr, nullptr, 0.0, S->d_cnt);
+        S->launches++;
+    }
+    // a ghost body's w is only complete on the rank that owns it: owners -> ghost copies
+    if (comm_multi(g.sys[0]))
+        CB_TRY(comm_halo6(g, 0));
     return CB200_OK;
 }
 
 template <int ROWS>
-static int nsc_setup(System* S) {
-    const cb200_settings& st = S->set;
-    const uint32_t nb = S->nb;
-    const int G = nsc_grid(S);
-    k_nsc_body_prep<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->bflags.p, S->mass.p, S->inv_inertia.p, S->rot.p,
-                                                               S->vel.p, S->hf.p, S->n_mk.p, S->n_w0.p, S->b_deg.p,
-                                                               S->d_cnt);
-    CB_CUDA(cudaMemsetAsync(S->b_cursor.p, 0, (size_t)nb * 4, S->stream));
-    NscSetupParams P;
-    P.inv_h = 1 / st.step_size;
-    P.inv_hpa = 1 / (st.step_size + st.alpha);
-    P.inv_hhpa = P.inv_h * P.inv_hpa;
-    P.alpha = st.alpha;
-    P.recovery_speed = st.contact_recovery_speed;
-    P.mode = st.solver_mode;
-    P.nm = S->nm_nsc;
-    P.has_aux = S->nsc_has_aux;
-    k_nsc_setup<ROWS><<<G, NSC_THREADS, 0, S->stream>>>(P, S->c_bids.p, S->c_mats.p, S->c_norm.p, S->c_pta.p,
-                                                        S->c_ptb.p, S->c_depth.p, S->pos.p, S->bflags.p,
-                                                        S->mat_nsc.p, S->n_w0.p, S->n_frame.p, S->n_aux.p,
-                                                        S->n_rfull.p, S->gamma.p, S->b_deg.p, S->d_cnt);
-    S->launches += 2;
-    CB_TRY(scan_u32(S, S->b_deg.p, S->b_deg.p, &S->d_cnt->n_bodies, nb));
-    k_nsc_inc_fill<<<G, 256, 0, S->stream>>>(S->c_bids.p, S->bflags.p, S->b_deg.p, S->b_cursor.p, S->b_inc.p,
-                                             S->d_cnt);
-    k_nsc_inc_sort<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->b_deg.p, S->b_inc.p, S->d_cnt);
-    S->launches += 2;
-    CB_CUDA(cudaGetLastError());
+static int nsc_setup(Group& g) {
+    const bool multi = comm_multi(g.sys[0]);
+    for (System* S : g.sys) {
+        const uint32_t nb = S->nb;
+        k_nsc_body_prep<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->bflags.p, S->mass.p, S->inv_inertia.p,
+                                                                   S->rot.p, S->vel.p, S->hf.p, S->n_mk.p, S->n_w0.p,
+                                                                   S->b_deg.p, S->d_cnt);
+        CB_CUDA(cudaMemsetAsync(S->b_cursor.p, 0, (size_t)nb * 4, S->stream));
+        S->launches++;
+    }
+    // M_invk = v + M^-1 hf of a ghost body is the owner's (here the ghost is inactive: no M^-1)
+    if (multi)
+        CB_TRY(comm_halo6(g, 1));
+    for (System* S : g.sys) {
+        const cb200_settings& st = S->set;
+        const uint32_t nb = S->nb;
+        const int G = nsc_grid(S);
+        NscSetupParams P;
+        P.inv_h = 1 / st.step_size;
+        P.inv_hpa = 1 / (st.step_size + st.alpha);
+        P.inv_hhpa = P.inv_h * P.inv_hpa;
+        P.alpha = st.alpha;
+        P.recovery_speed = st.contact_recovery_speed;
+        P.mode = st.solver_mode;
+        P.nm = S->nm_nsc;
+        P.has_aux = S->nsc_has_aux;
+        k_nsc_setup<ROWS><<<G, NSC_THREADS, 0, S->stream>>>(P, S->c_bids.p, S->c_mats.p, S->c_norm.p, S->c_pta.p,
+                                                            S->c_ptb.p, S->c_depth.p, S->pos.p, S->bflags.p,
+                                                            S->mat_nsc.p, S->n_w0.p, S->n_frame.p, S->n_aux.p,
+                                                            S->n_rfull.p, S->gamma.p, S->b_deg.p, S->d_cnt);
+        S->launches++;
+        CB_TRY(scan_u32(S, S->b_deg.p, S->b_deg.p, &S->d_cnt->n_bodies, nb));
+        k_nsc_inc_fill<<<G, 256, 0, S->stream>>>(S->c_bids.p, S->bflags.p, S->b_deg.p, S->b_cursor.p, S->b_inc.p,
+                                                 S->d_cnt);
+        k_nsc_inc_sort<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->b_deg.p, S->b_inc.p, S->d_cnt);
+        S->launches += 2;
+        if (multi) {
+            CB_CUDA(cudaMemsetAsync(comm_gsum(S) + NSC_NGLOB, 0, sizeof(double), S->stream));
+            k_nsc_own<<<G, 256, 0, S->stream>>>(S->c_bids.p, S->bflags.p, S->b_gid.p, S->slab_nb_static, S->c_own.p,
+                                                comm_gsum(S) + NSC_NGLOB, S->d_cnt);
+            S->launches++;
+        }
+        CB_CUDA(cudaGetLastError());
+    }
+    if (multi)
+        CB_TRY(comm_allreduce(g, NSC_NGLOB, 1));  // contacts of the whole system
     return CB200_OK;
 }
 
 // one Solve call of the reference (one phase): ChSolverMulticoreAPGD::Solve with local_solver_mode = phase
 template <int ROWS>
-static int nsc_phase(System* S, int act, int max_iter, bool first_phase) {
-    const cb200_settings& st = S->set;
-    NscCtl* ctl = (NscCtl*)S->n_ctl;
-    const int G = nsc_grid(S);
-    double* part0 = S->n_part.p;
-    double* part1 = S->n_part.p + (size_t)G * NSC_PART;
-    double* part2 = S->n_part.p + (size_t)2 * G * NSC_PART;
-    const double* aux = S->n_aux.p;
-    const int has_aux = S->nsc_has_aux;
-    k_nsc_phase_begin<<<1, 1, 0, S->stream>>>(ctl, act, max_iter, ROWS, st.solver_type == 1 ? 1 : 0,
-                                              st.step_size * st.tolerance, first_phase ? 1 : 0, S->nsc_hist_cap,
-                                              S->d_cnt);
-    // initial step length: temp = gamma - 1, L = |N temp| / |temp|
-    k_nsc_init_temp<ROWS><<<G, NSC_THREADS, 0, S->stream>>>(S->gamma.p, S->n_gn.p, part0, S->d_cnt);
-    S->launches += 2;
-    CB_TRY(nsc_schur_pass<ROWS>(S, S->n_gn.p, 0));
-    k_nsc_gather_norm<ROWS><<<G, NSC_THREADS, 0, S->stream>>>(ctl, S->c_bids.p, S->n_frame.p, aux, has_aux, S->n_w.p,
-                                                              S->n_gn.p, nullptr, part1, S->d_cnt);
-    k_nsc_init_L<<<1, NSC_THREADS, 0, S->stream>>>(ctl, part0, part1, G, S->d_cnt);
-    k_nsc_start<ROWS><<<G, NSC_THREADS, 0, S->stream>>>(ctl, S->gamma.p, S->n_y.p, S->n_gamma_hat.p, S->d_cnt);
-    S->launches += 3;
-    const int slots = max_iter + max_iter / 2 + 16 + S->nsc_extra_slots;
-    for (int s = 0; s < slots; s++) {
-        CB_TRY(nsc_schur_pass<ROWS>(S, S->n_y.p, 1));  // A: w = M^-1 D y
-        k_nsc_grad<ROWS><<<G, NSC_THREADS, 0, S->stream>>>(ctl, S->c_bids.p, S->n_frame.p, aux, has_aux, S->n_w.p,
-                                                           S->n_y.p, S->n_rfull.p, S->n_g.p, S->n_gn.p, part1,
-                                                           S->d_cnt);                          // B
-        S->launches++;
-        CB_TRY(nsc_schur_pass<ROWS>(S, S->n_gn.p, 0));  // C: w = M^-1 D gamma_new
-        k_nsc_eval<ROWS><<<G, NSC_THREADS, 0, S->stream>>>(ctl, S->c_bids.p, S->n_frame.p, aux, has_aux, S->n_w.p,
-                                                           S->n_y.p, S->n_rfull.p, S->n_g.p, S->n_gn.p, S->gamma.p,
-                                                           part2, S->d_cnt);                   // D
-        k_nsc_scalar<<<1, NSC_THREADS, 0, S->stream>>>(ctl, part1, part2, G, S->n_hist.p, S->d_cnt);  // E
-        k_nsc_commit<ROWS><<<G, NSC_THREADS, 0, S->stream>>>(ctl, S->n_gn.p, S->gamma.p, S->n_y.p, S->n_gamma_hat.p,
-                                                             S->d_cnt);                        // F
-        S->launches += 3;
+static int nsc_phase(Group& g, int act, int max_iter, bool first_phase) {
+    const bool multi = comm_multi(g.sys[0]);
+    struct Ptr {
+        double *part0, *part1, *part2, *gs;
+        const double* ng;
+        const uint8_t* own;
+    };
+    auto ptrs = [&](System* S) {
+        const int G = nsc_grid(S);
+        Ptr p;
+        p.part0 = S->n_part.p, p.part1 = S->n_part.p + (size_t)G * NSC_PART, p.part2 = S->n_part.p + (size_t)2 * G * NSC_PART;
+        p.gs = multi ? comm_gsum(S) : nullptr;
+        p.ng = multi ? comm_gsum(S) + NSC_NGLOB : nullptr;
+        p.own = multi ? S->c_own.p : nullptr;
+        return p;
+    };
+    for (System* S : g.sys) {
+        const cb200_settings& st = S->set;
+        const Ptr P = ptrs(S);
+        k_nsc_phase_begin<<<1, 1, 0, S->stream>>>((NscCtl*)S->n_ctl, act, max_iter, ROWS, st.solver_type == 1 ? 1 : 0,
+                                                  st.step_size * st.tolerance, first_phase ? 1 : 0, S->nsc_hist_cap,
+                                                  P.ng, S->d_cnt);
+        // initial step length: temp = gamma - 1, L = |N temp| / |temp|
+        k_nsc_init_temp<ROWS><<<nsc_grid(S), NSC_THREADS, 0, S->stream>>>(S->gamma.p, S->n_gn.p, P.part0, P.own, S->d_cnt);
+        S->launches += 2;
     }
-    k_nsc_phase_end<ROWS><<<G, NSC_THREADS, 0, S->stream>>>(ctl, S->n_gamma_hat.p, S->gamma.p, 1, S->d_cnt);
-    S->launches++;
-    CB_CUDA(cudaGetLastError());
+    CB_TRY(nsc_schur_pass<ROWS>(g, 0, 0));
+    for (System* S : g.sys) {
+        const Ptr P = ptrs(S);
+        const int G = nsc_grid(S);
+        k_nsc_gather_norm<ROWS><<<G, NSC_THREADS, 0, S->stream>>>((NscCtl*)S->n_ctl, S->c_bids.p, S->n_frame.p, S->n_aux.p,
+                                                                  S->nsc_has_aux, S->n_w.p, S->n_gn.p, nullptr, P.part1,
+                                                                  P.own, S->d_cnt);
+        if (multi)
+            k_nsc_fold<<<1, NSC_THREADS, 0, S->stream>>>((NscCtl*)S->n_ctl, P.part0, P.part1, G, P.gs, S->d_cnt);
+        S->launches += multi ? 2 : 1;
+    }
+    if (multi)
+        CB_TRY(comm_allreduce(g, 0, 2 * NSC_PART));
+    for (System* S : g.sys) {
+        const Ptr P = ptrs(S);
+        NscCtl* ctl = (NscCtl*)S->n_ctl;
+        if (multi)
+            k_nsc_init_L<<<1, NSC_THREADS, 0, S->stream>>>(ctl, P.gs, P.gs + NSC_PART, 1, S->d_cnt);
+        else
+            k_nsc_init_L<<<1, NSC_THREADS, 0, S->stream>>>(ctl, P.part0, P.part1, nsc_grid(S), S->d_cnt);
+        k_nsc_start<ROWS><<<nsc_grid(S), NSC_THREADS, 0, S->stream>>>(ctl, S->gamma.p, S->n_y.p, S->n_gamma_hat.p, S->d_cnt);
+        S->launches += 2;
+    }
+    const int slots = max_iter + max_iter / 2 + 16 + g.sys[0]->nsc_extra_slots;
+    for (int s = 0; s < slots; s++) {
+        CB_TRY(nsc_schur_pass<ROWS>(g, 1, 1));  // A: w = M^-1 D y
+        for (System* S : g.sys) {
+            const Ptr P = ptrs(S);
+            k_nsc_grad<ROWS><<<nsc_grid(S), NSC_THREADS, 0, S->stream>>>((NscCtl*)S->n_ctl, S->c_bids.p, S->n_frame.p,
+                                                                         S->n_aux.p, S->nsc_has_aux, S->n_w.p, S->n_y.p,
+                                                                         S->n_rfull.p, S->n_g.p, S->n_gn.p, P.part1, P.own,
+                                                                         S->d_cnt);  // B
+            S->launches++;
+        }
+        CB_TRY(nsc_schur_pass<ROWS>(g, 0, 0));  // C: w = M^-1 D gamma_new
+        for (System* S : g.sys) {
+            const Ptr P = ptrs(S);
+            const int G = nsc_grid(S);
+            k_nsc_eval<ROWS><<<G, NSC_THREADS, 0, S->stream>>>((NscCtl*)S->n_ctl, S->c_bids.p, S->n_frame.p, S->n_aux.p,
+                                                               S->nsc_has_aux, S->n_w.p, S->n_y.p, S->n_rfull.p, S->n_g.p,
+                                                               S->n_gn.p, S->gamma.p, P.part2, P.own, S->d_cnt);  // D
+            if (multi)
+                k_nsc_fold<<<1, NSC_THREADS, 0, S->stream>>>((NscCtl*)S->n_ctl, P.part1, P.part2, G, P.gs, S->d_cnt);
+            S->launches += multi ? 2 : 1;
+        }
+        // the one synchronisation point of a slot: {y.Ny, y.r} and {g'.Ng', g'.r, d.g, |d|^2, g.dgamma, |res|^2} over
+        // all ranks (ChSolverMulticoreAPGD.cpp:145,147,160,173 in one message)
+        if (multi)
+            CB_TRY(comm_allreduce(g, 0, 2 * NSC_PART));
+        for (System* S : g.sys) {
+            const Ptr P = ptrs(S);
+            NscCtl* ctl = (NscCtl*)S->n_ctl;
+            if (multi)
+                k_nsc_scalar<<<1, NSC_THREADS, 0, S->stream>>>(ctl, P.gs, P.gs + NSC_PART, 1, S->n_hist.p, S->d_cnt);  // E
+            else
+                k_nsc_scalar<<<1, NSC_THREADS, 0, S->stream>>>(ctl, P.part1, P.part2, nsc_grid(S), S->n_hist.p, S->d_cnt);
+            k_nsc_commit<ROWS><<<nsc_grid(S), NSC_THREADS, 0, S->stream>>>(ctl, S->n_gn.p, S->gamma.p, S->n_y.p,
+                                                                           S->n_gamma_hat.p, S->d_cnt);  // F
+            S->launches += 2;
+        }
+    }
+    for (System* S : g.sys) {
+        k_nsc_phase_end<ROWS><<<nsc_grid(S), NSC_THREADS, 0, S->stream>>>((NscCtl*)S->n_ctl, S->n_gamma_hat.p, S->gamma.p, 1,
+                                                                          S->d_cnt);
+        S->launches++;
+        CB_CUDA(cudaGetLastError());
+    }
     return CB200_OK;
 }
 
 template <int ROWS>
-static int nsc_run(System* S) {
-    const cb200_settings& st = S->set;
-    CB_TRY(nsc_setup<ROWS>(S));
+static int nsc_run(Group& g) {
+    const cb200_settings& st = g.sys[0]->set;
+    CB_TRY(nsc_setup<ROWS>(g));
     const int iters[3] = {st.max_iteration_normal, st.max_iteration_sliding, st.max_iteration_spinning};
     const int acts[3] = {1, 3, 6};
     bool first = true;
     for (int ph = 0; ph <= st.solver_mode; ph++) {
         if (iters[ph] <= 0)
             continue;
-        CB_TRY((nsc_phase<ROWS>(S, acts[ph], iters[ph], first)));
+        CB_TRY((nsc_phase<ROWS>(g, acts[ph], iters[ph], first)));
         first = false;
     }
-    if (first) {  // no phase ran: counters of an empty solve
-        k_nsc_phase_begin<<<1, 1, 0, S->stream>>>((NscCtl*)S->n_ctl, ROWS, 0, ROWS, 0, 0.0, 1, S->nsc_hist_cap,
-                                                  S->d_cnt);
-        k_nsc_phase_end<ROWS><<<1, NSC_THREADS, 0, S->stream>>>((NscCtl*)S->n_ctl, S->n_gamma_hat.p, S->gamma.p, 0,
-                                                                S->d_cnt);
-        S->launches += 2;
+    for (System* S : g.sys) {
+        if (first) {  // no phase ran: counters of an empty solve
+            k_nsc_phase_begin<<<1, 1, 0, S->stream>>>((NscCtl*)S->n_ctl, ROWS, 0, ROWS, 0, 0.0, 1, S->nsc_hist_cap, nullptr,
+                                                      S->d_cnt);
+            k_nsc_phase_end<ROWS><<<1, NSC_THREADS, 0, S->stream>>>((NscCtl*)S->n_ctl, S->n_gamma_hat.p, S->gamma.p, 0,
+                                                                    S->d_cnt);
+            S->launches += 2;
+        }
+        // ComputeImpulses + CalculateContactForces
+        k_nsc_scatter<ROWS, 1><<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(
+            S->nb, (NscCtl*)S->n_ctl, 0, S->bflags.p, S->mass.p, S->inv_inertia.p, S->rot.p, S->b_deg.p, S->b_inc.p,
+            S->n_frame.p, S->gamma.p, nullptr, S->n_mk.p, S->vel.p, S->b_force.p, 1 / st.step_size, S->d_cnt);
+        S->launches++;
+        CB_CUDA(cudaGetLastError());
     }
-    // ComputeImpulses + CalculateContactForces
-    k_nsc_scatter<ROWS, 1><<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(
-        S->nb, (NscCtl*)S->n_ctl, 0, S->bflags.p, S->mass.p, S->inv_inertia.p, S->rot.p, S->b_deg.p, S->b_inc.p,
-        S->n_frame.p, S->gamma.p, nullptr, S->n_mk.p, S->vel.p, S->b_force.p, 1 / st.step_size, S->d_cnt);
-    S->launches++;
-    CB_CUDA(cudaGetLastError());
     return CB200_OK;
 }
 
@@ -1167,23 +1303,33 @@ int nsc_contact_forces_inactive(System* S) {
     return CB200_OK;
 }
 
-int enqueue_nsc(System* S) {
-    if (S->nb == 0)
-        return CB200_OK;
-    const cb200_settings& st = S->set;
-    if (S->ns > 0 && S->nm_nsc == 0)
-        return set_error(CB200_ERR_STATE, "cb200_set_materials_nsc was not called");
-    if (st.solver_type != 0 && st.solver_type != 1)
-        return set_error(CB200_ERR_UNSUPPORTED, "only the APGD and APGDREF solvers are implemented");
-    if (st.solver_mode < 0 || st.solver_mode > 2)
-        return set_error(CB200_ERR_ARG, "solver_mode must be NORMAL, SLIDING or SPINNING");
-    CB_TRY(nsc_reserve(S));
-    S->nsc_fc_current = false;
-    switch (nsc_rows_of(S)) {
-        case 1: return nsc_run<1>(S);
-        case 3: return nsc_run<3>(S);
-        default: return nsc_run<6>(S);
+int enqueue_nsc_group(Group& g) {
+    for (System* S : g.sys) {
+        if (S->nb == 0)
+            return CB200_OK;
+        const cb200_settings& st = S->set;
+        if (S->ns > 0 && S->nm_nsc == 0)
+            return set_error(CB200_ERR_STATE, "cb200_set_materials_nsc was not called");
+        if (st.solver_type != 0 && st.solver_type != 1)
+            return set_error(CB200_ERR_UNSUPPORTED, "only the APGD and APGDREF solvers are implemented");
+        if (st.solver_mode < 0 || st.solver_mode > 2)
+            return set_error(CB200_ERR_ARG, "solver_mode must be NORMAL, SLIDING or SPINNING");
+        CB_TRY(nsc_reserve(S));
+        if (comm_multi(S))
+            CB_TRY(S->c_own.reserve(S->cap_contacts));
+        S->nsc_fc_current = false;
     }
+    switch (nsc_rows_of(g.sys[0])) {
+        case 1: return nsc_run<1>(g);
+        case 3: return nsc_run<3>(g);
+        default: return nsc_run<6>(g);
+    }
+}
+
+int enqueue_nsc(System* S) {
+    Group g;
+    g.sys.push_back(S);
+    return enqueue_nsc_group(g);
 }
 
 }  // namespace cb200
@@ -1315,10 +1461,12 @@ static int schur_host(System* S, int act, const double* x, double* out) {
     NscCtl* ctl = (NscCtl*)S->n_ctl;
     CB_TRY(upload_rows_vector(S, x, S->n_gn));
     k_nsc_set_act<<<1, 1, 0, S->stream>>>(ctl, act);
-    CB_TRY(nsc_schur_pass<ROWS>(S, S->n_gn.p, 0));
+    Group g;
+    g.sys.push_back(S);
+    CB_TRY(nsc_schur_pass<ROWS>(g, 0, 0));
     k_nsc_gather_norm<ROWS><<<nsc_grid(S), NSC_THREADS, 0, S->stream>>>(ctl, S->c_bids.p, S->n_frame.p, S->n_aux.p,
                                                                         S->nsc_has_aux, S->n_w.p, S->n_gn.p, S->n_g.p,
-                                                                        S->n_part.p, S->d_cnt);
+                                                                        S->n_part.p, nullptr, S->d_cnt);
     S->launches += 2;
     CB_CUDA(cudaGetLastError());
     return download_rows_vector(S, S->n_g.p, out, -1);

@@ -22,7 +22,7 @@ import numpy as np
 
 from . import _lib
 from ._lib import check
-from .system import ChSystemMulticoreSMC, load_scene
+from .system import ChSystemMulticoreNSC, ChSystemMulticoreSMC, load_scene
 
 REC = 33   # doubles per record (csrc/slab.cu)
 HDR = 2
@@ -89,6 +89,67 @@ def split_scene(scene, layout, gids=None):
     n_dyn = int(mine.sum())
     out["shape_body"] = np.concatenate([sb[:ns_static], np.arange(nb_static, nb_static + n_dyn)]).astype(np.uint32)
     return out, gids[mine], nb_static, ns_static
+
+
+def nccl_library_path():
+    """The NCCL shared library the process already uses (torch's bundled copy), for cb200_comm_init_nccl."""
+    import glob
+    import os
+
+    import torch
+
+    base = os.path.dirname(os.path.dirname(torch.__file__))
+    hits = sorted(glob.glob(os.path.join(base, "nvidia", "nccl", "lib", "libnccl.so*")))
+    return hits[0] if hits else "libnccl.so.2"
+
+
+class LibraryExchange:
+    """The data plane in the library (csrc/comm.cu): ghost exchange, NSC halo and all-reduce are NCCL calls the
+    library itself enqueues on the system's stream.  torch.distributed is used once, to hand rank 0's NCCL id round."""
+
+    def __init__(self, layout):
+        self.layout = layout
+
+    def attach(self, system):
+        import torch
+        import torch.distributed as dist
+
+        lib, L = system._lib, self.layout
+        path = nccl_library_path().encode()
+        dev = torch.device("cuda", system.device)
+        ident = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if L.rank == 0:
+            buf = (C.c_char * 128)()
+            check(lib.cb200_comm_unique_id(path, C.cast(buf, C.c_void_p)))
+            ident = torch.tensor(list(buf.raw), dtype=torch.uint8, device=dev)
+        if L.world > 1:
+            dist.broadcast(ident, 0)
+        raw = bytes(ident.cpu().tolist())
+        check(lib.cb200_comm_init_nccl(system._h, path, L.rank, L.world, C.cast(C.c_char_p(raw), C.c_void_p)))
+
+
+class LocalGroup:
+    """All slabs of a decomposed system in ONE process, on one stream (tests, single-GPU emulation): the library steps
+    them in lockstep and the transfers are device copies (cb200_comm_init_local)."""
+
+    def __init__(self, systems):
+        self.systems = list(systems)
+        s0 = self.systems[0]
+        for s in self.systems[1:]:
+            check(s._lib.cb200_set_stream(s._h, C.c_void_p(s0.stream.cuda_stream), 0))
+            s.stream = s0.stream
+        self._arr = (C.c_void_p * len(self.systems))(*[s._h for s in self.systems])
+        check(s0._lib.cb200_comm_init_local(self._arr, len(self.systems)))
+
+    def Exchange(self):
+        check(self.systems[0]._lib.cb200_comm_exchange(self._arr, len(self.systems)))
+
+    def DoSteps(self, n):
+        for s in self.systems:
+            s._push_settings()
+        check(self.systems[0]._lib.cb200_comm_steps(self._arr, len(self.systems), int(n)))
+        for s in self.systems:
+            s.ch_time += n * s.settings.step_size
 
 
 class DistExchange:
@@ -185,6 +246,9 @@ class _SlabMixin:
             if self._own_stream:
                 self.stream.wait_stream(torch.cuda.current_stream(dev))
             check(self._lib.cb200_set_stream(self._h, C.c_void_p(self.stream.cuda_stream), 0))
+        if isinstance(self.exchange, LibraryExchange):
+            self.exchange.attach(self)
+            self._one = (C.c_void_p * 1)(self._h)
         return self
 
     def _on_stream(self):
@@ -206,6 +270,9 @@ class _SlabMixin:
         check(self._lib.cb200_slab_unpack_dev(self._h, self._ptr(self.recv_left, L.left), self._ptr(self.recv_right, L.right)))
 
     def ExchangeGhosts(self):
+        if isinstance(self.exchange, LibraryExchange):
+            check(self._lib.cb200_comm_exchange(self._one, 1))
+            return
         with self._on_stream():
             self.Pack()
             if self.exchange is not None:
@@ -215,10 +282,13 @@ class _SlabMixin:
     def DoSteps(self, n):
         """n steps, each followed by the ghost exchange; asynchronous (call Check() or Synchronize())."""
         self._push_settings()
-        with self._on_stream():
-            for _ in range(int(n)):
-                check(self._lib.cb200_enqueue_steps(self._h, 1))
-                self.ExchangeGhosts()
+        if isinstance(self.exchange, LibraryExchange):
+            check(self._lib.cb200_comm_steps(self._one, 1, int(n)))  # step + exchange enqueued by the library
+        else:
+            with self._on_stream():
+                for _ in range(int(n)):
+                    check(self._lib.cb200_enqueue_steps(self._h, 1))
+                    self.ExchangeGhosts()
         self.ch_time += n * self.settings.step_size
 
     def StepOnly(self):
@@ -256,4 +326,13 @@ class _SlabMixin:
 class SlabSystemSMC(_SlabMixin, ChSystemMulticoreSMC):
     def __init__(self, layout, device=0, exchange=None, owned_cap=None, ghost_cap=None, own_stream=False):
         ChSystemMulticoreSMC.__init__(self, device)
+        self._slab_init(layout, exchange, owned_cap, ghost_cap, own_stream)
+
+
+class SlabSystemNSC(_SlabMixin, ChSystemMulticoreNSC):
+    """One slab of an NSC (DVI) system.  The APGD solve runs over all slabs at once: the exchange must be the
+    library's (``LibraryExchange`` over NCCL, or a ``LocalGroup`` when all slabs live in one process)."""
+
+    def __init__(self, layout, device=0, exchange=None, owned_cap=None, ghost_cap=None, own_stream=False):
+        ChSystemMulticoreNSC.__init__(self, device)
         self._slab_init(layout, exchange, owned_cap, ghost_cap, own_stream)

@@ -268,6 +268,20 @@ int cb200_slab_pack_dev(cb200_system* sys, void* send_left_dev, void* send_right
 /* Rebuild the ghost regions from the two received DEVICE buffers; records inside [lo, hi) are adopted as owned. */
 int cb200_slab_unpack_dev(cb200_system* sys, const void* recv_left_dev, const void* recv_right_dev);
 
+/* --- the data plane of a decomposed system, in the library (csrc/comm.cu): ghost exchange every step, and for NSC the
+ * halo of the body-space vector inside every Schur product plus one all-reduce of the APGD scalars per iteration
+ * (ChSolverMulticoreAPGD.cpp:145,147,160,173).  Slab i is rank i; neighbours are rank +- 1. ---------------------- */
+/* ncclGetUniqueId from the NCCL library at nccl_path (NULL or "": libnccl.so.2); 128 bytes, rank 0 shares them */
+int cb200_comm_unique_id(const char* nccl_path, char* out128);
+/* One slab per process: join an NCCL communicator (the library is resolved with dlopen, so the process keeps one NCCL) */
+int cb200_comm_init_nccl(cb200_system* sys, const char* nccl_path, int rank, int world, const char* id128);
+/* All slabs in one process, in rank order, on one stream (tests, single-GPU emulation): transfers are device copies */
+int cb200_comm_init_local(cb200_system** systems, int n);
+/* Ghost-layer exchange of the listed slabs (n = 1 over NCCL).  NSC systems exchange twice and fetch the record counts. */
+int cb200_comm_exchange(cb200_system** systems, int n);
+/* nsteps x (step of every listed slab + ghost exchange), enqueued by the library.  SMC: asynchronous (cb200_check). */
+int cb200_comm_steps(cb200_system** systems, int n, int nsteps);
+
 #ifdef __cplusplus
 }
 #endif

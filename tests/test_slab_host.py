@@ -110,3 +110,89 @@ def test_exchange_over_gloo(world):
         p.join(timeout=60)
     assert all(ok for _, ok, _ in res), res
     assert sum(n for _, _, n in res) == 400
+
+
+def _nsc_worker(rank, world, port, q):
+    """The algebra of the decomposed NSC solve (csrc/comm.cu + nsc.cu) restated in numpy over gloo: contacts in the
+    overlap are duplicated, the body-space vector w = M^-1 D x of a ghost body comes from its owner (halo BROADCAST, no
+    sum), dot products count every contact on the rank that owns its dynamic body with the smaller global id, and one
+    all-reduce gives every rank the global scalars.  Checked against the undecomposed product N x = D^T M^-1 D x."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+
+    from chrono_wisc_b200.slab import SlabLayout
+
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(17)  # same on all ranks: every rank can form the global truth
+        n, width = 120, 0.12
+        xs = np.sort(rng.uniform(-1.4, 1.4, n))
+        L = SlabLayout(world, rank, np.linspace(-1.5, 1.5, world + 1), width=width)
+        pairs = [(i, j) for i in range(n) for j in range(i + 1, n) if xs[j] - xs[i] <= width]  # "contacts"
+        m = len(pairs)
+        J = rng.normal(size=(m, 2, 6))          # the two 1x6 blocks of a contact's row of D^T
+        Minv = rng.uniform(0.5, 2.0, size=(n, 6))
+        x = rng.normal(size=m)                  # multipliers, replicated wherever the contact is visible
+        # ---- global truth
+        w = np.zeros((n, 6))
+        for c, (i, j) in enumerate(pairs):
+            w[i] += J[c, 0] * x[c]
+            w[j] += J[c, 1] * x[c]
+        w *= Minv
+        Nx = np.array([J[c, 0] @ w[i] + J[c, 1] @ w[j] for c, (i, j) in enumerate(pairs)])
+        # ---- this rank: owned bodies + ghost band, the contacts among them
+        owned = L.owns(xs)
+        visible = owned | ((xs >= L.lo - width) & (xs < L.hi + width))
+        mine = [c for c, (i, j) in enumerate(pairs) if visible[i] and visible[j]]
+        wl = np.zeros((n, 6))
+        for c in mine:
+            i, j = pairs[c]
+            wl[i] += J[c, 0] * x[c]
+            wl[j] += J[c, 1] * x[c]
+        wl *= Minv
+        assert np.allclose(wl[owned], w[owned], rtol=0, atol=1e-13)  # every contact of an owned body is visible
+        # halo: owners send the rows of their bodies inside the neighbour's band, ghosts take them
+        for nb, band in ((L.left, lambda c: c < L.lo + width), (L.right, lambda c: c >= L.hi - width)):
+            if nb is None:
+                continue
+            ids = np.nonzero(owned & band(xs))[0]
+            send = torch.from_numpy(np.concatenate([[float(ids.size)], ids.astype(float), wl[ids].ravel()]))
+            recv = torch.zeros(1 + 7 * n, dtype=torch.float64)
+            pad = torch.zeros(1 + 7 * n, dtype=torch.float64)
+            pad[:send.numel()] = send
+            ops = [dist.P2POp(dist.isend, pad, nb), dist.P2POp(dist.irecv, recv, nb)]
+            for r in dist.batch_isend_irecv(ops):
+                r.wait()
+            k = int(recv[0])
+            gid = recv[1:1 + k].numpy().astype(int)
+            wl[gid] = recv[1 + k:1 + 7 * k].numpy().reshape(k, 6)
+        Nx_l = np.array([J[c, 0] @ wl[pairs[c][0]] + J[c, 1] @ wl[pairs[c][1]] for c in mine])
+        ok = np.allclose(Nx_l, Nx[mine], rtol=0, atol=1e-12)
+        # dot product with every contact counted once: owner of the body with the smaller global id
+        own_c = np.array([owned[min(pairs[c])] for c in mine])
+        part = torch.tensor([float((x[mine] * Nx_l)[own_c].sum()), float(own_c.sum())], dtype=torch.float64)
+        dist.all_reduce(part)
+        ok &= abs(part[0].item() - float(x @ Nx)) <= 1e-10 * abs(float(x @ Nx)) and int(part[1].item()) == m
+        q.put((rank, bool(ok), int(own_c.sum())))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_nsc_halo_and_allreduce_algebra_over_gloo(world):
+    import torch.multiprocessing as mp
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_nsc_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(ok for _, ok, _ in res), res
