@@ -549,7 +549,73 @@ def run_b200_nsc(args, rank, world, local, barrier):
 
 
 def run_b200_nsc_slabs(args, rank, world, local, barrier):
-    raise SystemExit("bench.py: --config nsc at N > 1 needs the NSC slab path (see DESIGN.md section 7)")
+    """configs[3] at N > 1: the SAME 262,144-sphere NSC bed cut into N slabs along x (strong scaling).  Every Schur
+    product exchanges the body-space vector of the ghost bodies with the neighbours, every APGD slot ends in one NCCL
+    all-reduce of the 16 scalars (csrc/comm.cu, nsc.cu)."""
+    import torch
+    import torch.distributed as dist
+
+    from chrono_wisc_b200 import scenes, slab
+
+    scene = scenes.balls_nsc(args.nsc_nx, args.nsc_ny, args.nsc_nz, iterations=args.nsc_iters)
+    nb = scene["mass"].size
+    spacing = 2.05 * 0.15
+    x_of = lambda i: (i - (args.nsc_nx - 1) / 2) * spacing
+    cuts = [x_of(round(g * args.nsc_nx / world)) - spacing / 2 for g in range(world + 1)]
+    cuts[0], cuts[-1] = -1e3, 1e3
+    layout = slab.SlabLayout(world, rank, cuts, axis=0, width=0.35)
+    sys_ = slab.SlabSystemNSC(layout, device=local, exchange=slab.LibraryExchange(layout), own_stream=True)
+    sys_.LoadSlab(scene)
+    sys_.ExchangeGhosts()
+    sys_.DoSteps(args.nsc_settle)
+    sys_.DoSteps(min(args.warmup, 5))
+    sys_.Check()
+    sys_.ResetTimers()
+    steps = max(1, min(args.steps, args.nsc_steps))
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = sys_.KernelLaunches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t0 = time.perf_counter()
+    e0.record(sys_.stream)
+    sys_.DoSteps(steps)
+    e1.record(sys_.stream)
+    torch.cuda.synchronize()
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.result()
+    sys_.Check()
+    launches = sys_.KernelLaunches() - l0
+    dev_ms = e0.elapsed_time(e1) / steps
+    counts = sys_.GetCounts()
+    adv_ms = sys_.GetTimer("advance") * 1e3
+    t = torch.tensor([dev_ms, wall, adv_ms], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, wall, adv_ms = (float(x) for x in t)
+    own = torch.tensor([sys_.GetOwned()[0].size, counts.num_rigid_contacts], dtype=torch.float64, device="cuda")
+    dist.all_reduce(own)
+    assert int(own[0].item()) == nb - 1, "slabs lost or duplicated bodies"
+    if rank == 0:
+        peak, peak_kind = measured_peak_gbs()
+        it = max(1, counts.solver_iterations)
+        nc_rank, nb_rank = counts.num_rigid_contacts, sys_.GetOwned()[0].size + sys_.GetGhostIds().size
+        bytes_it = 2 * (nc_rank * (2 * 144 + 48) + nb_rank * 96) + 240 * nc_rank
+        ach = bytes_it / (adv_ms * 1e-3 / it) / 1e9
+        cfg = nsc_config(args, nb, counts)
+        cfg.update({"parallelism": f"slab{world}", "N_c_rank0": nc_rank, "N_c_sum_over_ranks": int(own[1].item()),
+                    "ghost_width": 0.35, "per_slot": "2 halo exchanges of 48 B per ghost body + 1 all-reduce of 16 doubles"})
+        line = {"metric": METRIC, "value": (nb - 1) * steps / (dev_ms * 1e-3 * steps), "unit": METRIC, "n_gpus": world,
+                "steps": steps, "warmup": min(args.warmup, 5), "ms_per_step": dev_ms, "wall_ms_per_step": wall / steps * 1e3,
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": cfg, "clocks": clocks, "gpu_launches": int(launches),
+                "e2e": {"value": (nb - 1) * steps / wall, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                        "note": "device-resident slabs; wall clock of the same steps incl. the per-step host sync"},
+                "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                             "peak_kind": peak_kind, "kernel": "one APGD iteration of rank 0's slab, halo + all-reduce included",
+                             "us_per_iteration": adv_ms * 1e3 / it, "algorithmic_bytes_per_iteration": bytes_it}}
+        print(json.dumps(line))
+    dist.destroy_process_group()
 
 
 def run_b200_slabs(args, rank, world, local, barrier):
@@ -568,7 +634,8 @@ def run_b200_slabs(args, rank, world, local, barrier):
     ghost_cap = int(2.5 * args.ny * args.nz * (width / spacing + 1)) + 1024
     layout = slab.SlabLayout(world, rank, cuts, axis=0, width=width)
     n_owned0 = gids.size
-    sys_ = slab.SlabSystemSMC(layout, device=local, exchange=slab.DistExchange(layout), ghost_cap=ghost_cap,
+    # the data plane (pack, NCCL send/recv, unpack) is enqueued by the library itself (csrc/comm.cu)
+    sys_ = slab.SlabSystemSMC(layout, device=local, exchange=slab.LibraryExchange(layout), ghost_cap=ghost_cap,
                               own_stream=True,
                               owned_cap=int(n_owned0 * 1.1) + 4096)
     nb_static = 1

@@ -783,6 +783,7 @@ static int capture_step_graph(System* S, int par) {
         cudaGraphExecDestroy(S->step_graph[par]);
         S->step_graph[par] = nullptr;
     }
+    S->step_graph_meta[par] = S->meta_dirty;  // the captured step rebuilds the per-shape records
     CB_CUDA(cudaStreamBeginCapture(S->stream, cudaStreamCaptureModeThreadLocal));
     S->capturing = true;
     const int rc = enqueue_one_step(S);
@@ -814,15 +815,18 @@ static bool graph_capable(const System* S) {
 
 // A step through the cached graph (captured once a directly enqueued step has made every lazy allocation).
 static int replay_or_enqueue_step(System* S) {
-    // the captured step relies on the previous step's integration for the spheres' records and on clean shape records
-    if (S->direct_steps < 1 || !S->sphere_aabb_valid || S->meta_dirty) {
+    // Single systems: the captured step relies on the previous step's integration for the spheres' records (and swaps
+    // the double-buffered records), so it needs them valid and clean shape records.  Slab systems rebuild the shape
+    // records every step (bodies come and go): their graph holds k_build_meta and k_aabb<false> and has no such needs.
+    const bool fused = !S->slab_on;
+    if (S->direct_steps < 1 || (fused && (!S->sphere_aabb_valid || S->meta_dirty))) {
         S->direct_steps++;
         return enqueue_one_step(S);
     }
-    const int par = S->wpos_parity;
-    if (!S->step_graph[par]) {
+    const int par = fused ? S->wpos_parity : 0;
+    if (!S->step_graph[par] || (S->meta_dirty && !S->step_graph_meta[par])) {
         CB_TRY(capture_step_graph(S, par));  // leaves the host-side state as if the step had been enqueued
-    } else {
+    } else if (fused) {
         // what enqueue_one_step does on the host side for such a step
         std::swap(S->s_wpos, S->s_wpos_alt);
         S->wpos_parity ^= 1;
@@ -832,7 +836,9 @@ static int replay_or_enqueue_step(System* S) {
     S->pairs_valid = false;
     S->contacts_geom_valid = false;  // the replayed step made a new key list; the records are those of an older one
     S->box_relative = true;
-    S->sphere_aabb_valid = true;
+    S->sphere_aabb_valid = fused;
+    if (!fused)
+        S->meta_dirty = false;  // (the slab graph was captured with k_build_meta in it: meta is dirty at every capture)
     return CB200_OK;
 }
 

@@ -288,6 +288,7 @@ struct System {
     // whole step, see integrate.cu), so consecutive steps capture different pointers.
     cudaGraphExec_t step_graph[2] = {nullptr, nullptr};
     int step_graph_launches[2] = {0, 0};  // kernel / memset nodes of one captured step
+    bool step_graph_meta[2] = {false, false};
     int wpos_parity = 0;             // flips with every s_wpos / s_wpos_alt swap
     int direct_steps = 0;            // steps enqueued directly since the graph was last invalidated
     unsigned async_calls = 0;

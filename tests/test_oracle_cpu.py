@@ -193,3 +193,19 @@ def test_oracle_omp_threads_do_not_change_results():
 
 
 # ---- world_size-2 host logic is covered in tests/test_slab_gloo.py -------------------------------------------------
+
+
+def test_reference_code_reproduces_its_mpr_unit_test_vectors(ref):
+    """tests/golden/mpr_ref_tests.json: transcribed from utest_COLL_narrow_mpr.cpp (tolerance 5e-6 as there)."""
+    cases = json.load(open(os.path.join(GOLD, "mpr_ref_tests.json")))
+    assert len(cases) >= 17
+    for c in cases:
+        A, B = c["A"], c["B"]
+        hit, out = ref.mpr_pair(A["type"], A["pos"], A["rot"], A["dims"], B["type"], B["pos"], B["rot"], B["dims"],
+                                c["envelope"])
+        assert bool(hit) == c["hit"], c["name"]
+        if c["expect"]:
+            d = float(np.dot(out["normal"], out["pt_b"] - out["pt_a"])) if c["depth_is_dot"] else out["depth"]
+            for k in ("normal", "pt_a", "pt_b"):
+                assert np.allclose(out[k], c["expect"][k], rtol=0, atol=c["tol"]), (c["name"], k)
+            assert abs(d - c["expect"]["depth"]) <= c["tol"], c["name"]
