@@ -246,6 +246,100 @@ def mixed_bed(nx=180, ny=180, nz=16, radius=0.1, seed=7, step=1e-3, algorithm=HY
     return b.finish([smc_material(young=2e5, friction=0.4, restitution=0.1)], settings)
 
 
+def poisson_disk_2d(half_x, half_y, min_dist, rng, k=30):
+    """Poisson-disk sample of the rectangle [-half_x, half_x] x [-half_y, half_y]: no two points closer than min_dist,
+    dart throwing around active points with a background grid (Bridson) -- the scheme of utils::ChPDSampler
+    (src/chrono/utils/ChUtilsSamplers.h:264-469: grid of cell size min_dist / sqrt(2), up to 30 candidates in the annulus
+    [d, 2d] around an active point).  Not the reference's random stream: both arms of a comparison get the same sample."""
+    cell = min_dist / np.sqrt(2.0)
+    nx, ny = int(np.ceil(2 * half_x / cell)) + 1, int(np.ceil(2 * half_y / cell)) + 1
+    grid = -np.ones((nx, ny), dtype=np.int64)
+    pts = []
+
+    def put(p):
+        grid[int((p[0] + half_x) / cell), int((p[1] + half_y) / cell)] = len(pts)
+        pts.append(p)
+
+    put(np.array([rng.uniform(-half_x, half_x), rng.uniform(-half_y, half_y)]))
+    active = [0]
+    d2 = min_dist * min_dist
+    while active:
+        ai = int(rng.integers(len(active)))
+        base = pts[active[ai]]
+        rad = min_dist * np.sqrt(rng.uniform(1.0, 4.0, k))
+        ang = rng.uniform(0.0, 2 * np.pi, k)
+        cand = base + np.stack([rad * np.cos(ang), rad * np.sin(ang)], 1)
+        placed = False
+        for c in cand:
+            if abs(c[0]) > half_x or abs(c[1]) > half_y:
+                continue
+            gx, gy = int((c[0] + half_x) / cell), int((c[1] + half_y) / cell)
+            nb = grid[max(gx - 2, 0):gx + 3, max(gy - 2, 0):gy + 3].ravel()
+            nb = nb[nb >= 0]
+            if nb.size and (((np.asarray([pts[j] for j in nb]) - c) ** 2).sum(1) < d2).any():
+                continue
+            put(c)
+            active.append(len(pts) - 1)
+            placed = True
+            break
+        if not placed:
+            active[ai] = active[-1]
+            active.pop()
+    return np.asarray(pts)
+
+
+def settling_pd(half=(2.0, 2.0), layers=8, radius=0.02, seed=0, step=1e-3, bins=(10, 10, 1)):
+    """BASELINE.json configs[0], the reference's own settling benchmark scene
+    (src/tests/benchmark_tests/multicore/btest_MCORE_settling.cpp:59-131): a fixed bin of five boxes
+    (AddBoxContainer, frame (0, 0, 0.5), size (2 hx, 2 hy, 1), thickness 0.2, faces (2, 2, -1)); spheres r = 0.02,
+    rho = 2000, E = 2e6, mu = 0.4, cr = 0.4, no adhesion, in `layers` layers at z = 2r', 4r', ... (r' = 1.01 r), each a
+    Poisson-disk sample with minimum distance 2r' over +-(h - r'); Hertz, OneStep, material properties, HYBRID
+    narrowphase, FIXED_RESOLUTION bins_per_axis = 10 x 10 x 1.  half = (2, 2), 8 layers is the reference's size (~55 k
+    spheres); smaller footprints give the "~10k" variants."""
+    b = SceneBuilder()
+    bin_body = b.add_bodies(1.0, (1.0, 1.0, 1.0), [[0.0, 0.0, 0.0]], active=0, collide=1)
+    b.add_box_container(bin_body, (0, 0, 0.5), (2 * half[0], 2 * half[1], 1.0), 0.2, faces=(2, 2, -1))
+    rp = 1.01 * radius
+    rng = np.random.default_rng(seed)
+    pos = []
+    for il in range(layers):
+        xy = poisson_disk_2d(half[0] - rp, half[1] - rp, 2 * rp, rng)
+        pos.append(np.concatenate([xy, np.full((xy.shape[0], 1), 2 * rp * (il + 1))], 1))
+    pos = np.concatenate(pos)
+    m = 2000.0 * 4.0 / 3.0 * np.pi * radius ** 3
+    first = b.add_bodies(m, (0.4 * m * radius * radius,) * 3, pos)
+    n = pos.shape[0]
+    b.add_shapes(SPHERE, np.arange(first, first + n), np.full((n, 1), radius))
+    settings = dict(system_type=1, step_size=step, gravity=(0.0, 0.0, -9.81), contact_force_model=HERTZ,
+                    adhesion_force_model=0, tangential_displ_mode=1, use_material_properties=1,
+                    narrowphase_algorithm=HYBRID, collision_envelope=0.0, broadphase_grid=FIXED_RESOLUTION,
+                    bins_per_axis=tuple(bins), tolerance=1e-3)
+    return b.finish([smc_material(young=2e6, friction=0.4, restitution=0.4)], settings)
+
+
+def contact_force_test(method="nsc"):
+    """The scene of the reference's contact-force acceptance test (src/tests/unit_tests/multicore/
+    utest_MCORE_contact_forces.cpp:42-152): 8 balls (r = 0.5, m = 5) on a diagonal at 1.1 r above the floor of a
+    20 x 20 x 2r box container, h = 1e-3; NSC: SLIDING, APGD, 100 iterations, tolerance 1e-5, mu 0.4, cr 0; SMC: Hooke
+    with user coefficients kn = 2e4, gn = 5e2, kt = gt = 0, OneStep.  Once at rest the contact force on the container
+    equals the weight of the balls (rel 1e-3 in the reference, checked from t = 0.5 s to 3 s)."""
+    b = SceneBuilder()
+    r, m, n = 0.5, 5.0, 8
+    ground = b.add_bodies(1.0, (1.0, 1.0, 1.0), [[0.0, 0.0, 0.0]], active=0, collide=1)
+    b.add_box_container(ground, (0, 0, r), (20, 20, 2 * r), 0.1, faces=(2, 2, -1))
+    pos = np.array([[i * 2 * r, i * 2 * r, 1.1 * r] for i in range(n)]) - np.array([7 * r, 7 * r, 0.0])
+    first = b.add_bodies(m, (0.4 * m * r * r,) * 3, pos)
+    b.add_shapes(SPHERE, np.arange(first, first + n), np.full((n, 1), r))
+    common = dict(step_size=1e-3, gravity=(0.0, 0.0, -9.81), narrowphase_algorithm=HYBRID, broadphase_grid=FIXED_RESOLUTION,
+                  bins_per_axis=(10, 10, 10), tolerance=1e-5)
+    if method == "nsc":
+        settings = dict(common, system_type=0, collision_envelope=0.0, solver_type=SOLVER_APGD, solver_mode=MODE_SLIDING,
+                        max_iteration_normal=0, max_iteration_sliding=100, max_iteration_spinning=0)
+        return b.finish([nsc_material(friction=0.4, restitution=0.0)], settings)
+    settings = dict(common, system_type=1, contact_force_model=0, tangential_displ_mode=1, use_material_properties=0)
+    return b.finish([smc_material(young=2e4, friction=0.4, restitution=0.0, kn=2e4, gn=5e2, kt=0.0, gt=0.0)], settings)
+
+
 def balls_nsc(nx=16, ny=16, nz=4, radius=0.15, seed=3, step=1e-2, envelope=0.01, iterations=100, mu=0.4):
     """NSC ball bed (config D, after src/demos/multicore/demo_MCORE_ballsNSC.cpp:121-149): unit-mass spheres with
     I = 0.4 m r^2, friction 0.4, SLIDING mode, alpha = 0, recovery speed 1e4, APGD with a fixed iteration count.

@@ -157,3 +157,21 @@ def test_slot_budget_growth():
     sys = cw.load_scene(cw.ChSystemMulticoreNSC(), scene)
     sys.DoSteps(3)
     assert sys.GetCounts().solver_iterations == 4
+
+
+@pytest.mark.parametrize("method", ["nsc", "smc"])
+def test_reference_contact_force_acceptance(method):
+    """utest_MCORE_contact_forces.cpp:154-177 on the reference's own scene and settings: from t = 0.5 s to t = 3 s the
+    contact force on the container equals the total weight of the balls within rel 1e-3 (the reference's tolerance)."""
+    scene = scenes.contact_force_test(method)
+    sys = cw.load_scene(cw.ChSystemMulticoreNSC() if method == "nsc" else cw.ChSystemMulticoreSMC(), scene)
+    weight = 9.81 * scene["mass"][1:].sum()
+    worst, t = 0.0, 0.0
+    while t < 3.0 - 1e-9:
+        sys.DoSteps(20)
+        t += 20e-3
+        if t > 0.5:
+            f, _ = sys.GetBodyContactForces()
+            worst = max(worst, abs(1 - (-f[0, 2]) / weight))
+    assert sys.GetNumContacts() == 8
+    assert worst < 1e-3, worst
