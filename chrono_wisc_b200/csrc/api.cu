@@ -711,15 +711,21 @@ int cb200_run_collision(cb200_system* sys, int stages) {
     CB_TRY(clear_unsupported(S));
     return run_stage(S, [&]() -> int {
         // a retry after a capacity overflow restarts from the AABBs (OffsetAABB rewrites the boxes in place)
+        CB_TRY(timer_start(S, "collision_broad"));
         if ((stages & 1) || ((stages & 2) && S->box_relative))
             CB_TRY(enqueue_aabb(S));
         if (stages & 2) {
             if (!S->pairs.p)
                 CB_TRY(alloc_pairs(S, 8 * S->ns + 1024));
-            CB_TRY(enqueue_broadphase(S, true, (stages & 4) != 0));
-        } else if (stages & 4) {
-            CB_TRY(enqueue_pairs_only(S, false, true));
+            CB_TRY(enqueue_bins(S));
         }
+        CB_TRY(timer_stop(S, "collision_broad"));
+        CB_TRY(timer_start(S, "collision_narrow"));
+        if (stages & 2)
+            CB_TRY(enqueue_pairs_only(S, true, (stages & 4) != 0));
+        else if (stages & 4)
+            CB_TRY(enqueue_pairs_only(S, false, true));
+        CB_TRY(timer_stop(S, "collision_narrow"));
         return CB200_OK;
     });
 }
