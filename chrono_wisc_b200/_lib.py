@@ -90,6 +90,9 @@ _SIGNATURES = {
     "cb200_upload_state": (C.c_int, [_P, C.c_int, C.c_int, _P, _P, _P]),
     "cb200_upload_applied_forces": (C.c_int, [_P, C.c_int, C.c_int, _P]),
     "cb200_set_body_flags": (C.c_int, [_P, C.c_int, C.c_int, _P, _P]),
+    "cb200_download_body_flags": (C.c_int, [_P, C.c_int, C.c_int, _P, _P]),
+    "cb200_set_active_aabb": (C.c_int, [_P, C.c_int, _P, _P]),
+    "cb200_set_speed_limits": (C.c_int, [_P, C.c_int, C.c_int, _P, _P]),
     "cb200_update_forces": (C.c_int, [_P]),
     "cb200_run_collision": (C.c_int, [_P, C.c_int]),
     "cb200_run_solver_smc": (C.c_int, [_P]),

@@ -333,7 +333,7 @@ void cb200_destroy(cb200_system* sys) {
     cudaStreamSynchronize(S->stream);
     comm_release(S);
 #define REL(x) S->x.release()
-    REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(bflags); REL(heavy); REL(b_sphere); REL(b_rad); REL(c_own);
+    REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(bflags); REL(heavy); REL(b_sphere); REL(b_rad); REL(c_own); REL(vlim); REL(b_inbox);
     REL(s_type); REL(s_body); REL(s_fam); REL(s_mat); REL(s_lpos); REL(s_lrot); REL(s_dims); REL(general_ids); REL(s_verts); REL(sh_neigh); REL(sh_touch); REL(sh_disp); REL(sh_relvel); REL(sh_dur); REL(s_wpos); REL(s_wpos_alt); REL(s_wrot);
     REL(s_box); REL(s_meta); REL(mat_smc); REL(mat_nsc); REL(bin_intersections); REL(bin_start); REL(bin_cursor);
     REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_mask); REL(ent_off); REL(slow_bins); REL(long_bins); REL(pair_q); REL(large_list); REL(pairs);
@@ -411,6 +411,7 @@ int cb200_append_bodies(cb200_system* sys, int n, const double* mass, const doub
     CB_TRY(S->inv_inertia.reserve(3 * nb1, true, st));
     CB_TRY(S->bflags.reserve(nb1, true, st));
     CB_TRY(S->heavy.reserve(nb1, true, st));
+    CB_TRY(S->vlim.reserve(2 * nb1, true, st));
     std::vector<double> inv(3 * (size_t)n), rot0(4 * (size_t)n, 0.0);
     std::vector<uint8_t> fl(n);
     for (int i = 0; i < n; i++) {
@@ -429,6 +430,7 @@ int cb200_append_bodies(cb200_system* sys, int n, const double* mass, const doub
     CB_CUDA(cudaMemsetAsync(S->hf.p + 6 * nb0, 0, 6 * (size_t)n * 8, st));
     CB_CUDA(cudaMemsetAsync(S->fapp.p + 6 * nb0, 0, 6 * (size_t)n * 8, st));
     CB_CUDA(cudaMemsetAsync(S->heavy.p + nb0, 0, (size_t)n, st));
+    CB_CUDA(cudaMemsetAsync(S->vlim.p + 2 * nb0, 0, 2 * (size_t)n * 8, st));  // no speed limit
     S->h_b_sphere.resize(nb1, -1);
     S->h_b_rad.resize(nb1, 0.0);
     CB_TRY(S->b_sphere.reserve(nb1, true, st));
@@ -680,6 +682,57 @@ int cb200_upload_applied_forces(cb200_system* sys, int first, int n, const doubl
     }
     S->has_fapp = true;
     return upload(S, S->fapp, 6 * (size_t)first, ft, 6 * (size_t)n);
+}
+
+// ChCollisionSystemMulticore::SetActiveBoundingBox / collision_settings.use_aabb_active (MC/ChSettings.h:60-66)
+int cb200_set_active_aabb(cb200_system* sys, int enabled, const double* aabb_min, const double* aabb_max) {
+    System* S = SYS(sys);
+    if (!S || (enabled && (!aabb_min || !aabb_max)))
+        return set_error(CB200_ERR_ARG, "bad argument to cb200_set_active_aabb");
+    invalidate_step_graph(S);
+    S->use_aabb_active = enabled != 0;
+    for (int a = 0; a < 3 && enabled; a++)
+        S->active_min[a] = aabb_min[a], S->active_max[a] = aabb_max[a];
+    return CB200_OK;
+}
+
+// ChBody::SetLimitSpeed / SetMaxLinVel / SetMaxAngVel of bodies [first, first+n); NULL switches the clamp off everywhere
+int cb200_set_speed_limits(cb200_system* sys, int first, int n, const double* max_speed, const double* max_wvel) {
+    System* S = SYS(sys);
+    if (!S || first < 0 || n < 0 || (uint32_t)(first + n) > S->nb)
+        return set_error(CB200_ERR_ARG, "body range out of bounds");
+    CB_CUDA(cudaSetDevice(S->device));
+    invalidate_step_graph(S);
+    if (!max_speed || !max_wvel) {
+        S->has_vlim = false;
+        return CB200_OK;
+    }
+    std::vector<double> v(2 * (size_t)n);
+    for (int i = 0; i < n; i++)
+        v[2 * i] = max_speed[i], v[2 * i + 1] = max_wvel[i];
+    CB_TRY(upload(S, S->vlim, 2 * (size_t)first, v.data(), v.size()));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    S->has_vlim = true;
+    return CB200_OK;
+}
+
+// host_data.active_rigid / collide_rigid as the device holds them (the active box deactivates bodies on the device)
+int cb200_download_body_flags(cb200_system* sys, int first, int n, char* active, char* collide) {
+    System* S = SYS(sys);
+    if (!S || first < 0 || n < 0 || (uint32_t)(first + n) > S->nb)
+        return set_error(CB200_ERR_ARG, "body range out of bounds");
+    CB_CUDA(cudaSetDevice(S->device));
+    std::vector<uint8_t> fl((size_t)n);
+    if (n)
+        CB_CUDA(cudaMemcpyAsync(fl.data(), S->bflags.p + first, (size_t)n, cudaMemcpyDeviceToHost, S->stream));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    for (int i = 0; i < n; i++) {
+        if (active)
+            active[i] = (char)(fl[i] & 1u);
+        if (collide)
+            collide[i] = (char)((fl[i] >> 1) & 1u);
+    }
+    return CB200_OK;
 }
 
 int cb200_set_body_flags(cb200_system* sys, int first, int n, const char* active, const char* collide) {

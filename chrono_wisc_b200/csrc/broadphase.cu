@@ -227,6 +227,45 @@ __global__ void __launch_bounds__(256) k_aabb(uint32_t ns, const uint32_t* __res
     bbox_block_merge(cnt, mn, mx, counted);
 }
 
+// ---- active bounding box (ChCollisionSystemMulticore::Run, CMC/ChCollisionSystemMulticore.cpp:289-304 with
+// GetOverlappingAABB, :547-562): a body that is active and collides stays active only if the box of one of its shapes
+// overlaps the active box.  (The reference then puts the others to sleep, :275-283: the change is permanent.)
+__global__ void __launch_bounds__(256) k_active_mark(uint32_t ns, const ShapeMeta* __restrict__ meta,
+                                                     const double* __restrict__ s_wpos, const ShapeBox* __restrict__ s_box,
+                                                     double envelope, d3 amin, d3 amax, uint8_t* __restrict__ inbox,
+                                                     const DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    const double zero[3] = {0, 0, 0};
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ns; i += gridDim.x * blockDim.x) {
+        const ShapeMeta m = meta[i];
+        if (m.body == UINT_MAX)
+            continue;
+        double mn[3], mx[3];
+        shape_box_rel(i, m.info, s_wpos, s_box, zero, envelope, mn, mx);  // absolute: the boxes are not offset yet
+        if ((amin.x <= mx[0] && mn[0] <= amax.x) && (amin.y <= mx[1] && mn[1] <= amax.y) && (amin.z <= mx[2] && mn[2] <= amax.z))
+            inbox[m.body] = 1;
+    }
+}
+__global__ void __launch_bounds__(256) k_active_apply(uint32_t nb, const uint8_t* __restrict__ inbox,
+                                                      uint8_t* __restrict__ bflags, const DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < nb && (bflags[b] & 3u) == 3u && !inbox[b])
+        bflags[b] &= ~1u;
+}
+__global__ void __launch_bounds__(256) k_active_meta(uint32_t ns, const uint8_t* __restrict__ bflags,
+                                                     ShapeMeta* __restrict__ meta, const DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ns; i += gridDim.x * blockDim.x) {
+        const uint32_t body = meta[i].body;
+        if (body != UINT_MAX && !(bflags[body] & 1u))
+            meta[i].info &= ~1u;
+    }
+}
+
 // DetermineBoundingBox + ComputeTopLevelResolution (CMC/ChBroadphase.cpp:142-208) and Compute_Grid_Resolution
 // (CMC/ChCollisionUtilsBroadphase.cpp:36-46).  Evaluated by one thread per CTA; all CTAs get the same bits.
 // (FIXED_DENSITY uses pow(): CUDA's differs from glibc's by at most 2 ulp, which can change the truncated bin count
@@ -511,6 +550,17 @@ int enqueue_aabb(System* S) {
             ng, listed ? S->general_ids.p : nullptr, S->s_meta.p, S->s_lpos.p, S->s_lrot.p, S->s_dims.p, S->s_verts.p,
             S->pos.p, S->rot.p, S->set.collision_envelope, S->s_wpos.p, S->s_wrot.p, S->s_box.p, S->d_cnt);
     S->launches += 2;
+    if (S->use_aabb_active) {
+        CB_TRY(S->b_inbox.reserve(S->nb));
+        CB_CUDA(cudaMemsetAsync(S->b_inbox.p, 0, S->nb, S->stream));
+        k_active_mark<<<grid_for(S, S->ns, 256), 256, 0, S->stream>>>(
+            S->ns, S->s_meta.p, S->s_wpos.p, S->s_box.p, S->set.collision_envelope,
+            mk3(S->active_min[0], S->active_min[1], S->active_min[2]), mk3(S->active_max[0], S->active_max[1], S->active_max[2]),
+            S->b_inbox.p, S->d_cnt);
+        k_active_apply<<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(S->nb, S->b_inbox.p, S->bflags.p, S->d_cnt);
+        k_active_meta<<<grid_for(S, S->ns, 256), 256, 0, S->stream>>>(S->ns, S->bflags.p, S->s_meta.p, S->d_cnt);
+        S->launches += 3;
+    }
     S->pairs_valid = false;
     S->box_relative = false;
     CB_CUDA(cudaGetLastError());

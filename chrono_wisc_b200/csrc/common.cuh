@@ -149,6 +149,12 @@ struct System {
     DevBuf<double> hf;       // 6 nb
     DevBuf<double> fapp;     // 6 nb applied (non-gravity) force, torque; may stay zero
     bool has_fapp = false;
+    DevBuf<double> vlim;     // 2 nb (max_speed, max_wvel) of ChBody::SetLimitSpeed; <= 0: no limit
+    bool has_vlim = false;
+    // ChCollisionSystemMulticore::SetActiveBoundingBox (use_aabb_active, CMC/ChCollisionSystemMulticore.cpp:289-304)
+    bool use_aabb_active = false;
+    double active_min[3] = {0, 0, 0}, active_max[3] = {0, 0, 0};
+    DevBuf<uint8_t> b_inbox;  // body has a shape whose box overlaps the active box
     DevBuf<double> mass;     // nb
     DevBuf<double> inertia;  // 3 nb (body-frame diagonal)
     DevBuf<double> inv_inertia;  // 3 nb

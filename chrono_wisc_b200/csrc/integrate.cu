@@ -63,6 +63,7 @@ __global__ void __launch_bounds__(256) k_integrate(uint32_t nb, double h, const 
                                                    double* __restrict__ rot, const double* __restrict__ mass,
                                                    const double* __restrict__ inv_inertia,
                                                    const double* __restrict__ hf, AabbArgs A,
+                                                   const double* __restrict__ vlim /* (max_speed, max_wvel) per body or null */,
                                                    DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
@@ -119,6 +120,22 @@ __global__ void __launch_bounds__(256) k_integrate(uint32_t nb, double h, const 
             qn.z = d0 * e2 + d2 * e0 + d3_ * e1 - d1 * e3;
             qn.w = d0 * e3 + d3_ * e0 - d2 * e1 + d1 * e2;
             reinterpret_cast<double4*>(rot)[b] = qn;
+            if (vlim && vlim[2 * b] > 0) {
+                // ChBody::ClampSpeed in VariablesQbSetSpeed (src/chrono/physics/ChBody.cpp:268-286,319-329), which the
+                // reference calls AFTER VariablesQbIncrementPosition (ChSystemMulticore.cpp:145-146): the pose above
+                // moved with the solver's velocity, the stored one is clamped.  The quaternion rate is 0.5 q (0, w),
+                // so w = 2 |rot_dt| = |angular velocity|.
+                const double w = sqrt(v[3] * v[3] + v[4] * v[4] + v[5] * v[5]);
+                if (w > vlim[2 * b + 1]) {
+                    const double s = vlim[2 * b + 1] / w;
+                    v[3] *= s, v[4] *= s, v[5] *= s;
+                }
+                const double sp = sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+                if (sp > vlim[2 * b]) {
+                    const double s = vlim[2 * b] / sp;
+                    v[0] *= s, v[1] *= s, v[2] *= s;
+                }
+            }
         }
         if (AABB) {
             const int32_t si = A.b_sphere[b];
@@ -165,7 +182,8 @@ int enqueue_integrate(System* S) {
     AabbArgs A = {S->b_sphere.p, S->b_rad.p, S->s_wpos_alt.p, S->set.collision_envelope};
 #define INTEGRATE(VEL, AABB)                                                                                          \
     k_integrate<VEL, AABB><<<grid, 256, 0, S->stream>>>(S->nb, S->set.step_size, S->bflags.p, S->vel.p, S->pos.p,      \
-                                                        S->rot.p, S->mass.p, S->inv_inertia.p, S->hf.p, A, S->d_cnt)
+                                                        S->rot.p, S->mass.p, S->inv_inertia.p, S->hf.p, A,                     \
+                                                        S->has_vlim ? S->vlim.p : nullptr, S->d_cnt)
     if (fuse) {
         k_reset_bbox<<<1, 32, 0, S->stream>>>(S->d_cnt);
         S->launches++;

@@ -102,6 +102,28 @@ class ChSystemMulticore:
             n = next(a.size // k for a, k in zip(arrs, (3, 4, 6)) if a is not None)
         check(self._lib.cb200_upload_state(self._h, int(first), int(n), _ptr(arrs[0]), _ptr(arrs[1]), _ptr(arrs[2])))
 
+    def SetActiveBoundingBox(self, aabb_min=None, aabb_max=None):
+        """``ChCollisionSystemMulticore::SetActiveBoundingBox`` (ChCollisionSystemMulticore.cpp:72-77); None: off."""
+        if aabb_min is None:
+            check(self._lib.cb200_set_active_aabb(self._h, 0, None, None))
+        else:
+            lo, hi = _f64(aabb_min), _f64(aabb_max)
+            check(self._lib.cb200_set_active_aabb(self._h, 1, _ptr(lo), _ptr(hi)))
+
+    def SetSpeedLimits(self, first, max_speed, max_wvel):
+        """``ChBody::SetLimitSpeed(true)`` + ``SetMaxLinVel`` / ``SetMaxAngVel`` (ChBody.cpp:319-329) per body."""
+        if max_speed is None:
+            check(self._lib.cb200_set_speed_limits(self._h, 0, 0, None, None))
+            return
+        a, b = _f64(max_speed), _f64(max_wvel)
+        check(self._lib.cb200_set_speed_limits(self._h, int(first), int(a.size), _ptr(a), _ptr(b)))
+
+    def GetBodyFlags(self, first=0, n=None):
+        n = self.num_bodies - first if n is None else n
+        act, col = np.zeros(n, dtype=np.int8), np.zeros(n, dtype=np.int8)
+        check(self._lib.cb200_download_body_flags(self._h, int(first), int(n), _ptr(act), _ptr(col)))
+        return act.astype(bool), col.astype(bool)
+
     def SetAppliedForces(self, first, force_torque):
         ft = None if force_torque is None else _f64(force_torque)
         n = self.num_bodies - first if ft is None else ft.size // 6

@@ -161,6 +161,17 @@ int cb200_upload_state(cb200_system* sys, int first, int n, const double* pos, c
  * src/chrono/physics/ChBody.cpp:552-574): 6 doubles per body (F global, T local).  NULL clears. */
 int cb200_upload_applied_forces(cb200_system* sys, int first, int n, const double* force_torque);
 int cb200_set_body_flags(cb200_system* sys, int first, int n, const char* active, const char* collide);
+/* host_data.active_rigid / collide_rigid as the device holds them now (either pointer may be NULL) */
+int cb200_download_body_flags(cb200_system* sys, int first, int n, char* active, char* collide);
+/* ChCollisionSystemMulticore::SetActiveBoundingBox (collision_settings.use_aabb_active,
+ * src/chrono/collision/multicore/ChCollisionSystemMulticore.cpp:289-304 and GetOverlappingAABB :547-562): after the
+ * AABB stage of every collision pass, an active colliding body none of whose shape boxes touches [min, max] is
+ * deactivated for good (the reference puts it to sleep).  enabled = 0 switches the test off. */
+int cb200_set_active_aabb(cb200_system* sys, int enabled, const double* aabb_min, const double* aabb_max);
+/* ChBody::SetLimitSpeed / SetMaxLinVel / SetMaxAngVel (src/chrono/physics/ChBody.cpp:319-329, applied in
+ * VariablesQbSetSpeed :268-286 to the new velocities, before the position increment) for bodies [first, first+n);
+ * max_speed[i] <= 0: no limit on body i.  NULL arrays switch the clamp off for all bodies. */
+int cb200_set_speed_limits(cb200_system* sys, int first, int n, const double* max_speed, const double* max_wvel);
 
 /* ChSystem::DoStepDynamics for a caller that keeps the body state in host memory (what the reference does: gather from
  * the ChBody objects before, scatter to them after every step, MC/physics/ChSystemMulticore.cpp:329-377, :134-153):

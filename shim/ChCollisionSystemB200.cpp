@@ -130,6 +130,12 @@ void ChCollisionSystemB200::UploadState() {
     Check(cb200_upload_state(sys, 0, (int)nb, pos3.data(), rot4.data(), nullptr));
 }
 
+void ChCollisionSystemB200::SetActiveBoundingBox(const real3& aabbmin, const real3& aabbmax) {
+    const double lo[3] = {aabbmin.x, aabbmin.y, aabbmin.z}, hi[3] = {aabbmax.x, aabbmax.y, aabbmax.z};
+    Check(cb200_set_active_aabb(sys, 1, lo, hi));
+    use_aabb_active = true;
+}
+
 void ChCollisionSystemB200::PreProcess() {
     PushSettings();
     PushNewBodiesAndShapes();
@@ -156,6 +162,10 @@ void ChCollisionSystemB200::PostProcess() {
     cd_data->global_origin = cd_data->min_bounding_point;
     cd_data->bin_size = real3(c.bin_size[0], c.bin_size[1], c.bin_size[2]);
     cd_data->inv_bin_size = real3(1.0 / c.bin_size[0], 1.0 / c.bin_size[1], 1.0 / c.bin_size[2]);
+    if (use_aabb_active) {  // ChCollisionSystemMulticore.cpp:297-303 writes the flags of the data manager
+        auto& act = *cd_data->state_data.active_rigid;
+        Check(cb200_download_body_flags(sys, 0, (int)act.size(), act.data(), nullptr));
+    }
 }
 
 void ChCollisionSystemB200::GetBoundingBox(real3& aabb_min, real3& aabb_max) const {

@@ -40,6 +40,9 @@ class ChCollisionSystemB200 B200_BASE {
     void SetBroadphaseGridDensity(real density);                   // GridType::FIXED_DENSITY
     void SetNarrowphaseAlgorithm(int algorithm);                   // ChNarrowphase::Algorithm (MPR 0, PRIMS 1, HYBRID 2)
     void SetEnvelope(real envelope) { cd_data->collision_envelope = envelope; }
+    /// ChCollisionSystemMulticore::SetActiveBoundingBox (ChCollisionSystemMulticore.cpp:72-77); the flags the box clears
+    /// on the device are written back to state_data.active_rigid in PostProcess, where the reference's Run leaves them.
+    void SetActiveBoundingBox(const real3& aabbmin, const real3& aabbmax);
 
     // ---- the ChCollisionSystem virtuals on the hot path
     void PreProcess() B200_OVERRIDE;   ///< new shapes / bodies and the current pose go to the device
@@ -70,6 +73,7 @@ class ChCollisionSystemB200 B200_BASE {
     std::shared_ptr<ChCollisionData> cd_data;
     cb200_system* sys = nullptr;
     cb200_settings settings;
+    bool use_aabb_active = false;
     size_t bodies_on_device = 0, shapes_on_device = 0, verts_on_device = 0;
     std::vector<double> pos3, rot4;  // packed staging copies of the padded real3 / quaternion arrays
 };
