@@ -96,6 +96,7 @@ static int download(System* S, const T* dev, T* dst, size_t n) {
 // ---- capacities -------------------------------------------------------------------------------------------
 static int alloc_bins(System* S, uint32_t n) {
     invalidate_step_graph(S);
+    S->bins_clean = false;
     CB_TRY(S->bin_start.reserve((size_t)n + 2));
     CB_TRY(S->bin_cursor.reserve((size_t)n + 1));
     S->cap_bins = (uint32_t)std::min<size_t>(S->bin_cursor.cap - 1, S->bin_start.cap - 2);
@@ -167,6 +168,8 @@ static int alloc_pairs(System* S, uint32_t n) {
 // re-run of the step that found out (grow_after_overflow).
 int ensure_capacity(System* S) {
     const size_t nb = S->nb, ns = S->ns;
+    if (S->b_deg.cap < nb + 2 || S->b_cursor.cap < nb + 1)
+        S->body_scratch_clean = false;
     CB_TRY(S->b_deg.reserve(nb + 2));
     CB_TRY(S->b_cursor.reserve(nb + 1));
     CB_TRY(S->b_force.reserve(6 * nb + 6));
@@ -197,6 +200,8 @@ int grow_after_overflow(System* S) {
     // the steps enqueued behind the overflow were no-ops on the device (their integration prepared nothing) while the
     // host-side bookkeeping went on: the next step computes the spheres' records itself
     S->sphere_aabb_valid = false;
+    S->bins_clean = S->body_scratch_clean = false;  // the step stopped half way
+    invalidate_step_graph(S);  // the clears are part of the next (directly enqueued) step, not of the graphs
     if (c.overflow & OVF_LARGE)
         return set_error(CB200_ERR_UNSUPPORTED, "more than 4096 shapes span more than 48 bins each");
     if (c.overflow & OVF_HEAVY)
@@ -362,9 +367,55 @@ void cb200_destroy(cb200_system* sys) {
     S->b_gid.release(); S->slab_flags.release(); S->slab_vacant.release();
     if (S->slab_cnt)
         cudaFree(S->slab_cnt);
+    for (int i = 0; i < 2; i++)
+        if (S->aux[i])
+            cudaStreamDestroy(S->aux[i]);
+    for (int i = 0; i < S->aux_ev_made; i++)
+        cudaEventDestroy(S->aux_ev[i]);
     cudaStreamDestroy(S->own_stream);
     delete S;
 }
+
+}  // extern "C"
+
+namespace cb200 {
+static int aux_event(System* S, cudaEvent_t* ev) {
+    if (S->aux_ev_next == 32)  // a step uses about a dozen: an event is re-recorded long after its waits were enqueued
+        S->aux_ev_next = 0;
+    if (S->aux_ev_next == S->aux_ev_made) {
+        CB_CUDA(cudaEventCreateWithFlags(&S->aux_ev[S->aux_ev_made], cudaEventDisableTiming));
+        S->aux_ev_made++;
+    }
+    *ev = S->aux_ev[S->aux_ev_next++];
+    return CB200_OK;
+}
+// Branch i of the step starts here: everything enqueued on the main stream so far happens before it.
+int aux_fork(System* S, int i, cudaStream_t* out) {
+    *out = S->stream;
+    if (!S->aux_enabled)
+        return CB200_OK;
+    if (!S->aux[i])
+        CB_CUDA(cudaStreamCreateWithFlags(&S->aux[i], cudaStreamNonBlocking));
+    cudaEvent_t ev;
+    CB_TRY(aux_event(S, &ev));
+    CB_CUDA(cudaEventRecord(ev, S->stream));
+    CB_CUDA(cudaStreamWaitEvent(S->aux[i], ev, 0));
+    *out = S->aux[i];
+    return CB200_OK;
+}
+// ... and ends here: what follows on the main stream happens after it.
+int aux_join(System* S, int i) {
+    if (!S->aux_enabled || !S->aux[i])
+        return CB200_OK;
+    cudaEvent_t ev;
+    CB_TRY(aux_event(S, &ev));
+    CB_CUDA(cudaEventRecord(ev, S->aux[i]));
+    CB_CUDA(cudaStreamWaitEvent(S->stream, ev, 0));
+    return CB200_OK;
+}
+}  // namespace cb200
+
+extern "C" {
 
 int cb200_set_settings(cb200_system* sys, const cb200_settings* s) {
     System* S = SYS(sys);
@@ -802,6 +853,7 @@ int cb200_integrate(cb200_system* sys) {
 }
 
 static int enqueue_one_step(System* S) {
+    S->aux_ev_next = 0;
     CB_TRY(timer_start(S, "step"));
     CB_TRY(timer_start(S, "update"));
     if (S->set.system_type != 1)  // SMC: formed in k_body_reduce<true> (defer_update_forces below)
@@ -818,14 +870,15 @@ static int enqueue_one_step(System* S) {
     CB_TRY(timer_stop(S, "collision"));
     CB_TRY(timer_start(S, "advance"));
     S->defer_vel_update = S->defer_update_forces = S->set.system_type == 1;  // SMC: done in k_integrate<true> / k_body_reduce<true>
+    S->fuse_aabb = !S->slab_on;  // back-to-back steps: this integration also prepares the next step's sphere boxes
     int rc = S->set.system_type == 1 ? enqueue_smc(S) : enqueue_nsc(S);
     if (rc == CB200_OK) {
         CB_TRY(timer_stop(S, "advance"));
         CB_TRY(timer_start(S, "integrate"));
-        S->fuse_aabb = !S->slab_on;  // back-to-back steps: this integration also prepares the next step's sphere boxes
         rc = enqueue_integrate(S);
-        S->fuse_aabb = false;
     }
+    S->fuse_aabb = false;
+    S->bbox_reset_done = false;
     S->defer_vel_update = S->defer_update_forces = false;
     CB_TRY(rc);
     CB_TRY(timer_stop(S, "integrate"));

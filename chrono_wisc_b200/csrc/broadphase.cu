@@ -90,6 +90,11 @@ __global__ void k_reset_counters(DevCounters* cnt, uint32_t nb, uint32_t ns, boo
         cnt->n_large = 0;
         cnt->n_heavy = 0;
         cnt->ct_body_count = 0;
+        // the counters of the pair pass that follows (pairs.cu pair_cnt_clean)
+        cnt->n_pairs = 0;
+        cnt->n_slow = cnt->n_long = cnt->n_pairq = 0;
+        cnt->n_complex = cnt->n_cslots = 0;
+        cnt->n_cls[0] = cnt->n_cls[1] = cnt->n_cls[2] = cnt->n_cls[3] = 0;
         // cnt->unsupported is sticky: only the host clears it, after it has read it (api.cu clear_unsupported)
     }
 }
@@ -535,7 +540,9 @@ int enqueue_aabb(System* S) {
         S->wpos_parity ^= 1;
     }
     k_reset_counters<<<1, 32, 0, S->stream>>>(S->d_cnt, S->nb, S->ns, spheres_done);
-    CB_CUDA(cudaMemsetAsync(S->heavy.p, 0, S->nb, S->stream));
+    S->pair_cnt_clean = true;
+    if (!(spheres_done && S->body_scratch_clean))  // the fused integration left the heavy flags cleared
+        CB_CUDA(cudaMemsetAsync(S->heavy.p, 0, S->nb, S->stream));
     if (!spheres_done) {
         k_aabb<false><<<grid_for(S, S->ns, 256), 256, 0, S->stream>>>(
             S->ns, nullptr, S->s_meta.p, S->s_lpos.p, S->s_lrot.p, S->s_dims.p, S->s_verts.p, S->pos.p, S->rot.p,
@@ -584,7 +591,9 @@ int enqueue_bins(System* S) {
     const int sgrid = grid_for(S, S->ns, 256);
     S->box_relative = true;
 
-    CB_CUDA(cudaMemsetAsync(S->bin_cursor.p, 0, (size_t)S->cap_bins * 4, S->stream));
+    if (!S->bins_clean)
+        CB_CUDA(cudaMemsetAsync(S->bin_cursor.p, 0, (size_t)S->cap_bins * 4, S->stream));
+    S->bins_clean = false;
     CB_TRY(timer_start(S, "k_bin_count"));
     k_bin_count<<<sgrid, 256, 0, S->stream>>>(gs, env, S->s_meta.p, S->s_wpos.p, S->s_box.p, S->bin_intersections.p,
                                               S->bin_cursor.p, S->large_list.p, S->heavy.p, S->d_cnt);
@@ -593,14 +602,18 @@ int enqueue_bins(System* S) {
                                                   S->cap_entries, S->bin_cursor.p, nullptr, nullptr, nullptr);
     S->launches += 2;
     CB_TRY(scan_bins(S, S->bin_cursor.p, S->bin_start.p, &S->d_cnt->num_bins, S->cap_bins));
+    cudaStream_t s_large;  // large shapes (a container wall) scatter their entries beside everybody else's
+    CB_TRY(aux_fork(S, 0, &s_large));
     CB_TRY(timer_start(S, "k_bin_fill"));
     k_bin_fill<<<sgrid, 256, 0, S->stream>>>(S->ns, env, S->s_meta.p, S->s_wpos.p, S->s_box.p, S->bin_intersections.p,
                                              S->bin_start.p, S->cap_entries, S->bin_cursor.p, S->ent_tmp.p,
                                              S->ent_bin.p, S->d_cnt);
     CB_TRY(timer_stop(S, "k_bin_fill"));
-    k_bin_large<true><<<S->num_sms * 4, 256, 0, S->stream>>>(S->s_meta.p, S->s_wpos.p, S->s_box.p, env, S->large_list.p, S->d_cnt,
+    k_bin_large<true><<<S->num_sms * 4, 256, 0, s_large>>>(S->s_meta.p, S->s_wpos.p, S->s_box.p, env, S->large_list.p, S->d_cnt,
                                                  S->cap_entries, S->bin_cursor.p, S->bin_start.p, S->ent_tmp.p,
                                                  S->ent_bin.p);
+    CB_TRY(aux_join(S, 0));
+    S->bins_clean = true;  // every count was taken back by the scatter (unless the step overflowed: api.cu resets this)
     // the in-bin sort by shape id happens in the pair kernel, on the staged tile (pairs.cu)
     S->launches += 2;
     CB_CUDA(cudaGetLastError());

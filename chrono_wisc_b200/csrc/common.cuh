@@ -279,6 +279,19 @@ struct System {
     DevBuf<uint32_t> slab_vacant;   // vacant owned slots in slot order
     uint32_t* slab_cnt = nullptr;   // device: [0] owned_cap (scan extent) [1] n_vacant [2] arrivals of last unpack
     cudaStream_t own_stream = nullptr;  // the stream cb200_create made (stream may be the caller's, cb200_set_stream)
+    // Side branches of a step (api.cu aux_fork / aux_join): short latency-bound kernels that do not depend on each other
+    // (wall-bin pairs | slow bins | long bins; container-body sums | per-body sums) run on two auxiliary streams
+    // between an event fork and an event join -- parallel branches of the step graph when the step is captured.
+    cudaStream_t aux[2] = {nullptr, nullptr};
+    cudaEvent_t aux_ev[32] = {};
+    int aux_ev_made = 0, aux_ev_next = 0;
+    bool aux_enabled = true;
+    // Scratch that a completed step leaves zeroed, so the next one need not clear it (one graph node less each): the
+    // bin histogram is counted back down to zero by the scatter; the integration of a whole step clears the body
+    // degrees, the incidence cursors and the heavy flags.  Anything that can leave them dirty (an overflow, a
+    // reallocation, a stage call) resets the flag and the next enqueue clears them the slow way.
+    bool bins_clean = false, body_scratch_clean = false, pair_cnt_clean = false;
+    bool bbox_reset_done = false;  // k_reset_bbox of this step already ran on a side branch (smc.cu)
 
     // ---- scan scratch / counters ----
     DevBuf<uint64_t> scan_tmp;
@@ -337,6 +350,10 @@ bool comm_multi(const System* S);     // S is one slab of a decomposed system (h
 double* comm_gsum(System* S);         // 24 doubles of device scratch for sums over all ranks
 int comm_halo6(Group& g, int which);  // owners' 6 doubles per body (0: n_w, 1: n_w0) -> the neighbours' ghost copies
 int comm_allreduce(Group& g, int first, int n);  // gsum[first..first+n) summed over all ranks, in place
+int aux_fork(System* S, int i, cudaStream_t* out);  // `out`: the stream to launch the branch on
+int aux_join(System* S, int i);
+bool integrate_fuses_aabb(const System* S);
+int enqueue_reset_bbox(System* S, cudaStream_t st);
 int enqueue_nsc_group(Group& g);      // nsc.cu: the NSC solve of all systems of the group, slot by slot
 
 // exclusive scans (scan.cu) over a device-side element count (*n_dev <= n_cap). n+1 outputs: out[n] = total.

@@ -55,6 +55,10 @@ struct AabbArgs {
     const double* b_rad;
     double* s_wpos;
     double envelope;
+    // per-body scratch of the step that ends here, cleared for the next one (common.cuh body_scratch_clean)
+    uint32_t* b_deg;
+    uint32_t* b_cursor;
+    uint8_t* heavy;
 };
 
 template <bool VEL, bool AABB>
@@ -138,6 +142,11 @@ __global__ void __launch_bounds__(256) k_integrate(uint32_t nb, double h, const 
             }
         }
         if (AABB) {
+            if (A.b_deg) {  // SMC steps only: NSC keeps its CSR by body for the queries that follow a step
+                A.b_deg[b] = 0u, A.b_cursor[b] = 0u, A.heavy[b] = 0;
+                if (b == 0)
+                    A.b_deg[nb] = 0u;
+            }
             const int32_t si = A.b_sphere[b];
             if (si >= 0) {
                 // k_aabb<false>: centred sphere, Rotate(0, q) + p == p
@@ -174,20 +183,36 @@ int enqueue_update_forces(System* S) {
     return CB200_OK;
 }
 
+bool integrate_fuses_aabb(const System* S) {
+    return S->fuse_aabb && S->b_sphere.p && S->s_wpos_alt.p && S->ns > 0 && !S->meta_dirty;
+}
+
+// The fused integration merges the next step's sphere boxes into the global box: it starts from an empty one.  Anywhere
+// after k_bin_count (the only reader of the previous box) will do, so the SMC path runs it on a side branch.
+int enqueue_reset_bbox(System* S, cudaStream_t st) {
+    if (S->bbox_reset_done)
+        return CB200_OK;
+    k_reset_bbox<<<1, 32, 0, st>>>(S->d_cnt);
+    S->launches++;
+    S->bbox_reset_done = true;
+    return CB200_OK;
+}
+
 int enqueue_integrate(System* S) {
     if (S->nb == 0)
         return CB200_OK;
     const int grid = blocks_for(S->nb, 256);
-    const bool fuse = S->fuse_aabb && S->b_sphere.p && S->s_wpos_alt.p && S->ns > 0 && !S->meta_dirty;
-    AabbArgs A = {S->b_sphere.p, S->b_rad.p, S->s_wpos_alt.p, S->set.collision_envelope};
+    const bool fuse = integrate_fuses_aabb(S);
+    const bool clear = fuse && S->set.system_type == 1 && S->b_deg.p && S->b_cursor.p;
+    AabbArgs A = {S->b_sphere.p, S->b_rad.p, S->s_wpos_alt.p, S->set.collision_envelope,
+                  clear ? S->b_deg.p : nullptr, S->b_cursor.p, S->heavy.p};
 #define INTEGRATE(VEL, AABB)                                                                                          \
     k_integrate<VEL, AABB><<<grid, 256, 0, S->stream>>>(S->nb, S->set.step_size, S->bflags.p, S->vel.p, S->pos.p,      \
                                                         S->rot.p, S->mass.p, S->inv_inertia.p, S->hf.p, A,                     \
                                                         S->has_vlim ? S->vlim.p : nullptr, S->d_cnt)
-    if (fuse) {
-        k_reset_bbox<<<1, 32, 0, S->stream>>>(S->d_cnt);
-        S->launches++;
-    }
+    if (fuse)
+        CB_TRY(enqueue_reset_bbox(S, S->stream));
+    S->bbox_reset_done = false;
     CB_TRY(timer_start(S, "k_integrate"));
     if (fuse) {
         if (S->defer_vel_update)
@@ -202,6 +227,7 @@ int enqueue_integrate(System* S) {
 #undef INTEGRATE
     CB_TRY(timer_stop(S, "k_integrate"));
     S->sphere_aabb_valid = fuse;
+    S->body_scratch_clean = clear;
     S->launches++;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;

@@ -1243,16 +1243,21 @@ template <bool CPLX>
 static int enqueue_pair_pass_t(System* S, int mode, int64_t* out, uint32_t cap) {
     const double env = S->set.collision_envelope;
     const int algorithm = S->set.narrowphase_algorithm;
-    if (mode == MODE_CONTACTS)
+    // the counters of this pass: cleared by k_reset_counters at the start of a collision pass (broadphase.cu); a second
+    // pass over the same bins (pair list download) clears them itself
+    const bool clean = S->pair_cnt_clean;
+    S->pair_cnt_clean = false;
+    if (mode == MODE_CONTACTS && !clean)
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_pairs, 0, 4, S->stream));
     const int gm = grid_for(S, S->cap_entries, PAIR_TILE, 4);  // 4 resident CTAs per SM, tiles grid-stride
-    CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_slow, 0, 12, S->stream));  // n_slow, n_long, n_pairq
+    if (!clean)
+        CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_slow, 0, 12, S->stream));  // n_slow, n_long, n_pairq
     const int gs = S->num_sms * 8;
     CplxArgs X = {};
     X.s_lrot = S->s_lrot.p, X.rot = S->rot.p, X.s_verts = S->s_verts.p, X.cplx_out = S->cplx_out.p;
     X.cap_slots = S->cap_cslots;
     uint64_t* cmask = CPLX ? S->ent_cmask.p : nullptr;
-    if (CPLX) {
+    if (CPLX && !clean) {
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_complex, 0, 4, S->stream));
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_cslots, 0, 4, S->stream));
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_cls[0], 0, 16, S->stream));
@@ -1263,6 +1268,11 @@ static int enqueue_pair_pass_t(System* S, int mode, int64_t* out, uint32_t cap) 
         S->ent_shape.p, S->ent_mask.p, cmask, S->ent_off.p, S->slow_bins.p, S->long_bins.p,
         reinterpret_cast<uint2*>(S->pair_q.p), S->cap_pairq, S->d_cnt);
     CB_TRY(timer_stop(S, "k_pair_masks"));
+    // three independent branches consume the queues the tile kernel filled (they touch disjoint bins, or only add
+    // bits with atomics): wall-bin pairs here, whole slow bins and long bins on the side streams
+    cudaStream_t s_slow, s_long;
+    CB_TRY(aux_fork(S, 0, &s_slow));
+    CB_TRY(aux_fork(S, 1, &s_long));
     CB_TRY(timer_start(S, "k_pair_queue"));
     k_pair_queue<CPLX><<<grid_for(S, S->cap_pairq, 128, 8), 128, 0, S->stream>>>(
         S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
@@ -1270,17 +1280,17 @@ static int enqueue_pair_pass_t(System* S, int mode, int64_t* out, uint32_t cap) 
         reinterpret_cast<unsigned long long*>(S->ent_mask.p), reinterpret_cast<unsigned long long*>(cmask),
         S->ent_off.p, S->d_cnt);
     CB_TRY(timer_stop(S, "k_pair_queue"));
-    CB_TRY(timer_start(S, "k_pair_masks_slow"));
-    k_pair_masks_slow<CPLX><<<gs, 32 * SLOW_WARPS, 0, S->stream>>>(
+    k_pair_masks_slow<CPLX><<<gs, 32 * SLOW_WARPS, 0, s_slow>>>(
         S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_tmp.p, S->ent_shape.p, S->ent_bin.p,
         S->bin_start.p, env, algorithm, mode, S->ent_mask.p, cmask, S->ent_off.p, S->slow_bins.p, X, S->d_cnt);
-    k_long_sort<<<64, 256, 0, S->stream>>>(S->ent_tmp.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p, S->long_bins.p,
-                                           S->d_cnt);
-    k_long_rows<CPLX, false><<<dim3(8, 64), 128, 0, S->stream>>>(
+    k_long_sort<<<64, 256, 0, s_long>>>(S->ent_tmp.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p, S->long_bins.p,
+                                        S->d_cnt);
+    k_long_rows<CPLX, false><<<dim3(8, 64), 128, 0, s_long>>>(
         S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
         env, algorithm, mode, S->ent_mask.p, cmask, S->ent_off.p, nullptr, nullptr, 0, nullptr, nullptr, nullptr,
         S->long_bins.p, X, S->d_cnt);
-    CB_TRY(timer_stop(S, "k_pair_masks_slow"));
+    CB_TRY(aux_join(S, 0));
+    CB_TRY(aux_join(S, 1));
     S->launches += 5;
     if (CPLX) {
         k_cplx_collect<<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
@@ -1293,17 +1303,19 @@ static int enqueue_pair_pass_t(System* S, int mode, int64_t* out, uint32_t cap) 
         S->launches += 2;
     }
     CB_TRY(scan_u32(S, S->ent_off.p, S->ent_off.p, &S->d_cnt->n_intersections, S->cap_entries));
+    CB_TRY(aux_fork(S, 1, &s_long));  // the rows of long bins are stored beside the others
     CB_TRY(timer_start(S, "k_pair_store"));
     k_pair_store<CPLX><<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
         S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
         env, algorithm, mode, S->ent_mask.p, S->ent_off.p, out, cap, cmask, CPLX ? S->ent_cbase.p : nullptr,
         CPLX ? S->cplx_rec.p : nullptr, CPLX ? S->cplx_n.p : nullptr, CPLX ? S->c_src.p : nullptr, S->c_bids.p,
         S->c_mats.p, X, S->d_cnt);
-    k_long_rows<CPLX, true><<<dim3(8, 64), 128, 0, S->stream>>>(
+    CB_TRY(timer_stop(S, "k_pair_store"));
+    k_long_rows<CPLX, true><<<dim3(8, 64), 128, 0, s_long>>>(
         S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
         env, algorithm, mode, nullptr, nullptr, nullptr, S->ent_off.p, out, cap, CPLX ? S->c_src.p : nullptr,
         S->c_bids.p, S->c_mats.p, S->long_bins.p, X, S->d_cnt);
-    CB_TRY(timer_stop(S, "k_pair_store"));
+    CB_TRY(aux_join(S, 1));
     S->launches += 2;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;

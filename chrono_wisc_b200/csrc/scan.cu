@@ -128,19 +128,25 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_onepass(const typename L:
     __shared__ T sm[33];
     __shared__ uint32_t s_ticket;
     __shared__ T s_prefix;
-    if (cnt->overflow)
-        return;
-    const size_t n = *n_dev;
-    if (n == 0) {
-        if (blockIdx.x == 0 && threadIdx.x == 0)
-            out[0] = T(0);
-        return;
-    }
-    const uint32_t ntiles = (uint32_t)((n + SCAN_TILE - 1) / SCAN_TILE);
+    // Control block: [0] tile ticket, [1] CTAs done, [2] epoch.  Tile flags carry the epoch of the launch that wrote
+    // them (flag = epoch << 2 | status), so records of earlier scans read as "not ready" and nothing has to be cleared
+    // between scans: the last CTA to leave resets the ticket and advances the epoch.  Every CTA takes part in that
+    // count, also one that skips its work, so the block stays consistent whatever the overflow mask does meanwhile.
     uint32_t* ticket = reinterpret_cast<uint32_t*>(state_raw);
+    const uint32_t ep = reinterpret_cast<volatile uint32_t*>(ticket)[2] + 1u;
+    const uint32_t F1 = ep << 2 | 1u, F2 = ep << 2 | 2u;
+    const size_t n = *n_dev;
+    __shared__ uint32_t s_skip;  // one answer per CTA: the mask may be raised by a side branch while this kernel runs
+    if (threadIdx.x == 0)
+        s_skip = cnt->overflow != 0u || n == 0;
+    __syncthreads();
+    const bool skip = s_skip != 0u;
+    if (n == 0 && blockIdx.x == 0 && threadIdx.x == 0)
+        out[0] = T(0);
+    const uint32_t ntiles = (uint32_t)((n + SCAN_TILE - 1) / SCAN_TILE);
     volatile TileState* st = reinterpret_cast<volatile TileState*>(state_raw + 4);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    while (true) {
+    while (!skip) {
         if (threadIdx.x == 0)
             s_ticket = atomicAdd(ticket, 1u);
         __syncthreads();
@@ -163,11 +169,11 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_onepass(const typename L:
             if (tile == 0) {
                 st[0].incl = (uint64_t)total;
                 __threadfence();
-                st[0].flag = 2u;
+                st[0].flag = F2;
             } else {
                 st[tile].agg = (uint64_t)total;
                 __threadfence();
-                st[tile].flag = 1u;
+                st[tile].flag = F1;
             }
         }
         if (tile > 0 && wid == 0) {
@@ -175,16 +181,16 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_onepass(const typename L:
             int look = (int)tile - 1;
             while (true) {
                 const int idx = look - lane;
-                uint32_t f = 2u;  // lanes before tile 0 act as a zero-valued terminator
+                uint32_t f = F2;  // lanes before tile 0 act as a zero-valued terminator
                 T v = 0;
                 if (idx >= 0) {
                     do {
                         f = st[idx].flag;
-                    } while (f == 0u);
+                    } while (f != F1 && f != F2);  // anything else was left by an earlier scan
                     __threadfence();
-                    v = (T)(f == 2u ? st[idx].incl : st[idx].agg);
+                    v = (T)(f == F2 ? st[idx].incl : st[idx].agg);
                 }
-                const unsigned pm = __ballot_sync(0xffffffffu, f == 2u);
+                const unsigned pm = __ballot_sync(0xffffffffu, f == F2);
                 const int first = pm ? __ffs(pm) - 1 : 31;  // nearest predecessor holding an inclusive prefix
                 T c = lane <= first ? v : T(0);
 #pragma unroll
@@ -199,7 +205,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_onepass(const typename L:
                 s_prefix = prefix;
                 st[tile].incl = (uint64_t)(prefix + total);
                 __threadfence();
-                st[tile].flag = 2u;
+                st[tile].flag = F2;
             }
         }
         __syncthreads();
@@ -216,6 +222,15 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_onepass(const typename L:
             out[n] = carry + total;
         __syncthreads();
     }
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(ticket + 1, 1u) == gridDim.x - 1) {  // everybody else has left
+            ticket[0] = 0u;
+            ticket[1] = 0u;
+            __threadfence();
+            ticket[2] = ep;
+        }
+    }
 }
 
 template <typename L>
@@ -229,9 +244,10 @@ static int scan_impl(System* S, const typename L::in_t* in, typename L::out_t* o
         if (S->capturing)
             return set_error(CB200_ERR_STATE, "scan scratch must be allocated before a step is captured");
         invalidate_step_graph(S);
+        CB_CUDA(cudaStreamSynchronize(S->stream));
         CB_TRY(S->scan_tmp.reserve(words));
+        CB_CUDA(cudaMemsetAsync(S->scan_tmp.p, 0, S->scan_tmp.cap * sizeof(uint64_t), S->stream));  // once: epoch 0
     }
-    CB_CUDA(cudaMemsetAsync(S->scan_tmp.p, 0, words * sizeof(uint64_t), S->stream));
     const int grid = grid_for(S, n_cap, SCAN_TILE, 2);
     k_scan_onepass<L><<<grid, SCAN_THREADS, 0, S->stream>>>(in, out, S->scan_tmp.p, n_dev, S->d_cnt);
     S->launches += 1;

@@ -818,8 +818,11 @@ int enqueue_smc(System* S) {
     P.nm = S->nm_smc;
     const uint32_t chunk_cap = S->cap_contacts / HEAVY_CHUNK + 1;
     const int cgrid = grid_for(S, S->cap_contacts, 256);
-    CB_CUDA(cudaMemsetAsync(S->b_deg.p, 0, (size_t)(nb + 1) * 4, S->stream));
-    CB_CUDA(cudaMemsetAsync(S->b_cursor.p, 0, (size_t)nb * 4, S->stream));
+    if (!S->body_scratch_clean) {
+        CB_CUDA(cudaMemsetAsync(S->b_deg.p, 0, (size_t)(nb + 1) * 4, S->stream));
+        CB_CUDA(cudaMemsetAsync(S->b_cursor.p, 0, (size_t)nb * 4, S->stream));
+    }
+    S->body_scratch_clean = false;
     const int fgrid = grid_for(S, S->cap_contacts, 128, 16);
     GenArgs G;
     G.c_shapes = S->c_shapes.p, G.meta = S->s_meta.p, G.s_wpos = S->s_wpos.p, G.s_wrot = S->s_wrot.p;
@@ -858,11 +861,18 @@ int enqueue_smc(System* S) {
                                                                               S->sh_neigh.p, S->d_cnt);
         S->launches++;
     }
+    // side branch: the partial sums of container bodies need the force records only
+    cudaStream_t hs;
+    CB_TRY(aux_fork(S, 0, &hs));
+    k_heavy_list<<<blocks_for(nb, 256), 256, 0, hs>>>(nb, S->heavy.p, S->heavy_list.p, S->d_cnt);
+    k_heavy_partial<<<dim3(grid_for(S, chunk_cap, 1, 4), 4), 256, 0, hs>>>(
+        S->c_bids.p, S->ct_force.p, S->ct_torque.p, S->heavy_list.p, S->d_cnt, chunk_cap, S->heavy_part.p);
+    if (integrate_fuses_aabb(S))
+        CB_TRY(enqueue_reset_bbox(S, hs));
     CB_TRY(scan_u32(S, S->b_deg.p, S->b_deg.p, &S->d_cnt->n_bodies, nb));
     CB_TRY(timer_start(S, "k_inc_fill"));
     k_inc_fill<<<cgrid, 256, 0, S->stream>>>(S->c_bids.p, S->heavy.p, S->b_deg.p, S->b_cursor.p, S->b_inc.p, S->d_cnt);
     CB_TRY(timer_stop(S, "k_inc_fill"));
-    k_heavy_list<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->heavy.p, S->heavy_list.p, S->d_cnt);
     CB_TRY(timer_start(S, "k_body_reduce"));
     UpdArgs U;
     U.g = mk3(st.gravity[0], st.gravity[1], st.gravity[2]);
@@ -876,8 +886,7 @@ int enqueue_smc(System* S) {
                                                                          S->ct_force.p, S->ct_torque.p, st.step_size,
                                                                          S->b_force.p, S->hf.p, U, S->d_cnt);
     CB_TRY(timer_stop(S, "k_body_reduce"));
-    k_heavy_partial<<<dim3(grid_for(S, chunk_cap, 1, 4), 4), 256, 0, S->stream>>>(
-        S->c_bids.p, S->ct_force.p, S->ct_torque.p, S->heavy_list.p, S->d_cnt, chunk_cap, S->heavy_part.p);
+    CB_TRY(aux_join(S, 0));
     k_heavy_final<<<MAX_HEAVY, 256, 0, S->stream>>>(S->heavy_list.p, S->d_cnt, chunk_cap, S->heavy_part.p,
                                                     st.step_size, S->b_force.p, S->hf.p, S->d_cnt);
     if (!S->defer_vel_update)

@@ -26,8 +26,8 @@ for r in rows:
         continue
     if r[0].isdigit():
         k = (fname, int(r[0]))
-        agg[k] += int(r[ie] or 0)
-        samp[k] += int(r[sm] or 0)
+        agg[k] += int(r[ie]) if r[ie].isdigit() else 0
+        samp[k] += int(r[sm]) if r[sm].isdigit() else 0
         src[k] = r[1]
 tot, ts = sum(agg.values()) or 1, sum(samp.values()) or 1
 print(f"total {tot / 1e6:.2f} M warp instructions, {ts} samples")
