@@ -118,6 +118,11 @@ _SIGNATURES = {
     "cb200_nsc_project": (C.c_int, [_P, C.c_int, _P]),
     "cb200_get_timer": (C.c_int, [_P, C.c_char_p, C.POINTER(C.c_double)]),
     "cb200_kernel_launches": (C.c_int64, [_P]),
+    "cb200_filter_contacts": (C.c_int, [_P, C.c_int, _P]),
+    "cb200_download_contact_materials": (C.c_int, [_P, C.c_int, _P, _P]),
+    "cb200_upload_contact_materials": (C.c_int, [_P, C.c_int, _P]),
+    "cb200_report_contacts": (C.c_int, [_P, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "cb200_selftest_scan": (C.c_int, [_P, C.c_int64, C.c_uint32, C.c_int, _P]),
     "cb200_device_array": (C.c_int, [_P, C.c_char_p, C.POINTER(_P), C.POINTER(C.c_int64)]),
     "cb200_set_stream": (C.c_int, [_P, _P, C.c_int]),
     "cb200_enqueue_steps": (C.c_int, [_P, C.c_int]),

@@ -338,7 +338,7 @@ void cb200_destroy(cb200_system* sys) {
     cudaStreamSynchronize(S->stream);
     comm_release(S);
 #define REL(x) S->x.release()
-    REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(bflags); REL(heavy); REL(b_sphere); REL(b_rad); REL(c_own); REL(vlim); REL(b_inbox);
+    REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(bflags); REL(heavy); REL(b_sphere); REL(b_rad); REL(c_own); REL(vlim); REL(b_inbox); REL(report); REL(mat_ovr);
     REL(s_type); REL(s_body); REL(s_fam); REL(s_mat); REL(s_lpos); REL(s_lrot); REL(s_dims); REL(general_ids); REL(s_verts); REL(sh_neigh); REL(sh_touch); REL(sh_disp); REL(sh_relvel); REL(sh_dur); REL(s_wpos); REL(s_wpos_alt); REL(s_wrot);
     REL(s_box); REL(s_meta); REL(mat_smc); REL(mat_nsc); REL(bin_intersections); REL(bin_start); REL(bin_cursor);
     REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_mask); REL(ent_off); REL(slow_bins); REL(long_bins); REL(pair_q); REL(large_list); REL(pairs);
@@ -413,6 +413,29 @@ int aux_join(System* S, int i) {
     CB_CUDA(cudaStreamWaitEvent(S->stream, ev, 0));
     return CB200_OK;
 }
+}  // namespace cb200
+
+namespace cb200 {
+// gather of fixed-size records: dst[j] = src[idx[j]], W 4-byte words per record
+template <int W>
+__global__ void __launch_bounds__(256) k_gather_words(uint32_t m, const uint32_t* __restrict__ idx,
+                                                      const uint32_t* __restrict__ src, uint32_t* __restrict__ dst) {
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < m * W; t += gridDim.x * blockDim.x)
+        dst[t] = src[(size_t)idx[t / W] * W + t % W];
+}
+
+template <int W, typename T>
+static int compact_array(System* S, DevBuf<T>& buf, uint32_t m, const uint32_t* idx_dev, uint32_t* scratch) {
+    static_assert(sizeof(T) % 4 == 0 || W * 4 % sizeof(T) == 0, "record made of 4-byte words");
+    if (!buf.p || m == 0)
+        return CB200_OK;
+    k_gather_words<W><<<grid_for(S, (size_t)m * W, 256), 256, 0, S->stream>>>(
+        m, idx_dev, reinterpret_cast<const uint32_t*>(buf.p), scratch);
+    CB_CUDA(cudaMemcpyAsync(buf.p, scratch, (size_t)m * W * 4, cudaMemcpyDeviceToDevice, S->stream));
+    S->launches++;
+    return CB200_OK;
+}
+
 }  // namespace cb200
 
 extern "C" {
@@ -1322,6 +1345,176 @@ int cb200_download_contact_forces(cb200_system* sys, double* ct_force, double* c
     return CB200_OK;
 }
 
+// ---- contact callbacks: the host walks the contact list between the collision stage and the solver ----
+
+// ChCollisionSystem::NarrowphaseCallback (OnNarrowphase returning false drops the contact,
+// src/chrono/collision/multicore/ChCollisionSystemMulticore.cpp:361-368): keep[i] != 0 keeps contact i; the list is
+// compacted in place, order preserved.
+int cb200_filter_contacts(cb200_system* sys, int n, const uint8_t* keep) {
+    System* S = SYS(sys);
+    if (!S || n < 0 || (n && !keep))
+        return set_error(CB200_ERR_ARG, "bad argument to cb200_filter_contacts");
+    CB_CUDA(cudaSetDevice(S->device));
+    CB_TRY(fetch_counters(S));
+    if ((uint32_t)n != S->h_cnt->n_contacts)
+        return set_error(CB200_ERR_ARG, "keep[] must have one entry per contact of the current list");
+    std::vector<uint32_t> idx;
+    idx.reserve(n);
+    for (int i = 0; i < n; i++)
+        if (keep[i])
+            idx.push_back((uint32_t)i);
+    const uint32_t m = (uint32_t)idx.size();
+    if (m == (uint32_t)n)
+        return CB200_OK;
+    uint32_t *d_idx = nullptr, *scratch = nullptr;
+    CB_CUDA(cudaMalloc(&d_idx, (size_t)std::max(m, 1u) * 4));
+    CB_CUDA(cudaMalloc(&scratch, (size_t)std::max(m, 1u) * 24));  // largest record: 3 doubles
+    CB_CUDA(cudaMemcpyAsync(d_idx, idx.data(), (size_t)m * 4, cudaMemcpyHostToDevice, S->stream));
+    int rc = CB200_OK;
+#define COMPACT(W, buf) if (rc == CB200_OK) rc = compact_array<W>(S, S->buf, m, d_idx, scratch)
+    COMPACT(2, c_shapes);
+    COMPACT(2, c_bids);
+    COMPACT(1, c_mats);
+    if (use_complex(S))
+        COMPACT(1, c_src);
+    if (S->contacts_geom_valid) {
+        COMPACT(6, c_norm);
+        COMPACT(6, c_pta);
+        COMPACT(6, c_ptb);
+        COMPACT(2, c_depth);
+        COMPACT(2, c_erad);
+    }
+#undef COMPACT
+    if (rc == CB200_OK) {
+        CB_CUDA(cudaMemcpyAsync(&S->d_cnt->n_contacts, &m, 4, cudaMemcpyHostToDevice, S->stream));
+        CB_CUDA(cudaStreamSynchronize(S->stream));
+        S->h_cnt->n_contacts = m;
+        S->mat_ovr_valid = false;
+    }
+    cudaFree(d_idx), cudaFree(scratch);
+    return rc;
+}
+
+// The composite material of every contact as ChContactContainerMulticoreSMC/NSC::AddContact forms it before the
+// AddContactCallback sees it (MC/collision/ChContactContainerMulticoreSMC.cpp:123-174, ...NSC.cpp:126-187).
+// SMC, 13 per contact: mu, muRoll, muSpin, E, G, adhesion, adhesionMultDMT, adhesionSPerko, cr, kn, kt, gn, gt.
+// NSC, 8 per contact: mu (sliding), muRoll, muSpin, cohesion, compliance, complianceT, complianceRoll, complianceSpin.
+int cb200_download_contact_materials(cb200_system* sys, int capacity, double* composite, int* stride) {
+    System* S = SYS(sys);
+    if (!S || !stride)
+        return set_error(CB200_ERR_ARG, "null argument");
+    CB_CUDA(cudaSetDevice(S->device));
+    const bool smc = S->set.system_type == 1;
+    const int W = smc ? 13 : 8, TW = smc ? (int)SMC_MAT_STRIDE : (int)NSC_MAT_STRIDE;
+    *stride = W;
+    CB_TRY(fetch_counters(S));
+    const size_t nc = S->h_cnt->n_contacts;
+    if (nc == 0 || !composite)
+        return CB200_OK;
+    if ((size_t)capacity < nc)
+        return set_error(CB200_ERR_ARG, "output capacity smaller than num_rigid_contacts");
+    const int nm = smc ? S->nm_smc : S->nm_nsc;
+    DevBuf<double>& tab = smc ? S->mat_smc : S->mat_nsc;
+    if (nm == 0 || !tab.p)
+        return set_error(CB200_ERR_STATE, "no materials set");
+    std::vector<double> t((size_t)nm * nm * TW);
+    std::vector<uint32_t> mm(nc);
+    CB_TRY(download(S, tab.p, t.data(), t.size()));
+    CB_TRY(download(S, S->c_mats.p, mm.data(), nc));
+    std::vector<double> ovr;
+    if (S->mat_ovr_valid) {
+        ovr.resize(nc * TW);
+        CB_TRY(download(S, S->mat_ovr.p, ovr.data(), ovr.size()));
+    }
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    for (size_t i = 0; i < nc; i++) {
+        const double* M = S->mat_ovr_valid ? ovr.data() + i * TW
+                                           : t.data() + ((size_t)(mm[i] & 0xffff) * nm + (mm[i] >> 16)) * TW;
+        for (int k = 0; k < W; k++)
+            composite[W * i + k] = M[k];
+    }
+    return CB200_OK;
+}
+
+// ... and the records the callback handed back: they replace the table lookup for the current contact list (until the
+// next collision pass).
+int cb200_upload_contact_materials(cb200_system* sys, int n, const double* composite) {
+    System* S = SYS(sys);
+    if (!S || n < 0 || (n && !composite))
+        return set_error(CB200_ERR_ARG, "bad argument to cb200_upload_contact_materials");
+    CB_CUDA(cudaSetDevice(S->device));
+    CB_TRY(fetch_counters(S));
+    if ((uint32_t)n != S->h_cnt->n_contacts)
+        return set_error(CB200_ERR_ARG, "one record per contact of the current list expected");
+    if (n == 0)
+        return CB200_OK;
+    const bool smc = S->set.system_type == 1;
+    const int W = smc ? 13 : 8, TW = smc ? (int)SMC_MAT_STRIDE : (int)NSC_MAT_STRIDE;
+    std::vector<double> h((size_t)n * TW);
+    bool aux = false;
+    for (int i = 0; i < n; i++) {
+        double* o = h.data() + (size_t)i * TW;
+        for (int k = 0; k < W; k++)
+            o[k] = composite[(size_t)W * i + k];
+        if (smc) {  // the tabulated Hertz damping ratio follows the (possibly changed) restitution
+            const double cr = o[8], eps = std::numeric_limits<double>::epsilon();
+            const double loge = (cr < eps) ? std::log(eps) : std::log(cr);
+            o[13] = loge / std::sqrt(loge * loge + M_PI * M_PI);
+        } else {
+            for (int k = 1; k < 8; k++)
+                aux |= o[k] != 0;
+        }
+    }
+    if (S->mat_ovr.cap < h.size())
+        invalidate_step_graph(S);
+    CB_TRY(S->mat_ovr.reserve(h.size()));
+    CB_TRY(upload(S, S->mat_ovr, 0, h.data(), h.size()));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    if (aux && !S->nsc_has_aux) {
+        S->nsc_has_aux = 1;
+        invalidate_step_graph(S);
+    }
+    S->mat_ovr_valid = true;
+    return CB200_OK;
+}
+
+// ChContactContainerMulticore::ReportAllContacts, batched: one row per contact with the arguments of OnReportContact
+int cb200_report_contacts(cb200_system* sys, int capacity, double* pA, double* pB, double* plane, double* distance,
+                          double* eff_radius, double* force, double* torque, int32_t* body_ids, int* count) {
+    System* S = SYS(sys);
+    if (!S || !count)
+        return set_error(CB200_ERR_ARG, "null argument");
+    CB_CUDA(cudaSetDevice(S->device));
+    CB_TRY(fetch_counters(S));
+    const size_t nc = S->h_cnt->n_contacts;
+    *count = (int)nc;
+    if (nc == 0 || capacity <= 0)
+        return CB200_OK;
+    if ((size_t)capacity < nc)
+        return set_error(CB200_ERR_ARG, "output capacity smaller than num_rigid_contacts");
+    CB_TRY(enqueue_report(S));
+    const int W = 21;
+    std::vector<double> h(W * nc);
+    CB_TRY(download(S, S->report.p, h.data(), W * nc));
+    CB_TRY(download(S, S->c_depth.p, distance, nc));
+    CB_TRY(download(S, S->c_erad.p, eff_radius, nc));
+    CB_TRY(download(S, S->c_bids.p, body_ids, 2 * nc));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    for (size_t i = 0; i < nc; i++) {
+        const double* r = h.data() + W * i;
+        for (int a = 0; a < 3; a++) {
+            if (pA) pA[3 * i + a] = r[a];
+            if (pB) pB[3 * i + a] = r[3 + a];
+            if (force) force[3 * i + a] = r[15 + a];
+            if (torque) torque[3 * i + a] = r[18 + a];
+        }
+        if (plane)
+            for (int a = 0; a < 9; a++)
+                plane[9 * i + a] = r[6 + a];
+    }
+    return CB200_OK;
+}
+
 int cb200_download_body_contact_forces(cb200_system* sys, double* force, double* torque) {
     System* S = SYS(sys);
     CB_CUDA(cudaSetDevice(S->device));
@@ -1366,6 +1559,45 @@ int cb200_get_timer(cb200_system* sys, const char* name, double* seconds) {
 }
 
 int64_t cb200_kernel_launches(cb200_system* sys) { return SYS(sys)->launches; }
+
+// Self-test of the one-pass scan every list of the step is built with: exclusive scan of n pseudo-random counts, run
+// `repeats` times back to back (the scratch is not cleared between scans), compared with a host scan.
+int cb200_selftest_scan(cb200_system* sys, int64_t n, uint32_t seed, int repeats, int64_t* mismatches) {
+    System* S = SYS(sys);
+    if (!S || n < 0 || n > (int64_t)1 << 31 || !mismatches || repeats < 1)
+        return set_error(CB200_ERR_ARG, "bad argument to cb200_selftest_scan");
+    CB_CUDA(cudaSetDevice(S->device));
+    std::vector<uint32_t> h((size_t)n + 1), ref((size_t)n + 1), got((size_t)n + 1);
+    uint32_t x = seed * 2654435761u + 1u, acc = 0;
+    for (int64_t i = 0; i < n; i++) {
+        x = x * 1664525u + 1013904223u;
+        h[i] = (x >> 24) % 7u;
+        ref[i] = acc;
+        acc += h[i];
+    }
+    ref[n] = acc;
+    uint32_t *d_in = nullptr, *d_out = nullptr, *d_n = nullptr;
+    CB_CUDA(cudaMalloc(&d_in, ((size_t)n + 4) * 4));
+    CB_CUDA(cudaMalloc(&d_out, ((size_t)n + 4) * 4));
+    CB_CUDA(cudaMalloc(&d_n, 4));
+    const uint32_t n32 = (uint32_t)n;
+    CB_CUDA(cudaMemcpyAsync(d_in, h.data(), (size_t)n * 4, cudaMemcpyHostToDevice, S->stream));
+    CB_CUDA(cudaMemcpyAsync(d_n, &n32, 4, cudaMemcpyHostToDevice, S->stream));
+    *mismatches = 0;
+    int rc = CB200_OK;
+    for (int r = 0; r < repeats && rc == CB200_OK; r++) {
+        CB_CUDA(cudaMemsetAsync(d_out, 0xff, ((size_t)n + 1) * 4, S->stream));
+        rc = scan_u32(S, d_in, d_out, d_n, (size_t)n + (size_t)(r % 3) * 1000);  // capacity above the extent, as in a step
+        if (rc != CB200_OK)
+            break;
+        CB_CUDA(cudaMemcpyAsync(got.data(), d_out, ((size_t)n + 1) * 4, cudaMemcpyDeviceToHost, S->stream));
+        CB_CUDA(cudaStreamSynchronize(S->stream));
+        for (int64_t i = 0; i <= n; i++)
+            *mismatches += got[i] != ref[i];
+    }
+    cudaFree(d_in), cudaFree(d_out), cudaFree(d_n);
+    return rc;
+}
 
 int cb200_device_array(cb200_system* sys, const char* name, void** dev_ptr, int64_t* count) {
     System* S = SYS(sys);

@@ -196,6 +196,8 @@ struct System {
     int nm_smc = 0, nm_nsc = 0;
     DevBuf<double> mat_smc;  // nm*nm*SMC_MAT_STRIDE
     DevBuf<double> mat_nsc;
+    DevBuf<double> mat_ovr;  // per-contact composite records of the current contact list (AddContactCallback), or unused
+    bool mat_ovr_valid = false;
 
     // ---- broadphase (CMC/ChCollisionData.h:199-221); capacities cap_* are what the kernels check against ----
     uint32_t cap_bins = 0, cap_entries = 0, cap_contacts = 0, cap_pairs = 0;
@@ -237,6 +239,7 @@ struct System {
     // CT_STRIDE N_c: per contact (force on body 2 [body 1 gets the negative], pad) (torque on body 1, pad) (torque on
     // body 2, pad), torques in the body frames -- three 32-byte sectors
     DevBuf<double> ct_force;
+    DevBuf<double> report;      // 21 per contact: the batch of cb200_report_contacts (report.cu)
     DevBuf<double> ct_torque;   // unused (kept for the release list)
     // MultiStep tangential displacement history, 20 slots per body (allocated on first use, smc.cu)
     DevBuf<int32_t> sh_neigh;   // 3 x 20 nb
@@ -350,6 +353,7 @@ bool comm_multi(const System* S);     // S is one slab of a decomposed system (h
 double* comm_gsum(System* S);         // 24 doubles of device scratch for sums over all ranks
 int comm_halo6(Group& g, int which);  // owners' 6 doubles per body (0: n_w, 1: n_w0) -> the neighbours' ghost copies
 int comm_allreduce(Group& g, int first, int n);  // gsum[first..first+n) summed over all ranks, in place
+int enqueue_report(System* S);  // report.cu
 int aux_fork(System* S, int i, cudaStream_t* out);  // `out`: the stream to launch the branch on
 int aux_join(System* S, int i);
 bool integrate_fuses_aabb(const System* S);

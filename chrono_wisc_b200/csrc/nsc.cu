@@ -277,6 +277,7 @@ __global__ void __launch_bounds__(256) k_nsc_body_prep(uint32_t nb, const uint8_
 struct NscSetupParams {
     double inv_h, inv_hpa, inv_hhpa, alpha, recovery_speed;
     int mode, nm, has_aux;
+    const double* mat_ovr;  // per-contact composite records set through an AddContactCallback (api.cu), else null
 };
 
 // Per contact: frame, composite material, b (Build_b), E (Build_E), R_full = -b - D^T M_invk, gamma = 0, and the
@@ -306,7 +307,8 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_setup(NscSetupParams P, con
         F.sA = mk3(c_pta[3 * i], c_pta[3 * i + 1], c_pta[3 * i + 2]) - mk3(pos[3 * bA], pos[3 * bA + 1], pos[3 * bA + 2]);
         F.sB = mk3(c_ptb[3 * i], c_ptb[3 * i + 1], c_ptb[3 * i + 2]) - mk3(pos[3 * bB], pos[3 * bB + 1], pos[3 * bB + 2]);
         const uint32_t mm = c_mats[i];
-        const double* M = mat + ((size_t)(mm & 0xffff) * P.nm + (mm >> 16)) * NSC_MAT_STRIDE;
+        const double* M = P.mat_ovr ? P.mat_ovr + (size_t)i * NSC_MAT_STRIDE
+                                    : mat + ((size_t)(mm & 0xffff) * P.nm + (mm >> 16)) * NSC_MAT_STRIDE;
         F.mu = M[0];
         double* fo = frame + (size_t)NSC_FRAME * i;
         fo[0] = F.U.x, fo[1] = F.U.y, fo[2] = F.U.z, fo[3] = F.sA.x, fo[4] = F.sA.y, fo[5] = F.sA.z;
@@ -1133,6 +1135,7 @@ static int nsc_setup(Group& g) {
         P.mode = st.solver_mode;
         P.nm = S->nm_nsc;
         P.has_aux = S->nsc_has_aux;
+        P.mat_ovr = S->mat_ovr_valid ? S->mat_ovr.p : nullptr;
         k_nsc_setup<ROWS><<<G, NSC_THREADS, 0, S->stream>>>(P, S->c_bids.p, S->c_mats.p, S->c_norm.p, S->c_pta.p,
                                                             S->c_ptb.p, S->c_depth.p, S->pos.p, S->bflags.p,
                                                             S->mat_nsc.p, S->n_w0.p, S->n_frame.p, S->n_aux.p,

@@ -1360,6 +1360,7 @@ int enqueue_pairs_only(System* S, bool want_pairs, bool want_contacts, bool defe
     if (want_contacts) {
         CB_TRY(enqueue_pair_pass(S, MODE_CONTACTS, S->c_shapes.p, S->cap_contacts));
         S->contacts_geom_valid = false;
+        S->mat_ovr_valid = false;  // per-contact material records belonged to the previous list
         if (!defer_geometry)
             CB_TRY(enqueue_contact_gen(S));
     }

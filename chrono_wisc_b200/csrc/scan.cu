@@ -127,7 +127,6 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_onepass(const typename L:
     typedef typename L::in_t I;
     __shared__ T sm[33];
     __shared__ uint32_t s_ticket;
-    __shared__ T s_prefix;
     // Control block: [0] tile ticket, [1] CTAs done, [2] epoch.  Tile flags carry the epoch of the launch that wrote
     // them (flag = epoch << 2 | status), so records of earlier scans read as "not ready" and nothing has to be cleared
     // between scans: the last CTA to leave resets the ticket and advances the epoch.  Every CTA takes part in that
@@ -166,50 +165,48 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_onepass(const typename L:
         T total;
         T ex = block_excl_scan(s, &total, sm);
         if (threadIdx.x == 0) {
-            if (tile == 0) {
-                st[0].incl = (uint64_t)total;
-                __threadfence();
-                st[0].flag = F2;
-            } else {
-                st[tile].agg = (uint64_t)total;
-                __threadfence();
-                st[tile].flag = F1;
-            }
+            st[tile].agg = (uint64_t)total;
+            __threadfence();
+            st[tile].flag = F1;
         }
-        if (tile > 0 && wid == 0) {
-            T prefix = 0;
-            int look = (int)tile - 1;
-            while (true) {
-                const int idx = look - lane;
-                uint32_t f = F2;  // lanes before tile 0 act as a zero-valued terminator
-                T v = 0;
-                if (idx >= 0) {
-                    do {
-                        f = st[idx].flag;
-                    } while (f != F1 && f != F2);  // anything else was left by an earlier scan
-                    __threadfence();
-                    v = (T)(f == F2 ? st[idx].incl : st[idx].agg);
+        // Look-back by the whole CTA at once: thread i takes the aggregate of tile - 1 - i, thread 0 also the inclusive
+        // prefix of the tile just before that window (only systems of more than SCAN_THREADS tiles have one).  The
+        // predecessors were handed out earlier, so they are running and publish their aggregate before they wait for
+        // anything: one polling round instead of a chain of warp-sized hops.
+        T mine = 0;
+        {
+            const int idx = (int)tile - 1 - (int)threadIdx.x;
+            if (idx >= 0) {
+                uint32_t f;
+                do {
+                    f = st[idx].flag;
+                } while (f != F1 && f != F2);  // anything else was left by an earlier scan
+                __threadfence();
+                mine = (T)st[idx].agg;
+            }
+            const int far = (int)tile - 1 - SCAN_THREADS;
+            if (threadIdx.x == 0 && far >= 0) {
+                while (st[far].flag != F2) {
                 }
-                const unsigned pm = __ballot_sync(0xffffffffu, f == F2);
-                const int first = pm ? __ffs(pm) - 1 : 31;  // nearest predecessor holding an inclusive prefix
-                T c = lane <= first ? v : T(0);
-#pragma unroll
-                for (int d = 16; d > 0; d >>= 1)
-                    c += __shfl_xor_sync(0xffffffffu, c, d);
-                prefix += c;
-                if (pm)
-                    break;
-                look -= 32;
-            }
-            if (lane == 0) {
-                s_prefix = prefix;
-                st[tile].incl = (uint64_t)(prefix + total);
                 __threadfence();
-                st[tile].flag = F2;
+                mine += (T)st[far].incl;
             }
         }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1)
+            mine += __shfl_xor_sync(0xffffffffu, mine, d);
+        if (lane == 0)
+            sm[wid] = mine;
         __syncthreads();
-        const T carry = tile > 0 ? s_prefix : T(0);
+        T carry = 0;
+#pragma unroll
+        for (int w = 0; w < SCAN_THREADS / 32; w++)
+            carry += sm[w];
+        if (threadIdx.x == 0) {
+            st[tile].incl = (uint64_t)(carry + total);
+            __threadfence();
+            st[tile].flag = F2;
+        }
         ex += carry;
         T o[SCAN_ITEMS];
 #pragma unroll

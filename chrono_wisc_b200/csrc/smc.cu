@@ -25,6 +25,7 @@ struct SmcParams {
     int force_model, adhesion_model, displ_mode, use_mat_props;
     double char_vel, min_slip_vel, min_roll_vel, min_spin_vel, dT;
     int nm;
+    const double* mat_ovr;  // per-contact composite records set through an AddContactCallback (api.cu), else null
 };
 
 struct BodyView {
@@ -194,7 +195,8 @@ __global__ void __launch_bounds__(128, 4) k_smc_force(SmcParams P, GenArgs G, Sh
 
         // composite material (:140-160)
         const double m_eff = B1.mass * B2.mass / (B1.mass + B2.mass);
-        const double* M = mat + ((size_t)(mm & 0xffff) * P.nm + (mm >> 16)) * SMC_MAT_STRIDE;
+        const double* M = P.mat_ovr ? P.mat_ovr + (size_t)i * SMC_MAT_STRIDE
+                                    : mat + ((size_t)(mm & 0xffff) * P.nm + (mm >> 16)) * SMC_MAT_STRIDE;
         const double mu_eff = M[0];
         double muRoll_eff = M[1], muSpin_eff = M[2];
         const double E_eff = M[3], G_eff = M[4];
@@ -535,6 +537,24 @@ __device__ __forceinline__ void reduce_sorted(const uint32_t* __restrict__ codes
             add_record(ct_force, c[r], r == 0, F, T);
 }
 
+// hf of a body before its contacts: h (m g + F_applied, T_applied - w x J w), the operations of k_update_forces
+__device__ __forceinline__ void base_hf(uint32_t b, const UpdArgs& U, double h, d3& bF, d3& bT) {
+    const double m = U.mass[b];
+    const double* v = U.vel + 6 * (size_t)b;
+    const d3 w = mk3(v[3], v[4], v[5]);
+    const d3 Jw = mk3(U.inertia[3 * b] * w.x, U.inertia[3 * b + 1] * w.y, U.inertia[3 * b + 2] * w.z);
+    const d3 gyro = cross3(w, Jw);
+    d3 F = U.g * m;
+    d3 T = mk3(0);
+    if (U.fapp) {
+        const double* a = U.fapp + 6 * (size_t)b;
+        F += mk3(a[0], a[1], a[2]);
+        T += mk3(a[3], a[4], a[5]);
+    }
+    bF = h * F;
+    bT = h * (T - gyro);
+}
+
 // one thread per body: add the body's contacts in ascending contact index, then hf += h * (F, T)
 template <bool UPD>
 __global__ void __launch_bounds__(256) k_body_reduce(uint32_t nb, const uint8_t* __restrict__ heavy,
@@ -548,26 +568,8 @@ __global__ void __launch_bounds__(256) k_body_reduce(uint32_t nb, const uint8_t*
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     bool touched = false;
     d3 bF = mk3(0), bT = mk3(0);
-    if (UPD && b < nb) {
-        const double m = U.mass[b];
-        const double* v = U.vel + 6 * (size_t)b;
-        const d3 w = mk3(v[3], v[4], v[5]);
-        const d3 Jw = mk3(U.inertia[3 * b] * w.x, U.inertia[3 * b + 1] * w.y, U.inertia[3 * b + 2] * w.z);
-        const d3 gyro = cross3(w, Jw);
-        d3 F = U.g * m;
-        d3 T = mk3(0);
-        if (U.fapp) {
-            const double* a = U.fapp + 6 * (size_t)b;
-            F += mk3(a[0], a[1], a[2]);
-            T += mk3(a[3], a[4], a[5]);
-        }
-        bF = h * F;
-        bT = h * (T - gyro);
-        if (heavy[b]) {  // its contacts are added by k_heavy_final
-            double* q = hf + 6 * (size_t)b;
-            q[0] = bF.x, q[1] = bF.y, q[2] = bF.z, q[3] = bT.x, q[4] = bT.y, q[5] = bT.z;
-        }
-    }
+    if (UPD && b < nb && !heavy[b])
+        base_hf(b, U, h, bF, bT);  // a container body's hf is formed by k_heavy_final<true>
     if (b < nb && !heavy[b]) {
         const uint32_t s = off[b], d = off[b + 1] - s;
         d3 F = mk3(0), T = mk3(0);
@@ -693,11 +695,12 @@ __global__ void __launch_bounds__(256) k_heavy_partial(const int32_t* __restrict
     }
 }
 
+template <bool UPD>
 __global__ void __launch_bounds__(256) k_heavy_final(const uint32_t* __restrict__ list,
                                                      const DevCounters* __restrict__ cnt_in, uint32_t chunk_cap,
                                                      const double* __restrict__ part, double h,
                                                      double* __restrict__ b_force, double* __restrict__ hf,
-                                                     DevCounters* __restrict__ cnt) {
+                                                     UpdArgs U, DevCounters* __restrict__ cnt) {
     __shared__ double sm[8][7];
     if (cnt_in->overflow)
         return;
@@ -730,10 +733,20 @@ __global__ void __launch_bounds__(256) k_heavy_final(const uint32_t* __restrict_
         const uint32_t body = list[hI];
         double* o = b_force + 6 * (size_t)body;
         double* f = hf + 6 * (size_t)body;
-        for (int q = 0; q < 6; q++) {
-            o[q] = s[q];
-            if (s[6] > 0)
-                f[q] += h * s[q];
+        if (UPD) {  // whole step: nobody has written this body's hf yet (k_body_reduce<true> leaves it out)
+            d3 bF, bT;
+            base_hf(body, U, h, bF, bT);
+            const double base[6] = {bF.x, bF.y, bF.z, bT.x, bT.y, bT.z};
+            for (int q = 0; q < 6; q++) {
+                o[q] = s[q];
+                f[q] = s[6] > 0 ? base[q] + h * s[q] : base[q];
+            }
+        } else {
+            for (int q = 0; q < 6; q++) {
+                o[q] = s[q];
+                if (s[6] > 0)
+                    f[q] += h * s[q];
+            }
         }
         if (s[6] > 0)
             atomicAdd(&cnt->ct_body_count, 1u);
@@ -816,6 +829,7 @@ int enqueue_smc(System* S) {
     P.min_spin_vel = st.min_spin_vel;
     P.dT = st.step_size;
     P.nm = S->nm_smc;
+    P.mat_ovr = S->mat_ovr_valid ? S->mat_ovr.p : nullptr;
     const uint32_t chunk_cap = S->cap_contacts / HEAVY_CHUNK + 1;
     const int cgrid = grid_for(S, S->cap_contacts, 256);
     if (!S->body_scratch_clean) {
@@ -867,6 +881,12 @@ int enqueue_smc(System* S) {
     k_heavy_list<<<blocks_for(nb, 256), 256, 0, hs>>>(nb, S->heavy.p, S->heavy_list.p, S->d_cnt);
     k_heavy_partial<<<dim3(grid_for(S, chunk_cap, 1, 4), 4), 256, 0, hs>>>(
         S->c_bids.p, S->ct_force.p, S->ct_torque.p, S->heavy_list.p, S->d_cnt, chunk_cap, S->heavy_part.p);
+    UpdArgs U;
+    U.g = mk3(st.gravity[0], st.gravity[1], st.gravity[2]);
+    U.mass = S->mass.p, U.inertia = S->inertia.p, U.vel = S->vel.p, U.fapp = S->has_fapp ? S->fapp.p : nullptr;
+    if (S->defer_update_forces)  // the body's whole hf is formed there: no dependence on k_body_reduce
+        k_heavy_final<true><<<MAX_HEAVY, 256, 0, hs>>>(S->heavy_list.p, S->d_cnt, chunk_cap, S->heavy_part.p,
+                                                       st.step_size, S->b_force.p, S->hf.p, U, S->d_cnt);
     if (integrate_fuses_aabb(S))
         CB_TRY(enqueue_reset_bbox(S, hs));
     CB_TRY(scan_u32(S, S->b_deg.p, S->b_deg.p, &S->d_cnt->n_bodies, nb));
@@ -874,9 +894,6 @@ int enqueue_smc(System* S) {
     k_inc_fill<<<cgrid, 256, 0, S->stream>>>(S->c_bids.p, S->heavy.p, S->b_deg.p, S->b_cursor.p, S->b_inc.p, S->d_cnt);
     CB_TRY(timer_stop(S, "k_inc_fill"));
     CB_TRY(timer_start(S, "k_body_reduce"));
-    UpdArgs U;
-    U.g = mk3(st.gravity[0], st.gravity[1], st.gravity[2]);
-    U.mass = S->mass.p, U.inertia = S->inertia.p, U.vel = S->vel.p, U.fapp = S->has_fapp ? S->fapp.p : nullptr;
     if (S->defer_update_forces)
         k_body_reduce<true><<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->heavy.p, S->b_deg.p, S->b_inc.p,
                                                                         S->ct_force.p, S->ct_torque.p, st.step_size,
@@ -887,8 +904,9 @@ int enqueue_smc(System* S) {
                                                                          S->b_force.p, S->hf.p, U, S->d_cnt);
     CB_TRY(timer_stop(S, "k_body_reduce"));
     CB_TRY(aux_join(S, 0));
-    k_heavy_final<<<MAX_HEAVY, 256, 0, S->stream>>>(S->heavy_list.p, S->d_cnt, chunk_cap, S->heavy_part.p,
-                                                    st.step_size, S->b_force.p, S->hf.p, S->d_cnt);
+    if (!S->defer_update_forces)  // hf += h (F, T) on top of what k_update_forces wrote
+        k_heavy_final<false><<<MAX_HEAVY, 256, 0, S->stream>>>(S->heavy_list.p, S->d_cnt, chunk_cap, S->heavy_part.p,
+                                                               st.step_size, S->b_force.p, S->hf.p, U, S->d_cnt);
     if (!S->defer_vel_update)
         k_vel_update<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->bflags.p, S->mass.p, S->inv_inertia.p, S->hf.p,
                                                                  S->vel.p, S->d_cnt);

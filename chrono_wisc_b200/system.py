@@ -40,6 +40,13 @@ def _ptr(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
+# composite material records handed to an AddContactCallback (ChContactMaterialCompositeSMC / NSC members)
+COMPOSITE_FIELDS_SMC = ("mu_eff", "muRoll_eff", "muSpin_eff", "E_eff", "G_eff", "adhesion_eff", "adhesionMultDMT_eff",
+                        "adhesionSPerko_eff", "cr_eff", "kn", "kt", "gn", "gt")
+COMPOSITE_FIELDS_NSC = ("sliding_friction", "rolling_friction", "spinning_friction", "cohesion", "compliance",
+                        "complianceT", "complianceRoll", "complianceSpin")
+
+
 class ChSystemMulticore:
     """Common part (reference: ChSystemMulticore, src/chrono_multicore/physics/ChSystemMulticore.{h,cpp})."""
 
@@ -56,6 +63,8 @@ class ChSystemMulticore:
         self.num_bodies = 0
         self.num_shapes = 0
         self.ch_time = 0.0
+        self._narrow_callback = None
+        self._add_contact_callback = None
 
     def __del__(self):
         try:
@@ -189,8 +198,62 @@ class ChSystemMulticore:
 
     def DoSteps(self, n):
         self._push_settings()
+        if self._narrow_callback is not None or self._add_contact_callback is not None:
+            for _ in range(int(n)):  # the callbacks sit between the collision stage and the solver: staged steps
+                self.Update()
+                self.RunCollision(7)
+                self.RunContactCallbacks()
+                self.RunSolver()
+                self.Integrate()
+            return
         check(self._lib.cb200_do_steps(self._h, int(n)))
         self.ch_time += n * self.settings.step_size
+
+    # ---- contact callbacks -----------------------------------------------------------------------
+    def RegisterNarrowphaseCallback(self, callback):
+        """``ChCollisionSystem::RegisterNarrowphaseCallback``: ``callback(cinfo) -> bool``; False drops the contact
+        (ChCollisionSystemMulticore.cpp:361-368).  ``cinfo``: dict(bodyA, bodyB, shapeA, shapeB, vN, vpA, vpB, distance,
+        eff_radius).  None unregisters."""
+        self._narrow_callback = callback
+
+    def RegisterAddContactCallback(self, callback):
+        """``ChContactContainer::RegisterAddContactCallback``: ``callback(cinfo, material)`` may modify the composite
+        material record of the contact in place (a numpy row; fields in ``COMPOSITE_FIELDS_SMC / _NSC``).  As in the
+        reference (ChContactContainerMulticoreSMC.cpp:147-165) ``cinfo['vpA'] / ['vpB']`` passed to THIS callback are
+        the contact points plus the body positions."""
+        self._add_contact_callback = callback
+
+    def RunContactCallbacks(self):
+        if self._narrow_callback is None and self._add_contact_callback is None:
+            return
+        c = self.GetContacts()
+        n = c["depth"].size
+        if n == 0:
+            return
+        sa, sb = (c["shape_ids"] >> 32).astype(np.int64), (c["shape_ids"] & 0xFFFFFFFF).astype(np.int64)
+
+        def cinfo(i, offset_a=0.0, offset_b=0.0):
+            return dict(bodyA=int(c["body_ids"][i, 0]), bodyB=int(c["body_ids"][i, 1]), shapeA=int(sa[i]),
+                        shapeB=int(sb[i]), vN=c["normal"][i], vpA=c["pt_a"][i] + offset_a, vpB=c["pt_b"][i] + offset_b,
+                        distance=float(c["depth"][i]), eff_radius=float(c["eff_radius"][i]))
+
+        keep = np.ones(n, dtype=np.uint8)
+        if self._narrow_callback is not None:
+            for i in range(n):
+                keep[i] = 1 if self._narrow_callback(cinfo(i)) else 0
+            if not keep.all():
+                check(self._lib.cb200_filter_contacts(self._h, n, _ptr(keep)))
+        if self._add_contact_callback is not None:
+            kept = np.flatnonzero(keep)
+            stride = C.c_int()
+            check(self._lib.cb200_download_contact_materials(self._h, 0, None, C.byref(stride)))
+            mats = np.empty((kept.size, stride.value))
+            check(self._lib.cb200_download_contact_materials(self._h, kept.size, _ptr(mats), C.byref(stride)))
+            pos, _, _ = self.GetBodyState()
+            for j, i in enumerate(kept):
+                ci = cinfo(i, pos[c["body_ids"][i, 0]], pos[c["body_ids"][i, 1]])
+                self._add_contact_callback(ci, mats[j])
+            check(self._lib.cb200_upload_contact_materials(self._h, kept.size, _ptr(mats)))
 
     # the reference's own seams, for stage-level parity tests
     def Update(self):
@@ -257,6 +320,28 @@ class ChSystemMulticore:
                                                 _ptr(out["depth"]), _ptr(out["eff_radius"]), _ptr(out["body_ids"]),
                                                 _ptr(out["shape_ids"])))
         return out
+
+    def GetContactReport(self):
+        """The batch behind ``ReportAllContacts``: one row per contact with the arguments of
+        ``ReportContactCallback::OnReportContact`` (ChContactContainerMulticore.cpp:65-149)."""
+        n = self.GetCounts().num_rigid_contacts
+        out = dict(pA=np.empty((n, 3)), pB=np.empty((n, 3)), plane=np.empty((n, 3, 3)), distance=np.empty(n),
+                   eff_radius=np.empty(n), force=np.empty((n, 3)), torque=np.empty((n, 3)),
+                   body_ids=np.empty((n, 2), np.int32))
+        cnt = C.c_int()
+        check(self._lib.cb200_report_contacts(self._h, n, _ptr(out["pA"]), _ptr(out["pB"]), _ptr(out["plane"]),
+                                              _ptr(out["distance"]), _ptr(out["eff_radius"]), _ptr(out["force"]),
+                                              _ptr(out["torque"]), _ptr(out["body_ids"]), C.byref(cnt)))
+        return out
+
+    def ReportAllContacts(self, callback):
+        """``ChContactContainer::ReportAllContacts``: ``callback(pA, pB, plane, distance, eff_radius, force, torque,
+        bodyA, bodyB)`` once per contact, in list order; a False return stops the walk (as ``proceed`` does)."""
+        r = self.GetContactReport()
+        for i in range(r["distance"].size):
+            if callback(r["pA"][i], r["pB"][i], r["plane"][i], r["distance"][i], r["eff_radius"][i], r["force"][i],
+                        r["torque"][i], int(r["body_ids"][i, 0]), int(r["body_ids"][i, 1])) is False:
+                break
 
     def GetContactForces(self):
         """host_data.ct_force / ct_torque, two rows per contact (body 1, body 2)."""

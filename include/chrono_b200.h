@@ -214,6 +214,26 @@ int cb200_download_contacts(cb200_system* sys, double* normal, double* pt_a, dou
 int cb200_download_contact_forces(cb200_system* sys, double* ct_force, double* ct_torque);
 /* ChSystemMulticoreSMC::GetBodyContactForce/Torque for all bodies (MC/physics/ChSystemMulticoreSMC.cpp:74-90):
  * 3 doubles per body each, zero for bodies without contacts. */
+/* Contact callbacks.  The reference calls them on the host, one contact at a time, between the narrowphase and the
+ * solver (ChCollisionSystemMulticore::ReportContacts, src/chrono/collision/multicore/ChCollisionSystemMulticore.cpp:
+ * 326-372 -> ChContactContainerMulticoreSMC/NSC::AddContact).  Here the caller runs its loop over the downloaded list
+ * (cb200_download_contacts) after cb200_run_collision and hands the outcome back before cb200_run_solver_*:
+ *   - NarrowphaseCallback::OnNarrowphase == false  -> keep[i] = 0 in cb200_filter_contacts (list compacted in place);
+ *   - AddContactCallback::OnAddContact(cinfo, composite material) -> cb200_download_contact_materials gives the
+ *     composite records the container formed (SMC 13 doubles per contact: mu, muRoll, muSpin, E, G, adhesion, DMT,
+ *     Perko, cr, kn, kt, gn, gt; NSC 8: mu, muRoll, muSpin, cohesion, compliance, complianceT,
+ *     complianceRoll, complianceSpin), cb200_upload_contact_materials the modified ones; they hold for the current list. */
+int cb200_filter_contacts(cb200_system* sys, int n, const uint8_t* keep);
+int cb200_download_contact_materials(cb200_system* sys, int capacity, double* composite, int* stride);
+int cb200_upload_contact_materials(cb200_system* sys, int n, const double* composite);
+/* ChContactContainerMulticore::ReportAllContacts (src/chrono_multicore/collision/ChContactContainerMulticore.cpp:65-149),
+ * batched: row i holds the arguments the reference passes to ReportContactCallback::OnReportContact for contact i --
+ * pA, pB (absolute), plane (3x3 row-major, X axis = contact normal, SetFromAxisX(normal, VECT_Y)), distance,
+ * eff_radius, react_forces and react_torques in the contact frame (NSC: multipliers / step, SMC: force and torque on
+ * body B, the torque moved to the contact point), the two body indices.  Any output pointer may be NULL; capacity in
+ * contacts; *count = num_rigid_contacts.  The caller runs its callback loop over the batch. */
+int cb200_report_contacts(cb200_system* sys, int capacity, double* pA, double* pB, double* plane, double* distance,
+                          double* eff_radius, double* force, double* torque, int32_t* body_ids, int* count);
 int cb200_download_body_contact_forces(cb200_system* sys, double* force, double* torque);
 /* host_data.hf (h * generalized force, 6 per body) as consumed by ComputeInvMassMatrix */
 int cb200_download_hf(cb200_system* sys, double* hf);
@@ -246,6 +266,10 @@ int cb200_nsc_project(cb200_system* sys, int local_mode, double* gamma);
 int cb200_get_timer(cb200_system* sys, const char* name, double* seconds);
 /* Number of kernels this library launched since creation (for bench.py's gpu_launches). */
 int64_t cb200_kernel_launches(cb200_system* sys);
+/* Self-test of the device scan (the replacement of the thrust::exclusive_scan / inclusive_scan calls of
+ * src/chrono/collision/multicore/ChBroadphase.cpp:271-301 and ChNarrowphase.cpp:141-150): n pseudo-random counts,
+ * `repeats` scans back to back, every output compared with a host scan; *mismatches = entries that differ. */
+int cb200_selftest_scan(cb200_system* sys, int64_t n, uint32_t seed, int repeats, int64_t* mismatches);
 
 /* --- device-pointer access for zero-copy tooling and multi-GPU halo exchange ---------------------- */
 /* names: "pos","rot","vel","hf","aabb_min","aabb_max","contact_normal",... ; returns device pointer + element count */

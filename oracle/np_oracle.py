@@ -162,3 +162,52 @@ def smc_step(scene, ref, pos, rot, vel, fast=True, history=None):
     v2 = velocity_update(vel, hf, scene["mass"], inv_inertia, active)
     p2, q2 = integrate(pos, rot, v2, h, active)
     return p2, q2, v2, dict(contacts=c, hf=hf, body_force=F, body_torque=T)
+
+
+def contact_plane(normal):
+    """ChMatrix33::SetFromAxisX(normal, VECT_Y) (src/chrono/core/ChMatrix33.h:389-395 over
+    ChVector3::GetDirectionAxesAsX, ChVector3.h:899-921): columns X (the normal), Y, Z."""
+    tiny = np.finfo(float).tiny
+
+    def normalize(v):
+        n = np.sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2])
+        if n < tiny:
+            return np.array([1.0, 0.0, 0.0]), False
+        return v * (1.0 / n), True
+
+    X, ok = normalize(np.asarray(normal, float))
+    sugg = np.array([0.0, 1.0, 0.0])
+    Z, ok = normalize(np.cross(X, sugg))
+    idx = 0
+    while not ok:
+        sugg[idx] += 1.0
+        Z, ok = normalize(np.cross(X, sugg))
+        idx += 1
+    Y = np.cross(Z, X)
+    return np.stack([X, Y, Z], axis=1)
+
+
+def report_contacts(method, contacts, pos, rot, h, ct_force=None, ct_torque=None, gamma=None, rows=3):
+    """ChContactContainerMulticore::ReportAllContacts (MC/collision/ChContactContainerMulticore.cpp:65-149): the
+    arguments of OnReportContact per contact.  `gamma` in the reference's layout (normals | u v pairs | spinning)."""
+    n = contacts["depth"].size
+    planes, F, T = np.empty((n, 3, 3)), np.zeros((n, 3)), np.zeros((n, 3))
+    for i in range(n):
+        P = contact_plane(contacts["normal"][i])
+        planes[i] = P
+        if method == "nsc":
+            F[i, 0] = gamma[i] / h
+            if rows >= 3:
+                F[i, 1], F[i, 2] = gamma[n + 2 * i] / h, gamma[n + 2 * i + 1] / h
+            if rows >= 6:
+                T[i] = gamma[3 * n + 3 * i:3 * n + 3 * i + 3] / h
+        else:
+            b = contacts["body_ids"][i, 1]
+            R = rotmat(np.asarray(rot[b], float)[None])[0]
+            f_abs, t_loc = ct_force[2 * i + 1], ct_torque[2 * i + 1]
+            f_loc = R.T @ f_abs
+            pB_loc = R.T @ (contacts["pt_b"][i] - pos[b])
+            t_abs = R @ (t_loc - np.cross(pB_loc, f_loc))
+            F[i], T[i] = P.T @ f_abs, P.T @ t_abs
+    return dict(pA=contacts["pt_a"], pB=contacts["pt_b"], plane=planes, distance=contacts["depth"],
+                eff_radius=contacts["eff_radius"], force=F, torque=T, body_ids=contacts["body_ids"])

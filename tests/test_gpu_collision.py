@@ -158,3 +158,18 @@ def test_empty_system():
     sys = cw.ChSystemMulticoreSMC()
     sys.RunCollision(7)
     assert sys.GetNumContacts() == 0
+
+
+@pytest.mark.parametrize("n", [0, 1, 17, 8192, 8193, 300_000, 2_750_000, 4_300_000, 9_000_000])
+def test_device_scan_against_host_scan(n):
+    """The one-pass scan behind every list offset: sizes around one tile (8192 items), the bench's entry count, and
+    more than 512 tiles (the look-back then needs the inclusive prefix in front of its window); repeated scans reuse
+    the scratch without clearing it."""
+    import ctypes as C
+
+    from chrono_wisc_b200._lib import check
+
+    sys = cw.ChSystemMulticoreSMC()
+    bad = C.c_int64(-1)
+    check(sys._lib.cb200_selftest_scan(sys._h, n, 7, 4, C.byref(bad)))
+    assert bad.value == 0
