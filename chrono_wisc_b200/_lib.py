@@ -118,6 +118,8 @@ _SIGNATURES = {
     "cb200_nsc_project": (C.c_int, [_P, C.c_int, _P]),
     "cb200_get_timer": (C.c_int, [_P, C.c_char_p, C.POINTER(C.c_double)]),
     "cb200_kernel_launches": (C.c_int64, [_P]),
+    "cb200_set_bilaterals": (C.c_int, [_P, C.c_int, _P, _P, _P, _P, C.c_int, C.c_double]),
+    "cb200_download_bilateral_gamma": (C.c_int, [_P, _P, _P, _P]),
     "cb200_filter_contacts": (C.c_int, [_P, C.c_int, _P]),
     "cb200_download_contact_materials": (C.c_int, [_P, C.c_int, _P, _P]),
     "cb200_upload_contact_materials": (C.c_int, [_P, C.c_int, _P]),

@@ -338,7 +338,7 @@ void cb200_destroy(cb200_system* sys) {
     cudaStreamSynchronize(S->stream);
     comm_release(S);
 #define REL(x) S->x.release()
-    REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(bflags); REL(heavy); REL(b_sphere); REL(b_rad); REL(c_own); REL(vlim); REL(b_inbox); REL(report); REL(mat_ovr);
+    REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(bflags); REL(heavy); REL(b_sphere); REL(b_rad); REL(c_own); REL(vlim); REL(b_inbox); REL(report); REL(mat_ovr); REL(bil_ids); REL(bil_cq); REL(bil_b); REL(bil_R); REL(bil_gamma); REL(bil_N); REL(bil_vec); REL(bil_info);
     REL(s_type); REL(s_body); REL(s_fam); REL(s_mat); REL(s_lpos); REL(s_lrot); REL(s_dims); REL(general_ids); REL(s_verts); REL(sh_neigh); REL(sh_touch); REL(sh_disp); REL(sh_relvel); REL(sh_dur); REL(s_wpos); REL(s_wpos_alt); REL(s_wrot);
     REL(s_box); REL(s_meta); REL(mat_smc); REL(mat_nsc); REL(bin_intersections); REL(bin_start); REL(bin_cursor);
     REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_mask); REL(ent_off); REL(slow_bins); REL(long_bins); REL(pair_q); REL(large_list); REL(pairs);

@@ -239,6 +239,13 @@ struct System {
     // CT_STRIDE N_c: per contact (force on body 2 [body 1 gets the negative], pad) (torque on body 1, pad) (torque on
     // body 2, pad), torques in the body frames -- three 32-byte sectors
     DevBuf<double> ct_force;
+    // ---- bilateral rows (bilateral.cu) ----
+    uint32_t n_bil = 0;
+    int bil_max_iter = 100;
+    double bil_tol = 1e-4;
+    DevBuf<int32_t> bil_ids;   // 2 per row
+    DevBuf<double> bil_cq;     // 12 per row: Cq_a | Cq_b
+    DevBuf<double> bil_b, bil_R, bil_gamma, bil_N, bil_vec, bil_info;
     DevBuf<double> report;      // 21 per contact: the batch of cb200_report_contacts (report.cu)
     DevBuf<double> ct_torque;   // unused (kept for the release list)
     // MultiStep tangential displacement history, 20 slots per body (allocated on first use, smc.cu)
@@ -354,6 +361,7 @@ double* comm_gsum(System* S);         // 24 doubles of device scratch for sums o
 int comm_halo6(Group& g, int which);  // owners' 6 doubles per body (0: n_w, 1: n_w0) -> the neighbours' ghost copies
 int comm_allreduce(Group& g, int first, int n);  // gsum[first..first+n) summed over all ranks, in place
 int enqueue_report(System* S);  // report.cu
+int enqueue_bilateral(System* S);  // bilateral.cu
 int aux_fork(System* S, int i, cudaStream_t* out);  // `out`: the stream to launch the branch on
 int aux_join(System* S, int i);
 bool integrate_fuses_aabb(const System* S);

@@ -907,6 +907,7 @@ int enqueue_smc(System* S) {
     if (!S->defer_update_forces)  // hf += h (F, T) on top of what k_update_forces wrote
         k_heavy_final<false><<<MAX_HEAVY, 256, 0, S->stream>>>(S->heavy_list.p, S->d_cnt, chunk_cap, S->heavy_part.p,
                                                                st.step_size, S->b_force.p, S->hf.p, U, S->d_cnt);
+    CB_TRY(enqueue_bilateral(S));  // joints / motors: hf += D_b gamma_b (RunTimeStep :816-842)
     if (!S->defer_vel_update)
         k_vel_update<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->bflags.p, S->mass.p, S->inv_inertia.p, S->hf.p,
                                                                  S->vel.p, S->d_cnt);

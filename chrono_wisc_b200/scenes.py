@@ -165,6 +165,36 @@ def settling_smc(nx=32, ny=32, nz=8, radius=0.02, seed=12345, grid="density", bi
     return b.finish([smc_material(young=young, friction=mu, restitution=cr)], settings)
 
 
+def mixer_smc(nx=24, ny=24, nz=6, radius=0.02, seed=5, step=5e-4, blade=(0.3, 0.02, 0.06), blade_mass=5.0):
+    """demo_MCORE_mixerSMC-style scene (config E flavour): a sphere bed in a box with a blade (a box body) standing in
+    it, to be driven about the vertical axis by a speed motor (links.motor_rotation_speed_z).  Returns the scene, the
+    index of the blade body and its anchor point."""
+    b = SceneBuilder()
+    spacing = 2.02 * radius
+    sx, sy = nx * spacing + radius, ny * spacing + radius
+    sz = max(0.5, (nz + 4) * spacing)
+    bin_body = b.add_bodies(1.0, (1.0, 1.0, 1.0), [[0.0, 0.0, 0.0]], active=0, collide=1)
+    b.add_box_container(bin_body, (0, 0, sz / 2), (sx, sy, sz), 0.2, faces=(2, 2, -1))
+    m = 2000.0 * 4.0 / 3.0 * np.pi * radius ** 3
+    pos = lattice_positions(nx, ny, nz, spacing, 0.005 * radius, 1.01 * radius, seed)
+    hx, hy, hz = blade
+    anchor = np.array([0.0, 0.0, 1.01 * radius + hz + 0.5 * radius])
+    # leave room for the blade: drop the spheres its swept disc would start inside of
+    keep = ~((np.hypot(pos[:, 0], pos[:, 1]) < hx + 1.5 * radius) & (pos[:, 2] < anchor[2] + hz + 1.5 * radius))
+    pos = pos[keep]
+    first = b.add_bodies(m, (0.4 * m * radius * radius,) * 3, pos)
+    n = pos.shape[0]
+    b.add_shapes(SPHERE, np.arange(first, first + n), np.full((n, 1), radius))
+    ib = blade_mass / 3.0 * np.array([hy * hy + hz * hz, hx * hx + hz * hz, hx * hx + hy * hy])
+    blade_body = b.add_bodies(blade_mass, tuple(ib), [anchor])
+    b.add_shapes(BOX, [blade_body], np.array([[hx, hy, hz]]))
+    settings = dict(system_type=1, step_size=step, gravity=(0.0, 0.0, -9.81), contact_force_model=HERTZ,
+                    adhesion_force_model=0, tangential_displ_mode=1, use_material_properties=1,
+                    narrowphase_algorithm=HYBRID, collision_envelope=0.0, broadphase_grid=FIXED_BIN_SIZE,
+                    bin_size=(2.5 * 2 * radius,) * 3)
+    return b.finish([smc_material(young=2e6, friction=0.4, restitution=0.4)], settings), blade_body, anchor
+
+
 def mixed_smc(n_side=6, seed=7, radius=0.1, step=1e-3, shapes=("sphere", "box", "capsule")):
     """Small mixed-shape SMC scene (config E flavour, after src/demos/multicore/demo_MCORE_mixerSMC.cpp:51-169):
     a lattice cycling through the requested shape kinds inside an open box."""

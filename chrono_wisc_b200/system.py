@@ -209,6 +209,24 @@ class ChSystemMulticore:
         check(self._lib.cb200_do_steps(self._h, int(n)))
         self.ch_time += n * self.settings.step_size
 
+    # ---- bilateral constraints --------------------------------------------------------------------
+    def SetBilaterals(self, body_ids, cq_a, cq_b, rhs, max_iteration_bilateral=100, tol_speed=1e-4):
+        """BODY_BODY rows of ``ChConstraintBilateral`` (Build_D / Build_b): ``cq_a . v_a + cq_b . v_b + rhs = 0`` per
+        row; ``None`` removes all rows.  Defaults of ``max_iteration_bilateral`` / ``tol_speed``: MC/ChSettings.h."""
+        if body_ids is None:
+            check(self._lib.cb200_set_bilaterals(self._h, 0, None, None, None, None, 0, 0.0))
+            return
+        self._push_settings()
+        ids = np.ascontiguousarray(body_ids, dtype=np.int32).reshape(-1, 2)
+        a, b, r = _f64(cq_a, (-1, 6)), _f64(cq_b, (-1, 6)), _f64(rhs).ravel()
+        check(self._lib.cb200_set_bilaterals(self._h, ids.shape[0], _ptr(ids), _ptr(a), _ptr(b), _ptr(r),
+                                             int(max_iteration_bilateral), float(tol_speed)))
+
+    def GetBilateralGamma(self, n):
+        g, it, res = np.zeros(n), C.c_int(), C.c_double()
+        check(self._lib.cb200_download_bilateral_gamma(self._h, _ptr(g), C.byref(it), C.byref(res)))
+        return g, it.value, res.value
+
     # ---- contact callbacks (SURVEY 8 f2) -----------------------------------------------------------------------
     def RegisterNarrowphaseCallback(self, callback):
         """``ChCollisionSystem::RegisterNarrowphaseCallback``: ``callback(cinfo) -> bool``; False drops the contact

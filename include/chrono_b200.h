@@ -214,6 +214,18 @@ int cb200_download_contacts(cb200_system* sys, double* normal, double* pt_a, dou
 int cb200_download_contact_forces(cb200_system* sys, double* ct_force, double* ct_torque);
 /* ChSystemMulticoreSMC::GetBodyContactForce/Torque for all bodies (MC/physics/ChSystemMulticoreSMC.cpp:74-90):
  * 3 doubles per body each, zero for bodies without contacts. */
+/* Bilateral constraints (joints, motors) between bodies -- ChSystemMulticore::UpdateBilaterals +
+ * ChConstraintBilateral::Build_D / Build_b, BODY_BODY rows (src/chrono_multicore/constraints/ChConstraintBilateral.cpp:
+ * 34-78).  Row i couples bodies body_ids[2i], body_ids[2i+1] with the Jacobian blocks cq_a[6i..6i+5], cq_b[6i..6i+5]
+ * of its ChConstraintTwoBodies (linear part in the absolute frame, angular part in the body frame) and right-hand side
+ * rhs[i]: cq_a.v_a + cq_b.v_b + rhs = 0.  SMC systems solve the rows with MINRES on D_b^T M^-1 D_b after the contact
+ * forces are known (ChIterativeSolverMulticoreSMC::RunTimeStep :816-842, ChSolverMulticoreMinRes::Solve;
+ * settings.solver.max_iteration_bilateral, tol_speed) and add M^-1 D_b gamma_b to the velocities.  The rows stay in
+ * force until replaced; n = 0 removes them.  Shaft rows and NSC systems: CB200_ERR_UNSUPPORTED. */
+int cb200_set_bilaterals(cb200_system* sys, int n, const int32_t* body_ids, const double* cq_a, const double* cq_b,
+                         const double* rhs, int max_iteration_bilateral, double tol_speed);
+/* gamma_b of the last solve (impulses: ConstraintsFetch_react divides by the step), MINRES iterations, residual */
+int cb200_download_bilateral_gamma(cb200_system* sys, double* gamma, int* iterations, double* residual);
 /* Contact callbacks.  The reference calls them on the host, one contact at a time, between the narrowphase and the
  * solver (ChCollisionSystemMulticore::ReportContacts, src/chrono/collision/multicore/ChCollisionSystemMulticore.cpp:
  * 326-372 -> ChContactContainerMulticoreSMC/NSC::AddContact).  Here the caller runs its loop over the downloaded list

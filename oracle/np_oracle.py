@@ -211,3 +211,63 @@ def report_contacts(method, contacts, pos, rot, h, ct_force=None, ct_torque=None
             F[i], T[i] = P.T @ f_abs, P.T @ t_abs
     return dict(pA=contacts["pt_a"], pB=contacts["pt_b"], plane=planes, distance=contacts["depth"],
                 eff_radius=contacts["eff_radius"], force=F, torque=T, body_ids=contacts["body_ids"])
+
+
+def minres(N, mb, max_iter, tol):
+    """ChSolverMulticoreMinRes::Solve (MC/solver/ChSolverMulticoreMINRES.cpp:19-112) on an explicit matrix, x0 = 0.
+    Returns (x, iterations, residual)."""
+    n = mb.size
+    x = np.zeros(n)
+    v_hat = mb - N @ x
+    beta = np.linalg.norm(v_hat)
+    c, eta, norm_rMR, norm_r0, c_old, s_old, s = 1.0, beta, beta, beta, 1.0, 0.0, 0.0
+    v, w, w_old = np.zeros(n), np.zeros(n), np.zeros(n)
+    if beta == 0 or norm_rMR / norm_r0 < tol:
+        return x, 0, (0.0 if beta == 0 else 1.0)
+    residual, it = 1.0, 0
+    for it in range(max_iter):
+        v_old = v
+        v = 1.0 / beta * v_hat
+        Av = N @ v
+        alpha = v @ Av
+        v_hat = Av - alpha * v
+        v_hat = v_hat - beta * v_old
+        beta_old = beta
+        beta = np.linalg.norm(v_hat)
+        c_oold, c_old, s_oold, s_old = c_old, c, s_old, s
+        r1_hat = c_old * alpha - c_oold * s_old * beta_old
+        r1 = 1 / np.sqrt(r1_hat * r1_hat + beta * beta)
+        r2 = s_old * alpha + c_oold * c_old * beta_old
+        r3 = s_oold * beta_old
+        c, s = r1_hat * r1, beta * r1
+        w_oold, w_old = w_old, w
+        w = (v - r3 * w_oold - r2 * w_old) * r1
+        x = x + c * eta * w
+        norm_rMR = norm_rMR * abs(s)
+        eta = -s * eta
+        residual = norm_rMR / norm_r0
+        if residual < tol:
+            break
+    else:
+        it = max_iter
+    return x, it, residual
+
+
+def bilateral_solve(ids, cq_a, cq_b, rhs, vel, hf, mass, inv_inertia, active, max_iter=100, tol=1e-4):
+    """ChIterativeSolverMulticoreSMC::RunTimeStep :808-845 for BODY_BODY rows: M_invk = v + M^-1 hf (active bodies),
+    R = -b - D^T M_invk (ComputeR :772-783), N = D^T M^-1 D (ChSchurProductBilateral), MINRES (PerformStabilization),
+    v = M_invk + M^-1 D gamma (ComputeImpulses :854-868).  Returns (v, gamma, iterations, residual)."""
+    nb, n = mass.size, rhs.size
+    act = np.asarray(active, dtype=bool)
+    minv = np.concatenate([np.repeat(1.0 / mass[:, None], 3, 1), inv_inertia.reshape(nb, 3)], 1) * act[:, None]
+    M_invk = vel + minv * hf
+    D = np.zeros((n, 6 * nb))
+    for i in range(n):
+        D[i, 6 * ids[i, 0]:6 * ids[i, 0] + 6] += cq_a[i]
+        D[i, 6 * ids[i, 1]:6 * ids[i, 1] + 6] += cq_b[i]
+    Minv = minv.reshape(-1)
+    R = -rhs - D @ M_invk.reshape(-1)
+    N = (D * Minv) @ D.T
+    gamma, it, res = minres(N, R, max_iter, tol)
+    v = M_invk.reshape(-1) + Minv * (D.T @ gamma)
+    return v.reshape(nb, 6), gamma, it, res
