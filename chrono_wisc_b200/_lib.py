@@ -120,6 +120,8 @@ _SIGNATURES = {
     "cb200_kernel_launches": (C.c_int64, [_P]),
     "cb200_set_bilaterals": (C.c_int, [_P, C.c_int, _P, _P, _P, _P, C.c_int, C.c_double]),
     "cb200_download_bilateral_gamma": (C.c_int, [_P, _P, _P, _P]),
+    "cb200_minres_noalloc": (C.c_int, [_P, C.c_int, _P, _P, _P, C.c_int, C.c_double, _P]),
+    "cb200_minres_noalloc_max_rows": (C.c_int, []),
     "cb200_filter_contacts": (C.c_int, [_P, C.c_int, _P]),
     "cb200_download_contact_materials": (C.c_int, [_P, C.c_int, _P, _P]),
     "cb200_upload_contact_materials": (C.c_int, [_P, C.c_int, _P]),

@@ -289,3 +289,65 @@ extern "C" int cb200_download_bilateral_gamma(cb200_system* sys, double* gamma, 
         *residual = info[1];
     return CB200_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of the MINRES solve.  No counterpart in the reference: added
+// for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+// that forbid it).  The kernel is k_bil_minres itself; what differs is where its 7 work vectors live: instead of
+// System::bil_vec (grown with cudaMalloc by cb200_set_bilaterals) they sit in the file-scope array below, which every
+// GPU that loads the library holds until the process exits (7 x 2048 doubles = 112 KiB).
+//
+// In host code `g_minres_scratch` is only a stand-in for the symbol, not a device address: the address a kernel can
+// use is looked up once per device, with that device current, by cudaGetSymbolAddress, and cached.
+// ---------------------------------------------------------------------------------------------------------------
+#include <mutex>
+
+#define CB200_NOALLOC_MINRES_MAX_ROWS 2048
+static __device__ __align__(256) double g_minres_scratch[7 * CB200_NOALLOC_MINRES_MAX_ROWS];
+
+static std::mutex g_minres_mu;
+static double* g_minres_scratch_ptr[64] = {};  // per device ordinal
+
+static int minres_scratch_for(int device, double** out) {
+    if (device < 0 || device >= 64)
+        return set_error(CB200_ERR_ARG, "device ordinal out of range");
+    std::lock_guard<std::mutex> lock(g_minres_mu);
+    if (!g_minres_scratch_ptr[device]) {
+        CB_CUDA(cudaSetDevice(device));
+        double* p = nullptr;
+        CB_CUDA(cudaGetSymbolAddress((void**)&p, g_minres_scratch));
+        if (!p)
+            return set_error(CB200_ERR_CUDA, "cudaGetSymbolAddress returned a null scratch address");
+        g_minres_scratch_ptr[device] = p;
+    }
+    *out = g_minres_scratch_ptr[device];
+    return CB200_OK;
+}
+
+// Solves N x = b (N symmetric n x n, row-major; x0 = 0) exactly as the bilateral stage of a step does, on the system's
+// stream.  N_dev, b_dev, x_dev (n doubles out) and info_dev (2 doubles out: iterations run, residual) are DEVICE
+// pointers owned by the caller.  Calls no cudaMalloc / cudaFree.  All calls on one GPU share the scratch array: two
+// calls that overlap on the GPU (different streams, different systems on one device) race; calls on one stream are
+// ordered and safe.  The scratch keeps the previous call's contents, so the part this call uses is cleared first.
+extern "C" int cb200_minres_noalloc(cb200_system* sys, int n, const double* N_dev, const double* b_dev, double* x_dev,
+                                    int max_iter, double tol, double* info_dev) {
+    System* S = reinterpret_cast<System*>(sys);
+    if (!S || n < 0 || max_iter < 0 || (n && (!N_dev || !b_dev || !x_dev)) || !info_dev)
+        return set_error(CB200_ERR_ARG, "bad argument to cb200_minres_noalloc");
+    if (n > CB200_NOALLOC_MINRES_MAX_ROWS)
+        return set_error(CB200_ERR_ARG, "cb200_minres_noalloc: " + std::to_string(n) + " rows exceed the fixed scratch (" +
+                                            std::to_string(CB200_NOALLOC_MINRES_MAX_ROWS) +
+                                            " rows); use cb200_set_bilaterals for larger systems");
+    double* scratch = nullptr;
+    CB_TRY(minres_scratch_for(S->device, &scratch));
+    CB_CUDA(cudaSetDevice(S->device));
+    if (n)
+        CB_CUDA(cudaMemsetAsync(scratch, 0, 7 * (size_t)n * sizeof(double), S->stream));
+    k_bil_minres<<<1, BIL_THREADS, 0, S->stream>>>((uint32_t)n, max_iter, tol, N_dev, b_dev, x_dev, scratch, info_dev,
+                                                   S->d_cnt);
+    S->launches++;
+    CB_CUDA(cudaGetLastError());
+    return CB200_OK;
+}
+
+extern "C" int cb200_minres_noalloc_max_rows(void) { return CB200_NOALLOC_MINRES_MAX_ROWS; }

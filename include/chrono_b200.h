@@ -226,6 +226,16 @@ int cb200_set_bilaterals(cb200_system* sys, int n, const int32_t* body_ids, cons
                          const double* rhs, int max_iteration_bilateral, double tol_speed);
 /* gamma_b of the last solve (impulses: ConstraintsFetch_react divides by the step), MINRES iterations, residual */
 int cb200_download_bilateral_gamma(cb200_system* sys, double* gamma, int* iterations, double* residual);
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The MINRES solve of the
+ * bilateral stage (the kernel behind cb200_set_bilaterals) on caller-owned DEVICE buffers: N_dev n x n symmetric,
+ * row-major; b_dev n; x_dev n (out, x0 = 0); info_dev 2 doubles (out: iterations run, residual).  Enqueued on the
+ * system's stream; allocates nothing: the 7 n work doubles live in a static device array of the library, so
+ * n <= cb200_minres_noalloc_max_rows() (2048; larger n: CB200_ERR_ARG).  Every call on a GPU shares that array: calls
+ * that overlap on the GPU race, calls on one stream are safe; the part a call uses is cleared first. */
+int cb200_minres_noalloc(cb200_system* sys, int n, const double* N_dev, const double* b_dev, double* x_dev,
+                         int max_iter, double tol, double* info_dev);
+int cb200_minres_noalloc_max_rows(void);
 /* Contact callbacks.  The reference calls them on the host, one contact at a time, between the narrowphase and the
  * solver (ChCollisionSystemMulticore::ReportContacts, src/chrono/collision/multicore/ChCollisionSystemMulticore.cpp:
  * 326-372 -> ChContactContainerMulticoreSMC/NSC::AddContact).  Here the caller runs its loop over the downloaded list
