@@ -364,7 +364,7 @@ void cb200_destroy(cb200_system* sys) {
         }
     cudaFree(S->d_cnt);
     cudaFreeHost(S->h_cnt);
-    S->b_gid.release(); S->slab_flags.release(); S->slab_vacant.release();
+    S->b_gid.release(); S->slab_flags.release(); S->slab_vacant.release(); S->slab_cta.release();
     if (S->slab_cnt)
         cudaFree(S->slab_cnt);
     for (int i = 0; i < 2; i++)
@@ -845,6 +845,7 @@ int cb200_run_collision(cb200_system* sys, int stages) {
             if (!S->pairs.p)
                 CB_TRY(alloc_pairs(S, 8 * S->ns + 1024));
             CB_TRY(enqueue_bins(S));
+            S->body_scratch_clean = false;  // the heavy flags are set again and no integration follows in this call
         }
         CB_TRY(timer_stop(S, "collision_broad"));
         CB_TRY(timer_start(S, "collision_narrow"));
@@ -875,7 +876,14 @@ int cb200_integrate(cb200_system* sys) {
     return run_stage(S, [&] { return enqueue_integrate(S); });
 }
 
+static int enqueue_one_step_(System* S);
 static int enqueue_one_step(System* S) {
+    S->whole_step = true;
+    const int rc = enqueue_one_step_(S);
+    S->whole_step = false;
+    return rc;
+}
+static int enqueue_one_step_(System* S) {
     S->aux_ev_next = 0;
     CB_TRY(timer_start(S, "step"));
     CB_TRY(timer_start(S, "update"));

@@ -520,17 +520,21 @@ __global__ void __launch_bounds__(256) k_bin_fill(uint32_t ns, double envelope, 
 // --------------------------------------------------------------------------------------------------------------
 // host side: enqueue only, no synchronisation
 // --------------------------------------------------------------------------------------------------------------
+int enqueue_build_meta(System* S) {
+    k_build_meta<<<grid_for(S, S->ns, 256), 256, 0, S->stream>>>(S->ns, S->s_type.p, S->s_body.p, S->s_fam.p,
+                                                                 S->s_mat.p, S->s_lpos.p, S->bflags.p,
+                                                                 S->slab_on ? nullptr : S->b_sphere.p, S->s_meta.p);
+    S->meta_dirty = false;
+    S->sphere_aabb_valid = false;
+    S->launches++;
+    return CB200_OK;
+}
+
 int enqueue_aabb(System* S) {
     if (S->ns == 0)
         return CB200_OK;
-    if (S->meta_dirty) {
-        k_build_meta<<<grid_for(S, S->ns, 256), 256, 0, S->stream>>>(S->ns, S->s_type.p, S->s_body.p, S->s_fam.p,
-                                                                     S->s_mat.p, S->s_lpos.p, S->bflags.p,
-                                                                     S->slab_on ? nullptr : S->b_sphere.p, S->s_meta.p);
-        S->meta_dirty = false;
-        S->sphere_aabb_valid = false;
-        S->launches++;
-    }
+    if (S->meta_dirty)
+        CB_TRY(enqueue_build_meta(S));
     // the bodies' own spheres: done by the integration that ended the previous step, unless something touched the
     // state since (uploads, new bodies / shapes, flags, settings)
     const bool spheres_done = S->sphere_aabb_valid && !S->slab_on;
@@ -541,7 +545,7 @@ int enqueue_aabb(System* S) {
     }
     k_reset_counters<<<1, 32, 0, S->stream>>>(S->d_cnt, S->nb, S->ns, spheres_done);
     S->pair_cnt_clean = true;
-    if (!(spheres_done && S->body_scratch_clean))  // the fused integration left the heavy flags cleared
+    if (!S->body_scratch_clean)  // the integration of a whole step left the heavy flags cleared
         CB_CUDA(cudaMemsetAsync(S->heavy.p, 0, S->nb, S->stream));
     if (!spheres_done) {
         k_aabb<false><<<grid_for(S, S->ns, 256), 256, 0, S->stream>>>(

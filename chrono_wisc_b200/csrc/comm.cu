@@ -18,6 +18,7 @@
 // device-to-device copies and the all-reduce a small kernel).  That is how the decomposition is tested on a single
 // GPU; nothing waits on another launch.
 #include "common.cuh"
+#include "slab.cuh"
 #include <dlfcn.h>
 #include <nccl.h>
 #include <algorithm>
@@ -183,26 +184,33 @@ int comm_allreduce(Group& g, int first, int n) {
 
 // ---- NSC halo: the owner's 6 doubles per body -> the ghost copies on the neighbours -------------------------------
 // The records of the last ghost exchange define the mapping: the j-th record a rank sent to a side is the j-th ghost
-// slot of that neighbour's region for this rank (slab.cu); slab_flags still holds the scanned send offsets.
-__global__ void __launch_bounds__(256) k_halo_pack(uint32_t owned_cap, uint32_t nb_static,
-                                                   const uint64_t* __restrict__ offs, const double* __restrict__ arr,
-                                                   double* __restrict__ send_left, double* __restrict__ send_right,
-                                                   const DevCounters* __restrict__ cnt) {
+// slot of that neighbour's region for this rank (slab.cu); the flags and CTA offsets of that pack are still there
+// (slab.cuh).
+__global__ void __launch_bounds__(SLAB_CTA) k_halo_pack(uint32_t owned_cap, uint32_t nb_static,
+                                                        const uint8_t* __restrict__ flags,
+                                                        const uint32_t* __restrict__ cta_off,
+                                                        const double* __restrict__ arr, double* __restrict__ send_left,
+                                                        double* __restrict__ send_right,
+                                                        const DevCounters* __restrict__ cnt) {
+    __shared__ uint32_t wtot[3][8];
     if (cnt->overflow)
         return;
-    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < owned_cap; s += gridDim.x * blockDim.x) {
-        const uint64_t o = offs[s], f = offs[s + 1] - o;
-        const double* a = arr + 6 * (size_t)(nb_static + s);
-        if ((f & 1ull) && send_left) {
-            double* d = send_left + 6 * (size_t)(uint32_t)(o & 0x1fffff);
-            for (int k = 0; k < 6; k++)
-                d[k] = a[k];
-        }
-        if ((f & (1ull << 21)) && send_right) {
-            double* d = send_right + 6 * (size_t)(uint32_t)((o >> 21) & 0x1fffff);
-            for (int k = 0; k < 6; k++)
-                d[k] = a[k];
-        }
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;  // one thread per owned slot, as in the pack pass
+    const uint32_t f = s < owned_cap ? flags[s] : 0u;
+    uint32_t rank[3];
+    slab_ranks(f, cta_off, wtot, rank);
+    if (s >= owned_cap)
+        return;
+    const double* a = arr + 6 * (size_t)(nb_static + s);
+    if ((f & SLAB_F_LEFT) && send_left) {
+        double* d = send_left + 6 * (size_t)rank[0];
+        for (int k = 0; k < 6; k++)
+            d[k] = a[k];
+    }
+    if ((f & SLAB_F_RIGHT) && send_right) {
+        double* d = send_right + 6 * (size_t)rank[1];
+        for (int k = 0; k < 6; k++)
+            d[k] = a[k];
     }
 }
 
@@ -226,9 +234,9 @@ int comm_halo6(Group& g, int which) {
     for (System* S : g.sys) {
         Comm* C = S->comm;
         const double* arr = which == 0 ? S->n_w.p : S->n_w0.p;
-        k_halo_pack<<<grid_for(S, S->slab_owned_cap, 256), 256, 0, S->stream>>>(
-            S->slab_owned_cap, S->slab_nb_static, S->slab_flags.p, arr, S->slab_has_left ? C->hsend[0].p : nullptr,
-            S->slab_has_right ? C->hsend[1].p : nullptr, S->d_cnt);
+        k_halo_pack<<<(S->slab_owned_cap + SLAB_CTA - 1) / SLAB_CTA, SLAB_CTA, 0, S->stream>>>(
+            S->slab_owned_cap, S->slab_nb_static, reinterpret_cast<const uint8_t*>(S->slab_flags.p), S->slab_cta.p, arr,
+            S->slab_has_left ? C->hsend[0].p : nullptr, S->slab_has_right ? C->hsend[1].p : nullptr, S->d_cnt);
         S->launches++;
     }
     const bool exact = g.sys[0]->comm->counts_valid;

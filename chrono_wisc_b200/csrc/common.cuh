@@ -285,7 +285,8 @@ struct System {
     double slab_lo = 0, slab_hi = 0, slab_w = 0;
     uint32_t slab_nb_static = 0, slab_ns_static = 0, slab_owned_cap = 0, slab_ghost_cap = 0;
     DevBuf<int64_t> b_gid;          // global body id per slot
-    DevBuf<uint64_t> slab_flags;    // owned_cap + 2: packed (to-left | to-right << 21 | vacant << 42), then offsets
+    DevBuf<uint64_t> slab_flags;    // owned_cap BYTES: per owned slot the flags of the last pack (slab.cuh)
+    DevBuf<uint32_t> slab_cta;      // 3 per CTA of 256 slots: counts, then exclusive offsets; totals behind the last
     DevBuf<uint32_t> slab_vacant;   // vacant owned slots in slot order
     uint32_t* slab_cnt = nullptr;   // device: [0] owned_cap (scan extent) [1] n_vacant [2] arrivals of last unpack
     cudaStream_t own_stream = nullptr;  // the stream cb200_create made (stream may be the caller's, cb200_set_stream)
@@ -301,6 +302,7 @@ struct System {
     // degrees, the incidence cursors and the heavy flags.  Anything that can leave them dirty (an overflow, a
     // reallocation, a stage call) resets the flag and the next enqueue clears them the slow way.
     bool bins_clean = false, body_scratch_clean = false, pair_cnt_clean = false;
+    bool whole_step = false;       // inside enqueue_one_step (api.cu): the integration that ends it may clear scratch
     bool bbox_reset_done = false;  // k_reset_bbox of this step already ran on a side branch (smc.cu)
 
     // ---- scan scratch / counters ----
@@ -360,6 +362,7 @@ bool comm_multi(const System* S);     // S is one slab of a decomposed system (h
 double* comm_gsum(System* S);         // 24 doubles of device scratch for sums over all ranks
 int comm_halo6(Group& g, int which);  // owners' 6 doubles per body (0: n_w, 1: n_w0) -> the neighbours' ghost copies
 int comm_allreduce(Group& g, int first, int n);  // gsum[first..first+n) summed over all ranks, in place
+int enqueue_build_meta(System* S);  // broadphase.cu
 int enqueue_report(System* S);  // report.cu
 int enqueue_bilateral(System* S);  // bilateral.cu
 int aux_fork(System* S, int i, cudaStream_t* out);  // `out`: the stream to launch the branch on

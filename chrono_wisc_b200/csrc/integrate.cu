@@ -141,12 +141,12 @@ __global__ void __launch_bounds__(256) k_integrate(uint32_t nb, double h, const 
                 }
             }
         }
+        if (A.b_deg) {  // whole SMC steps only: NSC keeps its CSR by body for the queries that follow a step
+            A.b_deg[b] = 0u, A.b_cursor[b] = 0u, A.heavy[b] = 0;
+            if (b == 0)
+                A.b_deg[nb] = 0u;
+        }
         if (AABB) {
-            if (A.b_deg) {  // SMC steps only: NSC keeps its CSR by body for the queries that follow a step
-                A.b_deg[b] = 0u, A.b_cursor[b] = 0u, A.heavy[b] = 0;
-                if (b == 0)
-                    A.b_deg[nb] = 0u;
-            }
             const int32_t si = A.b_sphere[b];
             if (si >= 0) {
                 // k_aabb<false>: centred sphere, Rotate(0, q) + p == p
@@ -203,7 +203,7 @@ int enqueue_integrate(System* S) {
         return CB200_OK;
     const int grid = blocks_for(S->nb, 256);
     const bool fuse = integrate_fuses_aabb(S);
-    const bool clear = fuse && S->set.system_type == 1 && S->b_deg.p && S->b_cursor.p;
+    const bool clear = S->whole_step && S->set.system_type == 1 && S->b_deg.p && S->b_cursor.p && S->heavy.p;
     AabbArgs A = {S->b_sphere.p, S->b_rad.p, S->s_wpos_alt.p, S->set.collision_envelope,
                   clear ? S->b_deg.p : nullptr, S->b_cursor.p, S->heavy.p};
 #define INTEGRATE(VEL, AABB)                                                                                          \

@@ -23,6 +23,7 @@
 // Record = 33 doubles: gid, pos 3, rot 4, vel 6, mass, inertia 3, inv_inertia 3, shape dims 4, shape local pos 3,
 // local rot 4, packed (type | material << 8 | family << 32).  Buffer = [count, 0, records...].
 #include "common.cuh"
+#include "slab.cuh"
 #include <float.h>
 #include <limits.h>
 #include <vector>
@@ -38,8 +39,24 @@ struct SlabArrays {
     double *s_dims, *s_lpos, *s_lrot;
     int32_t *s_type, *s_mat;
     uint32_t* s_fam;
+    ShapeMeta* meta;  // kept current slot by slot (what k_build_meta would write), so an exchange does not force a rebuild
     uint32_t nb_static, ns_static;
 };
+
+// The integer record of the shape of dynamic slot b, as k_build_meta (broadphase.cu) forms it for a slab system
+__device__ __forceinline__ void slab_write_meta(const SlabArrays& A, uint32_t b, uint32_t fl) {
+    const uint32_t s = A.ns_static + (b - A.nb_static);
+    ShapeMeta m;
+    m.body = (fl & 4u) ? UINT_MAX : b;
+    m.fam = A.s_fam[s];
+    m.pad = 0;
+    const uint32_t type = (uint32_t)A.s_type[s] & 0xff;
+    m.info = type << 8 | ((uint32_t)A.s_mat[s] & 0xffff) << 16 | (fl & 3u);
+    if (type == CB200_SPHERE && A.s_lpos[3 * (size_t)s] == 0 && A.s_lpos[3 * (size_t)s + 1] == 0 &&
+        A.s_lpos[3 * (size_t)s + 2] == 0)
+        m.info |= 4u;
+    A.meta[s] = m;
+}
 
 __device__ __forceinline__ void slab_write_record(const SlabArrays& A, uint32_t b, double* __restrict__ r) {
     const uint32_t s = A.ns_static + (b - A.nb_static);
@@ -91,6 +108,7 @@ __device__ __forceinline__ void slab_read_record(const SlabArrays& A, uint32_t b
     A.s_mat[s] = (int32_t)((bits >> 8) & 0xffff);
     A.s_fam[s] = (uint32_t)(bits >> 32);
     A.bflags[b] = flags;
+    slab_write_meta(A, b, flags);
 }
 
 struct SlabGeom {
@@ -99,35 +117,89 @@ struct SlabGeom {
     uint32_t owned_cap, ghost_cap;
 };
 
-// flags of one owned slot: bit 0 send left, bit 21 send right, bit 42 vacant after this step's departures
-__global__ void __launch_bounds__(256) k_slab_flags(SlabGeom G, SlabArrays A, uint64_t* __restrict__ flags,
-                                                    const DevCounters* __restrict__ cnt) {
-    if (cnt->overflow)
-        return;
-    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < G.owned_cap; s += gridDim.x * blockDim.x) {
+// Pack, pass 1: flags of one owned slot (slab.cuh) and the three counts of every CTA of 256 slots.  One thread per slot.
+__global__ void __launch_bounds__(SLAB_CTA) k_slab_flags(SlabGeom G, SlabArrays A, uint8_t* __restrict__ flags,
+                                                         uint32_t* __restrict__ cta_cnt) {
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t f = 0;
+    if (s < G.owned_cap) {
         const uint32_t b = A.nb_static + s;
-        uint64_t f = 0;
         if (A.bflags[b] & (4u | 8u)) {
-            f = 1ull << 42;  // vacant, or left during the previous exchange (kept one step as a ghost, see k_slab_pack)
+            f = SLAB_F_VACANT;  // vacant, or left during the previous exchange (kept one step as a ghost, see k_slab_pack)
         } else {
             const double p = A.pos[3 * (size_t)b + G.axis];
             if (G.has_left && p < G.lo + G.w)
-                f |= 1ull;
+                f |= SLAB_F_LEFT;
             if (G.has_right && p >= G.hi - G.w)
-                f |= 1ull << 21;
+                f |= SLAB_F_RIGHT;
         }
-        flags[s] = f;
+        flags[s] = (uint8_t)f;
+    }
+    const int cl = __syncthreads_count(f & 1u), cr = __syncthreads_count(f & 2u), cv = __syncthreads_count(f & 4u);
+    if (threadIdx.x == 0) {
+        cta_cnt[3 * blockIdx.x] = (uint32_t)cl;
+        cta_cnt[3 * blockIdx.x + 1] = (uint32_t)cr;
+        cta_cnt[3 * blockIdx.x + 2] = (uint32_t)cv;
     }
 }
 
-__global__ void __launch_bounds__(256) k_slab_pack(SlabGeom G, SlabArrays A, const uint64_t* __restrict__ offs,
-                                                   double* __restrict__ send_left, double* __restrict__ send_right,
-                                                   uint32_t* __restrict__ vacant, uint32_t* __restrict__ scnt,
-                                                   DevCounters* __restrict__ cnt) {
+// Pass 2: exclusive scan of the per-CTA counts (a few thousand triples: one CTA), totals behind the last triple
+__global__ void __launch_bounds__(1024) k_slab_cta_scan(uint32_t ncta, uint32_t* __restrict__ cta_cnt) {
+    __shared__ uint32_t sm[3][32];
+    const uint32_t per = (ncta + blockDim.x - 1) / blockDim.x;
+    const uint32_t c0 = min(threadIdx.x * per, ncta), c1 = min(c0 + per, ncta);
+    uint32_t t[3] = {0, 0, 0};
+    for (uint32_t c = c0; c < c1; c++)
+        for (int k = 0; k < 3; k++)
+            t[k] += cta_cnt[3 * c + k];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t ex[3];
+    for (int k = 0; k < 3; k++) {
+        uint32_t v = t[k];
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t o = __shfl_up_sync(0xffffffffu, v, d);
+            if (lane >= d)
+                v += o;
+        }
+        if (lane == 31)
+            sm[k][wid] = v;
+        ex[k] = v - t[k];
+    }
+    __syncthreads();
+    if (wid == 0) {
+        for (int k = 0; k < 3; k++) {
+            const uint32_t w = sm[k][lane];
+            uint32_t v = w;
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t o = __shfl_up_sync(0xffffffffu, v, d);
+                if (lane >= d)
+                    v += o;
+            }
+            sm[k][lane] = v - w;
+            if (lane == 31)
+                cta_cnt[3 * ncta + k] = v;  // totals
+        }
+    }
+    __syncthreads();
+    uint32_t run[3] = {ex[0] + sm[0][wid], ex[1] + sm[1][wid], ex[2] + sm[2][wid]};
+    for (uint32_t c = c0; c < c1; c++)
+        for (int k = 0; k < 3; k++) {
+            const uint32_t v = cta_cnt[3 * c + k];
+            cta_cnt[3 * c + k] = run[k];
+            run[k] += v;
+        }
+}
+
+// Pass 3: records into the send buffers, vacant list, departures; the slot order is kept (CTA offset + rank in CTA)
+__global__ void __launch_bounds__(SLAB_CTA) k_slab_pack(SlabGeom G, SlabArrays A, const uint8_t* __restrict__ flags,
+                                                        const uint32_t* __restrict__ cta_off, uint32_t ncta,
+                                                        double* __restrict__ send_left, double* __restrict__ send_right,
+                                                        uint32_t* __restrict__ vacant, uint32_t* __restrict__ scnt,
+                                                        DevCounters* __restrict__ cnt) {
+    __shared__ uint32_t wtot[3][8];
     if (cnt->overflow)
         return;
-    const uint64_t tot = offs[G.owned_cap];
-    const uint32_t nL = (uint32_t)(tot & 0x1fffff), nR = (uint32_t)((tot >> 21) & 0x1fffff), nV = (uint32_t)(tot >> 42);
+    const uint32_t nL = cta_off[3 * ncta], nR = cta_off[3 * ncta + 1], nV = cta_off[3 * ncta + 2];
     if (nL > G.ghost_cap || nR > G.ghost_cap) {
         if (blockIdx.x == 0 && threadIdx.x == 0)
             atomicOr(&cnt->overflow, (uint32_t)OVF_SLAB);
@@ -140,23 +212,31 @@ __global__ void __launch_bounds__(256) k_slab_pack(SlabGeom G, SlabArrays A, con
             send_right[0] = (double)nR, send_right[1] = 0;
         scnt[1] = nV;
     }
-    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < G.owned_cap; s += gridDim.x * blockDim.x) {
-        const uint32_t b = A.nb_static + s;
-        const uint64_t o = offs[s], f = offs[s + 1] - o;  // exclusive scan: the slot's own flags are the difference
-        if (f & 1ull)
-            slab_write_record(A, b, send_left + SLAB_HDR + (size_t)SLAB_REC * (uint32_t)(o & 0x1fffff));
-        if (f & (1ull << 21))
-            slab_write_record(A, b, send_right + SLAB_HDR + (size_t)SLAB_REC * (uint32_t)((o >> 21) & 0x1fffff));
-        if (f & (1ull << 42)) {
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t f = s < G.owned_cap ? flags[s] : 0u;
+    uint32_t rank[3];
+    slab_ranks(f, cta_off, wtot, rank);
+    if (s >= G.owned_cap)
+        return;
+    const uint32_t b = A.nb_static + s;
+    if (f & SLAB_F_LEFT)
+        slab_write_record(A, b, send_left + SLAB_HDR + (size_t)SLAB_REC * rank[0]);
+    if (f & SLAB_F_RIGHT)
+        slab_write_record(A, b, send_right + SLAB_HDR + (size_t)SLAB_REC * rank[1]);
+    if (f & SLAB_F_VACANT) {
+        if (A.bflags[b] != 4) {
             A.bflags[b] = 4;
-            vacant[(uint32_t)(o >> 42)] = b;
-        } else {
-            // A body past the plane now belongs to the neighbour (it is in the buffer just written).  Its slot stays
-            // one more step as a ghost -- the neighbour's own ghost layer will only list it from the next exchange
-            // on -- and is released by the next pack (bit 3).
-            const double p = A.pos[3 * (size_t)b + G.axis];
-            if ((G.has_left && p < G.lo) || (G.has_right && p >= G.hi))
-                A.bflags[b] = 2 | 8;
+            slab_write_meta(A, b, 4);
+        }
+        vacant[rank[2]] = b;
+    } else {
+        // A body past the plane now belongs to the neighbour (it is in the buffer just written).  Its slot stays
+        // one more step as a ghost -- the neighbour's own ghost layer will only list it from the next exchange
+        // on -- and is released by the next pack (bit 3).
+        const double p = A.pos[3 * (size_t)b + G.axis];
+        if ((G.has_left && p < G.lo) || (G.has_right && p >= G.hi)) {
+            A.bflags[b] = 2 | 8;
+            slab_write_meta(A, b, 2 | 8);
         }
     }
 }
@@ -169,13 +249,17 @@ __device__ __forceinline__ bool slab_is_arrival(const SlabGeom& G, const double*
     return (!G.has_left || p >= G.lo) && (!G.has_right || p < G.hi);
 }
 
-__global__ void __launch_bounds__(1024) k_slab_unpack(SlabGeom G, SlabArrays A, const double* __restrict__ recv,
-                                                      uint32_t ghost_base, const uint32_t* __restrict__ vacant,
-                                                      uint32_t* __restrict__ scnt, int first_side,
+// blockIdx.y = side (0: the left neighbour's buffer, unpacked "first": its arrivals take the first vacant slots).
+__global__ void __launch_bounds__(1024) k_slab_unpack(SlabGeom G, SlabArrays A, const double* __restrict__ recv_left,
+                                                      const double* __restrict__ recv_right, uint32_t ghost_base_left,
+                                                      const uint32_t* __restrict__ vacant, uint32_t* __restrict__ scnt,
                                                       DevCounters* __restrict__ cnt) {
     __shared__ uint32_t warp_tot[32];
     if (cnt->overflow)
         return;
+    const int first_side = blockIdx.y == 0;
+    const double* __restrict__ recv = first_side ? recv_left : recv_right;
+    const uint32_t ghost_base = first_side ? ghost_base_left : ghost_base_left + G.ghost_cap;
     const uint32_t n = recv ? (uint32_t)recv[0] : 0u;
     const uint32_t n_vac = scnt[1];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -194,7 +278,22 @@ __global__ void __launch_bounds__(1024) k_slab_unpack(SlabGeom G, SlabArrays A, 
     for (int w = 0; w < (int)(blockDim.x >> 5); w++)
         counted += warp_tot[w];
     __syncthreads();
-    const uint32_t side_base = first_side ? 0u : scnt[2];  // arrivals of the side unpacked first
+    // arrivals of the side unpacked first: the other side's CTAs count them themselves (one launch for both sides)
+    uint32_t side_base = 0;
+    if (!first_side && recv_left) {
+        const uint32_t nl = (uint32_t)recv_left[0];
+        uint32_t m2 = 0;
+        for (uint32_t i = threadIdx.x; i < ((nl + 31u) & ~31u); i += blockDim.x) {
+            const bool a = i < nl && slab_is_arrival(G, recv_left, i);
+            m2 += (uint32_t)__popc(__ballot_sync(0xffffffffu, a));
+        }
+        if (lane == 0)
+            warp_tot[wid] = m2;
+        __syncthreads();
+        for (int w = 0; w < (int)(blockDim.x >> 5); w++)
+            side_base += warp_tot[w];
+        __syncthreads();
+    }
     if (blockIdx.x == 0 && threadIdx.x == 0)
         scnt[first_side ? 2 : 3] = first_side ? counted : side_base + counted;
     const uint32_t base = side_base + (blockIdx.x == 0 ? 0u : counted);
@@ -219,7 +318,10 @@ __global__ void __launch_bounds__(1024) k_slab_unpack(SlabGeom G, SlabArrays A, 
         if (j < n && !arrival) {
             slab_read_record(A, gslot, r, 2);  // ghost: collides, not integrated
         } else {
-            A.bflags[gslot] = 4;
+            if (A.bflags[gslot] != 4) {
+                A.bflags[gslot] = 4;
+                slab_write_meta(A, gslot, 4);
+            }
             if (arrival) {
                 if (rank < n_vac)
                     slab_read_record(A, vacant[rank], r, 3);
@@ -235,7 +337,7 @@ static SlabArrays slab_arrays(System* S) {
     A.pos = S->pos.p, A.rot = S->rot.p, A.vel = S->vel.p, A.mass = S->mass.p, A.inertia = S->inertia.p;
     A.inv_inertia = S->inv_inertia.p, A.gid = S->b_gid.p, A.bflags = S->bflags.p;
     A.s_dims = S->s_dims.p, A.s_lpos = S->s_lpos.p, A.s_lrot = S->s_lrot.p;
-    A.s_type = S->s_type.p, A.s_mat = S->s_mat.p, A.s_fam = S->s_fam.p;
+    A.s_type = S->s_type.p, A.s_mat = S->s_mat.p, A.s_fam = S->s_fam.p, A.meta = S->s_meta.p;
     A.nb_static = S->slab_nb_static, A.ns_static = S->slab_ns_static;
     return A;
 }
@@ -337,7 +439,8 @@ int cb200_slab_configure(cb200_system* sys, int nb_static, int ns_static, int ax
         if (old == 0)
             CB_CUDA(cudaMemset(S->b_gid.p, 0xff, (size_t)S->nb * 8));
     }
-    CB_TRY(S->slab_flags.reserve((size_t)owned_cap + 4));
+    CB_TRY(S->slab_flags.reserve((size_t)owned_cap / 8 + 4));  // one byte per owned slot
+    CB_TRY(S->slab_cta.reserve(3 * ((size_t)owned_cap / SLAB_CTA + 2)));
     CB_TRY(S->slab_vacant.reserve((size_t)owned_cap + 1));
     CB_CUDA(cudaMalloc(&S->slab_cnt, 16));
     const uint32_t init[4] = {(uint32_t)owned_cap, 0, 0, 0};
@@ -367,13 +470,15 @@ int cb200_slab_pack_dev(cb200_system* sys, void* send_left_dev, void* send_right
     CB_CUDA(cudaSetDevice(S->device));
     const SlabGeom G = slab_geom(S);
     const SlabArrays A = slab_arrays(S);
-    const int grid = grid_for(S, G.owned_cap, 256);
-    k_slab_flags<<<grid, 256, 0, S->stream>>>(G, A, S->slab_flags.p, S->d_cnt);
-    S->launches++;
-    CB_TRY(scan_u64(S, S->slab_flags.p, S->slab_flags.p, S->slab_cnt, G.owned_cap));
-    k_slab_pack<<<grid, 256, 0, S->stream>>>(G, A, S->slab_flags.p, (double*)send_left_dev, (double*)send_right_dev,
-                                             S->slab_vacant.p, S->slab_cnt, S->d_cnt);
-    S->launches++;
+    if (S->meta_dirty)  // the kernels below keep the shape records current slot by slot: they must exist first
+        CB_TRY(enqueue_build_meta(S));
+    const uint32_t ncta = (G.owned_cap + SLAB_CTA - 1) / SLAB_CTA;
+    uint8_t* flags = reinterpret_cast<uint8_t*>(S->slab_flags.p);
+    k_slab_flags<<<ncta, SLAB_CTA, 0, S->stream>>>(G, A, flags, S->slab_cta.p);
+    k_slab_cta_scan<<<1, 1024, 0, S->stream>>>(ncta, S->slab_cta.p);
+    k_slab_pack<<<ncta, SLAB_CTA, 0, S->stream>>>(G, A, flags, S->slab_cta.p, ncta, (double*)send_left_dev,
+                                                  (double*)send_right_dev, S->slab_vacant.p, S->slab_cnt, S->d_cnt);
+    S->launches += 3;
     CB_CUDA(cudaGetLastError());
     return CB200_OK;
 }
@@ -388,13 +493,13 @@ int cb200_slab_unpack_dev(cb200_system* sys, const void* recv_left_dev, const vo
     const SlabArrays A = slab_arrays(S);
     const uint32_t gl = S->slab_nb_static + G.owned_cap, gr = gl + G.ghost_cap;
     const uint32_t ug = (G.ghost_cap + 1023u) / 1024u;
-    k_slab_unpack<<<ug, 1024, 0, S->stream>>>(G, A, S->slab_has_left ? (const double*)recv_left_dev : nullptr, gl,
-                                              S->slab_vacant.p, S->slab_cnt, 1, S->d_cnt);
-    k_slab_unpack<<<ug, 1024, 0, S->stream>>>(G, A, S->slab_has_right ? (const double*)recv_right_dev : nullptr, gr,
-                                              S->slab_vacant.p, S->slab_cnt, 0, S->d_cnt);
-    S->launches += 2;
+    (void)gr;
+    k_slab_unpack<<<dim3(ug, 2), 1024, 0, S->stream>>>(G, A, S->slab_has_left ? (const double*)recv_left_dev : nullptr,
+                                                       S->slab_has_right ? (const double*)recv_right_dev : nullptr, gl,
+                                                       S->slab_vacant.p, S->slab_cnt, S->d_cnt);
+    S->launches++;
     CB_CUDA(cudaGetLastError());
-    S->meta_dirty = true;
+    S->sphere_aabb_valid = false;  // ghost and adopted bodies changed behind the integration's back
     return CB200_OK;
 }
 
