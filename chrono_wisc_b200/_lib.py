@@ -62,7 +62,8 @@ class cb200_counts(C.Structure):
         ("num_rigid_contacts", C.c_uint32),
         ("ct_body_count", C.c_uint32),
         ("solver_iterations", C.c_uint32),
-        ("reserved", C.c_uint32 * 3),
+        ("solver_slots", C.c_uint32),
+        ("reserved", C.c_uint32 * 2),
         ("min_bounding_point", C.c_double * 3),
         ("max_bounding_point", C.c_double * 3),
         ("bin_size", C.c_double * 3),

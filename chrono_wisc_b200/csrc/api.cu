@@ -346,7 +346,7 @@ void cb200_destroy(cb200_system* sys) {
     REL(ent_cmask); REL(ent_cbase); REL(cplx_rec); REL(cplx_n); REL(cplx_cls); REL(cplx_out); REL(c_src);
     REL(ct_force); REL(ct_torque); REL(b_deg); REL(b_cursor); REL(b_inc); REL(b_force); REL(heavy_list);
     REL(heavy_part); REL(n_frame); REL(n_aux); REL(gamma); REL(n_gamma_hat); REL(n_y); REL(n_gn); REL(n_g); REL(n_rfull);
-    REL(n_w); REL(n_w0); REL(n_mk); REL(n_part); REL(n_hist); REL(n_rows);
+    REL(n_w); REL(n_w0); REL(n_wy); REL(n_wg); REL(n_mk); REL(n_part); REL(n_hist); REL(n_rows);
     invalidate_step_graph(S);
     if (S->copy_stream) {
         cudaStreamDestroy(S->copy_stream);
@@ -1202,6 +1202,7 @@ int cb200_get_counts(cb200_system* sys, cb200_counts* out) {
     out->num_rigid_contacts = c.n_contacts;
     out->ct_body_count = c.ct_body_count;
     out->solver_iterations = c.nsc_iters;
+    out->solver_slots = c.nsc_slots;
     out->solver_residual = c.nsc_residual;
     out->solver_objective = c.nsc_objective;
     return CB200_OK;

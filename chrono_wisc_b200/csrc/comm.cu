@@ -233,7 +233,7 @@ __global__ void __launch_bounds__(256) k_halo_unpack(uint32_t ghost_cap, uint32_
 int comm_halo6(Group& g, int which) {
     for (System* S : g.sys) {
         Comm* C = S->comm;
-        const double* arr = which == 0 ? S->n_w.p : S->n_w0.p;
+        const double* arr = which == 0 ? S->n_w.p : (which == 1 ? S->n_w0.p : S->n_wy.p);
         k_halo_pack<<<(S->slab_owned_cap + SLAB_CTA - 1) / SLAB_CTA, SLAB_CTA, 0, S->stream>>>(
             S->slab_owned_cap, S->slab_nb_static, reinterpret_cast<const uint8_t*>(S->slab_flags.p), S->slab_cta.p, arr,
             S->slab_has_left ? C->hsend[0].p : nullptr, S->slab_has_right ? C->hsend[1].p : nullptr, S->d_cnt);
@@ -243,7 +243,7 @@ int comm_halo6(Group& g, int which) {
     CB_TRY(comm_sendrecv(g, BUF_HALO, exact ? 0 : 6 * (size_t)g.sys[0]->slab_ghost_cap, 6));
     for (System* S : g.sys) {
         Comm* C = S->comm;
-        double* arr = which == 0 ? S->n_w.p : S->n_w0.p;
+        double* arr = which == 0 ? S->n_w.p : (which == 1 ? S->n_w0.p : S->n_wy.p);
         const uint32_t gl = S->slab_nb_static + S->slab_owned_cap, gr = gl + S->slab_ghost_cap;
         const int grid = grid_for(S, S->slab_ghost_cap, 256);
         if (S->slab_has_left)

@@ -110,6 +110,7 @@ struct DevCounters {
     uint32_t need_bins, need_entries, need_contacts, need_pairs, need_complex;
     uint32_t steps_done;         // steps fully applied since the host last reset it
     uint32_t nsc_iters;
+    uint32_t nsc_slots;          // APGD slots the last solve used: iterations + back-tracking retries
     uint32_t n_bodies, n_shapes; // extents of body / shape arrays (for device-count scans)
     uint32_t need_nsc_slots;     // APGD slot budget that would have sufficed (OVF_NSC)
     double nsc_residual, nsc_objective;
@@ -267,6 +268,7 @@ struct System {
     DevBuf<double> n_aux;     // 8 per contact: cohesion, E_n, E_t, mu_roll, mu_spin, E_spin, E_roll (only if nsc_has_aux)
     DevBuf<double> gamma, n_gamma_hat, n_y, n_gn, n_g, n_rfull;  // rows per contact each, interleaved (n,u,v[,tn,tu,tv])
     DevBuf<double> n_w, n_w0, n_mk;  // 6 nb: M^-1 D x (world angular part), M_invk world / body frame
+    DevBuf<double> n_wy, n_wg;       // 6 nb: M^-1 D y and M^-1 D gamma, carried along by linearity (nsc.cu nsc_phase)
     DevBuf<double> n_part;    // per-CTA partial sums of the fixed-shape reductions
     DevBuf<double> n_hist;    // (residual, objective) per APGD iteration of the last solve
     DevBuf<double> n_rows;    // D_T rows on request (parity path)
@@ -360,7 +362,7 @@ struct Group {
 void comm_release(System* S);         // frees the communicator (cb200_destroy)
 bool comm_multi(const System* S);     // S is one slab of a decomposed system (has a communicator or a local group)
 double* comm_gsum(System* S);         // 24 doubles of device scratch for sums over all ranks
-int comm_halo6(Group& g, int which);  // owners' 6 doubles per body (0: n_w, 1: n_w0) -> the neighbours' ghost copies
+int comm_halo6(Group& g, int which);  // owners' 6 doubles per body (0: n_w, 1: n_w0, 2: n_wy) -> the neighbours' ghost copies
 int comm_allreduce(Group& g, int first, int n);  // gsum[first..first+n) summed over all ranks, in place
 int enqueue_build_meta(System* S);  // broadphase.cu
 int enqueue_report(System* S);  // report.cu

@@ -28,6 +28,7 @@
 // The host enqueues a fixed budget of "slots" (one slot = one APGD iteration or one back-tracking retry); kernels
 // of slots past termination return at once.  A budget that proves too small raises OVF_NSC like any other capacity.
 #include "common.cuh"
+#include <stdlib.h>
 #include <float.h>
 #include <algorithm>
 #include <cstring>
@@ -39,7 +40,8 @@ enum { NSC_FRAME = 10, NSC_PART = 8, NSC_THREADS = 256, NSC_NGLOB = 16 /* slot o
 struct NscCtl {
     double L, t, theta, theta_new, beta, obj2, residual, objective, g_diff, tol_speed, norm_temp, dot_g_temp;
     int32_t iter, max_iter, act, done, redo, accepted, improved, restart, ref_variant, slots, total_iter, hist_cap;
-    int32_t ret_iter, pad;  // sum of the values Solve() returned over the phases (measures.solver.total_iteration)
+    int32_t ret_iter;       // sum of the values Solve() returned over the phases (measures.solver.total_iteration)
+    uint32_t ticket;        // CTAs of k_nsc_eval that have delivered their partial sums (last one runs the scalar part)
 };
 
 struct NscFrame {
@@ -185,6 +187,39 @@ __device__ __forceinline__ void rows_dot(const NscFrame& F, int act, const doubl
     const double2 a0 = pa[0], a1 = pa[1], a2 = pa[2], b0 = pb[0], b1 = pb[1], b2 = pb[2];
     const d3 vA = mk3(a0.x, a0.y, a1.x), wA = mk3(a1.y, a2.x, a2.y);
     const d3 vB = mk3(b0.x, b0.y, b1.x), wB = mk3(b1.y, b2.x, b2.y);
+    const d3 d = (vB + cross3(wB, F.sB)) - (vA + cross3(wA, F.sA));
+    out[0] = dot3(F.U, d);
+    if (ROWS >= 3) {
+        out[1] = out[2] = 0;
+        if (ROWS == 6)
+            out[3] = out[4] = out[5] = 0;
+        if (act >= 3) {
+            d3 V, W;
+            orthogonalize(F.U, V, W);
+            out[1] = dot3(V, d);
+            out[2] = dot3(W, d);
+            if (ROWS == 6 && act == 6) {
+                const d3 dw = wB - wA;
+                out[3] = dot3(F.U, dw);
+                out[4] = dot3(V, dw);
+                out[5] = dot3(W, dw);
+            }
+        }
+    }
+}
+
+// ... applied to the difference wa - wb of two body-space vectors (subtracted per component first)
+template <int ROWS>
+__device__ __forceinline__ void rows_dot_diff(const NscFrame& F, int act, const double* __restrict__ wa,
+                                              const double* __restrict__ wb, uint32_t bA, uint32_t bB, double* out) {
+    const double2* pa = reinterpret_cast<const double2*>(wa + 6 * (size_t)bA);
+    const double2* pb = reinterpret_cast<const double2*>(wa + 6 * (size_t)bB);
+    const double2* qa = reinterpret_cast<const double2*>(wb + 6 * (size_t)bA);
+    const double2* qb = reinterpret_cast<const double2*>(wb + 6 * (size_t)bB);
+    const double2 a0 = pa[0], a1 = pa[1], a2 = pa[2], b0 = pb[0], b1 = pb[1], b2 = pb[2];
+    const double2 c0 = qa[0], c1 = qa[1], c2 = qa[2], e0 = qb[0], e1 = qb[1], e2 = qb[2];
+    const d3 vA = mk3(a0.x - c0.x, a0.y - c0.y, a1.x - c1.x), wA = mk3(a1.y - c1.y, a2.x - c2.x, a2.y - c2.y);
+    const d3 vB = mk3(b0.x - e0.x, b0.y - e0.y, b1.x - e1.x), wB = mk3(b1.y - e1.y, b2.x - e2.x, b2.y - e2.y);
     const d3 d = (vB + cross3(wB, F.sB)) - (vA + cross3(wA, F.sA));
     out[0] = dot3(F.U, d);
     if (ROWS >= 3) {
@@ -553,7 +588,7 @@ __device__ __forceinline__ void reduce_partials(const double* __restrict__ part,
     for (int b = threadIdx.x; b < nblocks; b += NSC_THREADS)
 #pragma unroll
         for (int q = 0; q < NP; q++)
-            acc[q] += part[(size_t)b * NSC_PART + q];
+            acc[q] += __ldcg(part + (size_t)b * NSC_PART + q);  // possibly written by other CTAs of this very launch
 #pragma unroll
     for (int q = 0; q < NP; q++)
 #pragma unroll
@@ -708,31 +743,44 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_grad(const NscCtl* __restri
         block_partials<2>(acc, part);
 }
 
-// slot kernel D: N gamma_new (rows via w_gn) and every dot product of :144-147, :159-173
-// partials: [0] gn.Ngn  [1] gn.r  [2] (gn-y).g  [3] |gn-y|^2  [4] g.(gn-gamma)  [5] |res|^2
+__device__ __forceinline__ void nsc_scalar_body(NscCtl* __restrict__ ctl, const double* __restrict__ partG,
+                                                const double* __restrict__ partE, int nblocks,
+                                                double* __restrict__ hist);
+
+// slot kernel D: N gamma_new and every dot product of :144-147, :159-173
+// partials: [0] gn.Ngn  [1] gn.r  [2] (gn-y).g  [3] |gn-y|^2  [4] g.(gn-gamma)  [5] |res|^2  [6] (gn-y).N(gn-y)
+// With d = gn - y:  N gn = N y + N d = (g + r) + N d, and N d comes from the body-space difference w_gn - w_y.  The
+// last partial is what the back-tracking test needs (k_nsc_scalar).
 template <int ROWS>
-__global__ void __launch_bounds__(NSC_THREADS) k_nsc_eval(const NscCtl* __restrict__ ctl,
+__global__ void __launch_bounds__(NSC_THREADS) k_nsc_eval(NscCtl* ctl, const double* partG /* null: no scalar part */,
+                                                          double* __restrict__ hist,
                                                           const int32_t* __restrict__ bids,
                                                           const double* __restrict__ frame,
                                                           const double* __restrict__ aux, int has_aux,
-                                                          const double* __restrict__ w, const double* __restrict__ y,
+                                                          const double* __restrict__ w, const double* __restrict__ wy,
+                                                          const double* __restrict__ y,
                                                           const double* __restrict__ rfull,
                                                           const double* __restrict__ g, const double* __restrict__ gn,
                                                           const double* __restrict__ gamma, double* __restrict__ part,
                                                           const uint8_t* __restrict__ own,
                                                           const DevCounters* __restrict__ cnt) {
-    if (cnt->overflow || ctl->done)
+    if (cnt->overflow)
         return;
+    if (ctl->done) {
+        if (partG && blockIdx.x == 0 && threadIdx.x == 0)
+            ctl->accepted = 0;  // what k_nsc_scalar does for a finished phase: the commit kernel has nothing to do
+        return;
+    }
     const uint32_t nc = cnt->n_contacts;
     const int act = ctl->act;
     const double g_diff = ctl->g_diff, inv_g_diff = 1.0 / g_diff;
-    double acc[6] = {0, 0, 0, 0, 0, 0};
+    double acc[7] = {0, 0, 0, 0, 0, 0, 0};
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nc; i += gridDim.x * blockDim.x) {
         const int2 bb = reinterpret_cast<const int2*>(bids)[i];
         const NscFrame F = load_frame(frame, i);
         const NscAux A = load_aux(aux, i, has_aux != 0);
-        double n[ROWS], gnv[ROWS], yv[ROWS], gv[ROWS], gam[ROWS], rv[ROWS], tmp[ROWS];
-        rows_dot<ROWS>(F, act, w, (uint32_t)bb.x, (uint32_t)bb.y, n);
+        double n[ROWS], nd[ROWS], gnv[ROWS], yv[ROWS], gv[ROWS], gam[ROWS], rv[ROWS], tmp[ROWS];
+        rows_dot_diff<ROWS>(F, act, w, wy, (uint32_t)bb.x, (uint32_t)bb.y, nd);
         load_vec<ROWS>(gn, i, gnv);
         load_vec<ROWS>(y, i, yv);
         load_vec<ROWS>(g, i, gv);
@@ -741,13 +789,17 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_eval(const NscCtl* __restri
         const double mine = (!own || own[i]) ? 1.0 : 0.0;
 #pragma unroll
         for (int k = 0; k < ROWS; k++) {
-            if (k >= act)
-                n[k] = 0, rv[k] = 0;
-            else if (has_aux)
-                n[k] += aux_E<ROWS>(A, k) * gnv[k];
+            const double d = gnv[k] - yv[k];
+            if (k >= act) {
+                n[k] = 0, rv[k] = 0, nd[k] = 0;
+            } else {
+                if (has_aux)
+                    nd[k] += aux_E<ROWS>(A, k) * d;
+                n[k] = (gv[k] + rv[k]) + nd[k];
+            }
             acc[0] += mine * (gnv[k] * n[k]);
             acc[1] += mine * (gnv[k] * rv[k]);
-            const double d = gnv[k] - yv[k];
+            acc[6] += mine * (d * nd[k]);
             acc[2] += mine * (d * gv[k]);
             acc[3] += mine * (d * d);
             acc[4] += mine * (gv[k] * (gnv[k] - gam[k]));
@@ -760,7 +812,23 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_eval(const NscCtl* __restri
             acc[5] += mine * (e * e);
         }
     }
-    block_partials<6>(acc, part);
+    block_partials<7>(acc, part);
+    if (!partG)
+        return;
+    // single-system solve: the CTA that delivers last also runs the scalar part of the slot (k_nsc_scalar's work),
+    // which saves a launch of one CTA per slot on the critical path
+    __shared__ uint32_t s_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0)
+        s_last = atomicAdd(&ctl->ticket, 1u) == gridDim.x - 1 ? 1u : 0u;
+    __syncthreads();
+    if (!s_last)
+        return;
+    if (threadIdx.x == 0)
+        ctl->ticket = 0;
+    __threadfence();
+    nsc_scalar_body(ctl, partG, part, (int)gridDim.x, hist);
 }
 
 // slot kernel E (one CTA): the scalar part of an iteration -- back-tracking test (:147), theta/beta (:155-156),
@@ -776,12 +844,19 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_scalar(NscCtl* __restrict__
             ctl->accepted = 0;
         return;
     }
-    double sg[2], se[6];
+    nsc_scalar_body(ctl, partG, partE, nblocks, hist);
+}
+
+// (one whole CTA; the caller has checked that the phase is not done)
+__device__ __forceinline__ void nsc_scalar_body(NscCtl* __restrict__ ctl, const double* __restrict__ partG,
+                                                const double* __restrict__ partE, int nblocks,
+                                                double* __restrict__ hist) {
+    double sg[2], se[7];
     const bool redo = ctl->redo != 0;
     if (!redo)
         reduce_partials<2>(partG, nblocks, sg);
     __syncthreads();
-    reduce_partials<6>(partE, nblocks, se);
+    reduce_partials<7>(partE, nblocks, se);
     if (threadIdx.x != 0)
         return;
     ctl->slots++;
@@ -789,8 +864,12 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_scalar(NscCtl* __restrict__
         ctl->obj2 = 0.5 * sg[0] - sg[1];
     double L = ctl->L;
     const double lhs = 0.5 * se[0] - se[1];
-    const double rhs = ctl->obj2 + se[2] + 0.5 * L * se[3];
-    if (ctl->ref_variant ? (lhs >= rhs) : (lhs > rhs)) {
+    // The reference's test (:147)  obj(gn) > obj(y) + d.g + L/2 |d|^2,  d = gn - y, g = N y - r.  With N symmetric
+    // obj(gn) - obj(y) - d.g = 1/2 d.N d exactly, so the test is  d.N d > L |d|^2.  It is evaluated in that form: the
+    // two objectives agree to ~13 digits near convergence and their difference is then rounding noise, which the
+    // reference only survives because both are summed by the same code in the same order -- not so here, where N y is
+    // carried along by linearity (k_nsc_commit) while N gn is summed afresh.
+    if (ctl->ref_variant ? (se[6] >= L * se[3]) : (se[6] > L * se[3])) {
         L = 2.0 * L;
         ctl->L = L;
         ctl->t = 1.0 / L;
@@ -845,6 +924,8 @@ template <int ROWS>
 __global__ void __launch_bounds__(NSC_THREADS) k_nsc_commit(const NscCtl* __restrict__ ctl,
                                                             const double* __restrict__ gn, double* __restrict__ gamma,
                                                             double* __restrict__ y, double* __restrict__ gamma_hat,
+                                                            uint32_t nw /* 6 nb */, const double* __restrict__ w_new,
+                                                            double* __restrict__ w_y, double* __restrict__ w_g,
                                                             const DevCounters* __restrict__ cnt) {
     if (cnt->overflow || !ctl->accepted)
         return;
@@ -852,6 +933,15 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_commit(const NscCtl* __rest
     const bool improved = ctl->improved != 0, restart = ctl->restart != 0;
     const bool stop_tol = ctl->done && ctl->iter < ctl->max_iter;  // left by the tolerance break: nothing else moves
     const double beta = ctl->beta;
+    // The body-space images follow their vectors by linearity: M^-1 D y' = M^-1 D (gamma' + beta (gamma' - gamma)) is
+    // formed from M^-1 D gamma' (what pass C left in w_new) and M^-1 D gamma, instead of a pass over all contacts at
+    // the start of the next iteration (the reference evaluates N y afresh, ChSolverMulticoreAPGD.cpp:136).
+    if (!stop_tol)
+        for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < nw; j += gridDim.x * blockDim.x) {
+            const double a = w_new[j];
+            w_y[j] = restart ? a : beta * (a - w_g[j]) + a;
+            w_g[j] = a;
+        }
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nc; i += gridDim.x * blockDim.x) {
         double a[ROWS], o[ROWS];
         load_vec<ROWS>(gn, i, a);
@@ -889,6 +979,7 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_phase_end(const NscCtl* __r
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         cnt->nsc_iters = (uint32_t)ctl->ret_iter;
+        cnt->nsc_slots = (uint32_t)ctl->slots;
         cnt->nsc_hist_count = (uint32_t)ctl->total_iter;
         cnt->nsc_residual = ctl->residual;
         cnt->nsc_objective = ctl->objective;
@@ -1036,6 +1127,8 @@ static int nsc_reserve(System* S) {
     S->nsc_rows_alloc = rows;
     CB_TRY(S->n_w.reserve(6 * nb + 6));
     CB_TRY(S->n_w0.reserve(6 * nb + 6));
+    CB_TRY(S->n_wy.reserve(6 * nb + 6));
+    CB_TRY(S->n_wg.reserve(6 * nb + 6));
     CB_TRY(S->n_mk.reserve(6 * nb + 6));
     CB_TRY(S->n_part.reserve((size_t)3 * nsc_grid(S) * NSC_PART));
     const int iters = std::max(0, S->set.max_iteration_normal) + std::max(0, S->set.max_iteration_sliding) +
@@ -1093,18 +1186,18 @@ __global__ void __launch_bounds__(NSC_THREADS) k_nsc_fold(const NscCtl* __restri
 }
 
 template <int ROWS>
-static int nsc_schur_pass(Group& g, int xsel /* 0: gamma_new, 1: y */, int skip_on_redo) {
+static int nsc_schur_pass(Group& g, int xsel /* 0: gamma_new -> n_w, 1: y -> n_wy */, int skip_on_redo) {
     for (System* S : g.sys) {
         NscCtl* ctl = (NscCtl*)S->n_ctl;
         const double* x = xsel == 0 ? S->n_gn.p : S->n_y.p;
         k_nsc_scatter<ROWS, 0><<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(
             S->nb, ctl, skip_on_redo, S->bflags.p, S->mass.p, S->inv_inertia.p, S->rot.p, S->b_deg.p, S->b_inc.p,
-            S->n_frame.p, x, S->n_w.p, nullptr, nullptr, nullptr, 0.0, S->d_cnt);
+            S->n_frame.p, x, xsel == 0 ? S->n_w.p : S->n_wy.p, nullptr, nullptr, nullptr, 0.0, S->d_cnt);
         S->launches++;
     }
     // a ghost body's w is only complete on the rank that owns it: owners -> ghost copies
     if (comm_multi(g.sys[0]))
-        CB_TRY(comm_halo6(g, 0));
+        CB_TRY(comm_halo6(g, xsel == 0 ? 0 : 2));
     return CB200_OK;
 }
 
@@ -1210,13 +1303,20 @@ static int nsc_phase(Group& g, int act, int max_iter, bool first_phase) {
         k_nsc_start<ROWS><<<nsc_grid(S), NSC_THREADS, 0, S->stream>>>(ctl, S->gamma.p, S->n_y.p, S->n_gamma_hat.p, S->d_cnt);
         S->launches += 2;
     }
+    // A, once per phase: w_y = w_g = M^-1 D y for y = gamma_0; afterwards k_nsc_commit carries both along
+    CB_TRY(nsc_schur_pass<ROWS>(g, 1, 0));
+    for (System* S : g.sys)
+        CB_CUDA(cudaMemcpyAsync(S->n_wg.p, S->n_wy.p, 6 * (size_t)S->nb * sizeof(double), cudaMemcpyDeviceToDevice,
+                                S->stream));
     const int slots = max_iter + max_iter / 2 + 16 + g.sys[0]->nsc_extra_slots;
+    static const bool direct_wy = getenv("CB200_NSC_DIRECT_WY") != nullptr;  // debugging aid: N y by a pass of its own
     for (int s = 0; s < slots; s++) {
-        CB_TRY(nsc_schur_pass<ROWS>(g, 1, 1));  // A: w = M^-1 D y
+        if (direct_wy)
+            CB_TRY(nsc_schur_pass<ROWS>(g, 1, 1));
         for (System* S : g.sys) {
             const Ptr P = ptrs(S);
             k_nsc_grad<ROWS><<<nsc_grid(S), NSC_THREADS, 0, S->stream>>>((NscCtl*)S->n_ctl, S->c_bids.p, S->n_frame.p,
-                                                                         S->n_aux.p, S->nsc_has_aux, S->n_w.p, S->n_y.p,
+                                                                         S->n_aux.p, S->nsc_has_aux, S->n_wy.p, S->n_y.p,
                                                                          S->n_rfull.p, S->n_g.p, S->n_gn.p, P.part1, P.own,
                                                                          S->d_cnt);  // B
             S->launches++;
@@ -1225,9 +1325,10 @@ static int nsc_phase(Group& g, int act, int max_iter, bool first_phase) {
         for (System* S : g.sys) {
             const Ptr P = ptrs(S);
             const int G = nsc_grid(S);
-            k_nsc_eval<ROWS><<<G, NSC_THREADS, 0, S->stream>>>((NscCtl*)S->n_ctl, S->c_bids.p, S->n_frame.p, S->n_aux.p,
-                                                               S->nsc_has_aux, S->n_w.p, S->n_y.p, S->n_rfull.p, S->n_g.p,
-                                                               S->n_gn.p, S->gamma.p, P.part2, P.own, S->d_cnt);  // D
+            k_nsc_eval<ROWS><<<G, NSC_THREADS, 0, S->stream>>>((NscCtl*)S->n_ctl, multi ? nullptr : P.part1, S->n_hist.p,
+                                                               S->c_bids.p, S->n_frame.p, S->n_aux.p,
+                                                               S->nsc_has_aux, S->n_w.p, S->n_wy.p, S->n_y.p, S->n_rfull.p,
+                                                               S->n_g.p, S->n_gn.p, S->gamma.p, P.part2, P.own, S->d_cnt);  // D
             if (multi)
                 k_nsc_fold<<<1, NSC_THREADS, 0, S->stream>>>((NscCtl*)S->n_ctl, P.part1, P.part2, G, P.gs, S->d_cnt);
             S->launches += multi ? 2 : 1;
@@ -1239,13 +1340,12 @@ static int nsc_phase(Group& g, int act, int max_iter, bool first_phase) {
         for (System* S : g.sys) {
             const Ptr P = ptrs(S);
             NscCtl* ctl = (NscCtl*)S->n_ctl;
-            if (multi)
+            if (multi)  // (a single system ran this part in the last CTA of k_nsc_eval)
                 k_nsc_scalar<<<1, NSC_THREADS, 0, S->stream>>>(ctl, P.gs, P.gs + NSC_PART, 1, S->n_hist.p, S->d_cnt);  // E
-            else
-                k_nsc_scalar<<<1, NSC_THREADS, 0, S->stream>>>(ctl, P.part1, P.part2, nsc_grid(S), S->n_hist.p, S->d_cnt);
             k_nsc_commit<ROWS><<<nsc_grid(S), NSC_THREADS, 0, S->stream>>>(ctl, S->n_gn.p, S->gamma.p, S->n_y.p,
-                                                                           S->n_gamma_hat.p, S->d_cnt);  // F
-            S->launches += 2;
+                                                                           S->n_gamma_hat.p, 6 * S->nb, S->n_w.p,
+                                                                           S->n_wy.p, S->n_wg.p, S->d_cnt);  // F
+            S->launches += multi ? 2 : 1;
         }
     }
     for (System* S : g.sys) {

@@ -94,7 +94,8 @@ typedef struct cb200_counts {
     uint32_t num_rigid_contacts;         /* N_c */
     uint32_t ct_body_count;              /* bodies with >= 1 contact, MC/solver/ChIterativeSolverMulticoreSMC.cpp:726 */
     uint32_t solver_iterations;          /* NSC: iterations of the last Solve */
-    uint32_t reserved[3];
+    uint32_t solver_slots;               /* NSC: ... plus its back-tracking retries (:148-154), summed over the phases */
+    uint32_t reserved[2];
     double min_bounding_point[3];        /* global_origin */
     double max_bounding_point[3];
     double bin_size[3];

@@ -20,7 +20,7 @@ l0 = s.KernelLaunches()
 t0 = time.time(); s.DoSteps(steps); s.Synchronize(); dt = time.time() - t0
 c = s.GetCounts()
 nb = scene['mass'].size
-print(f"timed: {dt/steps*1e3:.3f} ms/step wall, {nb*steps/dt/1e6:.2f} M particle-steps/s, N_c={c.num_rigid_contacts} iters={c.solver_iterations} launches/step={(s.KernelLaunches()-l0)/steps:.0f}")
+print(f"timed: {dt/steps*1e3:.3f} ms/step wall, {nb*steps/dt/1e6:.2f} M particle-steps/s, N_c={c.num_rigid_contacts} iters={c.solver_iterations} slots={c.solver_slots} launches/step={(s.KernelLaunches()-l0)/steps:.0f}")
 for name in ("step", "update", "collision", "collision_broad", "collision_narrow", "advance", "integrate"):
     print(f"  {name:18s} {s.GetTimer(name)*1e3:.4f} ms")
 nc = c.num_rigid_contacts
