@@ -153,6 +153,7 @@ static int alloc_complex(System* S, uint32_t nrec, uint32_t nslots) {
     S->cap_complex = (uint32_t)(S->cplx_rec.cap / 4);
     CB_TRY(S->cplx_n.reserve(S->cap_complex));
     CB_TRY(S->cplx_cls.reserve(4 * (size_t)S->cap_complex));
+    CB_TRY(S->cplx_bb.reserve(5 * (size_t)S->cap_complex));
     CB_TRY(S->cplx_out.reserve(11 * (size_t)nslots));
     S->cap_cslots = (uint32_t)(S->cplx_out.cap / 11);
     return CB200_OK;
@@ -343,7 +344,7 @@ void cb200_destroy(cb200_system* sys) {
     REL(s_box); REL(s_meta); REL(mat_smc); REL(mat_nsc); REL(bin_intersections); REL(bin_start); REL(bin_cursor);
     REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_mask); REL(ent_off); REL(slow_bins); REL(long_bins); REL(pair_q); REL(large_list); REL(pairs);
     REL(c_norm); REL(c_pta); REL(c_ptb); REL(c_depth); REL(c_erad); REL(c_bids); REL(c_shapes); REL(c_mats);
-    REL(ent_cmask); REL(ent_cbase); REL(cplx_rec); REL(cplx_n); REL(cplx_cls); REL(cplx_out); REL(c_src);
+    REL(ent_cmask); REL(ent_cbase); REL(cplx_rec); REL(cplx_n); REL(cplx_cls); REL(cplx_bb); REL(cplx_out); REL(c_src);
     REL(ct_force); REL(ct_torque); REL(b_deg); REL(b_cursor); REL(b_inc); REL(b_force); REL(heavy_list);
     REL(heavy_part); REL(n_frame); REL(n_aux); REL(gamma); REL(n_gamma_hat); REL(n_y); REL(n_gn); REL(n_g); REL(n_rfull);
     REL(n_w); REL(n_w0); REL(n_wy); REL(n_wg); REL(n_mk); REL(n_part); REL(n_hist); REL(n_rows);

@@ -95,6 +95,7 @@ __global__ void k_reset_counters(DevCounters* cnt, uint32_t nb, uint32_t ns, boo
         cnt->n_slow = cnt->n_long = cnt->n_pairq = 0;
         cnt->n_complex = cnt->n_cslots = 0;
         cnt->n_cls[0] = cnt->n_cls[1] = cnt->n_cls[2] = cnt->n_cls[3] = 0;
+        cnt->n_bb[0] = cnt->n_bb[1] = cnt->n_bb[2] = cnt->n_bb[3] = cnt->n_bb[4] = 0;
         // cnt->unsupported is sticky: only the host clears it, after it has read it (api.cu clear_unsupported)
     }
 }

@@ -122,6 +122,7 @@ struct DevCounters {
     uint32_t n_pairq;            // (wall-bin pairs with a non-sphere) queued for k_pair_queue (right behind n_long)
     uint32_t need_pairq;
     uint32_t n_cls[4];           // complex pairs per narrowphase class (k_cplx_collect buckets them for k_cplx_narrow)
+    uint32_t n_bb[5];            // box-box pairs per branch of box_box (right behind n_cls: cleared together)
 };
 
 struct Timer {
@@ -233,6 +234,7 @@ struct System {
     DevBuf<uint32_t> cplx_rec;   // 4 per record: entry, shape A, shape B, first slot
     DevBuf<uint32_t> cplx_n;     // contacts found per record
     DevBuf<uint32_t> cplx_cls;   // 4 x cap_complex: record indices bucketed by narrowphase class
+    DevBuf<uint32_t> cplx_bb;    // 5 x cap_complex: box-box records bucketed by the branch of box_box they take
     DevBuf<double> cplx_out;     // 11 per slot: normal, point A, point B, depth, effective radius
     DevBuf<uint32_t> c_src;      // cap_contacts  slot + 1 of a contact computed by the complex path, 0 otherwise
 

@@ -855,6 +855,24 @@ __global__ void __launch_bounds__(256) k_cplx_collect(const ShapeMeta* __restric
     }
 }
 
+// capacity check of the complex path: one thread, before the class kernels (which simply return on overflow)
+__global__ void k_cplx_check(uint32_t cap_rec, uint32_t cap_slots, DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    const uint32_t nrec = cnt->n_complex, nslots = cnt->n_cslots;
+    if (nrec > cap_rec || nslots > cap_slots) {
+        cnt->need_complex = nrec;
+        cnt->need_cslots = nslots;
+        __threadfence();
+        atomicOr(&cnt->overflow, (uint32_t)OVF_COMPLEX);
+    }
+}
+
+// One kernel per narrowphase class (pair_class): a kernel is allocated the registers of the heaviest function it can
+// reach, so capsule-capsule pairs should not run at the occupancy box-box pairs force (15-axis SAT + clipping), and
+// inside a class the warps stay convergent.  CLS 0..2 call their function directly when the analytic path is on
+// (algorithm != MPR); CLS 3 and the all-MPR mode go through the general dispatcher.
+template <int CLS>
 __global__ void __launch_bounds__(128) k_cplx_narrow(const ShapeMeta* __restrict__ meta,
                                                      const double* __restrict__ s_wpos,
                                                      const double* __restrict__ s_wrot,
@@ -864,39 +882,36 @@ __global__ void __launch_bounds__(128) k_cplx_narrow(const ShapeMeta* __restrict
                                                      const double* __restrict__ s_verts, double envelope, int algorithm,
                                                      const uint32_t* __restrict__ rec,
                                                      const uint32_t* __restrict__ cls_list, uint32_t cap_rec,
-                                                     uint32_t cap_slots, uint32_t* __restrict__ cplx_n,
-                                                     double* __restrict__ cplx_out, uint32_t* __restrict__ ent_cnt,
-                                                     DevCounters* __restrict__ cnt) {
+                                                     uint32_t* __restrict__ cplx_n, double* __restrict__ cplx_out,
+                                                     uint32_t* __restrict__ ent_cnt, DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
-    const uint32_t nrec = cnt->n_complex, nslots = cnt->n_cslots;
-    if (nrec > cap_rec || nslots > cap_slots) {
-        // every CTA sees the same counters, so all of them leave; the last CTA of the grid records what was needed
-        // and only then raises the flag (the CTAs before it may still be about to read `overflow`)
-        if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) {
-            cnt->need_complex = nrec;
-            cnt->need_cslots = nslots;
-            __threadfence();
-            atomicOr(&cnt->overflow, (uint32_t)OVF_COMPLEX);
-        }
-        return;
-    }
     uint32_t bad = 0;
-    // thread t takes the t-th record of the class-by-class order (classes padded to whole warps)
-    const uint32_t c0 = (cnt->n_cls[0] + 31u) & ~31u, c1 = c0 + ((cnt->n_cls[1] + 31u) & ~31u);
-    const uint32_t c2 = c1 + ((cnt->n_cls[2] + 31u) & ~31u), c3 = c2 + ((cnt->n_cls[3] + 31u) & ~31u);
-    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < c3; t += gridDim.x * blockDim.x) {
-        const int cls = t < c0 ? 0 : (t < c1 ? 1 : (t < c2 ? 2 : 3));
-        const uint32_t k = t - (cls == 0 ? 0u : (cls == 1 ? c0 : (cls == 2 ? c1 : c2)));
-        if (k >= cnt->n_cls[cls])
-            continue;
-        const uint32_t i = cls_list[(size_t)cls * cap_rec + k];
+    const uint32_t ncls = cnt->n_cls[CLS];
+    const double sep = 2 * envelope;
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < ncls; k += gridDim.x * blockDim.x) {
+        const uint32_t i = cls_list[(size_t)CLS * cap_rec + k];
         const uint4 r = reinterpret_cast<const uint4*>(rec)[i];
         const ShapeMeta mA = meta[r.y], mB = meta[r.z];
         const ShapeView A = make_view_full(r.y, mA, s_wpos, s_wrot, s_dims, s_lrot, rot, s_verts);
         const ShapeView B = make_view_full(r.z, mB, s_wpos, s_wrot, s_dims, s_lrot, rot, s_verts);
         Contact out[MAX_PAIR_CONTACTS];
-        int n = narrow_complex(A, B, algorithm, envelope, out);
+        int n;
+        if (CLS == 0 && algorithm != 0) {
+            n = capsule_capsule(A.pos, A.rot, A.d0, A.d1, B.pos, B.rot, B.d0, B.d1, sep, out);
+        } else if (CLS == 1 && algorithm != 0) {
+            // one call site for both orders (two would be two divergent copies of the function in a warp)
+            const bool swap = A.type != CB200_BOX;
+            const ShapeView& X = swap ? B : A;
+            const ShapeView& Y = swap ? A : B;
+            n = box_capsule(X.pos, X.rot, mk3(X.d0, X.d1, X.d2), Y.pos, Y.rot, Y.d0, Y.d1, sep, out);
+            if (swap)
+                flip_contacts(out, n);
+        } else if (CLS == 2 && algorithm != 0) {
+            n = box_box(A.pos, A.rot, mk3(A.d0, A.d1, A.d2), B.pos, B.rot, mk3(B.d0, B.d1, B.d2), sep, out);
+        } else {
+            n = narrow_complex(A, B, algorithm, envelope, out);
+        }
         if (n < 0) {
             bad++;
             n = 0;
@@ -917,6 +932,87 @@ __global__ void __launch_bounds__(128) k_cplx_narrow(const ShapeMeta* __restrict
     }
     if (bad)
         atomicAdd(&cnt->unsupported, bad);
+}
+
+// Box-box pairs (class 2 under PRIMS / HYBRID) in two steps.  box_box has six branches of very different length
+// (nothing, one corner contact, edge-edge, face-face clipping with up to 8 contacts, ...); run pair by pair the threads
+// of a warp wait for each other (measured: 5.8 of 32 lanes active, 2.2 ms per step in the 518k mixed bed).
+//   k_bb_classify  SAT + feature codes only (the same arithmetic as the head of box_box): separated pairs are done,
+//                  the others are bucketed by branch (atomic cursors: the order inside a bucket is irrelevant, every
+//                  record writes its own slots)
+//   k_bb_contacts  walks the buckets branch by branch (padded to whole warps) and runs box_box
+__global__ void __launch_bounds__(128) k_bb_classify(const ShapeMeta* __restrict__ meta,
+                                                     const double* __restrict__ s_wpos,
+                                                     const double* __restrict__ s_wrot,
+                                                     const double* __restrict__ s_dims,
+                                                     const double* __restrict__ s_lrot, const double* __restrict__ rot,
+                                                     const double* __restrict__ s_verts, double envelope,
+                                                     const uint32_t* __restrict__ rec,
+                                                     const uint32_t* __restrict__ cls_list, uint32_t cap_rec,
+                                                     uint32_t* __restrict__ cplx_n, uint32_t* __restrict__ bb_list,
+                                                     DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    const uint32_t ncls = cnt->n_cls[2];
+    const double sep = 2 * envelope;
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < ncls; k += gridDim.x * blockDim.x) {
+        const uint32_t i = cls_list[(size_t)2 * cap_rec + k];
+        const uint4 r = reinterpret_cast<const uint4*>(rec)[i];
+        const ShapeView A = make_view_full(r.y, meta[r.y], s_wpos, s_wrot, s_dims, s_lrot, rot, s_verts);
+        const ShapeView B = make_view_full(r.z, meta[r.z], s_wpos, s_wrot, s_dims, s_lrot, rot, s_verts);
+        const int key = box_box_case(A.pos, A.rot, mk3(A.d0, A.d1, A.d2), B.pos, B.rot, mk3(B.d0, B.d1, B.d2), sep);
+        if (key == 0 || key == 6)
+            cplx_n[i] = 0;
+        else
+            bb_list[(size_t)(key - 1) * cap_rec + atomicAdd(&cnt->n_bb[key - 1], 1u)] = i;
+    }
+}
+
+__global__ void __launch_bounds__(128) k_bb_contacts(const ShapeMeta* __restrict__ meta,
+                                                     const double* __restrict__ s_wpos,
+                                                     const double* __restrict__ s_wrot,
+                                                     const double* __restrict__ s_dims,
+                                                     const double* __restrict__ s_lrot, const double* __restrict__ rot,
+                                                     const double* __restrict__ s_verts, double envelope,
+                                                     const uint32_t* __restrict__ rec,
+                                                     const uint32_t* __restrict__ bb_list, uint32_t cap_rec,
+                                                     uint32_t* __restrict__ cplx_n, double* __restrict__ cplx_out,
+                                                     uint32_t* __restrict__ ent_cnt, DevCounters* __restrict__ cnt) {
+    if (cnt->overflow)
+        return;
+    const double sep = 2 * envelope;
+    uint32_t start[6];
+    start[0] = 0;
+#pragma unroll
+    for (int q = 0; q < 5; q++)
+        start[q + 1] = start[q] + ((cnt->n_bb[q] + 31u) & ~31u);
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < start[5]; t += gridDim.x * blockDim.x) {
+        int q = 0;
+#pragma unroll
+        for (int u = 1; u < 5; u++)
+            q += t >= start[u] ? 1 : 0;
+        const uint32_t k = t - start[q];
+        if (k >= cnt->n_bb[q])
+            continue;
+        const uint32_t i = bb_list[(size_t)q * cap_rec + k];
+        const uint4 r = reinterpret_cast<const uint4*>(rec)[i];
+        const ShapeView A = make_view_full(r.y, meta[r.y], s_wpos, s_wrot, s_dims, s_lrot, rot, s_verts);
+        const ShapeView B = make_view_full(r.z, meta[r.z], s_wpos, s_wrot, s_dims, s_lrot, rot, s_verts);
+        Contact out[MAX_PAIR_CONTACTS];
+        int n = box_box(A.pos, A.rot, mk3(A.d0, A.d1, A.d2), B.pos, B.rot, mk3(B.d0, B.d1, B.d2), sep, out);
+        if (n > 8)
+            n = 8;  // pair_slots(box, box)
+        cplx_n[i] = (uint32_t)n;
+        for (int c = 0; c < n; c++) {
+            double* o = cplx_out + 11 * (size_t)(r.w + c);
+            o[0] = out[c].n.x, o[1] = out[c].n.y, o[2] = out[c].n.z;
+            o[3] = out[c].p1.x, o[4] = out[c].p1.y, o[5] = out[c].p1.z;
+            o[6] = out[c].p2.x, o[7] = out[c].p2.y, o[8] = out[c].p2.z;
+            o[9] = out[c].depth, o[10] = out[c].erad;
+        }
+        if (n)
+            atomicAdd(&ent_cnt[r.x], (uint32_t)n);
+    }
 }
 
 // k_pair_store: one thread per entry; turns masks (or, for long bins, a re-walk of the row) into 64-bit shape-pair
@@ -1260,7 +1356,7 @@ static int enqueue_pair_pass_t(System* S, int mode, int64_t* out, uint32_t cap) 
     if (CPLX && !clean) {
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_complex, 0, 4, S->stream));
         CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_cslots, 0, 4, S->stream));
-        CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_cls[0], 0, 16, S->stream));
+        CB_CUDA(cudaMemsetAsync(&S->d_cnt->n_cls[0], 0, 16 + 20, S->stream));  // n_cls, n_bb
     }
     CB_TRY(timer_start(S, "k_pair_masks"));
     k_pair_masks<CPLX><<<gm, PAIR_THREADS, 0, S->stream>>>(
@@ -1296,11 +1392,27 @@ static int enqueue_pair_pass_t(System* S, int mode, int64_t* out, uint32_t cap) 
         k_cplx_collect<<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
             S->s_meta.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p, S->ent_cmask.p, algorithm, S->ent_cbase.p,
             S->cplx_rec.p, S->cplx_cls.p, S->cap_complex, S->d_cnt);
-        k_cplx_narrow<<<grid_for(S, S->cap_complex, 128), 128, 0, S->stream>>>(
-            S->s_meta.p, S->s_wpos.p, S->s_wrot.p, S->s_dims.p, S->s_lrot.p, S->rot.p, S->s_verts.p, env, algorithm,
-            S->cplx_rec.p, S->cplx_cls.p, S->cap_complex, S->cap_cslots, S->cplx_n.p, S->cplx_out.p, S->ent_off.p,
-            S->d_cnt);
-        S->launches += 2;
+        k_cplx_check<<<1, 1, 0, S->stream>>>(S->cap_complex, S->cap_cslots, S->d_cnt);
+#define CPLX_NARROW(CLS, STREAM)                                                                                      \
+    k_cplx_narrow<CLS><<<grid_for(S, S->cap_complex, 128), 128, 0, STREAM>>>(                                         \
+        S->s_meta.p, S->s_wpos.p, S->s_wrot.p, S->s_dims.p, S->s_lrot.p, S->rot.p, S->s_verts.p, env, algorithm,      \
+        S->cplx_rec.p, S->cplx_cls.p, S->cap_complex, S->cplx_n.p, S->cplx_out.p, S->ent_off.p, S->d_cnt)
+        CPLX_NARROW(0, S->stream);
+        CPLX_NARROW(1, S->stream);
+        if (algorithm != 0) {
+            k_bb_classify<<<grid_for(S, S->cap_complex, 128), 128, 0, S->stream>>>(
+                S->s_meta.p, S->s_wpos.p, S->s_wrot.p, S->s_dims.p, S->s_lrot.p, S->rot.p, S->s_verts.p, env,
+                S->cplx_rec.p, S->cplx_cls.p, S->cap_complex, S->cplx_n.p, S->cplx_bb.p, S->d_cnt);
+            k_bb_contacts<<<grid_for(S, S->cap_complex, 128), 128, 0, S->stream>>>(
+                S->s_meta.p, S->s_wpos.p, S->s_wrot.p, S->s_dims.p, S->s_lrot.p, S->rot.p, S->s_verts.p, env,
+                S->cplx_rec.p, S->cplx_bb.p, S->cap_complex, S->cplx_n.p, S->cplx_out.p, S->ent_off.p, S->d_cnt);
+            S->launches++;
+        } else {
+            CPLX_NARROW(2, S->stream);
+        }
+        CPLX_NARROW(3, S->stream);
+#undef CPLX_NARROW
+        S->launches += 6;
     }
     CB_TRY(scan_u32(S, S->ent_off.p, S->ent_off.p, &S->d_cnt->n_intersections, S->cap_entries));
     CB_TRY(aux_fork(S, 1, &s_long));  // the rows of long bins are stored beside the others

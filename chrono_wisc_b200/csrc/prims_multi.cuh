@@ -399,6 +399,38 @@ __device__ __forceinline__ void push_pointpair(Contact* out, int& j, const d3& p
     push_contact(out, j, delta / dist, pT, pO, penetrated * dist, erad);
 }
 
+// Which branch of box_box a pair takes: 0 separated, 1 corner, 2 edge-edge, 3 face-face, 4 face of T / edge of O,
+// 5 face of O / edge of T (6: none of them, no contact).  Same arithmetic as the head of box_box; used to order the
+// box-box pairs so that the threads of a warp run the same branch (pairs.cu k_bb_classify).
+__device__ inline int box_box_case(const d3& posT, const q4& rotT, const d3& hdimsT, const d3& posO, const q4& rotO,
+                                   const d3& hdimsO, double separation) {
+    const d3 pos = rotate_t(posO - posT, rotT);
+    const q4 rot = qmul(qinv(rotT), rotO);
+    d3 dirT;
+    const int penetrated = box_intersects_box(hdimsT, hdimsO, pos, rot, separation, dirT);
+    if (penetrated == 0)
+        return 0;
+    if (dot3(pos, dirT) > 0)
+        dirT = -dirT;
+    const d3 dirO = rotate_t(-dirT, rot);
+    const unsigned codeT = box_closest_feature(dirT), codeO = box_closest_feature(dirO);
+    const bool Tcorner = (codeT == 7), Tedge = (codeT == 3) || (codeT == 5) || (codeT == 6),
+               Tface = (codeT == 1) || (codeT == 2) || (codeT == 4);
+    const bool Ocorner = (codeO == 7), Oedge = (codeO == 3) || (codeO == 5) || (codeO == 6),
+               Oface = (codeO == 1) || (codeO == 2) || (codeO == 4);
+    if (Tcorner || Ocorner)
+        return 1;
+    if (Tedge && Oedge)
+        return 2;
+    if (Tface && Oface)
+        return 3;
+    if (Tface)
+        return 4;
+    if (Oface)
+        return 5;
+    return 6;
+}
+
 // ChNarrowphasePRIMS.cpp:924-1224
 __device__ inline int box_box(const d3& posT, const q4& rotT, const d3& hdimsT, const d3& posO, const q4& rotO,
                               const d3& hdimsO, double separation, Contact* out) {
