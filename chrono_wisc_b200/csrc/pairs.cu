@@ -665,6 +665,7 @@ __global__ void __launch_bounds__(32 * SLOW_WARPS) k_pair_masks_slow(
     __shared__ WindowT<SLOW_WIN> W[SLOW_WARPS];
     __shared__ unsigned long long smask[SLOW_WARPS][SLOW_WIN];
     __shared__ unsigned long long scmask[CPLX ? SLOW_WARPS : 1][SLOW_WIN];
+    __shared__ uint16_t squeue[SLOW_WARPS][64];  // (lower entry << 8 | higher entry) of pairs that passed the filter
     if (cnt->overflow)
         return;
     const GridParams g = load_grid(cnt);
@@ -695,8 +696,47 @@ __global__ void __launch_bounds__(32 * SLOW_WARPS) k_pair_masks_slow(
             const uint32_t full = bk * h;
             const uint32_t total = full + ((bk & 1u) ? 0u : (bk >> 1));
             const uint32_t M = ((1u << 20) + bk - 1) / bk;  // p / k == (p * M) >> 20 for p < 2048, k <= 64
+            // Two phases, so that the lanes of the warp do the same thing: (1) the pair filter and the AABB test of 32
+            // pairs, survivors compacted into a small queue; (2) whenever 32 of them are waiting (and at the end) the
+            // narrowphase decision -- analytic single-contact tests against spheres, "complex" marking for the rest.
+            // In a mixed bed two thirds of the entries are not spheres and one pair in seven survives the filter.
+            uint32_t qn = 0;  // queued survivors (warp-uniform)
+            auto drain = [&](uint32_t upto) {
+                if (lane < upto) {
+                    const uint32_t ac = squeue[wid][lane];
+                    const uint32_t a = ac >> 8, c = ac & 0xffu;
+                    Rec RA, RB;
+                    win_get(W[wid], (int)a, RA);
+                    win_get(W[wid], (int)c, RB);
+                    np++;
+                    int dec = 1;
+                    if (mode != MODE_PAIRS) {
+                        const int n = pair_hit(RA, RB, sep, algorithm, s_wrot, s_dims);
+                        dec = n < 0 ? 2 : n;
+                    }
+                    if (dec == 1)
+                        atomicOr(&smask[wid][a], 1ull << c);
+                    else if (dec == 2) {
+                        if (CPLX)
+                            atomicOr(&scmask[CPLX ? wid : 0][a], 1ull << c);
+                        else
+                            ncx++;
+                    }
+                }
+                __syncwarp();
+                // what is left moves to the front
+                const uint32_t rest = qn - upto;
+                const uint32_t mv = lane < rest ? squeue[wid][upto + lane] : 0u;
+                __syncwarp();
+                if (lane < rest)
+                    squeue[wid][lane] = (uint16_t)mv;
+                __syncwarp();
+                qn = rest;
+            };
             for (uint32_t p0 = 0; p0 < total; p0 += 32) {
                 const uint32_t p = p0 + lane;
+                bool pass = false;
+                uint32_t a = 0, c = 0;
                 if (p < total) {
                     uint32_t i, j;
                     if (p < full) {
@@ -709,21 +749,22 @@ __global__ void __launch_bounds__(32 * SLOW_WARPS) k_pair_masks_slow(
                         i = p - full;
                         j = i + (bk >> 1);
                     }
-                    const uint32_t a = min(i, j), c = max(i, j);
+                    a = min(i, j), c = max(i, j);
                     Rec RA, RB;
                     win_get(W[wid], (int)a, RA);
                     win_get(W[wid], (int)c, RB);
-                    const int dec = pair_decide<true>(RA, RB, g, b, mode, sep, algorithm, s_wrot, s_dims, np);
-                    if (dec == 1)
-                        atomicOr(&smask[wid][a], 1ull << c);
-                    else if (dec == 2) {
-                        if (CPLX)
-                            atomicOr(&scmask[CPLX ? wid : 0][a], 1ull << c);
-                        else
-                            ncx++;
-                    }
+                    pass = !(RA.body == UINT_MAX || !(RA.info & 2u)) && pair_passes<true>(RA, RB, g, b);
                 }
+                const unsigned m = __ballot_sync(0xffffffffu, pass);
+                if (pass)
+                    squeue[wid][qn + (uint32_t)__popc(m & ((1u << lane) - 1u))] = (uint16_t)(a << 8 | c);
+                qn += (uint32_t)__popc(m);
+                __syncwarp();
+                if (qn >= 32)
+                    drain(32);
             }
+            if (qn)
+                drain(qn);
             __syncwarp();
             for (uint32_t x = lane; x < bk; x += 32) {
                 const unsigned long long mk = smask[wid][x];
@@ -782,75 +823,125 @@ __global__ void __launch_bounds__(256) k_cplx_collect(const ShapeMeta* __restric
         return;
     const uint32_t ni = cnt->n_intersections;
     const int lane = threadIdx.x & 31;
-    // warp-uniform trip count: the record / slot ranges of a warp's entries are reserved with one atomic each
+    // A warp takes 32 entries.  Their complex candidates (the set bits of the 32 masks, 0..64 each) are numbered through
+    // by a warp scan and then dealt out evenly to the lanes, 32 at a time -- an entry with 40 candidates does not keep
+    // 31 lanes waiting.  Record t of the warp belongs to the entry whose scanned range holds t; inside an entry the
+    // records follow the bit order, which is what k_pair_store relies on (ent_cbase + rank of the bit).
     for (uint32_t e0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; e0 < ni; e0 += gridDim.x * blockDim.x) {
         const uint32_t e = e0 + lane;
-        unsigned long long m = e < ni ? ent_cmask[e] : 0ull;
+        const unsigned long long m = e < ni ? ent_cmask[e] : 0ull;
         if (!__any_sync(0xffffffffu, m != 0ull))
             continue;
-        uint32_t s = 0, sA = 0, count = 0, nslots = 0;
-        unsigned long long kk = 0ull;
+        uint32_t s = 0, sA = 0;
         int tA = 0;
         if (m) {
             s = (uint32_t)bin_start[ent_bin[e]];
             sA = ent_shape[e];
             tA = (meta[sA].info >> 8) & 0xff;
-            count = (uint32_t)__popcll(m);
-            for (unsigned long long u = m; u; u &= u - 1) {
-                const int j = __ffsll((long long)u) - 1;
-                const int tB = (meta[ent_shape[s + j]].info >> 8) & 0xff;
-                nslots += pair_slots(tA, tB, algorithm);
-                kk += 1ull << (16 * pair_class(tA, tB, algorithm));  // per-class counts, packed 4 x 16 bit
-            }
         }
-        uint32_t pc = count, ps = nslots;  // inclusive warp scans
-        unsigned long long pk = kk;        // 32 lanes x 64 pairs = 2048 < 65536: the packed counts cannot carry over
+        const uint32_t count = (uint32_t)__popcll(m);
+        uint32_t pc = count;  // inclusive warp scan
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t a = __shfl_up_sync(0xffffffffu, pc, d), b = __shfl_up_sync(0xffffffffu, ps, d);
-            const unsigned long long c = __shfl_up_sync(0xffffffffu, pk, d);
+            const uint32_t a = __shfl_up_sync(0xffffffffu, pc, d);
             if (lane >= d)
-                pc += a, ps += b, pk += c;
+                pc += a;
         }
-        uint32_t bc = 0, bs = 0, b0 = 0, b1 = 0, b2 = 0, b3 = 0;
-        if (lane == 31) {
-            bc = atomicAdd(&cnt->n_complex, pc);
-            bs = atomicAdd(&cnt->n_cslots, ps);
-            const uint32_t t0 = (uint32_t)(pk & 0xffff), t1 = (uint32_t)((pk >> 16) & 0xffff);
-            const uint32_t t2 = (uint32_t)((pk >> 32) & 0xffff), t3 = (uint32_t)((pk >> 48) & 0xffff);
-            if (t0) b0 = atomicAdd(&cnt->n_cls[0], t0);
-            if (t1) b1 = atomicAdd(&cnt->n_cls[1], t1);
-            if (t2) b2 = atomicAdd(&cnt->n_cls[2], t2);
-            if (t3) b3 = atomicAdd(&cnt->n_cls[3], t3);
+        const uint32_t total = __shfl_sync(0xffffffffu, pc, 31);
+        uint32_t bc = 0;
+        if (lane == 31)
+            bc = atomicAdd(&cnt->n_complex, total);
+        bc = __shfl_sync(0xffffffffu, bc, 31);
+        if (m)
+            ent_cbase[e] = bc + pc - count;
+        // the partner of record t (the r-th set bit of its owner's mask), its class and its contact slots
+        auto record = [&](uint32_t t, int& L, uint32_t& sB, int& c, uint32_t& slots) {
+            // owner: the first lane whose inclusive count exceeds t (all lanes take part in the shuffles)
+            L = 0;
+#pragma unroll
+            for (int step = 16; step > 0; step >>= 1) {
+                const uint32_t v = __shfl_sync(0xffffffffu, pc, L + step - 1);
+                if (v <= t)
+                    L += step;
+            }
+            L = min(L, 31);
+            const uint32_t incl = __shfl_sync(0xffffffffu, pc, L), cntL = __shfl_sync(0xffffffffu, count, L);
+            const unsigned long long mL = __shfl_sync(0xffffffffu, m, L);
+            const uint32_t sL = __shfl_sync(0xffffffffu, s, L);
+            const int tAL = __shfl_sync(0xffffffffu, tA, L);
+            c = 0, slots = 0, sB = 0;
+            if (t < total) {
+                const uint32_t r = t - (incl - cntL);
+                const uint32_t lo = (uint32_t)mL, hi = (uint32_t)(mL >> 32), nlo = (uint32_t)__popc(lo);
+                const int j = r < nlo ? (int)__fns(lo, 0, (int)r + 1) : 32 + (int)__fns(hi, 0, (int)(r - nlo) + 1);
+                sB = ent_shape[sL + j];
+                const int tB = (meta[sB].info >> 8) & 0xff;
+                c = pair_class(tAL, tB, algorithm);
+                slots = pair_slots(tAL, tB, algorithm);
+            }
+        };
+        // pass 1: what the warp needs of the contact slots and of each class list -> one atomic each (any disjoint
+        // range will do: k_pair_store finds the slots through the record, the order inside a class list is irrelevant)
+        uint32_t my_slots = 0;
+        unsigned long long my_cls = 0ull;  // 4 x 16 bit
+        for (uint32_t t0 = 0; t0 < total; t0 += 32) {
+            int L, c;
+            uint32_t sB, slots;
+            record(t0 + lane, L, sB, c, slots);
+            if (t0 + lane < total) {
+                my_slots += slots;
+                my_cls += 1ull << (16 * c);
+            }
         }
-        bc = __shfl_sync(0xffffffffu, bc, 31), bs = __shfl_sync(0xffffffffu, bs, 31);
-        b0 = __shfl_sync(0xffffffffu, b0, 31), b1 = __shfl_sync(0xffffffffu, b1, 31);
-        b2 = __shfl_sync(0xffffffffu, b2, 31), b3 = __shfl_sync(0xffffffffu, b3, 31);
-        if (!m)
-            continue;
-        uint32_t base = bc + pc - count, slot = bs + ps - nslots;
-        const unsigned long long ex = pk - kk;  // exclusive per-class prefix of this lane
-        b0 += (uint32_t)(ex & 0xffff), b1 += (uint32_t)((ex >> 16) & 0xffff);
-        b2 += (uint32_t)((ex >> 32) & 0xffff), b3 += (uint32_t)((ex >> 48) & 0xffff);
-        ent_cbase[e] = base;
-        while (m) {
-            const int j = __ffsll((long long)m) - 1;
-            m &= m - 1;
-            const uint32_t sB = ent_shape[s + j];
-            const int tB = (meta[sB].info >> 8) & 0xff;
-            if (base < cap_rec) {
-                reinterpret_cast<uint4*>(rec)[base] = make_uint4(e, sA, sB, slot);
-                const int c = pair_class(tA, tB, algorithm);
-                const uint32_t k = c == 0 ? b0 : (c == 1 ? b1 : (c == 2 ? b2 : b3));
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            my_slots += __shfl_xor_sync(0xffffffffu, my_slots, d);
+            my_cls += __shfl_xor_sync(0xffffffffu, my_cls, d);  // 32 x 64 records at most: no carry between the fields
+        }
+        uint32_t base_slot = 0, base_cls[4] = {0, 0, 0, 0};
+        if (lane == 0) {
+            base_slot = atomicAdd(&cnt->n_cslots, my_slots);
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const uint32_t nq = (uint32_t)((my_cls >> (16 * q)) & 0xffff);
+                if (nq)
+                    base_cls[q] = atomicAdd(&cnt->n_cls[q], nq);
+            }
+        }
+        base_slot = __shfl_sync(0xffffffffu, base_slot, 0);
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+            base_cls[q] = __shfl_sync(0xffffffffu, base_cls[q], 0);
+        // pass 2: the records
+        for (uint32_t t0 = 0; t0 < total; t0 += 32) {
+            const uint32_t t = t0 + lane;
+            const bool have = t < total;
+            int L, c;
+            uint32_t sB, slots;
+            record(t, L, sB, c, slots);
+            const uint32_t sAL = __shfl_sync(0xffffffffu, sA, L);
+            uint32_t ps = slots;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t a = __shfl_up_sync(0xffffffffu, ps, d);
+                if (lane >= d)
+                    ps += a;
+            }
+            uint32_t k = 0;
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const unsigned mq = __ballot_sync(0xffffffffu, have && c == q);
+                if (have && c == q)
+                    k = base_cls[q] + (uint32_t)__popc(mq & ((1u << lane) - 1u));
+                base_cls[q] += (uint32_t)__popc(mq);
+            }
+            const uint32_t base = bc + t;
+            if (have && base < cap_rec) {
+                reinterpret_cast<uint4*>(rec)[base] = make_uint4(e0 + (uint32_t)L, sAL, sB, base_slot + ps - slots);
                 if (k < cap_rec)
                     cls_list[(size_t)c * cap_rec + k] = base;
             }
-            {
-                const int c = pair_class(tA, tB, algorithm);
-                b0 += c == 0, b1 += c == 1, b2 += c == 2, b3 += c == 3;
-            }
-            slot += pair_slots(tA, tB, algorithm);
-            base++;
+            base_slot += __shfl_sync(0xffffffffu, ps, 31);
         }
     }
 }
