@@ -57,7 +57,6 @@ struct AabbArgs {
     double envelope;
     // per-body scratch of the step that ends here, cleared for the next one (common.cuh body_scratch_clean)
     uint32_t* b_deg;
-    uint32_t* b_cursor;
     uint8_t* heavy;
 };
 
@@ -142,7 +141,7 @@ __global__ void __launch_bounds__(256) k_integrate(uint32_t nb, double h, const 
             }
         }
         if (A.b_deg) {  // whole SMC steps only: NSC keeps its CSR by body for the queries that follow a step
-            A.b_deg[b] = 0u, A.b_cursor[b] = 0u, A.heavy[b] = 0;
+            A.b_deg[b] = 0u, A.heavy[b] = 0;
             if (b == 0)
                 A.b_deg[nb] = 0u;
         }
@@ -203,9 +202,9 @@ int enqueue_integrate(System* S) {
         return CB200_OK;
     const int grid = blocks_for(S->nb, 256);
     const bool fuse = integrate_fuses_aabb(S);
-    const bool clear = S->whole_step && S->set.system_type == 1 && S->b_deg.p && S->b_cursor.p && S->heavy.p;
+    const bool clear = S->whole_step && S->set.system_type == 1 && S->b_deg.p && S->heavy.p;
     AabbArgs A = {S->b_sphere.p, S->b_rad.p, S->s_wpos_alt.p, S->set.collision_envelope,
-                  clear ? S->b_deg.p : nullptr, S->b_cursor.p, S->heavy.p};
+                  clear ? S->b_deg.p : nullptr, S->heavy.p};
 #define INTEGRATE(VEL, AABB)                                                                                          \
     k_integrate<VEL, AABB><<<grid, 256, 0, S->stream>>>(S->nb, S->set.step_size, S->bflags.p, S->vel.p, S->pos.p,      \
                                                         S->rot.p, S->mass.p, S->inv_inertia.p, S->hf.p, A,                     \

@@ -473,19 +473,21 @@ __global__ void __launch_bounds__(256) k_shear_sweep(uint32_t nslots, const uint
 }
 
 // ---- body -> contact incidence lists (counting sort by body id) ------------------------------------------------
+// The scanned offsets double as the cursors: every incidence advances its body's offset, so that afterwards off[b] is
+// the END of body b's list and off[b - 1] its start (one random 4-byte access per incidence less than with a separate
+// cursor array, which also would have to be cleared).
 __global__ void __launch_bounds__(256) k_inc_fill(const int32_t* __restrict__ bids,
-                                                  const uint8_t* __restrict__ heavy, const uint32_t* __restrict__ off,
-                                                  uint32_t* __restrict__ cursor, uint32_t* __restrict__ inc,
-                                                  const DevCounters* __restrict__ cnt) {
+                                                  const uint8_t* __restrict__ heavy, uint32_t* __restrict__ off,
+                                                  uint32_t* __restrict__ inc, const DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
     const uint32_t nc = cnt->n_contacts;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nc; i += gridDim.x * blockDim.x) {
         const uint32_t b1 = (uint32_t)bids[2 * i], b2 = (uint32_t)bids[2 * i + 1];
         if (!heavy[b1])
-            inc[off[b1] + atomicAdd(&cursor[b1], 1u)] = i << 1;
+            inc[atomicAdd(&off[b1], 1u)] = i << 1;
         if (!heavy[b2])
-            inc[off[b2] + atomicAdd(&cursor[b2], 1u)] = (i << 1) | 1u;
+            inc[atomicAdd(&off[b2], 1u)] = (i << 1) | 1u;
     }
 }
 
@@ -571,7 +573,7 @@ __global__ void __launch_bounds__(256) k_body_reduce(uint32_t nb, const uint8_t*
     if (UPD && b < nb && !heavy[b])
         base_hf(b, U, h, bF, bT);  // a container body's hf is formed by k_heavy_final<true>
     if (b < nb && !heavy[b]) {
-        const uint32_t s = off[b], d = off[b + 1] - s;
+        const uint32_t s = b ? off[b - 1] : 0u, d = off[b] - s;  // k_inc_fill moved the offsets to the list ends
         d3 F = mk3(0), T = mk3(0);
         // ascending contact code == the order the reference's stable sort leaves.  Up to 16 incidences (every sphere
         // of a bed): the codes are read once, sorted in registers by a fixed network, and the records gathered with
@@ -834,7 +836,6 @@ int enqueue_smc(System* S) {
     const int cgrid = grid_for(S, S->cap_contacts, 256);
     if (!S->body_scratch_clean) {
         CB_CUDA(cudaMemsetAsync(S->b_deg.p, 0, (size_t)(nb + 1) * 4, S->stream));
-        CB_CUDA(cudaMemsetAsync(S->b_cursor.p, 0, (size_t)nb * 4, S->stream));
     }
     S->body_scratch_clean = false;
     const int fgrid = grid_for(S, S->cap_contacts, 128, 16);
@@ -891,7 +892,7 @@ int enqueue_smc(System* S) {
         CB_TRY(enqueue_reset_bbox(S, hs));
     CB_TRY(scan_u32(S, S->b_deg.p, S->b_deg.p, &S->d_cnt->n_bodies, nb));
     CB_TRY(timer_start(S, "k_inc_fill"));
-    k_inc_fill<<<cgrid, 256, 0, S->stream>>>(S->c_bids.p, S->heavy.p, S->b_deg.p, S->b_cursor.p, S->b_inc.p, S->d_cnt);
+    k_inc_fill<<<cgrid, 256, 0, S->stream>>>(S->c_bids.p, S->heavy.p, S->b_deg.p, S->b_inc.p, S->d_cnt);
     CB_TRY(timer_stop(S, "k_inc_fill"));
     CB_TRY(timer_start(S, "k_body_reduce"));
     if (S->defer_update_forces)
