@@ -48,9 +48,11 @@ struct WindowT {
 // operations that produced it), plus a float copy for the conservative pre-test and the float classification.
 struct TileSmem {
     double c[4][WIN];
-    float4 f[WIN];   // centre relative to the bin's lower corner, in float; .w = upper bound of radius + envelope
-                     // (margin included), its low 4 mantissa bits replaced by flags: bits 0..2 "lower corner hashes
-                     // to this bin's x / y / z", bit 3 "sphere that can collide"
+    float4 f[2 * WIN];  // a bin at window offset w0 with k rows holds its records TWICE in a row, [2 w0, 2 w0 + 2k): row
+                        // i reaches its partners i + 1 .. i + nd (mod k) as consecutive records, no wrap-around test.
+                        // Centre relative to the bin's lower corner, in float; .w = upper bound of radius + envelope
+                     // (margin included), its low 4 mantissa bits replaced by flags, stored INVERTED: bits 0..2 clear
+                     // = "lower corner hashes to this bin's x / y / z", bit 3 clear = "sphere that can collide"
     float rm[WIN];   // lower bound of radius + envelope (margin subtracted)
     uint32_t body[WIN], fam[WIN], info[WIN], sid[WIN];
     unsigned long long smask[WIN];
@@ -445,11 +447,12 @@ __global__ void __launch_bounds__(PAIR_THREADS, 4) k_pair_masks(const ShapeMeta*
             const double R = w.w + envelope;
             const double me = m_rel * (Bmax + R) + m_abs;
             // upper bound of R + me that survives the replacement of its 4 low mantissa bits by the flags
-            const uint32_t rp = ((__float_as_uint(__double2float_ru(R + me)) & ~15u) + 16u) | (fl >> 3) | (ok ? 8u : 0u);
+            const uint32_t rp = ((__float_as_uint(__double2float_ru(R + me)) & ~15u) + 16u) | (~((fl >> 3) | (ok ? 8u : 0u)) & 15u);
             T.rm[p] = __double2float_rd(R - me);
-            T.f[p] = make_float4(__double2float_rn(w.x - (g.origin[0] + bx * cnt->bin_size[0])),
-                                 __double2float_rn(w.y - (g.origin[1] + by * cnt->bin_size[1])),
-                                 __double2float_rn(w.z - (g.origin[2] + bz * cnt->bin_size[2])), __uint_as_float(rp));
+            T.f[p + w0] = T.f[p + w0 + k] =
+                make_float4(__double2float_rn(w.x - (g.origin[0] + bx * cnt->bin_size[0])),
+                            __double2float_rn(w.y - (g.origin[1] + by * cnt->bin_size[1])),
+                            __double2float_rn(w.z - (g.origin[2] + bz * cnt->bin_size[2])), __uint_as_float(rp));
         }
         __syncthreads();
         // ---- from here on thread t is row t of the sorted window (same bin, hence same s and k, as its staged entry)
@@ -460,23 +463,31 @@ __global__ void __launch_bounds__(PAIR_THREADS, 4) k_pair_masks(const ShapeMeta*
         const uint32_t i = e - s;
         uint32_t cand = 0u, nd = 0u;  // bit (nd - d) of cand: partner j = i + d (mod k) may pair with this row
         if (own && bin_here) {
-            const float4 A = T.f[t];
+            const float4 A = T.f[w0 + t];
             const uint32_t ab = __float_as_uint(A.w);
-            if (ab & 8u) {
-                const uint32_t am = ab & 7u;
+            if (!(ab & 8u)) {
+                // a partner must be a sphere that can collide (its bit 3 clear) and, on every axis, one of the two
+                // lower corners must hash to this bin (not both inverted bits set): one AND against this row's mask
+                const uint32_t am = (ab & 7u) | 8u;
                 nd = ((k - 1) >> 1) + (((k & 1u) || i >= (k >> 1)) ? 0u : 1u);
-                const float4* Fb = &T.f[w0];
-#pragma unroll 2
-                for (uint32_t d = 1; d <= nd; d++) {
-                    uint32_t j = i + d;
-                    if (j >= k)
-                        j -= k;
-                    const float4 B = Fb[j];
-                    const float rs = A.w + B.w;
-                    const bool maybe = fabsf(B.x - A.x) <= rs && fabsf(B.y - A.y) <= rs && fabsf(B.z - A.z) <= rs &&
-                                       ((__float_as_uint(B.w) | am) & 15u) == 15u;
-                    cand = (cand << 1) | (maybe ? 1u : 0u);
+                const float4* P = &T.f[w0 + t + 1];
+#define CB_PHASE1_TEST(B)                                                                                          \
+    {                                                                                                              \
+        const float rs = A.w + (B).w;                                                                              \
+        const bool maybe = (fabsf((B).x - A.x) <= rs) & (fabsf((B).y - A.y) <= rs) & (fabsf((B).z - A.z) <= rs) &  \
+                           ((__float_as_uint((B).w) & am) == 0u);                                                  \
+        cand = (cand << 1) | (maybe ? 1u : 0u);                                                                    \
+    }
+                uint32_t d = 0;
+                for (; d + 4 <= nd; d += 4) {
+                    const float4 B0 = P[d], B1 = P[d + 1], B2 = P[d + 2], B3 = P[d + 3];
+                    CB_PHASE1_TEST(B0) CB_PHASE1_TEST(B1) CB_PHASE1_TEST(B2) CB_PHASE1_TEST(B3)
                 }
+                for (; d < nd; d++) {
+                    const float4 B0 = P[d];
+                    CB_PHASE1_TEST(B0)
+                }
+#undef CB_PHASE1_TEST
             }
         }
         // ---- phase 2: the candidates of the warp's rows, compacted and spread over the lanes
@@ -500,7 +511,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 4) k_pair_masks(const ShapeMeta*
                 const uint32_t lo = min(pi, pj), hi = max(pi, pj);
                 const uint32_t sa = bw + lo, sb = bw + hi;
                 // float classification: certainly overlapping boxes?  certainly touching / certainly apart spheres?
-                const float4 FA = T.f[sa], FB = T.f[sb];
+                const float4 FA = T.f[sa + bw], FB = T.f[sb + bw];
                 const float dx = FB.x - FA.x, dy = FB.y - FA.y, dz = FB.z - FA.z;
                 const float rsM = T.rm[sa] + T.rm[sb], rsP = FA.w + FB.w;
                 const float d2 = dx * dx + dy * dy + dz * dz;
