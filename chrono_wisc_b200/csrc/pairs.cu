@@ -443,12 +443,21 @@ __global__ void __launch_bounds__(PAIR_THREADS, 4) k_pair_masks(const ShapeMeta*
             const uint32_t fl = corner_flags(mn, g, bx, by, bz);
             T.c[0][p] = w.x, T.c[1][p] = w.y, T.c[2][p] = w.z, T.c[3][p] = w.w;
             T.body[p] = m.body, T.fam[p] = m.fam, T.info[p] = (m.info & ~56u) | fl;
+            if (!sphere) {
+                // nobody reads a non-sphere's row in this kernel (its pairs are decided by k_pair_queue from the global
+                // records), so the row keeps the shape's box instead: the sphere rows of the bin test against it before
+                // they queue a pair
+                T.c[0][p] = mn[0], T.c[1][p] = mn[1], T.c[2][p] = mn[2], T.c[3][p] = mx[0];
+                T.body[p] = (uint32_t)__double2hiint(mx[1]), T.fam[p] = (uint32_t)__double2loint(mx[1]);
+                T.info[p] = (uint32_t)__double2hiint(mx[2]), T.rm[p] = __int_as_float(__double2loint(mx[2]));
+            }
             const bool ok = sphere && m.body != UINT_MAX && (m.info & 2u);
             const double R = w.w + envelope;
             const double me = m_rel * (Bmax + R) + m_abs;
             // upper bound of R + me that survives the replacement of its 4 low mantissa bits by the flags
             const uint32_t rp = ((__float_as_uint(__double2float_ru(R + me)) & ~15u) + 16u) | (~((fl >> 3) | (ok ? 8u : 0u)) & 15u);
-            T.rm[p] = __double2float_rd(R - me);
+            if (sphere)
+                T.rm[p] = __double2float_rd(R - me);
             T.f[p + w0] = T.f[p + w0 + k] =
                 make_float4(__double2float_rn(w.x - (g.origin[0] + bx * cnt->bin_size[0])),
                             __double2float_rn(w.y - (g.origin[1] + by * cnt->bin_size[1])),
@@ -558,6 +567,25 @@ __global__ void __launch_bounds__(PAIR_THREADS, 4) k_pair_masks(const ShapeMeta*
             if (own && bin_here && nn > 0) {
                 const bool row_ns = (nsm >> i) & 1ull;
                 mine = row_ns ? (nsm & ~((2ull << i) - 1ull)) : nsm;
+                if (!row_ns) {
+                    // a pair whose boxes do not overlap is in no list (f_Count_AABB_AABB_Intersection,
+                    // CMC/ChCollisionUtilsBroadphase.cpp:114-140): most spheres of a wall bin do not reach the wall.
+                    // Both boxes exactly as GenerateAABB + OffsetAABB leave them.
+                    const double ar = T.c[3][t] + envelope;
+                    const double an0 = (T.c[0][t] - ar) - g.origin[0], an1 = (T.c[1][t] - ar) - g.origin[1],
+                                 an2 = (T.c[2][t] - ar) - g.origin[2];
+                    const double ax0 = (T.c[0][t] + ar) - g.origin[0], ax1 = (T.c[1][t] + ar) - g.origin[1],
+                                 ax2 = (T.c[2][t] + ar) - g.origin[2];
+                    for (unsigned long long rest = mine; rest; rest &= rest - 1ull) {
+                        const uint32_t a = (uint32_t)__ffsll((long long)rest) - 1u, q = w0 + a;
+                        const double bx1 = __hiloint2double((int)T.body[q], (int)T.fam[q]);
+                        const double bx2 = __hiloint2double((int)T.info[q], __float_as_int(T.rm[q]));
+                        const bool ov = (an0 <= T.c[3][q]) & (T.c[0][q] <= ax0) & (an1 <= bx1) & (T.c[1][q] <= ax1) &
+                                        (an2 <= bx2) & (T.c[2][q] <= ax2);
+                        if (!ov)
+                            mine &= ~(1ull << a);
+                    }
+                }
             }
             const uint32_t c = (uint32_t)__popcll(mine);
             if (__any_sync(0xffffffffu, c != 0u)) {
