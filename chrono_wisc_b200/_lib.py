@@ -86,6 +86,7 @@ _SIGNATURES = {
     "cb200_append_bodies": (C.c_int, [_P, C.c_int, _P, _P, _P, _P, _P, C.POINTER(C.c_int)]),
     "cb200_append_shapes": (C.c_int, [_P, C.c_int, _P, _P, _P, _P, _P, _P, _P]),
     "cb200_append_shape_vertices": (C.c_int, [_P, C.c_int, _P, _P]),
+    "cb200_update_shape_vertices": (C.c_int, [_P, C.c_int, C.c_int, _P]),
     "cb200_set_materials_smc": (C.c_int, [_P, C.c_int, _P]),
     "cb200_set_materials_nsc": (C.c_int, [_P, C.c_int, _P]),
     "cb200_upload_state": (C.c_int, [_P, C.c_int, C.c_int, _P, _P, _P]),

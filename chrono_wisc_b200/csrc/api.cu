@@ -641,6 +641,21 @@ int cb200_append_shape_vertices(cb200_system* sys, int n, const double* xyz, int
     return CB200_OK;
 }
 
+int cb200_update_shape_vertices(cb200_system* sys, int first, int n, const double* xyz) {
+    System* S = SYS(sys);
+    if (!S || first < 0 || n < 0 || (n > 0 && !xyz))
+        return set_error(CB200_ERR_ARG, "bad argument to cb200_update_shape_vertices");
+    if ((size_t)first + (size_t)n > S->n_verts)
+        return set_error(CB200_ERR_ARG, "cb200_update_shape_vertices: range beyond the vertex pool");
+    if (n == 0)
+        return CB200_OK;
+    CB_CUDA(cudaSetDevice(S->device));
+    // same addresses, new values: the captured step graph stays valid
+    CB_TRY(upload(S, S->s_verts, 3 * (size_t)first, xyz, 3 * (size_t)n));
+    CB_CUDA(cudaStreamSynchronize(S->stream));
+    return CB200_OK;
+}
+
 // Composite of two SMC materials in float, term for term as ChContactMaterialCompositeSMC's constructor
 // (src/chrono/physics/ChContactMaterialSMC.cpp:107-130) with the default composition strategy
 // (src/chrono/physics/ChContactMaterial.h:157-169).

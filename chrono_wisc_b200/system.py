@@ -169,6 +169,12 @@ class ChSystemMulticore:
         check(self._lib.cb200_append_shape_vertices(self._h, xyz.shape[0], _ptr(xyz), C.byref(first)))
         return first.value
 
+    def UpdateShapeVertices(self, first, xyz):
+        """Overwrite part of the vertex pool in place (the terrain node's per-exchange write into
+        shape_data.triangle_rigid, ChVehicleCosimTerrainNodeGranularOMP.cpp:858-911)."""
+        xyz = _f64(xyz, (-1, 3))
+        check(self._lib.cb200_update_shape_vertices(self._h, int(first), xyz.shape[0], _ptr(xyz)))
+
     def SetMaterials(self, table):
         table = np.ascontiguousarray(table, dtype=np.float32)
         if self.system_type == 1:

@@ -143,6 +143,12 @@ int cb200_append_shapes(cb200_system* sys, int n, const int32_t* type, const uin
  * Add the vertices before the shapes that refer to them. */
 int cb200_append_shape_vertices(cb200_system* sys, int n, const double* xyz, int* first);
 
+/* Overwrite n points of the vertex pool from index first.  The reference's co-simulation terrain node writes the faces
+ * of a deformable tire straight into shape_data.triangle_rigid at every exchange
+ * (src/chrono_vehicle/cosim/terrain/ChVehicleCosimTerrainNodeGranularOMP.cpp:858-911, UpdateMeshProxy); this is that
+ * write.  Addresses do not change, so a captured step graph stays valid. */
+int cb200_update_shape_vertices(cb200_system* sys, int first, int n, const double* xyz);
+
 /* Per-shape contact materials replacing the per-contact pointer chase of
  * ChContactContainerMulticoreSMC::AddContact (MC/collision/ChContactContainerMulticoreSMC.cpp:123-174).
  * 14 floats per material in ChContactMaterialSMC member order: young_modulus, poisson_ratio, static_friction,
