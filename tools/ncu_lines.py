@@ -24,8 +24,8 @@ for r in rows:
     if H is None or want not in func or not r[0].isdigit():
         continue
     a = agg.setdefault((fname, int(r[0])), [0, 0, r[1]])
-    a[0] += int(r[ie] or 0)
-    a[1] += int(r[sm] or 0)
+    a[0] += int(r[ie]) if r[ie].isdigit() else 0
+    a[1] += int(r[sm]) if r[sm].isdigit() else 0
 tot = sum(v[0] for v in agg.values()) or 1
 tots = sum(v[1] for v in agg.values()) or 1
 print("total warp-instr", tot, "samples", tots)
