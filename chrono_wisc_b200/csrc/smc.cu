@@ -482,11 +482,32 @@ __global__ void __launch_bounds__(256) k_inc_fill(const int32_t* __restrict__ bi
     if (cnt->overflow)
         return;
     const uint32_t nc = cnt->n_contacts;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nc; i += gridDim.x * blockDim.x) {
-        const uint32_t b1 = (uint32_t)bids[2 * i], b2 = (uint32_t)bids[2 * i + 1];
-        if (!heavy[b1])
-            inc[atomicAdd(&off[b1], 1u)] = i << 1;
-        if (!heavy[b2])
+    const int lane = threadIdx.x & 31;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i0 = blockIdx.x * blockDim.x + threadIdx.x - lane; i0 < nc; i0 += stride) {
+        const uint32_t i = i0 + lane;
+        const bool have = i < nc;
+        const int2 bb = have ? reinterpret_cast<const int2*>(bids)[i] : make_int2(-1, -1);
+        const uint32_t b1 = (uint32_t)bb.x, b2 = (uint32_t)bb.y;
+        // Side 1: the list is ordered (bin, shape A, shape B), so the contacts a shape has as A inside one bin sit next
+        // to each other: one atomic per run of equal body ids in the warp instead of one per contact
+        const bool on1 = have && !heavy[b1];
+        const uint32_t prev = __shfl_up_sync(0xffffffffu, b1, 1);
+        const bool prev_on = __shfl_up_sync(0xffffffffu, (int)on1, 1) != 0;  // (every lane takes part: not inside the || below)
+        const bool head = on1 && (lane == 0 || prev != b1 || !prev_on);
+        const uint32_t heads = __ballot_sync(0xffffffffu, head || !on1);  // a lane without a slot ends a run too
+        const uint32_t upto = (2u << lane) - 1u;  // lanes 0..lane (lane 31: 2u << 31 == 0, all ones)
+        const int start = 31 - __clz((int)(heads & upto));
+        uint32_t base = 0;
+        if (head) {
+            const uint32_t above = heads & ~upto;
+            const int end = above ? __ffs((int)above) - 1 : 32;
+            base = atomicAdd(&off[b1], (uint32_t)(end - lane));
+        }
+        base = __shfl_sync(0xffffffffu, base, start);
+        if (on1)
+            inc[base + (uint32_t)(lane - start)] = i << 1;
+        if (have && !heavy[b2])
             inc[atomicAdd(&off[b2], 1u)] = (i << 1) | 1u;
     }
 }
