@@ -61,7 +61,7 @@ struct AabbArgs {
 };
 
 template <bool VEL, bool AABB>
-__global__ void __launch_bounds__(256) k_integrate(uint32_t nb, double h, const uint8_t* __restrict__ bflags,
+__global__ void __launch_bounds__(256, 4) k_integrate(uint32_t nb, double h, const uint8_t* __restrict__ bflags,
                                                    double* __restrict__ vel, double* __restrict__ pos,
                                                    double* __restrict__ rot, const double* __restrict__ mass,
                                                    const double* __restrict__ inv_inertia,
