@@ -501,19 +501,34 @@ __global__ void __launch_bounds__(256) k_bin_fill(uint32_t ns, double envelope, 
             }
         }
         int ix = lo[0], iy = lo[1], iz = lo[2];
-        for (uint32_t it = 0; it < mine; it++) {
-            const uint32_t b = (uint32_t)((iz * g.bins[1]) * g.bins[0] + iy * g.bins[0] + ix);
-            if (++iz > hi[2]) {
-                iz = lo[2];
-                if (++iy > hi[1]) {
-                    iy = lo[1];
-                    ++ix;
+        // four bins at a time: the returning atomics and the bin_start loads of a group are issued together, the stores
+        // follow (one dependent round trip per group instead of one per entry)
+        for (uint32_t it = 0; it < mine; it += 4) {
+            uint32_t bb[4], slot[4], first[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                bb[k] = (uint32_t)((iz * g.bins[1]) * g.bins[0] + iy * g.bins[0] + ix);
+                if (++iz > hi[2]) {
+                    iz = lo[2];
+                    if (++iy > hi[1]) {
+                        iy = lo[1];
+                        ++ix;
+                    }
                 }
             }
-            const uint32_t slot = atomicSub(&cursor[b], 1u) - 1u;
-            const uint32_t e = (uint32_t)bin_start[b] + slot;
-            ent_tmp[e] = i;
-            ent_bin[e] = b;
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                if (it + k < mine) {
+                    slot[k] = atomicSub(&cursor[bb[k]], 1u) - 1u;
+                    first[k] = (uint32_t)bin_start[bb[k]];
+                }
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                if (it + k < mine) {
+                    const uint32_t e = first[k] + slot[k];
+                    ent_tmp[e] = i;
+                    ent_bin[e] = bb[k];
+                }
         }
     }
 }
