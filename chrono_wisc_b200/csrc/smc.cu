@@ -491,7 +491,7 @@ __global__ void __launch_bounds__(256) k_inc_fill(const int32_t* __restrict__ bi
         const uint32_t b1 = (uint32_t)bb.x, b2 = (uint32_t)bb.y;
         // Side 1: the list is ordered (bin, shape A, shape B), so the contacts a shape has as A inside one bin sit next
         // to each other: one atomic per run of equal body ids in the warp instead of one per contact
-        const bool on1 = have && !heavy[b1];
+        const bool on1 = have && !heavy[b1], on2 = have && !heavy[b2];
         const uint32_t prev = __shfl_up_sync(0xffffffffu, b1, 1);
         const bool prev_on = __shfl_up_sync(0xffffffffu, (int)on1, 1) != 0;  // (every lane takes part: not inside the || below)
         const bool head = on1 && (lane == 0 || prev != b1 || !prev_on);
@@ -504,11 +504,12 @@ __global__ void __launch_bounds__(256) k_inc_fill(const int32_t* __restrict__ bi
             const int end = above ? __ffs((int)above) - 1 : 32;
             base = atomicAdd(&off[b1], (uint32_t)(end - lane));
         }
+        const uint32_t slot2 = on2 ? atomicAdd(&off[b2], 1u) : 0u;  // (in flight together with the one above)
         base = __shfl_sync(0xffffffffu, base, start);
         if (on1)
             inc[base + (uint32_t)(lane - start)] = i << 1;
-        if (have && !heavy[b2])
-            inc[atomicAdd(&off[b2], 1u)] = (i << 1) | 1u;
+        if (on2)
+            inc[slot2] = (i << 1) | 1u;
     }
 }
 
