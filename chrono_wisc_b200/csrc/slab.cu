@@ -146,48 +146,58 @@ __global__ void __launch_bounds__(SLAB_CTA) k_slab_flags(SlabGeom G, SlabArrays 
 // Pass 2: exclusive scan of the per-CTA counts (a few thousand triples: one CTA), totals behind the last triple
 __global__ void __launch_bounds__(1024) k_slab_cta_scan(uint32_t ncta, uint32_t* __restrict__ cta_cnt) {
     __shared__ uint32_t sm[3][32];
-    const uint32_t per = (ncta + blockDim.x - 1) / blockDim.x;
-    const uint32_t c0 = min(threadIdx.x * per, ncta), c1 = min(c0 + per, ncta);
-    uint32_t t[3] = {0, 0, 0};
-    for (uint32_t c = c0; c < c1; c++)
-        for (int k = 0; k < 3; k++)
-            t[k] += cta_cnt[3 * c + k];
+    __shared__ uint32_t carry[3];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    uint32_t ex[3];
-    for (int k = 0; k < 3; k++) {
-        uint32_t v = t[k];
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t o = __shfl_up_sync(0xffffffffu, v, d);
-            if (lane >= d)
-                v += o;
-        }
-        if (lane == 31)
-            sm[k][wid] = v;
-        ex[k] = v - t[k];
-    }
+    if (threadIdx.x < 3)
+        carry[threadIdx.x] = 0;
     __syncthreads();
-    if (wid == 0) {
+    // chunks of 1024 triples, a triple per thread (consecutive threads, consecutive words), the running totals carried
+    for (uint32_t c0 = 0; c0 < ncta; c0 += blockDim.x) {
+        const uint32_t c = c0 + threadIdx.x;
+        uint32_t t[3] = {0, 0, 0}, in[3];
+        if (c < ncta)
+            for (int k = 0; k < 3; k++)
+                t[k] = cta_cnt[3 * c + k];
         for (int k = 0; k < 3; k++) {
-            const uint32_t w = sm[k][lane];
-            uint32_t v = w;
+            uint32_t v = t[k];
             for (int d = 1; d < 32; d <<= 1) {
                 const uint32_t o = __shfl_up_sync(0xffffffffu, v, d);
                 if (lane >= d)
                     v += o;
             }
-            sm[k][lane] = v - w;
             if (lane == 31)
-                cta_cnt[3 * ncta + k] = v;  // totals
+                sm[k][wid] = v;
+            in[k] = v;
         }
-    }
-    __syncthreads();
-    uint32_t run[3] = {ex[0] + sm[0][wid], ex[1] + sm[1][wid], ex[2] + sm[2][wid]};
-    for (uint32_t c = c0; c < c1; c++)
+        __syncthreads();
+        if (wid == 0) {
+            for (int k = 0; k < 3; k++) {
+                const uint32_t w = sm[k][lane];
+                uint32_t v = w;
+                for (int d = 1; d < 32; d <<= 1) {
+                    const uint32_t o = __shfl_up_sync(0xffffffffu, v, d);
+                    if (lane >= d)
+                        v += o;
+                }
+                sm[k][lane] = v - w;  // exclusive over the warps
+            }
+        }
+        __syncthreads();
+        uint32_t tot[3];
         for (int k = 0; k < 3; k++) {
-            const uint32_t v = cta_cnt[3 * c + k];
-            cta_cnt[3 * c + k] = run[k];
-            run[k] += v;
+            const uint32_t base = carry[k];
+            if (c < ncta)
+                cta_cnt[3 * c + k] = base + sm[k][wid] + in[k] - t[k];
+            tot[k] = base + sm[k][wid] + in[k];  // inclusive: the last thread's is the new carry
         }
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1)
+            for (int k = 0; k < 3; k++)
+                carry[k] = tot[k];
+        __syncthreads();
+    }
+    if (threadIdx.x < 3)
+        cta_cnt[3 * ncta + threadIdx.x] = carry[threadIdx.x];  // totals
 }
 
 // Pass 3: records into the send buffers, vacant list, departures; the slot order is kept (CTA offset + rank in CTA)
@@ -212,6 +222,11 @@ __global__ void __launch_bounds__(SLAB_CTA) k_slab_pack(SlabGeom G, SlabArrays A
             send_right[0] = (double)nR, send_right[1] = 0;
         scnt[1] = nV;
     }
+    // nothing flagged among this CTA's 256 slots (all but the CTAs of the two ghost bands and of vacant slots): done.
+    // (The totals sit behind the last triple, so the difference works for the last CTA too.)
+    const uint32_t* co = cta_off + 3 * (size_t)blockIdx.x;
+    if (co[3] == co[0] && co[4] == co[1] && co[5] == co[2])
+        return;
     const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t f = s < G.owned_cap ? flags[s] : 0u;
     uint32_t rank[3];
@@ -229,10 +244,10 @@ __global__ void __launch_bounds__(SLAB_CTA) k_slab_pack(SlabGeom G, SlabArrays A
             slab_write_meta(A, b, 4);
         }
         vacant[rank[2]] = b;
-    } else {
-        // A body past the plane now belongs to the neighbour (it is in the buffer just written).  Its slot stays
-        // one more step as a ghost -- the neighbour's own ghost layer will only list it from the next exchange
-        // on -- and is released by the next pack (bit 3).
+    } else if (f & (SLAB_F_LEFT | SLAB_F_RIGHT)) {
+        // A body past the plane now belongs to the neighbour (it is in the buffer just written; being past the plane it
+        // is inside the band, hence flagged).  Its slot stays one more step as a ghost -- the neighbour's own ghost
+        // layer will only list it from the next exchange on -- and is released by the next pack (bit 3).
         const double p = A.pos[3 * (size_t)b + G.axis];
         if ((G.has_left && p < G.lo) || (G.has_right && p >= G.hi)) {
             A.bflags[b] = 2 | 8;

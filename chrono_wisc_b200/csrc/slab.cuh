@@ -24,6 +24,8 @@ __device__ __forceinline__ void slab_ranks(uint32_t f, const uint32_t* __restric
             wtot[k][wid] = (uint32_t)__popc(m);
     }
     __syncthreads();
+    if (!(f & 7u))
+        return;  // only a flagged slot's ranks are ever used (a few per CTA: most warps are done here)
 #pragma unroll
     for (int k = 0; k < 3; k++) {
         for (int w = 0; w < wid; w++)
