@@ -556,7 +556,8 @@ __global__ void __launch_bounds__(PAIR_THREADS, 4) k_pair_masks(const ShapeMeta*
                 if (mode == MODE_CONTACTS)
                     hit = hit & touch;
                 if (hit)
-                    atomicOr(&T.smask[sa], 1ull << hi);
+                    // (a 32-bit shared atomic is one instruction, the 64-bit one a compare-and-swap loop)
+                    atomicOr(reinterpret_cast<uint32_t*>(&T.smask[sa]) + (hi >> 5), 1u << (hi & 31u));
             }
             __syncwarp();
         }
@@ -754,7 +755,7 @@ __global__ void __launch_bounds__(32 * SLOW_WARPS) k_pair_masks_slow(
                         dec = n < 0 ? 2 : n;
                     }
                     if (dec == 1)
-                        atomicOr(&smask[wid][a], 1ull << c);
+                        atomicOr(reinterpret_cast<uint32_t*>(&smask[wid][a]) + (c >> 5), 1u << (c & 31u));
                     else if (dec == 2) {
                         if (CPLX)
                             atomicOr(&scmask[CPLX ? wid : 0][a], 1ull << c);
