@@ -45,7 +45,9 @@ class cb200_settings(C.Structure):
         ("contact_recovery_speed", C.c_double),
         ("tolerance", C.c_double),
         ("deterministic", C.c_int32),
-        ("reserved", C.c_int32 * 7),
+        ("test_objective", C.c_int32),
+        ("tolerance_objective", C.c_double),
+        ("reserved", C.c_int32 * 4),
     ]
 
 

@@ -304,6 +304,8 @@ void cb200_default_settings(cb200_settings* s) {
     s->contact_recovery_speed = .6;
     s->tolerance = 1e-4;
     s->deterministic = 1;
+    s->test_objective = 0;
+    s->tolerance_objective = 1e-6;
 }
 
 int cb200_create(int device, cb200_system** out) {

@@ -39,7 +39,9 @@ enum { NSC_FRAME = 10, NSC_PART = 8, NSC_THREADS = 256, NSC_NGLOB = 16 /* slot o
 
 struct NscCtl {
     double L, t, theta, theta_new, beta, obj2, residual, objective, g_diff, tol_speed, norm_temp, dot_g_temp;
+    double tol_objective;   // settings.solver.tolerance_objective, looked at when test_objective is set
     int32_t iter, max_iter, act, done, redo, accepted, improved, restart, ref_variant, slots, total_iter, hist_cap;
+    int32_t test_objective; // settings.solver.test_objective (ChSolverMulticoreAPGD.cpp:184-188)
     int32_t ret_iter;       // sum of the values Solve() returned over the phases (measures.solver.total_iteration)
     uint32_t ticket;        // CTAs of k_nsc_eval that have delivered their partial sums (last one runs the scalar part)
 };
@@ -613,7 +615,8 @@ __device__ __forceinline__ void reduce_partials(const double* __restrict__ part,
 // start of a phase (one Solve call): scalars of :74-83
 // nglob: decomposed systems -- the number of contacts of the whole system (every contact counted on one rank)
 __global__ void k_nsc_phase_begin(NscCtl* __restrict__ ctl, int act, int max_iter, int rows, int ref_variant,
-                                  double tol_speed, int first_phase, int hist_cap, const double* __restrict__ nglob,
+                                  double tol_speed, int test_objective, double tol_objective, int first_phase,
+                                  int hist_cap, const double* __restrict__ nglob,
                                   const DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
         return;
@@ -637,6 +640,8 @@ __global__ void k_nsc_phase_begin(NscCtl* __restrict__ ctl, int act, int max_ite
     ctl->obj2 = 0;
     ctl->dot_g_temp = 0;
     ctl->tol_speed = tol_speed;
+    ctl->test_objective = test_objective;
+    ctl->tol_objective = tol_objective;
     ctl->hist_cap = hist_cap;
     if (first_phase) {
         ctl->total_iter = 0;
@@ -898,7 +903,9 @@ __device__ __forceinline__ void nsc_scalar_body(NscCtl* __restrict__ ctl, const 
         hist[2 * gi + 1] = ctl->objective;
     }
     ctl->total_iter = gi + 1;
-    if (ctl->residual < ctl->tol_speed) {
+    // :184-192: the objective (of the best iterate so far) against tolerance_objective, or the residual against tol_speed
+    if ((ctl->test_objective && !ctl->ref_variant) ? ctl->objective <= ctl->tol_objective
+                                                   : ctl->residual < ctl->tol_speed) {  // (APGDREF.cpp:174: residual only)
         ctl->done = 1;  // break: the iteration counter is not advanced (:189-191)
         ctl->restart = 0;
         ctl->ret_iter += ctl->iter;
@@ -1274,7 +1281,8 @@ static int nsc_phase(Group& g, int act, int max_iter, bool first_phase) {
         const cb200_settings& st = S->set;
         const Ptr P = ptrs(S);
         k_nsc_phase_begin<<<1, 1, 0, S->stream>>>((NscCtl*)S->n_ctl, act, max_iter, ROWS, st.solver_type == 1 ? 1 : 0,
-                                                  st.step_size * st.tolerance, first_phase ? 1 : 0, S->nsc_hist_cap,
+                                                  st.step_size * st.tolerance, st.test_objective,
+                                                  st.tolerance_objective, first_phase ? 1 : 0, S->nsc_hist_cap,
                                                   P.ng, S->d_cnt);
         // initial step length: temp = gamma - 1, L = |N temp| / |temp|
         k_nsc_init_temp<ROWS><<<nsc_grid(S), NSC_THREADS, 0, S->stream>>>(S->gamma.p, S->n_gn.p, P.part0, P.own, S->d_cnt);
@@ -1372,7 +1380,7 @@ static int nsc_run(Group& g) {
     }
     for (System* S : g.sys) {
         if (first) {  // no phase ran: counters of an empty solve
-            k_nsc_phase_begin<<<1, 1, 0, S->stream>>>((NscCtl*)S->n_ctl, ROWS, 0, ROWS, 0, 0.0, 1, S->nsc_hist_cap, nullptr,
+            k_nsc_phase_begin<<<1, 1, 0, S->stream>>>((NscCtl*)S->n_ctl, ROWS, 0, ROWS, 0, 0.0, 0, 0.0, 1, S->nsc_hist_cap, nullptr,
                                                       S->d_cnt);
             k_nsc_phase_end<ROWS><<<1, NSC_THREADS, 0, S->stream>>>((NscCtl*)S->n_ctl, S->n_gamma_hat.p, S->gamma.p, 0,
                                                                     S->d_cnt);

@@ -77,7 +77,11 @@ typedef struct cb200_settings {
     double tolerance;
     /* --- backend-only knobs (no reference counterpart) */
     int32_t deterministic;         /* 1: fixed summation order everywhere (default); 0: allow FP64 atomics */
-    int32_t reserved[7];
+    /* --- solver_settings, NSC part, continued (carved out of the reserved words: the struct keeps its size) */
+    int32_t test_objective;        /* APGD stops on objective <= tolerance_objective instead of residual < tol_speed
+                                      (MC/solver/ChSolverMulticoreAPGD.cpp:184-192, MC/ChSettings.h:100; default 0) */
+    double tolerance_objective;    /* MC/ChSettings.h:98, default 1e-6 */
+    int32_t reserved[4];
 } cb200_settings;
 
 /* Counters of the last step: measures_container (MC/ChMeasures.h:34-120) + cd_data counters

@@ -756,6 +756,8 @@ void orc_default_settings(cb200_settings* s) {
     s->contact_recovery_speed = .6;
     s->tolerance = 1e-4;
     s->deterministic = 1;
+    s->test_objective = 0;         // MC/ChSettings.h:100
+    s->tolerance_objective = 1e-6;  // MC/ChSettings.h:98
 }
 
 void orc_set_bodies(orc_system* S, int nb, const double* mass, const double* inertia, const char* active,

@@ -52,7 +52,7 @@ class OrcSettings(C.Structure):
         ("solver_mode", C.c_int32), ("max_iteration_normal", C.c_int32), ("max_iteration_sliding", C.c_int32),
         ("max_iteration_spinning", C.c_int32), ("cache_step_length", C.c_int32), ("alpha", C.c_double),
         ("contact_recovery_speed", C.c_double), ("tolerance", C.c_double), ("deterministic", C.c_int32),
-        ("reserved", C.c_int32 * 7),
+        ("test_objective", C.c_int32), ("tolerance_objective", C.c_double), ("reserved", C.c_int32 * 4),
     ]
 
 

@@ -121,6 +121,32 @@ def test_phases_normal_then_sliding_and_tolerance_stop():
     assert relerr(sys.GetGamma(), orc.nsc_vectors()["gamma"]) < 1e-8
 
 
+def test_objective_stop():
+    """settings.solver.test_objective (ChSolverMulticoreAPGD.cpp:184-192): APGD leaves when the objective of its best
+    iterate is at or below tolerance_objective; APGDREF keeps the residual test (APGDREF.cpp:174)."""
+    full = bed(8, 8, 4, iterations=40)
+    sys0, _ = both(full)
+    _, o0 = sys0.GetSolverHistory()
+    k = 12
+    assert o0[k] < o0[k - 1]  # the objective still falls there: a threshold between the two stops at iteration k
+    thr = 0.5 * (o0[k] + o0[k - 1])
+    scene = bed(8, 8, 4, iterations=40, test_objective=1, tolerance_objective=float(thr))
+    sys, orc = both(scene)
+    info = orc.nsc_info()
+    r, o = sys.GetSolverHistory()
+    assert r.size == k + 1 and o[-1] <= thr < o[-2]
+    assert sys.GetCounts().solver_iterations == info["iterations"] == k  # the break does not advance the counter
+    assert relerr(sys.GetGamma(), orc.nsc_vectors()["gamma"]) < 1e-8
+    # a tolerance on the residual that would have stopped at once is not looked at any more ...
+    scene2 = bed(8, 8, 4, iterations=15, test_objective=1, tolerance_objective=-1e300, tolerance=1e9)
+    sys2, _ = both(scene2)
+    assert sys2.GetCounts().solver_iterations == 15
+    # ... except by APGDREF
+    scene3 = bed(8, 8, 4, iterations=15, solver_type=1, test_objective=1, tolerance_objective=-1e300, tolerance=1e9)
+    sys3, orc3 = both(scene3)
+    assert sys3.GetCounts().solver_iterations == orc3.nsc_info()["iterations"] < 15
+
+
 def test_spinning_mode_solve():
     scene = bed(6, 6, 3, mode=cw.system.MODE_SPINNING, iterations=10, max_iteration_normal=5,
                 max_iteration_spinning=10)
