@@ -86,6 +86,7 @@ _SIGNATURES = {
     "cb200_default_settings": (None, [C.POINTER(cb200_settings)]),
     "cb200_set_settings": (C.c_int, [_P, C.POINTER(cb200_settings)]),
     "cb200_append_bodies": (C.c_int, [_P, C.c_int, _P, _P, _P, _P, _P, C.POINTER(C.c_int)]),
+    "cb200_set_inertia_full": (C.c_int, [_P, C.c_int, C.c_int, _P, _P]),
     "cb200_append_shapes": (C.c_int, [_P, C.c_int, _P, _P, _P, _P, _P, _P, _P]),
     "cb200_append_shape_vertices": (C.c_int, [_P, C.c_int, _P, _P]),
     "cb200_update_shape_vertices": (C.c_int, [_P, C.c_int, C.c_int, _P]),

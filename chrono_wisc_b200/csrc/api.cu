@@ -341,7 +341,7 @@ void cb200_destroy(cb200_system* sys) {
     cudaStreamSynchronize(S->stream);
     comm_release(S);
 #define REL(x) S->x.release()
-    REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(bflags); REL(heavy); REL(b_sphere); REL(b_rad); REL(c_own); REL(vlim); REL(b_inbox); REL(report); REL(mat_ovr); REL(bil_ids); REL(bil_cq); REL(bil_b); REL(bil_R); REL(bil_gamma); REL(bil_N); REL(bil_vec); REL(bil_info);
+    REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(inertia_off); REL(inv_inertia_off); REL(bflags); REL(heavy); REL(b_sphere); REL(b_rad); REL(c_own); REL(vlim); REL(b_inbox); REL(report); REL(mat_ovr); REL(bil_ids); REL(bil_cq); REL(bil_b); REL(bil_R); REL(bil_gamma); REL(bil_N); REL(bil_vec); REL(bil_info);
     REL(s_type); REL(s_body); REL(s_fam); REL(s_mat); REL(s_lpos); REL(s_lrot); REL(s_dims); REL(general_ids); REL(s_verts); REL(sh_neigh); REL(sh_touch); REL(sh_disp); REL(sh_relvel); REL(sh_dur); REL(s_wpos); REL(s_wpos_alt); REL(s_wrot);
     REL(s_box); REL(s_meta); REL(mat_smc); REL(mat_nsc); REL(bin_intersections); REL(bin_start); REL(bin_cursor);
     REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_mask); REL(ent_off); REL(slow_bins); REL(long_bins); REL(pair_q); REL(large_list); REL(pairs);
@@ -508,6 +508,12 @@ int cb200_append_bodies(cb200_system* sys, int n, const double* mass, const doub
     CB_CUDA(cudaMemsetAsync(S->fapp.p + 6 * nb0, 0, 6 * (size_t)n * 8, st));
     CB_CUDA(cudaMemsetAsync(S->heavy.p + nb0, 0, (size_t)n, st));
     CB_CUDA(cudaMemsetAsync(S->vlim.p + 2 * nb0, 0, 2 * (size_t)n * 8, st));  // no speed limit
+    if (S->inertia_off.p) {  // some earlier body has products of inertia: the new ones have none
+        CB_TRY(S->inertia_off.reserve(3 * nb1, true, st));
+        CB_TRY(S->inv_inertia_off.reserve(3 * nb1, true, st));
+        CB_CUDA(cudaMemsetAsync(S->inertia_off.p + 3 * nb0, 0, 3 * (size_t)n * 8, st));
+        CB_CUDA(cudaMemsetAsync(S->inv_inertia_off.p + 3 * nb0, 0, 3 * (size_t)n * 8, st));
+    }
     S->h_b_sphere.resize(nb1, -1);
     S->h_b_rad.resize(nb1, 0.0);
     CB_TRY(S->b_sphere.reserve(nb1, true, st));
@@ -640,6 +646,46 @@ int cb200_append_shape_vertices(cb200_system* sys, int n, const double* xyz, int
     S->n_verts = (uint32_t)n1;
     if (first)
         *first = (int)n0;
+    return CB200_OK;
+}
+
+int cb200_set_inertia_full(cb200_system* sys, int first, int n, const double* inertia9, const double* inv_inertia9) {
+    System* S = SYS(sys);
+    if (S)
+        invalidate_step_graph(S);  // the kernels of a captured step were handed null off-diagonal pointers
+    if (!S || first < 0 || n < 0 || (n > 0 && (!inertia9 || !inv_inertia9)) || (size_t)first + (size_t)n > S->nb)
+        return set_error(CB200_ERR_ARG, "bad argument to cb200_set_inertia_full");
+    if (S->slab_on)
+        return set_error(CB200_ERR_UNSUPPORTED, "products of inertia do not travel with the slab records yet");
+    if (S->n_bil > 0)
+        return set_error(CB200_ERR_UNSUPPORTED, "bilateral rows use the diagonal of the inverse inertia only");
+    if (n == 0)
+        return CB200_OK;
+    CB_CUDA(cudaSetDevice(S->device));
+    cudaStream_t st = S->stream;
+    const size_t had = S->inertia_off.p ? S->inertia_off.cap : 0;
+    CB_TRY(S->inertia_off.reserve(3 * (size_t)S->nb, true, st));
+    CB_TRY(S->inv_inertia_off.reserve(3 * (size_t)S->nb, true, st));
+    if (had < S->inertia_off.cap) {  // bodies never given products of inertia have none
+        CB_CUDA(cudaMemsetAsync(S->inertia_off.p + had, 0, (S->inertia_off.cap - had) * sizeof(double), st));
+        CB_CUDA(cudaMemsetAsync(S->inv_inertia_off.p + had, 0, (S->inv_inertia_off.cap - had) * sizeof(double), st));
+    }
+    std::vector<double> d(3 * (size_t)n), o(3 * (size_t)n), di(3 * (size_t)n), oi(3 * (size_t)n);
+    for (int i = 0; i < n; i++) {
+        const double* J = inertia9 + 9 * (size_t)i;
+        const double* K = inv_inertia9 + 9 * (size_t)i;
+        if (J[1] != J[3] || J[2] != J[6] || J[5] != J[7] || K[1] != K[3] || K[2] != K[6] || K[5] != K[7])
+            return set_error(CB200_ERR_ARG, "cb200_set_inertia_full: the matrices must be symmetric");
+        d[3 * i] = J[0], d[3 * i + 1] = J[4], d[3 * i + 2] = J[8];
+        o[3 * i] = J[1], o[3 * i + 1] = J[2], o[3 * i + 2] = J[5];
+        di[3 * i] = K[0], di[3 * i + 1] = K[4], di[3 * i + 2] = K[8];
+        oi[3 * i] = K[1], oi[3 * i + 1] = K[2], oi[3 * i + 2] = K[5];
+    }
+    CB_TRY(upload(S, S->inertia, 3 * (size_t)first, d.data(), d.size()));
+    CB_TRY(upload(S, S->inv_inertia, 3 * (size_t)first, di.data(), di.size()));
+    CB_TRY(upload(S, S->inertia_off, 3 * (size_t)first, o.data(), o.size()));
+    CB_TRY(upload(S, S->inv_inertia_off, 3 * (size_t)first, oi.data(), oi.size()));
+    CB_CUDA(cudaStreamSynchronize(st));
     return CB200_OK;
 }
 

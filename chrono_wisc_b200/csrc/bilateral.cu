@@ -239,6 +239,9 @@ extern "C" int cb200_set_bilaterals(cb200_system* sys, int n, const int32_t* bod
     for (int i = 0; i < 2 * n; i++)
         if (body_ids[i] < 0 || (uint32_t)body_ids[i] >= S->nb)
             return set_error(CB200_ERR_ARG, "bilateral row refers to a body that does not exist");
+    if (n > 0 && S->inertia_off.p)
+        return set_error(CB200_ERR_UNSUPPORTED, "bilateral rows use the diagonal of the inverse inertia only "
+                                                "(cb200_set_inertia_full was called)");
     if ((uint32_t)n != S->n_bil)
         invalidate_step_graph(S);  // the launch geometry of the bilateral kernels is part of the step graph
     S->n_bil = (uint32_t)n;

@@ -160,6 +160,9 @@ struct System {
     DevBuf<double> mass;     // nb
     DevBuf<double> inertia;  // 3 nb (body-frame diagonal)
     DevBuf<double> inv_inertia;  // 3 nb
+    // products of inertia (use_full_inertia_tensor, MC/ChSettings.h:107): (xy, xz, yz) of the inertia matrix and of its
+    // inverse, 3 nb each; null until cb200_set_inertia_full is called (bodies given principal moments only)
+    DevBuf<double> inertia_off, inv_inertia_off;
     DevBuf<uint8_t> bflags;  // bit0 active, bit1 collide, bit2 vacant slot (slab decomposition: no body lives here)
     DevBuf<uint8_t> heavy;   // body owns a large shape this step
     // a body's own centred sphere (the first sphere shape with ObA == 0 added for it; -1: none) and its radius: the

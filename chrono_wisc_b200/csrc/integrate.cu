@@ -17,6 +17,7 @@ namespace cb200 {
 // hf = h * (m g + F_applied ,  T_applied - w x (J w))
 __global__ void __launch_bounds__(256) k_update_forces(uint32_t nb, double h, d3 g, const double* __restrict__ mass,
                                                        const double* __restrict__ inertia,
+                                                       const double* __restrict__ inertia_off /* may be null */,
                                                        const double* __restrict__ vel,
                                                        const double* __restrict__ fapp /* may be null */,
                                                        double* __restrict__ hf, const DevCounters* __restrict__ cnt) {
@@ -28,8 +29,8 @@ __global__ void __launch_bounds__(256) k_update_forces(uint32_t nb, double h, d3
     const double m = mass[b];
     const double* v = vel + 6 * (size_t)b;
     const d3 w = mk3(v[3], v[4], v[5]);
-    // ComputeGyro: gyro = w x (J w), J diagonal in the body frame
-    const d3 Jw = mk3(inertia[3 * b] * w.x, inertia[3 * b + 1] * w.y, inertia[3 * b + 2] * w.z);
+    // ComputeGyro: gyro = w x (J w), J in the body frame (diagonal unless the body was given products of inertia)
+    const d3 Jw = sym3_apply(inertia, inertia_off, b, w);
     const d3 gyro = cross3(w, Jw);
     d3 F = g * m;   // UpdateForces: Xforce = G_acc * mass
     d3 T = mk3(0);
@@ -65,6 +66,7 @@ __global__ void __launch_bounds__(256, 4) k_integrate(uint32_t nb, double h, con
                                                    double* __restrict__ vel, double* __restrict__ pos,
                                                    double* __restrict__ rot, const double* __restrict__ mass,
                                                    const double* __restrict__ inv_inertia,
+                                                   const double* __restrict__ inv_inertia_off /* may be null */,
                                                    const double* __restrict__ hf, AabbArgs A,
                                                    const double* __restrict__ vlim /* (max_speed, max_wvel) per body or null */,
                                                    DevCounters* __restrict__ cnt) {
@@ -87,9 +89,10 @@ __global__ void __launch_bounds__(256, 4) k_integrate(uint32_t nb, double h, con
                 v[0] = v[0] + inv_mass * f[0];
                 v[1] = v[1] + inv_mass * f[1];
                 v[2] = v[2] + inv_mass * f[2];
-                v[3] = v[3] + inv_inertia[3 * b] * f[3];
-                v[4] = v[4] + inv_inertia[3 * b + 1] * f[4];
-                v[5] = v[5] + inv_inertia[3 * b + 2] * f[5];
+                const d3 dw = sym3_apply(inv_inertia, inv_inertia_off, b, mk3(f[3], f[4], f[5]));
+                v[3] = v[3] + dw.x;
+                v[4] = v[4] + dw.y;
+                v[5] = v[5] + dw.z;
             }
             pn = mk3(pn.x + v[0] * h, pn.y + v[1] * h, pn.z + v[2] * h);
             p[0] = pn.x, p[1] = pn.y, p[2] = pn.z;
@@ -175,7 +178,7 @@ int enqueue_update_forces(System* S) {
         return CB200_OK;
     const d3 g = mk3(S->set.gravity[0], S->set.gravity[1], S->set.gravity[2]);
     k_update_forces<<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(S->nb, S->set.step_size, g, S->mass.p, S->inertia.p,
-                                                                   S->vel.p, S->has_fapp ? S->fapp.p : nullptr,
+                                                                   S->inertia_off.p, S->vel.p, S->has_fapp ? S->fapp.p : nullptr,
                                                                    S->hf.p, S->d_cnt);
     S->launches++;
     CB_CUDA(cudaGetLastError());
@@ -207,7 +210,7 @@ int enqueue_integrate(System* S) {
                   clear ? S->b_deg.p : nullptr, S->heavy.p};
 #define INTEGRATE(VEL, AABB)                                                                                          \
     k_integrate<VEL, AABB><<<grid, 256, 0, S->stream>>>(S->nb, S->set.step_size, S->bflags.p, S->vel.p, S->pos.p,      \
-                                                        S->rot.p, S->mass.p, S->inv_inertia.p, S->hf.p, A,                     \
+                                                        S->rot.p, S->mass.p, S->inv_inertia.p, S->inv_inertia_off.p, S->hf.p, A,                     \
                                                         S->has_vlim ? S->vlim.p : nullptr, S->d_cnt)
     if (fuse)
         CB_TRY(enqueue_reset_bbox(S, S->stream));

@@ -275,6 +275,7 @@ __device__ __forceinline__ void block_partials(double* acc, double* __restrict__
 __global__ void __launch_bounds__(256) k_nsc_body_prep(uint32_t nb, const uint8_t* __restrict__ bflags,
                                                        const double* __restrict__ mass,
                                                        const double* __restrict__ inv_inertia,
+                                                       const double* __restrict__ inv_off /* may be null */,
                                                        const double* __restrict__ rot, const double* __restrict__ vel,
                                                        const double* __restrict__ hf, double* __restrict__ mk,
                                                        double* __restrict__ w0, uint32_t* __restrict__ deg,
@@ -293,9 +294,10 @@ __global__ void __launch_bounds__(256) k_nsc_body_prep(uint32_t nb, const uint8_
     if (bflags[b] & 1u) {
         const double im = 1.0 / mass[b];
         m[0] = v[0] + im * f[0], m[1] = v[1] + im * f[1], m[2] = v[2] + im * f[2];
-        m[3] = v[3] + inv_inertia[3 * b] * f[3];
-        m[4] = v[4] + inv_inertia[3 * b + 1] * f[4];
-        m[5] = v[5] + inv_inertia[3 * b + 2] * f[5];
+        const d3 dw = sym3_apply(inv_inertia, inv_off, b, mk3(f[3], f[4], f[5]));
+        m[3] = v[3] + dw.x;
+        m[4] = v[4] + dw.y;
+        m[5] = v[5] + dw.z;
     } else {
 #pragma unroll
         for (int k = 0; k < 6; k++)
@@ -433,6 +435,7 @@ __global__ void __launch_bounds__(256) k_nsc_scatter(uint32_t nb, const NscCtl* 
                                                      const uint8_t* __restrict__ bflags,
                                                      const double* __restrict__ mass,
                                                      const double* __restrict__ inv_inertia,
+                                                     const double* __restrict__ inv_off /* may be null */,
                                                      const double* __restrict__ rot, const uint32_t* __restrict__ off,
                                                      const uint32_t* __restrict__ inc,
                                                      const double* __restrict__ frame, const double* __restrict__ x,
@@ -481,8 +484,7 @@ __global__ void __launch_bounds__(256) k_nsc_scatter(uint32_t nb, const NscCtl* 
         double* o = w + 6 * (size_t)b;
         if (active) {
             const double im = 1.0 / mass[b];
-            const d3 wl = mk3(inv_inertia[3 * b] * ang_l.x, inv_inertia[3 * b + 1] * ang_l.y,
-                              inv_inertia[3 * b + 2] * ang_l.z);
+            const d3 wl = sym3_apply(inv_inertia, inv_off, b, ang_l);
             const d3 ww = rotate(wl, q);
             o[0] = im * lin.x, o[1] = im * lin.y, o[2] = im * lin.z, o[3] = ww.x, o[4] = ww.y, o[5] = ww.z;
         } else {
@@ -497,9 +499,10 @@ __global__ void __launch_bounds__(256) k_nsc_scatter(uint32_t nb, const NscCtl* 
         if (active) {
             const double im = 1.0 / mass[b];
             v[0] = m[0] + im * lin.x, v[1] = m[1] + im * lin.y, v[2] = m[2] + im * lin.z;
-            v[3] = m[3] + inv_inertia[3 * b] * ang_l.x;
-            v[4] = m[4] + inv_inertia[3 * b + 1] * ang_l.y;
-            v[5] = m[5] + inv_inertia[3 * b + 2] * ang_l.z;
+            const d3 dw = sym3_apply(inv_inertia, inv_off, b, ang_l);
+            v[3] = m[3] + dw.x;
+            v[4] = m[4] + dw.y;
+            v[5] = m[5] + dw.z;
         } else {
 #pragma unroll
             for (int k = 0; k < 6; k++)
@@ -1198,7 +1201,8 @@ static int nsc_schur_pass(Group& g, int xsel /* 0: gamma_new -> n_w, 1: y -> n_w
         NscCtl* ctl = (NscCtl*)S->n_ctl;
         const double* x = xsel == 0 ? S->n_gn.p : S->n_y.p;
         k_nsc_scatter<ROWS, 0><<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(
-            S->nb, ctl, skip_on_redo, S->bflags.p, S->mass.p, S->inv_inertia.p, S->rot.p, S->b_deg.p, S->b_inc.p,
+            S->nb, ctl, skip_on_redo, S->bflags.p, S->mass.p, S->inv_inertia.p, S->inv_inertia_off.p, S->rot.p, S->b_deg.p,
+            S->b_inc.p,
             S->n_frame.p, x, xsel == 0 ? S->n_w.p : S->n_wy.p, nullptr, nullptr, nullptr, 0.0, S->d_cnt);
         S->launches++;
     }
@@ -1214,6 +1218,7 @@ static int nsc_setup(Group& g) {
     for (System* S : g.sys) {
         const uint32_t nb = S->nb;
         k_nsc_body_prep<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->bflags.p, S->mass.p, S->inv_inertia.p,
+                                                                    S->inv_inertia_off.p,
                                                                    S->rot.p, S->vel.p, S->hf.p, S->n_mk.p, S->n_w0.p,
                                                                    S->b_deg.p, S->d_cnt);
         CB_CUDA(cudaMemsetAsync(S->b_cursor.p, 0, (size_t)nb * 4, S->stream));
@@ -1388,7 +1393,8 @@ static int nsc_run(Group& g) {
         }
         // ComputeImpulses + CalculateContactForces
         k_nsc_scatter<ROWS, 1><<<blocks_for(S->nb, 256), 256, 0, S->stream>>>(
-            S->nb, (NscCtl*)S->n_ctl, 0, S->bflags.p, S->mass.p, S->inv_inertia.p, S->rot.p, S->b_deg.p, S->b_inc.p,
+            S->nb, (NscCtl*)S->n_ctl, 0, S->bflags.p, S->mass.p, S->inv_inertia.p, S->inv_inertia_off.p, S->rot.p, S->b_deg.p,
+            S->b_inc.p,
             S->n_frame.p, S->gamma.p, nullptr, S->n_mk.p, S->vel.p, S->b_force.p, 1 / st.step_size, S->d_cnt);
         S->launches++;
         CB_CUDA(cudaGetLastError());

@@ -413,6 +413,8 @@ int cb200_slab_configure(cb200_system* sys, int nb_static, int ns_static, int ax
         return set_error(CB200_ERR_ARG, "bad argument to cb200_slab_configure");
     if (S->slab_on)
         return set_error(CB200_ERR_STATE, "the system is already configured as a slab");
+    if (S->inertia_off.p)
+        return set_error(CB200_ERR_UNSUPPORTED, "products of inertia do not travel with the slab records yet");
     if (ghost_cap >= (1 << 21) || owned_cap >= (1 << 22))
         return set_error(CB200_ERR_UNSUPPORTED, "slab capacities above 2^21 ghost / 2^22 owned slots");
     CB_CUDA(cudaSetDevice(S->device));

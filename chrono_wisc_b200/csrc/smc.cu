@@ -518,6 +518,7 @@ __global__ void __launch_bounds__(256) k_inc_fill(const int32_t* __restrict__ bi
 struct UpdArgs {
     d3 g;
     const double *mass, *inertia, *vel, *fapp;
+    const double* inertia_off;  // products of inertia (null: none)
 };
 
 // F, T (+)= the record of incidence `code` (contact << 1 | side): force on body 2 of the contact (body 1 gets the
@@ -566,7 +567,7 @@ __device__ __forceinline__ void base_hf(uint32_t b, const UpdArgs& U, double h, 
     const double m = U.mass[b];
     const double* v = U.vel + 6 * (size_t)b;
     const d3 w = mk3(v[3], v[4], v[5]);
-    const d3 Jw = mk3(U.inertia[3 * b] * w.x, U.inertia[3 * b + 1] * w.y, U.inertia[3 * b + 2] * w.z);
+    const d3 Jw = sym3_apply(U.inertia, U.inertia_off, b, w);
     const d3 gyro = cross3(w, Jw);
     d3 F = U.g * m;
     d3 T = mk3(0);
@@ -781,6 +782,7 @@ __global__ void __launch_bounds__(256) k_heavy_final(const uint32_t* __restrict_
 __global__ void __launch_bounds__(256) k_vel_update(uint32_t nb, const uint8_t* __restrict__ bflags,
                                                     const double* __restrict__ mass,
                                                     const double* __restrict__ inv_inertia,
+                                                    const double* __restrict__ inv_inertia_off /* may be null */,
                                                     const double* __restrict__ hf, double* __restrict__ vel,
                                                     const DevCounters* __restrict__ cnt) {
     if (cnt->overflow)
@@ -794,9 +796,10 @@ __global__ void __launch_bounds__(256) k_vel_update(uint32_t nb, const uint8_t* 
     v[0] = v[0] + inv_mass * f[0];
     v[1] = v[1] + inv_mass * f[1];
     v[2] = v[2] + inv_mass * f[2];
-    v[3] = v[3] + inv_inertia[3 * b] * f[3];
-    v[4] = v[4] + inv_inertia[3 * b + 1] * f[4];
-    v[5] = v[5] + inv_inertia[3 * b + 2] * f[5];
+    const d3 dw = sym3_apply(inv_inertia, inv_inertia_off, b, mk3(f[3], f[4], f[5]));
+    v[3] = v[3] + dw.x;
+    v[4] = v[4] + dw.y;
+    v[5] = v[5] + dw.z;
 }
 
 // History arrays for MultiStep: slots of new bodies start free with zero displacement
@@ -907,6 +910,7 @@ int enqueue_smc(System* S) {
     UpdArgs U;
     U.g = mk3(st.gravity[0], st.gravity[1], st.gravity[2]);
     U.mass = S->mass.p, U.inertia = S->inertia.p, U.vel = S->vel.p, U.fapp = S->has_fapp ? S->fapp.p : nullptr;
+    U.inertia_off = S->inertia_off.p;
     if (S->defer_update_forces)  // the body's whole hf is formed there: no dependence on k_body_reduce
         k_heavy_final<true><<<MAX_HEAVY, 256, 0, hs>>>(S->heavy_list.p, S->d_cnt, chunk_cap, S->heavy_part.p,
                                                        st.step_size, S->b_force.p, S->hf.p, U, S->d_cnt);
@@ -932,7 +936,8 @@ int enqueue_smc(System* S) {
                                                                st.step_size, S->b_force.p, S->hf.p, U, S->d_cnt);
     CB_TRY(enqueue_bilateral(S));  // joints / motors: hf += D_b gamma_b (RunTimeStep :816-842)
     if (!S->defer_vel_update)
-        k_vel_update<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->bflags.p, S->mass.p, S->inv_inertia.p, S->hf.p,
+        k_vel_update<<<blocks_for(nb, 256), 256, 0, S->stream>>>(nb, S->bflags.p, S->mass.p, S->inv_inertia.p,
+                                                                 S->inv_inertia_off.p, S->hf.p,
                                                                  S->vel.p, S->d_cnt);
     S->launches += S->defer_vel_update ? 5 : 6;
     CB_CUDA(cudaGetLastError());

@@ -98,6 +98,17 @@ HD d3 abs_rotate(const q4& q, const d3& v) {
 
 // MM/utility.h:48-57
 HD d3 local_to_parent(const d3& p, const q4& q, const d3& rl) { return p + rotate(rl, q); }
+// y = S x for a symmetric 3 x 3 matrix kept as its diagonal (diag[3b..]) and, when the system has bodies with products of
+// inertia, its off-diagonal part (off[3b..] = xy, xz, yz; null otherwise).  Row sums in column order, as a row-major
+// sparse product forms them.
+HD d3 sym3_apply(const double* __restrict__ diag, const double* __restrict__ off, size_t b, const d3& x) {
+    const double d0 = diag[3 * b], d1 = diag[3 * b + 1], d2 = diag[3 * b + 2];
+    if (!off)
+        return mk3(d0 * x.x, d1 * x.y, d2 * x.z);
+    const double xy = off[3 * b], xz = off[3 * b + 1], yz = off[3 * b + 2];
+    return mk3((d0 * x.x + xy * x.y) + xz * x.z, (xy * x.x + d1 * x.y) + yz * x.z, (xz * x.x + yz * x.y) + d2 * x.z);
+}
+
 HD d3 parent_to_local(const d3& p, const q4& q, const d3& rp) { return rotate_t(rp - p, q); }
 
 // columns of R(q): AMatU / AMatV / AMatW (real4.cpp:200-250)

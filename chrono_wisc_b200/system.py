@@ -104,6 +104,17 @@ class ChSystemMulticore:
         self.SetBodyState(first.value, pos, rot, vel, n)
         return first.value
 
+    def SetInertiaFull(self, first, inertia, inv_inertia=None):
+        """``ChBody::SetInertia`` with products of inertia (``use_full_inertia_tensor``, MC/ChSettings.h:107): n x 3 x 3
+        symmetric matrices in the body frame; the inverse defaults to numpy's (symmetrised)."""
+        J = _f64(inertia, (-1, 3, 3))
+        if inv_inertia is None:
+            K = np.linalg.inv(J)
+            K = np.ascontiguousarray(0.5 * (K + K.transpose(0, 2, 1)))
+        else:
+            K = _f64(inv_inertia, (-1, 3, 3))
+        check(self._lib.cb200_set_inertia_full(self._h, int(first), J.shape[0], _ptr(J), _ptr(K)))
+
     def SetBodyState(self, first, pos=None, rot=None, vel=None, n=None):
         """Gather of UpdateRigidBodies (ChSystemMulticore.cpp:329-377): host pose/velocity -> device."""
         arrs = [None if a is None else _f64(a) for a in (pos, rot, vel)]

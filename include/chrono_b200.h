@@ -127,10 +127,17 @@ int cb200_set_settings(cb200_system* sys, const cb200_settings* s);
 
 /* ChSystemMulticore::AddBody (MC/physics/ChSystemMulticore.cpp:205-226) for n bodies at once: mass, body-frame
  * inertia diagonal (ChBody::GetInertiaXX), the diagonal of ChBody::GetInvInertia() as Chrono computed it (NULL:
- * 1/inertia_xx is used) and flags.  Bodies with off-diagonal inertia are not supported yet.
+ * 1/inertia_xx is used) and flags.  Products of inertia: cb200_set_inertia_full.
  * Returns the index of the first new body in *first. */
 int cb200_append_bodies(cb200_system* sys, int n, const double* mass, const double* inertia_xx,
                         const double* inv_inertia_xx, const char* active, const char* collide, int* first);
+
+/* use_full_inertia_tensor (MC/ChSettings.h:107, the reference's default; consumed by ComputeInvMassMatrix,
+ * MC/solver/ChIterativeSolverMulticore.cpp:61-147, and by ChBody::ComputeGyro): inertia matrix and its inverse, both in
+ * the body frame, 9 doubles each (row-major, symmetric), for bodies first .. first+n-1 -- ChBody::GetInertia() and
+ * GetInvInertia().  Bodies never named here keep the principal moments of cb200_append_bodies.  Not combined with
+ * bilateral rows or slabs yet (CB200_ERR_UNSUPPORTED). */
+int cb200_set_inertia_full(cb200_system* sys, int first, int n, const double* inertia9, const double* inv_inertia9);
 
 /* ChCollisionSystemMulticore::Add (CMC/ChCollisionSystemMulticore.cpp:86-187): append n shapes as shape_container
  * slices.  dims is 4 doubles per shape: sphere (r,-,-,-); ellipsoid/box/cylinder/cylshell/cone (B.x,B.y,B.z,-);
