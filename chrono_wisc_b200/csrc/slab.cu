@@ -58,57 +58,122 @@ __device__ __forceinline__ void slab_write_meta(const SlabArrays& A, uint32_t b,
     A.meta[s] = m;
 }
 
+// Both directions fetch the whole record into registers before the first store: with a store after every load the
+// in-order issue waits for each load in turn (the arrays may alias as far as the compiler knows), 33 round trips in a row
+// for the one or two flagged slots of a CTA -- which was most of the duration of the pack and unpack kernels.
 __device__ __forceinline__ void slab_write_record(const SlabArrays& A, uint32_t b, double* __restrict__ r) {
     const uint32_t s = A.ns_static + (b - A.nb_static);
-    r[0] = (double)A.gid[b];
+    double v[SLAB_REC];
+    v[0] = (double)A.gid[b];
+#pragma unroll
     for (int k = 0; k < 3; k++)
-        r[1 + k] = A.pos[3 * (size_t)b + k];
+        v[1 + k] = A.pos[3 * (size_t)b + k];
+#pragma unroll
     for (int k = 0; k < 4; k++)
-        r[4 + k] = A.rot[4 * (size_t)b + k];
+        v[4 + k] = A.rot[4 * (size_t)b + k];
+#pragma unroll
     for (int k = 0; k < 6; k++)
-        r[8 + k] = A.vel[6 * (size_t)b + k];
-    r[14] = A.mass[b];
+        v[8 + k] = A.vel[6 * (size_t)b + k];
+    v[14] = A.mass[b];
+#pragma unroll
     for (int k = 0; k < 3; k++) {
-        r[15 + k] = A.inertia[3 * (size_t)b + k];
-        r[18 + k] = A.inv_inertia[3 * (size_t)b + k];
-        r[25 + k] = A.s_lpos[3 * (size_t)s + k];
+        v[15 + k] = A.inertia[3 * (size_t)b + k];
+        v[18 + k] = A.inv_inertia[3 * (size_t)b + k];
+        v[25 + k] = A.s_lpos[3 * (size_t)s + k];
     }
+#pragma unroll
     for (int k = 0; k < 4; k++) {
-        r[21 + k] = A.s_dims[4 * (size_t)s + k];
-        r[28 + k] = A.s_lrot[4 * (size_t)s + k];
+        v[21 + k] = A.s_dims[4 * (size_t)s + k];
+        v[28 + k] = A.s_lrot[4 * (size_t)s + k];
     }
     const unsigned long long bits = ((unsigned long long)A.s_type[s] & 0xffull) |
                                     (((unsigned long long)A.s_mat[s] & 0xffffull) << 8) |
                                     ((unsigned long long)A.s_fam[s] << 32);
-    r[32] = __longlong_as_double((long long)bits);
+    v[32] = __longlong_as_double((long long)bits);
+#pragma unroll
+    for (int k = 0; k < SLAB_REC; k++)
+        r[k] = v[k];
+}
+
+// The same record written by a whole warp: lane k fetches word k (ten short divergent paths, every load in flight at
+// once, no record held in registers) -- the pack kernel keeps the occupancy its 5000 CTAs need.
+__device__ __forceinline__ void slab_write_record_warp(const SlabArrays& A, uint32_t b, double* __restrict__ r,
+                                                       int lane) {
+    const size_t s = A.ns_static + (b - A.nb_static);
+    double v;
+    if (lane == 0)
+        v = (double)A.gid[b];
+    else if (lane < 4)
+        v = A.pos[3 * (size_t)b + (lane - 1)];
+    else if (lane < 8)
+        v = A.rot[4 * (size_t)b + (lane - 4)];
+    else if (lane < 14)
+        v = A.vel[6 * (size_t)b + (lane - 8)];
+    else if (lane == 14)
+        v = A.mass[b];
+    else if (lane < 18)
+        v = A.inertia[3 * (size_t)b + (lane - 15)];
+    else if (lane < 21)
+        v = A.inv_inertia[3 * (size_t)b + (lane - 18)];
+    else if (lane < 25)
+        v = A.s_dims[4 * s + (lane - 21)];
+    else if (lane < 28)
+        v = A.s_lpos[3 * s + (lane - 25)];
+    else
+        v = A.s_lrot[4 * s + (lane - 28)];
+    r[lane] = v;
+    if (lane == 0) {
+        const unsigned long long bits = ((unsigned long long)A.s_type[s] & 0xffull) |
+                                        (((unsigned long long)A.s_mat[s] & 0xffffull) << 8) |
+                                        ((unsigned long long)A.s_fam[s] << 32);
+        r[32] = __longlong_as_double((long long)bits);
+    }
 }
 
 __device__ __forceinline__ void slab_read_record(const SlabArrays& A, uint32_t b, const double* __restrict__ r,
                                                  uint8_t flags) {
     const uint32_t s = A.ns_static + (b - A.nb_static);
-    A.gid[b] = (int64_t)r[0];
+    double v[SLAB_REC];
+#pragma unroll
+    for (int k = 0; k < SLAB_REC; k++)
+        v[k] = r[k];
+    A.gid[b] = (int64_t)v[0];
+#pragma unroll
     for (int k = 0; k < 3; k++)
-        A.pos[3 * (size_t)b + k] = r[1 + k];
+        A.pos[3 * (size_t)b + k] = v[1 + k];
+#pragma unroll
     for (int k = 0; k < 4; k++)
-        A.rot[4 * (size_t)b + k] = r[4 + k];
+        A.rot[4 * (size_t)b + k] = v[4 + k];
+#pragma unroll
     for (int k = 0; k < 6; k++)
-        A.vel[6 * (size_t)b + k] = r[8 + k];
-    A.mass[b] = r[14];
+        A.vel[6 * (size_t)b + k] = v[8 + k];
+    A.mass[b] = v[14];
+#pragma unroll
     for (int k = 0; k < 3; k++) {
-        A.inertia[3 * (size_t)b + k] = r[15 + k];
-        A.inv_inertia[3 * (size_t)b + k] = r[18 + k];
-        A.s_lpos[3 * (size_t)s + k] = r[25 + k];
+        A.inertia[3 * (size_t)b + k] = v[15 + k];
+        A.inv_inertia[3 * (size_t)b + k] = v[18 + k];
+        A.s_lpos[3 * (size_t)s + k] = v[25 + k];
     }
+#pragma unroll
     for (int k = 0; k < 4; k++) {
-        A.s_dims[4 * (size_t)s + k] = r[21 + k];
-        A.s_lrot[4 * (size_t)s + k] = r[28 + k];
+        A.s_dims[4 * (size_t)s + k] = v[21 + k];
+        A.s_lrot[4 * (size_t)s + k] = v[28 + k];
     }
-    const unsigned long long bits = (unsigned long long)__double_as_longlong(r[32]);
-    A.s_type[s] = (int32_t)(bits & 0xff);
-    A.s_mat[s] = (int32_t)((bits >> 8) & 0xffff);
-    A.s_fam[s] = (uint32_t)(bits >> 32);
+    const unsigned long long bits = (unsigned long long)__double_as_longlong(v[32]);
+    const uint32_t type = (uint32_t)(bits & 0xff), mat = (uint32_t)((bits >> 8) & 0xffff), fam = (uint32_t)(bits >> 32);
+    A.s_type[s] = (int32_t)type;
+    A.s_mat[s] = (int32_t)mat;
+    A.s_fam[s] = fam;
     A.bflags[b] = flags;
-    slab_write_meta(A, b, flags);
+    // (slab_write_meta without reading back what was just stored)
+    ShapeMeta m;
+    m.body = (flags & 4u) ? UINT_MAX : b;
+    m.fam = fam;
+    m.pad = 0;
+    m.info = type << 8 | mat << 16 | (flags & 3u);
+    if (type == CB200_SPHERE && v[25] == 0 && v[26] == 0 && v[27] == 0)
+        m.info |= 4u;
+    A.meta[s] = m;
 }
 
 struct SlabGeom {
@@ -231,13 +296,22 @@ __global__ void __launch_bounds__(SLAB_CTA) k_slab_pack(SlabGeom G, SlabArrays A
     const uint32_t f = s < G.owned_cap ? flags[s] : 0u;
     uint32_t rank[3];
     slab_ranks(f, cta_off, wtot, rank);
+    const uint32_t b = A.nb_static + s;
+    {
+        // the records of the warp's flagged slots, one after the other, each by all 32 lanes
+        const int lane = threadIdx.x & 31;
+        for (int side = 0; side < 2; side++) {
+            double* buf = side ? send_right : send_left;
+            for (unsigned m = __ballot_sync(0xffffffffu, f & (side ? SLAB_F_RIGHT : SLAB_F_LEFT)); m; m &= m - 1u) {
+                const int src = __ffs((int)m) - 1;
+                const uint32_t bs = __shfl_sync(0xffffffffu, b, src);
+                const uint32_t rk = __shfl_sync(0xffffffffu, rank[side], src);
+                slab_write_record_warp(A, bs, buf + SLAB_HDR + (size_t)SLAB_REC * rk, lane);
+            }
+        }
+    }
     if (s >= G.owned_cap)
         return;
-    const uint32_t b = A.nb_static + s;
-    if (f & SLAB_F_LEFT)
-        slab_write_record(A, b, send_left + SLAB_HDR + (size_t)SLAB_REC * rank[0]);
-    if (f & SLAB_F_RIGHT)
-        slab_write_record(A, b, send_right + SLAB_HDR + (size_t)SLAB_REC * rank[1]);
     if (f & SLAB_F_VACANT) {
         if (A.bflags[b] != 4) {
             A.bflags[b] = 4;
@@ -265,7 +339,7 @@ __device__ __forceinline__ bool slab_is_arrival(const SlabGeom& G, const double*
 }
 
 // blockIdx.y = side (0: the left neighbour's buffer, unpacked "first": its arrivals take the first vacant slots).
-__global__ void __launch_bounds__(1024) k_slab_unpack(SlabGeom G, SlabArrays A, const double* __restrict__ recv_left,
+__global__ void __launch_bounds__(512) k_slab_unpack(SlabGeom G, SlabArrays A, const double* __restrict__ recv_left,
                                                       const double* __restrict__ recv_right, uint32_t ghost_base_left,
                                                       const uint32_t* __restrict__ vacant, uint32_t* __restrict__ scnt,
                                                       DevCounters* __restrict__ cnt) {
@@ -509,9 +583,9 @@ int cb200_slab_unpack_dev(cb200_system* sys, const void* recv_left_dev, const vo
     const SlabGeom G = slab_geom(S);
     const SlabArrays A = slab_arrays(S);
     const uint32_t gl = S->slab_nb_static + G.owned_cap, gr = gl + G.ghost_cap;
-    const uint32_t ug = (G.ghost_cap + 1023u) / 1024u;
+    const uint32_t ug = (G.ghost_cap + 511u) / 512u;  // (512 threads: room for a whole record in registers)
     (void)gr;
-    k_slab_unpack<<<dim3(ug, 2), 1024, 0, S->stream>>>(G, A, S->slab_has_left ? (const double*)recv_left_dev : nullptr,
+    k_slab_unpack<<<dim3(ug, 2), 512, 0, S->stream>>>(G, A, S->slab_has_left ? (const double*)recv_left_dev : nullptr,
                                                        S->slab_has_right ? (const double*)recv_right_dev : nullptr, gl,
                                                        S->slab_vacant.p, S->slab_cnt, S->d_cnt);
     S->launches++;
