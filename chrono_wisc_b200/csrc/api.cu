@@ -114,6 +114,7 @@ static int alloc_entries(System* S, uint32_t n) {
     CB_TRY(S->ent_bin.reserve(n));
     CB_TRY(S->ent_shape.reserve(n));
     CB_TRY(S->ent_mask.reserve(n));
+    CB_TRY(S->ent_mask_hi.reserve(n));
     S->cap_entries = (uint32_t)S->ent_tmp.cap;
     CB_TRY(S->ent_off.reserve((size_t)S->cap_entries + 4));
     CB_TRY(S->slow_bins.reserve((size_t)S->cap_entries + 4));
@@ -344,7 +345,7 @@ void cb200_destroy(cb200_system* sys) {
     REL(pos); REL(rot); REL(vel); REL(hf); REL(fapp); REL(mass); REL(inertia); REL(inv_inertia); REL(inertia_off); REL(inv_inertia_off); REL(bflags); REL(heavy); REL(b_sphere); REL(b_rad); REL(c_own); REL(vlim); REL(b_inbox); REL(report); REL(mat_ovr); REL(bil_ids); REL(bil_cq); REL(bil_b); REL(bil_R); REL(bil_gamma); REL(bil_N); REL(bil_vec); REL(bil_info);
     REL(s_type); REL(s_body); REL(s_fam); REL(s_mat); REL(s_lpos); REL(s_lrot); REL(s_dims); REL(general_ids); REL(s_verts); REL(sh_neigh); REL(sh_touch); REL(sh_disp); REL(sh_relvel); REL(sh_dur); REL(s_wpos); REL(s_wpos_alt); REL(s_wrot);
     REL(s_box); REL(s_meta); REL(mat_smc); REL(mat_nsc); REL(bin_intersections); REL(bin_start); REL(bin_cursor);
-    REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_mask); REL(ent_off); REL(slow_bins); REL(long_bins); REL(pair_q); REL(large_list); REL(pairs);
+    REL(ent_tmp); REL(ent_bin); REL(ent_shape); REL(ent_mask); REL(ent_mask_hi); REL(ent_off); REL(slow_bins); REL(long_bins); REL(pair_q); REL(large_list); REL(pairs);
     REL(c_norm); REL(c_pta); REL(c_ptb); REL(c_depth); REL(c_erad); REL(c_bids); REL(c_shapes); REL(c_mats);
     REL(ent_cmask); REL(ent_cbase); REL(cplx_rec); REL(cplx_n); REL(cplx_cls); REL(cplx_bb); REL(cplx_out); REL(c_src);
     REL(ct_force); REL(ct_torque); REL(b_deg); REL(b_cursor); REL(b_inc); REL(b_force); REL(heavy_list);

@@ -213,6 +213,7 @@ struct System {
     DevBuf<uint32_t> ent_bin;            // cap_entries  bin of every entry
     DevBuf<uint32_t> ent_shape;          // cap_entries  shape ids sorted inside a bin == bin_aabb_number (written by the pair kernels)
     DevBuf<uint64_t> ent_mask;           // cap_entries  bit j set: the entry pairs with the j-th entry of its bin
+    DevBuf<uint64_t> ent_mask_hi;        // cap_entries  bits 64..127 of the same, for bins of 65..128 entries (k_long_rows)
     DevBuf<uint32_t> ent_off;            // cap_entries+2 outputs per entry -> exclusive offsets
     DevBuf<uint32_t> slow_bins;          // cap_entries  first entries of the bins the warp-per-bin pair kernel takes
     DevBuf<uint32_t> long_bins;          // cap_entries / 64 + 1  ... of those with more than 64 entries

@@ -1159,6 +1159,7 @@ __global__ void __launch_bounds__(256) k_pair_store(const ShapeMeta* __restrict_
                                                     const uint32_t* __restrict__ ent_bin,
                                                     const uint64_t* __restrict__ bin_start, double envelope,
                                                     int algorithm, int mode, const uint64_t* __restrict__ ent_mask,
+                                                    const uint64_t* __restrict__ ent_mask_hi,
                                                     const uint32_t* __restrict__ ent_off, int64_t* __restrict__ out,
                                                     uint32_t cap, const uint64_t* __restrict__ ent_cmask,
                                                     const uint32_t* __restrict__ ent_cbase,
@@ -1246,7 +1247,24 @@ __global__ void __launch_bounds__(256) k_pair_store(const ShapeMeta* __restrict_
                 }
             }
         }
-        // rows of bins with more than 64 entries: k_pair_store_long
+        else if (!CPLX && k <= 128) {
+            // bins of 65..128 entries: k_long_rows<false> left 128-bit masks (no second walk over the pairs)
+            for (int half = 0; half < 2; half++) {
+                unsigned long long m = half ? ent_mask_hi[e] : ent_mask[e];
+                while (m) {
+                    const int j = __ffsll((long long)m) - 1 + 64 * half;
+                    m &= m - 1;
+                    const uint32_t idB = ent_shape[s + j];
+                    if (ids) {
+                        const ShapeMeta mB = meta[idB];
+                        reinterpret_cast<int2*>(c_bids)[o] = make_int2((int)mA.body, (int)mB.body);
+                        c_mats[o] = (mA.info >> 16) | (mB.info >> 16) << 16;
+                    }
+                    out[o++] = hiA | (int64_t)idB;
+                }
+            }
+        }
+        // rows of longer bins (and of all bins of more than 64 entries when complex pairs are in play): k_long_rows<true>
     }
 }
 
@@ -1258,6 +1276,12 @@ __global__ void __launch_bounds__(256) k_pair_store(const ShapeMeta* __restrict_
 //   k_long_store  the same walk again after the scan; a lane's slot = row offset + hits of the lanes before it, i.e.
 //                 the reference's (shape A, shape B) order
 // --------------------------------------------------------------------------------------------------------------
+// Bins in flight per launch of the three kernels.  A bed that has compacted for seconds holds thousands of bins of 65 - 80
+// entries at a bin edge of 2.5 diameters (not the handful of the first second): with 64 bins in flight these kernels
+// grew to a quarter of the step.  CTAs beyond the number of long bins leave at once.
+constexpr int LONG_GRID_Y = 592;
+constexpr int LONG_STAGE = 128;  // entries of a long bin kept in shared memory by k_long_rows (12 KB)
+
 __global__ void __launch_bounds__(256) k_long_sort(const uint32_t* __restrict__ ent_tmp, uint32_t* __restrict__ ent_shape,
                                                    const uint32_t* __restrict__ ent_bin,
                                                    const uint64_t* __restrict__ bin_start,
@@ -1281,13 +1305,17 @@ __global__ void __launch_bounds__(256) k_long_sort(const uint32_t* __restrict__ 
 
 // decision for the lane's partner j of row A, and the number of outputs it gives (contacts, or 1 in pair-list mode)
 template <bool CPLX>
-__device__ __forceinline__ int long_pair(const Rec& A, uint32_t idB, const GridParams& g, uint32_t bin, int mode,
+__device__ __forceinline__ int long_pair(const Rec& A, uint32_t idB, const Rec* staged, const GridParams& g,
+                                         uint32_t bin, int mode,
                                          double envelope, int algorithm, const ShapeMeta* __restrict__ meta,
                                          const double* __restrict__ s_wpos, const ShapeBox* __restrict__ s_box,
                                          const double* __restrict__ s_wrot, const double* __restrict__ s_dims,
                                          const CplxArgs& X, Contact* tmp, uint32_t& n, uint32_t& np, uint32_t& ncx) {
     Rec B;
-    load_rec(B, idB, meta, s_wpos, s_box, g.origin, envelope);
+    if (staged)
+        B = *staged;  // the bin's records sit in shared memory (k_long_rows)
+    else
+        load_rec(B, idB, meta, s_wpos, s_box, g.origin, envelope);
     const int dec = pair_decide<false>(A, B, g, bin, mode, 2 * envelope, algorithm, s_wrot, s_dims, np);
     n = dec == 1 ? 1u : 0u;
     if (dec == 2) {
@@ -1310,6 +1338,7 @@ __global__ void __launch_bounds__(128) k_long_rows(const ShapeMeta* __restrict__
                                                    const uint32_t* __restrict__ ent_bin,
                                                    const uint64_t* __restrict__ bin_start, double envelope,
                                                    int algorithm, int mode, uint64_t* __restrict__ ent_mask,
+                                                   uint64_t* __restrict__ ent_mask_hi,
                                                    uint64_t* __restrict__ ent_cmask, uint32_t* __restrict__ ent_cnt,
                                                    const uint32_t* __restrict__ ent_off, int64_t* __restrict__ out,
                                                    uint32_t cap, uint32_t* __restrict__ c_src,
@@ -1327,10 +1356,22 @@ __global__ void __launch_bounds__(128) k_long_rows(const ShapeMeta* __restrict__
     const int lane = threadIdx.x & 31;
     const uint32_t wpb = blockDim.x >> 5;
     uint32_t np = 0, ncx = 0;
+    // A bin of up to LONG_STAGE entries is fetched once per CTA into shared memory (a compacted bed has thousands of
+    // bins of 65 - 80 entries: a dependent gather per partner was most of these kernels); longer bins go through global.
+    __shared__ Rec srec[LONG_STAGE];
     for (uint32_t q = blockIdx.y; q < nl; q += gridDim.y) {
         const uint32_t s = long_bins[q];
         const uint32_t bin = ent_bin[s];
         const uint32_t k = (uint32_t)bin_start[bin + 1] - s;
+        const bool staged = k <= LONG_STAGE;
+        const bool masked = !CPLX && k <= 128;  // the count pass records 128-bit masks, k_pair_store writes the keys
+        if (STORE && masked)
+            continue;
+        __syncthreads();  // the previous bin's readers are done
+        if (staged)
+            for (uint32_t x = threadIdx.x; x < k; x += blockDim.x)
+                load_rec(srec[x], ent_shape[s + x], meta, s_wpos, s_box, g.origin, envelope);
+        __syncthreads();
         for (uint32_t i = blockIdx.x * wpb + (threadIdx.x >> 5); i < k; i += gridDim.x * wpb) {
             const uint32_t e = s + i;
             uint32_t o = 0;
@@ -1340,21 +1381,37 @@ __global__ void __launch_bounds__(128) k_long_rows(const ShapeMeta* __restrict__
                     continue;
             }
             Rec A;
-            load_rec(A, ent_shape[e], meta, s_wpos, s_box, g.origin, envelope);
+            if (staged)
+                A = srec[i];
+            else
+                load_rec(A, ent_shape[e], meta, s_wpos, s_box, g.origin, envelope);
             const int64_t hiA = (int64_t)A.id << 32;
             uint32_t hits = 0;
+            unsigned long long mlo = 0ull, mhi = 0ull;
             for (uint32_t j0 = i + 1; j0 < k; j0 += 32) {
                 const uint32_t j = j0 + lane;
                 Contact tmp[CPLX ? MAX_PAIR_CONTACTS : 1];
                 uint32_t n = 0, idB = 0;
                 int dec = 0;
                 if (j < k) {
-                    idB = ent_shape[s + j];
-                    dec = long_pair<CPLX>(A, idB, g, bin, mode, envelope, algorithm, meta, s_wpos, s_box, s_wrot, s_dims, X,
-                                          tmp, n, np, ncx);
+                    idB = staged ? srec[j].id : ent_shape[s + j];
+                    dec = long_pair<CPLX>(A, idB, staged ? &srec[j] : nullptr, g, bin, mode, envelope, algorithm, meta,
+                                          s_wpos, s_box, s_wrot, s_dims, X, tmp, n, np, ncx);
                 }
                 const uint32_t incl = warp_incl_scan_bp(n, lane);
                 hits += __shfl_sync(0xffffffffu, incl, 31);
+                if (!STORE && masked) {
+                    // partners j0 .. j0+31 of this trip as bits j0 .. j0+31 of the 128-bit mask
+                    const unsigned long long w = (unsigned long long)__ballot_sync(0xffffffffu, n != 0);
+                    const uint32_t sh = j0 & 63u;
+                    if (j0 < 64) {
+                        mlo |= w << sh;
+                        if (sh > 32)
+                            mhi |= w >> (64 - sh);
+                    } else {
+                        mhi |= w << sh;
+                    }
+                }
                 if (STORE && n) {
                     uint32_t p = o + incl - n;
                     const int64_t key = hiA | (int64_t)idB;
@@ -1393,7 +1450,9 @@ __global__ void __launch_bounds__(128) k_long_rows(const ShapeMeta* __restrict__
                     o += __shfl_sync(0xffffffffu, incl, 31);
             }
             if (!STORE && lane == 0) {
-                ent_mask[e] = 0ull;
+                ent_mask[e] = mlo;
+                if (masked)
+                    ent_mask_hi[e] = mhi;
                 ent_cnt[e] = hits;
                 if (CPLX)
                     ent_cmask[e] = 0ull;
@@ -1510,11 +1569,12 @@ static int enqueue_pair_pass_t(System* S, int mode, int64_t* out, uint32_t cap) 
     k_pair_masks_slow<CPLX><<<gs, 32 * SLOW_WARPS, 0, s_slow>>>(
         S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_tmp.p, S->ent_shape.p, S->ent_bin.p,
         S->bin_start.p, env, algorithm, mode, S->ent_mask.p, cmask, S->ent_off.p, S->slow_bins.p, X, S->d_cnt);
-    k_long_sort<<<64, 256, 0, s_long>>>(S->ent_tmp.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p, S->long_bins.p,
+    k_long_sort<<<LONG_GRID_Y, 256, 0, s_long>>>(S->ent_tmp.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p, S->long_bins.p,
                                         S->d_cnt);
-    k_long_rows<CPLX, false><<<dim3(8, 64), 128, 0, s_long>>>(
+    k_long_rows<CPLX, false><<<dim3(8, LONG_GRID_Y), 128, 0, s_long>>>(
         S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
-        env, algorithm, mode, S->ent_mask.p, cmask, S->ent_off.p, nullptr, nullptr, 0, nullptr, nullptr, nullptr,
+        env, algorithm, mode, S->ent_mask.p, S->ent_mask_hi.p, cmask, S->ent_off.p, nullptr, nullptr, 0, nullptr,
+        nullptr, nullptr,
         S->long_bins.p, X, S->d_cnt);
     CB_TRY(aux_join(S, 0));
     CB_TRY(aux_join(S, 1));
@@ -1550,13 +1610,14 @@ static int enqueue_pair_pass_t(System* S, int mode, int64_t* out, uint32_t cap) 
     CB_TRY(timer_start(S, "k_pair_store"));
     k_pair_store<CPLX><<<grid_for(S, S->cap_entries, 256), 256, 0, S->stream>>>(
         S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
-        env, algorithm, mode, S->ent_mask.p, S->ent_off.p, out, cap, cmask, CPLX ? S->ent_cbase.p : nullptr,
+        env, algorithm, mode, S->ent_mask.p, S->ent_mask_hi.p, S->ent_off.p, out, cap, cmask,
+        CPLX ? S->ent_cbase.p : nullptr,
         CPLX ? S->cplx_rec.p : nullptr, CPLX ? S->cplx_n.p : nullptr, CPLX ? S->c_src.p : nullptr, S->c_bids.p,
         S->c_mats.p, X, S->d_cnt);
     CB_TRY(timer_stop(S, "k_pair_store"));
-    k_long_rows<CPLX, true><<<dim3(8, 64), 128, 0, s_long>>>(
+    k_long_rows<CPLX, true><<<dim3(8, LONG_GRID_Y), 128, 0, s_long>>>(
         S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
-        env, algorithm, mode, nullptr, nullptr, nullptr, S->ent_off.p, out, cap, CPLX ? S->c_src.p : nullptr,
+        env, algorithm, mode, nullptr, nullptr, nullptr, nullptr, S->ent_off.p, out, cap, CPLX ? S->c_src.p : nullptr,
         S->c_bids.p, S->c_mats.p, S->long_bins.p, X, S->d_cnt);
     CB_TRY(aux_join(S, 1));
     S->launches += 2;

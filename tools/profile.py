@@ -9,7 +9,8 @@ from chrono_wisc_b200 import scenes
 nx, ny, nz, warm, steps = (int(a) for a in sys.argv[1:6])
 edge = float(sys.argv[6]) if len(sys.argv) > 6 else 2.0
 rt = ctypes.CDLL("libcudart.so.12")
-scene = scenes.settling_smc(nx, ny, nz, grid="bin_size", bin_edge=edge)
+sp = float(sys.argv[7]) if len(sys.argv) > 7 else 2.02
+scene = scenes.settling_smc(nx, ny, nz, grid="bin_size", bin_edge=edge, spacing_factor=sp)
 s = cw.load_scene(cw.ChSystemMulticoreSMC(), scene)
 s.DoSteps(warm)
 s.Synchronize()
