@@ -421,7 +421,11 @@ def run_b200(args):
     ke = kinetic_energy_per_particle(scene, v0)
 
     # ---- window 3: the settled bed, kinetic energy per particle below 1e-9 J -- or as close as
-    # --settle-max further steps bring it (untimed, a look at the energy every 500), then K' timed steps
+    # --settle-max further steps bring it (untimed, a look at the energy every 500), then K' timed steps.  With the
+    # OneStep tangential model at h = 1e-3 the criterion is out of reach for the reference's scheme as for this one:
+    # the translational energy falls to ~1e-5 J, the rotational one stays at ~4.6e-4 J (explicit friction at its Coulomb
+    # limit flips the spin of a loaded sphere every step).  What the window does show is the
+    # COMPACTED bed: a quarter more contacts and thousands of bins of more than 64 entries.
     settled = None
     if args.settle_max > 0:
         ke_s, more = ke, 0
@@ -450,7 +454,7 @@ def run_b200(args):
             "timed": {"steps": f"{2 * args.warmup + args.settle}..{2 * args.warmup + args.settle + args.steps}",
                       "ms_per_step": dev_ms, "N_c": counts.num_rigid_contacts, "ke_per_particle_J": ke,
                       "settled_by_SURVEY_8d_criterion": bool(ke < 1e-9)},
-            **({"settled": settled} if settled else {})},
+            **({"late": settled} if settled else {})},
         "stage_ms": stage_ms,
         "stage_ms_note": "stage and kernel timers are CUDA-event pairs of the directly enqueued (non-graph) steps only, "
                          "one per 64-step chunk; ms_per_step covers all K steps, graph replays included",
