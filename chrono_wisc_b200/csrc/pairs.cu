@@ -1398,11 +1398,12 @@ __global__ void __launch_bounds__(128) k_long_rows(const ShapeMeta* __restrict__
                     dec = long_pair<CPLX>(A, idB, staged ? &srec[j] : nullptr, g, bin, mode, envelope, algorithm, meta,
                                           s_wpos, s_box, s_wrot, s_dims, X, tmp, n, np, ncx);
                 }
-                const uint32_t incl = warp_incl_scan_bp(n, lane);
-                hits += __shfl_sync(0xffffffffu, incl, 31);
+                uint32_t incl = 0;
                 if (!STORE && masked) {
-                    // partners j0 .. j0+31 of this trip as bits j0 .. j0+31 of the 128-bit mask
+                    // (n is 0 or 1 here: one vote instead of a scan)  partners j0 .. j0+31 of this trip as bits
+                    // j0 .. j0+31 of the 128-bit mask
                     const unsigned long long w = (unsigned long long)__ballot_sync(0xffffffffu, n != 0);
+                    hits += (uint32_t)__popcll(w);
                     const uint32_t sh = j0 & 63u;
                     if (j0 < 64) {
                         mlo |= w << sh;
@@ -1411,6 +1412,9 @@ __global__ void __launch_bounds__(128) k_long_rows(const ShapeMeta* __restrict__
                     } else {
                         mhi |= w << sh;
                     }
+                } else {
+                    incl = warp_incl_scan_bp(n, lane);
+                    hits += __shfl_sync(0xffffffffu, incl, 31);
                 }
                 if (STORE && n) {
                     uint32_t p = o + incl - n;
@@ -1571,7 +1575,7 @@ static int enqueue_pair_pass_t(System* S, int mode, int64_t* out, uint32_t cap) 
         S->bin_start.p, env, algorithm, mode, S->ent_mask.p, cmask, S->ent_off.p, S->slow_bins.p, X, S->d_cnt);
     k_long_sort<<<LONG_GRID_Y, 256, 0, s_long>>>(S->ent_tmp.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p, S->long_bins.p,
                                         S->d_cnt);
-    k_long_rows<CPLX, false><<<dim3(8, LONG_GRID_Y), 128, 0, s_long>>>(
+    k_long_rows<CPLX, false><<<dim3(1, 8 * LONG_GRID_Y), 128, 0, s_long>>>(
         S->s_meta.p, S->s_wpos.p, S->s_box.p, S->s_wrot.p, S->s_dims.p, S->ent_shape.p, S->ent_bin.p, S->bin_start.p,
         env, algorithm, mode, S->ent_mask.p, S->ent_mask_hi.p, cmask, S->ent_off.p, nullptr, nullptr, 0, nullptr,
         nullptr, nullptr,
