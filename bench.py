@@ -656,7 +656,10 @@ def run_b200_slabs(args, rank, world, local, barrier):
                                                         bin_edge=args.bin_edge if args.bin_edge > 0 else 2.5,
                                                         spacing_factor=args.spacing, jitter_factor=0.005)
     spacing = args.spacing * 0.02
-    ghost_cap = int(2.5 * args.ny * args.nz * (width / spacing + 1)) + 1024
+    # records per exchange buffer: the band holds ny * nz * width / spacing bodies (4,900 at the default sizes, fewer
+    # than 5,500 once the bed has compacted); the buffers travel at capacity (the counts live on the device), so the
+    # head-room is paid on the link at every step: twice the expected count, not the five-fold of round 1
+    ghost_cap = int(2.0 * args.ny * args.nz * (width / spacing)) + 1024
     layout = slab.SlabLayout(world, rank, cuts, axis=0, width=width)
     n_owned0 = gids.size
     # the data plane (pack, NCCL send/recv, unpack) is enqueued by the library itself (csrc/comm.cu)
