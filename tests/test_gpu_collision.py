@@ -35,6 +35,11 @@ CASES = {
     "small_density": lambda: overlapping_bed(16, 16, 6),
     "fixed_10x10x1": lambda: overlapping_bed(24, 24, 4, grid="fixed", bins=(10, 10, 1)),
     "fixed_1x1x1": lambda: overlapping_bed(6, 6, 3, grid="fixed", bins=(1, 1, 1)),
+    # bins of 65..128 entries (128-bit masks left by k_long_rows, keys written by k_pair_store) and of more than 128
+    # (both walks by k_long_rows, records from global memory)
+    "fixed_2x2x1_long": lambda: overlapping_bed(12, 12, 3, grid="fixed", bins=(2, 2, 1)),
+    "fixed_1x1x1_longer": lambda: overlapping_bed(8, 8, 3, grid="fixed", bins=(1, 1, 1)),
+    "fixed_3x3x1_mixed": lambda: overlapping_bed(16, 16, 3, grid="fixed", bins=(3, 3, 1)),
     "mid_density": lambda: overlapping_bed(48, 48, 10),
     "no_contacts": lambda: scenes.settling_smc(8, 8, 3),
 }
