@@ -390,6 +390,8 @@ def run_b200(args):
     stage_ms = {n: sys_.GetTimer(n) * 1e3 for n in ("update", "collision_broad", "collision_narrow", "advance",
                                                    "integrate")}
     value = nb * args.steps / (dev_ms * 1e-3 * args.steps)
+    # per-kernel timers of THIS window (read before the e2e and late windows enqueue further timed steps)
+    kr, traffic_src = kernel_rooflines(sys_, nb, ns, counts, measured_peak_gbs()[0])
 
     # ---- e2e: same steps through the public API with HOST state: upload pose+velocity, step, download ----------
     n_e2e = max(1, min(args.steps, args.e2e_steps))
@@ -466,7 +468,6 @@ def run_b200(args):
                           "frac": achieved / peak, "peak_kind": peak_kind, "kernel": "whole step (all kernels)",
                           "algorithmic_bytes_per_step": bytes_step},
     }
-    kr, traffic_src = kernel_rooflines(sys_, nb, ns, counts, peak)
     line["kernels"] = kr
     line["kernels_traffic_source"] = traffic_src
     if kr:
