@@ -966,7 +966,7 @@ static int enqueue_one_step_(System* S) {
     CB_TRY(timer_stop(S, "collision"));
     CB_TRY(timer_start(S, "advance"));
     S->defer_vel_update = S->defer_update_forces = S->set.system_type == 1;  // SMC: done in k_integrate<true> / k_body_reduce<true>
-    S->fuse_aabb = !S->slab_on;  // back-to-back steps: this integration also prepares the next step's sphere boxes
+    S->fuse_aabb = !S->slab_on && !getenv("CB200_NO_FUSE_AABB");  // this integration also prepares the next step's sphere boxes
     int rc = S->set.system_type == 1 ? enqueue_smc(S) : enqueue_nsc(S);
     if (rc == CB200_OK) {
         CB_TRY(timer_stop(S, "advance"));
@@ -1026,7 +1026,7 @@ static int replay_or_enqueue_step(System* S) {
     // Single systems: the captured step relies on the previous step's integration for the spheres' records (and swaps
     // the double-buffered records), so it needs them valid and clean shape records.  Slab systems rebuild the shape
     // records every step (bodies come and go): their graph holds k_build_meta and k_aabb<false> and has no such needs.
-    const bool fused = !S->slab_on;
+    const bool fused = !S->slab_on && !getenv("CB200_NO_FUSE_AABB");
     if (S->direct_steps < 1 || (fused && (!S->sphere_aabb_valid || S->meta_dirty))) {
         S->direct_steps++;
         return enqueue_one_step(S);
